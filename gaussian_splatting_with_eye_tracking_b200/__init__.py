@@ -1,0 +1,29 @@
+"""B200-native differentiable Gaussian-splatting rasterizer (hot path of
+XinShuo-ph/gaussian_splatting_with_eye_tracking), behind the reference's own operator API.
+
+Layout
+------
+csrc/            hand-written sm_100a CUDA kernels + the extern "C" ABI (include/gsr_b200.h)
+_capi.py         ctypes binding of that ABI (loads libgsr_b200.so; raises if it cannot)
+_host.py         PyTorch host shim with the reference's `_C` call signatures
+rasterizer.py    GaussianRasterizationSettings / GaussianRasterizer / autograd functions (baseline + AMR)
+scenes.py        deterministic synthetic Gaussian clouds and cameras
+dist.py          data-parallel views (NCCL gradient all-reduce) and screen-tile-band split
+
+The drop-in packages `diff_gaussian_rasterization` and `diff_gaussian_rasterization_amr` at the repository root
+re-export this API under the reference's import names.
+"""
+from .rasterizer import (  # noqa: F401
+    GaussianRasterizationSettings,
+    GaussianRasterizerAMR,
+    GaussianRasterizerBaseline,
+    RasterizeGaussiansAMR,
+    RasterizeGaussiansBaseline,
+    rasterize_gaussians_amr,
+    rasterize_gaussians_baseline,
+)
+
+__all__ = [
+    "GaussianRasterizationSettings", "GaussianRasterizerBaseline", "GaussianRasterizerAMR",
+    "RasterizeGaussiansBaseline", "RasterizeGaussiansAMR", "rasterize_gaussians_baseline", "rasterize_gaussians_amr",
+]

@@ -1,0 +1,122 @@
+"""ctypes binding of include/gsr_b200.h.
+
+This module is the only place that touches the shared library.  It fails loudly: if libgsr_b200.so is missing and
+cannot be built, importing it raises -- there is no CPU or PyTorch fallback anywhere in the product path.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+from . import build as _build
+
+c_float_p = C.POINTER(C.c_float)
+c_int_p = C.POINTER(C.c_int)
+
+# status codes (gsr_b200.h)
+GSR_OK, GSR_ERR_INVALID, GSR_ERR_CUDA, GSR_ERR_ALLOC, GSR_ERR_WORKSPACE, GSR_ERR_SORT = range(6)
+GSR_BUF_GEOM, GSR_BUF_BINNING, GSR_BUF_IMAGE = range(3)
+GSR_MODE_BASELINE, GSR_MODE_AMR = 0, 1
+
+ALLOC_FN = C.CFUNCTYPE(C.c_void_p, C.c_void_p, C.c_int, C.c_size_t)
+
+
+class GsrScene(C.Structure):
+    _fields_ = [
+        ("P", C.c_int), ("sh_degree", C.c_int), ("sh_coeffs", C.c_int),
+        ("means3D", C.c_void_p), ("shs", C.c_void_p), ("colors_precomp", C.c_void_p), ("opacities", C.c_void_p),
+        ("scales", C.c_void_p), ("rotations", C.c_void_p), ("cov3D_precomp", C.c_void_p),
+        ("scale_modifier", C.c_float),
+    ]
+
+
+class GsrCamera(C.Structure):
+    _fields_ = [
+        ("width", C.c_int), ("height", C.c_int), ("tan_fovx", C.c_float), ("tan_fovy", C.c_float),
+        ("background", C.c_void_p), ("viewmatrix", C.c_void_p), ("projmatrix", C.c_void_p), ("cam_pos", C.c_void_p),
+        ("prefiltered", C.c_int),
+    ]
+
+
+class GsrGaze(C.Structure):
+    _fields_ = [("cx", C.c_float), ("cy", C.c_float), ("radii", C.c_float * 4)]
+
+
+class GsrGrads(C.Structure):
+    _fields_ = [(n, C.c_void_p) for n in (
+        "dL_dmeans2D", "dL_dcolors", "dL_dopacity", "dL_dmeans3D", "dL_dcov3D", "dL_dsh", "dL_dscales",
+        "dL_drotations", "dL_dconic", "scratch")]
+
+
+class GsrGeomView(C.Structure):
+    _fields_ = [("P", C.c_int)] + [(n, C.c_void_p) for n in (
+        "depths", "clamped", "radii", "means2D", "cov3D", "conic_opacity", "rgb", "tiles_touched", "block_offsets",
+        "num_rendered")]
+
+
+class GsrBinningView(C.Structure):
+    _fields_ = [("N", C.c_longlong)] + [(n, C.c_void_p) for n in (
+        "keys_unsorted", "values_unsorted", "keys_sorted", "point_list")]
+
+
+class GsrImageView(C.Structure):
+    _fields_ = [(n, C.c_int) for n in ("width", "height", "mode", "tiles_x", "tiles_y")] + [(n, C.c_void_p) for n in (
+        "accum_alpha", "n_contrib", "ranges", "n_intersections", "levels", "levels_last", "levels_current",
+        "thresholds")]
+
+
+# every symbol include/gsr_b200.h declares: name -> (restype, argtypes)
+SYMBOLS = {
+    "gsr_geom_bytes": (C.c_size_t, [C.c_int]),
+    "gsr_binning_bytes": (C.c_size_t, [C.c_longlong]),
+    "gsr_image_bytes": (C.c_size_t, [C.c_int, C.c_int, C.c_int]),
+    "gsr_forward": (C.c_int, [C.POINTER(GsrScene), C.POINTER(GsrCamera), ALLOC_FN, C.c_void_p, C.c_void_p, C.c_void_p,
+                              c_int_p, C.c_int, C.c_void_p]),
+    "gsr_backward": (C.c_int, [C.POINTER(GsrScene), C.POINTER(GsrCamera), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                               C.c_int, C.c_void_p, C.POINTER(GsrGrads), C.c_int, C.c_void_p]),
+    "gsr_mark_visible": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "gsr_amr_forward": (C.c_int, [C.POINTER(GsrScene), C.POINTER(GsrCamera), C.c_int, C.c_void_p, C.c_void_p, C.c_void_p,
+                                  C.c_void_p, C.c_int, C.POINTER(GsrGaze), ALLOC_FN, C.c_void_p, C.c_void_p, C.c_void_p,
+                                  c_int_p, C.c_int, C.c_void_p]),
+    "gsr_view_geom": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(GsrGeomView)]),
+    "gsr_view_binning": (C.c_int, [C.c_void_p, C.c_longlong, C.POINTER(GsrBinningView)]),
+    "gsr_view_image": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.POINTER(GsrImageView)]),
+    "gsr_sort_temp_bytes": (C.c_size_t, [C.c_longlong]),
+    "gsr_sort_pairs": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_longlong,
+                                 C.c_int, C.c_void_p, C.c_size_t, C.c_void_p]),
+    "gsr_higher_msb": (C.c_uint, [C.c_uint]),
+    "gsr_launch_count": (C.c_ulonglong, []),
+    "gsr_last_error": (C.c_char_p, []),
+    "gsr_version": (C.c_char_p, []),
+}
+
+
+def _load() -> C.CDLL:
+    path = _build.LIB_PATH
+    if not os.path.exists(path):
+        # first use in a fresh checkout: compile in-tree (needs nvcc); raises if that is impossible
+        _build.build()
+    lib = C.CDLL(path)
+    for name, (res, args) in SYMBOLS.items():
+        fn = getattr(lib, name)          # AttributeError here = header/library mismatch: fail loudly
+        fn.restype = res
+        fn.argtypes = args
+    return lib
+
+
+lib = _load()
+LIB_PATH = _build.LIB_PATH
+
+
+class GsrError(RuntimeError):
+    pass
+
+
+def check(rc: int, what: str) -> None:
+    if rc != GSR_OK:
+        msg = lib.gsr_last_error()
+        raise GsrError(f"{what} failed (status {rc}): {msg.decode() if msg else ''}")
+
+
+def launch_count() -> int:
+    return int(lib.gsr_launch_count())

@@ -1,0 +1,205 @@
+"""PyTorch host side of the `_C` operator surface.
+
+Mirrors, argument for argument, what the reference's pybind module exposes:
+
+* ``rasterize_gaussians``          <- RasterizeGaussiansCUDA          (rasterize_points.cu:35-115, 19 args -> 6-tuple)
+* ``rasterize_gaussians_backward`` <- RasterizeGaussiansBackwardCUDA  (rasterize_points.cu:117-196, 21 args -> 8-tuple)
+* ``mark_visible``                 <- markVisible                     (rasterize_points.cu:198-217)
+* ``rasterize_gaussians_amr``      <- AMR RasterizeGaussiansCUDA      (diff-gaussian-rasterization-amr/rasterize_points.cu:65-202, 25 args)
+
+PyTorch is plumbing only: it owns device memory (outputs and the three growable work buffers, handed to the
+library through an allocation callback -- the C analogue of ``resizeFunctional``), supplies the current stream,
+and wraps results as tensors.  All compute is in libgsr_b200.so.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from types import SimpleNamespace
+
+import torch
+
+from . import _capi
+from ._capi import GsrCamera, GsrGaze, GsrGrads, GsrScene, lib
+
+
+def _dev_tensor(t: torch.Tensor, name: str, dtype=torch.float32):
+    """Absent input (numel == 0, reference: empty CPU tensor -> null data pointer) -> None; else contiguous CUDA."""
+    if t is None or t.numel() == 0:
+        return None
+    if not t.is_cuda:
+        raise RuntimeError(f"{name} must be a CUDA tensor")
+    if t.dtype != dtype:
+        raise RuntimeError(f"{name} must have dtype {dtype}, got {t.dtype}")
+    return t.contiguous()
+
+
+def _p(t):
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+class _Arena:
+    """Receives the library's allocation requests and keeps the byte tensors (geom / binning / image)."""
+
+    def __init__(self, device):
+        self.device = device
+        self.bufs = {}
+        self.cb = _capi.ALLOC_FN(self._alloc)
+
+    def _alloc(self, _user, which, nbytes):
+        try:
+            t = torch.empty(int(nbytes), dtype=torch.uint8, device=self.device)
+        except Exception:  # out of memory etc.: report through the status code
+            return None
+        self.bufs[int(which)] = t
+        return t.data_ptr()
+
+    def get(self, which):
+        t = self.bufs.get(which)
+        return t if t is not None else torch.empty(0, dtype=torch.uint8, device=self.device)
+
+
+def _scene_camera(background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp, viewmatrix,
+                  projmatrix, tan_fovx, tan_fovy, image_height, image_width, sh, degree, campos, prefiltered):
+    if means3D.ndimension() != 2 or means3D.size(1) != 3:
+        raise RuntimeError("means3D must have dimensions (num_points, 3)")
+    P = int(means3D.size(0))
+    keep = SimpleNamespace()
+    keep.means3D = _dev_tensor(means3D, "means3D") if P else None
+    keep.colors = _dev_tensor(colors, "colors_precomp")
+    keep.opacity = _dev_tensor(opacity, "opacities")
+    keep.scales = _dev_tensor(scales, "scales")
+    keep.rotations = _dev_tensor(rotations, "rotations")
+    keep.cov3D = _dev_tensor(cov3D_precomp, "cov3D_precomp")
+    keep.sh = _dev_tensor(sh, "sh")
+    keep.bg = _dev_tensor(background, "bg")
+    keep.view = _dev_tensor(viewmatrix, "viewmatrix")
+    keep.proj = _dev_tensor(projmatrix, "projmatrix")
+    keep.campos = _dev_tensor(campos, "campos")
+    M = int(sh.size(1)) if (sh is not None and sh.dim() >= 2 and sh.size(0) != 0) else 0
+    sc = GsrScene(P=P, sh_degree=int(degree), sh_coeffs=M, means3D=_p(keep.means3D), shs=_p(keep.sh),
+                  colors_precomp=_p(keep.colors), opacities=_p(keep.opacity), scales=_p(keep.scales),
+                  rotations=_p(keep.rotations), cov3D_precomp=_p(keep.cov3D), scale_modifier=float(scale_modifier))
+    cam = GsrCamera(width=int(image_width), height=int(image_height), tan_fovx=float(tan_fovx), tan_fovy=float(tan_fovy),
+                    background=_p(keep.bg), viewmatrix=_p(keep.view), projmatrix=_p(keep.proj), cam_pos=_p(keep.campos),
+                    prefiltered=1 if prefiltered else 0)
+    return sc, cam, keep, P, M
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+# ----------------------------------------------------------------------------------------------------------------
+# baseline
+# ----------------------------------------------------------------------------------------------------------------
+def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp,
+                        viewmatrix, projmatrix, tan_fovx, tan_fovy, image_height, image_width, sh, degree, campos,
+                        prefiltered, debug):
+    sc, cam, keep, P, _ = _scene_camera(background, means3D, colors, opacity, scales, rotations, scale_modifier,
+                                        cov3D_precomp, viewmatrix, projmatrix, tan_fovx, tan_fovy, image_height,
+                                        image_width, sh, degree, campos, prefiltered)
+    dev = means3D.device if means3D.is_cuda else torch.device("cuda")
+    with torch.cuda.device(dev):
+        out_color = torch.empty((3, int(image_height), int(image_width)), dtype=torch.float32, device=dev)
+        radii = torch.empty((P,), dtype=torch.int32, device=dev)
+        arena = _Arena(dev)
+        rendered = C.c_int(0)
+        rc = lib.gsr_forward(C.byref(sc), C.byref(cam), arena.cb, None, _p(out_color), _p(radii) if P else None,
+                             C.byref(rendered), 1 if debug else 0, _stream())
+        _capi.check(rc, "gsr_forward")
+    return (int(rendered.value), out_color, radii, arena.get(_capi.GSR_BUF_GEOM), arena.get(_capi.GSR_BUF_BINNING),
+            arena.get(_capi.GSR_BUF_IMAGE))
+
+
+def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rotations, scale_modifier, cov3D_precomp,
+                                 viewmatrix, projmatrix, tan_fovx, tan_fovy, dL_dout_color, sh, degree, campos,
+                                 geomBuffer, R, binningBuffer, imageBuffer, debug):
+    H, W = int(dL_dout_color.size(1)), int(dL_dout_color.size(2))
+    sc, cam, keep, P, M = _scene_camera(background, means3D, colors, torch.empty(0), scales, rotations, scale_modifier,
+                                        cov3D_precomp, viewmatrix, projmatrix, tan_fovx, tan_fovy, H, W, sh, degree,
+                                        campos, False)
+    dev = means3D.device
+    f32 = dict(dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        dL_dmeans3D = torch.empty((P, 3), **f32)
+        dL_dmeans2D = torch.empty((P, 3), **f32)
+        dL_dcolors = torch.empty((P, 3), **f32)
+        dL_dconic = torch.empty((P, 2, 2), **f32)
+        dL_dopacity = torch.empty((P, 1), **f32)
+        dL_dcov3D = torch.empty((P, 6), **f32)
+        dL_dsh = torch.empty((P, M, 3), **f32)
+        dL_dscales = torch.empty((P, 3), **f32)
+        dL_drotations = torch.empty((P, 4), **f32)
+        if P != 0:
+            scratch = torch.empty((P, 12), **f32)
+            dpix = _dev_tensor(dL_dout_color, "dL_dout_color")
+            radii_t = _dev_tensor(radii, "radii", torch.int32)
+            grads = GsrGrads(dL_dmeans2D=_p(dL_dmeans2D), dL_dcolors=_p(dL_dcolors), dL_dopacity=_p(dL_dopacity),
+                             dL_dmeans3D=_p(dL_dmeans3D), dL_dcov3D=_p(dL_dcov3D), dL_dsh=_p(dL_dsh) if M else None,
+                             dL_dscales=_p(dL_dscales), dL_drotations=_p(dL_drotations), dL_dconic=_p(dL_dconic),
+                             scratch=_p(scratch))
+            rc = lib.gsr_backward(C.byref(sc), C.byref(cam), _p(radii_t), _p(geomBuffer.contiguous()),
+                                  _p(binningBuffer.contiguous()), _p(imageBuffer.contiguous()), int(R), _p(dpix),
+                                  C.byref(grads), 1 if debug else 0, _stream())
+            _capi.check(rc, "gsr_backward")
+    return (dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations)
+
+
+def mark_visible(means3D, viewmatrix, projmatrix):
+    P = int(means3D.size(0))
+    present = torch.empty((P,), dtype=torch.bool, device=means3D.device)
+    if P != 0:
+        m = _dev_tensor(means3D, "means3D")
+        v = _dev_tensor(viewmatrix, "viewmatrix")
+        pr = _dev_tensor(projmatrix, "projmatrix")
+        with torch.cuda.device(means3D.device):
+            rc = lib.gsr_mark_visible(P, _p(m), _p(v), _p(pr), _p(present), _stream())
+            _capi.check(rc, "gsr_mark_visible")
+    return present
+
+
+# ----------------------------------------------------------------------------------------------------------------
+# AMR / foveated
+# ----------------------------------------------------------------------------------------------------------------
+def rasterize_gaussians_amr(background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp,
+                            viewmatrix, projmatrix, tan_fovx, tan_fovy, image_height, image_width, sh, degree, campos,
+                            prefiltered, foveaStep, out_color_precomp, geomBuffer_precomp, binningBuffer_precomp,
+                            imageBuffer_precomp, interpolate_image, debug, gaze=None):
+    """``gaze`` = (cx, cy, (r1, r2, r3, r4)) enables the gaze-driven level cap (extension; None = reference)."""
+    sc, cam, keep, P, _ = _scene_camera(background, means3D, colors, opacity, scales, rotations, scale_modifier,
+                                        cov3D_precomp, viewmatrix, projmatrix, tan_fovx, tan_fovy, image_height,
+                                        image_width, sh, degree, campos, prefiltered)
+    dev = means3D.device if means3D.is_cuda else torch.device("cuda")
+    step = int(foveaStep)
+    gz = None
+    if gaze is not None:
+        gz = GsrGaze(cx=float(gaze[0]), cy=float(gaze[1]), radii=(C.c_float * 4)(*[float(r) for r in gaze[2]]))
+    with torch.cuda.device(dev):
+        out_color = torch.empty((3, int(image_height), int(image_width)), dtype=torch.float32, device=dev)
+        radii = torch.empty((P,), dtype=torch.int32, device=dev)
+        if step >= 1:
+            radii.zero_()          # steps >= 1 do not preprocess; the reference returns its zero-filled radii
+        arena = _Arena(dev)
+        rendered = C.c_int(0)
+        precomp = _dev_tensor(out_color_precomp, "out_color_precomp")
+        gp = geomBuffer_precomp if (geomBuffer_precomp is not None and geomBuffer_precomp.numel()) else None
+        bp = binningBuffer_precomp if (binningBuffer_precomp is not None and binningBuffer_precomp.numel()) else None
+        ip = imageBuffer_precomp if (imageBuffer_precomp is not None and imageBuffer_precomp.numel()) else None
+        rc = lib.gsr_amr_forward(C.byref(sc), C.byref(cam), step, _p(precomp), _p(gp), _p(bp), _p(ip),
+                                 1 if interpolate_image else 0, C.byref(gz) if gz is not None else None, arena.cb, None,
+                                 _p(out_color), _p(radii) if (P and step < 1) else None, C.byref(rendered),
+                                 1 if debug else 0, _stream())
+        _capi.check(rc, "gsr_amr_forward")
+    if step > 0:   # the returned buffers ARE the passed-in ones (A/rasterize_points.cu:182-191)
+        return int(rendered.value), out_color, radii, geomBuffer_precomp, binningBuffer_precomp, imageBuffer_precomp
+    return (int(rendered.value), out_color, radii, arena.get(_capi.GSR_BUF_GEOM), arena.get(_capi.GSR_BUF_BINNING),
+            arena.get(_capi.GSR_BUF_IMAGE))
+
+
+# `_C`-shaped namespaces, one per reference extension module
+C_baseline = SimpleNamespace(rasterize_gaussians=rasterize_gaussians,
+                             rasterize_gaussians_backward=rasterize_gaussians_backward,
+                             mark_visible=mark_visible)
+C_amr = SimpleNamespace(rasterize_gaussians=rasterize_gaussians_amr,
+                        rasterize_gaussians_backward=rasterize_gaussians_backward,
+                        mark_visible=mark_visible)

@@ -1,0 +1,331 @@
+// gsr_api.cu -- extern "C" entry points (include/gsr_b200.h): orchestration only, every kernel lives in
+// gsr_preprocess.cu / gsr_binning.cu / gsr_blend.cu.  Replaces CudaRasterizer::Rasterizer::{forward,backward,
+// markVisible} (cuda_rasterizer/rasterizer_impl.cu:141-153,198-434; AMR fork :296-694).
+#include "gsr_common.cuh"
+#include <atomic>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+
+namespace gsr {
+
+static thread_local char g_err[512] = "";
+static std::atomic<unsigned long long> g_launches{0};
+
+void count_launch(int n) { g_launches.fetch_add((unsigned long long)n, std::memory_order_relaxed); }
+
+void set_error(const char* fmt, ...) {
+    va_list ap; va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+int check_cuda(cudaError_t e, const char* what) {
+    if (e == cudaSuccess) return GSR_OK;
+    set_error("%s: %s", what, cudaGetErrorString(e));
+    return GSR_ERR_CUDA;
+}
+
+// launch-error check; with debug also synchronises (reference CHECK_CUDA, auxiliary.h:166-173)
+int check_last(const char* what, bool debug, cudaStream_t s) {
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess && debug) e = cudaStreamSynchronize(s);
+    return check_cuda(e, what);
+}
+
+static uint32_t* pinned_mailbox() {
+    static thread_local uint32_t* box = nullptr;
+    if (!box) { if (cudaHostAlloc((void**)&box, 64, cudaHostAllocDefault) != cudaSuccess) { box = nullptr; cudaGetLastError(); } }
+    return box;
+}
+
+static int read_u32(const uint32_t* dev, uint32_t* host, int count, cudaStream_t s) {
+    uint32_t* box = pinned_mailbox();
+    if (box) {
+        int rc = check_cuda(cudaMemcpyAsync(box, dev, sizeof(uint32_t) * count, cudaMemcpyDeviceToHost, s), "D2H header");
+        if (rc) return rc;
+        rc = check_cuda(cudaStreamSynchronize(s), "stream sync (header)");
+        if (rc) return rc;
+        memcpy(host, box, sizeof(uint32_t) * count);
+        return GSR_OK;
+    }
+    int rc = check_cuda(cudaMemcpyAsync(host, dev, sizeof(uint32_t) * count, cudaMemcpyDeviceToHost, s), "D2H header");
+    if (rc) return rc;
+    return check_cuda(cudaStreamSynchronize(s), "stream sync (header)");
+}
+
+static unsigned higher_msb(unsigned n) {   // reference getHigherMsb (rasterizer_impl.cu:35-50)
+    unsigned msb = sizeof(n) * 4, step = msb;
+    while (step > 1) { step /= 2; if (n >> msb) msb += step; else msb -= step; }
+    if (n >> msb) msb++;
+    return msb;
+}
+
+static int validate(const gsr_scene* sc, const gsr_camera* cam, bool forward = true) {
+    if (!sc || !cam) { set_error("null scene/camera"); return GSR_ERR_INVALID; }
+    if (sc->P < 0 || cam->width <= 0 || cam->height <= 0) { set_error("bad sizes P=%d W=%d H=%d", sc->P, cam->width, cam->height); return GSR_ERR_INVALID; }
+    if (sc->P > 0) {
+        if (!sc->means3D || (forward && !sc->opacities)) { set_error("means3D/opacities are required"); return GSR_ERR_INVALID; }
+        if (!sc->colors_precomp && !sc->shs) { set_error("provide SHs or precomputed colors"); return GSR_ERR_INVALID; }
+        if (!sc->cov3D_precomp && (!sc->scales || !sc->rotations)) { set_error("provide scale/rotation or precomputed 3D covariance"); return GSR_ERR_INVALID; }
+        if (!sc->colors_precomp && (sc->sh_degree < 0 || sc->sh_degree > 3 || sc->sh_coeffs < (sc->sh_degree + 1) * (sc->sh_degree + 1))) {
+            set_error("sh_degree=%d needs %d coefficients, got M=%d", sc->sh_degree, (sc->sh_degree + 1) * (sc->sh_degree + 1), sc->sh_coeffs);
+            return GSR_ERR_INVALID;
+        }
+    }
+    if (!cam->background || !cam->viewmatrix || !cam->projmatrix || !cam->cam_pos) { set_error("camera pointers are required"); return GSR_ERR_INVALID; }
+    return GSR_OK;
+}
+
+// preprocess .. tile ranges; shared by the baseline and AMR forward.  On success *N_out = num_rendered.
+static int build_lists(const gsr_scene* sc, const gsr_camera* cam, int mode, gsr_alloc_fn alloc, void* user,
+                       int* radii_user, void** geom_out, void** bin_out, void** img_out, int* N_out, bool debug, cudaStream_t s) {
+    const int P = sc->P, W = cam->width, H = cam->height;
+    const size_t gbytes = gsr_geom_bytes(P), ibytes = gsr_image_bytes(W, H, mode);
+    void* geom = alloc(user, GSR_BUF_GEOM, gbytes);
+    void* img = alloc(user, GSR_BUF_IMAGE, ibytes);
+    if (!geom || !img) { set_error("allocation callback returned NULL"); return GSR_ERR_ALLOC; }
+    GeomPtrs g = geom_ptrs(geom, P);
+    ImgPtrs im = img_ptrs(img, W, H, mode);
+    const int num_tiles = im.tiles_x * im.tiles_y;
+    int rc = check_cuda(cudaMemsetAsync(g.header, 0, sizeof(GeomHeader), s), "memset header");
+    if (rc) return rc;
+
+    PreprocessArgs a;
+    a.P = P; a.D = sc->sh_degree; a.M = sc->sh_coeffs;
+    a.means3D = sc->means3D; a.scales = sc->scales; a.rotations = sc->rotations; a.opacities = sc->opacities;
+    a.shs = sc->shs; a.cov3D_precomp = sc->cov3D_precomp; a.colors_precomp = sc->colors_precomp;
+    a.scale_modifier = sc->scale_modifier;
+    a.viewmatrix = cam->viewmatrix; a.projmatrix = cam->projmatrix; a.cam_pos = cam->cam_pos;
+    a.W = W; a.H = H; a.tan_fovx = cam->tan_fovx; a.tan_fovy = cam->tan_fovy;
+    a.focal_y = H / (2.0f * cam->tan_fovy);          // rasterizer_impl.cu:222-223
+    a.focal_x = W / (2.0f * cam->tan_fovx);
+    a.tile = im.tile; a.grid_x = im.tiles_x; a.grid_y = im.tiles_y;
+    a.radii = radii_user ? radii_user : g.radii;
+    a.prefiltered = cam->prefiltered != 0;
+    launch_preprocess(a, g, s);
+    if ((rc = check_last("preprocess", debug, s))) return rc;
+    launch_block_scan(g, P, s);
+    if ((rc = check_last("block scan", debug, s))) return rc;
+
+    // the one host round-trip of the forward (reference: rasterizer_impl.cu:281): the binning buffer is sized by N
+    uint32_t hdr[4];
+    if ((rc = read_u32(&g.header->magic, hdr, 4, s))) return rc;
+    if (hdr[3] & 0x100u) { set_error("a Gaussian was culled although prefiltered=true (reference would __trap)"); return GSR_ERR_INVALID; }
+    const long long N = hdr[2];
+    void* bin = alloc(user, GSR_BUF_BINNING, gsr_binning_bytes(N));
+    if (!bin) { set_error("allocation callback returned NULL (binning)"); return GSR_ERR_ALLOC; }
+    BinPtrs b = bin_ptrs(bin, N);
+
+    if (N > 0) {
+        const SortPlan plan = make_sort_plan(32 + (int)higher_msb((unsigned)num_tiles));
+        uint64_t* k_start = (plan.passes & 1) ? b.keysX : b.keysY;
+        uint32_t* v_start = (plan.passes & 1) ? b.valsX : b.valsY;
+        uint32_t* hist = sort_hist_ptr(b.sort_temp);
+        if ((rc = check_cuda(cudaMemsetAsync(hist, 0, sizeof(uint32_t) * kSortMaxPasses * kSortMaxRadix, s), "memset hist"))) return rc;
+        launch_duplicate(g, P, a.radii, im.tile, im.tiles_x, im.tiles_y, k_start, v_start, hist, plan, s);
+        if ((rc = check_last("duplicate keys", debug, s))) return rc;
+        rc = launch_onesweep(k_start, v_start, b.keysY, b.valsY, b.keysX, b.valsX, N, plan, b.sort_temp, b.sort_temp_bytes,
+                             /*hist_ready=*/true, &g.header->sort_error, s);
+        if (rc) return rc;
+        if ((rc = check_last("radix sort", debug, s))) return rc;
+    }
+    launch_tile_ranges(b.keysY, N, im.ranges, im.n_intersections, num_tiles, s);
+    if ((rc = check_last("tile ranges", debug, s))) return rc;
+    *geom_out = geom; *bin_out = bin; *img_out = img; *N_out = (int)N;
+    return GSR_OK;
+}
+
+}  // namespace gsr
+
+using namespace gsr;
+
+extern "C" {
+
+size_t gsr_geom_bytes(int P) { return GeomLayout(P > 0 ? P : 0).total + kAlign; }
+size_t gsr_binning_bytes(long long N) { return BinLayout(N).total + kAlign; }
+size_t gsr_image_bytes(int W, int H, int mode) { return ImgLayout(W, H, mode).total + kAlign; }
+size_t gsr_sort_temp_bytes(long long n) { return sort_temp_bytes(n) + kAlign; }
+unsigned gsr_higher_msb(unsigned n) { return higher_msb(n); }
+unsigned long long gsr_launch_count(void) { return g_launches.load(); }
+const char* gsr_last_error(void) { return g_err; }
+const char* gsr_version(void) { return "gsr_b200 0.1 (sm_100a)"; }
+
+int gsr_forward(const gsr_scene* sc, const gsr_camera* cam, gsr_alloc_fn alloc, void* user,
+                float* out_color, int* radii, int* num_rendered, int debug, void* stream) {
+    cudaStream_t s = (cudaStream_t)stream;
+    int rc = validate(sc, cam);
+    if (rc) return rc;
+    if (!alloc || !out_color || !num_rendered) { set_error("alloc/out_color/num_rendered are required"); return GSR_ERR_INVALID; }
+    *num_rendered = 0;
+    const int W = cam->width, H = cam->height;
+    if (sc->P == 0) {   // reference: nothing is launched, out_color keeps its zero fill (rasterize_points.cu:68,80)
+        return check_cuda(cudaMemsetAsync(out_color, 0, sizeof(float) * 3 * (size_t)W * H, s), "memset out_color");
+    }
+    void *geom, *bin, *img; int N = 0;
+    rc = build_lists(sc, cam, GSR_MODE_BASELINE, alloc, user, radii, &geom, &bin, &img, &N, debug != 0, s);
+    if (rc) return rc;
+    GeomPtrs g = geom_ptrs(geom, sc->P);
+    BinPtrs b = bin_ptrs(bin, N);
+    ImgPtrs im = img_ptrs(img, W, H, GSR_MODE_BASELINE);
+    BlendArgs ba;
+    ba.W = W; ba.H = H; ba.ranges = im.ranges; ba.point_list = b.valsY; ba.means2D = g.means2D;
+    ba.conic_opacity = g.conic_opacity; ba.colors = sc->colors_precomp ? sc->colors_precomp : g.rgb;
+    ba.bg = cam->background; ba.final_T = im.accum_alpha; ba.n_contrib = im.n_contrib; ba.out_color = out_color;
+    launch_blend_forward(ba, s);
+    if ((rc = check_last("blend forward", debug != 0, s))) return rc;
+    *num_rendered = N;
+    return GSR_OK;
+}
+
+int gsr_backward(const gsr_scene* sc, const gsr_camera* cam, const int* radii, const void* geom_buffer,
+                 const void* binning_buffer, const void* image_buffer, int num_rendered, const float* dL_dpix,
+                 const gsr_grads* gr, int debug, void* stream) {
+    cudaStream_t s = (cudaStream_t)stream;
+    int rc = validate(sc, cam, /*forward=*/false);
+    if (rc) return rc;
+    if (!gr || !dL_dpix) { set_error("grads/dL_dpix are required"); return GSR_ERR_INVALID; }
+    const int P = sc->P, W = cam->width, H = cam->height;
+    if (P == 0) return GSR_OK;
+    if (!geom_buffer || !binning_buffer || !image_buffer) { set_error("work buffers are required"); return GSR_ERR_WORKSPACE; }
+    if (!gr->dL_dmeans2D || !gr->dL_dcolors || !gr->dL_dopacity || !gr->dL_dmeans3D || !gr->dL_dcov3D || !gr->dL_dscales ||
+        !gr->dL_drotations || !gr->scratch || (sc->sh_coeffs > 0 && sc->shs && !gr->dL_dsh)) {
+        set_error("gradient output pointers are required"); return GSR_ERR_INVALID;
+    }
+    if (((size_t)gr->scratch & 15) != 0) { set_error("scratch must be 16-byte aligned"); return GSR_ERR_INVALID; }
+    GeomPtrs g = geom_ptrs(geom_buffer, P);
+    BinPtrs b = bin_ptrs(binning_buffer, num_rendered);
+    ImgPtrs im = img_ptrs(image_buffer, W, H, GSR_MODE_BASELINE);
+    if (!radii) radii = g.radii;
+
+    if ((rc = check_cuda(cudaMemsetAsync(gr->scratch, 0, sizeof(float) * 12 * (size_t)P, s), "memset scratch"))) return rc;
+    BlendBwdArgs bb;
+    bb.W = W; bb.H = H; bb.ranges = im.ranges; bb.point_list = b.valsY; bb.means2D = g.means2D;
+    bb.conic_opacity = g.conic_opacity; bb.colors = sc->colors_precomp ? sc->colors_precomp : g.rgb;
+    bb.bg = cam->background; bb.final_T = im.accum_alpha; bb.n_contrib = im.n_contrib; bb.dL_dpix = dL_dpix;
+    bb.scratch = gr->scratch;
+    launch_blend_backward(bb, s);
+    if ((rc = check_last("blend backward", debug != 0, s))) return rc;
+
+    PreBwdArgs pb;
+    pb.P = P; pb.D = sc->sh_degree; pb.M = sc->sh_coeffs;
+    pb.means3D = sc->means3D; pb.scales = sc->scales; pb.rotations = sc->rotations; pb.shs = sc->shs;
+    pb.cov3D = sc->cov3D_precomp ? sc->cov3D_precomp : g.cov3D;
+    pb.cov_from_scales = (sc->cov3D_precomp == nullptr) && sc->scales && sc->rotations;   // backward.cu:394 `if (scales)`
+    pb.colors_from_sh = (sc->shs != nullptr) && (sc->colors_precomp == nullptr);          // backward.cu:390 `if (shs)`
+    pb.scale_modifier = sc->scale_modifier;
+    pb.viewmatrix = cam->viewmatrix; pb.projmatrix = cam->projmatrix; pb.cam_pos = cam->cam_pos;
+    pb.focal_y = H / (2.0f * cam->tan_fovy); pb.focal_x = W / (2.0f * cam->tan_fovx);
+    pb.tan_fovx = cam->tan_fovx; pb.tan_fovy = cam->tan_fovy;
+    pb.radii = radii; pb.clamped = g.clamped; pb.scratch = gr->scratch; pb.out = *gr;
+    if (sc->sh_coeffs == 0) pb.out.dL_dsh = nullptr;
+    launch_preprocess_backward(pb, s);
+    return check_last("preprocess backward", debug != 0, s);
+}
+
+int gsr_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix,
+                     unsigned char* present, void* stream) {
+    if (P < 0 || (P > 0 && (!means3D || !viewmatrix || !present))) { set_error("mark_visible: bad arguments"); return GSR_ERR_INVALID; }
+    launch_mark_visible(P, means3D, viewmatrix, projmatrix, present, (cudaStream_t)stream);
+    return check_last("mark_visible", false, (cudaStream_t)stream);
+}
+
+int gsr_amr_forward(const gsr_scene* sc, const gsr_camera* cam, int fovea_step, const float* out_color_precomp,
+                    void* geom_precomp, void* binning_precomp, void* image_precomp, int interpolate_image,
+                    const gsr_gaze* gaze, gsr_alloc_fn alloc, void* user, float* out_color, int* radii,
+                    int* num_rendered, int debug, void* stream) {
+    cudaStream_t s = (cudaStream_t)stream;
+    int rc = validate(sc, cam);
+    if (rc) return rc;
+    if (!out_color || !num_rendered) { set_error("out_color/num_rendered are required"); return GSR_ERR_INVALID; }
+    *num_rendered = 0;
+    const int P = sc->P, W = cam->width, H = cam->height;
+    // the AMR kernels write only the lattice pixels they render: everything else must read 0
+    // (reference: out_color = torch::full(0), A/rasterize_points.cu:116)
+    if ((rc = check_cuda(cudaMemsetAsync(out_color, 0, sizeof(float) * 3 * (size_t)W * H, s), "memset out_color"))) return rc;
+    if (P == 0) return GSR_OK;
+
+    void *geom = geom_precomp, *bin = binning_precomp, *img = image_precomp;
+    int N = 0;
+    if (fovea_step >= 1) {
+        // progressive round k: everything was built by step 0 (A/rasterizer_impl.cu:334-462)
+        if (!geom || !bin || !img) { set_error("fovea_step >= 1 needs the buffers built by step 0"); return GSR_ERR_WORKSPACE; }
+        GeomPtrs g0 = geom_ptrs(geom, P);
+        uint32_t hdr[4];
+        if ((rc = read_u32(&g0.header->magic, hdr, 4, s))) return rc;
+        if (hdr[0] != kGeomMagic || hdr[1] != (uint32_t)P) { set_error("geometry buffer does not belong to this scene (magic %08x, P %u)", hdr[0], hdr[1]); return GSR_ERR_WORKSPACE; }
+        N = (int)hdr[2];
+    } else {
+        if (!alloc) { set_error("alloc callback is required"); return GSR_ERR_INVALID; }
+        rc = build_lists(sc, cam, GSR_MODE_AMR, alloc, user, radii, &geom, &bin, &img, &N, debug != 0, s);
+        if (rc) return rc;
+    }
+    GeomPtrs g = geom_ptrs(geom, P);
+    BinPtrs b = bin_ptrs(bin, N);
+    ImgPtrs im = img_ptrs(img, W, H, GSR_MODE_AMR);
+    const int num_tiles = im.tiles_x * im.tiles_y;
+    *num_rendered = N;
+
+    if (fovea_step < 1) {
+        launch_amr_levels(im, num_tiles, s);
+        if ((rc = check_last("amr levels", debug != 0, s))) return rc;
+        if (fovea_step == 0) return GSR_OK;             // step 0: build only (A/rasterizer_impl.cu:650-653)
+    }
+    launch_fovea_levels(im, num_tiles, fovea_step, gaze, s);
+    if ((rc = check_last("fovea levels", debug != 0, s))) return rc;
+
+    AmrBlendArgs ab;
+    ab.b.W = W; ab.b.H = H; ab.b.ranges = im.ranges; ab.b.point_list = b.valsY; ab.b.means2D = g.means2D;
+    ab.b.conic_opacity = g.conic_opacity; ab.b.colors = sc->colors_precomp ? sc->colors_precomp : g.rgb;
+    ab.b.bg = cam->background; ab.b.final_T = im.accum_alpha; ab.b.n_contrib = im.n_contrib; ab.b.out_color = out_color;
+    // reference: steps >= 1 render with tile_AMR_levels_current, single pass with tile_AMR_levels (:401 vs :667)
+    ab.levels = (fovea_step >= 1) ? im.levels_current : im.levels;
+    ab.levels_last = im.levels_last;
+    ab.fovea_step = fovea_step; ab.out_color_precomp = out_color_precomp; ab.interpolate = interpolate_image != 0;
+    launch_blend_amr(ab, s);
+    return check_last("blend amr", debug != 0, s);
+}
+
+int gsr_view_geom(const void* geom_buffer, int P, gsr_geom_view* out) {
+    if (!geom_buffer || !out || P < 0) { set_error("view_geom: bad arguments"); return GSR_ERR_INVALID; }
+    GeomPtrs g = geom_ptrs(geom_buffer, P);
+    out->P = P; out->depths = g.depths; out->clamped = g.clamped; out->radii = g.radii;
+    out->means2D = (const float*)g.means2D; out->cov3D = g.cov3D; out->conic_opacity = (const float*)g.conic_opacity;
+    out->rgb = g.rgb; out->tiles_touched = g.tiles_touched; out->block_offsets = g.block_offsets;
+    out->num_rendered = &g.header->num_rendered;
+    return GSR_OK;
+}
+
+int gsr_view_binning(const void* binning_buffer, long long N, gsr_binning_view* out) {
+    if (!binning_buffer || !out || N < 0) { set_error("view_binning: bad arguments"); return GSR_ERR_INVALID; }
+    BinPtrs b = bin_ptrs(binning_buffer, N);
+    out->N = N; out->keys_unsorted = nullptr; out->values_unsorted = nullptr;   // consumed by the ping-pong passes
+    out->keys_sorted = b.keysY; out->point_list = b.valsY;
+    return GSR_OK;
+}
+
+int gsr_view_image(const void* image_buffer, int W, int H, int mode, gsr_image_view* out) {
+    if (!image_buffer || !out || W <= 0 || H <= 0) { set_error("view_image: bad arguments"); return GSR_ERR_INVALID; }
+    ImgPtrs im = img_ptrs(image_buffer, W, H, mode);
+    out->width = W; out->height = H; out->mode = mode; out->tiles_x = im.tiles_x; out->tiles_y = im.tiles_y;
+    out->accum_alpha = im.accum_alpha; out->n_contrib = im.n_contrib; out->ranges = (const uint32_t*)im.ranges;
+    out->n_intersections = im.n_intersections; out->levels = im.levels; out->levels_last = im.levels_last;
+    out->levels_current = im.levels_current; out->thresholds = im.thresholds;
+    return GSR_OK;
+}
+
+int gsr_sort_pairs(const uint64_t* keys_in, uint64_t* keys_out, const uint32_t* vals_in, uint32_t* vals_out,
+                   uint64_t* keys_tmp, uint32_t* vals_tmp, long long n, int end_bit, void* temp, size_t temp_bytes, void* stream) {
+    cudaStream_t s = (cudaStream_t)stream;
+    if (n < 0 || end_bit < 1 || end_bit > 64) { set_error("sort_pairs: bad n/end_bit"); return GSR_ERR_INVALID; }
+    if (n == 0) return GSR_OK;
+    if (!keys_in || !keys_out || !vals_in || !vals_out || !keys_tmp || !vals_tmp || !temp) { set_error("sort_pairs: null buffer"); return GSR_ERR_INVALID; }
+    const SortPlan plan = make_sort_plan(end_bit);
+    // the watchdog flag lives in the last word of the counters block
+    uint32_t* err = (uint32_t*)(aligned_base(temp) + align_up(sizeof(uint32_t) * kSortMaxPasses * kSortMaxRadix)) + 32;
+    int rc = launch_onesweep(keys_in, vals_in, keys_out, vals_out, keys_tmp, vals_tmp, n, plan, temp, temp_bytes, false, err, s);
+    if (rc) return rc;
+    return check_last("sort_pairs", false, s);
+}
+
+}  // extern "C"

@@ -1,0 +1,517 @@
+// gsr_blend.cu -- per-tile front-to-back alpha blending for sm_100a, forward / AMR-forward / backward.
+//
+//   blend_fwd_kernel   replaces renderCUDA<3> forward (cuda_rasterizer/forward.cu:261-374)
+//   blend_amr_kernel   replaces the AMR fork's renderCUDA<3> (A/cuda_rasterizer/forward.cu:261-518): ONE CTA per
+//                      32x32 binning tile walks the tile's list once and blends every active 2x2-lattice round
+//                      from the same staged batch (the reference launches 4 CTAs per tile that each re-stage it)
+//   interpolate_kernel replaces interpolateCUDA<3> (A/cuda_rasterizer/forward.cu:520-648)
+//   blend_bwd_kernel   replaces renderCUDA<3> backward (cuda_rasterizer/backward.cu:399-557): per-warp butterfly
+//                      reduction of the 9 per-Gaussian gradient terms, then ONE packed atomic set per
+//                      (warp, Gaussian) instead of 9 atomics per (pixel, Gaussian)
+//
+// Common structure: a batch of 256 list entries is gathered (id -> xy, conic, opacity, rgb) by the 256 threads of
+// the CTA, each loader thread runs an exact-preserving tile-level cull (a Gaussian whose best-case alpha over the
+// whole tile rectangle is below 1/255 can never pass the per-pixel test at forward.cu:343), survivors are
+// compacted into shared memory in list order together with their 1-based list position, and the next batch's
+// gathers are issued before the current batch is blended (register double buffering).  The per-pixel arithmetic
+// (power, expf, alpha, T test, accumulation order) is the reference's, operation for operation.
+#include "gsr_common.cuh"
+#include "gsr_math.cuh"
+
+namespace gsr {
+
+constexpr int kBlendThreads = 256;
+constexpr float kAlphaMin = 1.0f / 255.0f;
+
+struct GaussRec {        // what a loader thread holds for one list entry
+    float2 xy; float4 co; float3 col; uint32_t id;
+};
+
+// Exact-preserving cull: true  => for EVERY pixel centre in [x0,x1]x[y0,y1] the reference's per-pixel test yields
+// power > 0 or alpha < 1/255, so the entry cannot change any pixel (it only advances `contributor`).
+__device__ __forceinline__ bool cannot_touch(const float2 xy, const float4 co, float x0, float y0, float x1, float y1) {
+    const float a = co.x, b = co.y, c = co.z, o = co.w;
+    if (!(o >= kAlphaMin)) return true;                 // alpha = min(.99, o*exp(power<=0)) <= o
+    if (!(a > 0.f && c > 0.f && a * c - b * b > 0.f)) return false;   // not positive definite: do not reason about it
+    const float tau = __logf(255.0f * o) * 1.0001f + 0.02f;            // q > tau  <=>  o*exp(-q) < 1/255 (with margin)
+    const float cx = fminf(fmaxf(xy.x, x0), x1), cy = fminf(fmaxf(xy.y, y0), y1);
+    const float ex = xy.x - cx, ey = xy.y - cy;        // offset of the mean from the closest rect point
+    if (ex == 0.f && ey == 0.f) return false;           // mean inside the tile
+    // d = mean - pixel; over the rect d.x in [xy.x - x1, xy.x - x0], d.y likewise
+    const float dxlo = xy.x - x1, dxhi = xy.x - x0, dylo = xy.y - y1, dyhi = xy.y - y0;
+    float qmin = 3.0e38f;
+    if (ex != 0.f) {   // facing vertical edge: d.x fixed = ex, minimise over d.y
+        const float dy = fminf(fmaxf(-b * ex / c, dylo), dyhi);
+        const float t0 = 0.5f * a * ex * ex, t1 = 0.5f * c * dy * dy, t2 = b * ex * dy;
+        qmin = fminf(qmin, (t0 + t1 + t2) - 1e-5f * (t0 + t1 + fabsf(t2)));
+    }
+    if (ey != 0.f) {   // facing horizontal edge
+        const float dx = fminf(fmaxf(-b * ey / a, dxlo), dxhi);
+        const float t0 = 0.5f * a * dx * dx, t1 = 0.5f * c * ey * ey, t2 = b * dx * ey;
+        qmin = fminf(qmin, (t0 + t1 + t2) - 1e-5f * (t0 + t1 + fabsf(t2)));
+    }
+    return qmin > tau;
+}
+
+__device__ __forceinline__ GaussRec gather(const uint32_t* __restrict__ point_list, const float2* __restrict__ means2D,
+                                           const float4* __restrict__ conic_opacity, const float* __restrict__ colors, uint32_t li) {
+    GaussRec r;
+    r.id = __ldg(point_list + li);
+    r.xy = __ldg(means2D + r.id);
+    r.co = __ldg(conic_opacity + r.id);
+    r.col = make_float3(__ldg(colors + 3 * (size_t)r.id), __ldg(colors + 3 * (size_t)r.id + 1), __ldg(colors + 3 * (size_t)r.id + 2));
+    return r;
+}
+
+// CTA-wide stable compaction of `keep` flags; returns slot (or -1) and sets s_count.  Needs 8 warps.
+__device__ __forceinline__ int compact_slot(bool keep, uint32_t* s_wcnt, uint32_t* s_count) {
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const uint32_t m = __ballot_sync(0xffffffffu, keep);
+    if (lane == 0) s_wcnt[wid] = __popc(m);
+    __syncthreads();
+    uint32_t base = 0, tot = 0;
+#pragma unroll
+    for (int w = 0; w < kBlendThreads / 32; ++w) { const uint32_t c = s_wcnt[w]; base += (w < wid) ? c : 0u; tot += c; }
+    if (threadIdx.x == 0) *s_count = tot;
+    return keep ? (int)(base + __popc(m & ((1u << lane) - 1u))) : -1;
+}
+
+// ------------------------------------------------------------------------------------------------
+// forward, baseline 16x16 tiles
+// ------------------------------------------------------------------------------------------------
+struct FwdParams {
+    int W, H, tiles_x;
+    const uint2* __restrict__ ranges; const uint32_t* __restrict__ point_list;
+    const float2* __restrict__ means2D; const float4* __restrict__ conic_opacity; const float* __restrict__ colors;
+    const float* __restrict__ bg;
+    float* __restrict__ final_T; uint32_t* __restrict__ n_contrib; float* __restrict__ out_color;
+};
+
+__global__ void __launch_bounds__(kBlendThreads) blend_fwd_kernel(const FwdParams p) {
+    __shared__ float4 s_a[kBlendThreads];     // x, y, conic.x, conic.y
+    __shared__ float4 s_b[kBlendThreads];     // conic.z, opacity, r, g
+    __shared__ float2 s_c[kBlendThreads];     // b, list position (1-based, as float bits)
+    __shared__ uint32_t s_wcnt[kBlendThreads / 32];
+    __shared__ uint32_t s_count;
+
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    // warp = 8x4 pixel block (results do not depend on the thread->pixel map)
+    const uint32_t lx = (wid & 1) * 8 + (lane & 7), ly = (wid >> 1) * 4 + (lane >> 3);
+    const uint32_t pix_x = blockIdx.x * 16 + lx, pix_y = blockIdx.y * 16 + ly;
+    const bool inside = pix_x < (uint32_t)p.W && pix_y < (uint32_t)p.H;
+    const float pxf = (float)pix_x, pyf = (float)pix_y;
+    const float rx0 = (float)(blockIdx.x * 16), ry0 = (float)(blockIdx.y * 16);
+    const float rx1 = rx0 + 15.f, ry1 = ry0 + 15.f;
+
+    const uint2 range = p.ranges[blockIdx.y * p.tiles_x + blockIdx.x];
+    const int todo = (int)(range.y - range.x);
+    const int rounds = (todo + kBlendThreads - 1) / kBlendThreads;
+
+    float T = 1.0f, C0 = 0.f, C1 = 0.f, C2 = 0.f;
+    uint32_t last_contributor = 0;
+    bool done = !inside;
+
+    GaussRec nxt; bool nxt_valid = false;
+    if (tid < todo) { nxt = gather(p.point_list, p.means2D, p.conic_opacity, p.colors, range.x + tid); nxt_valid = true; }
+
+    for (int r = 0; r < rounds; ++r) {
+        // block vote doubles as the "everyone left the previous batch" barrier (forward.cu:309)
+        if (__syncthreads_count(done) == kBlendThreads) break;
+        const bool keep = nxt_valid && !cannot_touch(nxt.xy, nxt.co, rx0, ry0, rx1, ry1);
+        const int slot = compact_slot(keep, s_wcnt, &s_count);
+        if (slot >= 0) {
+            s_a[slot] = make_float4(nxt.xy.x, nxt.xy.y, nxt.co.x, nxt.co.y);
+            s_b[slot] = make_float4(nxt.co.z, nxt.co.w, nxt.col.x, nxt.col.y);
+            s_c[slot] = make_float2(nxt.col.z, __uint_as_float((uint32_t)(r * kBlendThreads + tid + 1)));
+        }
+        __syncthreads();
+        const int count = (int)s_count;
+        // issue the next batch's gathers; they complete while this batch is blended
+        const int nprog = (r + 1) * kBlendThreads + tid;
+        nxt_valid = nprog < todo;
+        if (nxt_valid) nxt = gather(p.point_list, p.means2D, p.conic_opacity, p.colors, range.x + nprog);
+
+        if (!__all_sync(0xffffffffu, done)) {
+            for (int j = 0; !done && j < count; ++j) {
+                const float4 A = s_a[j], B = s_b[j];
+                const float dx = __fadd_rn(A.x, -pxf), dy = __fadd_rn(A.y, -pyf);
+                const float power = blend_power(A.z, A.w, B.x, dx, dy);
+                if (power > 0.0f) continue;
+                const float alpha = fminf(0.99f, __fmul_rn(B.y, expf(power)));
+                if (alpha < kAlphaMin) continue;
+                const float test_T = __fmul_rn(T, __fadd_rn(1.f, -alpha));
+                if (test_T < 0.0001f) { done = true; continue; }
+                const float2 Cc = s_c[j];
+                C0 = __fmaf_rn(T, __fmul_rn(alpha, B.z), C0);
+                C1 = __fmaf_rn(T, __fmul_rn(alpha, B.w), C1);
+                C2 = __fmaf_rn(T, __fmul_rn(alpha, Cc.x), C2);
+                T = test_T;
+                last_contributor = __float_as_uint(Cc.y);
+            }
+        }
+    }
+    if (inside) {
+        const uint32_t pix_id = (uint32_t)p.W * pix_y + pix_x;
+        const size_t HW = (size_t)p.H * p.W;
+        p.final_T[pix_id] = T;
+        p.n_contrib[pix_id] = last_contributor;
+        p.out_color[pix_id] = __fmaf_rn(T, __ldg(p.bg), C0);
+        p.out_color[HW + pix_id] = __fmaf_rn(T, __ldg(p.bg + 1), C1);
+        p.out_color[2 * HW + pix_id] = __fmaf_rn(T, __ldg(p.bg + 2), C2);
+    }
+}
+
+void launch_blend_forward(const BlendArgs& a, cudaStream_t s) {
+    FwdParams p;
+    p.W = a.W; p.H = a.H; p.tiles_x = (a.W + 15) / 16;
+    p.ranges = a.ranges; p.point_list = a.point_list; p.means2D = a.means2D; p.conic_opacity = a.conic_opacity;
+    p.colors = a.colors; p.bg = a.bg; p.final_T = a.final_T; p.n_contrib = a.n_contrib; p.out_color = a.out_color;
+    dim3 grid((a.W + 15) / 16, (a.H + 15) / 16, 1);
+    blend_fwd_kernel<<<grid, kBlendThreads, 0, s>>>(p);
+    count_launch();
+}
+
+// ------------------------------------------------------------------------------------------------
+// forward, AMR: 32x32 binning tile, thread = one 2x2 quad, round k of the quad is pixel offset
+// (0,0),(1,1),(1,0),(0,1) for k = 1..4 (A/forward.cu:313-338).  Rounds blended: last < k <= min(level,4).
+// ------------------------------------------------------------------------------------------------
+struct AmrParams {
+    FwdParams f;
+    const uint32_t* __restrict__ levels; const uint32_t* __restrict__ levels_last;
+};
+
+__global__ void __launch_bounds__(kBlendThreads) blend_amr_kernel(const AmrParams q) {
+    const FwdParams& p = q.f;
+    __shared__ float4 s_a[kBlendThreads];
+    __shared__ float4 s_b[kBlendThreads];
+    __shared__ float2 s_c[kBlendThreads];
+    __shared__ uint32_t s_wcnt[kBlendThreads / 32];
+    __shared__ uint32_t s_count;
+
+    const int tile_id = blockIdx.y * p.tiles_x + blockIdx.x;
+    const uint32_t last = q.levels_last[tile_id];
+    uint32_t level = q.levels[tile_id];
+    if (level <= last) return;                  // A/forward.cu:285-288
+    if (level > 4u) level = 4u;                 // A/forward.cu:341-342
+    // active rounds: last < k <= level
+    const int k_lo = (int)last + 1, k_hi = (int)level;
+    if (k_lo > k_hi) return;
+
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const uint32_t qx = (wid & 1) * 8 + (lane & 7), qy = (wid >> 1) * 4 + (lane >> 3);   // quad coords 0..15
+    const uint32_t bx = blockIdx.x * 32 + 2 * qx, by = blockIdx.y * 32 + 2 * qy;
+    const float rx0 = (float)(blockIdx.x * 32), ry0 = (float)(blockIdx.y * 32);
+    const float rx1 = rx0 + 31.f, ry1 = ry0 + 31.f;
+
+    // per-round pixel state; index k-1
+    const int offx[4] = {0, 1, 1, 0}, offy[4] = {0, 1, 0, 1};
+    float T[4], Cr[4], Cg[4], Cb[4], pxf[4], pyf[4];
+    uint32_t lastc[4];
+    bool done[4], ins[4];
+    bool all_done = true;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const uint32_t px = bx + offx[k], py = by + offy[k];
+        const bool act = (k + 1 >= k_lo) && (k + 1 <= k_hi);
+        ins[k] = act && px < (uint32_t)p.W && py < (uint32_t)p.H;
+        done[k] = !ins[k];
+        all_done = all_done && done[k];
+        T[k] = 1.f; Cr[k] = Cg[k] = Cb[k] = 0.f; lastc[k] = 0;
+        pxf[k] = (float)px; pyf[k] = (float)py;
+    }
+
+    const uint2 range = p.ranges[tile_id];
+    const int todo = (int)(range.y - range.x);
+    const int rounds = (todo + kBlendThreads - 1) / kBlendThreads;
+
+    GaussRec nxt; bool nxt_valid = false;
+    if (tid < todo) { nxt = gather(p.point_list, p.means2D, p.conic_opacity, p.colors, range.x + tid); nxt_valid = true; }
+
+    for (int r = 0; r < rounds; ++r) {
+        if (__syncthreads_count(all_done) == kBlendThreads) break;
+        const bool keep = nxt_valid && !cannot_touch(nxt.xy, nxt.co, rx0, ry0, rx1, ry1);
+        const int slot = compact_slot(keep, s_wcnt, &s_count);
+        if (slot >= 0) {
+            s_a[slot] = make_float4(nxt.xy.x, nxt.xy.y, nxt.co.x, nxt.co.y);
+            s_b[slot] = make_float4(nxt.co.z, nxt.co.w, nxt.col.x, nxt.col.y);
+            s_c[slot] = make_float2(nxt.col.z, __uint_as_float((uint32_t)(r * kBlendThreads + tid + 1)));
+        }
+        __syncthreads();
+        const int count = (int)s_count;
+        const int nprog = (r + 1) * kBlendThreads + tid;
+        nxt_valid = nprog < todo;
+        if (nxt_valid) nxt = gather(p.point_list, p.means2D, p.conic_opacity, p.colors, range.x + nprog);
+
+        if (!__all_sync(0xffffffffu, all_done)) {
+            for (int j = 0; !all_done && j < count; ++j) {
+                const float4 A = s_a[j], B = s_b[j];
+                const float2 Cc = s_c[j];
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    if (done[k]) continue;
+                    const float dx = __fadd_rn(A.x, -pxf[k]), dy = __fadd_rn(A.y, -pyf[k]);
+                    const float power = blend_power(A.z, A.w, B.x, dx, dy);
+                    if (power > 0.0f) continue;
+                    const float alpha = fminf(0.99f, __fmul_rn(B.y, expf(power)));
+                    if (alpha < kAlphaMin) continue;
+                    const float test_T = __fmul_rn(T[k], __fadd_rn(1.f, -alpha));
+                    if (test_T < 0.0001f) { done[k] = true; continue; }
+                    Cr[k] = __fmaf_rn(T[k], __fmul_rn(alpha, B.z), Cr[k]);
+                    Cg[k] = __fmaf_rn(T[k], __fmul_rn(alpha, B.w), Cg[k]);
+                    Cb[k] = __fmaf_rn(T[k], __fmul_rn(alpha, Cc.x), Cb[k]);
+                    T[k] = test_T;
+                    lastc[k] = __float_as_uint(Cc.y);
+                }
+                all_done = done[0] && done[1] && done[2] && done[3];
+            }
+        }
+    }
+    const size_t HW = (size_t)p.H * p.W;
+    const float bg0 = __ldg(p.bg), bg1 = __ldg(p.bg + 1), bg2 = __ldg(p.bg + 2);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        if (!ins[k]) continue;
+        const uint32_t pix_id = (uint32_t)p.W * (by + offy[k]) + (bx + offx[k]);
+        p.final_T[pix_id] = T[k];
+        p.n_contrib[pix_id] = lastc[k];
+        p.out_color[pix_id] = __fmaf_rn(T[k], bg0, Cr[k]);
+        p.out_color[HW + pix_id] = __fmaf_rn(T[k], bg1, Cg[k]);
+        p.out_color[2 * HW + pix_id] = __fmaf_rn(T[k], bg2, Cb[k]);
+    }
+}
+
+// nearest-copy fill of the lattice pixels a tile's level does not render (A/forward.cu:520-648).
+// One thread per pixel.  Deterministic restatement: where the reference reads a pixel that another
+// CTA of the same launch is concurrently overwriting with out_color_precomp (level <= last in stepped
+// mode), the copied-in value is used.
+struct InterpParams {
+    int W, H, tiles_x, fovea_step;
+    const uint32_t* __restrict__ levels; const uint32_t* __restrict__ levels_last;
+    float* final_T; uint32_t* n_contrib; float* out_color; const float* out_color_precomp;
+};
+
+__global__ void __launch_bounds__(256) interpolate_kernel(const InterpParams p) {
+    const uint32_t x = blockIdx.x * 32 + (threadIdx.x & 31), y = blockIdx.y * 8 + (threadIdx.x >> 5);
+    if (x >= (uint32_t)p.W || y >= (uint32_t)p.H) return;
+    const int tile_id = (y / 32) * p.tiles_x + (x / 32);
+    const uint32_t ox = x & 1, oy = y & 1;
+    const int round = (ox == 0) ? (oy == 0 ? 1 : 4) : (oy == 0 ? 3 : 2);
+    uint32_t level = p.levels[tile_id];
+    if (level > 4u) level = 4u;
+    const size_t HW = (size_t)p.H * p.W;
+    const uint32_t pix = (uint32_t)p.W * y + x;
+    bool src_from_precomp = false;
+    if (p.fovea_step > 0) {
+        const int last = (int)p.levels_last[tile_id];
+        if ((int)level <= last) {
+            for (int ch = 0; ch < 3; ++ch) p.out_color[ch * HW + pix] = p.out_color_precomp[ch * HW + pix];
+            src_from_precomp = true;
+        }
+        if (round < last) {
+            for (int ch = 0; ch < 3; ++ch) p.out_color[ch * HW + pix] = p.out_color_precomp[ch * HW + pix];
+            return;
+        }
+    }
+    if ((uint32_t)round <= level) return;          // rendered accurately
+    const uint32_t sx = (x & ~1u) + (level >= 3u ? 1u : 0u), sy = (y & ~1u) + (level >= 3u ? 1u : 0u);
+    if (sx < (uint32_t)p.W && sy < (uint32_t)p.H) {
+        const uint32_t spix = (uint32_t)p.W * sy + sx;
+        p.final_T[pix] = p.final_T[spix];
+        p.n_contrib[pix] = p.n_contrib[spix];
+        const float* src = src_from_precomp ? p.out_color_precomp : p.out_color;
+        for (int ch = 0; ch < 3; ++ch) p.out_color[ch * HW + pix] = src[ch * HW + spix];
+    }
+}
+
+void launch_blend_amr(const AmrBlendArgs& a, cudaStream_t s) {
+    AmrParams q;
+    FwdParams& p = q.f;
+    const BlendArgs& b = a.b;
+    p.W = b.W; p.H = b.H; p.tiles_x = (b.W + 31) / 32;
+    p.ranges = b.ranges; p.point_list = b.point_list; p.means2D = b.means2D; p.conic_opacity = b.conic_opacity;
+    p.colors = b.colors; p.bg = b.bg; p.final_T = b.final_T; p.n_contrib = b.n_contrib; p.out_color = b.out_color;
+    q.levels = a.levels; q.levels_last = a.levels_last;
+    dim3 grid((b.W + 31) / 32, (b.H + 31) / 32, 1);
+    blend_amr_kernel<<<grid, kBlendThreads, 0, s>>>(q);
+    count_launch();
+    if (a.interpolate) {
+        InterpParams ip;
+        ip.W = b.W; ip.H = b.H; ip.tiles_x = p.tiles_x; ip.fovea_step = a.fovea_step;
+        ip.levels = a.levels; ip.levels_last = a.levels_last;
+        ip.final_T = b.final_T; ip.n_contrib = b.n_contrib; ip.out_color = b.out_color;
+        ip.out_color_precomp = a.out_color_precomp ? a.out_color_precomp : b.out_color;
+        dim3 g2((b.W + 31) / 32, (b.H + 7) / 8, 1);
+        interpolate_kernel<<<g2, 256, 0, s>>>(ip);
+        count_launch();
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// backward
+// ------------------------------------------------------------------------------------------------
+struct BwdParams {
+    int W, H, tiles_x;
+    const uint2* __restrict__ ranges; const uint32_t* __restrict__ point_list;
+    const float2* __restrict__ means2D; const float4* __restrict__ conic_opacity; const float* __restrict__ colors;
+    const float* __restrict__ bg; const float* __restrict__ final_T; const uint32_t* __restrict__ n_contrib;
+    const float* __restrict__ dL_dpix;
+    float* scratch;
+};
+
+__global__ void __launch_bounds__(kBlendThreads) blend_bwd_kernel(const BwdParams p) {
+    __shared__ float4 s_a[kBlendThreads];
+    __shared__ float4 s_b[kBlendThreads];
+    __shared__ float4 s_c[kBlendThreads];     // b, list position (1-based), id, unused
+    __shared__ uint32_t s_wcnt[kBlendThreads / 32];
+    __shared__ uint32_t s_count;
+
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const uint32_t lx = (wid & 1) * 8 + (lane & 7), ly = (wid >> 1) * 4 + (lane >> 3);
+    const uint32_t pix_x = blockIdx.x * 16 + lx, pix_y = blockIdx.y * 16 + ly;
+    const bool inside = pix_x < (uint32_t)p.W && pix_y < (uint32_t)p.H;
+    const uint32_t pix_id = (uint32_t)p.W * pix_y + pix_x;
+    const float pxf = (float)pix_x, pyf = (float)pix_y;
+    const float rx0 = (float)(blockIdx.x * 16), ry0 = (float)(blockIdx.y * 16);
+    const float rx1 = rx0 + 15.f, ry1 = ry0 + 15.f;
+    const size_t HW = (size_t)p.H * p.W;
+
+    const uint2 range = p.ranges[blockIdx.y * p.tiles_x + blockIdx.x];
+    const int todo = (int)(range.y - range.x);
+    const int rounds = (todo + kBlendThreads - 1) / kBlendThreads;
+
+    const float T_final = inside ? p.final_T[pix_id] : 0.f;
+    float T = T_final;
+    const uint32_t last_contributor = inside ? p.n_contrib[pix_id] : 0u;
+    float acc0 = 0.f, acc1 = 0.f, acc2 = 0.f;          // accum_rec
+    float lc0 = 0.f, lc1 = 0.f, lc2 = 0.f, last_alpha = 0.f;
+    float g0 = 0.f, g1 = 0.f, g2 = 0.f;
+    if (inside) { g0 = p.dL_dpix[pix_id]; g1 = p.dL_dpix[HW + pix_id]; g2 = p.dL_dpix[2 * HW + pix_id]; }
+    const float bg_dot = p.bg[0] * g0 + p.bg[1] * g1 + p.bg[2] * g2;
+    const float ddelx_dx = 0.5f * (float)p.W, ddely_dy = 0.5f * (float)p.H;
+
+    // the CTA only needs list entries up to the largest n_contrib of its pixels
+    __shared__ uint32_t s_maxc;
+    if (tid == 0) s_maxc = 0;
+    __syncthreads();
+    {
+        uint32_t m = last_contributor;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) m = max(m, __shfl_xor_sync(0xffffffffu, m, o));
+        if (lane == 0) atomicMax(&s_maxc, m);
+    }
+    __syncthreads();
+    const int max_c = (int)s_maxc;        // entries with 1-based position > max_c are skipped by every pixel
+
+    GaussRec nxt; bool nxt_valid = false;
+    // batch r covers 1-based positions todo - r*256 - tid   (back to front)
+    auto pos_of = [&](int r) { return todo - r * kBlendThreads - tid; };
+    const int r_first = (todo - max_c) / kBlendThreads;  // earlier batches hold only positions > max_c
+    {
+        const int pos = pos_of(r_first);
+        nxt_valid = pos >= 1 && pos <= max_c;
+        if (nxt_valid) nxt = gather(p.point_list, p.means2D, p.conic_opacity, p.colors, range.x + pos - 1);
+    }
+
+    for (int r = r_first; r < rounds; ++r) {
+        __syncthreads();
+        const bool keep = nxt_valid && !cannot_touch(nxt.xy, nxt.co, rx0, ry0, rx1, ry1);
+        const int slot = compact_slot(keep, s_wcnt, &s_count);
+        if (slot >= 0) {
+            s_a[slot] = make_float4(nxt.xy.x, nxt.xy.y, nxt.co.x, nxt.co.y);
+            s_b[slot] = make_float4(nxt.co.z, nxt.co.w, nxt.col.x, nxt.col.y);
+            s_c[slot] = make_float4(nxt.col.z, __uint_as_float((uint32_t)pos_of(r)), __uint_as_float(nxt.id), 0.f);
+        }
+        __syncthreads();
+        const int count = (int)s_count;
+        {
+            const int pos = pos_of(r + 1);
+            nxt_valid = (r + 1 < rounds) && pos >= 1 && pos <= max_c;
+            if (nxt_valid) nxt = gather(p.point_list, p.means2D, p.conic_opacity, p.colors, range.x + pos - 1);
+        }
+
+        for (int j = 0; j < count; ++j) {
+            const float4 A = s_a[j], B = s_b[j], Cc = s_c[j];
+            const uint32_t pos = __float_as_uint(Cc.y);
+            const float dx = A.x - pxf, dy = A.y - pyf;
+            const float power = blend_power(A.z, A.w, B.x, dx, dy);
+            const float G = expf(power);
+            const float alpha = fminf(0.99f, B.y * G);
+            const bool act = inside && pos <= last_contributor && !(power > 0.0f) && !(alpha < kAlphaMin);
+            if (!__any_sync(0xffffffffu, act)) continue;
+
+            float v[8], v8 = 0.f;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) v[i] = 0.f;
+            if (act) {
+                T = T / (1.f - alpha);
+                const float dchannel_dcolor = alpha * T;
+                acc0 = last_alpha * lc0 + (1.f - last_alpha) * acc0;
+                acc1 = last_alpha * lc1 + (1.f - last_alpha) * acc1;
+                acc2 = last_alpha * lc2 + (1.f - last_alpha) * acc2;
+                lc0 = B.z; lc1 = B.w; lc2 = Cc.x;
+                float dL_dalpha = (lc0 - acc0) * g0 + (lc1 - acc1) * g1 + (lc2 - acc2) * g2;
+                dL_dalpha *= T;
+                last_alpha = alpha;
+                dL_dalpha += (-T_final / (1.f - alpha)) * bg_dot;
+                const float dL_dG = B.y * dL_dalpha;
+                const float gdx = G * dx, gdy = G * dy;
+                const float dG_ddelx = -gdx * A.z - gdy * A.w;
+                const float dG_ddely = -gdy * B.x - gdx * A.w;
+                v[0] = dL_dG * dG_ddelx * ddelx_dx;
+                v[1] = dL_dG * dG_ddely * ddely_dy;
+                v[2] = -0.5f * gdx * dx * dL_dG;
+                v[3] = -0.5f * gdx * dy * dL_dG;
+                v[4] = -0.5f * gdy * dy * dL_dG;
+                v[5] = G * dL_dalpha;
+                v[6] = dchannel_dcolor * g0;
+                v[7] = dchannel_dcolor * g1;
+                v8 = dchannel_dcolor * g2;
+            }
+            // butterfly reduction: after three halving steps lane l holds value index (l>>2)&7 summed over
+            // lane bits 4,3,2; two more steps sum over bits 1,0.  9 shuffles for 8 values instead of 40.
+            float w4[4], w2[2], w1;
+            {
+                const bool hi = lane & 16;
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const float keepv = hi ? v[4 + i] : v[i], send = hi ? v[i] : v[4 + i];
+                    w4[i] = keepv + __shfl_xor_sync(0xffffffffu, send, 16);
+                }
+            }
+            {
+                const bool hi = lane & 8;
+#pragma unroll
+                for (int i = 0; i < 2; ++i) {
+                    const float keepv = hi ? w4[2 + i] : w4[i], send = hi ? w4[i] : w4[2 + i];
+                    w2[i] = keepv + __shfl_xor_sync(0xffffffffu, send, 8);
+                }
+            }
+            {
+                const bool hi = lane & 4;
+                const float keepv = hi ? w2[1] : w2[0], send = hi ? w2[0] : w2[1];
+                w1 = keepv + __shfl_xor_sync(0xffffffffu, send, 4);
+            }
+            w1 += __shfl_xor_sync(0xffffffffu, w1, 2);
+            w1 += __shfl_xor_sync(0xffffffffu, w1, 1);
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) v8 += __shfl_xor_sync(0xffffffffu, v8, o);
+
+            float* dst = p.scratch + 12 * (size_t)__float_as_uint(Cc.z);
+            if ((lane & 3) == 0) atomicAdd(dst + ((lane >> 2) & 7), w1);
+            if (lane == 1) atomicAdd(dst + 8, v8);
+        }
+    }
+}
+
+void launch_blend_backward(const BlendBwdArgs& a, cudaStream_t s) {
+    BwdParams p;
+    p.W = a.W; p.H = a.H; p.tiles_x = (a.W + 15) / 16;
+    p.ranges = a.ranges; p.point_list = a.point_list; p.means2D = a.means2D; p.conic_opacity = a.conic_opacity;
+    p.colors = a.colors; p.bg = a.bg; p.final_T = a.final_T; p.n_contrib = a.n_contrib; p.dL_dpix = a.dL_dpix;
+    p.scratch = a.scratch;
+    dim3 grid((a.W + 15) / 16, (a.H + 15) / 16, 1);
+    blend_bwd_kernel<<<grid, kBlendThreads, 0, s>>>(p);
+    count_launch();
+}
+
+}  // namespace gsr

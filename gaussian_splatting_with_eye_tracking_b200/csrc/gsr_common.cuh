@@ -1,0 +1,254 @@
+// gsr_common.cuh -- shared definitions for the sm_100a rasterizer kernels.
+//
+// Work-buffer layouts replace the reference's GeometryState / BinningState / ImageState
+// (submodules/diff-gaussian-rasterization/cuda_rasterizer/rasterizer_impl.h:31-63 and
+// rasterizer_impl.cu:155-194).  They are NOT byte-compatible with the reference (callers only ever
+// thread the opaque byte tensors back into this library); they are self-describing through a
+// device-side header so that backward / AMR steps can find num_rendered without host state.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stddef.h>
+#include "../../include/gsr_b200.h"
+
+namespace gsr {
+
+constexpr int kAlign = 256;
+constexpr int kPreBlock = 256;          // Gaussians per preprocess / duplicate CTA
+constexpr uint32_t kGeomMagic = 0x47535231u;  // "GSR1"
+
+__host__ __device__ inline size_t align_up(size_t x, size_t a = kAlign) { return (x + a - 1) / a * a; }
+
+// ---------------------------------------------------------------- geometry buffer
+struct GeomHeader {      // lives at the start of the (aligned) geometry buffer, device memory
+    uint32_t magic;
+    uint32_t P;
+    uint32_t num_rendered;   // = sum(tiles_touched); reference reads point_offsets[P-1] (rasterizer_impl.cu:281)
+    uint32_t sort_error;     // set by the radix-sort watchdog
+    uint32_t pad[60];
+};
+static_assert(sizeof(GeomHeader) == 256, "header is one alignment unit");
+
+struct GeomLayout {
+    size_t header, depths, clamped, radii, means2D, cov3D, conic_opacity, rgb, tiles_touched,
+           block_sums, block_offsets, total;
+    int nblocks;
+    __host__ __device__ explicit GeomLayout(int P) {
+        nblocks = (P + kPreBlock - 1) / kPreBlock;
+        size_t o = 0;
+        header = o;        o = align_up(o + sizeof(GeomHeader));
+        depths = o;        o = align_up(o + sizeof(float) * (size_t)P);
+        clamped = o;       o = align_up(o + 3 * (size_t)P);
+        radii = o;         o = align_up(o + sizeof(int) * (size_t)P);
+        means2D = o;       o = align_up(o + sizeof(float2) * (size_t)P);
+        cov3D = o;         o = align_up(o + sizeof(float) * 6 * (size_t)P);
+        conic_opacity = o; o = align_up(o + sizeof(float4) * (size_t)P);
+        rgb = o;           o = align_up(o + sizeof(float) * 3 * (size_t)P);
+        tiles_touched = o; o = align_up(o + sizeof(uint32_t) * (size_t)P);
+        block_sums = o;    o = align_up(o + sizeof(uint32_t) * (size_t)(nblocks + 1));
+        block_offsets = o; o = align_up(o + sizeof(uint32_t) * (size_t)(nblocks + 1));
+        total = o;
+    }
+};
+
+struct GeomPtrs {
+    GeomHeader* header;
+    float* depths; unsigned char* clamped; int* radii; float2* means2D; float* cov3D;
+    float4* conic_opacity; float* rgb; uint32_t* tiles_touched; uint32_t* block_sums; uint32_t* block_offsets;
+    int nblocks;
+};
+
+inline char* aligned_base(const void* p) { return (char*)align_up((size_t)p); }
+
+inline GeomPtrs geom_ptrs(const void* buf, int P) {
+    GeomLayout L(P);
+    char* b = aligned_base(buf);
+    GeomPtrs g;
+    g.header = (GeomHeader*)(b + L.header);
+    g.depths = (float*)(b + L.depths);
+    g.clamped = (unsigned char*)(b + L.clamped);
+    g.radii = (int*)(b + L.radii);
+    g.means2D = (float2*)(b + L.means2D);
+    g.cov3D = (float*)(b + L.cov3D);
+    g.conic_opacity = (float4*)(b + L.conic_opacity);
+    g.rgb = (float*)(b + L.rgb);
+    g.tiles_touched = (uint32_t*)(b + L.tiles_touched);
+    g.block_sums = (uint32_t*)(b + L.block_sums);
+    g.block_offsets = (uint32_t*)(b + L.block_offsets);
+    g.nblocks = L.nblocks;
+    return g;
+}
+
+// ---------------------------------------------------------------- binning buffer
+// keysX/valsX and keysY/valsY ping-pong through the radix passes; the final sorted list always
+// lands in (keysY, valsY) -- the duplicate kernel starts in X when the pass count is odd, in Y when
+// it is even.  `sort_temp` holds the digit histograms, the look-back status words and tile counters.
+constexpr int kSortTileItems = 384 * 12;   // must match SORT_THREADS * SORT_ITEMS in gsr_binning.cu
+constexpr int kSortMaxPasses = 8;
+constexpr int kSortMaxRadix = 512;
+
+__host__ __device__ inline size_t sort_temp_bytes(long long n) {
+    long long tiles = (n + kSortTileItems - 1) / kSortTileItems;
+    if (tiles < 1) tiles = 1;
+    size_t hist = sizeof(uint32_t) * kSortMaxPasses * kSortMaxRadix;        // global digit histograms
+    size_t counters = 256;                                                  // per-pass tile counters + flags
+    size_t status = sizeof(uint32_t) * (size_t)tiles * kSortMaxRadix;       // look-back words, ONE pass (re-zeroed per pass)
+    return align_up(hist) + align_up(counters) + align_up(status) * 2 + kAlign;
+}
+
+struct BinLayout {
+    size_t keysX, keysY, valsX, valsY, sort_temp, total;
+    __host__ __device__ explicit BinLayout(long long N) {
+        size_t n = (size_t)(N > 0 ? N : 0);
+        size_t o = 0;
+        keysX = o; o = align_up(o + 8 * n);
+        keysY = o; o = align_up(o + 8 * n);
+        valsX = o; o = align_up(o + 4 * n);
+        valsY = o; o = align_up(o + 4 * n);
+        sort_temp = o; o = align_up(o + sort_temp_bytes(N));
+        total = o;
+    }
+};
+
+struct BinPtrs {
+    uint64_t *keysX, *keysY; uint32_t *valsX, *valsY; void* sort_temp; size_t sort_temp_bytes;
+};
+
+inline BinPtrs bin_ptrs(const void* buf, long long N) {
+    BinLayout L(N);
+    char* b = aligned_base(buf);
+    BinPtrs p;
+    p.keysX = (uint64_t*)(b + L.keysX); p.keysY = (uint64_t*)(b + L.keysY);
+    p.valsX = (uint32_t*)(b + L.valsX); p.valsY = (uint32_t*)(b + L.valsY);
+    p.sort_temp = (void*)(b + L.sort_temp); p.sort_temp_bytes = sort_temp_bytes(N);
+    return p;
+}
+
+// ---------------------------------------------------------------- image buffer
+struct ImgLayout {
+    size_t accum_alpha, n_contrib, ranges, n_intersections, levels, levels_last, levels_current, thresholds, total;
+    int tiles_x, tiles_y, tile;
+    __host__ __device__ ImgLayout(int W, int H, int mode) {
+        tile = (mode == GSR_MODE_AMR) ? 32 : 16;
+        tiles_x = (W + tile - 1) / tile; tiles_y = (H + tile - 1) / tile;
+        size_t px = (size_t)W * H, nt = (size_t)tiles_x * tiles_y;
+        size_t o = 0;
+        accum_alpha = o; o = align_up(o + 4 * px);
+        n_contrib = o;   o = align_up(o + 4 * px);
+        ranges = o;      o = align_up(o + 8 * nt);
+        n_intersections = levels = levels_last = levels_current = thresholds = 0;
+        if (mode == GSR_MODE_AMR) {
+            n_intersections = o; o = align_up(o + 4 * nt);
+            levels = o;          o = align_up(o + 4 * nt);
+            levels_last = o;     o = align_up(o + 4 * nt);
+            levels_current = o;  o = align_up(o + 4 * nt);
+            thresholds = o;      o = align_up(o + 16);
+        }
+        total = o;
+    }
+};
+
+struct ImgPtrs {
+    float* accum_alpha; uint32_t* n_contrib; uint2* ranges;
+    uint32_t *n_intersections, *levels, *levels_last, *levels_current, *thresholds;
+    int tiles_x, tiles_y, tile;
+};
+
+inline ImgPtrs img_ptrs(const void* buf, int W, int H, int mode) {
+    ImgLayout L(W, H, mode);
+    char* b = aligned_base(buf);
+    ImgPtrs p;
+    p.accum_alpha = (float*)(b + L.accum_alpha);
+    p.n_contrib = (uint32_t*)(b + L.n_contrib);
+    p.ranges = (uint2*)(b + L.ranges);
+    bool amr = (mode == GSR_MODE_AMR);
+    p.n_intersections = amr ? (uint32_t*)(b + L.n_intersections) : nullptr;
+    p.levels = amr ? (uint32_t*)(b + L.levels) : nullptr;
+    p.levels_last = amr ? (uint32_t*)(b + L.levels_last) : nullptr;
+    p.levels_current = amr ? (uint32_t*)(b + L.levels_current) : nullptr;
+    p.thresholds = amr ? (uint32_t*)(b + L.thresholds) : nullptr;
+    p.tiles_x = L.tiles_x; p.tiles_y = L.tiles_y; p.tile = L.tile;
+    return p;
+}
+
+// ---------------------------------------------------------------- launch bookkeeping / errors
+void count_launch(int n = 1);
+void set_error(const char* fmt, ...);
+int check_cuda(cudaError_t e, const char* what);
+int check_last(const char* what, bool debug, cudaStream_t s);
+
+// ---------------------------------------------------------------- stage entry points (host)
+struct PreprocessArgs {
+    int P, D, M;
+    const float *means3D, *scales, *rotations, *opacities, *shs, *cov3D_precomp, *colors_precomp;
+    float scale_modifier;
+    const float *viewmatrix, *projmatrix, *cam_pos;
+    int W, H; float tan_fovx, tan_fovy, focal_x, focal_y;
+    int tile;              // 16 or 32
+    int grid_x, grid_y;    // tile grid
+    int* radii;            // output (caller's or internal)
+    bool prefiltered;
+};
+void launch_preprocess(const PreprocessArgs& a, const GeomPtrs& g, cudaStream_t s);
+void launch_block_scan(const GeomPtrs& g, int P, cudaStream_t s);
+void launch_mark_visible(int P, const float* means3D, const float* view, const float* proj, unsigned char* present, cudaStream_t s);
+
+struct SortPlan {
+    int passes; int shift[kSortMaxPasses]; int bits[kSortMaxPasses];
+};
+SortPlan make_sort_plan(int end_bit);
+
+void launch_duplicate(const GeomPtrs& g, int P, const int* radii, int tile, int grid_x, int grid_y,
+                      uint64_t* keys, uint32_t* vals, uint32_t* hist /* [passes][512] or null */, const SortPlan& plan, cudaStream_t s);
+// stable LSD sort of n pairs.  Reads (kin,vin), ends in (kout,vout), uses (ktmp,vtmp) as the ping-pong partner.
+// kin may alias ktmp (in-place use): pass order is in -> b1 -> b2 -> b1 ... with b1 = out when the pass count is
+// odd, tmp when it is even, so the last pass always writes `out`.
+int launch_onesweep(const uint64_t* kin, const uint32_t* vin, uint64_t* kout, uint32_t* vout, uint64_t* ktmp, uint32_t* vtmp,
+                    long long n, const SortPlan& plan, void* temp, size_t temp_bytes, bool hist_ready, uint32_t* err_flag, cudaStream_t s);
+uint32_t* sort_hist_ptr(void* temp);
+void launch_tile_ranges(const uint64_t* keys_sorted, long long n, uint2* ranges, uint32_t* n_intersections, int num_tiles, cudaStream_t s);
+
+void launch_amr_levels(const ImgPtrs& im, int num_tiles, cudaStream_t s);
+void launch_fovea_levels(const ImgPtrs& im, int num_tiles, int fovea_step, const gsr_gaze* gaze, cudaStream_t s);
+
+struct BlendArgs {
+    int W, H;
+    const uint2* ranges; const uint32_t* point_list;
+    const float2* means2D; const float4* conic_opacity; const float* colors;
+    const float* bg;
+    float* final_T; uint32_t* n_contrib; float* out_color;
+};
+void launch_blend_forward(const BlendArgs& a, cudaStream_t s);
+
+struct AmrBlendArgs {
+    BlendArgs b;
+    const uint32_t* levels;        // "tile_AMR_levels" argument of the reference kernel
+    const uint32_t* levels_last;
+    int fovea_step; const float* out_color_precomp; bool interpolate;
+};
+void launch_blend_amr(const AmrBlendArgs& a, cudaStream_t s);
+
+struct BlendBwdArgs {
+    int W, H;
+    const uint2* ranges; const uint32_t* point_list;
+    const float2* means2D; const float4* conic_opacity; const float* colors;
+    const float* bg; const float* final_T; const uint32_t* n_contrib; const float* dL_dpix;
+    float* scratch;   // [P][12] packed accumulator: {dmean.x, dmean.y, dconic.x, dconic.y | dconic.w, dopacity, dcol.r, dcol.g | dcol.b, 0,0,0}
+};
+void launch_blend_backward(const BlendBwdArgs& a, cudaStream_t s);
+
+struct PreBwdArgs {
+    int P, D, M;
+    const float *means3D, *scales, *rotations, *shs, *cov3D /*precomp or internal*/;
+    bool cov_from_scales, colors_from_sh;
+    float scale_modifier;
+    const float *viewmatrix, *projmatrix, *cam_pos;
+    float focal_x, focal_y, tan_fovx, tan_fovy;
+    const int* radii; const unsigned char* clamped;
+    const float* scratch;
+    gsr_grads out;
+};
+void launch_preprocess_backward(const PreBwdArgs& a, cudaStream_t s);
+
+}  // namespace gsr

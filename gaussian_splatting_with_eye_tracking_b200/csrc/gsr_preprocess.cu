@@ -1,0 +1,616 @@
+// gsr_preprocess.cu -- per-Gaussian stages of the rasterizer for sm_100a.
+//
+//   preprocess_fwd   replaces preprocessCUDA<3> + computeCov3D + computeCov2D + computeColorFromSH
+//                    (submodules/diff-gaussian-rasterization/cuda_rasterizer/forward.cu:20-256) and the
+//                    first half of the scan: each 256-Gaussian CTA also emits its tiles_touched sum.
+//   block_scan       replaces cub::DeviceScan::InclusiveSum (rasterizer_impl.cu:277) at CTA granularity;
+//                    the per-Gaussian prefix is re-derived inside the duplicate kernel (gsr_binning.cu).
+//   mark_visible     replaces checkFrustum (rasterizer_impl.cu:54-66).
+//   preprocess_bwd   replaces computeCov2DCUDA + preprocessCUDA(backward) + SH/cov3D backward
+//                    (backward.cu:20-396), fused into ONE pass that also finalises every gradient row
+//                    (so the host never zero-fills 300 B/Gaussian, rasterize_points.cu:151-159).
+//
+// HBM-bound stages: one thread per Gaussian, 128-bit loads where the AoS inputs allow it, culled
+// Gaussians leave after reading 12 B.
+#include "gsr_common.cuh"
+#include "gsr_math.cuh"
+
+namespace gsr {
+
+// ------------------------------------------------------------------------------------------------
+// forward
+// ------------------------------------------------------------------------------------------------
+struct PreFwdParams {
+    int P, D, M;
+    const float* __restrict__ means3D;
+    const float* __restrict__ scales;
+    const float* __restrict__ rotations;
+    const float* __restrict__ opacities;
+    const float* __restrict__ shs;
+    const float* __restrict__ cov3D_precomp;
+    const float* __restrict__ colors_precomp;
+    float scale_modifier;
+    const float* __restrict__ viewmatrix;
+    const float* __restrict__ projmatrix;
+    const float* __restrict__ cam_pos;
+    int W, H;
+    float tan_fovx, tan_fovy, focal_x, focal_y;
+    int tile, grid_x, grid_y;
+    int* __restrict__ radii;
+    float* __restrict__ depths;
+    unsigned char* __restrict__ clamped;
+    float2* __restrict__ means2D;
+    float* __restrict__ cov3D;
+    float4* __restrict__ conic_opacity;
+    float* __restrict__ rgb;
+    uint32_t* __restrict__ tiles_touched;
+    uint32_t* __restrict__ block_sums;
+    GeomHeader* header;
+    int prefiltered;
+};
+
+// SH -> RGB (forward.cu:20-71).  `sh` points at this Gaussian's [M][3] coefficients.
+__device__ __forceinline__ void sh_to_rgb(int deg, const float* __restrict__ sh, bool vec4_ok,
+                                          float dx, float dy, float dz, float out[3], bool clamp_flag[3]) {
+    // direction = (pos - campos) / |pos - campos|
+    const float len = __fsqrt_rn(sum3(dx, dx, dy, dy, dz, dz));
+    const float x = __fdiv_rn(dx, len), y = __fdiv_rn(dy, len), z = __fdiv_rn(dz, len);
+
+    float c[48];
+    const int ncoef = (deg + 1) * (deg + 1);
+    if (vec4_ok && deg == 3) {
+        const float4* s4 = reinterpret_cast<const float4*>(sh);
+#pragma unroll
+        for (int i = 0; i < 12; ++i) {
+            float4 v = __ldg(s4 + i);
+            c[4 * i] = v.x; c[4 * i + 1] = v.y; c[4 * i + 2] = v.z; c[4 * i + 3] = v.w;
+        }
+    } else {
+#pragma unroll
+        for (int i = 0; i < 48; ++i) c[i] = (i < 3 * ncoef) ? __ldg(sh + i) : 0.f;
+    }
+
+    float r[3];
+#pragma unroll
+    for (int ch = 0; ch < 3; ++ch) r[ch] = __fmul_rn(kSH_C0, c[ch]);
+    if (deg > 0) {
+        const float a = __fmul_rn(y, kSH_C1), b = __fmul_rn(z, kSH_C1), d = __fmul_rn(x, kSH_C1);
+#pragma unroll
+        for (int ch = 0; ch < 3; ++ch) {
+            r[ch] = __fmaf_rn(-a, c[3 + ch], r[ch]);
+            r[ch] = __fmaf_rn(b, c[6 + ch], r[ch]);
+            r[ch] = __fmaf_rn(-d, c[9 + ch], r[ch]);
+        }
+        if (deg > 1) {
+            const float xx = __fmul_rn(x, x), yy = __fmul_rn(y, y), zz = __fmul_rn(z, z);
+            const float xy = __fmul_rn(y, x), yz = __fmul_rn(z, y), xz = __fmul_rn(z, x);
+            const float zz2 = __fadd_rn(zz, zz);
+            const float t4 = __fmul_rn(xy, kSH_C2_0);
+            const float t5 = __fmul_rn(yz, kSH_C2_1);
+            const float t6 = __fmul_rn(__fadd_rn(__fadd_rn(zz2, -xx), -yy), kSH_C2_2);
+            const float t7 = __fmul_rn(xz, kSH_C2_3);
+            const float xx_yy = __fadd_rn(xx, -yy);
+            const float t8 = __fmul_rn(xx_yy, kSH_C2_4);
+#pragma unroll
+            for (int ch = 0; ch < 3; ++ch) {
+                r[ch] = __fmaf_rn(t4, c[12 + ch], r[ch]);
+                r[ch] = __fmaf_rn(t5, c[15 + ch], r[ch]);
+                r[ch] = __fmaf_rn(t6, c[18 + ch], r[ch]);
+                r[ch] = __fmaf_rn(t7, c[21 + ch], r[ch]);
+                r[ch] = __fmaf_rn(t8, c[24 + ch], r[ch]);
+            }
+            if (deg > 2) {
+                const float q = __fadd_rn(__fmaf_rn(zz, 4.f, -xx), -yy);     // 4zz - xx - yy
+                const float t9 = __fmul_rn(__fmul_rn(y, kSH_C3_0), __fmaf_rn(xx, 3.f, -yy));
+                const float t10 = __fmul_rn(__fmul_rn(xy, kSH_C3_1), z);
+                const float t11 = __fmul_rn(__fmul_rn(y, kSH_C3_2), q);
+                const float t12 = __fmul_rn(__fmul_rn(z, kSH_C3_3), __fmaf_rn(yy, -3.f, __fmaf_rn(xx, -3.f, zz2)));
+                const float t13 = __fmul_rn(q, __fmul_rn(x, kSH_C3_4));
+                const float t14 = __fmul_rn(xx_yy, __fmul_rn(z, kSH_C3_5));
+                const float t15 = __fmul_rn(__fmul_rn(x, kSH_C3_6), __fmaf_rn(yy, -3.f, xx));
+#pragma unroll
+                for (int ch = 0; ch < 3; ++ch) {
+                    r[ch] = __fmaf_rn(t9, c[27 + ch], r[ch]);
+                    r[ch] = __fmaf_rn(t10, c[30 + ch], r[ch]);
+                    r[ch] = __fmaf_rn(t11, c[33 + ch], r[ch]);
+                    r[ch] = __fmaf_rn(t12, c[36 + ch], r[ch]);
+                    r[ch] = __fmaf_rn(t13, c[39 + ch], r[ch]);
+                    r[ch] = __fmaf_rn(t14, c[42 + ch], r[ch]);
+                    r[ch] = __fmaf_rn(t15, c[45 + ch], r[ch]);
+                }
+            }
+        }
+    }
+#pragma unroll
+    for (int ch = 0; ch < 3; ++ch) {
+        const float v = __fadd_rn(r[ch], 0.5f);
+        clamp_flag[ch] = (v < 0.f);
+        out[ch] = fmaxf(v, 0.f);
+    }
+}
+
+// Sigma = (S R)^T (S R) (forward.cu:118-152).  Quaternion (r,x,y,z) is used un-normalised, as in the
+// reference.  Multiplications by the literal zeros of S are exact no-ops for finite inputs and dropped.
+__device__ __forceinline__ void cov3d_from_scale_rot(float sx, float sy, float sz, float mod, float4 q, float cov[6]) {
+    const float r = q.x, x = q.y, y = q.z, z = q.w;
+    sx = __fmul_rn(sx, mod); sy = __fmul_rn(sy, mod); sz = __fmul_rn(sz, mod);
+    const float xz = __fmul_rn(x, z), rx = __fmul_rn(r, x), rz = __fmul_rn(r, z);
+    const float yy = __fmul_rn(y, y), zz = __fmul_rn(z, z);
+    const float C = __fmaf_rn(r, y, xz);
+    const float G = __fmaf_rn(-r, y, xz);
+    const float F = __fmaf_rn(y, z, -rx);
+    const float Hh = __fmaf_rn(y, z, rx);
+    const float B = __fmaf_rn(x, y, -rz);
+    const float Dd = __fmaf_rn(x, y, rz);
+    const float xx_yy = __fmaf_rn(x, x, yy);
+    const float yy_zz = __fadd_rn(yy, zz);
+    const float xx_zz = __fmaf_rn(x, x, zz);
+    // R (column-major, glm): R[0]=(A,B2,C2) R[1]=(D2,E,F2) R[2]=(G2,H2,I)
+    const float A = __fadd_rn(1.f, -__fadd_rn(yy_zz, yy_zz));
+    const float E = __fadd_rn(1.f, -__fadd_rn(xx_zz, xx_zz));
+    const float I = __fadd_rn(1.f, -__fadd_rn(xx_yy, xx_yy));
+    const float B2 = __fadd_rn(B, B), C2 = __fadd_rn(C, C), D2 = __fadd_rn(Dd, Dd);
+    const float F2 = __fadd_rn(F, F), G2 = __fadd_rn(G, G), H2 = __fadd_rn(Hh, Hh);
+    // M = S * R : M[c] = (sx*R[c][0], sy*R[c][1], sz*R[c][2])
+    const float M00 = __fmul_rn(sx, A),  M01 = __fmul_rn(sy, B2), M02 = __fmul_rn(sz, C2);
+    const float M10 = __fmul_rn(sx, D2), M11 = __fmul_rn(sy, E),  M12 = __fmul_rn(sz, F2);
+    const float M20 = __fmul_rn(sx, G2), M21 = __fmul_rn(sy, H2), M22 = __fmul_rn(sz, I);
+    // Sigma = M^T M : Sigma[c][r] = M[r][0]M[c][0] + M[r][1]M[c][1] + M[r][2]M[c][2]
+    cov[0] = sum3(M00, M00, M01, M01, M02, M02);
+    cov[1] = sum3(M00, M10, M01, M11, M02, M12);
+    cov[2] = sum3(M00, M20, M01, M21, M02, M22);
+    cov[3] = sum3(M10, M10, M11, M11, M12, M12);
+    cov[4] = sum3(M10, M20, M11, M21, M12, M22);
+    cov[5] = sum3(M20, M20, M21, M21, M22, M22);
+}
+
+// EWA projection of the 3D covariance (forward.cu:74-113).  Returns (cov00, cov01, cov11) incl. the +0.3
+// low-pass.  t = view-space mean (already computed by the caller with xform_row).
+__device__ __forceinline__ float3 cov2d_from_cov3d(float tx, float ty, float tz, float focal_x, float focal_y,
+                                                   float tan_fovx, float tan_fovy, const float c[6], const float* V) {
+    const float limx = __fmul_rn(1.3f, tan_fovx), limy = __fmul_rn(1.3f, tan_fovy);
+    const float txtz = __fdiv_rn(tx, tz), tytz = __fdiv_rn(ty, tz);
+    const float cx = fminf(limx, fmaxf(-limx, txtz));
+    const float cy = fminf(limy, fmaxf(-limy, tytz));
+    const float tz2 = __fmul_rn(tz, tz);
+    const float J00 = __fdiv_rn(focal_x, tz);
+    const float J11 = __fdiv_rn(focal_y, tz);
+    const float J02 = __fdiv_rn(__fmul_rn(__fmul_rn(tz, -cx), focal_x), tz2);   // -(fx * (cx*tz)) / tz^2
+    const float J12 = __fdiv_rn(__fmul_rn(__fmul_rn(tz, -cy), focal_y), tz2);
+    // T = W * J, rows 0/1 of J only: T0r = W[0][r]*J00 + W[2][r]*J02 ; T1r = W[1][r]*J11 + W[2][r]*J12
+    // with W[0]=(V0,V4,V8) W[1]=(V1,V5,V9) W[2]=(V2,V6,V10)
+    const float T00 = __fmaf_rn(V[2], J02, __fmul_rn(V[0], J00));
+    const float T01 = __fmaf_rn(V[6], J02, __fmul_rn(V[4], J00));
+    const float T02 = __fmaf_rn(V[10], J02, __fmul_rn(V[8], J00));
+    const float T10 = __fmaf_rn(V[2], J12, __fmul_rn(V[1], J11));
+    const float T11 = __fmaf_rn(V[6], J12, __fmul_rn(V[5], J11));
+    const float T12 = __fmaf_rn(V[10], J12, __fmul_rn(V[9], J11));
+    // X = T^T * Vrk^T :  X[c][r] = T[r][0]*Vrk[0][c] + T[r][1]*Vrk[1][c] + T[r][2]*Vrk[2][c]
+    const float X00 = sum3(T00, c[0], T01, c[1], T02, c[2]);
+    const float X10 = sum3(T00, c[1], T01, c[3], T02, c[4]);
+    const float X20 = sum3(T00, c[2], T01, c[4], T02, c[5]);
+    const float X01 = sum3(T10, c[0], T11, c[1], T12, c[2]);
+    const float X11 = sum3(T10, c[1], T11, c[3], T12, c[4]);
+    const float X21 = sum3(T10, c[2], T11, c[4], T12, c[5]);
+    // cov = X * T
+    const float cov00 = sum3(T00, X00, T01, X10, T02, X20);
+    const float cov01 = sum3(T00, X01, T01, X11, T02, X21);
+    const float cov11 = sum3(T10, X01, T11, X11, T12, X21);
+    return make_float3(__fadd_rn(cov00, 0.3f), cov01, __fadd_rn(cov11, 0.3f));
+}
+
+__global__ void __launch_bounds__(kPreBlock) preprocess_fwd_kernel(const PreFwdParams p) {
+    __shared__ float sV[16], sPm[16], sCam[3];
+    __shared__ uint32_t s_warp_sum[kPreBlock / 32];
+    const int tid = threadIdx.x;
+    if (tid < 16) { sV[tid] = p.viewmatrix[tid]; sPm[tid] = p.projmatrix[tid]; }
+    if (tid < 3) sCam[tid] = p.cam_pos[tid];
+    __syncthreads();
+
+    const int idx = blockIdx.x * kPreBlock + tid;
+    uint32_t touched = 0;
+    int radius = 0;
+
+    if (idx < p.P) {
+        const float px = __ldg(p.means3D + 3 * (size_t)idx);
+        const float py = __ldg(p.means3D + 3 * (size_t)idx + 1);
+        const float pz = __ldg(p.means3D + 3 * (size_t)idx + 2);
+        // near-plane cull (auxiliary.h:139-164): p_view.z <= 0.2 -> invisible
+        const float depth = xform_row(sV[2], sV[6], sV[10], sV[14], px, py, pz);
+        bool alive = depth > 0.2f;
+        if (!alive && p.prefiltered) atomicOr(&p.header->sort_error, 0x100u);   // reference: printf + __trap()
+
+        float2 pix = make_float2(0.f, 0.f);
+        float3 conic = make_float3(0.f, 0.f, 0.f);
+        uint32_t x0 = 0, y0 = 0, x1 = 0, y1 = 0;
+        if (alive) {
+            const float hw = __fadd_rn(xform_row(sPm[3], sPm[7], sPm[11], sPm[15], px, py, pz), 0.0000001f);
+            const float hx = xform_row(sPm[0], sPm[4], sPm[8], sPm[12], px, py, pz);
+            const float hy = xform_row(sPm[1], sPm[5], sPm[9], sPm[13], px, py, pz);
+            const float pw = __frcp_rn(hw);
+            const float ndc_x = __fmul_rn(hx, pw), ndc_y = __fmul_rn(hy, pw);
+
+            float c3[6];
+            if (p.cov3D_precomp != nullptr) {
+#pragma unroll
+                for (int i = 0; i < 6; ++i) c3[i] = __ldg(p.cov3D_precomp + 6 * (size_t)idx + i);
+            } else {
+                const float sx = __ldg(p.scales + 3 * (size_t)idx), sy = __ldg(p.scales + 3 * (size_t)idx + 1),
+                            sz = __ldg(p.scales + 3 * (size_t)idx + 2);
+                const float4 q = __ldg(reinterpret_cast<const float4*>(p.rotations) + idx);
+                cov3d_from_scale_rot(sx, sy, sz, p.scale_modifier, q, c3);
+#pragma unroll
+                for (int i = 0; i < 6; ++i) p.cov3D[6 * (size_t)idx + i] = c3[i];
+            }
+            const float tx = xform_row(sV[0], sV[4], sV[8], sV[12], px, py, pz);
+            const float ty = xform_row(sV[1], sV[5], sV[9], sV[13], px, py, pz);
+            const float3 cov = cov2d_from_cov3d(tx, ty, depth, p.focal_x, p.focal_y, p.tan_fovx, p.tan_fovy, c3, sV);
+
+            const float det = __fmaf_rn(cov.x, cov.z, -__fmul_rn(cov.y, cov.y));
+            alive = (det != 0.0f);
+            if (alive) {
+                const float det_inv = __frcp_rn(det);
+                conic = make_float3(__fmul_rn(cov.z, det_inv), __fmul_rn(cov.y, -det_inv), __fmul_rn(cov.x, det_inv));
+                const float mid = __fmul_rn(__fadd_rn(cov.x, cov.z), 0.5f);
+                const float disc = __fsqrt_rn(fmaxf(0.1f, __fmaf_rn(mid, mid, -det)));
+                const float lam = fmaxf(__fadd_rn(mid, disc), __fadd_rn(mid, -disc));
+                radius = (int)ceilf(__fmul_rn(__fsqrt_rn(lam), 3.f));
+                pix = make_float2(ndc2pix(ndc_x, p.W), ndc2pix(ndc_y, p.H));
+                get_rect(pix.x, pix.y, radius, p.tile, p.grid_x, p.grid_y, x0, y0, x1, y1);
+                touched = (x1 - x0) * (y1 - y0);
+                alive = (touched != 0);
+                if (!alive) radius = 0;
+            }
+        }
+        if (alive) {
+            if (p.colors_precomp == nullptr) {
+                float rgb[3]; bool cl[3];
+                const size_t shoff = (size_t)idx * p.M * 3;
+                const bool vec_ok = ((p.M * 3) % 4 == 0) && ((reinterpret_cast<size_t>(p.shs) & 15) == 0);
+                sh_to_rgb(p.D, p.shs + shoff, vec_ok, __fadd_rn(px, -sCam[0]), __fadd_rn(py, -sCam[1]),
+                          __fadd_rn(pz, -sCam[2]), rgb, cl);
+                p.rgb[3 * (size_t)idx] = rgb[0]; p.rgb[3 * (size_t)idx + 1] = rgb[1]; p.rgb[3 * (size_t)idx + 2] = rgb[2];
+                p.clamped[3 * (size_t)idx] = cl[0]; p.clamped[3 * (size_t)idx + 1] = cl[1]; p.clamped[3 * (size_t)idx + 2] = cl[2];
+            }
+            p.depths[idx] = depth;
+            p.means2D[idx] = pix;
+            p.conic_opacity[idx] = make_float4(conic.x, conic.y, conic.z, __ldg(p.opacities + idx));
+        }
+        p.radii[idx] = radius;
+        p.tiles_touched[idx] = touched;
+    }
+
+    // CTA sum of tiles_touched -> block_sums[blockIdx.x] (first level of the scan)
+    uint32_t v = touched;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if ((tid & 31) == 0) s_warp_sum[tid >> 5] = v;
+    __syncthreads();
+    if (tid == 0) {
+        uint32_t s = 0;
+#pragma unroll
+        for (int w = 0; w < kPreBlock / 32; ++w) s += s_warp_sum[w];
+        p.block_sums[blockIdx.x] = s;
+    }
+}
+
+void launch_preprocess(const PreprocessArgs& a, const GeomPtrs& g, cudaStream_t s) {
+    PreFwdParams p;
+    p.P = a.P; p.D = a.D; p.M = a.M;
+    p.means3D = a.means3D; p.scales = a.scales; p.rotations = a.rotations; p.opacities = a.opacities;
+    p.shs = a.shs; p.cov3D_precomp = a.cov3D_precomp; p.colors_precomp = a.colors_precomp;
+    p.scale_modifier = a.scale_modifier;
+    p.viewmatrix = a.viewmatrix; p.projmatrix = a.projmatrix; p.cam_pos = a.cam_pos;
+    p.W = a.W; p.H = a.H; p.tan_fovx = a.tan_fovx; p.tan_fovy = a.tan_fovy; p.focal_x = a.focal_x; p.focal_y = a.focal_y;
+    p.tile = a.tile; p.grid_x = a.grid_x; p.grid_y = a.grid_y;
+    p.radii = a.radii; p.depths = g.depths; p.clamped = g.clamped; p.means2D = g.means2D; p.cov3D = g.cov3D;
+    p.conic_opacity = g.conic_opacity; p.rgb = g.rgb; p.tiles_touched = g.tiles_touched;
+    p.block_sums = g.block_sums; p.header = g.header; p.prefiltered = a.prefiltered ? 1 : 0;
+    preprocess_fwd_kernel<<<g.nblocks, kPreBlock, 0, s>>>(p);
+    count_launch();
+}
+
+// ------------------------------------------------------------------------------------------------
+// scan of the per-CTA sums: one CTA, exclusive offsets + grand total into the header.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(1024) block_scan_kernel(const uint32_t* __restrict__ sums, uint32_t* __restrict__ offsets,
+                                                          int n, GeomHeader* header, uint32_t P) {
+    __shared__ uint32_t s_warp[32];
+    __shared__ uint32_t s_carry;
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    if (tid == 0) s_carry = 0;
+    __syncthreads();
+    for (int base = 0; base < n; base += 1024) {
+        const int i = base + tid;
+        const uint32_t v = (i < n) ? sums[i] : 0u;
+        uint32_t inc = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { uint32_t t = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += t; }
+        if (lane == 31) s_warp[wid] = inc;
+        __syncthreads();
+        if (wid == 0) {
+            uint32_t w = s_warp[lane], winc = w;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) { uint32_t t = __shfl_up_sync(0xffffffffu, winc, o); if (lane >= o) winc += t; }
+            s_warp[lane] = winc - w;   // exclusive warp offsets
+        }
+        __syncthreads();
+        const uint32_t carry = s_carry;
+        const uint32_t excl = carry + s_warp[wid] + inc - v;
+        if (i < n) offsets[i] = excl;
+        __syncthreads();
+        if (tid == 1023) s_carry = excl + v;
+        __syncthreads();
+    }
+    if (tid == 0) {
+        offsets[n] = s_carry;
+        header->magic = kGeomMagic; header->P = P; header->num_rendered = s_carry;   // sort_error: zeroed by the host memset
+    }
+}
+
+void launch_block_scan(const GeomPtrs& g, int P, cudaStream_t s) {
+    block_scan_kernel<<<1, 1024, 0, s>>>(g.block_sums, g.block_offsets, g.nblocks, g.header, (uint32_t)P);
+    count_launch();
+}
+
+// ------------------------------------------------------------------------------------------------
+// mark_visible
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) mark_visible_kernel(int P, const float* __restrict__ means3D,
+                                                           const float* __restrict__ V, unsigned char* __restrict__ present) {
+    const int idx = blockIdx.x * 256 + threadIdx.x;
+    if (idx >= P) return;
+    const float x = __ldg(means3D + 3 * (size_t)idx), y = __ldg(means3D + 3 * (size_t)idx + 1), z = __ldg(means3D + 3 * (size_t)idx + 2);
+    const float depth = xform_row(__ldg(V + 2), __ldg(V + 6), __ldg(V + 10), __ldg(V + 14), x, y, z);
+    present[idx] = depth > 0.2f ? 1 : 0;
+}
+
+void launch_mark_visible(int P, const float* means3D, const float* view, const float* proj, unsigned char* present, cudaStream_t s) {
+    (void)proj;  // the reference computes p_proj but the side-plane test is commented out (auxiliary.h:154)
+    if (P <= 0) return;
+    mark_visible_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, means3D, view, present);
+    count_launch();
+}
+
+// ------------------------------------------------------------------------------------------------
+// backward: computeCov2DCUDA (backward.cu:144-274) + preprocessCUDA bwd (:346-396) + SH bwd (:20-139)
+// + cov3D bwd (:278-341), one pass.  Gradient tolerance is 1e-3 relative (the reference accumulates with
+// non-deterministic float atomics), so arithmetic here is plain FP32 without pinned contraction.
+// ------------------------------------------------------------------------------------------------
+struct PreBwdParams {
+    int P, D, M;
+    const float* __restrict__ means3D; const float* __restrict__ scales; const float* __restrict__ rotations;
+    const float* __restrict__ shs; const float* __restrict__ cov3D;
+    int cov_from_scales, colors_from_sh;
+    float scale_modifier;
+    const float* __restrict__ viewmatrix; const float* __restrict__ projmatrix; const float* __restrict__ cam_pos;
+    float focal_x, focal_y, tan_fovx, tan_fovy;
+    const int* __restrict__ radii; const unsigned char* __restrict__ clamped;
+    const float* __restrict__ scratch;
+    float *dL_dmeans2D, *dL_dcolors, *dL_dopacity, *dL_dmeans3D, *dL_dcov3D, *dL_dsh, *dL_dscales, *dL_drot, *dL_dconic;
+};
+
+__global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreBwdParams p) {
+    __shared__ float V[16], Pm[16], cam[3];
+    const int tid = threadIdx.x;
+    if (tid < 16) { V[tid] = p.viewmatrix[tid]; Pm[tid] = p.projmatrix[tid]; }
+    if (tid < 3) cam[tid] = p.cam_pos[tid];
+    __syncthreads();
+    const int idx = blockIdx.x * 256 + tid;
+    if (idx >= p.P) return;
+    const size_t i3 = 3 * (size_t)idx;
+
+    const bool visible = p.radii[idx] > 0;
+    float4 sA = make_float4(0, 0, 0, 0), sB = sA, sC = sA;
+    if (visible) {
+        const float4* sp = reinterpret_cast<const float4*>(p.scratch) + 3 * (size_t)idx;
+        sA = sp[0]; sB = sp[1]; sC = sp[2];
+    }
+    // blend-stage gradients leave in the reference's tensor shapes
+    p.dL_dmeans2D[i3] = sA.x; p.dL_dmeans2D[i3 + 1] = sA.y; p.dL_dmeans2D[i3 + 2] = 0.f;
+    p.dL_dopacity[idx] = sB.y;
+    p.dL_dcolors[i3] = sB.z; p.dL_dcolors[i3 + 1] = sB.w; p.dL_dcolors[i3 + 2] = sC.x;
+    if (p.dL_dconic) reinterpret_cast<float4*>(p.dL_dconic)[idx] = make_float4(sA.z, sA.w, 0.f, sB.x);
+
+    float dcov[6] = {0, 0, 0, 0, 0, 0};
+    float dmx = 0.f, dmy = 0.f, dmz = 0.f;
+    float dscale[3] = {0, 0, 0};
+    float4 drot = make_float4(0, 0, 0, 0);
+
+    const float mx = visible ? p.means3D[i3] : 0.f, my = visible ? p.means3D[i3 + 1] : 0.f, mz = visible ? p.means3D[i3 + 2] : 0.f;
+
+    if (visible) {
+        // ---------------- conic -> cov2D -> cov3D, mean (backward.cu:144-274)
+        float c3[6];
+#pragma unroll
+        for (int i = 0; i < 6; ++i) c3[i] = p.cov3D[6 * (size_t)idx + i];
+        const float dcx = sA.z, dcy = sA.w, dcz = sB.x;        // dL/dconic (x, y, w)
+        float tx = V[0] * mx + V[4] * my + V[8] * mz + V[12];
+        float ty = V[1] * mx + V[5] * my + V[9] * mz + V[13];
+        const float tz = V[2] * mx + V[6] * my + V[10] * mz + V[14];
+        const float limx = 1.3f * p.tan_fovx, limy = 1.3f * p.tan_fovy;
+        const float txtz = tx / tz, tytz = ty / tz;
+        tx = fminf(limx, fmaxf(-limx, txtz)) * tz;
+        ty = fminf(limy, fmaxf(-limy, tytz)) * tz;
+        const float x_grad_mul = (txtz < -limx || txtz > limx) ? 0.f : 1.f;
+        const float y_grad_mul = (tytz < -limy || tytz > limy) ? 0.f : 1.f;
+        const float hx = p.focal_x, hy = p.focal_y;
+        const float J00 = hx / tz, J11 = hy / tz, J02 = -(hx * tx) / (tz * tz), J12 = -(hy * ty) / (tz * tz);
+        const float T00 = V[0] * J00 + V[2] * J02, T01 = V[4] * J00 + V[6] * J02, T02 = V[8] * J00 + V[10] * J02;
+        const float T10 = V[1] * J11 + V[2] * J12, T11 = V[5] * J11 + V[6] * J12, T12 = V[9] * J11 + V[10] * J12;
+        // rows of T * Vrk (Vrk symmetric: c0 c1 c2 / c1 c3 c4 / c2 c4 c5)
+        const float A0 = T00 * c3[0] + T01 * c3[1] + T02 * c3[2];
+        const float A1 = T00 * c3[1] + T01 * c3[3] + T02 * c3[4];
+        const float A2 = T00 * c3[2] + T01 * c3[4] + T02 * c3[5];
+        const float B0 = T10 * c3[0] + T11 * c3[1] + T12 * c3[2];
+        const float B1 = T10 * c3[1] + T11 * c3[3] + T12 * c3[4];
+        const float B2 = T10 * c3[2] + T11 * c3[4] + T12 * c3[5];
+        const float a = A0 * T00 + A1 * T01 + A2 * T02 + 0.3f;
+        const float b = B0 * T00 + B1 * T01 + B2 * T02;
+        const float c = B0 * T10 + B1 * T11 + B2 * T12 + 0.3f;
+        const float denom = a * c - b * b;
+        const float denom2inv = 1.0f / ((denom * denom) + 0.0000001f);
+        float dL_da = 0.f, dL_db = 0.f, dL_dc = 0.f;
+        if (denom2inv != 0.f) {
+            dL_da = denom2inv * (-c * c * dcx + 2.f * b * c * dcy + (denom - a * c) * dcz);
+            dL_dc = denom2inv * (-a * a * dcz + 2.f * a * b * dcy + (denom - a * c) * dcx);
+            dL_db = denom2inv * 2.f * (b * c * dcx - (denom + 2.f * b * b) * dcy + a * b * dcz);
+            dcov[0] = T00 * T00 * dL_da + T00 * T10 * dL_db + T10 * T10 * dL_dc;
+            dcov[3] = T01 * T01 * dL_da + T01 * T11 * dL_db + T11 * T11 * dL_dc;
+            dcov[5] = T02 * T02 * dL_da + T02 * T12 * dL_db + T12 * T12 * dL_dc;
+            dcov[1] = 2.f * T00 * T01 * dL_da + (T00 * T11 + T01 * T10) * dL_db + 2.f * T10 * T11 * dL_dc;
+            dcov[2] = 2.f * T00 * T02 * dL_da + (T00 * T12 + T02 * T10) * dL_db + 2.f * T10 * T12 * dL_dc;
+            dcov[4] = 2.f * T02 * T01 * dL_da + (T01 * T12 + T02 * T11) * dL_db + 2.f * T11 * T12 * dL_dc;
+        }
+        const float dT00 = 2.f * A0 * dL_da + B0 * dL_db, dT01 = 2.f * A1 * dL_da + B1 * dL_db, dT02 = 2.f * A2 * dL_da + B2 * dL_db;
+        const float dT10 = 2.f * B0 * dL_dc + A0 * dL_db, dT11 = 2.f * B1 * dL_dc + A1 * dL_db, dT12 = 2.f * B2 * dL_dc + A2 * dL_db;
+        const float dJ00 = V[0] * dT00 + V[4] * dT01 + V[8] * dT02;
+        const float dJ02 = V[2] * dT00 + V[6] * dT01 + V[10] * dT02;
+        const float dJ11 = V[1] * dT10 + V[5] * dT11 + V[9] * dT12;
+        const float dJ12 = V[2] * dT10 + V[6] * dT11 + V[10] * dT12;
+        const float itz = 1.f / tz, itz2 = itz * itz, itz3 = itz2 * itz;
+        const float dtx = x_grad_mul * -hx * itz2 * dJ02;
+        const float dty = y_grad_mul * -hy * itz2 * dJ12;
+        const float dtz = -hx * itz2 * dJ00 - hy * itz2 * dJ11 + (2.f * hx * tx) * itz3 * dJ02 + (2.f * hy * ty) * itz3 * dJ12;
+        dmx = V[0] * dtx + V[1] * dty + V[2] * dtz;
+        dmy = V[4] * dtx + V[5] * dty + V[6] * dtz;
+        dmz = V[8] * dtx + V[9] * dty + V[10] * dtz;
+
+        // ---------------- screen-space mean -> 3D mean (backward.cu:369-387)
+        const float mw = 1.0f / (Pm[3] * mx + Pm[7] * my + Pm[11] * mz + Pm[15] + 0.0000001f);
+        const float mul1 = (Pm[0] * mx + Pm[4] * my + Pm[8] * mz + Pm[12]) * mw * mw;
+        const float mul2 = (Pm[1] * mx + Pm[5] * my + Pm[9] * mz + Pm[13]) * mw * mw;
+        const float d2x = sA.x, d2y = sA.y;
+        dmx += (Pm[0] * mw - Pm[3] * mul1) * d2x + (Pm[1] * mw - Pm[3] * mul2) * d2y;
+        dmy += (Pm[4] * mw - Pm[7] * mul1) * d2x + (Pm[5] * mw - Pm[7] * mul2) * d2y;
+        dmz += (Pm[8] * mw - Pm[11] * mul1) * d2x + (Pm[9] * mw - Pm[11] * mul2) * d2y;
+    }
+
+    // ---------------- SH (backward.cu:20-139)
+    if (p.dL_dsh != nullptr) {
+        float* out = p.dL_dsh + (size_t)idx * p.M * 3;
+        const int ncoef = (p.D + 1) * (p.D + 1);
+        if (visible && p.colors_from_sh) {
+            const float* sh = p.shs + (size_t)idx * p.M * 3;
+            const float ox = mx - cam[0], oy = my - cam[1], oz = mz - cam[2];
+            const float inv_len = 1.f / sqrtf(ox * ox + oy * oy + oz * oz);
+            const float x = ox * inv_len, y = oy * inv_len, z = oz * inv_len;
+            float g[3] = {sB.z, sB.w, sC.x};
+            g[0] *= p.clamped[i3] ? 0.f : 1.f; g[1] *= p.clamped[i3 + 1] ? 0.f : 1.f; g[2] *= p.clamped[i3 + 2] ? 0.f : 1.f;
+            float w[16];                       // dRGB/dsh_k (same for the three channels)
+            float dx_[3] = {0, 0, 0}, dy_[3] = {0, 0, 0}, dz_[3] = {0, 0, 0};   // dRGB/d(dir)
+            w[0] = kSH_C0;
+#pragma unroll
+            for (int k = 1; k < 16; ++k) w[k] = 0.f;
+            auto S = [&](int k, int ch) { return sh[3 * k + ch]; };
+            if (p.D > 0) {
+                w[1] = -kSH_C1 * y; w[2] = kSH_C1 * z; w[3] = -kSH_C1 * x;
+                for (int ch = 0; ch < 3; ++ch) { dx_[ch] = -kSH_C1 * S(3, ch); dy_[ch] = -kSH_C1 * S(1, ch); dz_[ch] = kSH_C1 * S(2, ch); }
+                if (p.D > 1) {
+                    const float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
+                    w[4] = kSH_C2_0 * xy; w[5] = kSH_C2_1 * yz; w[6] = kSH_C2_2 * (2.f * zz - xx - yy);
+                    w[7] = kSH_C2_3 * xz; w[8] = kSH_C2_4 * (xx - yy);
+                    for (int ch = 0; ch < 3; ++ch) {
+                        dx_[ch] += kSH_C2_0 * y * S(4, ch) + kSH_C2_2 * 2.f * -x * S(6, ch) + kSH_C2_3 * z * S(7, ch) + kSH_C2_4 * 2.f * x * S(8, ch);
+                        dy_[ch] += kSH_C2_0 * x * S(4, ch) + kSH_C2_1 * z * S(5, ch) + kSH_C2_2 * 2.f * -y * S(6, ch) + kSH_C2_4 * 2.f * -y * S(8, ch);
+                        dz_[ch] += kSH_C2_1 * y * S(5, ch) + kSH_C2_2 * 2.f * 2.f * z * S(6, ch) + kSH_C2_3 * x * S(7, ch);
+                    }
+                    if (p.D > 2) {
+                        w[9] = kSH_C3_0 * y * (3.f * xx - yy);
+                        w[10] = kSH_C3_1 * xy * z;
+                        w[11] = kSH_C3_2 * y * (4.f * zz - xx - yy);
+                        w[12] = kSH_C3_3 * z * (2.f * zz - 3.f * xx - 3.f * yy);
+                        w[13] = kSH_C3_4 * x * (4.f * zz - xx - yy);
+                        w[14] = kSH_C3_5 * z * (xx - yy);
+                        w[15] = kSH_C3_6 * x * (xx - 3.f * yy);
+                        for (int ch = 0; ch < 3; ++ch) {
+                            dx_[ch] += kSH_C3_0 * S(9, ch) * 3.f * 2.f * xy + kSH_C3_1 * S(10, ch) * yz + kSH_C3_2 * S(11, ch) * -2.f * xy +
+                                       kSH_C3_3 * S(12, ch) * -3.f * 2.f * xz + kSH_C3_4 * S(13, ch) * (-3.f * xx + 4.f * zz - yy) +
+                                       kSH_C3_5 * S(14, ch) * 2.f * xz + kSH_C3_6 * S(15, ch) * 3.f * (xx - yy);
+                            dy_[ch] += kSH_C3_0 * S(9, ch) * 3.f * (xx - yy) + kSH_C3_1 * S(10, ch) * xz + kSH_C3_2 * S(11, ch) * (-3.f * yy + 4.f * zz - xx) +
+                                       kSH_C3_3 * S(12, ch) * -3.f * 2.f * yz + kSH_C3_4 * S(13, ch) * -2.f * xy +
+                                       kSH_C3_5 * S(14, ch) * -2.f * yz + kSH_C3_6 * S(15, ch) * -3.f * 2.f * xy;
+                            dz_[ch] += kSH_C3_1 * S(10, ch) * xy + kSH_C3_2 * S(11, ch) * 4.f * 2.f * yz + kSH_C3_3 * S(12, ch) * 3.f * (2.f * zz - xx - yy) +
+                                       kSH_C3_4 * S(13, ch) * 4.f * 2.f * xz + kSH_C3_5 * S(14, ch) * (xx - yy);
+                        }
+                    }
+                }
+            }
+            for (int k = 0; k < p.M; ++k) {
+                const float wk = (k < ncoef && k < 16) ? w[k] : 0.f;
+                out[3 * k] = wk * g[0]; out[3 * k + 1] = wk * g[1]; out[3 * k + 2] = wk * g[2];
+            }
+            // direction gradient -> mean, through the normalisation (dnormvdv, auxiliary.h:107-118)
+            const float ddx = dx_[0] * g[0] + dx_[1] * g[1] + dx_[2] * g[2];
+            const float ddy = dy_[0] * g[0] + dy_[1] * g[1] + dy_[2] * g[2];
+            const float ddz = dz_[0] * g[0] + dz_[1] * g[1] + dz_[2] * g[2];
+            const float sum2 = ox * ox + oy * oy + oz * oz;
+            const float invsum32 = 1.0f / sqrtf(sum2 * sum2 * sum2);
+            dmx += ((sum2 - ox * ox) * ddx - oy * ox * ddy - oz * ox * ddz) * invsum32;
+            dmy += (-ox * oy * ddx + (sum2 - oy * oy) * ddy - oz * oy * ddz) * invsum32;
+            dmz += (-ox * oz * ddx - oy * oz * ddy + (sum2 - oz * oz) * ddz) * invsum32;
+        } else {
+            for (int k = 0; k < p.M * 3; ++k) out[k] = 0.f;
+        }
+    }
+
+    // ---------------- cov3D -> scale, rotation (backward.cu:278-341)
+    if (visible && p.cov_from_scales) {
+        const float4 q = reinterpret_cast<const float4*>(p.rotations)[idx];
+        const float r = q.x, x = q.y, y = q.z, z = q.w;
+        const float s0 = p.scale_modifier * p.scales[i3], s1 = p.scale_modifier * p.scales[i3 + 1], s2 = p.scale_modifier * p.scales[i3 + 2];
+        // R[c][r] as in the forward (glm column-major)
+        const float R00 = 1.f - 2.f * (y * y + z * z), R01 = 2.f * (x * y - r * z), R02 = 2.f * (x * z + r * y);
+        const float R10 = 2.f * (x * y + r * z), R11 = 1.f - 2.f * (x * x + z * z), R12 = 2.f * (y * z - r * x);
+        const float R20 = 2.f * (x * z - r * y), R21 = 2.f * (y * z + r * x), R22 = 1.f - 2.f * (x * x + y * y);
+        // M = S*R : M[c][r] = s_r * R[c][r]
+        const float M00 = s0 * R00, M01 = s1 * R01, M02 = s2 * R02;
+        const float M10 = s0 * R10, M11 = s1 * R11, M12 = s2 * R12;
+        const float M20 = s0 * R20, M21 = s1 * R21, M22 = s2 * R22;
+        // dL_dSigma (symmetric, off-diagonals halved)
+        const float S00 = dcov[0], S01 = 0.5f * dcov[1], S02 = 0.5f * dcov[2], S11 = dcov[3], S12 = 0.5f * dcov[4], S22 = dcov[5];
+        // dL_dM = 2 * M * dL_dSigma : dM[c][r] = 2 * sum_k M[k][r] * Sg[c][k]
+        const float dM00 = 2.f * (M00 * S00 + M10 * S01 + M20 * S02), dM01 = 2.f * (M01 * S00 + M11 * S01 + M21 * S02), dM02 = 2.f * (M02 * S00 + M12 * S01 + M22 * S02);
+        const float dM10 = 2.f * (M00 * S01 + M10 * S11 + M20 * S12), dM11 = 2.f * (M01 * S01 + M11 * S11 + M21 * S12), dM12 = 2.f * (M02 * S01 + M12 * S11 + M22 * S12);
+        const float dM20 = 2.f * (M00 * S02 + M10 * S12 + M20 * S22), dM21 = 2.f * (M01 * S02 + M11 * S12 + M21 * S22), dM22 = 2.f * (M02 * S02 + M12 * S12 + M22 * S22);
+        // Rt = transpose(R), dMt = transpose(dM): Rt[c][r] = R[r][c], dMt[c][r] = dM[r][c]
+        // dL_dscale_i = dot(Rt[i], dMt[i]) = sum_r R[r][i] * dM[r][i]
+        dscale[0] = R00 * dM00 + R10 * dM10 + R20 * dM20;
+        dscale[1] = R01 * dM01 + R11 * dM11 + R21 * dM21;
+        dscale[2] = R02 * dM02 + R12 * dM12 + R22 * dM22;
+        // dMt[i] *= s_i  => t[i][j] = dMt[i][j] * s_i = dM[j][i] * s_i
+        const float t00 = dM00 * s0, t01 = dM10 * s0, t02 = dM20 * s0;
+        const float t10 = dM01 * s1, t11 = dM11 * s1, t12 = dM21 * s1;
+        const float t20 = dM02 * s2, t21 = dM12 * s2, t22 = dM22 * s2;
+        drot.x = 2.f * z * (t01 - t10) + 2.f * y * (t20 - t02) + 2.f * x * (t12 - t21);
+        drot.y = 2.f * y * (t10 + t01) + 2.f * z * (t20 + t02) + 2.f * r * (t12 - t21) - 4.f * x * (t22 + t11);
+        drot.z = 2.f * x * (t10 + t01) + 2.f * r * (t20 - t02) + 2.f * z * (t12 + t21) - 4.f * y * (t22 + t00);
+        drot.w = 2.f * r * (t01 - t10) + 2.f * x * (t20 + t02) + 2.f * y * (t12 + t21) - 4.f * z * (t11 + t00);
+        // note: like the reference, dL_dscale is the gradient w.r.t. (modifier * scale); no extra factor is applied
+    }
+
+    p.dL_dmeans3D[i3] = dmx; p.dL_dmeans3D[i3 + 1] = dmy; p.dL_dmeans3D[i3 + 2] = dmz;
+#pragma unroll
+    for (int i = 0; i < 6; ++i) p.dL_dcov3D[6 * (size_t)idx + i] = dcov[i];
+    p.dL_dscales[i3] = dscale[0]; p.dL_dscales[i3 + 1] = dscale[1]; p.dL_dscales[i3 + 2] = dscale[2];
+    reinterpret_cast<float4*>(p.dL_drot)[idx] = drot;
+}
+
+void launch_preprocess_backward(const PreBwdArgs& a, cudaStream_t s) {
+    if (a.P <= 0) return;
+    PreBwdParams p;
+    p.P = a.P; p.D = a.D; p.M = a.M;
+    p.means3D = a.means3D; p.scales = a.scales; p.rotations = a.rotations; p.shs = a.shs; p.cov3D = a.cov3D;
+    p.cov_from_scales = a.cov_from_scales ? 1 : 0; p.colors_from_sh = a.colors_from_sh ? 1 : 0;
+    p.scale_modifier = a.scale_modifier;
+    p.viewmatrix = a.viewmatrix; p.projmatrix = a.projmatrix; p.cam_pos = a.cam_pos;
+    p.focal_x = a.focal_x; p.focal_y = a.focal_y; p.tan_fovx = a.tan_fovx; p.tan_fovy = a.tan_fovy;
+    p.radii = a.radii; p.clamped = a.clamped; p.scratch = a.scratch;
+    p.dL_dmeans2D = a.out.dL_dmeans2D; p.dL_dcolors = a.out.dL_dcolors; p.dL_dopacity = a.out.dL_dopacity;
+    p.dL_dmeans3D = a.out.dL_dmeans3D; p.dL_dcov3D = a.out.dL_dcov3D; p.dL_dsh = a.out.dL_dsh;
+    p.dL_dscales = a.out.dL_dscales; p.dL_drot = a.out.dL_drotations; p.dL_dconic = a.out.dL_dconic;
+    preprocess_bwd_kernel<<<(a.P + 255) / 256, 256, 0, s>>>(p);
+    count_launch();
+}
+
+}  // namespace gsr

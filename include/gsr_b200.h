@@ -1,0 +1,206 @@
+/*
+ * gsr_b200.h -- C ABI of the B200-native differentiable Gaussian-splatting rasterizer.
+ *
+ * This is the drop-in boundary for the hot path of
+ * XinShuo-ph/gaussian_splatting_with_eye_tracking.  Every entry point replaces one method of
+ * the reference's C++ core class CudaRasterizer::Rasterizer (the only thing its torch binding,
+ * and the SIBR viewer, ever call):
+ *
+ *   gsr_forward        <- Rasterizer::forward   submodules/diff-gaussian-rasterization/cuda_rasterizer/rasterizer.h:30-53
+ *   gsr_backward       <- Rasterizer::backward  .../cuda_rasterizer/rasterizer.h:55-84
+ *   gsr_mark_visible   <- Rasterizer::markVisible .../cuda_rasterizer/rasterizer.h:23-28
+ *   gsr_amr_forward    <- Rasterizer::forward (AMR fork)
+ *                         submodules/diff-gaussian-rasterization-amr/cuda_rasterizer/rasterizer.h:30-66
+ *   gsr_*_bytes        <- required<GeometryState|BinningState|ImageState>()
+ *                         .../cuda_rasterizer/rasterizer_impl.h:66-72
+ *
+ * Conventions (same as the reference unless stated):
+ *   - all data pointers are DEVICE pointers; NULL means "input absent" (reference: nullptr checks at
+ *     forward.cu:205,241, rasterizer_impl.cu:229,321,389,411).
+ *   - matrices are 16 floats read column-major: element (row r, col c) = m[c*4 + r]
+ *     (auxiliary.h:58-77); the Python side stores them transposed (scene/cameras.py:54-56).
+ *   - no exceptions, no std::function: status codes + gsr_last_error(); the three growable work
+ *     buffers are obtained through a C callback (the analogue of resizeFunctional,
+ *     rasterize_points.cu:27-33).
+ *   - every launch goes to the caller's stream; the library owns no device memory.
+ *
+ * No torch types appear here; the PyTorch host shim (gaussian_splatting_with_eye_tracking_b200/_capi.py)
+ * binds these with ctypes.
+ */
+#ifndef GSR_B200_H_INCLUDED
+#define GSR_B200_H_INCLUDED
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define GSR_API __attribute__((visibility("default")))
+#else
+#define GSR_API
+#endif
+
+/* status codes */
+enum {
+    GSR_OK = 0,
+    GSR_ERR_INVALID = 1,   /* bad argument (the reference would AT_ERROR / throw)        */
+    GSR_ERR_CUDA = 2,      /* a CUDA runtime call failed; see gsr_last_error()            */
+    GSR_ERR_ALLOC = 3,     /* the allocation callback returned NULL / too small a buffer  */
+    GSR_ERR_WORKSPACE = 4, /* a passed-in work buffer does not carry a valid header       */
+    GSR_ERR_SORT = 5       /* device-side watchdog tripped inside the radix sort          */
+};
+
+/* which work buffer an allocation request is for (reference: geomFunc/binningFunc/imgFunc) */
+enum { GSR_BUF_GEOM = 0, GSR_BUF_BINNING = 1, GSR_BUF_IMAGE = 2 };
+
+/* tile modes */
+enum {
+    GSR_MODE_BASELINE = 0, /* 16x16 tiles, reference R/ (config.h:16-17)                          */
+    GSR_MODE_AMR = 1       /* 32x32 binning tiles rendered as 2x2-strided 16x16 lattices, ref A/  */
+};
+
+/* Allocation callback: return a DEVICE pointer to at least `bytes` bytes, 256-byte aligned,
+ * valid until the caller of gsr_* releases it.  Called at most once per buffer per gsr_* call. */
+typedef void* (*gsr_alloc_fn)(void* user, int which, size_t bytes);
+
+typedef struct gsr_scene {
+    int P;                       /* number of Gaussians                                    */
+    int sh_degree;               /* D: active SH degree 0..3                               */
+    int sh_coeffs;               /* M: coefficients per Gaussian in `shs` (16 for deg 3)    */
+    const float* means3D;        /* [P,3]                                                  */
+    const float* shs;            /* [P,M,3] or NULL                                        */
+    const float* colors_precomp; /* [P,3]   or NULL                                        */
+    const float* opacities;      /* [P]  (activated)                                       */
+    const float* scales;         /* [P,3] (activated) or NULL                              */
+    const float* rotations;      /* [P,4] (r,x,y,z), not normalised by the kernel, or NULL */
+    const float* cov3D_precomp;  /* [P,6]  or NULL                                         */
+    float scale_modifier;
+} gsr_scene;
+
+typedef struct gsr_camera {
+    int width, height;
+    float tan_fovx, tan_fovy;
+    const float* background;     /* [3]  device */
+    const float* viewmatrix;     /* [16] device */
+    const float* projmatrix;     /* [16] device */
+    const float* cam_pos;        /* [3]  device */
+    int prefiltered;
+} gsr_camera;
+
+/* Gaze extension (no reference implementation exists -- the dead tensors at
+ * gaussian_renderer_amr/__init__.py:98-106 are its only spec).  NULL => reference behaviour. */
+typedef struct gsr_gaze {
+    float cx, cy;        /* gaze point in pixels                          */
+    float radii[4];      /* step k (1..4) renders tiles within radii[k-1] */
+} gsr_gaze;
+
+typedef struct gsr_grads {
+    float* dL_dmeans2D;   /* [P,3] (z column written as 0)  */
+    float* dL_dcolors;    /* [P,3]                          */
+    float* dL_dopacity;   /* [P]                            */
+    float* dL_dmeans3D;   /* [P,3]                          */
+    float* dL_dcov3D;     /* [P,6]                          */
+    float* dL_dsh;        /* [P,M,3] or NULL when M == 0    */
+    float* dL_dscales;    /* [P,3]                          */
+    float* dL_drotations; /* [P,4]                          */
+    float* dL_dconic;     /* [P,4] scratch (reference: internal dL_dconic, rasterize_points.cu:154) */
+    float* scratch;       /* [P,12] floats, packed blend-gradient accumulator; must be 16B aligned   */
+} gsr_grads;
+
+/* ---- sizes of the three work buffers (bytes, including alignment slack) ---- */
+GSR_API size_t gsr_geom_bytes(int P);
+GSR_API size_t gsr_binning_bytes(long long num_rendered);
+GSR_API size_t gsr_image_bytes(int width, int height, int mode);
+
+/* ---- baseline rasterizer ---- */
+GSR_API int gsr_forward(const gsr_scene* scene, const gsr_camera* cam,
+                        gsr_alloc_fn alloc, void* alloc_user,
+                        float* out_color /* [3,H,W] */, int* radii /* [P] or NULL */,
+                        int* num_rendered /* host out */, int debug, void* stream);
+
+GSR_API int gsr_backward(const gsr_scene* scene, const gsr_camera* cam,
+                         const int* radii, const void* geom_buffer, const void* binning_buffer,
+                         const void* image_buffer, int num_rendered,
+                         const float* dL_dpix /* [3,H,W] */, const gsr_grads* grads,
+                         int debug, void* stream);
+
+GSR_API int gsr_mark_visible(int P, const float* means3D, const float* viewmatrix,
+                             const float* projmatrix, unsigned char* present, void* stream);
+
+/* ---- AMR / foveated rasterizer (forward only; the reference AMR backward is non-functional,
+ *      SURVEY 2.3 K17) ----
+ * fovea_step < 0 : single-pass AMR render;  0 : build buffers + levels only (out_color untouched);
+ * 1..4 : progressive round k using the *_precomp buffers built by step 0.                        */
+GSR_API int gsr_amr_forward(const gsr_scene* scene, const gsr_camera* cam,
+                            int fovea_step, const float* out_color_precomp /* [3,H,W] or NULL */,
+                            void* geom_precomp, void* binning_precomp, void* image_precomp,
+                            int interpolate_image, const gsr_gaze* gaze /* NULL = reference */,
+                            gsr_alloc_fn alloc, void* alloc_user,
+                            float* out_color, int* radii, int* num_rendered,
+                            int debug, void* stream);
+
+/* ---- read-only views into the work buffers (tests, band-parallel driver, debugging) ----
+ * Fills `out` with device pointers; fields that do not exist for the buffer's mode are NULL. */
+typedef struct gsr_geom_view {
+    int P;
+    const float* depths;            /* [P]   */
+    const unsigned char* clamped;   /* [3P]  */
+    const int* radii;               /* [P]   */
+    const float* means2D;           /* [P,2] */
+    const float* cov3D;             /* [P,6] */
+    const float* conic_opacity;     /* [P,4] */
+    const float* rgb;               /* [P,3] */
+    const uint32_t* tiles_touched;  /* [P]   */
+    const uint32_t* block_offsets;  /* [ceil(P/256)] exclusive offsets of 256-Gaussian blocks */
+    const uint32_t* num_rendered;   /* [1]   */
+} gsr_geom_view;
+
+typedef struct gsr_binning_view {
+    long long N;
+    const uint64_t* keys_unsorted;  /* [N] */
+    const uint32_t* values_unsorted;/* [N] */
+    const uint64_t* keys_sorted;    /* [N] */
+    const uint32_t* point_list;     /* [N] */
+} gsr_binning_view;
+
+typedef struct gsr_image_view {
+    int width, height, mode, tiles_x, tiles_y;
+    const float* accum_alpha;        /* [H*W]              */
+    const uint32_t* n_contrib;       /* [H*W]              */
+    const uint32_t* ranges;          /* [tiles,2]          */
+    const uint32_t* n_intersections; /* [tiles] (AMR)      */
+    const uint32_t* levels;          /* [tiles] (AMR)      */
+    const uint32_t* levels_last;     /* [tiles] (AMR)      */
+    const uint32_t* levels_current;  /* [tiles] (AMR)      */
+    const uint32_t* thresholds;      /* [3]     (AMR)      */
+} gsr_image_view;
+
+GSR_API int gsr_view_geom(const void* geom_buffer, int P, gsr_geom_view* out);
+GSR_API int gsr_view_binning(const void* binning_buffer, long long N, gsr_binning_view* out);
+GSR_API int gsr_view_image(const void* image_buffer, int width, int height, int mode, gsr_image_view* out);
+
+/* ---- standalone stages (unit-level parity + roofline benches) ---- */
+/* stable LSD radix sort of (u64 key, u32 value) pairs on bits [0, end_bit); replaces
+ * cub::DeviceRadixSort::SortPairs (rasterizer_impl.cu:303-308).  temp >= gsr_sort_temp_bytes(n). */
+GSR_API size_t gsr_sort_temp_bytes(long long n);
+GSR_API int gsr_sort_pairs(const uint64_t* keys_in, uint64_t* keys_out,
+                           const uint32_t* vals_in, uint32_t* vals_out,
+                           uint64_t* keys_tmp, uint32_t* vals_tmp,
+                           long long n, int end_bit, void* temp, size_t temp_bytes, void* stream);
+
+/* number of bits needed for tile ids (reference getHigherMsb, rasterizer_impl.cu:35-50) */
+GSR_API unsigned gsr_higher_msb(unsigned n);
+
+/* counters: how many kernels this library launched since load (bench.py "gpu_launches") */
+GSR_API unsigned long long gsr_launch_count(void);
+
+GSR_API const char* gsr_last_error(void);
+GSR_API const char* gsr_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GSR_B200_H_INCLUDED */
