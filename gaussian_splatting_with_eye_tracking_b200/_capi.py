@@ -86,6 +86,8 @@ SYMBOLS = {
                                  C.c_int, C.c_void_p, C.c_size_t, C.c_void_p]),
     "gsr_higher_msb": (C.c_uint, [C.c_uint]),
     "gsr_launch_count": (C.c_ulonglong, []),
+    "gsr_profile_enable": (None, [C.c_int]),
+    "gsr_profile_read": (C.c_int, [C.POINTER(C.c_float), C.POINTER(C.c_int)]),
     "gsr_last_error": (C.c_char_p, []),
     "gsr_version": (C.c_char_p, []),
 }
@@ -116,6 +118,23 @@ def check(rc: int, what: str) -> None:
     if rc != GSR_OK:
         msg = lib.gsr_last_error()
         raise GsrError(f"{what} failed (status {rc}): {msg.decode() if msg else ''}")
+
+
+PROF_SLOTS = ["preprocess", "scan", "duplicate", "sort", "ranges", "blend", "amr_levels", "amr_blend", "bwd_blend",
+              "bwd_preprocess"] + [f"sort_pass{i}" for i in range(8)]
+
+
+def profile_enable(on: bool) -> None:
+    lib.gsr_profile_enable(1 if on else 0)
+
+
+def profile_read() -> dict:
+    """{stage: (total_ms, count)} of the intervals recorded since the last read (synchronises on them)."""
+    n = len(PROF_SLOTS)
+    ms = (C.c_float * n)()
+    cnt = (C.c_int * n)()
+    check(lib.gsr_profile_read(ms, cnt), "gsr_profile_read")
+    return {PROF_SLOTS[i]: (float(ms[i]), int(cnt[i])) for i in range(n) if cnt[i]}
 
 
 def launch_count() -> int:

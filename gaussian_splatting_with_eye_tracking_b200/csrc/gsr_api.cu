@@ -6,6 +6,8 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <mutex>
+#include <vector>
 
 namespace gsr {
 
@@ -31,6 +33,31 @@ int check_last(const char* what, bool debug, cudaStream_t s) {
     cudaError_t e = cudaGetLastError();
     if (e == cudaSuccess && debug) e = cudaStreamSynchronize(s);
     return check_cuda(e, what);
+}
+
+// ---- optional stage timing
+struct ProfRec { int slot; cudaEvent_t a, b; };
+static bool g_prof_on = false;
+static std::vector<ProfRec> g_prof_recs;
+static std::vector<cudaEvent_t> g_prof_pool;
+static cudaEvent_t g_prof_open[GSR_PROF_SLOTS];
+static std::mutex g_prof_mu;
+
+static cudaEvent_t prof_event() {
+    if (!g_prof_pool.empty()) { cudaEvent_t e = g_prof_pool.back(); g_prof_pool.pop_back(); return e; }
+    cudaEvent_t e = nullptr; cudaEventCreate(&e); return e;
+}
+void prof_begin(int slot, cudaStream_t s) {
+    if (!g_prof_on) return;
+    std::lock_guard<std::mutex> lk(g_prof_mu);
+    cudaEvent_t e = prof_event(); cudaEventRecord(e, s); g_prof_open[slot] = e;
+}
+void prof_end(int slot, cudaStream_t s) {
+    if (!g_prof_on) return;
+    std::lock_guard<std::mutex> lk(g_prof_mu);
+    if (!g_prof_open[slot]) return;
+    cudaEvent_t e = prof_event(); cudaEventRecord(e, s);
+    g_prof_recs.push_back({slot, g_prof_open[slot], e}); g_prof_open[slot] = nullptr;
 }
 
 static uint32_t* pinned_mailbox() {
@@ -103,9 +130,9 @@ static int build_lists(const gsr_scene* sc, const gsr_camera* cam, int mode, gsr
     a.tile = im.tile; a.grid_x = im.tiles_x; a.grid_y = im.tiles_y;
     a.radii = radii_user ? radii_user : g.radii;
     a.prefiltered = cam->prefiltered != 0;
-    launch_preprocess(a, g, s);
+    { ProfScope ps(GSR_PROF_PREPROCESS, s); launch_preprocess(a, g, s); }
     if ((rc = check_last("preprocess", debug, s))) return rc;
-    launch_block_scan(g, P, s);
+    { ProfScope ps(GSR_PROF_SCAN, s); launch_block_scan(g, P, s); }
     if ((rc = check_last("block scan", debug, s))) return rc;
 
     // the one host round-trip of the forward (reference: rasterizer_impl.cu:281): the binning buffer is sized by N
@@ -123,14 +150,17 @@ static int build_lists(const gsr_scene* sc, const gsr_camera* cam, int mode, gsr
         uint32_t* v_start = (plan.passes & 1) ? b.valsX : b.valsY;
         uint32_t* hist = sort_hist_ptr(b.sort_temp);
         if ((rc = check_cuda(cudaMemsetAsync(hist, 0, sizeof(uint32_t) * kSortMaxPasses * kSortMaxRadix, s), "memset hist"))) return rc;
-        launch_duplicate(g, P, a.radii, im.tile, im.tiles_x, im.tiles_y, k_start, v_start, hist, plan, s);
+        { ProfScope ps(GSR_PROF_DUPLICATE, s); launch_duplicate(g, P, a.radii, im.tile, im.tiles_x, im.tiles_y, k_start, v_start, hist, plan, s); }
         if ((rc = check_last("duplicate keys", debug, s))) return rc;
-        rc = launch_onesweep(k_start, v_start, b.keysY, b.valsY, b.keysX, b.valsX, N, plan, b.sort_temp, b.sort_temp_bytes,
-                             /*hist_ready=*/true, &g.header->sort_error, s);
+        {
+            ProfScope ps(GSR_PROF_SORT, s);
+            rc = launch_onesweep(k_start, v_start, b.keysY, b.valsY, b.keysX, b.valsX, N, plan, b.sort_temp, b.sort_temp_bytes,
+                                 /*hist_ready=*/true, &g.header->sort_error, s);
+        }
         if (rc) return rc;
         if ((rc = check_last("radix sort", debug, s))) return rc;
     }
-    launch_tile_ranges(b.keysY, N, im.ranges, im.n_intersections, num_tiles, s);
+    { ProfScope ps(GSR_PROF_RANGES, s); launch_tile_ranges(b.keysY, N, im.ranges, im.n_intersections, num_tiles, s); }
     if ((rc = check_last("tile ranges", debug, s))) return rc;
     *geom_out = geom; *bin_out = bin; *img_out = img; *N_out = (int)N;
     return GSR_OK;
@@ -148,6 +178,23 @@ size_t gsr_image_bytes(int W, int H, int mode) { return ImgLayout(W, H, mode).to
 size_t gsr_sort_temp_bytes(long long n) { return sort_temp_bytes(n) + kAlign; }
 unsigned gsr_higher_msb(unsigned n) { return higher_msb(n); }
 unsigned long long gsr_launch_count(void) { return g_launches.load(); }
+
+void gsr_profile_enable(int on) { std::lock_guard<std::mutex> lk(g_prof_mu); g_prof_on = on != 0; }
+
+int gsr_profile_read(float* ms, int* counts) {
+    std::lock_guard<std::mutex> lk(g_prof_mu);
+    int rc = GSR_OK;
+    for (const ProfRec& r : g_prof_recs) {
+        float t = 0.f;
+        cudaError_t e = cudaEventSynchronize(r.b);
+        if (e == cudaSuccess) e = cudaEventElapsedTime(&t, r.a, r.b);
+        if (e != cudaSuccess) { rc = check_cuda(e, "profile read"); }
+        else if (r.slot >= 0 && r.slot < GSR_PROF_SLOTS) { if (ms) ms[r.slot] += t; if (counts) counts[r.slot] += 1; }
+        g_prof_pool.push_back(r.a); g_prof_pool.push_back(r.b);
+    }
+    g_prof_recs.clear();
+    return rc;
+}
 const char* gsr_last_error(void) { return g_err; }
 const char* gsr_version(void) { return "gsr_b200 0.1 (sm_100a)"; }
 
@@ -172,7 +219,7 @@ int gsr_forward(const gsr_scene* sc, const gsr_camera* cam, gsr_alloc_fn alloc, 
     ba.W = W; ba.H = H; ba.ranges = im.ranges; ba.point_list = b.valsY; ba.means2D = g.means2D;
     ba.conic_opacity = g.conic_opacity; ba.colors = sc->colors_precomp ? sc->colors_precomp : g.rgb;
     ba.bg = cam->background; ba.final_T = im.accum_alpha; ba.n_contrib = im.n_contrib; ba.out_color = out_color;
-    launch_blend_forward(ba, s);
+    { ProfScope ps(GSR_PROF_BLEND, s); launch_blend_forward(ba, s); }
     if ((rc = check_last("blend forward", debug != 0, s))) return rc;
     *num_rendered = N;
     return GSR_OK;
@@ -204,7 +251,7 @@ int gsr_backward(const gsr_scene* sc, const gsr_camera* cam, const int* radii, c
     bb.conic_opacity = g.conic_opacity; bb.colors = sc->colors_precomp ? sc->colors_precomp : g.rgb;
     bb.bg = cam->background; bb.final_T = im.accum_alpha; bb.n_contrib = im.n_contrib; bb.dL_dpix = dL_dpix;
     bb.scratch = gr->scratch;
-    launch_blend_backward(bb, s);
+    { ProfScope ps(GSR_PROF_BWD_BLEND, s); launch_blend_backward(bb, s); }
     if ((rc = check_last("blend backward", debug != 0, s))) return rc;
 
     PreBwdArgs pb;
@@ -219,7 +266,7 @@ int gsr_backward(const gsr_scene* sc, const gsr_camera* cam, const int* radii, c
     pb.tan_fovx = cam->tan_fovx; pb.tan_fovy = cam->tan_fovy;
     pb.radii = radii; pb.clamped = g.clamped; pb.scratch = gr->scratch; pb.out = *gr;
     if (sc->sh_coeffs == 0) pb.out.dL_dsh = nullptr;
-    launch_preprocess_backward(pb, s);
+    { ProfScope ps(GSR_PROF_BWD_PREPROCESS, s); launch_preprocess_backward(pb, s); }
     return check_last("preprocess backward", debug != 0, s);
 }
 
@@ -267,7 +314,7 @@ int gsr_amr_forward(const gsr_scene* sc, const gsr_camera* cam, int fovea_step, 
     *num_rendered = N;
 
     if (fovea_step < 1) {
-        launch_amr_levels(im, num_tiles, s);
+        { ProfScope ps(GSR_PROF_AMR_LEVELS, s); launch_amr_levels(im, num_tiles, s); }
         if ((rc = check_last("amr levels", debug != 0, s))) return rc;
         if (fovea_step == 0) return GSR_OK;             // step 0: build only (A/rasterizer_impl.cu:650-653)
     }
@@ -282,7 +329,7 @@ int gsr_amr_forward(const gsr_scene* sc, const gsr_camera* cam, int fovea_step, 
     ab.levels = (fovea_step >= 1) ? im.levels_current : im.levels;
     ab.levels_last = im.levels_last;
     ab.fovea_step = fovea_step; ab.out_color_precomp = out_color_precomp; ab.interpolate = interpolate_image != 0;
-    launch_blend_amr(ab, s);
+    { ProfScope ps(GSR_PROF_AMR_BLEND, s); launch_blend_amr(ab, s); }
     return check_last("blend amr", debug != 0, s);
 }
 

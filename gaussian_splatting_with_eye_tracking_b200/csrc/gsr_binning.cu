@@ -404,9 +404,11 @@ int launch_onesweep(const uint64_t* kin0, const uint32_t* vin0, uint64_t* kout, 
         sp.bin_base = t.hist + ps * kSortMaxRadix; sp.status = t.status; sp.tile_counter = t.counters + ps; sp.err_flag = err_flag;
         if (plan.bits[ps] <= 8) {
             cudaMemsetAsync(t.status, 0, sizeof(uint32_t) * (size_t)tiles * 256, s);
+            ProfScope pr(GSR_PROF_SORT_PASS0 + ps, s);
             onesweep_kernel<256><<<(unsigned)tiles, SORT_THREADS, sweep_smem<256>(), s>>>(sp);
         } else {
             cudaMemsetAsync(t.status, 0, sizeof(uint32_t) * (size_t)tiles * 512, s);
+            ProfScope pr(GSR_PROF_SORT_PASS0 + ps, s);
             onesweep_kernel<512><<<(unsigned)tiles, SORT_THREADS, sweep_smem<512>(), s>>>(sp);
         }
         count_launch();

@@ -178,6 +178,17 @@ void set_error(const char* fmt, ...);
 int check_cuda(cudaError_t e, const char* what);
 int check_last(const char* what, bool debug, cudaStream_t s);
 
+// ---------------------------------------------------------------- optional per-stage CUDA-event timing
+// (gsr_profile_enable / gsr_profile_read in the C ABI).  No-ops unless enabled; events are recorded on the
+// caller's stream, so the figures are device time of the stage inside a real step, not a separate micro-run.
+void prof_begin(int slot, cudaStream_t s);
+void prof_end(int slot, cudaStream_t s);
+struct ProfScope {
+    int slot; cudaStream_t s;
+    ProfScope(int slot_, cudaStream_t s_) : slot(slot_), s(s_) { prof_begin(slot, s); }
+    ~ProfScope() { prof_end(slot, s); }
+};
+
 // ---------------------------------------------------------------- stage entry points (host)
 struct PreprocessArgs {
     int P, D, M;

@@ -194,6 +194,18 @@ GSR_API int gsr_sort_pairs(const uint64_t* keys_in, uint64_t* keys_out,
 /* number of bits needed for tile ids (reference getHigherMsb, rasterizer_impl.cu:35-50) */
 GSR_API unsigned gsr_higher_msb(unsigned n);
 
+/* ---- per-stage device timing (CUDA events on the caller's stream, recorded inside real calls) ---- */
+enum {
+    GSR_PROF_PREPROCESS = 0, GSR_PROF_SCAN, GSR_PROF_DUPLICATE, GSR_PROF_SORT, GSR_PROF_RANGES, GSR_PROF_BLEND,
+    GSR_PROF_AMR_LEVELS, GSR_PROF_AMR_BLEND, GSR_PROF_BWD_BLEND, GSR_PROF_BWD_PREPROCESS,
+    GSR_PROF_SORT_PASS0,                      /* .. GSR_PROF_SORT_PASS0 + 7: individual onesweep launches */
+    GSR_PROF_SLOTS = GSR_PROF_SORT_PASS0 + 8
+};
+GSR_API void gsr_profile_enable(int on);
+/* waits for the recorded intervals, ADDS their milliseconds into ms[slot] and their number into counts[slot]
+ * (both [GSR_PROF_SLOTS], caller-zeroed), then forgets them.  Returns GSR_OK or GSR_ERR_CUDA. */
+GSR_API int gsr_profile_read(float* ms, int* counts);
+
 /* counters: how many kernels this library launched since load (bench.py "gpu_launches") */
 GSR_API unsigned long long gsr_launch_count(void);
 
