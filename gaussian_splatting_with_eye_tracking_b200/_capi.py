@@ -51,12 +51,12 @@ class GsrGrads(C.Structure):
 class GsrGeomView(C.Structure):
     _fields_ = [("P", C.c_int)] + [(n, C.c_void_p) for n in (
         "depths", "clamped", "radii", "means2D", "cov3D", "conic_opacity", "rgb", "tiles_touched", "block_offsets",
-        "num_rendered")]
+        "depth_order", "num_rendered")]
 
 
 class GsrBinningView(C.Structure):
     _fields_ = [("N", C.c_longlong)] + [(n, C.c_void_p) for n in (
-        "keys_unsorted", "values_unsorted", "keys_sorted", "point_list")]
+        "keys_unsorted", "values_unsorted", "tiles_sorted", "point_list")]
 
 
 class GsrImageView(C.Structure):
@@ -121,7 +121,7 @@ def check(rc: int, what: str) -> None:
 
 
 PROF_SLOTS = ["preprocess", "scan", "duplicate", "sort", "ranges", "blend", "amr_levels", "amr_blend", "bwd_blend",
-              "bwd_preprocess"] + [f"sort_pass{i}" for i in range(8)]
+              "bwd_preprocess", "depth_sort"] + [f"sort_pass{i}" for i in range(8)]
 
 
 def profile_enable(on: bool) -> None:

@@ -48,12 +48,12 @@ static cudaEvent_t prof_event() {
     cudaEvent_t e = nullptr; cudaEventCreate(&e); return e;
 }
 void prof_begin(int slot, cudaStream_t s) {
-    if (!g_prof_on) return;
+    if (!g_prof_on || slot < 0) return;
     std::lock_guard<std::mutex> lk(g_prof_mu);
     cudaEvent_t e = prof_event(); cudaEventRecord(e, s); g_prof_open[slot] = e;
 }
 void prof_end(int slot, cudaStream_t s) {
-    if (!g_prof_on) return;
+    if (!g_prof_on || slot < 0) return;
     std::lock_guard<std::mutex> lk(g_prof_mu);
     if (!g_prof_open[slot]) return;
     cudaEvent_t e = prof_event(); cudaEventRecord(e, s);
@@ -135,9 +135,38 @@ static int build_lists(const gsr_scene* sc, const gsr_camera* cam, int mode, gsr
     { ProfScope ps(GSR_PROF_SCAN, s); launch_block_scan(g, P, s); }
     if ((rc = check_last("block scan", debug, s))) return rc;
 
-    // the one host round-trip of the forward (reference: rasterizer_impl.cu:281): the binning buffer is sized by N
+    // The one host round-trip of the forward (reference: rasterizer_impl.cu:281): the binning buffer is sized by N.
+    // The copy is queued BEFORE the depth sort and waited on through an event, so the host allocates the binning
+    // buffer while the GPU is already sorting the Gaussians by depth.
+    uint32_t* box = pinned_mailbox();
+    static thread_local cudaEvent_t ev_hdr = nullptr;
+    if (box && !ev_hdr) cudaEventCreateWithFlags(&ev_hdr, cudaEventDisableTiming);
+    if (box && ev_hdr) {
+        if ((rc = check_cuda(cudaMemcpyAsync(box, &g.header->magic, 16, cudaMemcpyDeviceToHost, s), "D2H header"))) return rc;
+        if ((rc = check_cuda(cudaEventRecord(ev_hdr, s), "event record"))) return rc;
+    }
+
+    // (1) stable sort of the Gaussians by depth bits (invisible ones keyed 0xffffffff go last and emit nothing)
+    {
+        ProfScope ps(GSR_PROF_DEPTH_SORT, s);
+        launch_depth_keys(P, g.depths, g.tiles_touched, g.dkeys_a, s);
+        const SortPlan dplan = make_sort_plan(32);
+        // pass order is in -> b1 -> b2 -> ...; pick (out, tmp) so that no pass reads and writes the same array
+        uint32_t* kout = (dplan.passes & 1) ? g.dkeys_b : g.dkeys_a;
+        uint32_t* ktmp = (dplan.passes & 1) ? g.dkeys_a : g.dkeys_b;
+        rc = launch_onesweep32(g.dkeys_a, nullptr, kout, g.order, ktmp, g.order_tmp, P, dplan, g.sort_temp, g.sort_temp_bytes,
+                               /*hist_ready=*/false, &g.header->sort_error, -1, s);
+        if (rc) return rc;
+        launch_order_block_sums(P, g.order, g.tiles_touched, g.oblock_sums, s);
+        launch_scan_u32(g.oblock_sums, g.oblock_offsets, g.nblocks, s);
+    }
+    if ((rc = check_last("depth sort", debug, s))) return rc;
+
     uint32_t hdr[4];
-    if ((rc = read_u32(&g.header->magic, hdr, 4, s))) return rc;
+    if (box && ev_hdr) {
+        if ((rc = check_cuda(cudaEventSynchronize(ev_hdr), "event sync (header)"))) return rc;
+        memcpy(hdr, box, 16);
+    } else if ((rc = read_u32(&g.header->magic, hdr, 4, s))) return rc;
     if (hdr[3] & 0x100u) { set_error("a Gaussian was culled although prefiltered=true (reference would __trap)"); return GSR_ERR_INVALID; }
     const long long N = hdr[2];
     void* bin = alloc(user, GSR_BUF_BINNING, gsr_binning_bytes(N));
@@ -145,22 +174,24 @@ static int build_lists(const gsr_scene* sc, const gsr_camera* cam, int mode, gsr
     BinPtrs b = bin_ptrs(bin, N);
 
     if (N > 0) {
-        const SortPlan plan = make_sort_plan(32 + (int)higher_msb((unsigned)num_tiles));
-        uint64_t* k_start = (plan.passes & 1) ? b.keysX : b.keysY;
+        // (2) emit (tile, id) pairs in depth order, (3) stable partition by tile id
+        const SortPlan plan = make_sort_plan((int)higher_msb((unsigned)num_tiles));
+        uint32_t* t_start = (plan.passes & 1) ? b.tilesX : b.tilesY;
         uint32_t* v_start = (plan.passes & 1) ? b.valsX : b.valsY;
         uint32_t* hist = sort_hist_ptr(b.sort_temp);
         if ((rc = check_cuda(cudaMemsetAsync(hist, 0, sizeof(uint32_t) * kSortMaxPasses * kSortMaxRadix, s), "memset hist"))) return rc;
-        { ProfScope ps(GSR_PROF_DUPLICATE, s); launch_duplicate(g, P, a.radii, im.tile, im.tiles_x, im.tiles_y, k_start, v_start, hist, plan, s); }
-        if ((rc = check_last("duplicate keys", debug, s))) return rc;
+        { ProfScope ps(GSR_PROF_DUPLICATE, s);
+          launch_emit_pairs(g, P, g.order, g.oblock_offsets, a.radii, im.tile, im.tiles_x, im.tiles_y, t_start, v_start, hist, plan, s); }
+        if ((rc = check_last("emit pairs", debug, s))) return rc;
         {
             ProfScope ps(GSR_PROF_SORT, s);
-            rc = launch_onesweep(k_start, v_start, b.keysY, b.valsY, b.keysX, b.valsX, N, plan, b.sort_temp, b.sort_temp_bytes,
-                                 /*hist_ready=*/true, &g.header->sort_error, s);
+            rc = launch_onesweep32(t_start, v_start, b.tilesY, b.valsY, b.tilesX, b.valsX, N, plan, b.sort_temp, b.sort_temp_bytes,
+                                   /*hist_ready=*/true, &g.header->sort_error, GSR_PROF_SORT_PASS0, s);
         }
         if (rc) return rc;
         if ((rc = check_last("radix sort", debug, s))) return rc;
     }
-    { ProfScope ps(GSR_PROF_RANGES, s); launch_tile_ranges(b.keysY, N, im.ranges, im.n_intersections, num_tiles, s); }
+    { ProfScope ps(GSR_PROF_RANGES, s); launch_tile_ranges(b.tilesY, N, im.ranges, im.n_intersections, num_tiles, s); }
     if ((rc = check_last("tile ranges", debug, s))) return rc;
     *geom_out = geom; *bin_out = bin; *img_out = img; *N_out = (int)N;
     return GSR_OK;
@@ -338,7 +369,7 @@ int gsr_view_geom(const void* geom_buffer, int P, gsr_geom_view* out) {
     GeomPtrs g = geom_ptrs(geom_buffer, P);
     out->P = P; out->depths = g.depths; out->clamped = g.clamped; out->radii = g.radii;
     out->means2D = (const float*)g.means2D; out->cov3D = g.cov3D; out->conic_opacity = (const float*)g.conic_opacity;
-    out->rgb = g.rgb; out->tiles_touched = g.tiles_touched; out->block_offsets = g.block_offsets;
+    out->rgb = g.rgb; out->tiles_touched = g.tiles_touched; out->block_offsets = g.block_offsets; out->depth_order = g.order;
     out->num_rendered = &g.header->num_rendered;
     return GSR_OK;
 }
@@ -347,7 +378,7 @@ int gsr_view_binning(const void* binning_buffer, long long N, gsr_binning_view* 
     if (!binning_buffer || !out || N < 0) { set_error("view_binning: bad arguments"); return GSR_ERR_INVALID; }
     BinPtrs b = bin_ptrs(binning_buffer, N);
     out->N = N; out->keys_unsorted = nullptr; out->values_unsorted = nullptr;   // consumed by the ping-pong passes
-    out->keys_sorted = b.keysY; out->point_list = b.valsY;
+    out->tiles_sorted = b.tilesY; out->point_list = b.valsY;
     return GSR_OK;
 }
 

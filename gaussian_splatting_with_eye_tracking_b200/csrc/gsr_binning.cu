@@ -1,14 +1,14 @@
 // gsr_binning.cu -- tile binning for sm_100a: key duplication, onesweep radix sort, tile ranges, AMR levels.
 //
-//   duplicate_kernel   replaces duplicateWithKeys (rasterizer_impl.cu:70-111) AND the second half of
+//   emit_pairs_kernel  replaces duplicateWithKeys (rasterizer_impl.cu:70-111) AND the second half of
 //                      cub::DeviceScan::InclusiveSum (:277) AND the histogram pass of the sort: a persistent grid
-//                      walks 256-Gaussian blocks, scans their tiles_touched in shared memory, emits
-//                      key = (tile << 32) | depth_bits / value = Gaussian id with fully coalesced stores
-//                      (one thread per PAIR, not per Gaussian -> no divergence on fat Gaussians), and accumulates
-//                      the per-pass digit histograms of the keys it just produced.
+//                      walks 256-Gaussian blocks IN DEPTH ORDER, scans their tiles_touched in shared memory, emits
+//                      (tile id, Gaussian id) with fully coalesced stores (one thread per PAIR, not per Gaussian ->
+//                      no divergence on fat Gaussians) and accumulates the digit histograms of the tile ids.
 //   onesweep_kernel    replaces cub::DeviceRadixSort::SortPairs<u64,u32> (rasterizer_impl.cu:303-308): stable LSD
 //                      radix sort, one read + one write of every pair per pass, chained-scan ("decoupled
-//                      look-back") prefix across tiles, 8- or 9-bit digits (45 key bits -> 5 passes).
+//                      look-back") prefix across tiles.  Used hierarchically: 4 passes over the P depth keys, then
+//                      2 passes over the N (tile, id) pairs -- 40 B/pair of traffic instead of 132 B/pair.
 //   tile_ranges_kernel replaces cudaMemset + identifyTileRanges (rasterizer_impl.cu:116-138,310-317) and the AMR
 //                      fork's calculateIntersections (A/rasterizer_impl.cu:181-188): per-tile binary search on
 //                      the sorted keys (8 B x 2 log2 N per tile instead of 16 B per pair).
@@ -39,47 +39,75 @@ SortPlan make_sort_plan(int end_bit) {
 }
 
 // ------------------------------------------------------------------------------------------------
-// duplicate + per-pass histograms
+// pair emission in depth order
 // ------------------------------------------------------------------------------------------------
-struct DupParams {
+// The reference sorts N (tile, depth) pairs on 45+ key bits.  The same permutation is obtained far more cheaply
+// hierarchically: (1) stable-sort the P Gaussians by their 32-bit depth key (invisible ones carry 0xffffffff and
+// tiles_touched = 0), (2) emit every Gaussian's pairs in THAT order, (3) stable-partition the pairs by tile id
+// (13-15 bits -> two radix passes on (u32 tile, u32 id) instead of five on (u64 key, u32 id)).  Ties between equal
+// depths inside a tile fall back to ascending Gaussian index in both schemes, so point_list is bit-identical.
+__global__ void __launch_bounds__(kPreBlock) depth_keys_kernel(int P, const float* __restrict__ depths,
+                                                               const uint32_t* __restrict__ tiles_touched, uint32_t* __restrict__ keys) {
+    const int i = blockIdx.x * kPreBlock + threadIdx.x;
+    if (i < P) keys[i] = tiles_touched[i] ? __float_as_uint(depths[i]) : 0xffffffffu;
+}
+
+// per-256 block sums of tiles_touched taken in sorted order (first level of the scan that places the pairs)
+__global__ void __launch_bounds__(kPreBlock) order_block_sums_kernel(int P, const uint32_t* __restrict__ order,
+                                                                     const uint32_t* __restrict__ tiles_touched, uint32_t* __restrict__ sums) {
+    __shared__ uint32_t s_w[kPreBlock / 32];
+    const int j = blockIdx.x * kPreBlock + threadIdx.x;
+    uint32_t v = (j < P) ? tiles_touched[order[j]] : 0u;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if ((threadIdx.x & 31) == 0) s_w[threadIdx.x >> 5] = v;
+    __syncthreads();
+    if (threadIdx.x == 0) { uint32_t t = 0; for (int w = 0; w < kPreBlock / 32; ++w) t += s_w[w]; sums[blockIdx.x] = t; }
+}
+
+struct EmitParams {
     int P, nblocks, tile, grid_x, grid_y;
+    const uint32_t* __restrict__ order;          // depth-sorted Gaussian ids
     const int* __restrict__ radii;
     const float2* __restrict__ means2D;
-    const float* __restrict__ depths;
     const uint32_t* __restrict__ tiles_touched;
-    const uint32_t* __restrict__ block_offsets;
-    uint64_t* __restrict__ keys;
-    uint32_t* __restrict__ vals;
-    uint32_t* hist;                 // [passes][kSortMaxRadix] global counts, or nullptr
+    const uint32_t* __restrict__ block_offsets;  // exclusive offsets of the sorted 256-blocks
+    uint32_t* __restrict__ tiles;                // out: tile id of every pair
+    uint32_t* __restrict__ vals;                 // out: Gaussian id of every pair
+    uint32_t* hist;                              // [passes][kSortMaxRadix] global digit counts of the tile ids
     int passes; int shift[kSortMaxPasses]; int bits[kSortMaxPasses];
 };
 
 constexpr int kDupThreads = 256;
 
-__global__ void __launch_bounds__(kDupThreads) duplicate_kernel(const DupParams p) {
+// Persistent grid over 256-Gaussian blocks (sorted order).  One thread per PAIR: the block's tiles_touched are
+// scanned in shared memory, thread q finds its Gaussian by bisection and its tile by a reciprocal multiply,
+// stores are fully coalesced, fat Gaussians do not serialise a warp (reference: one thread per Gaussian,
+// rasterizer_impl.cu:70-111).
+__global__ void __launch_bounds__(kDupThreads) emit_pairs_kernel(const EmitParams p) {
     extern __shared__ uint32_t s_hist[];            // [passes][kSortMaxRadix]
     __shared__ uint32_t s_off[kPreBlock + 1];
-    __shared__ uint32_t s_x0[kPreBlock], s_y0[kPreBlock], s_w[kPreBlock], s_depth[kPreBlock];
+    __shared__ uint32_t s_x0[kPreBlock], s_y0[kPreBlock], s_w[kPreBlock], s_id[kPreBlock];
+    __shared__ float s_invw[kPreBlock];
     __shared__ uint32_t s_wsum[kDupThreads / 32];
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-    const bool do_hist = (p.hist != nullptr);
-    if (do_hist) for (int i = tid; i < p.passes * kSortMaxRadix; i += kDupThreads) s_hist[i] = 0;
+    for (int i = tid; i < p.passes * kSortMaxRadix; i += kDupThreads) s_hist[i] = 0;
 
     for (int blk = blockIdx.x; blk < p.nblocks; blk += gridDim.x) {
         __syncthreads();                            // previous iteration's smem readers are done
-        const int idx = blk * kPreBlock + tid;
+        const int j = blk * kPreBlock + tid;
         uint32_t t = 0;
-        if (idx < p.P) {
-            t = p.tiles_touched[idx];
+        if (j < p.P) {
+            const uint32_t g = p.order[j];
+            t = p.tiles_touched[g];
             if (t > 0) {
-                const float2 xy = p.means2D[idx];
+                const float2 xy = p.means2D[g];
                 uint32_t x0, y0, x1, y1;
-                get_rect(xy.x, xy.y, p.radii[idx], p.tile, p.grid_x, p.grid_y, x0, y0, x1, y1);
-                s_x0[tid] = x0; s_y0[tid] = y0; s_w[tid] = x1 - x0;
-                s_depth[tid] = __float_as_uint(p.depths[idx]);
+                get_rect(xy.x, xy.y, p.radii[g], p.tile, p.grid_x, p.grid_y, x0, y0, x1, y1);
+                s_x0[tid] = x0; s_y0[tid] = y0; s_w[tid] = x1 - x0; s_id[tid] = g;
+                s_invw[tid] = 1.0f / (float)(x1 - x0);
             }
         }
-        // exclusive scan of t over the CTA
         uint32_t inc = t;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) { uint32_t u = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += u; }
@@ -97,38 +125,35 @@ __global__ void __launch_bounds__(kDupThreads) duplicate_kernel(const DupParams 
         for (uint32_t q0 = 0; q0 < total; q0 += kDupThreads) {
             const uint32_t q = q0 + tid;
             const bool valid = q < total;
-            uint64_t key = 0;
+            uint32_t tile_id = 0;
             if (valid) {
                 // largest g with s_off[g] <= q  (s_off non-decreasing, s_off[256] = total > q)
                 int lo = 0, hi = kPreBlock;
 #pragma unroll
-                for (int it = 0; it < 8; ++it) { int mid = (lo + hi) >> 1; if (s_off[mid] <= q) lo = mid; else hi = mid; }
-                const int g = lo;
-                const uint32_t k = q - s_off[g];
-                const uint32_t w = s_w[g];
-                const uint32_t ty = s_y0[g] + k / w, tx = s_x0[g] + k % w;
-                key = ((uint64_t)(ty * (uint32_t)p.grid_x + tx) << 32) | (uint64_t)s_depth[g];
-                p.keys[(size_t)gbase + q] = key;
-                p.vals[(size_t)gbase + q] = (uint32_t)(blk * kPreBlock + g);
+                for (int it = 0; it < 8; ++it) { const int mid = (lo + hi) >> 1; if (s_off[mid] <= q) lo = mid; else hi = mid; }
+                const uint32_t k = q - s_off[lo];
+                const uint32_t w = s_w[lo];
+                uint32_t row = (uint32_t)(((float)k + 0.5f) * s_invw[lo]);      // k / w for k < 2^22 (tiles per Gaussian)
+                uint32_t col = k - row * w;
+                if (col >= w) { row += 1; col -= w; }                            // guard against a 1-ulp reciprocal
+                tile_id = (s_y0[lo] + row) * (uint32_t)p.grid_x + s_x0[lo] + col;
+                p.tiles[(size_t)gbase + q] = tile_id;
+                p.vals[(size_t)gbase + q] = s_id[lo];
             }
-            if (do_hist) {
-                const uint32_t act = __ballot_sync(0xffffffffu, valid);
-                if (valid) {
-                    for (int ps = 0; ps < p.passes; ++ps) {
-                        const uint32_t d = (uint32_t)(key >> p.shift[ps]) & ((1u << p.bits[ps]) - 1u);
-                        const uint32_t peers = __match_any_sync(act, d);
-                        if (lane == (31 - __clz(peers))) atomicAdd(&s_hist[ps * kSortMaxRadix + d], (uint32_t)__popc(peers));
-                    }
+            const uint32_t act = __ballot_sync(0xffffffffu, valid);
+            if (valid) {
+                for (int ps = 0; ps < p.passes; ++ps) {
+                    const uint32_t d = (tile_id >> p.shift[ps]) & ((1u << p.bits[ps]) - 1u);
+                    const uint32_t peers = __match_any_sync(act, d);
+                    if (lane == (31 - __clz(peers))) atomicAdd(&s_hist[ps * kSortMaxRadix + d], (uint32_t)__popc(peers));
                 }
             }
         }
     }
-    if (do_hist) {
-        __syncthreads();
-        for (int i = tid; i < p.passes * kSortMaxRadix; i += kDupThreads) {
-            const uint32_t h = s_hist[i];
-            if (h) atomicAdd(&p.hist[i], h);
-        }
+    __syncthreads();
+    for (int i = tid; i < p.passes * kSortMaxRadix; i += kDupThreads) {
+        const uint32_t h = s_hist[i];
+        if (h) atomicAdd(&p.hist[i], h);
     }
 }
 
@@ -142,28 +167,39 @@ static int num_sms() {
     return g_num_sms;
 }
 
-void launch_duplicate(const GeomPtrs& g, int P, const int* radii, int tile, int grid_x, int grid_y,
-                      uint64_t* keys, uint32_t* vals, uint32_t* hist, const SortPlan& plan, cudaStream_t s) {
-    DupParams p;
+void launch_depth_keys(int P, const float* depths, const uint32_t* tiles_touched, uint32_t* keys, cudaStream_t s) {
+    depth_keys_kernel<<<(P + kPreBlock - 1) / kPreBlock, kPreBlock, 0, s>>>(P, depths, tiles_touched, keys);
+    count_launch();
+}
+
+void launch_order_block_sums(int P, const uint32_t* order, const uint32_t* tiles_touched, uint32_t* sums, cudaStream_t s) {
+    order_block_sums_kernel<<<(P + kPreBlock - 1) / kPreBlock, kPreBlock, 0, s>>>(P, order, tiles_touched, sums);
+    count_launch();
+}
+
+void launch_emit_pairs(const GeomPtrs& g, int P, const uint32_t* order, const uint32_t* block_offsets, const int* radii, int tile,
+                       int grid_x, int grid_y, uint32_t* tiles, uint32_t* vals, uint32_t* hist, const SortPlan& plan, cudaStream_t s) {
+    EmitParams p;
     p.P = P; p.nblocks = g.nblocks; p.tile = tile; p.grid_x = grid_x; p.grid_y = grid_y;
-    p.radii = radii; p.means2D = g.means2D; p.depths = g.depths; p.tiles_touched = g.tiles_touched;
-    p.block_offsets = g.block_offsets; p.keys = keys; p.vals = vals; p.hist = hist;
+    p.order = order; p.radii = radii; p.means2D = g.means2D; p.tiles_touched = g.tiles_touched;
+    p.block_offsets = block_offsets; p.tiles = tiles; p.vals = vals; p.hist = hist;
     p.passes = plan.passes;
     for (int i = 0; i < kSortMaxPasses; ++i) { p.shift[i] = i < plan.passes ? plan.shift[i] : 0; p.bits[i] = i < plan.passes ? plan.bits[i] : 1; }
-    int grid = num_sms() * 4;
+    int grid = num_sms() * 6;
     if (grid > g.nblocks) grid = g.nblocks;
     if (grid < 1) return;
-    size_t smem = hist ? sizeof(uint32_t) * plan.passes * kSortMaxRadix : 0;
-    duplicate_kernel<<<grid, kDupThreads, smem, s>>>(p);
+    emit_pairs_kernel<<<grid, kDupThreads, sizeof(uint32_t) * plan.passes * kSortMaxRadix, s>>>(p);
     count_launch();
 }
 
 // ------------------------------------------------------------------------------------------------
-// standalone histogram (used by gsr_sort_pairs when keys do not come from duplicate_kernel)
+// standalone digit histogram (keys that do not come out of emit_pairs_kernel: the depth sort, gsr_sort_pairs)
 // ------------------------------------------------------------------------------------------------
-struct HistParams { const uint64_t* keys; long long n; uint32_t* hist; int passes; int shift[kSortMaxPasses]; int bits[kSortMaxPasses]; };
+template <typename KeyT>
+struct HistParams { const KeyT* keys; long long n; uint32_t* hist; int passes; int shift[kSortMaxPasses]; int bits[kSortMaxPasses]; };
 
-__global__ void __launch_bounds__(256) sort_hist_kernel(const HistParams p) {
+template <typename KeyT>
+__global__ void __launch_bounds__(256) sort_hist_kernel(const HistParams<KeyT> p) {
     extern __shared__ uint32_t s_hist[];
     const int tid = threadIdx.x, lane = tid & 31;
     for (int i = tid; i < p.passes * kSortMaxRadix; i += 256) s_hist[i] = 0;
@@ -172,7 +208,7 @@ __global__ void __launch_bounds__(256) sort_hist_kernel(const HistParams p) {
     const long long n_round = (p.n + 31) / 32 * 32;
     for (long long i = (long long)blockIdx.x * 256 + tid; i < n_round; i += stride) {
         const bool valid = i < p.n;
-        const uint64_t key = valid ? p.keys[i] : 0;
+        const KeyT key = valid ? p.keys[i] : (KeyT)0;
         const uint32_t act = __ballot_sync(0xffffffffu, valid);
         if (valid) {
             for (int ps = 0; ps < p.passes; ++ps) {
@@ -204,19 +240,26 @@ __global__ void __launch_bounds__(kSortMaxRadix) hist_scan_kernel(uint32_t* hist
 }
 
 // ------------------------------------------------------------------------------------------------
-// onesweep pass
+// onesweep pass: one read and one write of every (key, value) pair, chained-scan prefix across tiles.
+//   KeyT = uint32_t : depth keys of Gaussians, tile ids of (tile, Gaussian) pairs   (the rasterizer's own sorts)
+//   KeyT = uint64_t : gsr_sort_pairs (the cub::DeviceRadixSort::SortPairs<u64,u32> replacement as a stand-alone op)
+// Tile = 512 threads x ITEMS keys, warp-striped loads (coalesced, order-preserving), match-any multi-split ranks,
+// keys AND values staged in shared memory so that each digit bin leaves as one contiguous run.
 // ------------------------------------------------------------------------------------------------
 constexpr int SORT_THREADS = 512;
-constexpr int SORT_ITEMS = 9;
-constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS;
 constexpr int SORT_WARPS = SORT_THREADS / 32;
-static_assert(SORT_TILE == kSortTileItems, "tile size mismatch with gsr_common.cuh");
+template <typename KeyT> struct SortCfg;
+template <> struct SortCfg<uint32_t> { static constexpr int ITEMS = 12; };
+template <> struct SortCfg<uint64_t> { static constexpr int ITEMS = 9; };
+static_assert(SORT_THREADS * SortCfg<uint64_t>::ITEMS == kSortTileItems, "smallest tile must match gsr_common.cuh (temp sizing)");
 
 constexpr uint32_t ST_AGG = 1u << 30, ST_INC = 2u << 30, ST_MASK = (1u << 30) - 1u;
 
+template <typename KeyT>
 struct SweepParams {
-    const uint64_t* __restrict__ keys_in; uint64_t* __restrict__ keys_out;
-    const uint32_t* __restrict__ vals_in; uint32_t* __restrict__ vals_out;
+    const KeyT* __restrict__ keys_in; KeyT* __restrict__ keys_out;
+    const uint32_t* __restrict__ vals_in;    // nullptr: value = global index (first pass of an index sort)
+    uint32_t* __restrict__ vals_out;
     long long n; int shift; int bits;
     const uint32_t* __restrict__ bin_base;   // [RADIX] exclusive global offsets of this pass
     uint32_t* status;                        // [tiles][RADIX]
@@ -224,14 +267,16 @@ struct SweepParams {
     uint32_t* err_flag;
 };
 
-template <int RADIX>
-__global__ void __launch_bounds__(SORT_THREADS, 2) onesweep_kernel(const SweepParams p) {
+template <typename KeyT, int RADIX>
+__global__ void __launch_bounds__(SORT_THREADS, 2) onesweep_kernel(const SweepParams<KeyT> p) {
+    constexpr int ITEMS = SortCfg<KeyT>::ITEMS;
+    constexpr int TILE = SORT_THREADS * ITEMS;
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    uint64_t* s_keys = reinterpret_cast<uint64_t*>(smem_raw);                       // [SORT_TILE]
-    uint32_t* s_vals = reinterpret_cast<uint32_t*>(smem_raw);                       // aliases s_keys (after keys are out)
-    uint32_t* s_whist = reinterpret_cast<uint32_t*>(smem_raw + sizeof(uint64_t) * SORT_TILE);   // [SORT_WARPS][RADIX]
-    uint32_t* s_bin_start = s_whist + SORT_WARPS * RADIX;                            // [RADIX]
-    uint32_t* s_gofs = s_bin_start + RADIX;                                          // [RADIX]
+    KeyT* s_keys = reinterpret_cast<KeyT*>(smem_raw);                                         // [TILE]
+    uint32_t* s_vals = reinterpret_cast<uint32_t*>(smem_raw + sizeof(KeyT) * TILE);           // [TILE]
+    uint32_t* s_whist = s_vals + TILE;                                                        // [SORT_WARPS][RADIX]
+    uint32_t* s_bin_start = s_whist + SORT_WARPS * RADIX;                                     // [RADIX]
+    uint32_t* s_gofs = s_bin_start + RADIX;                                                   // [RADIX]
     __shared__ uint32_t s_tile;
     __shared__ uint32_t s_wtot[RADIX / 32];
 
@@ -240,25 +285,36 @@ __global__ void __launch_bounds__(SORT_THREADS, 2) onesweep_kernel(const SweepPa
     for (int i = tid; i < SORT_WARPS * RADIX; i += SORT_THREADS) s_whist[i] = 0;
     __syncthreads();
     const uint32_t tile = s_tile;
-    const long long tile_base = (long long)tile * SORT_TILE;
-    const int count = (int)min((long long)SORT_TILE, p.n - tile_base);
+    const long long tile_base = (long long)tile * TILE;
+    const int count = (int)min((long long)TILE, p.n - tile_base);
     const uint32_t mask = (1u << p.bits) - 1u;
 
-    // ---- load keys, warp-striped: item i of lane l sits at warp_base + i*32 + l
-    uint64_t key[SORT_ITEMS];
-    const int wbase = wid * 32 * SORT_ITEMS;
+    // ---- load keys and values, warp-striped: item i of lane l sits at warp_base + i*32 + l
+    KeyT key[ITEMS];
+    uint32_t val[ITEMS];
+    const int wbase = wid * 32 * ITEMS;
 #pragma unroll
-    for (int i = 0; i < SORT_ITEMS; ++i) {
+    for (int i = 0; i < ITEMS; ++i) {
         const int lp = wbase + i * 32 + lane;
-        key[i] = (lp < count) ? p.keys_in[tile_base + lp] : ~0ull;
+        key[i] = (lp < count) ? p.keys_in[tile_base + lp] : (KeyT)~(KeyT)0;
+    }
+    if (p.vals_in != nullptr) {
+#pragma unroll
+        for (int i = 0; i < ITEMS; ++i) {
+            const int lp = wbase + i * 32 + lane;
+            val[i] = (lp < count) ? p.vals_in[tile_base + lp] : 0u;
+        }
+    } else {
+#pragma unroll
+        for (int i = 0; i < ITEMS; ++i) val[i] = (uint32_t)(tile_base + wbase + i * 32 + lane);
     }
 
     // ---- stable ranks inside the warp (match-any multi-split)
-    uint32_t rank[SORT_ITEMS];
+    uint32_t rank[ITEMS];
     uint32_t* wh = s_whist + wid * RADIX;
     const uint32_t lt = (1u << lane) - 1u;
 #pragma unroll
-    for (int i = 0; i < SORT_ITEMS; ++i) {
+    for (int i = 0; i < ITEMS; ++i) {
         const uint32_t d = (uint32_t)(key[i] >> p.shift) & mask;
         const uint32_t peers = __match_any_sync(0xffffffffu, d);
         const uint32_t pre = wh[d];
@@ -269,18 +325,16 @@ __global__ void __launch_bounds__(SORT_THREADS, 2) onesweep_kernel(const SweepPa
     }
     __syncthreads();
 
-    // ---- per-bin: exclusive scan across warps, publish tile aggregate, look back
+    // ---- per-bin: exclusive scan across warps, publish the tile aggregate as early as possible
     uint32_t bin_count = 0;
     if (tid < RADIX) {
         uint32_t acc = 0;
 #pragma unroll
         for (int w = 0; w < SORT_WARPS; ++w) { const uint32_t t = s_whist[w * RADIX + tid]; s_whist[w * RADIX + tid] = acc; acc += t; }
         bin_count = acc;
-        volatile uint32_t* st = p.status + (size_t)tile * RADIX + tid;
-        *st = (tile == 0 ? ST_INC : ST_AGG) | acc;
+        *((volatile uint32_t*)(p.status + (size_t)tile * RADIX + tid)) = (tile == 0 ? ST_INC : ST_AGG) | acc;
     }
-    // tile-local exclusive scan of bin counts (warps 0 .. RADIX/32-1)
-    {
+    {   // tile-local exclusive scan of the bin counts (warps 0 .. RADIX/32-1)
         uint32_t inc = bin_count;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) { uint32_t u = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += u; }
@@ -293,6 +347,18 @@ __global__ void __launch_bounds__(SORT_THREADS, 2) onesweep_kernel(const SweepPa
             s_bin_start[tid] = b + inc - bin_count;
         }
     }
+    __syncthreads();
+
+    // ---- stage keys and values in shared memory in bin order (overlaps the look-back below)
+#pragma unroll
+    for (int i = 0; i < ITEMS; ++i) {
+        const uint32_t d = (uint32_t)(key[i] >> p.shift) & mask;
+        const uint32_t lp = s_bin_start[d] + wh[d] + rank[i];
+        s_keys[lp] = key[i];
+        s_vals[lp] = val[i];
+    }
+
+    // ---- decoupled look-back, one thread per bin
     if (tid < RADIX) {
         uint32_t excl = 0;
         if (tile > 0) {
@@ -302,8 +368,8 @@ __global__ void __launch_bounds__(SORT_THREADS, 2) onesweep_kernel(const SweepPa
                 const uint32_t v = *((volatile uint32_t*)(p.status + (size_t)t * RADIX + tid));
                 const uint32_t f = v & ~ST_MASK;
                 if (f == 0) {
-                    __nanosleep(32);
-                    if (++spins > (1u << 24)) { atomicOr(p.err_flag, 1u); break; }   // watchdog: never hang the GPU
+                    if (++spins > 64u) __nanosleep(64);
+                    if (spins > (1u << 22)) { atomicOr(p.err_flag, 1u); break; }   // watchdog: never hang the GPU
                     continue;
                 }
                 excl += v & ST_MASK;
@@ -312,53 +378,31 @@ __global__ void __launch_bounds__(SORT_THREADS, 2) onesweep_kernel(const SweepPa
             }
             *((volatile uint32_t*)(p.status + (size_t)tile * RADIX + tid)) = ST_INC | ((excl + bin_count) & ST_MASK);
         }
-        s_gofs[tid] = p.bin_base[tid] + excl;
+        s_gofs[tid] = p.bin_base[tid] + excl - s_bin_start[tid];   // global position of smem slot j of this bin = s_gofs + j
     }
     __syncthreads();
 
-    // ---- reorder keys through shared memory so that each bin is one contiguous run
-    uint32_t lpos[SORT_ITEMS];
+    // ---- scatter: consecutive smem slots of one bin are consecutive global positions
 #pragma unroll
-    for (int i = 0; i < SORT_ITEMS; ++i) {
-        const uint32_t d = (uint32_t)(key[i] >> p.shift) & mask;
-        lpos[i] = s_bin_start[d] + wh[d] + rank[i];
-        s_keys[lpos[i]] = key[i];
-    }
-    __syncthreads();
-    uint32_t gpos[SORT_ITEMS];
-#pragma unroll
-    for (int i = 0; i < SORT_ITEMS; ++i) {
+    for (int i = 0; i < ITEMS; ++i) {
         const int j = tid + i * SORT_THREADS;
-        gpos[i] = 0xffffffffu;
         if (j < count) {
-            const uint64_t k = s_keys[j];
+            const KeyT k = s_keys[j];
             const uint32_t d = (uint32_t)(k >> p.shift) & mask;
-            gpos[i] = s_gofs[d] + ((uint32_t)j - s_bin_start[d]);
-            p.keys_out[gpos[i]] = k;
+            const uint32_t g = s_gofs[d] + (uint32_t)j;
+            p.keys_out[g] = k;
+            p.vals_out[g] = s_vals[j];
         }
-    }
-    __syncthreads();
-
-    // ---- values follow the same permutation
-#pragma unroll
-    for (int i = 0; i < SORT_ITEMS; ++i) {
-        const int lp = wbase + i * 32 + lane;
-        if (lp < count) s_vals[lpos[i]] = p.vals_in[tile_base + lp];
-    }
-    __syncthreads();
-#pragma unroll
-    for (int i = 0; i < SORT_ITEMS; ++i) {
-        const int j = tid + i * SORT_THREADS;
-        if (j < count) p.vals_out[gpos[i]] = s_vals[j];
     }
 }
 
-template <int RADIX>
-static size_t sweep_smem() { return sizeof(uint64_t) * SORT_TILE + sizeof(uint32_t) * (SORT_WARPS * RADIX + 2 * RADIX); }
+template <typename KeyT, int RADIX>
+static size_t sweep_smem() {
+    return (sizeof(KeyT) + sizeof(uint32_t)) * SORT_THREADS * SortCfg<KeyT>::ITEMS + sizeof(uint32_t) * (SORT_WARPS * RADIX + 2 * RADIX);
+}
 
 struct SortTemp { uint32_t* hist; uint32_t* counters; uint32_t* status; };
-static SortTemp carve_sort_temp(void* temp, long long n) {
-    long long tiles = (n + SORT_TILE - 1) / SORT_TILE; if (tiles < 1) tiles = 1;
+static SortTemp carve_sort_temp(void* temp) {
     char* b = aligned_base(temp);
     SortTemp t;
     t.hist = (uint32_t*)b; b += align_up(sizeof(uint32_t) * kSortMaxPasses * kSortMaxRadix);
@@ -368,48 +412,51 @@ static SortTemp carve_sort_temp(void* temp, long long n) {
 }
 uint32_t* sort_hist_ptr(void* temp) { return (uint32_t*)aligned_base(temp); }
 
-int launch_onesweep(const uint64_t* kin0, const uint32_t* vin0, uint64_t* kout, uint32_t* vout, uint64_t* ktmp, uint32_t* vtmp,
-                    long long n, const SortPlan& plan, void* temp, size_t temp_bytes, bool hist_ready, uint32_t* err_flag, cudaStream_t s) {
+template <typename KeyT>
+int launch_onesweep_t(const KeyT* kin0, const uint32_t* vin0, KeyT* kout, uint32_t* vout, KeyT* ktmp, uint32_t* vtmp,
+                      long long n, const SortPlan& plan, void* temp, size_t temp_bytes, bool hist_ready, uint32_t* err_flag,
+                      int prof_slot0, cudaStream_t s) {
     if (n <= 0) return GSR_OK;
     if (n >= (1ll << 30)) { set_error("radix sort: n=%lld exceeds 2^30 pairs", n); return GSR_ERR_INVALID; }
     if (temp_bytes < sort_temp_bytes(n)) { set_error("radix sort: temp too small"); return GSR_ERR_ALLOC; }
-    SortTemp t = carve_sort_temp(temp, n);
-    const long long tiles = (n + SORT_TILE - 1) / SORT_TILE;
+    constexpr int TILE = SORT_THREADS * SortCfg<KeyT>::ITEMS;
+    SortTemp t = carve_sort_temp(temp);
+    const long long tiles = (n + TILE - 1) / TILE;
     static bool attr_done = false;
     if (!attr_done) {
-        cudaFuncSetAttribute(onesweep_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sweep_smem<256>());
-        cudaFuncSetAttribute(onesweep_kernel<512>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sweep_smem<512>());
+        cudaFuncSetAttribute(onesweep_kernel<KeyT, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sweep_smem<KeyT, 256>());
+        cudaFuncSetAttribute(onesweep_kernel<KeyT, 512>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sweep_smem<KeyT, 512>());
+        cudaFuncSetAttribute(onesweep_kernel<KeyT, 128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sweep_smem<KeyT, 128>());
         attr_done = true;
     }
     if (!hist_ready) {
         cudaMemsetAsync(t.hist, 0, sizeof(uint32_t) * kSortMaxPasses * kSortMaxRadix, s);
-        HistParams hp; hp.keys = kin0; hp.n = n; hp.hist = t.hist; hp.passes = plan.passes;
+        HistParams<KeyT> hp; hp.keys = kin0; hp.n = n; hp.hist = t.hist; hp.passes = plan.passes;
         for (int i = 0; i < kSortMaxPasses; ++i) { hp.shift[i] = i < plan.passes ? plan.shift[i] : 0; hp.bits[i] = i < plan.passes ? plan.bits[i] : 1; }
         long long want = (n + 256 * 16 - 1) / (256 * 16);
         int grid = (int)min((long long)num_sms() * 4, want); if (grid < 1) grid = 1;
-        sort_hist_kernel<<<grid, 256, sizeof(uint32_t) * plan.passes * kSortMaxRadix, s>>>(hp);
+        sort_hist_kernel<KeyT><<<grid, 256, sizeof(uint32_t) * plan.passes * kSortMaxRadix, s>>>(hp);
         count_launch();
     }
     hist_scan_kernel<<<plan.passes, kSortMaxRadix, 0, s>>>(t.hist);
     count_launch();
     cudaMemsetAsync(t.counters, 0, 256, s);
-    const uint64_t* kin = kin0; const uint32_t* vin = vin0;
-    uint64_t* kb[2]; uint32_t* vb[2];
+    const KeyT* kin = kin0; const uint32_t* vin = vin0;
+    KeyT* kb[2]; uint32_t* vb[2];
     if (plan.passes & 1) { kb[0] = kout; vb[0] = vout; kb[1] = ktmp; vb[1] = vtmp; }
     else                 { kb[0] = ktmp; vb[0] = vtmp; kb[1] = kout; vb[1] = vout; }
     for (int ps = 0; ps < plan.passes; ++ps) {
-        SweepParams sp;
+        SweepParams<KeyT> sp;
         sp.keys_in = kin; sp.keys_out = kb[ps & 1]; sp.vals_in = vin; sp.vals_out = vb[ps & 1];
         sp.n = n; sp.shift = plan.shift[ps]; sp.bits = plan.bits[ps];
         sp.bin_base = t.hist + ps * kSortMaxRadix; sp.status = t.status; sp.tile_counter = t.counters + ps; sp.err_flag = err_flag;
-        if (plan.bits[ps] <= 8) {
-            cudaMemsetAsync(t.status, 0, sizeof(uint32_t) * (size_t)tiles * 256, s);
-            ProfScope pr(GSR_PROF_SORT_PASS0 + ps, s);
-            onesweep_kernel<256><<<(unsigned)tiles, SORT_THREADS, sweep_smem<256>(), s>>>(sp);
-        } else {
-            cudaMemsetAsync(t.status, 0, sizeof(uint32_t) * (size_t)tiles * 512, s);
-            ProfScope pr(GSR_PROF_SORT_PASS0 + ps, s);
-            onesweep_kernel<512><<<(unsigned)tiles, SORT_THREADS, sweep_smem<512>(), s>>>(sp);
+        const int radix = plan.bits[ps] <= 7 ? 128 : (plan.bits[ps] <= 8 ? 256 : 512);
+        cudaMemsetAsync(t.status, 0, sizeof(uint32_t) * (size_t)tiles * radix, s);
+        {
+            ProfScope pr(prof_slot0 >= 0 ? prof_slot0 + ps : -1, s);
+            if (radix == 128) onesweep_kernel<KeyT, 128><<<(unsigned)tiles, SORT_THREADS, sweep_smem<KeyT, 128>(), s>>>(sp);
+            else if (radix == 256) onesweep_kernel<KeyT, 256><<<(unsigned)tiles, SORT_THREADS, sweep_smem<KeyT, 256>(), s>>>(sp);
+            else onesweep_kernel<KeyT, 512><<<(unsigned)tiles, SORT_THREADS, sweep_smem<KeyT, 512>(), s>>>(sp);
         }
         count_launch();
         kin = kb[ps & 1]; vin = vb[ps & 1];
@@ -417,31 +464,41 @@ int launch_onesweep(const uint64_t* kin0, const uint32_t* vin0, uint64_t* kout, 
     return GSR_OK;
 }
 
+int launch_onesweep(const uint64_t* kin, const uint32_t* vin, uint64_t* kout, uint32_t* vout, uint64_t* ktmp, uint32_t* vtmp,
+                    long long n, const SortPlan& plan, void* temp, size_t temp_bytes, bool hist_ready, uint32_t* err_flag, cudaStream_t s) {
+    return launch_onesweep_t<uint64_t>(kin, vin, kout, vout, ktmp, vtmp, n, plan, temp, temp_bytes, hist_ready, err_flag, -1, s);
+}
+int launch_onesweep32(const uint32_t* kin, const uint32_t* vin, uint32_t* kout, uint32_t* vout, uint32_t* ktmp, uint32_t* vtmp,
+                      long long n, const SortPlan& plan, void* temp, size_t temp_bytes, bool hist_ready, uint32_t* err_flag,
+                      int prof_slot0, cudaStream_t s) {
+    return launch_onesweep_t<uint32_t>(kin, vin, kout, vout, ktmp, vtmp, n, plan, temp, temp_bytes, hist_ready, err_flag, prof_slot0, s);
+}
+
 // ------------------------------------------------------------------------------------------------
 // tile ranges by binary search on the sorted keys (+ AMR intersection counts)
 // ------------------------------------------------------------------------------------------------
-__device__ __forceinline__ uint32_t lower_bound_tile(const uint64_t* __restrict__ keys, uint32_t n, uint32_t tile) {
+__device__ __forceinline__ uint32_t lower_bound_tile(const uint32_t* __restrict__ tiles, uint32_t n, uint32_t tile) {
     uint32_t lo = 0, hi = n;
     while (lo < hi) {
         const uint32_t mid = lo + ((hi - lo) >> 1);
-        if ((uint32_t)(__ldg(keys + mid) >> 32) < tile) lo = mid + 1; else hi = mid;
+        if (__ldg(tiles + mid) < tile) lo = mid + 1; else hi = mid;
     }
     return lo;
 }
 
-__global__ void __launch_bounds__(128) tile_ranges_kernel(const uint64_t* __restrict__ keys, uint32_t n, uint2* __restrict__ ranges,
+__global__ void __launch_bounds__(128) tile_ranges_kernel(const uint32_t* __restrict__ tiles, uint32_t n, uint2* __restrict__ ranges,
                                                           uint32_t* __restrict__ n_intersections, int num_tiles) {
     const int t = blockIdx.x * 128 + threadIdx.x;
     if (t >= num_tiles) return;
     uint32_t lo = 0, hi = 0;
-    if (n > 0) { lo = lower_bound_tile(keys, n, (uint32_t)t); hi = lower_bound_tile(keys, n, (uint32_t)t + 1u); }
+    if (n > 0) { lo = lower_bound_tile(tiles, n, (uint32_t)t); hi = lower_bound_tile(tiles, n, (uint32_t)t + 1u); }
     // empty tiles keep the reference's memset value (0,0)
     ranges[t] = (hi > lo) ? make_uint2(lo, hi) : make_uint2(0u, 0u);
     if (n_intersections) n_intersections[t] = hi - lo;
 }
 
-void launch_tile_ranges(const uint64_t* keys_sorted, long long n, uint2* ranges, uint32_t* n_intersections, int num_tiles, cudaStream_t s) {
-    tile_ranges_kernel<<<(num_tiles + 127) / 128, 128, 0, s>>>(keys_sorted, (uint32_t)n, ranges, n_intersections, num_tiles);
+void launch_tile_ranges(const uint32_t* tiles_sorted, long long n, uint2* ranges, uint32_t* n_intersections, int num_tiles, cudaStream_t s) {
+    tile_ranges_kernel<<<(num_tiles + 127) / 128, 128, 0, s>>>(tiles_sorted, (uint32_t)n, ranges, n_intersections, num_tiles);
     count_launch();
 }
 

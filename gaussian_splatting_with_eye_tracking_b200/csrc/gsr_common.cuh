@@ -20,6 +20,20 @@ constexpr uint32_t kGeomMagic = 0x47535231u;  // "GSR1"
 
 __host__ __device__ inline size_t align_up(size_t x, size_t a = kAlign) { return (x + a - 1) / a * a; }
 
+// ---------------------------------------------------------------- radix sort temp sizing
+constexpr int kSortTileItems = 512 * 9;    // smallest tile (u64 keys); must match gsr_binning.cu
+constexpr int kSortMaxPasses = 8;
+constexpr int kSortMaxRadix = 512;
+
+__host__ __device__ inline size_t sort_temp_bytes(long long n) {
+    long long tiles = (n + kSortTileItems - 1) / kSortTileItems;
+    if (tiles < 1) tiles = 1;
+    size_t hist = sizeof(uint32_t) * kSortMaxPasses * kSortMaxRadix;        // global digit histograms
+    size_t counters = 256;                                                  // per-pass tile counters + flags
+    size_t status = sizeof(uint32_t) * (size_t)tiles * kSortMaxRadix;       // look-back words, ONE pass (re-zeroed per pass)
+    return ((hist + 255) / 256 * 256) + 256 + ((status + 255) / 256 * 256) + 256;
+}
+
 // ---------------------------------------------------------------- geometry buffer
 struct GeomHeader {      // lives at the start of the (aligned) geometry buffer, device memory
     uint32_t magic;
@@ -32,7 +46,7 @@ static_assert(sizeof(GeomHeader) == 256, "header is one alignment unit");
 
 struct GeomLayout {
     size_t header, depths, clamped, radii, means2D, cov3D, conic_opacity, rgb, tiles_touched,
-           block_sums, block_offsets, total;
+           block_sums, block_offsets, dkeys_a, dkeys_b, order_tmp, order, oblock_sums, oblock_offsets, sort_temp, total;
     int nblocks;
     __host__ __device__ explicit GeomLayout(int P) {
         nblocks = (P + kPreBlock - 1) / kPreBlock;
@@ -48,6 +62,14 @@ struct GeomLayout {
         tiles_touched = o; o = align_up(o + sizeof(uint32_t) * (size_t)P);
         block_sums = o;    o = align_up(o + sizeof(uint32_t) * (size_t)(nblocks + 1));
         block_offsets = o; o = align_up(o + sizeof(uint32_t) * (size_t)(nblocks + 1));
+        // depth sort of the Gaussians (keys ping-pong, index ping-pong) and the scan in sorted order
+        dkeys_a = o;       o = align_up(o + sizeof(uint32_t) * (size_t)P);
+        dkeys_b = o;       o = align_up(o + sizeof(uint32_t) * (size_t)P);
+        order_tmp = o;     o = align_up(o + sizeof(uint32_t) * (size_t)P);
+        order = o;         o = align_up(o + sizeof(uint32_t) * (size_t)P);
+        oblock_sums = o;   o = align_up(o + sizeof(uint32_t) * (size_t)(nblocks + 1));
+        oblock_offsets = o; o = align_up(o + sizeof(uint32_t) * (size_t)(nblocks + 1));
+        sort_temp = o;     o = align_up(o + sort_temp_bytes(P));
         total = o;
     }
 };
@@ -56,6 +78,7 @@ struct GeomPtrs {
     GeomHeader* header;
     float* depths; unsigned char* clamped; int* radii; float2* means2D; float* cov3D;
     float4* conic_opacity; float* rgb; uint32_t* tiles_touched; uint32_t* block_sums; uint32_t* block_offsets;
+    uint32_t *dkeys_a, *dkeys_b, *order_tmp, *order, *oblock_sums, *oblock_offsets; void* sort_temp; size_t sort_temp_bytes;
     int nblocks;
 };
 
@@ -76,34 +99,24 @@ inline GeomPtrs geom_ptrs(const void* buf, int P) {
     g.tiles_touched = (uint32_t*)(b + L.tiles_touched);
     g.block_sums = (uint32_t*)(b + L.block_sums);
     g.block_offsets = (uint32_t*)(b + L.block_offsets);
+    g.dkeys_a = (uint32_t*)(b + L.dkeys_a); g.dkeys_b = (uint32_t*)(b + L.dkeys_b);
+    g.order_tmp = (uint32_t*)(b + L.order_tmp); g.order = (uint32_t*)(b + L.order);
+    g.oblock_sums = (uint32_t*)(b + L.oblock_sums); g.oblock_offsets = (uint32_t*)(b + L.oblock_offsets);
+    g.sort_temp = (void*)(b + L.sort_temp); g.sort_temp_bytes = sort_temp_bytes(P);
     g.nblocks = L.nblocks;
     return g;
 }
 
 // ---------------------------------------------------------------- binning buffer
-// keysX/valsX and keysY/valsY ping-pong through the radix passes; the final sorted list always
-// lands in (keysY, valsY) -- the duplicate kernel starts in X when the pass count is odd, in Y when
-// it is even.  `sort_temp` holds the digit histograms, the look-back status words and tile counters.
-constexpr int kSortTileItems = 384 * 12;   // must match SORT_THREADS * SORT_ITEMS in gsr_binning.cu
-constexpr int kSortMaxPasses = 8;
-constexpr int kSortMaxRadix = 512;
-
-__host__ __device__ inline size_t sort_temp_bytes(long long n) {
-    long long tiles = (n + kSortTileItems - 1) / kSortTileItems;
-    if (tiles < 1) tiles = 1;
-    size_t hist = sizeof(uint32_t) * kSortMaxPasses * kSortMaxRadix;        // global digit histograms
-    size_t counters = 256;                                                  // per-pass tile counters + flags
-    size_t status = sizeof(uint32_t) * (size_t)tiles * kSortMaxRadix;       // look-back words, ONE pass (re-zeroed per pass)
-    return align_up(hist) + align_up(counters) + align_up(status) * 2 + kAlign;
-}
-
+// (tile id, Gaussian id) pairs; X and Y ping-pong through the radix passes and the final tile-sorted list always
+// lands in (tilesY, valsY).  `sort_temp` holds the digit histograms, the look-back status words and tile counters.
 struct BinLayout {
-    size_t keysX, keysY, valsX, valsY, sort_temp, total;
+    size_t tilesX, tilesY, valsX, valsY, sort_temp, total;
     __host__ __device__ explicit BinLayout(long long N) {
         size_t n = (size_t)(N > 0 ? N : 0);
         size_t o = 0;
-        keysX = o; o = align_up(o + 8 * n);
-        keysY = o; o = align_up(o + 8 * n);
+        tilesX = o; o = align_up(o + 4 * n);
+        tilesY = o; o = align_up(o + 4 * n);
         valsX = o; o = align_up(o + 4 * n);
         valsY = o; o = align_up(o + 4 * n);
         sort_temp = o; o = align_up(o + sort_temp_bytes(N));
@@ -112,14 +125,14 @@ struct BinLayout {
 };
 
 struct BinPtrs {
-    uint64_t *keysX, *keysY; uint32_t *valsX, *valsY; void* sort_temp; size_t sort_temp_bytes;
+    uint32_t *tilesX, *tilesY, *valsX, *valsY; void* sort_temp; size_t sort_temp_bytes;
 };
 
 inline BinPtrs bin_ptrs(const void* buf, long long N) {
     BinLayout L(N);
     char* b = aligned_base(buf);
     BinPtrs p;
-    p.keysX = (uint64_t*)(b + L.keysX); p.keysY = (uint64_t*)(b + L.keysY);
+    p.tilesX = (uint32_t*)(b + L.tilesX); p.tilesY = (uint32_t*)(b + L.tilesY);
     p.valsX = (uint32_t*)(b + L.valsX); p.valsY = (uint32_t*)(b + L.valsY);
     p.sort_temp = (void*)(b + L.sort_temp); p.sort_temp_bytes = sort_temp_bytes(N);
     return p;
@@ -210,15 +223,22 @@ struct SortPlan {
 };
 SortPlan make_sort_plan(int end_bit);
 
-void launch_duplicate(const GeomPtrs& g, int P, const int* radii, int tile, int grid_x, int grid_y,
-                      uint64_t* keys, uint32_t* vals, uint32_t* hist /* [passes][512] or null */, const SortPlan& plan, cudaStream_t s);
+void launch_depth_keys(int P, const float* depths, const uint32_t* tiles_touched, uint32_t* keys, cudaStream_t s);
+void launch_order_block_sums(int P, const uint32_t* order, const uint32_t* tiles_touched, uint32_t* sums, cudaStream_t s);
+void launch_scan_u32(const uint32_t* sums, uint32_t* offsets, int n, cudaStream_t s);
+void launch_emit_pairs(const GeomPtrs& g, int P, const uint32_t* order, const uint32_t* block_offsets, const int* radii, int tile,
+                       int grid_x, int grid_y, uint32_t* tiles, uint32_t* vals, uint32_t* hist, const SortPlan& plan, cudaStream_t s);
 // stable LSD sort of n pairs.  Reads (kin,vin), ends in (kout,vout), uses (ktmp,vtmp) as the ping-pong partner.
-// kin may alias ktmp (in-place use): pass order is in -> b1 -> b2 -> b1 ... with b1 = out when the pass count is
-// odd, tmp when it is even, so the last pass always writes `out`.
+// Pass order is in -> b1 -> b2 -> b1 ... with b1 = out when the pass count is odd, tmp when it is even, so the last
+// pass always writes `out`.  In-place use: kin may alias ktmp when the count is odd and kout when it is even (never
+// b1).  vin == nullptr: values = 0..n-1.
 int launch_onesweep(const uint64_t* kin, const uint32_t* vin, uint64_t* kout, uint32_t* vout, uint64_t* ktmp, uint32_t* vtmp,
                     long long n, const SortPlan& plan, void* temp, size_t temp_bytes, bool hist_ready, uint32_t* err_flag, cudaStream_t s);
+int launch_onesweep32(const uint32_t* kin, const uint32_t* vin, uint32_t* kout, uint32_t* vout, uint32_t* ktmp, uint32_t* vtmp,
+                      long long n, const SortPlan& plan, void* temp, size_t temp_bytes, bool hist_ready, uint32_t* err_flag,
+                      int prof_slot0, cudaStream_t s);
 uint32_t* sort_hist_ptr(void* temp);
-void launch_tile_ranges(const uint64_t* keys_sorted, long long n, uint2* ranges, uint32_t* n_intersections, int num_tiles, cudaStream_t s);
+void launch_tile_ranges(const uint32_t* tiles_sorted, long long n, uint2* ranges, uint32_t* n_intersections, int num_tiles, cudaStream_t s);
 
 void launch_amr_levels(const ImgPtrs& im, int num_tiles, cudaStream_t s);
 void launch_fovea_levels(const ImgPtrs& im, int num_tiles, int fovea_step, const gsr_gaze* gaze, cudaStream_t s);

@@ -344,12 +344,17 @@ __global__ void __launch_bounds__(1024) block_scan_kernel(const uint32_t* __rest
     }
     if (tid == 0) {
         offsets[n] = s_carry;
-        header->magic = kGeomMagic; header->P = P; header->num_rendered = s_carry;   // sort_error: zeroed by the host memset
+        if (header) { header->magic = kGeomMagic; header->P = P; header->num_rendered = s_carry; }   // sort_error: zeroed by the host memset
     }
 }
 
 void launch_block_scan(const GeomPtrs& g, int P, cudaStream_t s) {
     block_scan_kernel<<<1, 1024, 0, s>>>(g.block_sums, g.block_offsets, g.nblocks, g.header, (uint32_t)P);
+    count_launch();
+}
+
+void launch_scan_u32(const uint32_t* sums, uint32_t* offsets, int n, cudaStream_t s) {
+    block_scan_kernel<<<1, 1024, 0, s>>>(sums, offsets, n, nullptr, 0u);
     count_launch();
 }
 

@@ -36,6 +36,7 @@ def geom_view(geom: torch.Tensor, P: int) -> dict:
         rgb=_slice(geom, v.rgb, 12 * P, torch.float32).view(P, 3),
         tiles_touched=_slice(geom, v.tiles_touched, 4 * P, torch.int32),
         block_offsets=_slice(geom, v.block_offsets, 4 * (nblk + 1), torch.int32),
+        depth_order=_slice(geom, v.depth_order, 4 * P, torch.int32),
         num_rendered=_slice(geom, v.num_rendered, 4, torch.int32),
     )
 
@@ -43,8 +44,15 @@ def geom_view(geom: torch.Tensor, P: int) -> dict:
 def binning_view(binning: torch.Tensor, N: int) -> dict:
     v = GsrBinningView()
     _capi.check(lib.gsr_view_binning(C.c_void_p(binning.data_ptr()), N, C.byref(v)), "gsr_view_binning")
-    return dict(keys=_slice(binning, v.keys_sorted, 8 * N, torch.int64),
+    return dict(tiles=_slice(binning, v.tiles_sorted, 4 * N, torch.int32),
                 point_list=_slice(binning, v.point_list, 4 * N, torch.int32))
+
+
+def sorted_keys(tiles: torch.Tensor, point_list: torch.Tensor, depths: torch.Tensor) -> torch.Tensor:
+    """The reference's sorted 64-bit keys (tile << 32 | depth bits, rasterizer_impl.cu:102-105) recomposed from the
+    hierarchical sort's outputs, for bit-exact comparison."""
+    d = depths.view(torch.int32)[point_list.long()].long() & 0xFFFFFFFF
+    return (tiles.long() << 32) | d
 
 
 def image_view(image: torch.Tensor, W: int, H: int, amr: bool) -> dict:

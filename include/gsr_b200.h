@@ -155,15 +155,17 @@ typedef struct gsr_geom_view {
     const float* rgb;               /* [P,3] */
     const uint32_t* tiles_touched;  /* [P]   */
     const uint32_t* block_offsets;  /* [ceil(P/256)] exclusive offsets of 256-Gaussian blocks */
+    const uint32_t* depth_order;    /* [P] Gaussian ids sorted by depth bits (invisible last)  */
     const uint32_t* num_rendered;   /* [1]   */
 } gsr_geom_view;
 
 typedef struct gsr_binning_view {
     long long N;
-    const uint64_t* keys_unsorted;  /* [N] */
-    const uint32_t* values_unsorted;/* [N] */
-    const uint64_t* keys_sorted;    /* [N] */
-    const uint32_t* point_list;     /* [N] */
+    const uint64_t* keys_unsorted;  /* always NULL: unsorted pairs are consumed by the ping-pong passes      */
+    const uint32_t* values_unsorted;/* always NULL                                                          */
+    const uint32_t* tiles_sorted;   /* [N] tile id of every sorted pair; the reference's 64-bit key is      */
+                                    /*     (tiles_sorted[i] << 32) | depth_bits[point_list[i]]              */
+    const uint32_t* point_list;     /* [N] Gaussian id of every sorted pair (reference: point_list)         */
 } gsr_binning_view;
 
 typedef struct gsr_image_view {
@@ -197,7 +199,7 @@ GSR_API unsigned gsr_higher_msb(unsigned n);
 /* ---- per-stage device timing (CUDA events on the caller's stream, recorded inside real calls) ---- */
 enum {
     GSR_PROF_PREPROCESS = 0, GSR_PROF_SCAN, GSR_PROF_DUPLICATE, GSR_PROF_SORT, GSR_PROF_RANGES, GSR_PROF_BLEND,
-    GSR_PROF_AMR_LEVELS, GSR_PROF_AMR_BLEND, GSR_PROF_BWD_BLEND, GSR_PROF_BWD_PREPROCESS,
+    GSR_PROF_AMR_LEVELS, GSR_PROF_AMR_BLEND, GSR_PROF_BWD_BLEND, GSR_PROF_BWD_PREPROCESS, GSR_PROF_DEPTH_SORT,
     GSR_PROF_SORT_PASS0,                      /* .. GSR_PROF_SORT_PASS0 + 7: individual onesweep launches */
     GSR_PROF_SLOTS = GSR_PROF_SORT_PASS0 + 8
 };

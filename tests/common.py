@@ -126,6 +126,7 @@ def run_ours(sc, cam, dL_dpix=None, dev="cuda"):
         out.update(views.geom_view(geom, P))
         out["radii"] = radii
         out.update(views.binning_view(binning, N))
+        out["keys"] = views.sorted_keys(out["tiles"], out["point_list"], out["depths"])   # reference's (tile << 32 | depth) keys
         out.update(views.image_view(img, cam.image_width, cam.image_height, False))
     if dL_dpix is not None:
         g = _host.rasterize_gaussians_backward(
@@ -244,6 +245,7 @@ def run_ours_amr(sc, cam, stepped, interpolate, gaze=None, dev="cuda"):
     out.update(views.geom_view(gb, P))
     out["radii"] = radii
     out.update(views.binning_view(bb, N))
+    out["keys"] = views.sorted_keys(out["tiles"], out["point_list"], out["depths"])
     out.update(views.image_view(ib, cam.image_width, cam.image_height, True))
     torch.cuda.synchronize()
     return out
