@@ -34,7 +34,7 @@ sys.path.insert(0, ROOT)
 
 import torch  # noqa: E402
 
-ALG_BYTES_PER_PAIR_PER_PASS = 24      # 8 B key + 4 B value, read once and written once per onesweep pass
+ALG_BYTES_PER_PAIR_PER_PASS = 16      # 4 B tile id + 4 B Gaussian id, read once and written once per onesweep pass
 
 
 def parse_args():
@@ -452,7 +452,7 @@ def main():
         if passes and N:
             t_pass = sum(st[k] for k in passes) / len(passes)
             ach = ALG_BYTES_PER_PAIR_PER_PASS * N / (t_pass * 1e-3) / 1e9
-            line["roofline"] = {"kernel": "onesweep_kernel (one radix pass of the tile/depth key sort)", "bound": "hbm",
+            line["roofline"] = {"kernel": "onesweep_kernel<u32> (one radix pass of the (tile, Gaussian) pair partition)", "bound": "hbm",
                                 "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None,
                                 "peak_source": peak_src, "launch_ms": t_pass, "pairs_per_launch": N,
                                 "alg_bytes_per_pair": ALG_BYTES_PER_PAIR_PER_PASS, "passes": len(passes)}

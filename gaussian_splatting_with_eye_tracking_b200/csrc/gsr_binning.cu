@@ -140,12 +140,16 @@ __global__ void __launch_bounds__(kDupThreads) emit_pairs_kernel(const EmitParam
                 p.tiles[(size_t)gbase + q] = tile_id;
                 p.vals[(size_t)gbase + q] = s_id[lo];
             }
+            // digit histograms of the tile ids: a warp's pairs are mostly one Gaussian's row of consecutive tiles, i.e.
+            // all-distinct low digits (plain shared atomics, no conflicts) and one common high digit (one atomic per warp)
             const uint32_t act = __ballot_sync(0xffffffffu, valid);
             if (valid) {
                 for (int ps = 0; ps < p.passes; ++ps) {
                     const uint32_t d = (tile_id >> p.shift[ps]) & ((1u << p.bits[ps]) - 1u);
-                    const uint32_t peers = __match_any_sync(act, d);
-                    if (lane == (31 - __clz(peers))) atomicAdd(&s_hist[ps * kSortMaxRadix + d], (uint32_t)__popc(peers));
+                    int uniform = 0;
+                    __match_all_sync(act, d, &uniform);
+                    if (uniform) { if (lane == (31 - __clz(act))) atomicAdd(&s_hist[ps * kSortMaxRadix + d], (uint32_t)__popc(act)); }
+                    else atomicAdd(&s_hist[ps * kSortMaxRadix + d], 1u);
                 }
             }
         }
@@ -267,6 +271,22 @@ struct SweepParams {
     uint32_t* err_flag;
 };
 
+// lanes whose digit equals mine, built from one ballot per digit bit: constant cost whatever the number of distinct
+// digits in the warp (the hardware MATCH.ANY degrades with digit diversity, which is the common case here)
+template <int BITS>
+__device__ __forceinline__ uint32_t match_digit(uint32_t d) {
+    uint32_t peers = 0xffffffffu;
+#pragma unroll
+    for (int b = 0; b < BITS; ++b) {
+        const uint32_t bal = __ballot_sync(0xffffffffu, (d >> b) & 1u);
+        peers &= ((d >> b) & 1u) ? bal : ~bal;
+    }
+    return peers;
+}
+
+template <int R> struct Log2 { static constexpr int v = 1 + Log2<R / 2>::v; };
+template <> struct Log2<1> { static constexpr int v = 0; };
+
 template <typename KeyT, int RADIX>
 __global__ void __launch_bounds__(SORT_THREADS, 2) onesweep_kernel(const SweepParams<KeyT> p) {
     constexpr int ITEMS = SortCfg<KeyT>::ITEMS;
@@ -316,7 +336,7 @@ __global__ void __launch_bounds__(SORT_THREADS, 2) onesweep_kernel(const SweepPa
 #pragma unroll
     for (int i = 0; i < ITEMS; ++i) {
         const uint32_t d = (uint32_t)(key[i] >> p.shift) & mask;
-        const uint32_t peers = __match_any_sync(0xffffffffu, d);
+        const uint32_t peers = match_digit<Log2<RADIX>::v>(d);
         const uint32_t pre = wh[d];
         __syncwarp();
         if ((peers & lt) == 0) wh[d] = pre + __popc(peers);
