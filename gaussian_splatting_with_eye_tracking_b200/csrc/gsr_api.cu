@@ -181,7 +181,7 @@ static int build_lists(const gsr_scene* sc, const gsr_camera* cam, int mode, gsr
         uint32_t* hist = sort_hist_ptr(b.sort_temp);
         if ((rc = check_cuda(cudaMemsetAsync(hist, 0, sizeof(uint32_t) * kSortMaxPasses * kSortMaxRadix, s), "memset hist"))) return rc;
         { ProfScope ps(GSR_PROF_DUPLICATE, s);
-          launch_emit_pairs(g, P, g.order, g.oblock_offsets, a.radii, im.tile, im.tiles_x, im.tiles_y, t_start, v_start, hist, plan, s); }
+          launch_emit_pairs(g, P, N, g.order, g.oblock_offsets, a.radii, im.tile, im.tiles_x, im.tiles_y, t_start, v_start, hist, plan, s); }
         if ((rc = check_last("emit pairs", debug, s))) return rc;
         {
             ProfScope ps(GSR_PROF_SORT, s);
@@ -210,7 +210,11 @@ size_t gsr_sort_temp_bytes(long long n) { return sort_temp_bytes(n) + kAlign; }
 unsigned gsr_higher_msb(unsigned n) { return higher_msb(n); }
 unsigned long long gsr_launch_count(void) { return g_launches.load(); }
 
-void gsr_profile_enable(int on) { std::lock_guard<std::mutex> lk(g_prof_mu); g_prof_on = on != 0; }
+void gsr_profile_enable(int on) {
+    std::lock_guard<std::mutex> lk(g_prof_mu);
+    g_prof_on = on != 0;
+    if (g_prof_on) while (g_prof_pool.size() < 2048) { cudaEvent_t e = nullptr; if (cudaEventCreate(&e) != cudaSuccess) break; g_prof_pool.push_back(e); }
+}
 
 int gsr_profile_read(float* ms, int* counts) {
     std::lock_guard<std::mutex> lk(g_prof_mu);

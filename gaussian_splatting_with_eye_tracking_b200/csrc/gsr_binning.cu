@@ -67,11 +67,12 @@ __global__ void __launch_bounds__(kPreBlock) order_block_sums_kernel(int P, cons
 
 struct EmitParams {
     int P, nblocks, tile, grid_x, grid_y;
+    uint32_t N;
     const uint32_t* __restrict__ order;          // depth-sorted Gaussian ids
     const int* __restrict__ radii;
     const float2* __restrict__ means2D;
     const uint32_t* __restrict__ tiles_touched;
-    const uint32_t* __restrict__ block_offsets;  // exclusive offsets of the sorted 256-blocks
+    const uint32_t* __restrict__ block_offsets;  // [nblocks+1] exclusive offsets of the sorted 256-blocks, [nblocks] = N
     uint32_t* __restrict__ tiles;                // out: tile id of every pair
     uint32_t* __restrict__ vals;                 // out: Gaussian id of every pair
     uint32_t* hist;                              // [passes][kSortMaxRadix] global digit counts of the tile ids
@@ -79,11 +80,13 @@ struct EmitParams {
 };
 
 constexpr int kDupThreads = 256;
+constexpr uint32_t kEmitChunk = 8192;            // output pairs per CTA
 
-// Persistent grid over 256-Gaussian blocks (sorted order).  One thread per PAIR: the block's tiles_touched are
-// scanned in shared memory, thread q finds its Gaussian by bisection and its tile by a reciprocal multiply,
-// stores are fully coalesced, fat Gaussians do not serialise a warp (reference: one thread per Gaussian,
-// rasterizer_impl.cu:70-111).
+// One CTA per fixed-size chunk of the OUTPUT (perfectly balanced however fat individual Gaussians are: in depth
+// order the nearest, largest splats are adjacent).  The CTA finds the 256-Gaussian blocks that overlap its chunk,
+// scans each block's tiles_touched in shared memory, and then works one thread per PAIR: bisection for the
+// Gaussian, reciprocal multiply for the tile, fully coalesced stores (reference: one thread per Gaussian looping
+// over its rect, rasterizer_impl.cu:70-111).
 __global__ void __launch_bounds__(kDupThreads) emit_pairs_kernel(const EmitParams p) {
     extern __shared__ uint32_t s_hist[];            // [passes][kSortMaxRadix]
     __shared__ uint32_t s_off[kPreBlock + 1];
@@ -93,7 +96,17 @@ __global__ void __launch_bounds__(kDupThreads) emit_pairs_kernel(const EmitParam
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     for (int i = tid; i < p.passes * kSortMaxRadix; i += kDupThreads) s_hist[i] = 0;
 
-    for (int blk = blockIdx.x; blk < p.nblocks; blk += gridDim.x) {
+    const uint32_t c_lo = blockIdx.x * kEmitChunk;
+    const uint32_t c_hi = min(p.N, c_lo + kEmitChunk);
+    // last block whose first pair is at or before c_lo (ties = empty blocks: take the last one)
+    int lo = 0, hi = p.nblocks;                     // invariant: block_offsets[lo] <= c_lo < block_offsets[hi] (= N at nblocks)
+    while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (__ldg(p.block_offsets + mid) <= c_lo) lo = mid; else hi = mid; }
+
+    for (int blk = lo; blk < p.nblocks; ++blk) {
+        const uint32_t gbase = __ldg(p.block_offsets + blk);
+        if (gbase >= c_hi) break;
+        const uint32_t gnext = __ldg(p.block_offsets + blk + 1);
+        if (gnext == gbase) continue;               // empty block (CTA-uniform)
         __syncthreads();                            // previous iteration's smem readers are done
         const int j = blk * kPreBlock + tid;
         uint32_t t = 0;
@@ -120,25 +133,24 @@ __global__ void __launch_bounds__(kDupThreads) emit_pairs_kernel(const EmitParam
         if (tid == kDupThreads - 1) s_off[kPreBlock] = wbase + inc;
         __syncthreads();
 
-        const uint32_t total = s_off[kPreBlock];
-        const uint32_t gbase = p.block_offsets[blk];
-        for (uint32_t q0 = 0; q0 < total; q0 += kDupThreads) {
+        const uint32_t q_lo = max(c_lo, gbase) - gbase, q_hi = min(c_hi, gnext) - gbase;   // this block's pairs inside my chunk
+        for (uint32_t q0 = q_lo; q0 < q_hi; q0 += kDupThreads) {
             const uint32_t q = q0 + tid;
-            const bool valid = q < total;
+            const bool valid = q < q_hi;
             uint32_t tile_id = 0;
             if (valid) {
-                // largest g with s_off[g] <= q  (s_off non-decreasing, s_off[256] = total > q)
-                int lo = 0, hi = kPreBlock;
+                // largest g with s_off[g] <= q  (s_off non-decreasing, s_off[256] = block total > q)
+                int a = 0, b = kPreBlock;
 #pragma unroll
-                for (int it = 0; it < 8; ++it) { const int mid = (lo + hi) >> 1; if (s_off[mid] <= q) lo = mid; else hi = mid; }
-                const uint32_t k = q - s_off[lo];
-                const uint32_t w = s_w[lo];
-                uint32_t row = (uint32_t)(((float)k + 0.5f) * s_invw[lo]);      // k / w for k < 2^22 (tiles per Gaussian)
+                for (int it = 0; it < 8; ++it) { const int mid = (a + b) >> 1; if (s_off[mid] <= q) a = mid; else b = mid; }
+                const uint32_t k = q - s_off[a];
+                const uint32_t w = s_w[a];
+                uint32_t row = (uint32_t)(((float)k + 0.5f) * s_invw[a]);       // k / w for k < 2^22 (tiles per Gaussian)
                 uint32_t col = k - row * w;
                 if (col >= w) { row += 1; col -= w; }                            // guard against a 1-ulp reciprocal
-                tile_id = (s_y0[lo] + row) * (uint32_t)p.grid_x + s_x0[lo] + col;
+                tile_id = (s_y0[a] + row) * (uint32_t)p.grid_x + s_x0[a] + col;
                 p.tiles[(size_t)gbase + q] = tile_id;
-                p.vals[(size_t)gbase + q] = s_id[lo];
+                p.vals[(size_t)gbase + q] = s_id[a];
             }
             // digit histograms of the tile ids: a warp's pairs are mostly one Gaussian's row of consecutive tiles, i.e.
             // all-distinct low digits (plain shared atomics, no conflicts) and one common high digit (one atomic per warp)
@@ -181,16 +193,15 @@ void launch_order_block_sums(int P, const uint32_t* order, const uint32_t* tiles
     count_launch();
 }
 
-void launch_emit_pairs(const GeomPtrs& g, int P, const uint32_t* order, const uint32_t* block_offsets, const int* radii, int tile,
+void launch_emit_pairs(const GeomPtrs& g, int P, long long N, const uint32_t* order, const uint32_t* block_offsets, const int* radii, int tile,
                        int grid_x, int grid_y, uint32_t* tiles, uint32_t* vals, uint32_t* hist, const SortPlan& plan, cudaStream_t s) {
     EmitParams p;
-    p.P = P; p.nblocks = g.nblocks; p.tile = tile; p.grid_x = grid_x; p.grid_y = grid_y;
+    p.P = P; p.N = (uint32_t)N; p.nblocks = g.nblocks; p.tile = tile; p.grid_x = grid_x; p.grid_y = grid_y;
     p.order = order; p.radii = radii; p.means2D = g.means2D; p.tiles_touched = g.tiles_touched;
     p.block_offsets = block_offsets; p.tiles = tiles; p.vals = vals; p.hist = hist;
     p.passes = plan.passes;
     for (int i = 0; i < kSortMaxPasses; ++i) { p.shift[i] = i < plan.passes ? plan.shift[i] : 0; p.bits[i] = i < plan.passes ? plan.bits[i] : 1; }
-    int grid = num_sms() * 6;
-    if (grid > g.nblocks) grid = g.nblocks;
+    const int grid = (int)((N + kEmitChunk - 1) / kEmitChunk);
     if (grid < 1) return;
     emit_pairs_kernel<<<grid, kDupThreads, sizeof(uint32_t) * plan.passes * kSortMaxRadix, s>>>(p);
     count_launch();

@@ -226,7 +226,7 @@ SortPlan make_sort_plan(int end_bit);
 void launch_depth_keys(int P, const float* depths, const uint32_t* tiles_touched, uint32_t* keys, cudaStream_t s);
 void launch_order_block_sums(int P, const uint32_t* order, const uint32_t* tiles_touched, uint32_t* sums, cudaStream_t s);
 void launch_scan_u32(const uint32_t* sums, uint32_t* offsets, int n, cudaStream_t s);
-void launch_emit_pairs(const GeomPtrs& g, int P, const uint32_t* order, const uint32_t* block_offsets, const int* radii, int tile,
+void launch_emit_pairs(const GeomPtrs& g, int P, long long N, const uint32_t* order, const uint32_t* block_offsets, const int* radii, int tile,
                        int grid_x, int grid_y, uint32_t* tiles, uint32_t* vals, uint32_t* hist, const SortPlan& plan, cudaStream_t s);
 // stable LSD sort of n pairs.  Reads (kin,vin), ends in (kout,vout), uses (ktmp,vtmp) as the ping-pong partner.
 // Pass order is in -> b1 -> b2 -> b1 ... with b1 = out when the pass count is odd, tmp when it is even, so the last
