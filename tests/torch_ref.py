@@ -102,3 +102,21 @@ def render(means3D, scales, rotations, opacities, shs, deg, view_t, proj_t, camp
         rows.append(torch.stack(cols, 1))
     img = torch.stack(rows, 1)
     return img
+
+
+def autograd_grads(sc, cam, st, dL_dpix):
+    """float64 autograd gradients of sum(img * dL_dpix) w.r.t. the five parameter tensors.  `st` is the oracle's
+    forward state (per-tile ordered lists come from its ranges / point_list)."""
+    import numpy as np
+    dt = torch.float64
+    leaves = {k: sc[k].detach().to(dt).clone().requires_grad_(True) for k in ("means3D", "scales", "rotations", "opacities", "shs")}
+    ranges = np.asarray(st.ranges).reshape(-1, 2)
+    pl = np.asarray(st.point_list)
+    tile_lists = [pl[a:b].astype(np.int64).tolist() for a, b in ranges]
+    img = render(leaves["means3D"], leaves["scales"], leaves["rotations"], leaves["opacities"], leaves["shs"], sc["sh_degree"],
+                 cam.world_view_transform.to(dt), cam.full_proj_transform.to(dt), cam.camera_center.to(dt),
+                 cam.image_width, cam.image_height, cam.tanfovx, cam.tanfovy, sc["bg"].to(dt), tile_lists)
+    (img * dL_dpix.to(dt)).sum().backward()
+    return dict(dL_dmeans3D=leaves["means3D"].grad.numpy(), dL_dopacity=leaves["opacities"].grad.numpy(),
+                dL_dscales=leaves["scales"].grad.numpy(), dL_drotations=leaves["rotations"].grad.numpy(),
+                dL_dsh=leaves["shs"].grad.numpy())
