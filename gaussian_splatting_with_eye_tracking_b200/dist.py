@@ -1,0 +1,228 @@
+"""Multi-GPU plumbing for the two ways the rasterizer shards; one process per GPU, torch.distributed.
+
+* **Data-parallel views (config C4).**  Parameters are replicated; rank r renders view r forward+backward; the five
+  parameter-gradient tensors (means3D 3 + sh 48 + opacity 1 + scales 3 + rotations 4 = 59 floats per Gaussian) are
+  summed with bucketed asynchronous all-reduces on a side stream so that the reduction of one bucket overlaps the
+  flattening of the next (and, for a caller that defers ``wait()``, the next view's forward).  The per-view
+  densification statistic of the reference (``scene/gaussian_model.py:405-407``: ``||means2D.grad[:, :2]||`` and a
+  visibility count) is reduced as 2 floats per Gaussian instead of the 3-float dummy gradient.
+* **Screen-tile bands (config C5).**  Tiles are independent after binning, so a frame is split into contiguous
+  rows of binning tiles, balanced by the per-row pair counts of the previous frame (the foveal band is heavier).
+  The only cross-rank data on the path is the per-tile pair count (AMR percentiles are global, so every rank needs
+  all counts to obtain levels bit-identical to the single-GPU result) and the final gather of the bands.
+
+NCCL on GPUs; the same code runs under gloo on CPU tensors for the host-logic tests (tests/test_cpu_dist.py).
+"""
+from __future__ import annotations
+
+import os
+from typing import Iterable, List, Optional, Sequence, Tuple
+
+import torch
+import torch.distributed as dist
+
+GRAD_FLOATS_PER_GAUSSIAN = 59          # 3 + 48 + 1 + 3 + 4
+DEFAULT_BUCKET_BYTES = 128 << 20       # NVSwitch: size buckets for launch latency and overlap, not link count
+
+
+def init(backend: Optional[str] = None) -> Tuple[int, int]:
+    """Initialise the default process group from the torchrun environment.  Returns (rank, world)."""
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    if world > 1 and not dist.is_initialized():
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        if backend is None:
+            backend = "nccl" if torch.cuda.is_available() else "gloo"
+        kw = {}
+        if backend == "nccl":
+            local = int(os.environ.get("LOCAL_RANK", rank))
+            torch.cuda.set_device(local)
+            kw["device_id"] = torch.device("cuda", local)
+        dist.init_process_group(backend, **kw)
+    return rank, world
+
+
+def world_size() -> int:
+    return dist.get_world_size() if dist.is_initialized() else 1
+
+
+# ----------------------------------------------------------------------------------------------------------------
+# data-parallel views
+# ----------------------------------------------------------------------------------------------------------------
+def plan_buckets(numels: Sequence[int], bucket_bytes: int = DEFAULT_BUCKET_BYTES, itemsize: int = 4) -> List[List[Tuple[int, int, int]]]:
+    """Split tensors (given by element counts) into buckets of at most ``bucket_bytes``.  A bucket is a list of
+    (tensor index, start element, stop element); large tensors (the SH gradient is 81 % of the payload) are cut
+    so that the first bucket can be in flight while the rest is still being packed."""
+    cap = max(1, bucket_bytes // itemsize)
+    buckets, cur, room = [], [], cap
+    for ti, n in enumerate(numels):
+        start = 0
+        while start < n:
+            take = min(room, n - start)
+            cur.append((ti, start, start + take))
+            start += take
+            room -= take
+            if room == 0:
+                buckets.append(cur)
+                cur, room = [], cap
+    if cur:
+        buckets.append(cur)
+    return buckets
+
+
+class GradientAllReduce:
+    """Bucketed, asynchronous SUM all-reduce of a fixed list of gradient tensors (in place)."""
+
+    def __init__(self, bucket_bytes: int = DEFAULT_BUCKET_BYTES, group=None):
+        self.bucket_bytes = bucket_bytes
+        self.group = group
+        self._flat = {}
+        self._pending = []
+        self._stream = None
+
+    def _comm_stream(self, device):
+        if device.type != "cuda":
+            return None
+        if self._stream is None:
+            self._stream = torch.cuda.Stream(device=device)
+        return self._stream
+
+    def start(self, grads: Sequence[torch.Tensor]) -> None:
+        """Queue the reduction of ``grads`` (contiguous, same dtype/device).  Returns immediately."""
+        assert not self._pending, "previous reduction not waited for"
+        if world_size() == 1 or not grads:
+            return
+        dev, dt = grads[0].device, grads[0].dtype
+        flats = [g.view(-1) for g in grads]
+        plan = plan_buckets([f.numel() for f in flats], self.bucket_bytes, grads[0].element_size())
+        comm = self._comm_stream(dev)
+        if comm is not None:
+            comm.wait_stream(torch.cuda.current_stream(dev))       # gradients are final on the compute stream
+        ctx = torch.cuda.stream(comm) if comm is not None else _null()
+        with ctx:
+            for bi, bucket in enumerate(plan):
+                if len(bucket) == 1:                                 # a slice of one tensor: reduce in place, no copy
+                    ti, a, b = bucket[0]
+                    buf, scatter = flats[ti][a:b], None
+                else:
+                    n = sum(b - a for _, a, b in bucket)
+                    key = (bi, n, dev, dt)
+                    buf = self._flat.get(key)
+                    if buf is None:
+                        buf = self._flat[key] = torch.empty(n, dtype=dt, device=dev)
+                    o = 0
+                    for ti, a, b in bucket:
+                        buf[o:o + b - a].copy_(flats[ti][a:b]); o += b - a
+                    scatter = bucket
+                work = dist.all_reduce(buf, op=dist.ReduceOp.SUM, group=self.group, async_op=True)
+                self._pending.append((work, buf, scatter, flats))
+
+    def wait(self) -> None:
+        """Block the CURRENT stream (not the host, for NCCL) until every bucket is reduced and scattered back."""
+        for work, buf, scatter, flats in self._pending:
+            work.wait()
+            if scatter is not None:
+                o = 0
+                for ti, a, b in scatter:
+                    flats[ti][a:b].copy_(buf[o:o + b - a]); o += b - a
+        if self._stream is not None and self._pending:
+            torch.cuda.current_stream().wait_stream(self._stream)
+        self._pending = []
+
+    def __call__(self, grads: Sequence[torch.Tensor]) -> None:
+        self.start(grads)
+        self.wait()
+
+
+class _null:
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        return False
+
+
+def densification_stats(means2D_grad: torch.Tensor, radii: torch.Tensor, group=None) -> torch.Tensor:
+    """[P,2] = (sum over views of ||dL/dmeans2D[:, :2]||, number of views in which the Gaussian was visible):
+    the quantities add_densification_stats accumulates (scene/gaussian_model.py:405-407), reduced over ranks."""
+    vis = (radii > 0)
+    stat = torch.stack([means2D_grad[:, :2].norm(dim=-1) * vis, vis.to(means2D_grad.dtype)], dim=1).contiguous()
+    if world_size() > 1:
+        dist.all_reduce(stat, op=dist.ReduceOp.SUM, group=group)
+    return stat
+
+
+def view_of_rank(num_views: int, step: int, rank: int, world: int) -> int:
+    """View index rendered by ``rank`` at ``step``: consecutive blocks of ``world`` views, wrapping around."""
+    return (step * world + rank) % num_views
+
+
+# ----------------------------------------------------------------------------------------------------------------
+# screen-tile bands
+# ----------------------------------------------------------------------------------------------------------------
+def balanced_bands(row_cost: Sequence[float], world: int) -> List[Tuple[int, int]]:
+    """Cut ``len(row_cost)`` tile rows into ``world`` contiguous bands [r0, r1) of near-equal total cost.
+
+    Every rank gets at least one row while rows remain; cuts are placed where the running cost crosses k/world of
+    the total (ties to the earlier row), so equal costs give equal row counts +-1.  Deterministic: all ranks compute
+    the same partition from the same (all-reduced) costs."""
+    rows = len(row_cost)
+    if world <= 0:
+        raise ValueError("world must be positive")
+    cost = [max(0.0, float(c)) for c in row_cost]
+    total = sum(cost)
+    if total <= 0.0:
+        cost, total = [1.0] * rows, float(rows)
+    S = [0.0]
+    for c in cost:
+        S.append(S[-1] + c)
+    cuts = [0]
+    for k in range(1, world):
+        target = total * k / world
+        if rows >= world:
+            lo, hi = cuts[-1] + 1, rows - (world - k)        # every band keeps at least one row
+        else:
+            lo, hi = cuts[-1], rows
+        best = min(range(lo, hi + 1), key=lambda r: (abs(S[r] - target), r))
+        cuts.append(best)
+    cuts.append(rows)
+    return [(cuts[i], cuts[i + 1]) for i in range(world)]
+
+
+def row_costs_from_counts(n_intersections: torch.Tensor, tiles_x: int, tiles_y: int, levels: Optional[torch.Tensor] = None) -> List[float]:
+    """Per-tile-row blend cost estimate: pairs in the row, weighted by the number of lattice rounds (AMR level)."""
+    c = n_intersections.to(torch.float64).view(tiles_y, tiles_x)
+    if levels is not None:
+        c = c * levels.to(torch.float64).view(tiles_y, tiles_x).clamp(1, 4)
+    return [float(x) for x in c.sum(dim=1).cpu()]
+
+
+def allreduce_tile_counts(n_intersections: torch.Tensor, group=None) -> torch.Tensor:
+    """Bands are disjoint, so the SUM over ranks of the band-local per-tile pair counts is the global count vector
+    (8 160 x 4 B at 4K): what the AMR percentile thresholds must be taken from."""
+    if world_size() > 1:
+        dist.all_reduce(n_intersections, op=dist.ReduceOp.SUM, group=group)
+    return n_intersections
+
+
+def gather_bands(frame: torch.Tensor, bands: Sequence[Tuple[int, int]], tile_px: int, group=None) -> torch.Tensor:
+    """Assemble the full [3,H,W] frame from per-rank frames in which only the rank's band rows are valid.
+
+    Uses all_gather of equal-size padded band slabs (NCCL needs equal counts), then copies each slab into place."""
+    world = world_size()
+    if world == 1:
+        return frame
+    C_, H, W = frame.shape
+    rank = dist.get_rank(group)
+    max_rows = max(b - a for a, b in bands) * tile_px
+    a, b = bands[rank]
+    y0, y1 = min(a * tile_px, H), min(b * tile_px, H)
+    slab = torch.zeros((C_, max_rows, W), dtype=frame.dtype, device=frame.device)
+    slab[:, :y1 - y0] = frame[:, y0:y1]
+    out = [torch.empty_like(slab) for _ in range(world)]
+    dist.all_gather(out, slab, group=group)
+    full = torch.empty_like(frame)
+    for r, (ra, rb) in enumerate(bands):
+        ry0, ry1 = min(ra * tile_px, H), min(rb * tile_px, H)
+        full[:, ry0:ry1] = out[r][:, :ry1 - ry0]
+    return full

@@ -1,0 +1,164 @@
+"""Host-side logic of the multi-GPU paths on CPU: world_size-2 gloo process groups exercise the
+bucketed gradient all-reduce, the densification-statistic reduction, the global AMR tile counts and the band
+gather; the band partition and bucket plan are checked directly."""
+import os
+import socket
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from gaussian_splatting_with_eye_tracking_b200 import dist as gdist
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port, fn_name, ret):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world), LOCAL_RANK=str(rank))
+    r, w = gdist.init("gloo")
+    assert (r, w) == (rank, world)
+    try:
+        globals()[fn_name](rank, world)
+        ret[rank] = "ok"
+    except Exception as ex:      # surfaced by the parent
+        ret[rank] = f"{type(ex).__name__}: {ex}"
+    finally:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def _run(fn_name, world=2):
+    ctx = mp.get_context("spawn")
+    with ctx.Manager() as mgr:
+        ret = mgr.dict()
+        procs = [ctx.Process(target=_worker, args=(r, world, port, fn_name, ret)) for port in [_free_port()] for r in range(world)]
+        for p in procs:
+            p.start()
+        for p in procs:
+            p.join(120)
+            assert p.exitcode == 0, f"worker exit code {p.exitcode}"
+        assert dict(ret) == {r: "ok" for r in range(world)}, dict(ret)
+
+
+# ---- bodies executed inside the spawned ranks -------------------------------------------------------------------
+def _grads(rank, P=1000):
+    g = torch.Generator().manual_seed(100 + rank)
+    return [torch.randn(P, 3, generator=g), torch.randn(P, 16, 3, generator=g), torch.randn(P, 1, generator=g),
+            torch.randn(P, 3, generator=g), torch.randn(P, 4, generator=g)]
+
+
+def body_gradient_allreduce(rank, world):
+    want = [sum(_grads(r)[i] for r in range(world)) for i in range(5)]
+    for bucket_bytes in (1 << 30, 4096, 59 * 4 * 37):             # one bucket / many buckets / cuts inside tensors
+        mine = _grads(rank)
+        assert sum(t.numel() for t in mine) == gdist.GRAD_FLOATS_PER_GAUSSIAN * 1000
+        ar = gdist.GradientAllReduce(bucket_bytes=bucket_bytes)
+        ar.start(mine)
+        ar.wait()
+        for a, b in zip(mine, want):
+            assert torch.allclose(a, b, atol=1e-6), bucket_bytes
+        ar(mine)                                                     # reusable; second reduction doubles again
+        for a, b in zip(mine, want):
+            assert torch.allclose(a, world * b, atol=1e-5)
+
+
+def body_densification_stats(rank, world):
+    P = 257
+    g = torch.Generator().manual_seed(7 + rank)
+    grad = torch.randn(P, 3, generator=g)
+    radii = (torch.rand(P, generator=g) > 0.4).int() * 5
+    stat = gdist.densification_stats(grad, radii)
+    want = torch.zeros(P, 2)
+    for r in range(world):
+        g2 = torch.Generator().manual_seed(7 + r)
+        gr = torch.randn(P, 3, generator=g2)
+        ra = (torch.rand(P, generator=g2) > 0.4).int() * 5
+        want[:, 0] += gr[:, :2].norm(dim=-1) * (ra > 0)
+        want[:, 1] += (ra > 0).float()
+    assert torch.allclose(stat, want, atol=1e-6)
+
+
+def body_band_render_protocol(rank, world):
+    """The C5 protocol on synthetic per-tile data: band-local counts -> global counts -> identical partition on every
+    rank -> each rank fills its band -> gather == the full frame."""
+    tiles_x, tiles_y, tile_px, W, H = 7, 9, 32, 7 * 32 - 5, 9 * 32 - 11
+    g = torch.Generator().manual_seed(5)
+    full_counts = torch.randint(0, 4000, (tiles_y * tiles_x,), generator=g, dtype=torch.int32)
+    prev_bands = gdist.balanced_bands([1.0] * tiles_y, world)       # first frame: equal rows
+    a, b = prev_bands[rank]
+    local = torch.zeros_like(full_counts)
+    local.view(tiles_y, tiles_x)[a:b] = full_counts.view(tiles_y, tiles_x)[a:b]
+    glob = gdist.allreduce_tile_counts(local.clone())
+    assert torch.equal(glob, full_counts)
+    bands = gdist.balanced_bands(gdist.row_costs_from_counts(glob, tiles_x, tiles_y), world)
+    assert bands[0][0] == 0 and bands[-1][1] == tiles_y and all(bands[i][1] == bands[i + 1][0] for i in range(world - 1))
+    truth = torch.arange(3 * H * W, dtype=torch.float32).view(3, H, W)
+    mine = torch.zeros_like(truth)
+    y0, y1 = min(bands[rank][0] * tile_px, H), min(bands[rank][1] * tile_px, H)
+    mine[:, y0:y1] = truth[:, y0:y1]
+    out = gdist.gather_bands(mine, bands, tile_px)
+    assert torch.equal(out, truth)
+
+
+# ---- tests ---------------------------------------------------------------------------------------------------------
+def test_gradient_allreduce_gloo_world2():
+    _run("body_gradient_allreduce")
+
+
+def test_densification_stats_gloo_world2():
+    _run("body_densification_stats")
+
+
+def test_band_protocol_gloo_world2():
+    _run("body_band_render_protocol")
+
+
+def test_band_protocol_gloo_world3():
+    _run("body_band_render_protocol", world=3)
+
+
+def test_plan_buckets_covers_everything_once():
+    numels = [9, 144, 3, 9, 12, 0, 1]
+    for cap_bytes in (4, 64, 100, 1 << 20):
+        plan = gdist.plan_buckets(numels, cap_bytes, 4)
+        seen = [[0] * n for n in numels]
+        for bucket in plan:
+            assert sum(b - a for _, a, b in bucket) <= max(1, cap_bytes // 4)
+            for ti, a, b in bucket:
+                for i in range(a, b):
+                    seen[ti][i] += 1
+        assert all(all(c == 1 for c in s) for s in seen)
+
+
+def test_balanced_bands_properties():
+    assert gdist.balanced_bands([1] * 68, 8) == [(0, 8), (8, 17), (17, 25), (25, 34), (34, 42), (42, 51), (51, 59), (59, 68)]
+    # a heavy foveal band gets fewer rows
+    cost = [1] * 30 + [40] * 8 + [1] * 30
+    bands = gdist.balanced_bands(cost, 8)
+    sums = [sum(cost[a:b]) for a, b in bands]
+    assert max(sums) <= 2.0 * sum(cost) / 8
+    assert all(b > a for a, b in bands)                 # nobody idles while rows remain
+    assert min(b - a for a, b in bands) < max(b - a for a, b in bands)
+    # fewer rows than ranks / zero cost / one rank
+    assert gdist.balanced_bands([5, 5], 4)[-1][1] == 2
+    assert gdist.balanced_bands([0, 0, 0, 0], 2) == [(0, 2), (2, 4)]
+    assert gdist.balanced_bands([3, 1, 2], 1) == [(0, 3)]
+    with pytest.raises(ValueError):
+        gdist.balanced_bands([1], 0)
+
+
+def test_single_process_paths_are_noops():
+    g = _grads(0, 10)
+    keep = [t.clone() for t in g]
+    gdist.GradientAllReduce()(g)
+    assert all(torch.equal(a, b) for a, b in zip(g, keep))
+    f = torch.rand(3, 8, 8)
+    assert gdist.gather_bands(f, [(0, 1)], 32) is f
+    assert gdist.view_of_rank(8, 3, 1, 4) == 5
