@@ -88,6 +88,10 @@ typedef struct gsr_camera {
     const float* projmatrix;     /* [16] device */
     const float* cam_pos;        /* [3]  device */
     int prefiltered;
+    /* Screen-tile band (no reference counterpart): this call bins and blends only tile rows
+     * [band_row0, band_row1) of the mode's tile grid (16-px rows baseline, 32-px rows AMR).  Tile ids stay global.
+     * radii / num_rendered / out_color then describe the band only.  0,0 = whole frame (reference behaviour).  */
+    int band_row0, band_row1;
 } gsr_camera;
 
 /* Gaze extension (no reference implementation exists -- the dead tensors at
@@ -141,6 +145,17 @@ GSR_API int gsr_amr_forward(const gsr_scene* scene, const gsr_camera* cam,
                             gsr_alloc_fn alloc, void* alloc_user,
                             float* out_color, int* radii, int* num_rendered,
                             int debug, void* stream);
+
+/* ---- tile-band helpers for multi-GPU foveated frames ----
+ * After every rank has built its band with gsr_amr_forward(fovea_step = 0) and the per-tile pair counts
+ * (gsr_image_view.n_intersections) have been summed over ranks in place, gsr_amr_relevel recomputes the percentile
+ * thresholds and tile levels from those global counts (bit-identical to a single-GPU build), and
+ * gsr_amr_render_prebuilt renders the band in a single pass (all lattice rounds) from the prebuilt buffers. */
+GSR_API int gsr_amr_relevel(void* image_buffer, int width, int height, void* stream);
+GSR_API int gsr_amr_render_prebuilt(const gsr_scene* scene, const gsr_camera* cam,
+                                    const void* geom_buffer, const void* binning_buffer, void* image_buffer,
+                                    int interpolate_image, const gsr_gaze* gaze /* NULL = reference */,
+                                    float* out_color, int debug, void* stream);
 
 /* ---- read-only views into the work buffers (tests, band-parallel driver, debugging) ----
  * Fills `out` with device pointers; fields that do not exist for the buffer's mode are NULL. */
