@@ -34,7 +34,7 @@ class GsrCamera(C.Structure):
     _fields_ = [
         ("width", C.c_int), ("height", C.c_int), ("tan_fovx", C.c_float), ("tan_fovy", C.c_float),
         ("background", C.c_void_p), ("viewmatrix", C.c_void_p), ("projmatrix", C.c_void_p), ("cam_pos", C.c_void_p),
-        ("prefiltered", C.c_int),
+        ("prefiltered", C.c_int), ("band_row0", C.c_int), ("band_row1", C.c_int),
     ]
 
 
@@ -78,6 +78,9 @@ SYMBOLS = {
     "gsr_amr_forward": (C.c_int, [C.POINTER(GsrScene), C.POINTER(GsrCamera), C.c_int, C.c_void_p, C.c_void_p, C.c_void_p,
                                   C.c_void_p, C.c_int, C.POINTER(GsrGaze), ALLOC_FN, C.c_void_p, C.c_void_p, C.c_void_p,
                                   c_int_p, C.c_int, C.c_void_p]),
+    "gsr_amr_relevel": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
+    "gsr_amr_render_prebuilt": (C.c_int, [C.POINTER(GsrScene), C.POINTER(GsrCamera), C.c_void_p, C.c_void_p, C.c_void_p, C.c_int,
+                                          C.POINTER(GsrGaze), C.c_void_p, C.c_int, C.c_void_p]),
     "gsr_view_geom": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(GsrGeomView)]),
     "gsr_view_binning": (C.c_int, [C.c_void_p, C.c_longlong, C.POINTER(GsrBinningView)]),
     "gsr_view_image": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.POINTER(GsrImageView)]),
@@ -98,6 +101,11 @@ def _load() -> C.CDLL:
     if not os.path.exists(path):
         # first use in a fresh checkout: compile in-tree (needs nvcc); raises if that is impossible
         _build.build()
+    elif _build.is_stale():
+        try:                       # sources newer than the library: rebuild when a compiler is at hand
+            _build.build()
+        except RuntimeError:
+            pass                   # no nvcc here: the prebuilt library is used; a header/library mismatch raises below
     lib = C.CDLL(path)
     for name, (res, args) in SYMBOLS.items():
         fn = getattr(lib, name)          # AttributeError here = header/library mismatch: fail loudly

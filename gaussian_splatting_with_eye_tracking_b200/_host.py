@@ -59,7 +59,7 @@ class _Arena:
 
 
 def _scene_camera(background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp, viewmatrix,
-                  projmatrix, tan_fovx, tan_fovy, image_height, image_width, sh, degree, campos, prefiltered):
+                  projmatrix, tan_fovx, tan_fovy, image_height, image_width, sh, degree, campos, prefiltered, band=None):
     if means3D.ndimension() != 2 or means3D.size(1) != 3:
         raise RuntimeError("means3D must have dimensions (num_points, 3)")
     P = int(means3D.size(0))
@@ -81,7 +81,8 @@ def _scene_camera(background, means3D, colors, opacity, scales, rotations, scale
                   rotations=_p(keep.rotations), cov3D_precomp=_p(keep.cov3D), scale_modifier=float(scale_modifier))
     cam = GsrCamera(width=int(image_width), height=int(image_height), tan_fovx=float(tan_fovx), tan_fovy=float(tan_fovy),
                     background=_p(keep.bg), viewmatrix=_p(keep.view), projmatrix=_p(keep.proj), cam_pos=_p(keep.campos),
-                    prefiltered=1 if prefiltered else 0)
+                    prefiltered=1 if prefiltered else 0, band_row0=int(band[0]) if band else 0,
+                    band_row1=int(band[1]) if band else 0)
     return sc, cam, keep, P, M
 
 
@@ -94,10 +95,12 @@ def _stream():
 # ----------------------------------------------------------------------------------------------------------------
 def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp,
                         viewmatrix, projmatrix, tan_fovx, tan_fovy, image_height, image_width, sh, degree, campos,
-                        prefiltered, debug):
+                        prefiltered, debug, band=None):
+    """``band`` = (row0, row1): bin and blend only tile rows [row0, row1) (extension for multi-GPU tile bands;
+    rows of out_color outside the band are left unwritten).  None = the reference's whole-frame behaviour."""
     sc, cam, keep, P, _ = _scene_camera(background, means3D, colors, opacity, scales, rotations, scale_modifier,
                                         cov3D_precomp, viewmatrix, projmatrix, tan_fovx, tan_fovy, image_height,
-                                        image_width, sh, degree, campos, prefiltered)
+                                        image_width, sh, degree, campos, prefiltered, band)
     dev = means3D.device if means3D.is_cuda else torch.device("cuda")
     with torch.cuda.device(dev):
         out_color = torch.empty((3, int(image_height), int(image_width)), dtype=torch.float32, device=dev)
@@ -113,11 +116,11 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
 
 def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rotations, scale_modifier, cov3D_precomp,
                                  viewmatrix, projmatrix, tan_fovx, tan_fovy, dL_dout_color, sh, degree, campos,
-                                 geomBuffer, R, binningBuffer, imageBuffer, debug):
+                                 geomBuffer, R, binningBuffer, imageBuffer, debug, band=None):
     H, W = int(dL_dout_color.size(1)), int(dL_dout_color.size(2))
     sc, cam, keep, P, M = _scene_camera(background, means3D, colors, torch.empty(0), scales, rotations, scale_modifier,
                                         cov3D_precomp, viewmatrix, projmatrix, tan_fovx, tan_fovy, H, W, sh, degree,
-                                        campos, False)
+                                        campos, False, band)
     dev = means3D.device
     f32 = dict(dtype=torch.float32, device=dev)
     with torch.cuda.device(dev):
@@ -164,16 +167,15 @@ def mark_visible(means3D, viewmatrix, projmatrix):
 def rasterize_gaussians_amr(background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp,
                             viewmatrix, projmatrix, tan_fovx, tan_fovy, image_height, image_width, sh, degree, campos,
                             prefiltered, foveaStep, out_color_precomp, geomBuffer_precomp, binningBuffer_precomp,
-                            imageBuffer_precomp, interpolate_image, debug, gaze=None):
-    """``gaze`` = (cx, cy, (r1, r2, r3, r4)) enables the gaze-driven level cap (extension; None = reference)."""
+                            imageBuffer_precomp, interpolate_image, debug, gaze=None, band=None):
+    """``gaze`` = (cx, cy, (r1, r2, r3, r4)) enables the gaze-driven level cap (extension; None = reference).
+    ``band`` = (row0, row1) restricts binning and blending to 32-px tile rows [row0, row1) (extension)."""
     sc, cam, keep, P, _ = _scene_camera(background, means3D, colors, opacity, scales, rotations, scale_modifier,
                                         cov3D_precomp, viewmatrix, projmatrix, tan_fovx, tan_fovy, image_height,
-                                        image_width, sh, degree, campos, prefiltered)
+                                        image_width, sh, degree, campos, prefiltered, band)
     dev = means3D.device if means3D.is_cuda else torch.device("cuda")
     step = int(foveaStep)
-    gz = None
-    if gaze is not None:
-        gz = GsrGaze(cx=float(gaze[0]), cy=float(gaze[1]), radii=(C.c_float * 4)(*[float(r) for r in gaze[2]]))
+    gz = _gaze_struct(gaze)
     with torch.cuda.device(dev):
         out_color = torch.empty((3, int(image_height), int(image_width)), dtype=torch.float32, device=dev)
         radii = torch.empty((P,), dtype=torch.int32, device=dev)
@@ -194,6 +196,39 @@ def rasterize_gaussians_amr(background, means3D, colors, opacity, scales, rotati
         return int(rendered.value), out_color, radii, geomBuffer_precomp, binningBuffer_precomp, imageBuffer_precomp
     return (int(rendered.value), out_color, radii, arena.get(_capi.GSR_BUF_GEOM), arena.get(_capi.GSR_BUF_BINNING),
             arena.get(_capi.GSR_BUF_IMAGE))
+
+
+def _gaze_struct(gaze):
+    if gaze is None:
+        return None
+    return GsrGaze(cx=float(gaze[0]), cy=float(gaze[1]), radii=(C.c_float * 4)(*[float(r) for r in gaze[2]]))
+
+
+def amr_relevel(imageBuffer, image_height, image_width):
+    """Recompute percentile thresholds and tile levels from the per-tile pair counts stored in ``imageBuffer``
+    (after they were summed over tile-band ranks in place).  gsr_amr_relevel."""
+    with torch.cuda.device(imageBuffer.device):
+        rc = lib.gsr_amr_relevel(_p(imageBuffer), int(image_width), int(image_height), _stream())
+    _capi.check(rc, "gsr_amr_relevel")
+
+
+def amr_render_prebuilt(background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp, viewmatrix,
+                        projmatrix, tan_fovx, tan_fovy, image_height, image_width, sh, degree, campos, prefiltered,
+                        geomBuffer, binningBuffer, imageBuffer, interpolate_image, debug=False, gaze=None, band=None):
+    """Single-pass AMR render (all lattice rounds) from buffers built by ``rasterize_gaussians_amr(foveaStep=0)``.
+    gsr_amr_render_prebuilt; used by the tile-band driver after the global re-levelling."""
+    sc, cam, keep, P, _ = _scene_camera(background, means3D, colors, opacity, scales, rotations, scale_modifier,
+                                        cov3D_precomp, viewmatrix, projmatrix, tan_fovx, tan_fovy, image_height,
+                                        image_width, sh, degree, campos, prefiltered, band)
+    dev = means3D.device
+    gz = _gaze_struct(gaze)
+    with torch.cuda.device(dev):
+        out_color = torch.empty((3, int(image_height), int(image_width)), dtype=torch.float32, device=dev)
+        rc = lib.gsr_amr_render_prebuilt(C.byref(sc), C.byref(cam), _p(geomBuffer), _p(binningBuffer), _p(imageBuffer),
+                                         1 if interpolate_image else 0, C.byref(gz) if gz is not None else None,
+                                         _p(out_color), 1 if debug else 0, _stream())
+        _capi.check(rc, "gsr_amr_render_prebuilt")
+    return out_color
 
 
 # `_C`-shaped namespaces, one per reference extension module

@@ -101,6 +101,9 @@ static int validate(const gsr_scene* sc, const gsr_camera* cam, bool forward = t
         }
     }
     if (!cam->background || !cam->viewmatrix || !cam->projmatrix || !cam->cam_pos) { set_error("camera pointers are required"); return GSR_ERR_INVALID; }
+    if (cam->band_row0 < 0 || cam->band_row1 < 0 || (cam->band_row1 > 0 && cam->band_row0 >= cam->band_row1) || (cam->band_row1 == 0 && cam->band_row0 != 0)) {
+        set_error("bad tile band [%d,%d)", cam->band_row0, cam->band_row1); return GSR_ERR_INVALID;
+    }
     return GSR_OK;
 }
 
@@ -115,6 +118,7 @@ static int build_lists(const gsr_scene* sc, const gsr_camera* cam, int mode, gsr
     GeomPtrs g = geom_ptrs(geom, P);
     ImgPtrs im = img_ptrs(img, W, H, mode);
     const int num_tiles = im.tiles_x * im.tiles_y;
+    if (cam->band_row1 > im.tiles_y) { set_error("tile band [%d,%d) exceeds the %d tile rows", cam->band_row0, cam->band_row1, im.tiles_y); return GSR_ERR_INVALID; }
     int rc = check_cuda(cudaMemsetAsync(g.header, 0, sizeof(GeomHeader), s), "memset header");
     if (rc) return rc;
 
@@ -130,6 +134,7 @@ static int build_lists(const gsr_scene* sc, const gsr_camera* cam, int mode, gsr
     a.tile = im.tile; a.grid_x = im.tiles_x; a.grid_y = im.tiles_y;
     a.radii = radii_user ? radii_user : g.radii;
     a.prefiltered = cam->prefiltered != 0;
+    a.band_row0 = cam->band_row0; a.band_row1 = cam->band_row1;
     { ProfScope ps(GSR_PROF_PREPROCESS, s); launch_preprocess(a, g, s); }
     if ((rc = check_last("preprocess", debug, s))) return rc;
     { ProfScope ps(GSR_PROF_SCAN, s); launch_block_scan(g, P, s); }
@@ -181,7 +186,8 @@ static int build_lists(const gsr_scene* sc, const gsr_camera* cam, int mode, gsr
         uint32_t* hist = sort_hist_ptr(b.sort_temp);
         if ((rc = check_cuda(cudaMemsetAsync(hist, 0, sizeof(uint32_t) * kSortMaxPasses * kSortMaxRadix, s), "memset hist"))) return rc;
         { ProfScope ps(GSR_PROF_DUPLICATE, s);
-          launch_emit_pairs(g, P, N, g.order, g.oblock_offsets, a.radii, im.tile, im.tiles_x, im.tiles_y, t_start, v_start, hist, plan, s); }
+          launch_emit_pairs(g, P, N, g.order, g.oblock_offsets, a.radii, im.tile, im.tiles_x, im.tiles_y, cam->band_row0, cam->band_row1,
+                            t_start, v_start, hist, plan, s); }
         if ((rc = check_last("emit pairs", debug, s))) return rc;
         {
             ProfScope ps(GSR_PROF_SORT, s);
@@ -251,7 +257,7 @@ int gsr_forward(const gsr_scene* sc, const gsr_camera* cam, gsr_alloc_fn alloc, 
     BinPtrs b = bin_ptrs(bin, N);
     ImgPtrs im = img_ptrs(img, W, H, GSR_MODE_BASELINE);
     BlendArgs ba;
-    ba.W = W; ba.H = H; ba.ranges = im.ranges; ba.point_list = b.valsY; ba.means2D = g.means2D;
+    ba.W = W; ba.H = H; ba.row0 = cam->band_row0; ba.row1 = cam->band_row1; ba.ranges = im.ranges; ba.point_list = b.valsY; ba.means2D = g.means2D;
     ba.conic_opacity = g.conic_opacity; ba.colors = sc->colors_precomp ? sc->colors_precomp : g.rgb;
     ba.bg = cam->background; ba.final_T = im.accum_alpha; ba.n_contrib = im.n_contrib; ba.out_color = out_color;
     { ProfScope ps(GSR_PROF_BLEND, s); launch_blend_forward(ba, s); }
@@ -282,7 +288,7 @@ int gsr_backward(const gsr_scene* sc, const gsr_camera* cam, const int* radii, c
 
     if ((rc = check_cuda(cudaMemsetAsync(gr->scratch, 0, sizeof(float) * 12 * (size_t)P, s), "memset scratch"))) return rc;
     BlendBwdArgs bb;
-    bb.W = W; bb.H = H; bb.ranges = im.ranges; bb.point_list = b.valsY; bb.means2D = g.means2D;
+    bb.W = W; bb.H = H; bb.row0 = cam->band_row0; bb.row1 = cam->band_row1; bb.ranges = im.ranges; bb.point_list = b.valsY; bb.means2D = g.means2D;
     bb.conic_opacity = g.conic_opacity; bb.colors = sc->colors_precomp ? sc->colors_precomp : g.rgb;
     bb.bg = cam->background; bb.final_T = im.accum_alpha; bb.n_contrib = im.n_contrib; bb.dL_dpix = dL_dpix;
     bb.scratch = gr->scratch;
@@ -357,7 +363,7 @@ int gsr_amr_forward(const gsr_scene* sc, const gsr_camera* cam, int fovea_step, 
     if ((rc = check_last("fovea levels", debug != 0, s))) return rc;
 
     AmrBlendArgs ab;
-    ab.b.W = W; ab.b.H = H; ab.b.ranges = im.ranges; ab.b.point_list = b.valsY; ab.b.means2D = g.means2D;
+    ab.b.W = W; ab.b.H = H; ab.b.row0 = cam->band_row0; ab.b.row1 = cam->band_row1; ab.b.ranges = im.ranges; ab.b.point_list = b.valsY; ab.b.means2D = g.means2D;
     ab.b.conic_opacity = g.conic_opacity; ab.b.colors = sc->colors_precomp ? sc->colors_precomp : g.rgb;
     ab.b.bg = cam->background; ab.b.final_T = im.accum_alpha; ab.b.n_contrib = im.n_contrib; ab.b.out_color = out_color;
     // reference: steps >= 1 render with tile_AMR_levels_current, single pass with tile_AMR_levels (:401 vs :667)
@@ -366,6 +372,42 @@ int gsr_amr_forward(const gsr_scene* sc, const gsr_camera* cam, int fovea_step, 
     ab.fovea_step = fovea_step; ab.out_color_precomp = out_color_precomp; ab.interpolate = interpolate_image != 0;
     { ProfScope ps(GSR_PROF_AMR_BLEND, s); launch_blend_amr(ab, s); }
     return check_last("blend amr", debug != 0, s);
+}
+
+int gsr_amr_relevel(void* image_buffer, int W, int H, void* stream) {
+    if (!image_buffer || W <= 0 || H <= 0) { set_error("amr_relevel: bad arguments"); return GSR_ERR_INVALID; }
+    ImgPtrs im = img_ptrs(image_buffer, W, H, GSR_MODE_AMR);
+    launch_amr_levels(im, im.tiles_x * im.tiles_y, (cudaStream_t)stream);
+    return check_last("amr relevel", false, (cudaStream_t)stream);
+}
+
+int gsr_amr_render_prebuilt(const gsr_scene* sc, const gsr_camera* cam, const void* geom_buffer, const void* binning_buffer,
+                            void* image_buffer, int interpolate_image, const gsr_gaze* gaze, float* out_color, int debug, void* stream) {
+    cudaStream_t s = (cudaStream_t)stream;
+    int rc = validate(sc, cam);
+    if (rc) return rc;
+    if (!out_color) { set_error("out_color is required"); return GSR_ERR_INVALID; }
+    const int P = sc->P, W = cam->width, H = cam->height;
+    if ((rc = check_cuda(cudaMemsetAsync(out_color, 0, sizeof(float) * 3 * (size_t)W * H, s), "memset out_color"))) return rc;
+    if (P == 0) return GSR_OK;
+    if (!geom_buffer || !binning_buffer || !image_buffer) { set_error("prebuilt work buffers are required"); return GSR_ERR_WORKSPACE; }
+    GeomPtrs g = geom_ptrs(geom_buffer, P);
+    uint32_t hdr[4];
+    if ((rc = read_u32(&g.header->magic, hdr, 4, s))) return rc;
+    if (hdr[0] != kGeomMagic || hdr[1] != (uint32_t)P) { set_error("geometry buffer does not belong to this scene (magic %08x, P %u)", hdr[0], hdr[1]); return GSR_ERR_WORKSPACE; }
+    BinPtrs b = bin_ptrs(binning_buffer, (long long)hdr[2]);
+    ImgPtrs im = img_ptrs(image_buffer, W, H, GSR_MODE_AMR);
+    if (cam->band_row1 > im.tiles_y) { set_error("tile band exceeds the tile rows"); return GSR_ERR_INVALID; }
+    launch_fovea_levels(im, im.tiles_x * im.tiles_y, -1, gaze, s);
+    if ((rc = check_last("fovea levels", debug != 0, s))) return rc;
+    AmrBlendArgs ab;
+    ab.b.W = W; ab.b.H = H; ab.b.row0 = cam->band_row0; ab.b.row1 = cam->band_row1; ab.b.ranges = im.ranges; ab.b.point_list = b.valsY;
+    ab.b.means2D = g.means2D; ab.b.conic_opacity = g.conic_opacity; ab.b.colors = sc->colors_precomp ? sc->colors_precomp : g.rgb;
+    ab.b.bg = cam->background; ab.b.final_T = im.accum_alpha; ab.b.n_contrib = im.n_contrib; ab.b.out_color = out_color;
+    ab.levels = im.levels; ab.levels_last = im.levels_last; ab.fovea_step = -1; ab.out_color_precomp = nullptr;
+    ab.interpolate = interpolate_image != 0;
+    { ProfScope ps(GSR_PROF_AMR_BLEND, s); launch_blend_amr(ab, s); }
+    return check_last("blend amr (prebuilt)", debug != 0, s);
 }
 
 int gsr_view_geom(const void* geom_buffer, int P, gsr_geom_view* out) {

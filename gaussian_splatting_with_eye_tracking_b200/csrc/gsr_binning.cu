@@ -66,7 +66,7 @@ __global__ void __launch_bounds__(kPreBlock) order_block_sums_kernel(int P, cons
 }
 
 struct EmitParams {
-    int P, nblocks, tile, grid_x, grid_y;
+    int P, nblocks, tile, grid_x, grid_y, band_row0, band_row1;
     uint32_t N;
     const uint32_t* __restrict__ order;          // depth-sorted Gaussian ids
     const int* __restrict__ radii;
@@ -117,6 +117,7 @@ __global__ void __launch_bounds__(kDupThreads) emit_pairs_kernel(const EmitParam
                 const float2 xy = p.means2D[g];
                 uint32_t x0, y0, x1, y1;
                 get_rect(xy.x, xy.y, p.radii[g], p.tile, p.grid_x, p.grid_y, x0, y0, x1, y1);
+                clip_band(y0, y1, p.band_row0, p.band_row1);
                 s_x0[tid] = x0; s_y0[tid] = y0; s_w[tid] = x1 - x0; s_id[tid] = g;
                 s_invw[tid] = 1.0f / (float)(x1 - x0);
             }
@@ -194,8 +195,10 @@ void launch_order_block_sums(int P, const uint32_t* order, const uint32_t* tiles
 }
 
 void launch_emit_pairs(const GeomPtrs& g, int P, long long N, const uint32_t* order, const uint32_t* block_offsets, const int* radii, int tile,
-                       int grid_x, int grid_y, uint32_t* tiles, uint32_t* vals, uint32_t* hist, const SortPlan& plan, cudaStream_t s) {
+                       int grid_x, int grid_y, int band_row0, int band_row1, uint32_t* tiles, uint32_t* vals, uint32_t* hist,
+                       const SortPlan& plan, cudaStream_t s) {
     EmitParams p;
+    p.band_row0 = band_row0; p.band_row1 = band_row1;
     p.P = P; p.N = (uint32_t)N; p.nblocks = g.nblocks; p.tile = tile; p.grid_x = grid_x; p.grid_y = grid_y;
     p.order = order; p.radii = radii; p.means2D = g.means2D; p.tiles_touched = g.tiles_touched;
     p.block_offsets = block_offsets; p.tiles = tiles; p.vals = vals; p.hist = hist;

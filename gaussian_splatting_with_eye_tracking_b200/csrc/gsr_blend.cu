@@ -80,7 +80,7 @@ __device__ __forceinline__ int compact_slot(bool keep, uint32_t* s_wcnt, uint32_
 // forward, baseline 16x16 tiles
 // ------------------------------------------------------------------------------------------------
 struct FwdParams {
-    int W, H, tiles_x;
+    int W, H, tiles_x, row0;      // row0: first tile row of the launch (tile bands); blockIdx.y counts from it
     const uint2* __restrict__ ranges; const uint32_t* __restrict__ point_list;
     const float2* __restrict__ means2D; const float4* __restrict__ conic_opacity; const float* __restrict__ colors;
     const float* __restrict__ bg;
@@ -97,13 +97,14 @@ __global__ void __launch_bounds__(kBlendThreads) blend_fwd_kernel(const FwdParam
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     // warp = 8x4 pixel block (results do not depend on the thread->pixel map)
     const uint32_t lx = (wid & 1) * 8 + (lane & 7), ly = (wid >> 1) * 4 + (lane >> 3);
-    const uint32_t pix_x = blockIdx.x * 16 + lx, pix_y = blockIdx.y * 16 + ly;
+    const uint32_t tile_y = blockIdx.y + (uint32_t)p.row0;
+    const uint32_t pix_x = blockIdx.x * 16 + lx, pix_y = tile_y * 16 + ly;
     const bool inside = pix_x < (uint32_t)p.W && pix_y < (uint32_t)p.H;
     const float pxf = (float)pix_x, pyf = (float)pix_y;
-    const float rx0 = (float)(blockIdx.x * 16), ry0 = (float)(blockIdx.y * 16);
+    const float rx0 = (float)(blockIdx.x * 16), ry0 = (float)(tile_y * 16);
     const float rx1 = rx0 + 15.f, ry1 = ry0 + 15.f;
 
-    const uint2 range = p.ranges[blockIdx.y * p.tiles_x + blockIdx.x];
+    const uint2 range = p.ranges[tile_y * p.tiles_x + blockIdx.x];
     const int todo = (int)(range.y - range.x);
     const int rounds = (todo + kBlendThreads - 1) / kBlendThreads;
 
@@ -166,7 +167,11 @@ void launch_blend_forward(const BlendArgs& a, cudaStream_t s) {
     p.W = a.W; p.H = a.H; p.tiles_x = (a.W + 15) / 16;
     p.ranges = a.ranges; p.point_list = a.point_list; p.means2D = a.means2D; p.conic_opacity = a.conic_opacity;
     p.colors = a.colors; p.bg = a.bg; p.final_T = a.final_T; p.n_contrib = a.n_contrib; p.out_color = a.out_color;
-    dim3 grid((a.W + 15) / 16, (a.H + 15) / 16, 1);
+    const int tiles_y = (a.H + 15) / 16;
+    const int r0 = a.row1 > 0 ? a.row0 : 0, r1 = a.row1 > 0 ? a.row1 : tiles_y;
+    if (r1 <= r0) return;
+    p.row0 = r0;
+    dim3 grid((a.W + 15) / 16, r1 - r0, 1);
     blend_fwd_kernel<<<grid, kBlendThreads, 0, s>>>(p);
     count_launch();
 }
@@ -188,7 +193,8 @@ __global__ void __launch_bounds__(kBlendThreads) blend_amr_kernel(const AmrParam
     __shared__ uint32_t s_wcnt[kBlendThreads / 32];
     __shared__ uint32_t s_count;
 
-    const int tile_id = blockIdx.y * p.tiles_x + blockIdx.x;
+    const uint32_t tile_y = blockIdx.y + (uint32_t)p.row0;
+    const int tile_id = tile_y * p.tiles_x + blockIdx.x;
     const uint32_t last = q.levels_last[tile_id];
     uint32_t level = q.levels[tile_id];
     if (level <= last) return;                  // A/forward.cu:285-288
@@ -199,8 +205,8 @@ __global__ void __launch_bounds__(kBlendThreads) blend_amr_kernel(const AmrParam
 
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const uint32_t qx = (wid & 1) * 8 + (lane & 7), qy = (wid >> 1) * 4 + (lane >> 3);   // quad coords 0..15
-    const uint32_t bx = blockIdx.x * 32 + 2 * qx, by = blockIdx.y * 32 + 2 * qy;
-    const float rx0 = (float)(blockIdx.x * 32), ry0 = (float)(blockIdx.y * 32);
+    const uint32_t bx = blockIdx.x * 32 + 2 * qx, by = tile_y * 32 + 2 * qy;
+    const float rx0 = (float)(blockIdx.x * 32), ry0 = (float)(tile_y * 32);
     const float rx1 = rx0 + 31.f, ry1 = ry0 + 31.f;
 
     // per-round pixel state; index k-1
@@ -285,14 +291,14 @@ __global__ void __launch_bounds__(kBlendThreads) blend_amr_kernel(const AmrParam
 // CTA of the same launch is concurrently overwriting with out_color_precomp (level <= last in stepped
 // mode), the copied-in value is used.
 struct InterpParams {
-    int W, H, tiles_x, fovea_step;
+    int W, H, tiles_x, fovea_step, y_begin, y_end;     // pixel rows [y_begin, y_end) of the launch (tile bands)
     const uint32_t* __restrict__ levels; const uint32_t* __restrict__ levels_last;
     float* final_T; uint32_t* n_contrib; float* out_color; const float* out_color_precomp;
 };
 
 __global__ void __launch_bounds__(256) interpolate_kernel(const InterpParams p) {
-    const uint32_t x = blockIdx.x * 32 + (threadIdx.x & 31), y = blockIdx.y * 8 + (threadIdx.x >> 5);
-    if (x >= (uint32_t)p.W || y >= (uint32_t)p.H) return;
+    const uint32_t x = blockIdx.x * 32 + (threadIdx.x & 31), y = (uint32_t)p.y_begin + blockIdx.y * 8 + (threadIdx.x >> 5);
+    if (x >= (uint32_t)p.W || y >= (uint32_t)p.y_end) return;
     const int tile_id = (y / 32) * p.tiles_x + (x / 32);
     const uint32_t ox = x & 1, oy = y & 1;
     const int round = (ox == 0) ? (oy == 0 ? 1 : 4) : (oy == 0 ? 3 : 2);
@@ -331,7 +337,11 @@ void launch_blend_amr(const AmrBlendArgs& a, cudaStream_t s) {
     p.ranges = b.ranges; p.point_list = b.point_list; p.means2D = b.means2D; p.conic_opacity = b.conic_opacity;
     p.colors = b.colors; p.bg = b.bg; p.final_T = b.final_T; p.n_contrib = b.n_contrib; p.out_color = b.out_color;
     q.levels = a.levels; q.levels_last = a.levels_last;
-    dim3 grid((b.W + 31) / 32, (b.H + 31) / 32, 1);
+    const int tiles_y = (b.H + 31) / 32;
+    const int r0 = b.row1 > 0 ? b.row0 : 0, r1 = b.row1 > 0 ? b.row1 : tiles_y;
+    if (r1 <= r0) return;
+    p.row0 = r0;
+    dim3 grid((b.W + 31) / 32, r1 - r0, 1);
     blend_amr_kernel<<<grid, kBlendThreads, 0, s>>>(q);
     count_launch();
     if (a.interpolate) {
@@ -340,7 +350,8 @@ void launch_blend_amr(const AmrBlendArgs& a, cudaStream_t s) {
         ip.levels = a.levels; ip.levels_last = a.levels_last;
         ip.final_T = b.final_T; ip.n_contrib = b.n_contrib; ip.out_color = b.out_color;
         ip.out_color_precomp = a.out_color_precomp ? a.out_color_precomp : b.out_color;
-        dim3 g2((b.W + 31) / 32, (b.H + 7) / 8, 1);
+        ip.y_begin = r0 * 32; ip.y_end = min(b.H, r1 * 32);
+        dim3 g2((b.W + 31) / 32, (ip.y_end - ip.y_begin + 7) / 8, 1);
         interpolate_kernel<<<g2, 256, 0, s>>>(ip);
         count_launch();
     }
@@ -350,7 +361,7 @@ void launch_blend_amr(const AmrBlendArgs& a, cudaStream_t s) {
 // backward
 // ------------------------------------------------------------------------------------------------
 struct BwdParams {
-    int W, H, tiles_x;
+    int W, H, tiles_x, row0;
     const uint2* __restrict__ ranges; const uint32_t* __restrict__ point_list;
     const float2* __restrict__ means2D; const float4* __restrict__ conic_opacity; const float* __restrict__ colors;
     const float* __restrict__ bg; const float* __restrict__ final_T; const uint32_t* __restrict__ n_contrib;
@@ -367,15 +378,16 @@ __global__ void __launch_bounds__(kBlendThreads) blend_bwd_kernel(const BwdParam
 
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const uint32_t lx = (wid & 1) * 8 + (lane & 7), ly = (wid >> 1) * 4 + (lane >> 3);
-    const uint32_t pix_x = blockIdx.x * 16 + lx, pix_y = blockIdx.y * 16 + ly;
+    const uint32_t tile_y = blockIdx.y + (uint32_t)p.row0;
+    const uint32_t pix_x = blockIdx.x * 16 + lx, pix_y = tile_y * 16 + ly;
     const bool inside = pix_x < (uint32_t)p.W && pix_y < (uint32_t)p.H;
     const uint32_t pix_id = (uint32_t)p.W * pix_y + pix_x;
     const float pxf = (float)pix_x, pyf = (float)pix_y;
-    const float rx0 = (float)(blockIdx.x * 16), ry0 = (float)(blockIdx.y * 16);
+    const float rx0 = (float)(blockIdx.x * 16), ry0 = (float)(tile_y * 16);
     const float rx1 = rx0 + 15.f, ry1 = ry0 + 15.f;
     const size_t HW = (size_t)p.H * p.W;
 
-    const uint2 range = p.ranges[blockIdx.y * p.tiles_x + blockIdx.x];
+    const uint2 range = p.ranges[tile_y * p.tiles_x + blockIdx.x];
     const int todo = (int)(range.y - range.x);
     const int rounds = (todo + kBlendThreads - 1) / kBlendThreads;
 
@@ -509,7 +521,11 @@ void launch_blend_backward(const BlendBwdArgs& a, cudaStream_t s) {
     p.ranges = a.ranges; p.point_list = a.point_list; p.means2D = a.means2D; p.conic_opacity = a.conic_opacity;
     p.colors = a.colors; p.bg = a.bg; p.final_T = a.final_T; p.n_contrib = a.n_contrib; p.dL_dpix = a.dL_dpix;
     p.scratch = a.scratch;
-    dim3 grid((a.W + 15) / 16, (a.H + 15) / 16, 1);
+    const int tiles_y = (a.H + 15) / 16;
+    const int r0 = a.row1 > 0 ? a.row0 : 0, r1 = a.row1 > 0 ? a.row1 : tiles_y;
+    if (r1 <= r0) return;
+    p.row0 = r0;
+    dim3 grid((a.W + 15) / 16, r1 - r0, 1);
     blend_bwd_kernel<<<grid, kBlendThreads, 0, s>>>(p);
     count_launch();
 }

@@ -213,6 +213,7 @@ struct PreprocessArgs {
     int grid_x, grid_y;    // tile grid
     int* radii;            // output (caller's or internal)
     bool prefiltered;
+    int band_row0, band_row1;   // tile-row band [row0,row1); 0,0 = whole frame
 };
 void launch_preprocess(const PreprocessArgs& a, const GeomPtrs& g, cudaStream_t s);
 void launch_block_scan(const GeomPtrs& g, int P, cudaStream_t s);
@@ -227,7 +228,7 @@ void launch_depth_keys(int P, const float* depths, const uint32_t* tiles_touched
 void launch_order_block_sums(int P, const uint32_t* order, const uint32_t* tiles_touched, uint32_t* sums, cudaStream_t s);
 void launch_scan_u32(const uint32_t* sums, uint32_t* offsets, int n, cudaStream_t s);
 void launch_emit_pairs(const GeomPtrs& g, int P, long long N, const uint32_t* order, const uint32_t* block_offsets, const int* radii, int tile,
-                       int grid_x, int grid_y, uint32_t* tiles, uint32_t* vals, uint32_t* hist, const SortPlan& plan, cudaStream_t s);
+                       int grid_x, int grid_y, int band_row0, int band_row1, uint32_t* tiles, uint32_t* vals, uint32_t* hist, const SortPlan& plan, cudaStream_t s);
 // stable LSD sort of n pairs.  Reads (kin,vin), ends in (kout,vout), uses (ktmp,vtmp) as the ping-pong partner.
 // Pass order is in -> b1 -> b2 -> b1 ... with b1 = out when the pass count is odd, tmp when it is even, so the last
 // pass always writes `out`.  In-place use: kin may alias ktmp when the count is odd and kout when it is even (never
@@ -245,6 +246,7 @@ void launch_fovea_levels(const ImgPtrs& im, int num_tiles, int fovea_step, const
 
 struct BlendArgs {
     int W, H;
+    int row0, row1;        // tile rows to blend (in units of the kernel's CTA tile: 16 px baseline, 32 px AMR)
     const uint2* ranges; const uint32_t* point_list;
     const float2* means2D; const float4* conic_opacity; const float* colors;
     const float* bg;
@@ -262,6 +264,7 @@ void launch_blend_amr(const AmrBlendArgs& a, cudaStream_t s);
 
 struct BlendBwdArgs {
     int W, H;
+    int row0, row1;
     const uint2* ranges; const uint32_t* point_list;
     const float2* means2D; const float4* conic_opacity; const float* colors;
     const float* bg; const float* final_T; const uint32_t* n_contrib; const float* dL_dpix;

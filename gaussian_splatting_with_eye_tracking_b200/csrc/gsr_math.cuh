@@ -62,6 +62,14 @@ __device__ __forceinline__ void get_rect(float px, float py, int radius, int til
     y1 = min((uint32_t)grid_y, (uint32_t)max(0, by));
 }
 
+// screen-tile band (multi-GPU tile bands): keep only rows [row0,row1) of a rect; row1 == 0 means "no band"
+__device__ __forceinline__ void clip_band(uint32_t& y0, uint32_t& y1, int row0, int row1) {
+    if (row1 > 0) {
+        y0 = min(max(y0, (uint32_t)row0), (uint32_t)row1);
+        y1 = min(max(y1, (uint32_t)row0), (uint32_t)row1);
+    }
+}
+
 // the blend exponent (forward.cu:334): -0.5f*(cx*dx*dx + cz*dy*dy) - cy*dx*dy, contraction as compiled
 __device__ __forceinline__ float blend_power(float cx, float cy, float cz, float dx, float dy) {
     float s = __fmaf_rn(dx, __fmul_rn(dx, cx), __fmul_rn(dy, __fmul_rn(dy, cz)));

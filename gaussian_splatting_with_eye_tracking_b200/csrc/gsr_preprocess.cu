@@ -47,6 +47,7 @@ struct PreFwdParams {
     uint32_t* __restrict__ block_sums;
     GeomHeader* header;
     int prefiltered;
+    int band_row0, band_row1;
 };
 
 // SH -> RGB (forward.cu:20-71).  `sh` points at this Gaussian's [M][3] coefficients.
@@ -257,6 +258,7 @@ __global__ void __launch_bounds__(kPreBlock) preprocess_fwd_kernel(const PreFwdP
                 radius = (int)ceilf(__fmul_rn(__fsqrt_rn(lam), 3.f));
                 pix = make_float2(ndc2pix(ndc_x, p.W), ndc2pix(ndc_y, p.H));
                 get_rect(pix.x, pix.y, radius, p.tile, p.grid_x, p.grid_y, x0, y0, x1, y1);
+                clip_band(y0, y1, p.band_row0, p.band_row1);
                 touched = (x1 - x0) * (y1 - y0);
                 alive = (touched != 0);
                 if (!alive) radius = 0;
@@ -306,6 +308,7 @@ void launch_preprocess(const PreprocessArgs& a, const GeomPtrs& g, cudaStream_t 
     p.radii = a.radii; p.depths = g.depths; p.clamped = g.clamped; p.means2D = g.means2D; p.cov3D = g.cov3D;
     p.conic_opacity = g.conic_opacity; p.rgb = g.rgb; p.tiles_touched = g.tiles_touched;
     p.block_sums = g.block_sums; p.header = g.header; p.prefiltered = a.prefiltered ? 1 : 0;
+    p.band_row0 = a.band_row0; p.band_row1 = a.band_row1;
     preprocess_fwd_kernel<<<g.nblocks, kPreBlock, 0, s>>>(p);
     count_launch();
 }
@@ -395,27 +398,38 @@ struct PreBwdParams {
     float *dL_dmeans2D, *dL_dcolors, *dL_dopacity, *dL_dmeans3D, *dL_dcov3D, *dL_dsh, *dL_dscales, *dL_drot, *dL_dconic;
 };
 
+// SH rows are staged through shared memory (STAGED): a thread's 3M coefficients / gradients are 192 B apart from its
+// neighbour's, so direct per-thread access costs one 32 B sector per 4 useful bytes.  Rows sit in smem with an odd
+// stride (conflict-free per-thread access); a warp loads only its VISIBLE rows and stores all 32 gradient rows as one
+// contiguous 6 KB run with 128-bit accesses.
+constexpr int kShStride = 49;                 // floats per staged row (3 * 16 coefficients + 1 pad)
+
+template <bool STAGED>
 __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreBwdParams p) {
     __shared__ float V[16], Pm[16], cam[3];
-    const int tid = threadIdx.x;
+    extern __shared__ float s_sh[];           // STAGED: [256][kShStride]
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     if (tid < 16) { V[tid] = p.viewmatrix[tid]; Pm[tid] = p.projmatrix[tid]; }
     if (tid < 3) cam[tid] = p.cam_pos[tid];
     __syncthreads();
     const int idx = blockIdx.x * 256 + tid;
-    if (idx >= p.P) return;
+    const bool valid = idx < p.P;
+    if (!STAGED && !valid) return;
     const size_t i3 = 3 * (size_t)idx;
 
-    const bool visible = p.radii[idx] > 0;
+    const bool visible = valid && p.radii[idx] > 0;
     float4 sA = make_float4(0, 0, 0, 0), sB = sA, sC = sA;
     if (visible) {
         const float4* sp = reinterpret_cast<const float4*>(p.scratch) + 3 * (size_t)idx;
         sA = sp[0]; sB = sp[1]; sC = sp[2];
     }
     // blend-stage gradients leave in the reference's tensor shapes
-    p.dL_dmeans2D[i3] = sA.x; p.dL_dmeans2D[i3 + 1] = sA.y; p.dL_dmeans2D[i3 + 2] = 0.f;
-    p.dL_dopacity[idx] = sB.y;
-    p.dL_dcolors[i3] = sB.z; p.dL_dcolors[i3 + 1] = sB.w; p.dL_dcolors[i3 + 2] = sC.x;
-    if (p.dL_dconic) reinterpret_cast<float4*>(p.dL_dconic)[idx] = make_float4(sA.z, sA.w, 0.f, sB.x);
+    if (valid) {
+        p.dL_dmeans2D[i3] = sA.x; p.dL_dmeans2D[i3 + 1] = sA.y; p.dL_dmeans2D[i3 + 2] = 0.f;
+        p.dL_dopacity[idx] = sB.y;
+        p.dL_dcolors[i3] = sB.z; p.dL_dcolors[i3 + 1] = sB.w; p.dL_dcolors[i3 + 2] = sC.x;
+        if (p.dL_dconic) reinterpret_cast<float4*>(p.dL_dconic)[idx] = make_float4(sA.z, sA.w, 0.f, sB.x);
+    }
 
     float dcov[6] = {0, 0, 0, 0, 0, 0};
     float dmx = 0.f, dmy = 0.f, dmz = 0.f;
@@ -493,10 +507,30 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreBwdParams 
 
     // ---------------- SH (backward.cu:20-139)
     if (p.dL_dsh != nullptr) {
-        float* out = p.dL_dsh + (size_t)idx * p.M * 3;
+        const int L = 3 * p.M;
+        const int warp_idx0 = blockIdx.x * 256 + wid * 32;
+        float* wbase = s_sh + wid * 32 * kShStride;
+        float* out = STAGED ? (wbase + lane * kShStride) : (p.dL_dsh + (size_t)idx * L);
         const int ncoef = (p.D + 1) * (p.D + 1);
+        const int f4_per_row = L >> 2;
+        if (STAGED) {
+            // cooperative load of the visible rows: 32 / f4_per_row rows per instruction, 128-bit each
+            const uint32_t m = __ballot_sync(0xffffffffu, visible && p.colors_from_sh);
+            const int nv = __popc(m), rpi = 32 / f4_per_row;
+            const int sel = lane / f4_per_row, part = lane - sel * f4_per_row;
+            for (int i = 0; i < nv; i += rpi) {
+                const int k = i + sel;
+                if (sel < rpi && k < nv) {
+                    const int src_lane = __fns(m, 0, k + 1);
+                    const float4 v = __ldg(reinterpret_cast<const float4*>(p.shs + (size_t)(warp_idx0 + src_lane) * L) + part);
+                    float* dst = wbase + src_lane * kShStride + 4 * part;
+                    dst[0] = v.x; dst[1] = v.y; dst[2] = v.z; dst[3] = v.w;
+                }
+            }
+            __syncwarp();
+        }
         if (visible && p.colors_from_sh) {
-            const float* sh = p.shs + (size_t)idx * p.M * 3;
+            const float* sh = STAGED ? out : (p.shs + (size_t)idx * L);
             const float ox = mx - cam[0], oy = my - cam[1], oz = mz - cam[2];
             const float inv_len = 1.f / sqrtf(ox * ox + oy * oy + oz * oz);
             const float x = ox * inv_len, y = oy * inv_len, z = oz * inv_len;
@@ -554,10 +588,22 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreBwdParams 
             dmx += ((sum2 - ox * ox) * ddx - oy * ox * ddy - oz * ox * ddz) * invsum32;
             dmy += (-ox * oy * ddx + (sum2 - oy * oy) * ddy - oz * oy * ddz) * invsum32;
             dmz += (-ox * oz * ddx - oy * oz * ddy + (sum2 - oz * oz) * ddz) * invsum32;
-        } else {
-            for (int k = 0; k < p.M * 3; ++k) out[k] = 0.f;
+        } else if (STAGED || valid) {
+            for (int k = 0; k < L; ++k) out[k] = 0.f;
+        }
+        if (STAGED) {
+            __syncwarp();
+            const int nrows = min(32, p.P - warp_idx0);
+            const int total4 = nrows * f4_per_row;
+            float4* gout = reinterpret_cast<float4*>(p.dL_dsh + (size_t)warp_idx0 * L);
+            for (int e = lane; e < total4; e += 32) {
+                const int r = e / f4_per_row, c = (e - r * f4_per_row) * 4;
+                const float* src = wbase + r * kShStride + c;
+                gout[e] = make_float4(src[0], src[1], src[2], src[3]);
+            }
         }
     }
+    if (!valid) return;
 
     // ---------------- cov3D -> scale, rotation (backward.cu:278-341)
     if (visible && p.cov_from_scales) {
@@ -614,7 +660,17 @@ void launch_preprocess_backward(const PreBwdArgs& a, cudaStream_t s) {
     p.dL_dmeans2D = a.out.dL_dmeans2D; p.dL_dcolors = a.out.dL_dcolors; p.dL_dopacity = a.out.dL_dopacity;
     p.dL_dmeans3D = a.out.dL_dmeans3D; p.dL_dcov3D = a.out.dL_dcov3D; p.dL_dsh = a.out.dL_dsh;
     p.dL_dscales = a.out.dL_dscales; p.dL_drot = a.out.dL_drotations; p.dL_dconic = a.out.dL_dconic;
-    preprocess_bwd_kernel<<<(a.P + 255) / 256, 256, 0, s>>>(p);
+    // staged SH path: needs M % 4 == 0 (128-bit rows), M <= 16 (row fits the staged stride) and 16 B-aligned tensors
+    const bool staged = p.dL_dsh != nullptr && p.M > 0 && p.M <= 16 && (p.M % 4) == 0 && ((size_t)p.dL_dsh & 15) == 0 &&
+                        (!p.colors_from_sh || ((size_t)p.shs & 15) == 0);
+    if (staged) {
+        const int smem = 256 * kShStride * (int)sizeof(float);
+        static bool attr_done = false;
+        if (!attr_done) { cudaFuncSetAttribute(preprocess_bwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem); attr_done = true; }
+        preprocess_bwd_kernel<true><<<(a.P + 255) / 256, 256, smem, s>>>(p);
+    } else {
+        preprocess_bwd_kernel<false><<<(a.P + 255) / 256, 256, 0, s>>>(p);
+    }
     count_launch();
 }
 

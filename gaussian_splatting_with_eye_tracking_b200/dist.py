@@ -226,3 +226,29 @@ def gather_bands(frame: torch.Tensor, bands: Sequence[Tuple[int, int]], tile_px:
         ry0, ry1 = min(ra * tile_px, H), min(rb * tile_px, H)
         full[:, ry0:ry1] = out[r][:, :ry1 - ry0]
     return full
+
+
+def render_amr_frame_bands(fwd_args, image_height: int, image_width: int, bands: Sequence[Tuple[int, int]], rank: int,
+                           interpolate_image: bool = True, gaze=None, group=None, gather: bool = True):
+    """One foveated frame split by screen-tile band over the ranks of ``group`` (config C5).
+
+    ``fwd_args`` are the first 18 positional arguments of ``_C.rasterize_gaussians`` (bg ... prefiltered).  Every rank
+    (1) preprocesses all Gaussians but bins only its rows (``foveaStep=0`` build with ``band``), (2) all-reduces the
+    per-tile pair counts so that the AMR percentiles are the global ones, (3) re-levels and renders its band in a single
+    pass, (4) optionally gathers the bands.  Returns (frame, n_intersections, levels, (geom, binning, image) buffers);
+    the levels are bit-identical to a single-GPU render of the whole frame."""
+    from . import _host, views
+    dev = fwd_args[1].device
+    e = torch.empty(0, device=dev)
+    eb = torch.empty(0, dtype=torch.uint8, device=dev)
+    band = tuple(bands[rank])
+    if band[1] <= band[0]:
+        raise ValueError("empty band: use fewer ranks than tile rows")
+    N, _, radii, gb, bb, ib = _host.rasterize_gaussians_amr(*fwd_args, 0, e, eb, eb, eb, False, False, gaze=None, band=band)
+    iv = views.image_view(ib, image_width, image_height, True)
+    allreduce_tile_counts(iv["n_intersections"], group)
+    _host.amr_relevel(ib, image_height, image_width)
+    frame = _host.amr_render_prebuilt(*fwd_args, gb, bb, ib, interpolate_image, False, gaze=gaze, band=band)
+    if gather:
+        frame = gather_bands(frame, bands, 32, group)
+    return frame, iv["n_intersections"], iv["levels"], (gb, bb, ib)
