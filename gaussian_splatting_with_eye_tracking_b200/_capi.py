@@ -89,6 +89,7 @@ SYMBOLS = {
                                  C.c_int, C.c_void_p, C.c_size_t, C.c_void_p]),
     "gsr_higher_msb": (C.c_uint, [C.c_uint]),
     "gsr_launch_count": (C.c_ulonglong, []),
+    "gsr_set_option": (C.c_int, [C.c_int, C.c_int]),
     "gsr_profile_enable": (None, [C.c_int]),
     "gsr_profile_read": (C.c_int, [C.POINTER(C.c_float), C.POINTER(C.c_int)]),
     "gsr_last_error": (C.c_char_p, []),

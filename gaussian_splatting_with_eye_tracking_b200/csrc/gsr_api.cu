@@ -237,6 +237,11 @@ int gsr_profile_read(float* ms, int* counts) {
     return rc;
 }
 const char* gsr_last_error(void) { return g_err; }
+int gsr_set_option(int option, int value) {
+    if (option == GSR_OPT_SORT_VARIANT && value >= 0 && value <= 5) { set_sort_variant(value); return GSR_OK; }
+    set_error("unknown option %d / value %d", option, value);
+    return GSR_ERR_INVALID;
+}
 const char* gsr_version(void) { return "gsr_b200 0.1 (sm_100a)"; }
 
 int gsr_forward(const gsr_scene* sc, const gsr_camera* cam, gsr_alloc_fn alloc, void* user,

@@ -264,13 +264,6 @@ __global__ void __launch_bounds__(kSortMaxRadix) hist_scan_kernel(uint32_t* hist
 // Tile = 512 threads x ITEMS keys, warp-striped loads (coalesced, order-preserving), match-any multi-split ranks,
 // keys AND values staged in shared memory so that each digit bin leaves as one contiguous run.
 // ------------------------------------------------------------------------------------------------
-constexpr int SORT_THREADS = 512;
-constexpr int SORT_WARPS = SORT_THREADS / 32;
-template <typename KeyT> struct SortCfg;
-template <> struct SortCfg<uint32_t> { static constexpr int ITEMS = 12; };
-template <> struct SortCfg<uint64_t> { static constexpr int ITEMS = 9; };
-static_assert(SORT_THREADS * SortCfg<uint64_t>::ITEMS == kSortTileItems, "smallest tile must match gsr_common.cuh (temp sizing)");
-
 constexpr uint32_t ST_AGG = 1u << 30, ST_INC = 2u << 30, ST_MASK = (1u << 30) - 1u;
 
 template <typename KeyT>
@@ -301,22 +294,24 @@ __device__ __forceinline__ uint32_t match_digit(uint32_t d) {
 template <int R> struct Log2 { static constexpr int v = 1 + Log2<R / 2>::v; };
 template <> struct Log2<1> { static constexpr int v = 0; };
 
-template <typename KeyT, int RADIX>
-__global__ void __launch_bounds__(SORT_THREADS, 2) onesweep_kernel(const SweepParams<KeyT> p) {
-    constexpr int ITEMS = SortCfg<KeyT>::ITEMS;
-    constexpr int TILE = SORT_THREADS * ITEMS;
+// THREADS x ITEMS keys per tile; THREADS >= RADIX.  MINB = CTAs per SM the register budget is planned for.
+template <typename KeyT, int RADIX, int THREADS, int ITEMS, int MINB>
+__global__ void __launch_bounds__(THREADS, MINB) onesweep_kernel(const SweepParams<KeyT> p) {
+    static_assert(THREADS >= RADIX, "one thread per bin in the scan / look-back phases");
+    constexpr int WARPS = THREADS / 32;
+    constexpr int TILE = THREADS * ITEMS;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     KeyT* s_keys = reinterpret_cast<KeyT*>(smem_raw);                                         // [TILE]
     uint32_t* s_vals = reinterpret_cast<uint32_t*>(smem_raw + sizeof(KeyT) * TILE);           // [TILE]
-    uint32_t* s_whist = s_vals + TILE;                                                        // [SORT_WARPS][RADIX]
-    uint32_t* s_bin_start = s_whist + SORT_WARPS * RADIX;                                     // [RADIX]
+    uint32_t* s_whist = s_vals + TILE;                                                        // [WARPS][RADIX]
+    uint32_t* s_bin_start = s_whist + WARPS * RADIX;                                          // [RADIX]
     uint32_t* s_gofs = s_bin_start + RADIX;                                                   // [RADIX]
     __shared__ uint32_t s_tile;
     __shared__ uint32_t s_wtot[RADIX / 32];
 
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     if (tid == 0) s_tile = atomicAdd(p.tile_counter, 1u);
-    for (int i = tid; i < SORT_WARPS * RADIX; i += SORT_THREADS) s_whist[i] = 0;
+    for (int i = tid; i < WARPS * RADIX; i += THREADS) s_whist[i] = 0;
     __syncthreads();
     const uint32_t tile = s_tile;
     const long long tile_base = (long long)tile * TILE;
@@ -364,7 +359,7 @@ __global__ void __launch_bounds__(SORT_THREADS, 2) onesweep_kernel(const SweepPa
     if (tid < RADIX) {
         uint32_t acc = 0;
 #pragma unroll
-        for (int w = 0; w < SORT_WARPS; ++w) { const uint32_t t = s_whist[w * RADIX + tid]; s_whist[w * RADIX + tid] = acc; acc += t; }
+        for (int w = 0; w < WARPS; ++w) { const uint32_t t = s_whist[w * RADIX + tid]; s_whist[w * RADIX + tid] = acc; acc += t; }
         bin_count = acc;
         *((volatile uint32_t*)(p.status + (size_t)tile * RADIX + tid)) = (tile == 0 ? ST_INC : ST_AGG) | acc;
     }
@@ -419,7 +414,7 @@ __global__ void __launch_bounds__(SORT_THREADS, 2) onesweep_kernel(const SweepPa
     // ---- scatter: consecutive smem slots of one bin are consecutive global positions
 #pragma unroll
     for (int i = 0; i < ITEMS; ++i) {
-        const int j = tid + i * SORT_THREADS;
+        const int j = tid + i * THREADS;
         if (j < count) {
             const KeyT k = s_keys[j];
             const uint32_t d = (uint32_t)(k >> p.shift) & mask;
@@ -430,9 +425,9 @@ __global__ void __launch_bounds__(SORT_THREADS, 2) onesweep_kernel(const SweepPa
     }
 }
 
-template <typename KeyT, int RADIX>
+template <typename KeyT, int RADIX, int THREADS, int ITEMS>
 static size_t sweep_smem() {
-    return (sizeof(KeyT) + sizeof(uint32_t)) * SORT_THREADS * SortCfg<KeyT>::ITEMS + sizeof(uint32_t) * (SORT_WARPS * RADIX + 2 * RADIX);
+    return (sizeof(KeyT) + sizeof(uint32_t)) * THREADS * ITEMS + sizeof(uint32_t) * ((THREADS / 32) * RADIX + 2 * RADIX);
 }
 
 struct SortTemp { uint32_t* hist; uint32_t* counters; uint32_t* status; };
@@ -446,6 +441,47 @@ static SortTemp carve_sort_temp(void* temp) {
 }
 uint32_t* sort_hist_ptr(void* temp) { return (uint32_t*)aligned_base(temp); }
 
+// tile shapes (threads x items per thread, CTAs per SM).  Variant 0 is the default; the others exist for tuning
+// sweeps through gsr_set_option(GSR_OPT_SORT_VARIANT, v) and are all bit-identical in result.
+static int g_sort_variant = 0;
+void set_sort_variant(int v) { g_sort_variant = v; }
+
+template <typename KeyT, int RADIX, int THREADS, int ITEMS, int MINB>
+static void launch_sweep_cfg(const SweepParams<KeyT>& sp, long long n, cudaStream_t s) {
+    constexpr int TILE = THREADS * ITEMS;
+    static_assert(TILE >= kSortTileItems, "temp sizing assumes no tile is smaller than kSortTileItems");
+    static bool attr_done = false;
+    const size_t smem = sweep_smem<KeyT, RADIX, THREADS, ITEMS>();
+    if (!attr_done) {
+        cudaFuncSetAttribute(onesweep_kernel<KeyT, RADIX, THREADS, ITEMS, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        attr_done = true;
+    }
+    const long long tiles = (n + TILE - 1) / TILE;
+    onesweep_kernel<KeyT, RADIX, THREADS, ITEMS, MINB><<<(unsigned)tiles, THREADS, smem, s>>>(sp);
+}
+
+template <typename KeyT, int RADIX> struct SweepDispatch;
+template <int RADIX> struct SweepDispatch<uint64_t, RADIX> {
+    static int tile_items() { return 512 * 9; }
+    static void launch(const SweepParams<uint64_t>& sp, long long n, cudaStream_t s) { launch_sweep_cfg<uint64_t, RADIX, 512, 9, 2>(sp, n, s); }
+};
+template <int RADIX> struct SweepDispatch<uint32_t, RADIX> {
+    static int tile_items() {
+        switch (g_sort_variant) { case 1: return 256 * 12; case 2: return 256 * 16; case 3: return 384 * 12; case 4: return 256 * 8;
+                                  case 5: return 512 * 8; default: return 512 * 12; }
+    }
+    static void launch(const SweepParams<uint32_t>& sp, long long n, cudaStream_t s) {
+        switch (g_sort_variant) {
+            case 1: launch_sweep_cfg<uint32_t, RADIX, 256, 12, 4>(sp, n, s); break;
+            case 2: launch_sweep_cfg<uint32_t, RADIX, 256, 16, 3>(sp, n, s); break;
+            case 3: launch_sweep_cfg<uint32_t, RADIX, 384, 12, 2>(sp, n, s); break;
+            case 4: launch_sweep_cfg<uint32_t, RADIX, 256, 8, 5>(sp, n, s); break;
+            case 5: launch_sweep_cfg<uint32_t, RADIX, 512, 8, 2>(sp, n, s); break;
+            default: launch_sweep_cfg<uint32_t, RADIX, 512, 12, 2>(sp, n, s); break;
+        }
+    }
+};
+
 template <typename KeyT>
 int launch_onesweep_t(const KeyT* kin0, const uint32_t* vin0, KeyT* kout, uint32_t* vout, KeyT* ktmp, uint32_t* vtmp,
                       long long n, const SortPlan& plan, void* temp, size_t temp_bytes, bool hist_ready, uint32_t* err_flag,
@@ -453,16 +489,7 @@ int launch_onesweep_t(const KeyT* kin0, const uint32_t* vin0, KeyT* kout, uint32
     if (n <= 0) return GSR_OK;
     if (n >= (1ll << 30)) { set_error("radix sort: n=%lld exceeds 2^30 pairs", n); return GSR_ERR_INVALID; }
     if (temp_bytes < sort_temp_bytes(n)) { set_error("radix sort: temp too small"); return GSR_ERR_ALLOC; }
-    constexpr int TILE = SORT_THREADS * SortCfg<KeyT>::ITEMS;
     SortTemp t = carve_sort_temp(temp);
-    const long long tiles = (n + TILE - 1) / TILE;
-    static bool attr_done = false;
-    if (!attr_done) {
-        cudaFuncSetAttribute(onesweep_kernel<KeyT, 256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sweep_smem<KeyT, 256>());
-        cudaFuncSetAttribute(onesweep_kernel<KeyT, 512>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sweep_smem<KeyT, 512>());
-        cudaFuncSetAttribute(onesweep_kernel<KeyT, 128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sweep_smem<KeyT, 128>());
-        attr_done = true;
-    }
     if (!hist_ready) {
         cudaMemsetAsync(t.hist, 0, sizeof(uint32_t) * kSortMaxPasses * kSortMaxRadix, s);
         HistParams<KeyT> hp; hp.keys = kin0; hp.n = n; hp.hist = t.hist; hp.passes = plan.passes;
@@ -485,12 +512,15 @@ int launch_onesweep_t(const KeyT* kin0, const uint32_t* vin0, KeyT* kout, uint32
         sp.n = n; sp.shift = plan.shift[ps]; sp.bits = plan.bits[ps];
         sp.bin_base = t.hist + ps * kSortMaxRadix; sp.status = t.status; sp.tile_counter = t.counters + ps; sp.err_flag = err_flag;
         const int radix = plan.bits[ps] <= 7 ? 128 : (plan.bits[ps] <= 8 ? 256 : 512);
+        const int tile_items = radix == 128 ? SweepDispatch<KeyT, 128>::tile_items()
+                             : radix == 256 ? SweepDispatch<KeyT, 256>::tile_items() : 512 * 9;
+        const long long tiles = (n + tile_items - 1) / tile_items;
         cudaMemsetAsync(t.status, 0, sizeof(uint32_t) * (size_t)tiles * radix, s);
         {
             ProfScope pr(prof_slot0 >= 0 ? prof_slot0 + ps : -1, s);
-            if (radix == 128) onesweep_kernel<KeyT, 128><<<(unsigned)tiles, SORT_THREADS, sweep_smem<KeyT, 128>(), s>>>(sp);
-            else if (radix == 256) onesweep_kernel<KeyT, 256><<<(unsigned)tiles, SORT_THREADS, sweep_smem<KeyT, 256>(), s>>>(sp);
-            else onesweep_kernel<KeyT, 512><<<(unsigned)tiles, SORT_THREADS, sweep_smem<KeyT, 512>(), s>>>(sp);
+            if (radix == 128) SweepDispatch<KeyT, 128>::launch(sp, n, s);
+            else if (radix == 256) SweepDispatch<KeyT, 256>::launch(sp, n, s);
+            else launch_sweep_cfg<KeyT, 512, 512, 9, 2>(sp, n, s);
         }
         count_launch();
         kin = kb[ps & 1]; vin = vb[ps & 1];

@@ -21,7 +21,7 @@ constexpr uint32_t kGeomMagic = 0x47535231u;  // "GSR1"
 __host__ __device__ inline size_t align_up(size_t x, size_t a = kAlign) { return (x + a - 1) / a * a; }
 
 // ---------------------------------------------------------------- radix sort temp sizing
-constexpr int kSortTileItems = 512 * 9;    // smallest tile (u64 keys); must match gsr_binning.cu
+constexpr int kSortTileItems = 256 * 8;    // smallest tile of any onesweep variant (gsr_binning.cu); sizes the look-back words
 constexpr int kSortMaxPasses = 8;
 constexpr int kSortMaxRadix = 512;
 
@@ -239,6 +239,7 @@ int launch_onesweep32(const uint32_t* kin, const uint32_t* vin, uint32_t* kout, 
                       long long n, const SortPlan& plan, void* temp, size_t temp_bytes, bool hist_ready, uint32_t* err_flag,
                       int prof_slot0, cudaStream_t s);
 uint32_t* sort_hist_ptr(void* temp);
+void set_sort_variant(int v);
 void launch_tile_ranges(const uint32_t* tiles_sorted, long long n, uint2* ranges, uint32_t* n_intersections, int num_tiles, cudaStream_t s);
 
 void launch_amr_levels(const ImgPtrs& im, int num_tiles, cudaStream_t s);

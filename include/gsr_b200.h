@@ -223,6 +223,10 @@ GSR_API void gsr_profile_enable(int on);
  * (both [GSR_PROF_SLOTS], caller-zeroed), then forgets them.  Returns GSR_OK or GSR_ERR_CUDA. */
 GSR_API int gsr_profile_read(float* ms, int* counts);
 
+/* ---- tuning knobs (results never depend on them) ---- */
+enum { GSR_OPT_SORT_VARIANT = 0 /* onesweep tile shape for u32 keys: 0 = default, 1..5 see gsr_binning.cu */ };
+GSR_API int gsr_set_option(int option, int value);
+
 /* counters: how many kernels this library launched since load (bench.py "gpu_launches") */
 GSR_API unsigned long long gsr_launch_count(void);
 
