@@ -68,7 +68,7 @@ class GsrImageView(C.Structure):
 # every symbol include/gsr_b200.h declares: name -> (restype, argtypes)
 SYMBOLS = {
     "gsr_geom_bytes": (C.c_size_t, [C.c_int]),
-    "gsr_binning_bytes": (C.c_size_t, [C.c_longlong]),
+    "gsr_binning_bytes": (C.c_size_t, [C.c_longlong, C.c_longlong, C.c_int, C.c_int, C.c_int]),
     "gsr_image_bytes": (C.c_size_t, [C.c_int, C.c_int, C.c_int]),
     "gsr_forward": (C.c_int, [C.POINTER(GsrScene), C.POINTER(GsrCamera), ALLOC_FN, C.c_void_p, C.c_void_p, C.c_void_p,
                               c_int_p, C.c_int, C.c_void_p]),
@@ -130,7 +130,7 @@ def check(rc: int, what: str) -> None:
 
 
 PROF_SLOTS = ["preprocess", "scan", "duplicate", "sort", "ranges", "blend", "amr_levels", "amr_blend", "bwd_blend",
-              "bwd_preprocess", "depth_sort"] + [f"sort_pass{i}" for i in range(8)]
+              "bwd_preprocess", "depth_sort", "expand"] + [f"sort_pass{i}" for i in range(8)]
 
 
 def profile_enable(on: bool) -> None:

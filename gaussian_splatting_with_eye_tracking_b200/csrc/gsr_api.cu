@@ -119,6 +119,7 @@ static int build_lists(const gsr_scene* sc, const gsr_camera* cam, int mode, gsr
     ImgPtrs im = img_ptrs(img, W, H, mode);
     const int num_tiles = im.tiles_x * im.tiles_y;
     if (cam->band_row1 > im.tiles_y) { set_error("tile band [%d,%d) exceeds the %d tile rows", cam->band_row0, cam->band_row1, im.tiles_y); return GSR_ERR_INVALID; }
+    if (im.tiles_x > kRunFieldMask || im.tiles_y > kRunMaxRows) { set_error("image of %dx%d tiles exceeds the %dx%d tile grid limit", im.tiles_x, im.tiles_y, kRunFieldMask, kRunMaxRows); return GSR_ERR_INVALID; }
     int rc = check_cuda(cudaMemsetAsync(g.header, 0, sizeof(GeomHeader), s), "memset header");
     if (rc) return rc;
 
@@ -147,7 +148,7 @@ static int build_lists(const gsr_scene* sc, const gsr_camera* cam, int mode, gsr
     static thread_local cudaEvent_t ev_hdr = nullptr;
     if (box && !ev_hdr) cudaEventCreateWithFlags(&ev_hdr, cudaEventDisableTiming);
     if (box && ev_hdr) {
-        if ((rc = check_cuda(cudaMemcpyAsync(box, &g.header->magic, 16, cudaMemcpyDeviceToHost, s), "D2H header"))) return rc;
+        if ((rc = check_cuda(cudaMemcpyAsync(box, &g.header->magic, 32, cudaMemcpyDeviceToHost, s), "D2H header"))) return rc;
         if ((rc = check_cuda(cudaEventRecord(ev_hdr, s), "event record"))) return rc;
     }
 
@@ -162,43 +163,46 @@ static int build_lists(const gsr_scene* sc, const gsr_camera* cam, int mode, gsr
         rc = launch_onesweep32(g.dkeys_a, nullptr, kout, g.order, ktmp, g.order_tmp, P, dplan, g.sort_temp, g.sort_temp_bytes,
                                /*hist_ready=*/false, &g.header->sort_error, -1, s);
         if (rc) return rc;
-        launch_order_block_sums(P, g.order, g.tiles_touched, g.oblock_sums, s);
+        launch_order_block_sums(P, g.order, g.rects, g.oblock_sums, s);
         launch_scan_u32(g.oblock_sums, g.oblock_offsets, g.nblocks, s);
     }
     if ((rc = check_last("depth sort", debug, s))) return rc;
 
-    uint32_t hdr[4];
+    uint32_t hdr[8];
     if (box && ev_hdr) {
         if ((rc = check_cuda(cudaEventSynchronize(ev_hdr), "event sync (header)"))) return rc;
-        memcpy(hdr, box, 16);
-    } else if ((rc = read_u32(&g.header->magic, hdr, 4, s))) return rc;
+        memcpy(hdr, box, 32);
+    } else if ((rc = read_u32(&g.header->magic, hdr, 8, s))) return rc;
     if (hdr[3] & 0x100u) { set_error("a Gaussian was culled although prefiltered=true (reference would __trap)"); return GSR_ERR_INVALID; }
-    const long long N = hdr[2];
-    void* bin = alloc(user, GSR_BUF_BINNING, gsr_binning_bytes(N));
+    const long long N = hdr[2], R = hdr[4];
+    void* bin = alloc(user, GSR_BUF_BINNING, gsr_binning_bytes(N, R, W, H, mode));
     if (!bin) { set_error("allocation callback returned NULL (binning)"); return GSR_ERR_ALLOC; }
-    BinPtrs b = bin_ptrs(bin, N);
+    BinPtrs b = bin_ptrs(bin, N, R, im.tiles_x, im.tiles_y);
 
-    if (N > 0) {
-        // (2) emit (tile, id) pairs in depth order, (3) stable partition by tile id
-        const SortPlan plan = make_sort_plan((int)higher_msb((unsigned)num_tiles));
-        uint32_t* t_start = (plan.passes & 1) ? b.tilesX : b.tilesY;
-        uint32_t* v_start = (plan.passes & 1) ? b.valsX : b.valsY;
+    const uint32_t* rk_sorted = b.rkeyB; const uint32_t* rv_sorted = b.rvalB;
+    if (R > 0) {
+        // (2) emit one run per (Gaussian, tile row) in depth order, (3) stable partition of the runs by row
+        const SortPlan plan = make_sort_plan_range(kRunRowShift, (int)higher_msb((unsigned)im.tiles_y));
         uint32_t* hist = sort_hist_ptr(b.sort_temp);
         if ((rc = check_cuda(cudaMemsetAsync(hist, 0, sizeof(uint32_t) * kSortMaxPasses * kSortMaxRadix, s), "memset hist"))) return rc;
         { ProfScope ps(GSR_PROF_DUPLICATE, s);
-          launch_emit_pairs(g, P, N, g.order, g.oblock_offsets, a.radii, im.tile, im.tiles_x, im.tiles_y, cam->band_row0, cam->band_row1,
-                            t_start, v_start, hist, plan, s); }
-        if ((rc = check_last("emit pairs", debug, s))) return rc;
+          launch_emit_runs(g, P, g.order, g.oblock_offsets, b.rkeyA, b.rvalA, hist, plan, s); }
+        if ((rc = check_last("emit runs", debug, s))) return rc;
         {
             ProfScope ps(GSR_PROF_SORT, s);
-            rc = launch_onesweep32(t_start, v_start, b.tilesY, b.valsY, b.tilesX, b.valsX, N, plan, b.sort_temp, b.sort_temp_bytes,
+            // one pass (<= 512 tile rows): A -> B.  Two passes: A -> C -> B, the value partner being the not-yet-written
+            // point list (N >= R words).
+            if (plan.passes > 2 || (plan.passes == 2 && im.tiles_y <= kSortMaxRadix)) { set_error("unexpected row-sort plan"); return GSR_ERR_INVALID; }
+            rc = launch_onesweep32(b.rkeyA, b.rvalA, b.rkeyB, b.rvalB, (plan.passes & 1) ? b.rkeyA : b.rkeyC,
+                                   (plan.passes & 1) ? b.rvalA : b.vals, R, plan, b.sort_temp, b.sort_temp_bytes,
                                    /*hist_ready=*/true, &g.header->sort_error, GSR_PROF_SORT_PASS0, s);
         }
         if (rc) return rc;
         if ((rc = check_last("radix sort", debug, s))) return rc;
     }
-    { ProfScope ps(GSR_PROF_RANGES, s); launch_tile_ranges(b.tilesY, N, im.ranges, im.n_intersections, num_tiles, s); }
-    if ((rc = check_last("tile ranges", debug, s))) return rc;
+    // (4) expand the row-sorted runs into the per-tile lists; also yields tile ranges and AMR intersection counts
+    launch_expand_runs(b, rk_sorted, rv_sorted, R, im.tiles_x, im.tiles_y, im.ranges, im.n_intersections, GSR_PROF_RANGES, GSR_PROF_EXPAND, s);
+    if ((rc = check_last("expand runs", debug, s))) return rc;
     *geom_out = geom; *bin_out = bin; *img_out = img; *N_out = (int)N;
     return GSR_OK;
 }
@@ -210,7 +214,10 @@ using namespace gsr;
 extern "C" {
 
 size_t gsr_geom_bytes(int P) { return GeomLayout(P > 0 ? P : 0).total + kAlign; }
-size_t gsr_binning_bytes(long long N) { return BinLayout(N).total + kAlign; }
+size_t gsr_binning_bytes(long long N, long long R, int W, int H, int mode) {
+    ImgLayout il(W > 0 ? W : 1, H > 0 ? H : 1, mode);
+    return BinLayout(N, R, il.tiles_x, il.tiles_y).total + kAlign;
+}
 size_t gsr_image_bytes(int W, int H, int mode) { return ImgLayout(W, H, mode).total + kAlign; }
 size_t gsr_sort_temp_bytes(long long n) { return sort_temp_bytes(n) + kAlign; }
 unsigned gsr_higher_msb(unsigned n) { return higher_msb(n); }
@@ -259,10 +266,9 @@ int gsr_forward(const gsr_scene* sc, const gsr_camera* cam, gsr_alloc_fn alloc, 
     rc = build_lists(sc, cam, GSR_MODE_BASELINE, alloc, user, radii, &geom, &bin, &img, &N, debug != 0, s);
     if (rc) return rc;
     GeomPtrs g = geom_ptrs(geom, sc->P);
-    BinPtrs b = bin_ptrs(bin, N);
     ImgPtrs im = img_ptrs(img, W, H, GSR_MODE_BASELINE);
     BlendArgs ba;
-    ba.W = W; ba.H = H; ba.row0 = cam->band_row0; ba.row1 = cam->band_row1; ba.ranges = im.ranges; ba.point_list = b.valsY; ba.means2D = g.means2D;
+    ba.W = W; ba.H = H; ba.row0 = cam->band_row0; ba.row1 = cam->band_row1; ba.ranges = im.ranges; ba.point_list = bin_point_list(bin); ba.means2D = g.means2D;
     ba.conic_opacity = g.conic_opacity; ba.colors = sc->colors_precomp ? sc->colors_precomp : g.rgb;
     ba.bg = cam->background; ba.final_T = im.accum_alpha; ba.n_contrib = im.n_contrib; ba.out_color = out_color;
     { ProfScope ps(GSR_PROF_BLEND, s); launch_blend_forward(ba, s); }
@@ -287,13 +293,12 @@ int gsr_backward(const gsr_scene* sc, const gsr_camera* cam, const int* radii, c
     }
     if (((size_t)gr->scratch & 15) != 0) { set_error("scratch must be 16-byte aligned"); return GSR_ERR_INVALID; }
     GeomPtrs g = geom_ptrs(geom_buffer, P);
-    BinPtrs b = bin_ptrs(binning_buffer, num_rendered);
     ImgPtrs im = img_ptrs(image_buffer, W, H, GSR_MODE_BASELINE);
     if (!radii) radii = g.radii;
 
     if ((rc = check_cuda(cudaMemsetAsync(gr->scratch, 0, sizeof(float) * 12 * (size_t)P, s), "memset scratch"))) return rc;
     BlendBwdArgs bb;
-    bb.W = W; bb.H = H; bb.row0 = cam->band_row0; bb.row1 = cam->band_row1; bb.ranges = im.ranges; bb.point_list = b.valsY; bb.means2D = g.means2D;
+    bb.W = W; bb.H = H; bb.row0 = cam->band_row0; bb.row1 = cam->band_row1; bb.ranges = im.ranges; bb.point_list = bin_point_list(binning_buffer); bb.means2D = g.means2D;
     bb.conic_opacity = g.conic_opacity; bb.colors = sc->colors_precomp ? sc->colors_precomp : g.rgb;
     bb.bg = cam->background; bb.final_T = im.accum_alpha; bb.n_contrib = im.n_contrib; bb.dL_dpix = dL_dpix;
     bb.scratch = gr->scratch;
@@ -354,7 +359,6 @@ int gsr_amr_forward(const gsr_scene* sc, const gsr_camera* cam, int fovea_step, 
         if (rc) return rc;
     }
     GeomPtrs g = geom_ptrs(geom, P);
-    BinPtrs b = bin_ptrs(bin, N);
     ImgPtrs im = img_ptrs(img, W, H, GSR_MODE_AMR);
     const int num_tiles = im.tiles_x * im.tiles_y;
     *num_rendered = N;
@@ -368,7 +372,7 @@ int gsr_amr_forward(const gsr_scene* sc, const gsr_camera* cam, int fovea_step, 
     if ((rc = check_last("fovea levels", debug != 0, s))) return rc;
 
     AmrBlendArgs ab;
-    ab.b.W = W; ab.b.H = H; ab.b.row0 = cam->band_row0; ab.b.row1 = cam->band_row1; ab.b.ranges = im.ranges; ab.b.point_list = b.valsY; ab.b.means2D = g.means2D;
+    ab.b.W = W; ab.b.H = H; ab.b.row0 = cam->band_row0; ab.b.row1 = cam->band_row1; ab.b.ranges = im.ranges; ab.b.point_list = bin_point_list(bin); ab.b.means2D = g.means2D;
     ab.b.conic_opacity = g.conic_opacity; ab.b.colors = sc->colors_precomp ? sc->colors_precomp : g.rgb;
     ab.b.bg = cam->background; ab.b.final_T = im.accum_alpha; ab.b.n_contrib = im.n_contrib; ab.b.out_color = out_color;
     // reference: steps >= 1 render with tile_AMR_levels_current, single pass with tile_AMR_levels (:401 vs :667)
@@ -400,13 +404,12 @@ int gsr_amr_render_prebuilt(const gsr_scene* sc, const gsr_camera* cam, const vo
     uint32_t hdr[4];
     if ((rc = read_u32(&g.header->magic, hdr, 4, s))) return rc;
     if (hdr[0] != kGeomMagic || hdr[1] != (uint32_t)P) { set_error("geometry buffer does not belong to this scene (magic %08x, P %u)", hdr[0], hdr[1]); return GSR_ERR_WORKSPACE; }
-    BinPtrs b = bin_ptrs(binning_buffer, (long long)hdr[2]);
     ImgPtrs im = img_ptrs(image_buffer, W, H, GSR_MODE_AMR);
     if (cam->band_row1 > im.tiles_y) { set_error("tile band exceeds the tile rows"); return GSR_ERR_INVALID; }
     launch_fovea_levels(im, im.tiles_x * im.tiles_y, -1, gaze, s);
     if ((rc = check_last("fovea levels", debug != 0, s))) return rc;
     AmrBlendArgs ab;
-    ab.b.W = W; ab.b.H = H; ab.b.row0 = cam->band_row0; ab.b.row1 = cam->band_row1; ab.b.ranges = im.ranges; ab.b.point_list = b.valsY;
+    ab.b.W = W; ab.b.H = H; ab.b.row0 = cam->band_row0; ab.b.row1 = cam->band_row1; ab.b.ranges = im.ranges; ab.b.point_list = bin_point_list(binning_buffer);
     ab.b.means2D = g.means2D; ab.b.conic_opacity = g.conic_opacity; ab.b.colors = sc->colors_precomp ? sc->colors_precomp : g.rgb;
     ab.b.bg = cam->background; ab.b.final_T = im.accum_alpha; ab.b.n_contrib = im.n_contrib; ab.b.out_color = out_color;
     ab.levels = im.levels; ab.levels_last = im.levels_last; ab.fovea_step = -1; ab.out_color_precomp = nullptr;
@@ -427,9 +430,9 @@ int gsr_view_geom(const void* geom_buffer, int P, gsr_geom_view* out) {
 
 int gsr_view_binning(const void* binning_buffer, long long N, gsr_binning_view* out) {
     if (!binning_buffer || !out || N < 0) { set_error("view_binning: bad arguments"); return GSR_ERR_INVALID; }
-    BinPtrs b = bin_ptrs(binning_buffer, N);
-    out->N = N; out->keys_unsorted = nullptr; out->values_unsorted = nullptr;   // consumed by the ping-pong passes
-    out->tiles_sorted = b.tilesY; out->point_list = b.valsY;
+    out->N = N; out->keys_unsorted = nullptr; out->values_unsorted = nullptr;   // pairs are never materialised unsorted
+    out->tiles_sorted = nullptr;              // nor are their tile ids: they follow from the tile ranges
+    out->point_list = bin_point_list(binning_buffer);
     return GSR_OK;
 }
 

@@ -38,6 +38,12 @@ SortPlan make_sort_plan(int end_bit) {
     return pl;
 }
 
+SortPlan make_sort_plan_range(int begin_bit, int nbits) {
+    SortPlan pl = make_sort_plan(nbits);
+    for (int i = 0; i < pl.passes; ++i) pl.shift[i] += begin_bit;
+    return pl;
+}
+
 // ------------------------------------------------------------------------------------------------
 // pair emission in depth order
 // ------------------------------------------------------------------------------------------------
@@ -52,12 +58,13 @@ __global__ void __launch_bounds__(kPreBlock) depth_keys_kernel(int P, const floa
     if (i < P) keys[i] = tiles_touched[i] ? __float_as_uint(depths[i]) : 0xffffffffu;
 }
 
-// per-256 block sums of tiles_touched taken in sorted order (first level of the scan that places the pairs)
+// per-256 block sums, in depth order, of the number of tile rows each Gaussian's rect spans (= runs it emits)
 __global__ void __launch_bounds__(kPreBlock) order_block_sums_kernel(int P, const uint32_t* __restrict__ order,
-                                                                     const uint32_t* __restrict__ tiles_touched, uint32_t* __restrict__ sums) {
+                                                                     const uint2* __restrict__ rects, uint32_t* __restrict__ sums) {
     __shared__ uint32_t s_w[kPreBlock / 32];
     const int j = blockIdx.x * kPreBlock + threadIdx.x;
-    uint32_t v = (j < P) ? tiles_touched[order[j]] : 0u;
+    uint32_t v = 0;
+    if (j < P) { const uint32_t ry = rects[order[j]].y; v = (ry >> 16) - (ry & 0xffffu); }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
     if ((threadIdx.x & 31) == 0) s_w[threadIdx.x >> 5] = v;
@@ -65,112 +72,58 @@ __global__ void __launch_bounds__(kPreBlock) order_block_sums_kernel(int P, cons
     if (threadIdx.x == 0) { uint32_t t = 0; for (int w = 0; w < kPreBlock / 32; ++w) t += s_w[w]; sums[blockIdx.x] = t; }
 }
 
-struct EmitParams {
-    int P, nblocks, tile, grid_x, grid_y, band_row0, band_row1;
-    uint32_t N;
+// ------------------------------------------------------------------------------------------------
+// Run-length binning.  The reference materialises every (tile, Gaussian) pair with a 64-bit key and radix-sorts all
+// N of them (duplicateWithKeys + SortPairs, rasterizer_impl.cu:70-111,303-308).  A Gaussian's tiles form a rectangle,
+// so its pairs are h runs of w consecutive tiles: we emit one 8-byte RUN per (Gaussian, tile row) in depth order
+// (N / w-bar of them), stable-sort the runs by row (one radix pass), and expand each row's runs straight into the
+// per-tile lists with an exact rank computation -- the N pairs are written once (4 B each) and never sorted.
+//   rank of Gaussian j in tile (row, x) = number of runs of that row, earlier in depth order, that cover column x.
+// ------------------------------------------------------------------------------------------------
+struct EmitRunsParams {
+    int P;
     const uint32_t* __restrict__ order;          // depth-sorted Gaussian ids
-    const int* __restrict__ radii;
-    const float2* __restrict__ means2D;
-    const uint32_t* __restrict__ tiles_touched;
-    const uint32_t* __restrict__ block_offsets;  // [nblocks+1] exclusive offsets of the sorted 256-blocks, [nblocks] = N
-    uint32_t* __restrict__ tiles;                // out: tile id of every pair
-    uint32_t* __restrict__ vals;                 // out: Gaussian id of every pair
-    uint32_t* hist;                              // [passes][kSortMaxRadix] global digit counts of the tile ids
-    int passes; int shift[kSortMaxPasses]; int bits[kSortMaxPasses];
+    const uint2* __restrict__ rects;
+    const uint32_t* __restrict__ block_offsets;  // [nblocks+1] exclusive run offsets of the sorted 256-blocks
+    uint32_t* __restrict__ rkeys;                // out: (row << 20) | (x0 << 10) | w
+    uint32_t* __restrict__ rvals;                // out: Gaussian id
+    uint32_t* hist;                              // [passes][kSortMaxRadix] global digit counts of the row field
+    int passes, shift0, bits0, shift1, bits1;    // at most two passes (<= 4095 tile rows)
 };
 
-constexpr int kDupThreads = 256;
-constexpr uint32_t kEmitChunk = 8192;            // output pairs per CTA
-
-// One CTA per fixed-size chunk of the OUTPUT (perfectly balanced however fat individual Gaussians are: in depth
-// order the nearest, largest splats are adjacent).  The CTA finds the 256-Gaussian blocks that overlap its chunk,
-// scans each block's tiles_touched in shared memory, and then works one thread per PAIR: bisection for the
-// Gaussian, reciprocal multiply for the tile, fully coalesced stores (reference: one thread per Gaussian looping
-// over its rect, rasterizer_impl.cu:70-111).
-__global__ void __launch_bounds__(kDupThreads) emit_pairs_kernel(const EmitParams p) {
+__global__ void __launch_bounds__(kPreBlock) emit_runs_kernel(const EmitRunsParams p) {
     extern __shared__ uint32_t s_hist[];            // [passes][kSortMaxRadix]
-    __shared__ uint32_t s_off[kPreBlock + 1];
-    __shared__ uint32_t s_x0[kPreBlock], s_y0[kPreBlock], s_w[kPreBlock], s_id[kPreBlock];
-    __shared__ float s_invw[kPreBlock];
-    __shared__ uint32_t s_wsum[kDupThreads / 32];
+    __shared__ uint32_t s_wsum[kPreBlock / 32];
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-    for (int i = tid; i < p.passes * kSortMaxRadix; i += kDupThreads) s_hist[i] = 0;
-
-    const uint32_t c_lo = blockIdx.x * kEmitChunk;
-    const uint32_t c_hi = min(p.N, c_lo + kEmitChunk);
-    // last block whose first pair is at or before c_lo (ties = empty blocks: take the last one)
-    int lo = 0, hi = p.nblocks;                     // invariant: block_offsets[lo] <= c_lo < block_offsets[hi] (= N at nblocks)
-    while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (__ldg(p.block_offsets + mid) <= c_lo) lo = mid; else hi = mid; }
-
-    for (int blk = lo; blk < p.nblocks; ++blk) {
-        const uint32_t gbase = __ldg(p.block_offsets + blk);
-        if (gbase >= c_hi) break;
-        const uint32_t gnext = __ldg(p.block_offsets + blk + 1);
-        if (gnext == gbase) continue;               // empty block (CTA-uniform)
-        __syncthreads();                            // previous iteration's smem readers are done
-        const int j = blk * kPreBlock + tid;
-        uint32_t t = 0;
-        if (j < p.P) {
-            const uint32_t g = p.order[j];
-            t = p.tiles_touched[g];
-            if (t > 0) {
-                const float2 xy = p.means2D[g];
-                uint32_t x0, y0, x1, y1;
-                get_rect(xy.x, xy.y, p.radii[g], p.tile, p.grid_x, p.grid_y, x0, y0, x1, y1);
-                clip_band(y0, y1, p.band_row0, p.band_row1);
-                s_x0[tid] = x0; s_y0[tid] = y0; s_w[tid] = x1 - x0; s_id[tid] = g;
-                s_invw[tid] = 1.0f / (float)(x1 - x0);
-            }
-        }
-        uint32_t inc = t;
+    const uint32_t base = __ldg(p.block_offsets + blockIdx.x);
+    if (__ldg(p.block_offsets + blockIdx.x + 1) == base) return;        // nothing visible in this block (CTA-uniform)
+    for (int i = tid; i < p.passes * kSortMaxRadix; i += kPreBlock) s_hist[i] = 0;
+    const int j = blockIdx.x * kPreBlock + tid;
+    uint32_t g = 0, x0 = 0, w = 0, y0 = 0, h = 0;
+    if (j < p.P) {
+        g = p.order[j];
+        const uint2 r = p.rects[g];
+        x0 = r.x & 0xffffu; w = (r.x >> 16) - x0; y0 = r.y & 0xffffu; h = (r.y >> 16) - y0;
+    }
+    uint32_t inc = h;
 #pragma unroll
-        for (int o = 1; o < 32; o <<= 1) { uint32_t u = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += u; }
-        if (lane == 31) s_wsum[wid] = inc;
-        __syncthreads();
-        uint32_t wbase = 0;
+    for (int o = 1; o < 32; o <<= 1) { uint32_t u = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += u; }
+    if (lane == 31) s_wsum[wid] = inc;
+    __syncthreads();
+    uint32_t off = base + inc - h;
 #pragma unroll
-        for (int w = 0; w < kDupThreads / 32; ++w) wbase += (w < wid) ? s_wsum[w] : 0u;
-        s_off[tid] = wbase + inc - t;
-        if (tid == kDupThreads - 1) s_off[kPreBlock] = wbase + inc;
-        __syncthreads();
-
-        const uint32_t q_lo = max(c_lo, gbase) - gbase, q_hi = min(c_hi, gnext) - gbase;   // this block's pairs inside my chunk
-        for (uint32_t q0 = q_lo; q0 < q_hi; q0 += kDupThreads) {
-            const uint32_t q = q0 + tid;
-            const bool valid = q < q_hi;
-            uint32_t tile_id = 0;
-            if (valid) {
-                // largest g with s_off[g] <= q  (s_off non-decreasing, s_off[256] = block total > q)
-                int a = 0, b = kPreBlock;
-#pragma unroll
-                for (int it = 0; it < 8; ++it) { const int mid = (a + b) >> 1; if (s_off[mid] <= q) a = mid; else b = mid; }
-                const uint32_t k = q - s_off[a];
-                const uint32_t w = s_w[a];
-                uint32_t row = (uint32_t)(((float)k + 0.5f) * s_invw[a]);       // k / w for k < 2^22 (tiles per Gaussian)
-                uint32_t col = k - row * w;
-                if (col >= w) { row += 1; col -= w; }                            // guard against a 1-ulp reciprocal
-                tile_id = (s_y0[a] + row) * (uint32_t)p.grid_x + s_x0[a] + col;
-                p.tiles[(size_t)gbase + q] = tile_id;
-                p.vals[(size_t)gbase + q] = s_id[a];
-            }
-            // digit histograms of the tile ids: a warp's pairs are mostly one Gaussian's row of consecutive tiles, i.e.
-            // all-distinct low digits (plain shared atomics, no conflicts) and one common high digit (one atomic per warp)
-            const uint32_t act = __ballot_sync(0xffffffffu, valid);
-            if (valid) {
-                for (int ps = 0; ps < p.passes; ++ps) {
-                    const uint32_t d = (tile_id >> p.shift[ps]) & ((1u << p.bits[ps]) - 1u);
-                    int uniform = 0;
-                    __match_all_sync(act, d, &uniform);
-                    if (uniform) { if (lane == (31 - __clz(act))) atomicAdd(&s_hist[ps * kSortMaxRadix + d], (uint32_t)__popc(act)); }
-                    else atomicAdd(&s_hist[ps * kSortMaxRadix + d], 1u);
-                }
-            }
-        }
+    for (int k = 0; k < kPreBlock / 32; ++k) off += (k < wid) ? s_wsum[k] : 0u;
+    for (uint32_t k = 0; k < h; ++k) {
+        const uint32_t key = ((y0 + k) << kRunRowShift) | (x0 << kRunX0Shift) | w;
+        p.rkeys[off + k] = key;
+        p.rvals[off + k] = g;
+        atomicAdd(&s_hist[(key >> p.shift0) & ((1u << p.bits0) - 1u)], 1u);
+        if (p.passes > 1) atomicAdd(&s_hist[kSortMaxRadix + ((key >> p.shift1) & ((1u << p.bits1) - 1u))], 1u);
     }
     __syncthreads();
-    for (int i = tid; i < p.passes * kSortMaxRadix; i += kDupThreads) {
-        const uint32_t h = s_hist[i];
-        if (h) atomicAdd(&p.hist[i], h);
+    for (int i = tid; i < p.passes * kSortMaxRadix; i += kPreBlock) {
+        const uint32_t c = s_hist[i];
+        if (c) atomicAdd(&p.hist[i], c);
     }
 }
 
@@ -189,24 +142,20 @@ void launch_depth_keys(int P, const float* depths, const uint32_t* tiles_touched
     count_launch();
 }
 
-void launch_order_block_sums(int P, const uint32_t* order, const uint32_t* tiles_touched, uint32_t* sums, cudaStream_t s) {
-    order_block_sums_kernel<<<(P + kPreBlock - 1) / kPreBlock, kPreBlock, 0, s>>>(P, order, tiles_touched, sums);
+void launch_order_block_sums(int P, const uint32_t* order, const uint2* rects, uint32_t* sums, cudaStream_t s) {
+    order_block_sums_kernel<<<(P + kPreBlock - 1) / kPreBlock, kPreBlock, 0, s>>>(P, order, rects, sums);
     count_launch();
 }
 
-void launch_emit_pairs(const GeomPtrs& g, int P, long long N, const uint32_t* order, const uint32_t* block_offsets, const int* radii, int tile,
-                       int grid_x, int grid_y, int band_row0, int band_row1, uint32_t* tiles, uint32_t* vals, uint32_t* hist,
-                       const SortPlan& plan, cudaStream_t s) {
-    EmitParams p;
-    p.band_row0 = band_row0; p.band_row1 = band_row1;
-    p.P = P; p.N = (uint32_t)N; p.nblocks = g.nblocks; p.tile = tile; p.grid_x = grid_x; p.grid_y = grid_y;
-    p.order = order; p.radii = radii; p.means2D = g.means2D; p.tiles_touched = g.tiles_touched;
-    p.block_offsets = block_offsets; p.tiles = tiles; p.vals = vals; p.hist = hist;
+void launch_emit_runs(const GeomPtrs& g, int P, const uint32_t* order, const uint32_t* block_offsets, uint32_t* rkeys, uint32_t* rvals,
+                      uint32_t* hist, const SortPlan& plan, cudaStream_t s) {
+    EmitRunsParams p;
+    p.P = P; p.order = order; p.rects = g.rects; p.block_offsets = block_offsets; p.rkeys = rkeys; p.rvals = rvals; p.hist = hist;
     p.passes = plan.passes;
-    for (int i = 0; i < kSortMaxPasses; ++i) { p.shift[i] = i < plan.passes ? plan.shift[i] : 0; p.bits[i] = i < plan.passes ? plan.bits[i] : 1; }
-    const int grid = (int)((N + kEmitChunk - 1) / kEmitChunk);
-    if (grid < 1) return;
-    emit_pairs_kernel<<<grid, kDupThreads, sizeof(uint32_t) * plan.passes * kSortMaxRadix, s>>>(p);
+    p.shift0 = plan.shift[0]; p.bits0 = plan.bits[0];
+    p.shift1 = plan.passes > 1 ? plan.shift[1] : 0; p.bits1 = plan.passes > 1 ? plan.bits[1] : 1;
+    if (g.nblocks < 1) return;
+    emit_runs_kernel<<<g.nblocks, kPreBlock, sizeof(uint32_t) * plan.passes * kSortMaxRadix, s>>>(p);
     count_launch();
 }
 
@@ -539,31 +488,207 @@ int launch_onesweep32(const uint32_t* kin, const uint32_t* vin, uint32_t* kout, 
 }
 
 // ------------------------------------------------------------------------------------------------
-// tile ranges by binary search on the sorted keys (+ AMR intersection counts)
+// expansion of the row-sorted runs into per-tile lists (+ tile ranges, + AMR intersection counts)
+//   replaces cudaMemset + identifyTileRanges (rasterizer_impl.cu:116-138,310-317) and the AMR fork's
+//   calculateIntersections (A/rasterizer_impl.cu:181-188)
 // ------------------------------------------------------------------------------------------------
-__device__ __forceinline__ uint32_t lower_bound_tile(const uint32_t* __restrict__ tiles, uint32_t n, uint32_t tile) {
-    uint32_t lo = 0, hi = n;
-    while (lo < hi) {
-        const uint32_t mid = lo + ((hi - lo) >> 1);
-        if (__ldg(tiles + mid) < tile) lo = mid + 1; else hi = mid;
+// exclusive scan over a 1024-thread CTA; returns the exclusive prefix, *total = CTA sum.  s_warp: 32 words.
+__device__ __forceinline__ uint32_t cta1024_exclusive_scan(uint32_t v, uint32_t* s_warp, uint32_t* total) {
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    uint32_t inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { uint32_t t = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += t; }
+    __syncthreads();                         // s_warp may still be read from a previous call
+    if (lane == 31) s_warp[wid] = inc;
+    __syncthreads();
+    uint32_t wsum = s_warp[lane], winc = wsum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { uint32_t t = __shfl_up_sync(0xffffffffu, winc, o); if (lane >= o) winc += t; }
+    const uint32_t tot = __shfl_sync(0xffffffffu, winc, 31);
+    const uint32_t wexcl = __shfl_sync(0xffffffffu, winc - wsum, wid);
+    *total = tot;
+    return wexcl + inc - v;
+}
+
+// row_start[r] = first sorted run of tile row r (binary search on the row field); chunk_row_start[r] = first chunk of row r
+__global__ void __launch_bounds__(1024) chunk_table_kernel(const uint32_t* __restrict__ rkeys, uint32_t R, int tiles_y,
+                                                           uint32_t* __restrict__ row_start, uint32_t* __restrict__ chunk_row_start) {
+    __shared__ uint32_t s_warp[32];
+    const int tid = threadIdx.x;
+    for (int r = tid; r <= tiles_y; r += 1024) {
+        uint32_t lo = 0, hi = R;
+        while (lo < hi) { const uint32_t mid = lo + ((hi - lo) >> 1); if ((__ldg(rkeys + mid) >> kRunRowShift) < (uint32_t)r) lo = mid + 1; else hi = mid; }
+        row_start[r] = lo;
     }
-    return lo;
+    __syncthreads();
+    uint32_t carry = 0;
+    for (int base = 0; base <= tiles_y; base += 1024) {
+        const int r = base + tid;
+        uint32_t nch = 0;
+        if (r < tiles_y) { const uint32_t len = row_start[r + 1] - row_start[r]; nch = (len + kRunChunk - 1) / kRunChunk; }
+        uint32_t tot;
+        const uint32_t ex = cta1024_exclusive_scan(nch, s_warp, &tot);
+        if (r <= tiles_y) chunk_row_start[r] = carry + ex;      // entry [tiles_y] = total number of chunks
+        carry += tot;
+    }
 }
 
-__global__ void __launch_bounds__(128) tile_ranges_kernel(const uint32_t* __restrict__ tiles, uint32_t n, uint2* __restrict__ ranges,
-                                                          uint32_t* __restrict__ n_intersections, int num_tiles) {
-    const int t = blockIdx.x * 128 + threadIdx.x;
-    if (t >= num_tiles) return;
-    uint32_t lo = 0, hi = 0;
-    if (n > 0) { lo = lower_bound_tile(tiles, n, (uint32_t)t); hi = lower_bound_tile(tiles, n, (uint32_t)t + 1u); }
-    // empty tiles keep the reference's memset value (0,0)
-    ranges[t] = (hi > lo) ? make_uint2(lo, hi) : make_uint2(0u, 0u);
-    if (n_intersections) n_intersections[t] = hi - lo;
+struct ChunkCtx { int row; uint32_t r0, r1; };
+// which rows' runs does chunk c cover?  (binary search over the <= 4096 rows; CTA-uniform)
+__device__ __forceinline__ bool chunk_lookup(uint32_t c, int tiles_y, const uint32_t* __restrict__ chunk_row_start,
+                                             const uint32_t* __restrict__ row_start, ChunkCtx& cx) {
+    if (c >= __ldg(chunk_row_start + tiles_y)) return false;
+    int lo = 0, hi = tiles_y;                  // invariant: chunk_row_start[lo] <= c < chunk_row_start[hi]
+    while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (__ldg(chunk_row_start + mid) <= c) lo = mid; else hi = mid; }
+    cx.row = lo;
+    const uint32_t k = c - __ldg(chunk_row_start + lo);
+    cx.r0 = __ldg(row_start + lo) + k * kRunChunk;
+    cx.r1 = min(cx.r0 + (uint32_t)kRunChunk, __ldg(row_start + lo + 1));
+    return true;
 }
 
-void launch_tile_ranges(const uint32_t* tiles_sorted, long long n, uint2* ranges, uint32_t* n_intersections, int num_tiles, cudaStream_t s) {
-    tile_ranges_kernel<<<(num_tiles + 127) / 128, 128, 0, s>>>(tiles_sorted, (uint32_t)n, ranges, n_intersections, num_tiles);
-    count_launch();
+// per chunk: how many of its runs cover each tile column (difference array + scan)
+__global__ void __launch_bounds__(256) chunk_count_kernel(const uint32_t* __restrict__ rkeys, int tiles_x, int tiles_y,
+                                                          const uint32_t* __restrict__ chunk_row_start, const uint32_t* __restrict__ row_start,
+                                                          uint32_t* __restrict__ chunk_counts) {
+    extern __shared__ int s_diff[];               // [tiles_x + 1], then reused for the scanned counts
+    __shared__ int s_wsum[8];
+    ChunkCtx cx;
+    if (!chunk_lookup(blockIdx.x, tiles_y, chunk_row_start, row_start, cx)) return;
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    for (int i = tid; i <= tiles_x; i += 256) s_diff[i] = 0;
+    __syncthreads();
+    for (uint32_t r = cx.r0 + tid; r < cx.r1; r += 256) {
+        const uint32_t key = __ldg(rkeys + r);
+        const uint32_t x0 = (key >> kRunX0Shift) & kRunFieldMask, w = key & kRunFieldMask;
+        atomicAdd(&s_diff[x0], 1);
+        atomicAdd(&s_diff[x0 + w], -1);
+    }
+    __syncthreads();
+    // inclusive scan over the columns: 4 consecutive columns per thread (tiles_x <= 1023)
+    int v[4], sum = 0;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { const int x = 4 * tid + i; v[i] = (x < tiles_x) ? s_diff[x] : 0; sum += v[i]; }
+    int inc = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { int t = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += t; }
+    if (lane == 31) s_wsum[wid] = inc;
+    __syncthreads();
+    int run = inc - sum;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) run += (k < wid) ? s_wsum[k] : 0;
+    uint32_t* out = chunk_counts + (size_t)blockIdx.x * tiles_x;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { const int x = 4 * tid + i; run += v[i]; if (x < tiles_x) out[x] = (uint32_t)run; }
+}
+
+// per tile row: exclusive prefix over the row's chunks for every column (in place) + per-tile totals
+__global__ void __launch_bounds__(256) row_scan_kernel(int tiles_x, const uint32_t* __restrict__ chunk_row_start,
+                                                       uint32_t* __restrict__ chunk_counts, uint32_t* __restrict__ tile_count) {
+    const int row = blockIdx.x;
+    const uint32_t c0 = chunk_row_start[row], c1 = chunk_row_start[row + 1];
+    for (int x = threadIdx.x; x < tiles_x; x += 256) {
+        uint32_t base = 0;
+#pragma unroll 8
+        for (uint32_t c = c0; c < c1; ++c) {
+            uint32_t* q = chunk_counts + (size_t)c * tiles_x + x;
+            const uint32_t v = *q; *q = base; base += v;
+        }
+        tile_count[(size_t)row * tiles_x + x] = base;
+    }
+}
+
+// exclusive scan of the per-tile totals -> tile_start (in place), ranges, AMR intersection counts
+__global__ void __launch_bounds__(1024) tile_scan_kernel(uint32_t* __restrict__ tile_start, int num_tiles, uint2* __restrict__ ranges,
+                                                         uint32_t* __restrict__ n_intersections) {
+    __shared__ uint32_t s_warp[32];
+    uint32_t carry = 0;
+    for (int base = 0; base < num_tiles; base += 1024) {
+        const int t = base + threadIdx.x;
+        const uint32_t cnt = (t < num_tiles) ? tile_start[t] : 0u;
+        uint32_t tot;
+        const uint32_t st = carry + cta1024_exclusive_scan(cnt, s_warp, &tot);
+        if (t < num_tiles) {
+            tile_start[t] = st;
+            ranges[t] = cnt ? make_uint2(st, st + cnt) : make_uint2(0u, 0u);   // empty tiles keep the reference's memset value
+            if (n_intersections) n_intersections[t] = cnt;
+        }
+        carry += tot;
+    }
+}
+
+// per chunk: write every run's Gaussian id into the lists of the tiles it covers, at its exact depth-order rank
+constexpr int kExpandThreads = 256;
+__global__ void __launch_bounds__(kExpandThreads) expand_runs_kernel(const uint32_t* __restrict__ rkeys, const uint32_t* __restrict__ rvals,
+                                                                     int tiles_x, int tiles_y, const uint32_t* __restrict__ chunk_row_start,
+                                                                     const uint32_t* __restrict__ row_start, const uint32_t* __restrict__ chunk_counts,
+                                                                     const uint32_t* __restrict__ tile_start, uint32_t* __restrict__ point_list) {
+    extern __shared__ uint32_t s_mem[];
+    uint32_t* s_base = s_mem;                      // [tiles_x] next free slot of every column's list
+    uint32_t* s_cur = s_base + tiles_x;            // [tiles_x] slot base of the current batch
+    uint32_t* s_pfx = s_cur + tiles_x;             // [tiles_x][2] per-warp exclusive popcount prefixes, 8 x u8
+    uint32_t* s_bits = s_pfx + 2 * tiles_x;        // [8][tiles_x] coverage bits: warp-major, bit = lane
+    ChunkCtx cx;
+    if (!chunk_lookup(blockIdx.x, tiles_y, chunk_row_start, row_start, cx)) return;
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    for (int x = tid; x < tiles_x; x += kExpandThreads)
+        s_base[x] = __ldg(tile_start + (size_t)cx.row * tiles_x + x) + __ldg(chunk_counts + (size_t)blockIdx.x * tiles_x + x);
+    const uint32_t lt = (1u << lane) - 1u;
+    for (uint32_t b0 = cx.r0; b0 < cx.r1; b0 += kExpandThreads) {
+        const uint32_t r = b0 + tid;
+        uint32_t x0 = 0, w = 0, id = 0;
+        if (r < cx.r1) {
+            const uint32_t key = __ldg(rkeys + r);
+            x0 = (key >> kRunX0Shift) & kRunFieldMask; w = key & kRunFieldMask; id = __ldg(rvals + r);
+        }
+        for (int i = tid; i < 8 * tiles_x; i += kExpandThreads) s_bits[i] = 0;
+        __syncthreads();
+        uint32_t* mybits = s_bits + wid * tiles_x;
+        for (uint32_t i = 0; i < w; ++i) atomicOr(&mybits[x0 + i], 1u << lane);
+        __syncthreads();
+        for (int x = tid; x < tiles_x; x += kExpandThreads) {
+            uint32_t acc = 0, p0 = 0, p1 = 0;
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                if (k < 4) p0 |= acc << (8 * k); else p1 |= acc << (8 * (k - 4));
+                acc += __popc(s_bits[k * tiles_x + x]);
+            }
+            // acc <= 256; prefixes of warps 0..7 are <= 224 and fit a byte each
+            s_pfx[2 * x] = p0; s_pfx[2 * x + 1] = p1;
+            const uint32_t cur = s_base[x];
+            s_cur[x] = cur; s_base[x] = cur + acc;
+        }
+        __syncthreads();
+        for (uint32_t i = 0; i < w; ++i) {
+            const uint32_t x = x0 + i;
+            const uint32_t pf = (s_pfx[2 * x + (wid >> 2)] >> (8 * (wid & 3))) & 255u;
+            point_list[s_cur[x] + pf + __popc(mybits[x] & lt)] = id;
+        }
+        __syncthreads();
+    }
+}
+
+void launch_expand_runs(const BinPtrs& b, const uint32_t* rkeys_sorted, const uint32_t* rvals_sorted, long long R, int tiles_x, int tiles_y,
+                        uint2* ranges, uint32_t* n_intersections, int prof_ranges, int prof_expand, cudaStream_t s) {
+    const int num_tiles = tiles_x * tiles_y;
+    const unsigned grid = (unsigned)b.max_chunks;
+    {
+        ProfScope ps(prof_ranges, s);
+        chunk_table_kernel<<<1, 1024, 0, s>>>(rkeys_sorted, (uint32_t)R, tiles_y, b.row_start, b.chunk_row_start);
+        chunk_count_kernel<<<grid, 256, sizeof(int) * (tiles_x + 1), s>>>(rkeys_sorted, tiles_x, tiles_y, b.chunk_row_start, b.row_start, b.chunk_counts);
+        row_scan_kernel<<<tiles_y, 256, 0, s>>>(tiles_x, b.chunk_row_start, b.chunk_counts, b.tile_start);
+        tile_scan_kernel<<<1, 1024, 0, s>>>(b.tile_start, num_tiles, ranges, n_intersections);
+        count_launch(4);
+    }
+    {
+        ProfScope ps(prof_expand, s);
+        const size_t smem = sizeof(uint32_t) * (size_t)tiles_x * (1 + 1 + 2 + 8);
+        static bool attr_done = false;
+        if (!attr_done) { cudaFuncSetAttribute(expand_runs_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 12 * 4 * 1024); attr_done = true; }
+        expand_runs_kernel<<<grid, kExpandThreads, smem, s>>>(rkeys_sorted, rvals_sorted, tiles_x, tiles_y, b.chunk_row_start, b.row_start,
+                                                              b.chunk_counts, b.tile_start, b.vals);
+        count_launch();
+    }
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -40,13 +40,14 @@ struct GeomHeader {      // lives at the start of the (aligned) geometry buffer,
     uint32_t P;
     uint32_t num_rendered;   // = sum(tiles_touched); reference reads point_offsets[P-1] (rasterizer_impl.cu:281)
     uint32_t sort_error;     // set by the radix-sort watchdog
-    uint32_t pad[60];
+    uint32_t num_runs;       // = sum over visible Gaussians of the tile rows their rect spans ((Gaussian, row) runs)
+    uint32_t pad[59];
 };
 static_assert(sizeof(GeomHeader) == 256, "header is one alignment unit");
 
 struct GeomLayout {
-    size_t header, depths, clamped, radii, means2D, cov3D, conic_opacity, rgb, tiles_touched,
-           block_sums, block_offsets, dkeys_a, dkeys_b, order_tmp, order, oblock_sums, oblock_offsets, sort_temp, total;
+    size_t header, depths, clamped, radii, means2D, cov3D, conic_opacity, rgb, tiles_touched, rects,
+           block_sums, block_sums_r, block_offsets, dkeys_a, dkeys_b, order_tmp, order, oblock_sums, oblock_offsets, sort_temp, total;
     int nblocks;
     __host__ __device__ explicit GeomLayout(int P) {
         nblocks = (P + kPreBlock - 1) / kPreBlock;
@@ -60,7 +61,9 @@ struct GeomLayout {
         conic_opacity = o; o = align_up(o + sizeof(float4) * (size_t)P);
         rgb = o;           o = align_up(o + sizeof(float) * 3 * (size_t)P);
         tiles_touched = o; o = align_up(o + sizeof(uint32_t) * (size_t)P);
+        rects = o;         o = align_up(o + sizeof(uint2) * (size_t)P);
         block_sums = o;    o = align_up(o + sizeof(uint32_t) * (size_t)(nblocks + 1));
+        block_sums_r = o;  o = align_up(o + sizeof(uint32_t) * (size_t)(nblocks + 1));
         block_offsets = o; o = align_up(o + sizeof(uint32_t) * (size_t)(nblocks + 1));
         // depth sort of the Gaussians (keys ping-pong, index ping-pong) and the scan in sorted order
         dkeys_a = o;       o = align_up(o + sizeof(uint32_t) * (size_t)P);
@@ -77,7 +80,8 @@ struct GeomLayout {
 struct GeomPtrs {
     GeomHeader* header;
     float* depths; unsigned char* clamped; int* radii; float2* means2D; float* cov3D;
-    float4* conic_opacity; float* rgb; uint32_t* tiles_touched; uint32_t* block_sums; uint32_t* block_offsets;
+    float4* conic_opacity; float* rgb; uint32_t* tiles_touched; uint2* rects; uint32_t* block_sums; uint32_t* block_sums_r;
+    uint32_t* block_offsets;
     uint32_t *dkeys_a, *dkeys_b, *order_tmp, *order, *oblock_sums, *oblock_offsets; void* sort_temp; size_t sort_temp_bytes;
     int nblocks;
 };
@@ -97,7 +101,9 @@ inline GeomPtrs geom_ptrs(const void* buf, int P) {
     g.conic_opacity = (float4*)(b + L.conic_opacity);
     g.rgb = (float*)(b + L.rgb);
     g.tiles_touched = (uint32_t*)(b + L.tiles_touched);
+    g.rects = (uint2*)(b + L.rects);
     g.block_sums = (uint32_t*)(b + L.block_sums);
+    g.block_sums_r = (uint32_t*)(b + L.block_sums_r);
     g.block_offsets = (uint32_t*)(b + L.block_offsets);
     g.dkeys_a = (uint32_t*)(b + L.dkeys_a); g.dkeys_b = (uint32_t*)(b + L.dkeys_b);
     g.order_tmp = (uint32_t*)(b + L.order_tmp); g.order = (uint32_t*)(b + L.order);
@@ -108,35 +114,53 @@ inline GeomPtrs geom_ptrs(const void* buf, int P) {
 }
 
 // ---------------------------------------------------------------- binning buffer
-// (tile id, Gaussian id) pairs; X and Y ping-pong through the radix passes and the final tile-sorted list always
-// lands in (tilesY, valsY).  `sort_temp` holds the digit histograms, the look-back status words and tile counters.
+// point_list[N] (the only part backward needs, at offset 0), then the run-length binning scratch: a "run" is one
+// (Gaussian, tile row) span of consecutive tiles, key = (row << 20) | (x0 << 10) | width, value = Gaussian id.
+constexpr int kRunChunk = 1024;          // runs per expansion chunk (a chunk never straddles two tile rows)
+constexpr int kRunRowShift = 20, kRunX0Shift = 10, kRunFieldMask = 1023, kRunMaxRows = 4095;
+
 struct BinLayout {
-    size_t tilesX, tilesY, valsX, valsY, sort_temp, total;
-    __host__ __device__ explicit BinLayout(long long N) {
-        size_t n = (size_t)(N > 0 ? N : 0);
+    size_t vals, rkeyA, rkeyB, rkeyC, rvalA, rvalB, sort_temp, row_start, chunk_row_start, chunk_counts, tile_start, total;
+    long long max_chunks;
+    __host__ __device__ BinLayout(long long N, long long R, int tiles_x, int tiles_y) {
+        size_t n = (size_t)(N > 0 ? N : 0), r = (size_t)(R > 0 ? R : 0);
+        max_chunks = (long long)(r / kRunChunk) + tiles_y + 1;
         size_t o = 0;
-        tilesX = o; o = align_up(o + 4 * n);
-        tilesY = o; o = align_up(o + 4 * n);
-        valsX = o; o = align_up(o + 4 * n);
-        valsY = o; o = align_up(o + 4 * n);
-        sort_temp = o; o = align_up(o + sort_temp_bytes(N));
+        vals = o;  o = align_up(o + 4 * n);
+        rkeyA = o; o = align_up(o + 4 * r);
+        rkeyB = o; o = align_up(o + 4 * r);
+        rkeyC = o; o = align_up(o + (tiles_y > kSortMaxRadix ? 4 * r : 0));   // ping-pong partner of a two-pass row sort (> 512 rows)
+        rvalA = o; o = align_up(o + 4 * r);
+        rvalB = o; o = align_up(o + 4 * r);
+        sort_temp = o; o = align_up(o + sort_temp_bytes((long long)r));
+        row_start = o; o = align_up(o + 4 * (size_t)(tiles_y + 2));
+        chunk_row_start = o; o = align_up(o + 4 * (size_t)(tiles_y + 2));
+        chunk_counts = o; o = align_up(o + 4 * (size_t)max_chunks * (size_t)tiles_x);
+        tile_start = o; o = align_up(o + 4 * ((size_t)tiles_x * tiles_y + 1));
         total = o;
     }
 };
 
 struct BinPtrs {
-    uint32_t *tilesX, *tilesY, *valsX, *valsY; void* sort_temp; size_t sort_temp_bytes;
+    uint32_t *vals, *rkeyA, *rkeyB, *rkeyC, *rvalA, *rvalB; void* sort_temp; size_t sort_temp_bytes;
+    uint32_t *row_start, *chunk_row_start, *chunk_counts, *tile_start; long long max_chunks;
 };
 
-inline BinPtrs bin_ptrs(const void* buf, long long N) {
-    BinLayout L(N);
+inline BinPtrs bin_ptrs(const void* buf, long long N, long long R, int tiles_x, int tiles_y) {
+    BinLayout L(N, R, tiles_x, tiles_y);
     char* b = aligned_base(buf);
     BinPtrs p;
-    p.tilesX = (uint32_t*)(b + L.tilesX); p.tilesY = (uint32_t*)(b + L.tilesY);
-    p.valsX = (uint32_t*)(b + L.valsX); p.valsY = (uint32_t*)(b + L.valsY);
-    p.sort_temp = (void*)(b + L.sort_temp); p.sort_temp_bytes = sort_temp_bytes(N);
+    p.vals = (uint32_t*)(b + L.vals);
+    p.rkeyA = (uint32_t*)(b + L.rkeyA); p.rkeyB = (uint32_t*)(b + L.rkeyB); p.rkeyC = (uint32_t*)(b + L.rkeyC);
+    p.rvalA = (uint32_t*)(b + L.rvalA); p.rvalB = (uint32_t*)(b + L.rvalB);
+    p.sort_temp = (void*)(b + L.sort_temp); p.sort_temp_bytes = sort_temp_bytes(R > 0 ? R : 0);
+    p.row_start = (uint32_t*)(b + L.row_start); p.chunk_row_start = (uint32_t*)(b + L.chunk_row_start);
+    p.chunk_counts = (uint32_t*)(b + L.chunk_counts); p.tile_start = (uint32_t*)(b + L.tile_start);
+    p.max_chunks = L.max_chunks;
     return p;
 }
+// the sorted Gaussian-id list (reference: point_list) sits at the start of the buffer
+inline uint32_t* bin_point_list(const void* buf) { return (uint32_t*)aligned_base(buf); }
 
 // ---------------------------------------------------------------- image buffer
 struct ImgLayout {
@@ -224,11 +248,15 @@ struct SortPlan {
 };
 SortPlan make_sort_plan(int end_bit);
 
+SortPlan make_sort_plan_range(int begin_bit, int nbits);
 void launch_depth_keys(int P, const float* depths, const uint32_t* tiles_touched, uint32_t* keys, cudaStream_t s);
-void launch_order_block_sums(int P, const uint32_t* order, const uint32_t* tiles_touched, uint32_t* sums, cudaStream_t s);
+void launch_order_block_sums(int P, const uint32_t* order, const uint2* rects, uint32_t* sums, cudaStream_t s);
 void launch_scan_u32(const uint32_t* sums, uint32_t* offsets, int n, cudaStream_t s);
-void launch_emit_pairs(const GeomPtrs& g, int P, long long N, const uint32_t* order, const uint32_t* block_offsets, const int* radii, int tile,
-                       int grid_x, int grid_y, int band_row0, int band_row1, uint32_t* tiles, uint32_t* vals, uint32_t* hist, const SortPlan& plan, cudaStream_t s);
+// run-length binning (gsr_binning.cu): emit (Gaussian,row) runs in depth order -> [sort by row] -> expand into per-tile lists
+void launch_emit_runs(const GeomPtrs& g, int P, const uint32_t* order, const uint32_t* block_offsets, uint32_t* rkeys, uint32_t* rvals,
+                      uint32_t* hist, const SortPlan& plan, cudaStream_t s);
+void launch_expand_runs(const BinPtrs& b, const uint32_t* rkeys_sorted, const uint32_t* rvals_sorted, long long R, int tiles_x, int tiles_y,
+                        uint2* ranges, uint32_t* n_intersections, int prof_ranges, int prof_expand, cudaStream_t s);
 // stable LSD sort of n pairs.  Reads (kin,vin), ends in (kout,vout), uses (ktmp,vtmp) as the ping-pong partner.
 // Pass order is in -> b1 -> b2 -> b1 ... with b1 = out when the pass count is odd, tmp when it is even, so the last
 // pass always writes `out`.  In-place use: kin may alias ktmp when the count is odd and kout when it is even (never
@@ -240,7 +268,6 @@ int launch_onesweep32(const uint32_t* kin, const uint32_t* vin, uint32_t* kout, 
                       int prof_slot0, cudaStream_t s);
 uint32_t* sort_hist_ptr(void* temp);
 void set_sort_variant(int v);
-void launch_tile_ranges(const uint32_t* tiles_sorted, long long n, uint2* ranges, uint32_t* n_intersections, int num_tiles, cudaStream_t s);
 
 void launch_amr_levels(const ImgPtrs& im, int num_tiles, cudaStream_t s);
 void launch_fovea_levels(const ImgPtrs& im, int num_tiles, int fovea_step, const gsr_gaze* gaze, cudaStream_t s);

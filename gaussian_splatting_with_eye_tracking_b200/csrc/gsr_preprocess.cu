@@ -44,7 +44,9 @@ struct PreFwdParams {
     float4* __restrict__ conic_opacity;
     float* __restrict__ rgb;
     uint32_t* __restrict__ tiles_touched;
+    uint2* __restrict__ rects;              // (x0 | x1 << 16, y0 | y1 << 16) tile rect, (0,0) when nothing is touched
     uint32_t* __restrict__ block_sums;
+    uint32_t* __restrict__ block_sums_r;    // per-CTA sum of tile rows spanned (runs)
     GeomHeader* header;
     int prefiltered;
     int band_row0, band_row1;
@@ -200,16 +202,16 @@ __device__ __forceinline__ float3 cov2d_from_cov3d(float tx, float ty, float tz,
     return make_float3(__fadd_rn(cov00, 0.3f), cov01, __fadd_rn(cov11, 0.3f));
 }
 
-__global__ void __launch_bounds__(kPreBlock) preprocess_fwd_kernel(const PreFwdParams p) {
+__global__ void __launch_bounds__(kPreBlock, 4) preprocess_fwd_kernel(const PreFwdParams p) {
     __shared__ float sV[16], sPm[16], sCam[3];
-    __shared__ uint32_t s_warp_sum[kPreBlock / 32];
+    __shared__ uint32_t s_warp_sum[kPreBlock / 32], s_warp_sum_r[kPreBlock / 32];
     const int tid = threadIdx.x;
     if (tid < 16) { sV[tid] = p.viewmatrix[tid]; sPm[tid] = p.projmatrix[tid]; }
     if (tid < 3) sCam[tid] = p.cam_pos[tid];
     __syncthreads();
 
     const int idx = blockIdx.x * kPreBlock + tid;
-    uint32_t touched = 0;
+    uint32_t touched = 0, rows = 0;
     int radius = 0;
 
     if (idx < p.P) {
@@ -280,19 +282,23 @@ __global__ void __launch_bounds__(kPreBlock) preprocess_fwd_kernel(const PreFwdP
         }
         p.radii[idx] = radius;
         p.tiles_touched[idx] = touched;
+        if (!alive) { x0 = x1 = y0 = y1 = 0; }
+        p.rects[idx] = make_uint2(x0 | (x1 << 16), y0 | (y1 << 16));
+        rows = y1 - y0;
     }
 
     // CTA sum of tiles_touched -> block_sums[blockIdx.x] (first level of the scan)
-    uint32_t v = touched;
+    uint32_t v = touched, vr = rows;
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-    if ((tid & 31) == 0) s_warp_sum[tid >> 5] = v;
+    for (int o = 16; o > 0; o >>= 1) { v += __shfl_xor_sync(0xffffffffu, v, o); vr += __shfl_xor_sync(0xffffffffu, vr, o); }
+    if ((tid & 31) == 0) { s_warp_sum[tid >> 5] = v; s_warp_sum_r[tid >> 5] = vr; }
     __syncthreads();
     if (tid == 0) {
-        uint32_t s = 0;
+        uint32_t s = 0, sr = 0;
 #pragma unroll
-        for (int w = 0; w < kPreBlock / 32; ++w) s += s_warp_sum[w];
+        for (int w = 0; w < kPreBlock / 32; ++w) { s += s_warp_sum[w]; sr += s_warp_sum_r[w]; }
         p.block_sums[blockIdx.x] = s;
+        p.block_sums_r[blockIdx.x] = sr;
     }
 }
 
@@ -307,6 +313,7 @@ void launch_preprocess(const PreprocessArgs& a, const GeomPtrs& g, cudaStream_t 
     p.tile = a.tile; p.grid_x = a.grid_x; p.grid_y = a.grid_y;
     p.radii = a.radii; p.depths = g.depths; p.clamped = g.clamped; p.means2D = g.means2D; p.cov3D = g.cov3D;
     p.conic_opacity = g.conic_opacity; p.rgb = g.rgb; p.tiles_touched = g.tiles_touched;
+    p.rects = g.rects; p.block_sums_r = g.block_sums_r;
     p.block_sums = g.block_sums; p.header = g.header; p.prefiltered = a.prefiltered ? 1 : 0;
     p.band_row0 = a.band_row0; p.band_row1 = a.band_row1;
     preprocess_fwd_kernel<<<g.nblocks, kPreBlock, 0, s>>>(p);
@@ -317,12 +324,20 @@ void launch_preprocess(const PreprocessArgs& a, const GeomPtrs& g, cudaStream_t 
 // scan of the per-CTA sums: one CTA, exclusive offsets + grand total into the header.
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(1024) block_scan_kernel(const uint32_t* __restrict__ sums, uint32_t* __restrict__ offsets,
-                                                          int n, GeomHeader* header, uint32_t P) {
+                                                          int n, GeomHeader* header, uint32_t P, const uint32_t* __restrict__ sums_r) {
     __shared__ uint32_t s_warp[32];
-    __shared__ uint32_t s_carry;
+    __shared__ uint32_t s_carry, s_total_r;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-    if (tid == 0) s_carry = 0;
+    if (tid == 0) { s_carry = 0; s_total_r = 0; }
     __syncthreads();
+    if (sums_r != nullptr) {          // plain total of the second array (number of runs)
+        uint32_t t = 0;
+        for (int i = tid; i < n; i += 1024) t += sums_r[i];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+        if (lane == 0 && t) atomicAdd(&s_total_r, t);
+        __syncthreads();
+    }
     for (int base = 0; base < n; base += 1024) {
         const int i = base + tid;
         const uint32_t v = (i < n) ? sums[i] : 0u;
@@ -347,17 +362,17 @@ __global__ void __launch_bounds__(1024) block_scan_kernel(const uint32_t* __rest
     }
     if (tid == 0) {
         offsets[n] = s_carry;
-        if (header) { header->magic = kGeomMagic; header->P = P; header->num_rendered = s_carry; }   // sort_error: zeroed by the host memset
+        if (header) { header->magic = kGeomMagic; header->P = P; header->num_rendered = s_carry; header->num_runs = s_total_r; }   // sort_error: zeroed by the host memset
     }
 }
 
 void launch_block_scan(const GeomPtrs& g, int P, cudaStream_t s) {
-    block_scan_kernel<<<1, 1024, 0, s>>>(g.block_sums, g.block_offsets, g.nblocks, g.header, (uint32_t)P);
+    block_scan_kernel<<<1, 1024, 0, s>>>(g.block_sums, g.block_offsets, g.nblocks, g.header, (uint32_t)P, g.block_sums_r);
     count_launch();
 }
 
 void launch_scan_u32(const uint32_t* sums, uint32_t* offsets, int n, cudaStream_t s) {
-    block_scan_kernel<<<1, 1024, 0, s>>>(sums, offsets, n, nullptr, 0u);
+    block_scan_kernel<<<1, 1024, 0, s>>>(sums, offsets, n, nullptr, 0u, nullptr);
     count_launch();
 }
 

@@ -44,8 +44,16 @@ def geom_view(geom: torch.Tensor, P: int) -> dict:
 def binning_view(binning: torch.Tensor, N: int) -> dict:
     v = GsrBinningView()
     _capi.check(lib.gsr_view_binning(C.c_void_p(binning.data_ptr()), N, C.byref(v)), "gsr_view_binning")
-    return dict(tiles=_slice(binning, v.tiles_sorted, 4 * N, torch.int32),
-                point_list=_slice(binning, v.point_list, 4 * N, torch.int32))
+    # tile ids are never materialised per pair (run-length binning): see tiles_from_ranges
+    return dict(point_list=_slice(binning, v.point_list, 4 * N, torch.int32))
+
+
+def tiles_from_ranges(ranges: torch.Tensor, N: int) -> torch.Tensor:
+    """Tile id of every entry of the sorted list, from the tile ranges: lists are stored back to back in tile order."""
+    counts = (ranges[:, 1] - ranges[:, 0]).long()
+    tiles = torch.repeat_interleave(torch.arange(ranges.shape[0], device=ranges.device), counts)
+    assert tiles.numel() == N, f"tile ranges cover {tiles.numel()} entries, expected {N}"
+    return tiles.to(torch.int32)
 
 
 def sorted_keys(tiles: torch.Tensor, point_list: torch.Tensor, depths: torch.Tensor) -> torch.Tensor:

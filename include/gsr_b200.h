@@ -116,7 +116,7 @@ typedef struct gsr_grads {
 
 /* ---- sizes of the three work buffers (bytes, including alignment slack) ---- */
 GSR_API size_t gsr_geom_bytes(int P);
-GSR_API size_t gsr_binning_bytes(long long num_rendered);
+GSR_API size_t gsr_binning_bytes(long long num_rendered, long long num_runs, int width, int height, int mode);
 GSR_API size_t gsr_image_bytes(int width, int height, int mode);
 
 /* ---- baseline rasterizer ---- */
@@ -176,10 +176,10 @@ typedef struct gsr_geom_view {
 
 typedef struct gsr_binning_view {
     long long N;
-    const uint64_t* keys_unsorted;  /* always NULL: unsorted pairs are consumed by the ping-pong passes      */
-    const uint32_t* values_unsorted;/* always NULL                                                          */
-    const uint32_t* tiles_sorted;   /* [N] tile id of every sorted pair; the reference's 64-bit key is      */
-                                    /*     (tiles_sorted[i] << 32) | depth_bits[point_list[i]]              */
+    const uint64_t* keys_unsorted;  /* always NULL: pairs are never materialised unsorted (run-length binning)  */
+    const uint32_t* values_unsorted;/* always NULL                                                              */
+    const uint32_t* tiles_sorted;   /* always NULL: the tile of entry i follows from gsr_image_view.ranges; the */
+                                    /*     reference's 64-bit key is (tile << 32) | depth_bits[point_list[i]]   */
     const uint32_t* point_list;     /* [N] Gaussian id of every sorted pair (reference: point_list)         */
 } gsr_binning_view;
 
@@ -215,6 +215,7 @@ GSR_API unsigned gsr_higher_msb(unsigned n);
 enum {
     GSR_PROF_PREPROCESS = 0, GSR_PROF_SCAN, GSR_PROF_DUPLICATE, GSR_PROF_SORT, GSR_PROF_RANGES, GSR_PROF_BLEND,
     GSR_PROF_AMR_LEVELS, GSR_PROF_AMR_BLEND, GSR_PROF_BWD_BLEND, GSR_PROF_BWD_PREPROCESS, GSR_PROF_DEPTH_SORT,
+    GSR_PROF_EXPAND,
     GSR_PROF_SORT_PASS0,                      /* .. GSR_PROF_SORT_PASS0 + 7: individual onesweep launches */
     GSR_PROF_SLOTS = GSR_PROF_SORT_PASS0 + 8
 };

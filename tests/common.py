@@ -126,8 +126,9 @@ def run_ours(sc, cam, dL_dpix=None, dev="cuda"):
         out.update(views.geom_view(geom, P))
         out["radii"] = radii
         out.update(views.binning_view(binning, N))
-        out["keys"] = views.sorted_keys(out["tiles"], out["point_list"], out["depths"])   # reference's (tile << 32 | depth) keys
         out.update(views.image_view(img, cam.image_width, cam.image_height, False))
+        out["tiles"] = views.tiles_from_ranges(out["ranges"], N)
+        out["keys"] = views.sorted_keys(out["tiles"], out["point_list"], out["depths"])   # reference's (tile << 32 | depth) keys
     if dL_dpix is not None:
         g = _host.rasterize_gaussians_backward(
             d["bg"], d["means3D"], radii, d["colors_precomp"], d["scales"], d["rotations"], 1.0, d["cov3D_precomp"],
@@ -245,8 +246,9 @@ def run_ours_amr(sc, cam, stepped, interpolate, gaze=None, dev="cuda"):
     out.update(views.geom_view(gb, P))
     out["radii"] = radii
     out.update(views.binning_view(bb, N))
-    out["keys"] = views.sorted_keys(out["tiles"], out["point_list"], out["depths"])
     out.update(views.image_view(ib, cam.image_width, cam.image_height, True))
+    out["tiles"] = views.tiles_from_ranges(out["ranges"], N)
+    out["keys"] = views.sorted_keys(out["tiles"], out["point_list"], out["depths"])
     torch.cuda.synchronize()
     return out
 

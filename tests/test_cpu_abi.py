@@ -56,7 +56,8 @@ def test_version_and_size_queries():
         assert lib.gsr_higher_msb(n) == want
     g1, g2 = lib.gsr_geom_bytes(1000), lib.gsr_geom_bytes(2000)
     assert 0 < g1 < g2
-    assert lib.gsr_binning_bytes(0) > 0 and lib.gsr_binning_bytes(10_000) >= 16 * 10_000
+    assert lib.gsr_binning_bytes(0, 0, 1920, 1080, 0) > 0
+    assert lib.gsr_binning_bytes(10_000, 3_000, 1920, 1080, 0) >= 4 * 10_000 + 16 * 3_000
     base, amr = lib.gsr_image_bytes(1920, 1080, 0), lib.gsr_image_bytes(1920, 1080, 1)
     assert base >= 8 * 1920 * 1080 and amr >= 8 * 1920 * 1080
     assert lib.gsr_sort_temp_bytes(1) > 0
