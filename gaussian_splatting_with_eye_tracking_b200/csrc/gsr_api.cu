@@ -155,15 +155,15 @@ static int build_lists(const gsr_scene* sc, const gsr_camera* cam, int mode, gsr
     // (1) stable sort of the Gaussians by depth bits (invisible ones keyed 0xffffffff go last and emit nothing)
     {
         ProfScope ps(GSR_PROF_DEPTH_SORT, s);
-        launch_depth_keys(P, g.depths, g.tiles_touched, g.dkeys_a, s);
+        // compact the visible Gaussians (ascending index) into (dkeys_a, order), then 4 radix passes over those only
+        launch_compact_keys(g, P, g.dkeys_a, g.order, s);
         const SortPlan dplan = make_sort_plan(32);
-        // pass order is in -> b1 -> b2 -> ...; pick (out, tmp) so that no pass reads and writes the same array
-        uint32_t* kout = (dplan.passes & 1) ? g.dkeys_b : g.dkeys_a;
-        uint32_t* ktmp = (dplan.passes & 1) ? g.dkeys_a : g.dkeys_b;
-        rc = launch_onesweep32(g.dkeys_a, nullptr, kout, g.order, ktmp, g.order_tmp, P, dplan, g.sort_temp, g.sort_temp_bytes,
-                               /*hist_ready=*/false, &g.header->sort_error, -1, s);
+        if (dplan.passes & 1) { set_error("depth sort plan must have an even pass count"); return GSR_ERR_INVALID; }
+        // even pass count: keys a -> b -> a ..., values order -> order_tmp -> order ...; the result ends in (dkeys_a, order)
+        rc = launch_onesweep32(g.dkeys_a, g.order, g.dkeys_a, g.order, g.dkeys_b, g.order_tmp, P, dplan, g.sort_temp, g.sort_temp_bytes,
+                               /*hist_ready=*/false, &g.header->sort_error, -1, s, &g.header->num_visible);
         if (rc) return rc;
-        launch_order_block_sums(P, g.order, g.rects, g.oblock_sums, s);
+        launch_order_block_sums(P, &g.header->num_visible, g.order, g.rects, g.oblock_sums, s);
         launch_scan_u32(g.oblock_sums, g.oblock_offsets, g.nblocks, s);
     }
     if ((rc = check_last("depth sort", debug, s))) return rc;

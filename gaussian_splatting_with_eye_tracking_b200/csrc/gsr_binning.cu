@@ -48,23 +48,36 @@ SortPlan make_sort_plan_range(int begin_bit, int nbits) {
 // pair emission in depth order
 // ------------------------------------------------------------------------------------------------
 // The reference sorts N (tile, depth) pairs on 45+ key bits.  The same permutation is obtained far more cheaply
-// hierarchically: (1) stable-sort the P Gaussians by their 32-bit depth key (invisible ones carry 0xffffffff and
-// tiles_touched = 0), (2) emit every Gaussian's pairs in THAT order, (3) stable-partition the pairs by tile id
+// hierarchically: (1) stable-sort the VISIBLE Gaussians (compacted, ascending index) by their 32-bit depth key, (2) emit every Gaussian's pairs in THAT order, (3) stable-partition the pairs by tile id
 // (13-15 bits -> two radix passes on (u32 tile, u32 id) instead of five on (u64 key, u32 id)).  Ties between equal
 // depths inside a tile fall back to ascending Gaussian index in both schemes, so point_list is bit-identical.
-__global__ void __launch_bounds__(kPreBlock) depth_keys_kernel(int P, const float* __restrict__ depths,
-                                                               const uint32_t* __restrict__ tiles_touched, uint32_t* __restrict__ keys) {
+__global__ void __launch_bounds__(kPreBlock) compact_keys_kernel(int P, const float* __restrict__ depths,
+                                                                 const uint32_t* __restrict__ tiles_touched,
+                                                                 const uint32_t* __restrict__ vis_offsets,   // per 256-block, exclusive
+                                                                 uint32_t* __restrict__ keys, uint32_t* __restrict__ ids) {
+    __shared__ uint32_t s_w[kPreBlock / 32];
     const int i = blockIdx.x * kPreBlock + threadIdx.x;
-    if (i < P) keys[i] = tiles_touched[i] ? __float_as_uint(depths[i]) : 0xffffffffu;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const bool vis = (i < P) && tiles_touched[i] != 0;
+    const uint32_t m = __ballot_sync(0xffffffffu, vis);
+    if (lane == 0) s_w[wid] = __popc(m);
+    __syncthreads();
+    if (vis) {
+        uint32_t pos = vis_offsets[blockIdx.x] + __popc(m & ((1u << lane) - 1u));
+#pragma unroll
+        for (int k = 0; k < kPreBlock / 32; ++k) pos += (k < wid) ? s_w[k] : 0u;
+        keys[pos] = __float_as_uint(depths[i]);
+        ids[pos] = (uint32_t)i;
+    }
 }
 
 // per-256 block sums, in depth order, of the number of tile rows each Gaussian's rect spans (= runs it emits)
-__global__ void __launch_bounds__(kPreBlock) order_block_sums_kernel(int P, const uint32_t* __restrict__ order,
+__global__ void __launch_bounds__(kPreBlock) order_block_sums_kernel(const uint32_t* __restrict__ n_dev, const uint32_t* __restrict__ order,
                                                                      const uint2* __restrict__ rects, uint32_t* __restrict__ sums) {
     __shared__ uint32_t s_w[kPreBlock / 32];
-    const int j = blockIdx.x * kPreBlock + threadIdx.x;
+    const uint32_t j = blockIdx.x * kPreBlock + threadIdx.x;
     uint32_t v = 0;
-    if (j < P) { const uint32_t ry = rects[order[j]].y; v = (ry >> 16) - (ry & 0xffffu); }
+    if (j < __ldg(n_dev)) { const uint32_t ry = rects[order[j]].y; v = (ry >> 16) - (ry & 0xffffu); }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
     if ((threadIdx.x & 31) == 0) s_w[threadIdx.x >> 5] = v;
@@ -81,7 +94,7 @@ __global__ void __launch_bounds__(kPreBlock) order_block_sums_kernel(int P, cons
 //   rank of Gaussian j in tile (row, x) = number of runs of that row, earlier in depth order, that cover column x.
 // ------------------------------------------------------------------------------------------------
 struct EmitRunsParams {
-    int P;
+    const uint32_t* __restrict__ n_dev;          // number of depth-sorted (visible) Gaussians
     const uint32_t* __restrict__ order;          // depth-sorted Gaussian ids
     const uint2* __restrict__ rects;
     const uint32_t* __restrict__ block_offsets;  // [nblocks+1] exclusive run offsets of the sorted 256-blocks
@@ -98,9 +111,9 @@ __global__ void __launch_bounds__(kPreBlock) emit_runs_kernel(const EmitRunsPara
     const uint32_t base = __ldg(p.block_offsets + blockIdx.x);
     if (__ldg(p.block_offsets + blockIdx.x + 1) == base) return;        // nothing visible in this block (CTA-uniform)
     for (int i = tid; i < p.passes * kSortMaxRadix; i += kPreBlock) s_hist[i] = 0;
-    const int j = blockIdx.x * kPreBlock + tid;
+    const uint32_t j = blockIdx.x * kPreBlock + tid;
     uint32_t g = 0, x0 = 0, w = 0, y0 = 0, h = 0;
-    if (j < p.P) {
+    if (j < __ldg(p.n_dev)) {
         g = p.order[j];
         const uint2 r = p.rects[g];
         x0 = r.x & 0xffffu; w = (r.x >> 16) - x0; y0 = r.y & 0xffffu; h = (r.y >> 16) - y0;
@@ -137,20 +150,20 @@ static int num_sms() {
     return g_num_sms;
 }
 
-void launch_depth_keys(int P, const float* depths, const uint32_t* tiles_touched, uint32_t* keys, cudaStream_t s) {
-    depth_keys_kernel<<<(P + kPreBlock - 1) / kPreBlock, kPreBlock, 0, s>>>(P, depths, tiles_touched, keys);
+void launch_compact_keys(const GeomPtrs& g, int P, uint32_t* keys, uint32_t* ids, cudaStream_t s) {
+    compact_keys_kernel<<<(P + kPreBlock - 1) / kPreBlock, kPreBlock, 0, s>>>(P, g.depths, g.tiles_touched, g.block_offsets, keys, ids);
     count_launch();
 }
 
-void launch_order_block_sums(int P, const uint32_t* order, const uint2* rects, uint32_t* sums, cudaStream_t s) {
-    order_block_sums_kernel<<<(P + kPreBlock - 1) / kPreBlock, kPreBlock, 0, s>>>(P, order, rects, sums);
+void launch_order_block_sums(int P, const uint32_t* n_dev, const uint32_t* order, const uint2* rects, uint32_t* sums, cudaStream_t s) {
+    order_block_sums_kernel<<<(P + kPreBlock - 1) / kPreBlock, kPreBlock, 0, s>>>(n_dev, order, rects, sums);
     count_launch();
 }
 
 void launch_emit_runs(const GeomPtrs& g, int P, const uint32_t* order, const uint32_t* block_offsets, uint32_t* rkeys, uint32_t* rvals,
                       uint32_t* hist, const SortPlan& plan, cudaStream_t s) {
     EmitRunsParams p;
-    p.P = P; p.order = order; p.rects = g.rects; p.block_offsets = block_offsets; p.rkeys = rkeys; p.rvals = rvals; p.hist = hist;
+    p.n_dev = &g.header->num_visible; p.order = order; p.rects = g.rects; p.block_offsets = block_offsets; p.rkeys = rkeys; p.rvals = rvals; p.hist = hist;
     p.passes = plan.passes;
     p.shift0 = plan.shift[0]; p.bits0 = plan.bits[0];
     p.shift1 = plan.passes > 1 ? plan.shift[1] : 0; p.bits1 = plan.passes > 1 ? plan.bits[1] : 1;
@@ -163,7 +176,7 @@ void launch_emit_runs(const GeomPtrs& g, int P, const uint32_t* order, const uin
 // standalone digit histogram (keys that do not come out of emit_pairs_kernel: the depth sort, gsr_sort_pairs)
 // ------------------------------------------------------------------------------------------------
 template <typename KeyT>
-struct HistParams { const KeyT* keys; long long n; uint32_t* hist; int passes; int shift[kSortMaxPasses]; int bits[kSortMaxPasses]; };
+struct HistParams { const KeyT* keys; long long n; const uint32_t* n_dev; uint32_t* hist; int passes; int shift[kSortMaxPasses]; int bits[kSortMaxPasses]; };
 
 template <typename KeyT>
 __global__ void __launch_bounds__(256) sort_hist_kernel(const HistParams<KeyT> p) {
@@ -171,18 +184,22 @@ __global__ void __launch_bounds__(256) sort_hist_kernel(const HistParams<KeyT> p
     const int tid = threadIdx.x, lane = tid & 31;
     for (int i = tid; i < p.passes * kSortMaxRadix; i += 256) s_hist[i] = 0;
     __syncthreads();
+    const long long n = p.n_dev ? (long long)__ldg(p.n_dev) : p.n;
     const long long stride = (long long)gridDim.x * 256;
-    const long long n_round = (p.n + 31) / 32 * 32;
+    const long long n_round = (n + 31) / 32 * 32;
     for (long long i = (long long)blockIdx.x * 256 + tid; i < n_round; i += stride) {
-        const bool valid = i < p.n;
+        const bool valid = i < n;
         const KeyT key = valid ? p.keys[i] : (KeyT)0;
         const uint32_t act = __ballot_sync(0xffffffffu, valid);
         if (valid) {
-            for (int ps = 0; ps < p.passes; ++ps) {
-                const uint32_t d = (uint32_t)(key >> p.shift[ps]) & ((1u << p.bits[ps]) - 1u);
-                const uint32_t peers = __match_any_sync(act, d);
-                if (lane == (31 - __clz(peers))) atomicAdd(&s_hist[ps * kSortMaxRadix + d], (uint32_t)__popc(peers));
-            }
+            // low digits are close to uniform: plain shared atomics (few conflicts).  The most significant digit has a
+            // handful of distinct values (depth exponents, tile rows): aggregate equal digits in the warp first.
+            for (int ps = 0; ps + 1 < p.passes; ++ps)
+                atomicAdd(&s_hist[ps * kSortMaxRadix + ((uint32_t)(key >> p.shift[ps]) & ((1u << p.bits[ps]) - 1u))], 1u);
+            const int ps = p.passes - 1;
+            const uint32_t d = (uint32_t)(key >> p.shift[ps]) & ((1u << p.bits[ps]) - 1u);
+            const uint32_t peers = __match_any_sync(act, d);
+            if (lane == (31 - __clz(peers))) atomicAdd(&s_hist[ps * kSortMaxRadix + d], (uint32_t)__popc(peers));
         }
     }
     __syncthreads();
@@ -220,7 +237,8 @@ struct SweepParams {
     const KeyT* __restrict__ keys_in; KeyT* __restrict__ keys_out;
     const uint32_t* __restrict__ vals_in;    // nullptr: value = global index (first pass of an index sort)
     uint32_t* __restrict__ vals_out;
-    long long n; int shift; int bits;
+    long long n; const uint32_t* __restrict__ n_dev;   // n_dev != nullptr: the actual count lives on the device (<= n)
+    int shift; int bits;
     const uint32_t* __restrict__ bin_base;   // [RADIX] exclusive global offsets of this pass
     uint32_t* status;                        // [tiles][RADIX]
     uint32_t* tile_counter;
@@ -264,7 +282,9 @@ __global__ void __launch_bounds__(THREADS, MINB) onesweep_kernel(const SweepPara
     __syncthreads();
     const uint32_t tile = s_tile;
     const long long tile_base = (long long)tile * TILE;
-    const int count = (int)min((long long)TILE, p.n - tile_base);
+    const long long n_items = p.n_dev ? (long long)__ldg(p.n_dev) : p.n;
+    if (tile_base >= n_items) return;          // grid was sized for the upper bound (CTA-uniform exit; nobody waits on this tile)
+    const int count = (int)min((long long)TILE, n_items - tile_base);
     const uint32_t mask = (1u << p.bits) - 1u;
 
     // ---- load keys and values, warp-striped: item i of lane l sits at warp_base + i*32 + l
@@ -434,14 +454,14 @@ template <int RADIX> struct SweepDispatch<uint32_t, RADIX> {
 template <typename KeyT>
 int launch_onesweep_t(const KeyT* kin0, const uint32_t* vin0, KeyT* kout, uint32_t* vout, KeyT* ktmp, uint32_t* vtmp,
                       long long n, const SortPlan& plan, void* temp, size_t temp_bytes, bool hist_ready, uint32_t* err_flag,
-                      int prof_slot0, cudaStream_t s) {
+                      int prof_slot0, cudaStream_t s, const uint32_t* n_dev = nullptr) {
     if (n <= 0) return GSR_OK;
     if (n >= (1ll << 30)) { set_error("radix sort: n=%lld exceeds 2^30 pairs", n); return GSR_ERR_INVALID; }
     if (temp_bytes < sort_temp_bytes(n)) { set_error("radix sort: temp too small"); return GSR_ERR_ALLOC; }
     SortTemp t = carve_sort_temp(temp);
     if (!hist_ready) {
         cudaMemsetAsync(t.hist, 0, sizeof(uint32_t) * kSortMaxPasses * kSortMaxRadix, s);
-        HistParams<KeyT> hp; hp.keys = kin0; hp.n = n; hp.hist = t.hist; hp.passes = plan.passes;
+        HistParams<KeyT> hp; hp.keys = kin0; hp.n = n; hp.n_dev = n_dev; hp.hist = t.hist; hp.passes = plan.passes;
         for (int i = 0; i < kSortMaxPasses; ++i) { hp.shift[i] = i < plan.passes ? plan.shift[i] : 0; hp.bits[i] = i < plan.passes ? plan.bits[i] : 1; }
         long long want = (n + 256 * 16 - 1) / (256 * 16);
         int grid = (int)min((long long)num_sms() * 4, want); if (grid < 1) grid = 1;
@@ -458,7 +478,7 @@ int launch_onesweep_t(const KeyT* kin0, const uint32_t* vin0, KeyT* kout, uint32
     for (int ps = 0; ps < plan.passes; ++ps) {
         SweepParams<KeyT> sp;
         sp.keys_in = kin; sp.keys_out = kb[ps & 1]; sp.vals_in = vin; sp.vals_out = vb[ps & 1];
-        sp.n = n; sp.shift = plan.shift[ps]; sp.bits = plan.bits[ps];
+        sp.n = n; sp.n_dev = n_dev; sp.shift = plan.shift[ps]; sp.bits = plan.bits[ps];
         sp.bin_base = t.hist + ps * kSortMaxRadix; sp.status = t.status; sp.tile_counter = t.counters + ps; sp.err_flag = err_flag;
         const int radix = plan.bits[ps] <= 7 ? 128 : (plan.bits[ps] <= 8 ? 256 : 512);
         const int tile_items = radix == 128 ? SweepDispatch<KeyT, 128>::tile_items()
@@ -483,8 +503,8 @@ int launch_onesweep(const uint64_t* kin, const uint32_t* vin, uint64_t* kout, ui
 }
 int launch_onesweep32(const uint32_t* kin, const uint32_t* vin, uint32_t* kout, uint32_t* vout, uint32_t* ktmp, uint32_t* vtmp,
                       long long n, const SortPlan& plan, void* temp, size_t temp_bytes, bool hist_ready, uint32_t* err_flag,
-                      int prof_slot0, cudaStream_t s) {
-    return launch_onesweep_t<uint32_t>(kin, vin, kout, vout, ktmp, vtmp, n, plan, temp, temp_bytes, hist_ready, err_flag, prof_slot0, s);
+                      int prof_slot0, cudaStream_t s, const uint32_t* n_dev) {
+    return launch_onesweep_t<uint32_t>(kin, vin, kout, vout, ktmp, vtmp, n, plan, temp, temp_bytes, hist_ready, err_flag, prof_slot0, s, n_dev);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -582,19 +602,32 @@ __global__ void __launch_bounds__(256) chunk_count_kernel(const uint32_t* __rest
     for (int i = 0; i < 4; ++i) { const int x = 4 * tid + i; run += v[i]; if (x < tiles_x) out[x] = (uint32_t)run; }
 }
 
-// per tile row: exclusive prefix over the row's chunks for every column (in place) + per-tile totals
-__global__ void __launch_bounds__(256) row_scan_kernel(int tiles_x, const uint32_t* __restrict__ chunk_row_start,
-                                                       uint32_t* __restrict__ chunk_counts, uint32_t* __restrict__ tile_count) {
-    const int row = blockIdx.x;
+// per tile row: exclusive prefix over the row's chunks for every column (in place) + per-tile totals.
+// CTA = 32 chunk-lanes x 32 columns; a lane owns a contiguous slice of the row's chunks (two passes: slice sums, then
+// the running prefix), so the serial chain is chunks/32 long and every load is a coalesced 128 B row segment.
+__global__ void __launch_bounds__(1024) row_scan_kernel(int tiles_x, const uint32_t* __restrict__ chunk_row_start,
+                                                        uint32_t* __restrict__ chunk_counts, uint32_t* __restrict__ tile_count) {
+    __shared__ uint32_t s_part[32][33];
+    const int row = blockIdx.y;
+    const int xl = threadIdx.x & 31, l = threadIdx.x >> 5;
+    const int x = blockIdx.x * 32 + xl;
     const uint32_t c0 = chunk_row_start[row], c1 = chunk_row_start[row + 1];
-    for (int x = threadIdx.x; x < tiles_x; x += 256) {
-        uint32_t base = 0;
-#pragma unroll 8
-        for (uint32_t c = c0; c < c1; ++c) {
+    const uint32_t per = (c1 - c0 + 31) / 32;
+    const uint32_t a = min(c1, c0 + l * per), b = min(c1, a + per);
+    uint32_t sum = 0;
+    if (x < tiles_x)
+        for (uint32_t c = a; c < b; ++c) sum += chunk_counts[(size_t)c * tiles_x + x];
+    s_part[l][xl] = sum;
+    __syncthreads();
+    uint32_t base = 0, total = 0;
+#pragma unroll
+    for (int k = 0; k < 32; ++k) { const uint32_t v = s_part[k][xl]; base += (k < l) ? v : 0u; total += v; }
+    if (x < tiles_x) {
+        for (uint32_t c = a; c < b; ++c) {
             uint32_t* q = chunk_counts + (size_t)c * tiles_x + x;
             const uint32_t v = *q; *q = base; base += v;
         }
-        tile_count[(size_t)row * tiles_x + x] = base;
+        if (l == 0) tile_count[(size_t)row * tiles_x + x] = total;
     }
 }
 
@@ -676,7 +709,7 @@ void launch_expand_runs(const BinPtrs& b, const uint32_t* rkeys_sorted, const ui
         ProfScope ps(prof_ranges, s);
         chunk_table_kernel<<<1, 1024, 0, s>>>(rkeys_sorted, (uint32_t)R, tiles_y, b.row_start, b.chunk_row_start);
         chunk_count_kernel<<<grid, 256, sizeof(int) * (tiles_x + 1), s>>>(rkeys_sorted, tiles_x, tiles_y, b.chunk_row_start, b.row_start, b.chunk_counts);
-        row_scan_kernel<<<tiles_y, 256, 0, s>>>(tiles_x, b.chunk_row_start, b.chunk_counts, b.tile_start);
+        row_scan_kernel<<<dim3((tiles_x + 31) / 32, tiles_y), 1024, 0, s>>>(tiles_x, b.chunk_row_start, b.chunk_counts, b.tile_start);
         tile_scan_kernel<<<1, 1024, 0, s>>>(b.tile_start, num_tiles, ranges, n_intersections);
         count_launch(4);
     }

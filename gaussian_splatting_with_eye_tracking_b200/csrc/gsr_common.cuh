@@ -41,13 +41,14 @@ struct GeomHeader {      // lives at the start of the (aligned) geometry buffer,
     uint32_t num_rendered;   // = sum(tiles_touched); reference reads point_offsets[P-1] (rasterizer_impl.cu:281)
     uint32_t sort_error;     // set by the radix-sort watchdog
     uint32_t num_runs;       // = sum over visible Gaussians of the tile rows their rect spans ((Gaussian, row) runs)
-    uint32_t pad[59];
+    uint32_t num_visible;    // Gaussians with tiles_touched > 0: only these are depth-sorted
+    uint32_t pad[58];
 };
 static_assert(sizeof(GeomHeader) == 256, "header is one alignment unit");
 
 struct GeomLayout {
     size_t header, depths, clamped, radii, means2D, cov3D, conic_opacity, rgb, tiles_touched, rects,
-           block_sums, block_sums_r, block_offsets, dkeys_a, dkeys_b, order_tmp, order, oblock_sums, oblock_offsets, sort_temp, total;
+           block_sums, block_sums_r, block_sums_v, block_offsets, dkeys_a, dkeys_b, order_tmp, order, oblock_sums, oblock_offsets, sort_temp, total;
     int nblocks;
     __host__ __device__ explicit GeomLayout(int P) {
         nblocks = (P + kPreBlock - 1) / kPreBlock;
@@ -64,6 +65,7 @@ struct GeomLayout {
         rects = o;         o = align_up(o + sizeof(uint2) * (size_t)P);
         block_sums = o;    o = align_up(o + sizeof(uint32_t) * (size_t)(nblocks + 1));
         block_sums_r = o;  o = align_up(o + sizeof(uint32_t) * (size_t)(nblocks + 1));
+        block_sums_v = o;  o = align_up(o + sizeof(uint32_t) * (size_t)(nblocks + 1));
         block_offsets = o; o = align_up(o + sizeof(uint32_t) * (size_t)(nblocks + 1));
         // depth sort of the Gaussians (keys ping-pong, index ping-pong) and the scan in sorted order
         dkeys_a = o;       o = align_up(o + sizeof(uint32_t) * (size_t)P);
@@ -80,7 +82,7 @@ struct GeomLayout {
 struct GeomPtrs {
     GeomHeader* header;
     float* depths; unsigned char* clamped; int* radii; float2* means2D; float* cov3D;
-    float4* conic_opacity; float* rgb; uint32_t* tiles_touched; uint2* rects; uint32_t* block_sums; uint32_t* block_sums_r;
+    float4* conic_opacity; float* rgb; uint32_t* tiles_touched; uint2* rects; uint32_t* block_sums; uint32_t* block_sums_r; uint32_t* block_sums_v;
     uint32_t* block_offsets;
     uint32_t *dkeys_a, *dkeys_b, *order_tmp, *order, *oblock_sums, *oblock_offsets; void* sort_temp; size_t sort_temp_bytes;
     int nblocks;
@@ -104,6 +106,7 @@ inline GeomPtrs geom_ptrs(const void* buf, int P) {
     g.rects = (uint2*)(b + L.rects);
     g.block_sums = (uint32_t*)(b + L.block_sums);
     g.block_sums_r = (uint32_t*)(b + L.block_sums_r);
+    g.block_sums_v = (uint32_t*)(b + L.block_sums_v);
     g.block_offsets = (uint32_t*)(b + L.block_offsets);
     g.dkeys_a = (uint32_t*)(b + L.dkeys_a); g.dkeys_b = (uint32_t*)(b + L.dkeys_b);
     g.order_tmp = (uint32_t*)(b + L.order_tmp); g.order = (uint32_t*)(b + L.order);
@@ -249,8 +252,9 @@ struct SortPlan {
 SortPlan make_sort_plan(int end_bit);
 
 SortPlan make_sort_plan_range(int begin_bit, int nbits);
-void launch_depth_keys(int P, const float* depths, const uint32_t* tiles_touched, uint32_t* keys, cudaStream_t s);
-void launch_order_block_sums(int P, const uint32_t* order, const uint2* rects, uint32_t* sums, cudaStream_t s);
+// compaction of the visible Gaussians: keys[k] = depth bits, ids[k] = index, k = rank among the visible ones
+void launch_compact_keys(const GeomPtrs& g, int P, uint32_t* keys, uint32_t* ids, cudaStream_t s);
+void launch_order_block_sums(int P, const uint32_t* n_dev, const uint32_t* order, const uint2* rects, uint32_t* sums, cudaStream_t s);
 void launch_scan_u32(const uint32_t* sums, uint32_t* offsets, int n, cudaStream_t s);
 // run-length binning (gsr_binning.cu): emit (Gaussian,row) runs in depth order -> [sort by row] -> expand into per-tile lists
 void launch_emit_runs(const GeomPtrs& g, int P, const uint32_t* order, const uint32_t* block_offsets, uint32_t* rkeys, uint32_t* rvals,
@@ -265,7 +269,7 @@ int launch_onesweep(const uint64_t* kin, const uint32_t* vin, uint64_t* kout, ui
                     long long n, const SortPlan& plan, void* temp, size_t temp_bytes, bool hist_ready, uint32_t* err_flag, cudaStream_t s);
 int launch_onesweep32(const uint32_t* kin, const uint32_t* vin, uint32_t* kout, uint32_t* vout, uint32_t* ktmp, uint32_t* vtmp,
                       long long n, const SortPlan& plan, void* temp, size_t temp_bytes, bool hist_ready, uint32_t* err_flag,
-                      int prof_slot0, cudaStream_t s);
+                      int prof_slot0, cudaStream_t s, const uint32_t* n_dev = nullptr);   // n_dev: actual count on the device (<= n)
 uint32_t* sort_hist_ptr(void* temp);
 void set_sort_variant(int v);
 

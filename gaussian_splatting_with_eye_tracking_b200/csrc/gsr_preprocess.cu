@@ -47,6 +47,7 @@ struct PreFwdParams {
     uint2* __restrict__ rects;              // (x0 | x1 << 16, y0 | y1 << 16) tile rect, (0,0) when nothing is touched
     uint32_t* __restrict__ block_sums;
     uint32_t* __restrict__ block_sums_r;    // per-CTA sum of tile rows spanned (runs)
+    uint32_t* __restrict__ block_sums_v;    // per-CTA number of visible Gaussians
     GeomHeader* header;
     int prefiltered;
     int band_row0, band_row1;
@@ -204,7 +205,7 @@ __device__ __forceinline__ float3 cov2d_from_cov3d(float tx, float ty, float tz,
 
 __global__ void __launch_bounds__(kPreBlock, 4) preprocess_fwd_kernel(const PreFwdParams p) {
     __shared__ float sV[16], sPm[16], sCam[3];
-    __shared__ uint32_t s_warp_sum[kPreBlock / 32], s_warp_sum_r[kPreBlock / 32];
+    __shared__ uint32_t s_warp_sum[kPreBlock / 32], s_warp_sum_r[kPreBlock / 32], s_warp_sum_v[kPreBlock / 32];
     const int tid = threadIdx.x;
     if (tid < 16) { sV[tid] = p.viewmatrix[tid]; sPm[tid] = p.projmatrix[tid]; }
     if (tid < 3) sCam[tid] = p.cam_pos[tid];
@@ -289,16 +290,18 @@ __global__ void __launch_bounds__(kPreBlock, 4) preprocess_fwd_kernel(const PreF
 
     // CTA sum of tiles_touched -> block_sums[blockIdx.x] (first level of the scan)
     uint32_t v = touched, vr = rows;
+    const uint32_t vv = __popc(__ballot_sync(0xffffffffu, touched != 0));
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) { v += __shfl_xor_sync(0xffffffffu, v, o); vr += __shfl_xor_sync(0xffffffffu, vr, o); }
-    if ((tid & 31) == 0) { s_warp_sum[tid >> 5] = v; s_warp_sum_r[tid >> 5] = vr; }
+    if ((tid & 31) == 0) { s_warp_sum[tid >> 5] = v; s_warp_sum_r[tid >> 5] = vr; s_warp_sum_v[tid >> 5] = vv; }
     __syncthreads();
     if (tid == 0) {
-        uint32_t s = 0, sr = 0;
+        uint32_t s = 0, sr = 0, sv = 0;
 #pragma unroll
-        for (int w = 0; w < kPreBlock / 32; ++w) { s += s_warp_sum[w]; sr += s_warp_sum_r[w]; }
+        for (int w = 0; w < kPreBlock / 32; ++w) { s += s_warp_sum[w]; sr += s_warp_sum_r[w]; sv += s_warp_sum_v[w]; }
         p.block_sums[blockIdx.x] = s;
         p.block_sums_r[blockIdx.x] = sr;
+        p.block_sums_v[blockIdx.x] = sv;
     }
 }
 
@@ -313,7 +316,7 @@ void launch_preprocess(const PreprocessArgs& a, const GeomPtrs& g, cudaStream_t 
     p.tile = a.tile; p.grid_x = a.grid_x; p.grid_y = a.grid_y;
     p.radii = a.radii; p.depths = g.depths; p.clamped = g.clamped; p.means2D = g.means2D; p.cov3D = g.cov3D;
     p.conic_opacity = g.conic_opacity; p.rgb = g.rgb; p.tiles_touched = g.tiles_touched;
-    p.rects = g.rects; p.block_sums_r = g.block_sums_r;
+    p.rects = g.rects; p.block_sums_r = g.block_sums_r; p.block_sums_v = g.block_sums_v;
     p.block_sums = g.block_sums; p.header = g.header; p.prefiltered = a.prefiltered ? 1 : 0;
     p.band_row0 = a.band_row0; p.band_row1 = a.band_row1;
     preprocess_fwd_kernel<<<g.nblocks, kPreBlock, 0, s>>>(p);
@@ -324,18 +327,21 @@ void launch_preprocess(const PreprocessArgs& a, const GeomPtrs& g, cudaStream_t 
 // scan of the per-CTA sums: one CTA, exclusive offsets + grand total into the header.
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(1024) block_scan_kernel(const uint32_t* __restrict__ sums, uint32_t* __restrict__ offsets,
-                                                          int n, GeomHeader* header, uint32_t P, const uint32_t* __restrict__ sums_r) {
+                                                          int n, GeomHeader* header, uint32_t P, const uint32_t* __restrict__ sums_t,
+                                                          const uint32_t* __restrict__ sums_r) {
+    // offsets = exclusive scan of sums (+ grand total at [n]).  With a header: sums = visible counts, and the plain totals
+    // of sums_t (tiles touched -> num_rendered) and sums_r (tile rows -> num_runs) are taken on the way.
     __shared__ uint32_t s_warp[32];
-    __shared__ uint32_t s_carry, s_total_r;
+    __shared__ uint32_t s_carry, s_total_t, s_total_r;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-    if (tid == 0) { s_carry = 0; s_total_r = 0; }
+    if (tid == 0) { s_carry = 0; s_total_t = 0; s_total_r = 0; }
     __syncthreads();
-    if (sums_r != nullptr) {          // plain total of the second array (number of runs)
-        uint32_t t = 0;
-        for (int i = tid; i < n; i += 1024) t += sums_r[i];
+    if (header != nullptr) {
+        uint32_t t = 0, r = 0;
+        for (int i = tid; i < n; i += 1024) { t += sums_t[i]; r += sums_r[i]; }
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
-        if (lane == 0 && t) atomicAdd(&s_total_r, t);
+        for (int o = 16; o > 0; o >>= 1) { t += __shfl_xor_sync(0xffffffffu, t, o); r += __shfl_xor_sync(0xffffffffu, r, o); }
+        if (lane == 0) { if (t) atomicAdd(&s_total_t, t); if (r) atomicAdd(&s_total_r, r); }
         __syncthreads();
     }
     for (int base = 0; base < n; base += 1024) {
@@ -362,17 +368,20 @@ __global__ void __launch_bounds__(1024) block_scan_kernel(const uint32_t* __rest
     }
     if (tid == 0) {
         offsets[n] = s_carry;
-        if (header) { header->magic = kGeomMagic; header->P = P; header->num_rendered = s_carry; header->num_runs = s_total_r; }   // sort_error: zeroed by the host memset
+        if (header) {   // sort_error: zeroed by the host memset
+            header->magic = kGeomMagic; header->P = P; header->num_rendered = s_total_t; header->num_runs = s_total_r;
+            header->num_visible = s_carry;
+        }
     }
 }
 
 void launch_block_scan(const GeomPtrs& g, int P, cudaStream_t s) {
-    block_scan_kernel<<<1, 1024, 0, s>>>(g.block_sums, g.block_offsets, g.nblocks, g.header, (uint32_t)P, g.block_sums_r);
+    block_scan_kernel<<<1, 1024, 0, s>>>(g.block_sums_v, g.block_offsets, g.nblocks, g.header, (uint32_t)P, g.block_sums, g.block_sums_r);
     count_launch();
 }
 
 void launch_scan_u32(const uint32_t* sums, uint32_t* offsets, int n, cudaStream_t s) {
-    block_scan_kernel<<<1, 1024, 0, s>>>(sums, offsets, n, nullptr, 0u, nullptr);
+    block_scan_kernel<<<1, 1024, 0, s>>>(sums, offsets, n, nullptr, 0u, nullptr, nullptr);
     count_launch();
 }
 

@@ -169,8 +169,8 @@ typedef struct gsr_geom_view {
     const float* conic_opacity;     /* [P,4] */
     const float* rgb;               /* [P,3] */
     const uint32_t* tiles_touched;  /* [P]   */
-    const uint32_t* block_offsets;  /* [ceil(P/256)] exclusive offsets of 256-Gaussian blocks */
-    const uint32_t* depth_order;    /* [P] Gaussian ids sorted by depth bits (invisible last)  */
+    const uint32_t* block_offsets;  /* [ceil(P/256)+1] exclusive counts of VISIBLE Gaussians per 256-block */
+    const uint32_t* depth_order;    /* [num_visible] visible Gaussian ids, stable-sorted by depth bits     */
     const uint32_t* num_rendered;   /* [1]   */
 } gsr_geom_view;
 
