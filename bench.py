@@ -10,7 +10,7 @@ SURVEY 8(d)), cycling through 8 cameras on a ring.  Rank 0 prints ONE JSON line:
              allocations and the one D2H of num_rendered are inside, as in the reference's protocol, fps_test.py:50-65)
   e2e        the same through the public Python API (GaussianRasterizer module) with the per-step inputs (camera
              matrices) copied from pinned host memory and the rendered frame copied back to pinned host memory
-  roofline   the onesweep radix pass (dominant HBM-bound kernel): algorithmic bytes per launch / CUDA-event time
+  roofline   preprocess_fwd_kernel (dominant HBM-bound kernel): algorithmic bytes per launch / CUDA-event time
   cpu_baseline  the CPU oracle port rendering one frame of the same workload on all host cores
   extra      fwd+bwd ms/view, AMR single-pass / 5-step / gaze-foveated FPS, per-stage device times, the reference
              CUDA rasterizer timed in the same run, DP training-step throughput (NCCL all-reduce when N > 1)
@@ -34,7 +34,14 @@ sys.path.insert(0, ROOT)
 
 import torch  # noqa: E402
 
-ALG_BYTES_PER_PAIR_PER_PASS = 16      # 4 B tile id + 4 B Gaussian id, read once and written once per onesweep pass
+# preprocess_fwd_kernel, the dominant HBM-bound kernel: algorithmic bytes per unit
+ALG_BYTES_VISIBLE = 311               # 236 B of parameters read + 75 B of per-Gaussian results written
+ALG_BYTES_CULLED = 20                 # 12 B mean read + radius / tiles_touched written
+
+
+# dram__bytes_read.sum + dram__bytes_write.sum of one preprocess_fwd_kernel launch from the committed `ncu --set full`
+# capture (profiles/r1_v5_ncu_full_fwd_summary.csv; camera 0 of the C3 workload), keyed by the Gaussian count
+NCU_TRAFFIC_BYTES = {3_000_000: 553_534_208 + 207_832_064}
 
 
 def parse_args():
@@ -311,6 +318,7 @@ def measure(impl, args, d, cams, rank, world, timer, full):
         out["stages_ms"] = {k: round(v[0] / max(1, v[1]), 5) for k, v in prof.items()}
         out["stage_counts"] = {k: v[1] for k, v in prof.items()}
         out["mean_num_rendered"] = nr / K
+        out["mean_visible"] = sum(int((impl.forward_c(cam_of(Wm + i))[2] > 0).sum()) for i in range(min(K, ncam))) / min(K, ncam)
     del last["r"]
 
     # ---- e2e: public API, camera from pinned host memory, frame back to pinned host memory
@@ -456,19 +464,18 @@ def main():
         line.update(value=m["value"], ms_per_step=m["ms_per_step"], e2e=m["e2e"], gpu_launches=m["gpu_launches"])
         N = m["mean_num_rendered"]
         st = m["stages_ms"]
-        passes = [k for k in st if k.startswith("sort_pass")]
-        if passes and N:
-            t_pass = sum(st[k] for k in passes) / len(passes)
-            ach = ALG_BYTES_PER_PAIR_PER_PASS * N / (t_pass * 1e-3) / 1e9
-            line["roofline"] = {"kernel": "onesweep_kernel<u32> (one radix pass of the (tile, Gaussian) pair partition)", "bound": "hbm",
-                                "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None,
-                                "peak_source": peak_src, "launch_ms": t_pass, "pairs_per_launch": N,
-                                "alg_bytes_per_pair": ALG_BYTES_PER_PAIR_PER_PASS, "passes": len(passes)}
+        if "preprocess" in st:
+            vis = m["mean_visible"]
+            alg = ALG_BYTES_VISIBLE * vis + ALG_BYTES_CULLED * (args.gaussians - vis)
+            ach = alg / (st["preprocess"] * 1e-3) / 1e9
+            line["roofline"] = {"kernel": "preprocess_fwd_kernel (projection, cov3D->cov2D, SH->RGB, radius, tile rect; one launch per step)",
+                                "bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                                "traffic": NCU_TRAFFIC_BYTES.get(args.gaussians), "peak_source": peak_src, "launch_ms": st["preprocess"],
+                                "alg_bytes_per_launch": alg, "visible_per_launch": vis, "culled_per_launch": args.gaussians - vis,
+                                "alg_bytes_per_visible": ALG_BYTES_VISIBLE, "alg_bytes_per_culled": ALG_BYTES_CULLED}
         extra = {k: m[k] for k in ("num_rendered", "stages_ms", "fwd_bwd_ms_per_view", "bwd_stages_ms", "dp_train", "amr") if k in m}
         extra["pairs_per_gaussian_mean"] = N / args.gaussians
-        if "preprocess" in st:
-            vis_bytes = 311.0 * args.gaussians      # upper bound: every Gaussian counted as visible
-            extra["preprocess_gbs_upper"] = vis_bytes / (st["preprocess"] * 1e-3) / 1e9
+        extra["visible_mean"] = m.get("mean_visible")
         if full and rank == 0 and eff_world == 1:
             from oracle import ref_cuda
             if ref_cuda.available(False):

@@ -38,16 +38,47 @@ def _p(t):
 
 
 class _Arena:
-    """Receives the library's allocation requests and keeps the byte tensors (geom / binning / image)."""
+    """Receives the library's allocation requests and keeps the byte tensors (geom / binning / image).
+
+    One module-level C callback serves every call: the `user` pointer carries a ticket into `_LIVE`, so no per-call
+    ctypes thunk is created and -- more importantly -- no reference cycle (arena -> thunk -> bound method -> arena)
+    keeps the work buffers alive until Python's cyclic GC happens to run (measured: 35 GB of reserved memory and 2.6
+    cudaMalloc per frame with the cyclic version)."""
+
+    _LIVE = {}
+    _next_ticket = 1
 
     def __init__(self, device):
         self.device = device
         self.bufs = {}
-        self.cb = _capi.ALLOC_FN(self._alloc)
+        self.ticket = None
 
-    def _alloc(self, _user, which, nbytes):
+    def __enter__(self):
+        self.ticket = _Arena._next_ticket
+        _Arena._next_ticket += 1
+        _Arena._LIVE[self.ticket] = self
+        return self
+
+    def __exit__(self, *exc):
+        _Arena._LIVE.pop(self.ticket, None)
+        return False
+
+    @property
+    def user(self):
+        return C.c_void_p(self.ticket)
+
+    @staticmethod
+    def _bucket(nbytes: int) -> int:
+        """Round large requests up to a quarter-octave grid (<= 25 % slack): the binning buffer's size follows the
+        per-view pair count, and a handful of distinct sizes keeps torch's caching allocator in a steady state."""
+        if nbytes <= (1 << 20):
+            return nbytes
+        step = 1 << (nbytes.bit_length() - 3)
+        return (nbytes + step - 1) // step * step
+
+    def alloc(self, which, nbytes):
         try:
-            t = torch.empty(int(nbytes), dtype=torch.uint8, device=self.device)
+            t = torch.empty(self._bucket(int(nbytes)), dtype=torch.uint8, device=self.device)
         except Exception:  # out of memory etc.: report through the status code
             return None
         self.bufs[int(which)] = t
@@ -56,6 +87,14 @@ class _Arena:
     def get(self, which):
         t = self.bufs.get(which)
         return t if t is not None else torch.empty(0, dtype=torch.uint8, device=self.device)
+
+
+def _alloc_trampoline(user, which, nbytes):
+    arena = _Arena._LIVE.get(int(user or 0))
+    return arena.alloc(which, nbytes) if arena is not None else None
+
+
+_ALLOC_CB = _capi.ALLOC_FN(_alloc_trampoline)
 
 
 def _scene_camera(background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp, viewmatrix,
@@ -105,10 +144,10 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
     with torch.cuda.device(dev):
         out_color = torch.empty((3, int(image_height), int(image_width)), dtype=torch.float32, device=dev)
         radii = torch.empty((P,), dtype=torch.int32, device=dev)
-        arena = _Arena(dev)
         rendered = C.c_int(0)
-        rc = lib.gsr_forward(C.byref(sc), C.byref(cam), arena.cb, None, _p(out_color), _p(radii) if P else None,
-                             C.byref(rendered), 1 if debug else 0, _stream())
+        with _Arena(dev) as arena:
+            rc = lib.gsr_forward(C.byref(sc), C.byref(cam), _ALLOC_CB, arena.user, _p(out_color), _p(radii) if P else None,
+                                 C.byref(rendered), 1 if debug else 0, _stream())
         _capi.check(rc, "gsr_forward")
     return (int(rendered.value), out_color, radii, arena.get(_capi.GSR_BUF_GEOM), arena.get(_capi.GSR_BUF_BINNING),
             arena.get(_capi.GSR_BUF_IMAGE))
@@ -181,16 +220,16 @@ def rasterize_gaussians_amr(background, means3D, colors, opacity, scales, rotati
         radii = torch.empty((P,), dtype=torch.int32, device=dev)
         if step >= 1:
             radii.zero_()          # steps >= 1 do not preprocess; the reference returns its zero-filled radii
-        arena = _Arena(dev)
         rendered = C.c_int(0)
         precomp = _dev_tensor(out_color_precomp, "out_color_precomp")
         gp = geomBuffer_precomp if (geomBuffer_precomp is not None and geomBuffer_precomp.numel()) else None
         bp = binningBuffer_precomp if (binningBuffer_precomp is not None and binningBuffer_precomp.numel()) else None
         ip = imageBuffer_precomp if (imageBuffer_precomp is not None and imageBuffer_precomp.numel()) else None
-        rc = lib.gsr_amr_forward(C.byref(sc), C.byref(cam), step, _p(precomp), _p(gp), _p(bp), _p(ip),
-                                 1 if interpolate_image else 0, C.byref(gz) if gz is not None else None, arena.cb, None,
-                                 _p(out_color), _p(radii) if (P and step < 1) else None, C.byref(rendered),
-                                 1 if debug else 0, _stream())
+        with _Arena(dev) as arena:
+            rc = lib.gsr_amr_forward(C.byref(sc), C.byref(cam), step, _p(precomp), _p(gp), _p(bp), _p(ip),
+                                     1 if interpolate_image else 0, C.byref(gz) if gz is not None else None, _ALLOC_CB,
+                                     arena.user, _p(out_color), _p(radii) if (P and step < 1) else None, C.byref(rendered),
+                                     1 if debug else 0, _stream())
         _capi.check(rc, "gsr_amr_forward")
     if step > 0:   # the returned buffers ARE the passed-in ones (A/rasterize_points.cu:182-191)
         return int(rendered.value), out_color, radii, geomBuffer_precomp, binningBuffer_precomp, imageBuffer_precomp
