@@ -180,6 +180,7 @@ static int build_lists(const gsr_scene* sc, const gsr_camera* cam, int mode, gsr
     BinPtrs b = bin_ptrs(bin, N, R, im.tiles_x, im.tiles_y);
 
     const uint32_t* rk_sorted = b.rkeyB; const uint32_t* rv_sorted = b.rvalB;
+    const uint32_t* row_offsets = nullptr;
     if (R > 0) {
         // (2) emit one run per (Gaussian, tile row) in depth order, (3) stable partition of the runs by row
         const SortPlan plan = make_sort_plan_range(kRunRowShift, (int)higher_msb((unsigned)im.tiles_y));
@@ -199,9 +200,10 @@ static int build_lists(const gsr_scene* sc, const gsr_camera* cam, int mode, gsr
         }
         if (rc) return rc;
         if ((rc = check_last("radix sort", debug, s))) return rc;
+        if (plan.passes == 1 && plan.shift[0] == kRunRowShift) row_offsets = hist;   // exclusive digit offsets == first run of every row
     }
     // (4) expand the row-sorted runs into the per-tile lists; also yields tile ranges and AMR intersection counts
-    launch_expand_runs(b, rk_sorted, rv_sorted, R, im.tiles_x, im.tiles_y, im.ranges, im.n_intersections, GSR_PROF_RANGES, GSR_PROF_EXPAND, s);
+    launch_expand_runs(b, rk_sorted, rv_sorted, R, im.tiles_x, im.tiles_y, row_offsets, im.ranges, im.n_intersections, GSR_PROF_RANGES, GSR_PROF_EXPAND, s);
     if ((rc = check_last("expand runs", debug, s))) return rc;
     *geom_out = geom; *bin_out = bin; *img_out = img; *N_out = (int)N;
     return GSR_OK;

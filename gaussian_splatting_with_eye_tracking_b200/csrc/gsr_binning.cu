@@ -532,12 +532,14 @@ __device__ __forceinline__ uint32_t cta1024_exclusive_scan(uint32_t v, uint32_t*
 
 // row_start[r] = first sorted run of tile row r (binary search on the row field); chunk_row_start[r] = first chunk of row r
 __global__ void __launch_bounds__(1024) chunk_table_kernel(const uint32_t* __restrict__ rkeys, uint32_t R, int tiles_y,
+                                                           const uint32_t* __restrict__ row_offsets,   // sort's digit offsets or nullptr
                                                            uint32_t* __restrict__ row_start, uint32_t* __restrict__ chunk_row_start) {
     __shared__ uint32_t s_warp[32];
     const int tid = threadIdx.x;
     for (int r = tid; r <= tiles_y; r += 1024) {
         uint32_t lo = 0, hi = R;
-        while (lo < hi) { const uint32_t mid = lo + ((hi - lo) >> 1); if ((__ldg(rkeys + mid) >> kRunRowShift) < (uint32_t)r) lo = mid + 1; else hi = mid; }
+        if (row_offsets != nullptr) lo = (r < tiles_y) ? row_offsets[r] : R;     // one-pass row sort: the digit IS the row
+        else while (lo < hi) { const uint32_t mid = lo + ((hi - lo) >> 1); if ((__ldg(rkeys + mid) >> kRunRowShift) < (uint32_t)r) lo = mid + 1; else hi = mid; }
         row_start[r] = lo;
     }
     __syncthreads();
@@ -635,18 +637,19 @@ __global__ void __launch_bounds__(1024) row_scan_kernel(int tiles_x, const uint3
 __global__ void __launch_bounds__(1024) tile_scan_kernel(uint32_t* __restrict__ tile_start, int num_tiles, uint2* __restrict__ ranges,
                                                          uint32_t* __restrict__ n_intersections) {
     __shared__ uint32_t s_warp[32];
-    uint32_t carry = 0;
-    for (int base = 0; base < num_tiles; base += 1024) {
-        const int t = base + threadIdx.x;
-        const uint32_t cnt = (t < num_tiles) ? tile_start[t] : 0u;
-        uint32_t tot;
-        const uint32_t st = carry + cta1024_exclusive_scan(cnt, s_warp, &tot);
-        if (t < num_tiles) {
-            tile_start[t] = st;
-            ranges[t] = cnt ? make_uint2(st, st + cnt) : make_uint2(0u, 0u);   // empty tiles keep the reference's memset value
-            if (n_intersections) n_intersections[t] = cnt;
-        }
-        carry += tot;
+    const int tid = threadIdx.x;
+    const int per = (num_tiles + 1023) / 1024;
+    const int begin = min(num_tiles, tid * per), end = min(num_tiles, begin + per);
+    uint32_t local = 0;
+    for (int t = begin; t < end; ++t) local += tile_start[t];
+    uint32_t tot;
+    uint32_t st = cta1024_exclusive_scan(local, s_warp, &tot);
+    for (int t = begin; t < end; ++t) {
+        const uint32_t cnt = tile_start[t];
+        tile_start[t] = st;
+        ranges[t] = cnt ? make_uint2(st, st + cnt) : make_uint2(0u, 0u);   // empty tiles keep the reference's memset value
+        if (n_intersections) n_intersections[t] = cnt;
+        st += cnt;
     }
 }
 
@@ -702,12 +705,12 @@ __global__ void __launch_bounds__(kExpandThreads) expand_runs_kernel(const uint3
 }
 
 void launch_expand_runs(const BinPtrs& b, const uint32_t* rkeys_sorted, const uint32_t* rvals_sorted, long long R, int tiles_x, int tiles_y,
-                        uint2* ranges, uint32_t* n_intersections, int prof_ranges, int prof_expand, cudaStream_t s) {
+                        const uint32_t* row_offsets, uint2* ranges, uint32_t* n_intersections, int prof_ranges, int prof_expand, cudaStream_t s) {
     const int num_tiles = tiles_x * tiles_y;
     const unsigned grid = (unsigned)b.max_chunks;
     {
         ProfScope ps(prof_ranges, s);
-        chunk_table_kernel<<<1, 1024, 0, s>>>(rkeys_sorted, (uint32_t)R, tiles_y, b.row_start, b.chunk_row_start);
+        chunk_table_kernel<<<1, 1024, 0, s>>>(rkeys_sorted, (uint32_t)R, tiles_y, row_offsets, b.row_start, b.chunk_row_start);
         chunk_count_kernel<<<grid, 256, sizeof(int) * (tiles_x + 1), s>>>(rkeys_sorted, tiles_x, tiles_y, b.chunk_row_start, b.row_start, b.chunk_counts);
         row_scan_kernel<<<dim3((tiles_x + 31) / 32, tiles_y), 1024, 0, s>>>(tiles_x, b.chunk_row_start, b.chunk_counts, b.tile_start);
         tile_scan_kernel<<<1, 1024, 0, s>>>(b.tile_start, num_tiles, ranges, n_intersections);

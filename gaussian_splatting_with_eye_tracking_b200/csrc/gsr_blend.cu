@@ -88,9 +88,9 @@ struct FwdParams {
 };
 
 __global__ void __launch_bounds__(kBlendThreads) blend_fwd_kernel(const FwdParams p) {
-    __shared__ float4 s_a[kBlendThreads];     // x, y, conic.x, conic.y
-    __shared__ float4 s_b[kBlendThreads];     // conic.z, opacity, r, g
-    __shared__ float2 s_c[kBlendThreads];     // b, list position (1-based, as float bits)
+    // staged entry = 3 x float4: (x, y, conic.x, conic.y) (conic.z, opacity, r, g) (b, 1-based list position, -, -):
+    // one base pointer, immediate offsets, 128-bit broadcast loads
+    __shared__ float4 s_ent[3 * kBlendThreads];
     __shared__ uint32_t s_wcnt[kBlendThreads / 32];
     __shared__ uint32_t s_count;
 
@@ -121,9 +121,9 @@ __global__ void __launch_bounds__(kBlendThreads) blend_fwd_kernel(const FwdParam
         const bool keep = nxt_valid && !cannot_touch(nxt.xy, nxt.co, rx0, ry0, rx1, ry1);
         const int slot = compact_slot(keep, s_wcnt, &s_count);
         if (slot >= 0) {
-            s_a[slot] = make_float4(nxt.xy.x, nxt.xy.y, nxt.co.x, nxt.co.y);
-            s_b[slot] = make_float4(nxt.co.z, nxt.co.w, nxt.col.x, nxt.col.y);
-            s_c[slot] = make_float2(nxt.col.z, __uint_as_float((uint32_t)(r * kBlendThreads + tid + 1)));
+            s_ent[3 * slot] = make_float4(nxt.xy.x, nxt.xy.y, nxt.co.x, nxt.co.y);
+            s_ent[3 * slot + 1] = make_float4(nxt.co.z, nxt.co.w, nxt.col.x, nxt.col.y);
+            s_ent[3 * slot + 2] = make_float4(nxt.col.z, __uint_as_float((uint32_t)(r * kBlendThreads + tid + 1)), 0.f, 0.f);
         }
         __syncthreads();
         const int count = (int)s_count;
@@ -132,23 +132,25 @@ __global__ void __launch_bounds__(kBlendThreads) blend_fwd_kernel(const FwdParam
         nxt_valid = nprog < todo;
         if (nxt_valid) nxt = gather(p.point_list, p.means2D, p.conic_opacity, p.colors, range.x + nprog);
 
-        if (!__all_sync(0xffffffffu, done)) {
-            for (int j = 0; !done && j < count; ++j) {
-                const float4 A = s_a[j], B = s_b[j];
+        if (!done) {
+            const float4* e = s_ent;
+            int last_j = -1;
+            for (int j = 0; j < count; ++j, e += 3) {
+                const float4 A = e[0], B = e[1];
                 const float dx = __fadd_rn(A.x, -pxf), dy = __fadd_rn(A.y, -pyf);
                 const float power = blend_power(A.z, A.w, B.x, dx, dy);
                 if (power > 0.0f) continue;
                 const float alpha = fminf(0.99f, __fmul_rn(B.y, expf(power)));
                 if (alpha < kAlphaMin) continue;
                 const float test_T = __fmul_rn(T, __fadd_rn(1.f, -alpha));
-                if (test_T < 0.0001f) { done = true; continue; }
-                const float2 Cc = s_c[j];
+                if (test_T < 0.0001f) { done = true; break; }
                 C0 = __fmaf_rn(T, __fmul_rn(alpha, B.z), C0);
                 C1 = __fmaf_rn(T, __fmul_rn(alpha, B.w), C1);
-                C2 = __fmaf_rn(T, __fmul_rn(alpha, Cc.x), C2);
+                C2 = __fmaf_rn(T, __fmul_rn(alpha, e[2].x), C2);
                 T = test_T;
-                last_contributor = __float_as_uint(Cc.y);
+                last_j = j;
             }
+            if (last_j >= 0) last_contributor = __float_as_uint(s_ent[3 * last_j + 2].y);
         }
     }
     if (inside) {

@@ -260,7 +260,7 @@ void launch_scan_u32(const uint32_t* sums, uint32_t* offsets, int n, cudaStream_
 void launch_emit_runs(const GeomPtrs& g, int P, const uint32_t* order, const uint32_t* block_offsets, uint32_t* rkeys, uint32_t* rvals,
                       uint32_t* hist, const SortPlan& plan, cudaStream_t s);
 void launch_expand_runs(const BinPtrs& b, const uint32_t* rkeys_sorted, const uint32_t* rvals_sorted, long long R, int tiles_x, int tiles_y,
-                        uint2* ranges, uint32_t* n_intersections, int prof_ranges, int prof_expand, cudaStream_t s);
+                        const uint32_t* row_offsets /* digit offsets of a one-pass row sort, or nullptr */, uint2* ranges, uint32_t* n_intersections, int prof_ranges, int prof_expand, cudaStream_t s);
 // stable LSD sort of n pairs.  Reads (kin,vin), ends in (kout,vout), uses (ktmp,vtmp) as the ping-pong partner.
 // Pass order is in -> b1 -> b2 -> b1 ... with b1 = out when the pass count is odd, tmp when it is even, so the last
 // pass always writes `out`.  In-place use: kin may alias ktmp when the count is odd and kout when it is even (never

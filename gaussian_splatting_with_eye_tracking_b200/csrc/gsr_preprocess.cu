@@ -331,46 +331,31 @@ __global__ void __launch_bounds__(1024) block_scan_kernel(const uint32_t* __rest
                                                           const uint32_t* __restrict__ sums_r) {
     // offsets = exclusive scan of sums (+ grand total at [n]).  With a header: sums = visible counts, and the plain totals
     // of sums_t (tiles touched -> num_rendered) and sums_r (tile rows -> num_runs) are taken on the way.
-    __shared__ uint32_t s_warp[32];
-    __shared__ uint32_t s_carry, s_total_t, s_total_r;
+    // One pass: every thread owns a contiguous slice of the (small, cache-resident) array.
+    __shared__ uint32_t s_warp[32], s_warp_t[32], s_warp_r[32];
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-    if (tid == 0) { s_carry = 0; s_total_t = 0; s_total_r = 0; }
+    const int per = (n + 1023) / 1024;
+    const int begin = min(n, tid * per), end = min(n, begin + per);
+    uint32_t local = 0, t = 0, r = 0;
+    for (int i = begin; i < end; ++i) local += sums[i];
+    if (header != nullptr) for (int i = begin; i < end; ++i) { t += sums_t[i]; r += sums_r[i]; }
+    uint32_t inc = local;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { uint32_t u = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += u; }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) { t += __shfl_xor_sync(0xffffffffu, t, o); r += __shfl_xor_sync(0xffffffffu, r, o); }
+    if (lane == 31) s_warp[wid] = inc;
+    if (lane == 0) { s_warp_t[wid] = t; s_warp_r[wid] = r; }
     __syncthreads();
-    if (header != nullptr) {
-        uint32_t t = 0, r = 0;
-        for (int i = tid; i < n; i += 1024) { t += sums_t[i]; r += sums_r[i]; }
+    uint32_t wbase = 0, total = 0, tt = 0, tr = 0;
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) { t += __shfl_xor_sync(0xffffffffu, t, o); r += __shfl_xor_sync(0xffffffffu, r, o); }
-        if (lane == 0) { if (t) atomicAdd(&s_total_t, t); if (r) atomicAdd(&s_total_r, r); }
-        __syncthreads();
-    }
-    for (int base = 0; base < n; base += 1024) {
-        const int i = base + tid;
-        const uint32_t v = (i < n) ? sums[i] : 0u;
-        uint32_t inc = v;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) { uint32_t t = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += t; }
-        if (lane == 31) s_warp[wid] = inc;
-        __syncthreads();
-        if (wid == 0) {
-            uint32_t w = s_warp[lane], winc = w;
-#pragma unroll
-            for (int o = 1; o < 32; o <<= 1) { uint32_t t = __shfl_up_sync(0xffffffffu, winc, o); if (lane >= o) winc += t; }
-            s_warp[lane] = winc - w;   // exclusive warp offsets
-        }
-        __syncthreads();
-        const uint32_t carry = s_carry;
-        const uint32_t excl = carry + s_warp[wid] + inc - v;
-        if (i < n) offsets[i] = excl;
-        __syncthreads();
-        if (tid == 1023) s_carry = excl + v;
-        __syncthreads();
-    }
+    for (int k = 0; k < 32; ++k) { const uint32_t v = s_warp[k]; wbase += (k < wid) ? v : 0u; total += v; tt += s_warp_t[k]; tr += s_warp_r[k]; }
+    uint32_t running = wbase + inc - local;
+    for (int i = begin; i < end; ++i) { const uint32_t v = sums[i]; offsets[i] = running; running += v; }
     if (tid == 0) {
-        offsets[n] = s_carry;
+        offsets[n] = total;
         if (header) {   // sort_error: zeroed by the host memset
-            header->magic = kGeomMagic; header->P = P; header->num_rendered = s_total_t; header->num_runs = s_total_r;
-            header->num_visible = s_carry;
+            header->magic = kGeomMagic; header->P = P; header->num_rendered = tt; header->num_runs = tr; header->num_visible = total;
         }
     }
 }
