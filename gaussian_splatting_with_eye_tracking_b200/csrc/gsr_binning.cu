@@ -660,16 +660,18 @@ __global__ void __launch_bounds__(kExpandThreads) expand_runs_kernel(const uint3
                                                                      const uint32_t* __restrict__ row_start, const uint32_t* __restrict__ chunk_counts,
                                                                      const uint32_t* __restrict__ tile_start, uint32_t* __restrict__ point_list) {
     extern __shared__ uint32_t s_mem[];
+    const int stride = tiles_x + 1;
     uint32_t* s_base = s_mem;                      // [tiles_x] next free slot of every column's list
-    uint32_t* s_cur = s_base + tiles_x;            // [tiles_x] slot base of the current batch
-    uint32_t* s_pfx = s_cur + tiles_x;             // [tiles_x][2] per-warp exclusive popcount prefixes, 8 x u8
-    uint32_t* s_bits = s_pfx + 2 * tiles_x;        // [8][tiles_x] coverage bits: warp-major, bit = lane
+    uint32_t* s_wbase = s_base + tiles_x;          // [8][tiles_x] slot base of (warp, column) in the current batch
+    uint32_t* s_bits = s_wbase + 8 * tiles_x;      // [8][tiles_x + 1] coverage bits: warp-major, bit = lane
     ChunkCtx cx;
     if (!chunk_lookup(blockIdx.x, tiles_y, chunk_row_start, row_start, cx)) return;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     for (int x = tid; x < tiles_x; x += kExpandThreads)
         s_base[x] = __ldg(tile_start + (size_t)cx.row * tiles_x + x) + __ldg(chunk_counts + (size_t)blockIdx.x * tiles_x + x);
     const uint32_t lt = (1u << lane) - 1u;
+    uint32_t* mybits = s_bits + wid * stride;
+    uint32_t* mybase = s_wbase + wid * tiles_x;
     for (uint32_t b0 = cx.r0; b0 < cx.r1; b0 += kExpandThreads) {
         const uint32_t r = b0 + tid;
         uint32_t x0 = 0, w = 0, id = 0;
@@ -677,30 +679,36 @@ __global__ void __launch_bounds__(kExpandThreads) expand_runs_kernel(const uint3
             const uint32_t key = __ldg(rkeys + r);
             x0 = (key >> kRunX0Shift) & kRunFieldMask; w = key & kRunFieldMask; id = __ldg(rvals + r);
         }
-        for (int i = tid; i < 8 * tiles_x; i += kExpandThreads) s_bits[i] = 0;
-        __syncthreads();
-        uint32_t* mybits = s_bits + wid * tiles_x;
-        for (uint32_t i = 0; i < w; ++i) atomicOr(&mybits[x0 + i], 1u << lane);
+        // coverage of this warp's 32 runs: toggle the run's bit at its first column and one past its last, then a
+        // prefix-XOR along the columns turns the toggles into "run covers column" bits (2 atomics per run, not w)
+        for (int x = lane; x <= tiles_x; x += 32) mybits[x] = 0;
+        __syncwarp();
+        if (w) { atomicXor(&mybits[x0], 1u << lane); atomicXor(&mybits[x0 + w], 1u << lane); }
+        __syncwarp();
+        uint32_t carry = 0;
+        for (int xb = 0; xb < tiles_x; xb += 32) {
+            const int x = xb + lane;
+            uint32_t v = (x < tiles_x) ? mybits[x] : 0u;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) { const uint32_t t = __shfl_up_sync(0xffffffffu, v, o); if (lane >= o) v ^= t; }
+            v ^= carry;
+            if (x < tiles_x) mybits[x] = v;
+            carry = __shfl_sync(0xffffffffu, v, 31);
+        }
         __syncthreads();
         for (int x = tid; x < tiles_x; x += kExpandThreads) {
-            uint32_t acc = 0, p0 = 0, p1 = 0;
+            uint32_t acc = s_base[x];
 #pragma unroll
-            for (int k = 0; k < 8; ++k) {
-                if (k < 4) p0 |= acc << (8 * k); else p1 |= acc << (8 * (k - 4));
-                acc += __popc(s_bits[k * tiles_x + x]);
-            }
-            // acc <= 256; prefixes of warps 0..7 are <= 224 and fit a byte each
-            s_pfx[2 * x] = p0; s_pfx[2 * x + 1] = p1;
-            const uint32_t cur = s_base[x];
-            s_cur[x] = cur; s_base[x] = cur + acc;
+            for (int k = 0; k < 8; ++k) { s_wbase[k * tiles_x + x] = acc; acc += __popc(s_bits[k * stride + x]); }
+            s_base[x] = acc;
         }
         __syncthreads();
         for (uint32_t i = 0; i < w; ++i) {
             const uint32_t x = x0 + i;
-            const uint32_t pf = (s_pfx[2 * x + (wid >> 2)] >> (8 * (wid & 3))) & 255u;
-            point_list[s_cur[x] + pf + __popc(mybits[x] & lt)] = id;
+            point_list[mybase[x] + __popc(mybits[x] & lt)] = id;
         }
-        __syncthreads();
+        // no barrier here: a warp only rewrites its own plane before the next batch's first barrier, and s_wbase / s_base
+        // are rewritten after it
     }
 }
 
@@ -718,9 +726,9 @@ void launch_expand_runs(const BinPtrs& b, const uint32_t* rkeys_sorted, const ui
     }
     {
         ProfScope ps(prof_expand, s);
-        const size_t smem = sizeof(uint32_t) * (size_t)tiles_x * (1 + 1 + 2 + 8);
+        const size_t smem = sizeof(uint32_t) * ((size_t)tiles_x * (1 + 8) + 8 * (size_t)(tiles_x + 1));
         static bool attr_done = false;
-        if (!attr_done) { cudaFuncSetAttribute(expand_runs_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 12 * 4 * 1024); attr_done = true; }
+        if (!attr_done) { cudaFuncSetAttribute(expand_runs_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 17 * 4 * 1024 + 64); attr_done = true; }
         expand_runs_kernel<<<grid, kExpandThreads, smem, s>>>(rkeys_sorted, rvals_sorted, tiles_x, tiles_y, b.chunk_row_start, b.row_start,
                                                               b.chunk_counts, b.tile_start, b.vals);
         count_launch();

@@ -450,14 +450,16 @@ __global__ void __launch_bounds__(kBlendThreads) blend_bwd_kernel(const BwdParam
             const float power = blend_power(A.z, A.w, B.x, dx, dy);
             const float G = expf(power);
             const float alpha = fminf(0.99f, B.y * G);
-            const bool act = inside && pos <= last_contributor && !(power > 0.0f) && !(alpha < kAlphaMin);
+            // (!inside pixels carry last_contributor = 0 and positions are 1-based, so no separate `inside` test)
+            const bool act = pos <= last_contributor && !(power > 0.0f) && !(alpha < kAlphaMin);
             if (!__any_sync(0xffffffffu, act)) continue;
 
             float v[8], v8 = 0.f;
 #pragma unroll
             for (int i = 0; i < 8; ++i) v[i] = 0.f;
             if (act) {
-                T = T / (1.f - alpha);
+                const float inv_1ma = __frcp_rn(1.f - alpha);      // one correctly rounded reciprocal serves both divisions
+                T = T * inv_1ma;
                 const float dchannel_dcolor = alpha * T;
                 acc0 = last_alpha * lc0 + (1.f - last_alpha) * acc0;
                 acc1 = last_alpha * lc1 + (1.f - last_alpha) * acc1;
@@ -466,7 +468,7 @@ __global__ void __launch_bounds__(kBlendThreads) blend_bwd_kernel(const BwdParam
                 float dL_dalpha = (lc0 - acc0) * g0 + (lc1 - acc1) * g1 + (lc2 - acc2) * g2;
                 dL_dalpha *= T;
                 last_alpha = alpha;
-                dL_dalpha += (-T_final / (1.f - alpha)) * bg_dot;
+                dL_dalpha += (-T_final * inv_1ma) * bg_dot;
                 const float dL_dG = B.y * dL_dalpha;
                 const float gdx = G * dx, gdy = G * dy;
                 const float dG_ddelx = -gdx * A.z - gdy * A.w;
