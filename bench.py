@@ -109,7 +109,7 @@ def dist_env():
 class Timer:
     """barrier + synchronize on both sides, CUDA events on the launching stream, max over ranks."""
 
-    def __init__(self, world, windows, prime=8):
+    def __init__(self, world, windows, prime=16):
         self.world, self.windows, self.prime = world, windows, prime
 
     def run(self, fn, steps, warmup):

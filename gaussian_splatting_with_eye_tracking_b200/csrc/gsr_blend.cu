@@ -189,9 +189,7 @@ struct AmrParams {
 
 __global__ void __launch_bounds__(kBlendThreads) blend_amr_kernel(const AmrParams q) {
     const FwdParams& p = q.f;
-    __shared__ float4 s_a[kBlendThreads];
-    __shared__ float4 s_b[kBlendThreads];
-    __shared__ float2 s_c[kBlendThreads];
+    __shared__ float4 s_ent[3 * kBlendThreads];     // same staged-entry layout as blend_fwd_kernel
     __shared__ uint32_t s_wcnt[kBlendThreads / 32];
     __shared__ uint32_t s_count;
 
@@ -240,9 +238,9 @@ __global__ void __launch_bounds__(kBlendThreads) blend_amr_kernel(const AmrParam
         const bool keep = nxt_valid && !cannot_touch(nxt.xy, nxt.co, rx0, ry0, rx1, ry1);
         const int slot = compact_slot(keep, s_wcnt, &s_count);
         if (slot >= 0) {
-            s_a[slot] = make_float4(nxt.xy.x, nxt.xy.y, nxt.co.x, nxt.co.y);
-            s_b[slot] = make_float4(nxt.co.z, nxt.co.w, nxt.col.x, nxt.col.y);
-            s_c[slot] = make_float2(nxt.col.z, __uint_as_float((uint32_t)(r * kBlendThreads + tid + 1)));
+            s_ent[3 * slot] = make_float4(nxt.xy.x, nxt.xy.y, nxt.co.x, nxt.co.y);
+            s_ent[3 * slot + 1] = make_float4(nxt.co.z, nxt.co.w, nxt.col.x, nxt.col.y);
+            s_ent[3 * slot + 2] = make_float4(nxt.col.z, __uint_as_float((uint32_t)(r * kBlendThreads + tid + 1)), 0.f, 0.f);
         }
         __syncthreads();
         const int count = (int)s_count;
@@ -250,10 +248,11 @@ __global__ void __launch_bounds__(kBlendThreads) blend_amr_kernel(const AmrParam
         nxt_valid = nprog < todo;
         if (nxt_valid) nxt = gather(p.point_list, p.means2D, p.conic_opacity, p.colors, range.x + nprog);
 
-        if (!__all_sync(0xffffffffu, all_done)) {
-            for (int j = 0; !all_done && j < count; ++j) {
-                const float4 A = s_a[j], B = s_b[j];
-                const float2 Cc = s_c[j];
+        if (!all_done) {
+            const float4* e = s_ent;
+            for (int j = 0; !all_done && j < count; ++j, e += 3) {
+                const float4 A = e[0], B = e[1];
+                const float4 Cc = e[2];
 #pragma unroll
                 for (int k = 0; k < 4; ++k) {
                     if (done[k]) continue;
