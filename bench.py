@@ -377,16 +377,38 @@ def measure(impl, args, d, cams, rank, world, timer, full):
         prof = impl.capi.profile_read()
         out["bwd_stages_ms"] = {k: round(v[0] / max(1, v[1]), 5) for k, v in prof.items() if k.startswith("bwd")}
 
-    # ---- data-parallel training step: every rank one view fwd+bwd, then all-reduce of the 59 floats/Gaussian
+    # ---- data-parallel training step (config C4 shape): every rank one view fwd+bwd, then the bucketed NCCL all-reduce of
+    # the 59 floats/Gaussian of parameter gradients on a side stream (dist.GradientAllReduce)
+    from gaussian_splatting_with_eye_tracking_b200 import dist as gdist
+    reducer = gdist.GradientAllReduce()
+
     def dp_step(i):
         _, grads = impl.fwd_bwd(cam_of(i), w)
-        if world > 1:
-            hs = [dist.all_reduce(t, async_op=True) for t in grads]
-            for h in hs:
-                h.wait()
+        reducer.start(grads)
+        reducer.wait()
     ms = timer.run(dp_step, Kb, 2)
     out["dp_train"] = {"ms_per_step": ms / Kb, "views_per_s": world * Kb / (ms / 1e3),
-                       "allreduce_bytes_per_step": 59 * 4 * d["means3D"].shape[0] if world > 1 else 0}
+                       "allreduce_bytes_per_step": 59 * 4 * d["means3D"].shape[0] if world > 1 else 0,
+                       "bucket_bytes": reducer.bucket_bytes}
+
+    # ---- screen-tile bands (config C5 shape): ONE foveated frame split over the ranks by rows of 32-px tiles, balanced by the
+    # previous frame's per-row pair counts; per-tile counts all-reduced so the AMR levels equal the single-GPU ones
+    if is_ours:
+        tiles_x32, tiles_y32 = (args.width + 31) // 32, (args.height + 31) // 32
+        state = {"bands": gdist.balanced_bands([1.0] * tiles_y32, world)}
+
+        def band_step(i):
+            cam = cams[i % ncam]                      # every rank renders the SAME view
+            frame, counts, levels, _ = gdist.render_amr_frame_bands(impl._args(cam), args.height, args.width, state["bands"], rank,
+                                                                    interpolate_image=True, gather=True)
+            state["bands"] = gdist.balanced_bands(gdist.row_costs_from_counts(counts, tiles_x32, tiles_y32, levels), world)
+            return frame
+        try:
+            ms = timer.run(band_step, Kb, 2)
+            out["tile_bands"] = {"frames_per_s": Kb / (ms / 1e3), "ms_per_frame": ms / Kb, "bands": [list(b) for b in state["bands"]],
+                                 "what": "one AMR-foveated frame per step, all ranks on the same view (strong scaling)"}
+        except RuntimeError as ex:
+            out["tile_bands"] = {"error": str(ex)[:200]}
 
     # ---- AMR / foveated forward
     Ka = max(3, K // 2)
@@ -449,6 +471,7 @@ def main():
         return                                            # reference arm: rank 0 alone runs and prints
     if world > 1 and args.impl == "ours":
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ["NCCL_DEBUG"] = os.environ.get("GSR_NCCL_DEBUG", "WARN")     # keep stdout to the one JSON line (NCCL prints its version there)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     eff_world = world if args.impl == "ours" else 1
 
@@ -495,7 +518,7 @@ def main():
                                 "traffic": NCU_TRAFFIC_BYTES.get(args.gaussians), "peak_source": peak_src, "launch_ms": st["preprocess"],
                                 "alg_bytes_per_launch": alg, "visible_per_launch": vis, "culled_per_launch": args.gaussians - vis,
                                 "alg_bytes_per_visible": ALG_BYTES_VISIBLE, "alg_bytes_per_culled": ALG_BYTES_CULLED}
-        extra = {k: m[k] for k in ("num_rendered", "stages_ms", "fwd_bwd_ms_per_view", "bwd_stages_ms", "dp_train", "amr") if k in m}
+        extra = {k: m[k] for k in ("num_rendered", "stages_ms", "fwd_bwd_ms_per_view", "bwd_stages_ms", "dp_train", "tile_bands", "amr") if k in m}
         extra["pairs_per_gaussian_mean"] = N / args.gaussians
         extra["visible_mean"] = m.get("mean_visible")
         if full and rank == 0 and eff_world == 1:
