@@ -60,9 +60,16 @@ void prof_end(int slot, cudaStream_t s) {
     g_prof_recs.push_back({slot, g_prof_open[slot], e}); g_prof_open[slot] = nullptr;
 }
 
-static uint32_t* pinned_mailbox() {
+static uint32_t* pinned_mailbox(uint32_t** dev_alias = nullptr) {
+    // 64 B of mapped pinned host memory per host thread: target of the small D2H header copies, and -- through its
+    // device alias -- written directly by block_scan_kernel (no DMA; see build_lists)
     static thread_local uint32_t* box = nullptr;
-    if (!box) { if (cudaHostAlloc((void**)&box, 64, cudaHostAllocDefault) != cudaSuccess) { box = nullptr; cudaGetLastError(); } }
+    static thread_local uint32_t* box_dev = nullptr;
+    if (!box) {
+        if (cudaHostAlloc((void**)&box, 64, cudaHostAllocMapped) != cudaSuccess) { box = nullptr; cudaGetLastError(); }
+        else if (cudaHostGetDevicePointer((void**)&box_dev, box, 0) != cudaSuccess) { box_dev = nullptr; cudaGetLastError(); }
+    }
+    if (dev_alias) *dev_alias = box_dev;
     return box;
 }
 
@@ -79,6 +86,22 @@ static int read_u32(const uint32_t* dev, uint32_t* host, int count, cudaStream_t
     int rc = check_cuda(cudaMemcpyAsync(host, dev, sizeof(uint32_t) * count, cudaMemcpyDeviceToHost, s), "D2H header");
     if (rc) return rc;
     return check_cuda(cudaStreamSynchronize(s), "stream sync (header)");
+}
+
+// Header of the geometry buffer this host thread built last: lets the follow-up calls of the 5-step fovea protocol and
+// gsr_amr_render_prebuilt skip the blocking header read-back (and the pipeline bubble behind it) when they are handed
+// that same buffer, which is the only way the reference's Python ever calls them (gaussian_renderer_amr/__init__.py).
+struct LastBuild { const void* geom; int P; int N; };
+static thread_local LastBuild g_last_build = {nullptr, 0, 0};
+
+static int geom_header(const void* geom, const GeomHeader* header, int P, int* N, cudaStream_t s) {
+    if (geom == g_last_build.geom && P == g_last_build.P) { *N = g_last_build.N; return GSR_OK; }
+    uint32_t hdr[4];
+    int rc = read_u32(&header->magic, hdr, 4, s);
+    if (rc) return rc;
+    if (hdr[0] != kGeomMagic || hdr[1] != (uint32_t)P) { set_error("geometry buffer does not belong to this scene (magic %08x, P %u)", hdr[0], hdr[1]); return GSR_ERR_WORKSPACE; }
+    *N = (int)hdr[2];
+    return GSR_OK;
 }
 
 static unsigned higher_msb(unsigned n) {   // reference getHigherMsb (rasterizer_impl.cu:35-50)
@@ -112,6 +135,7 @@ static int build_lists(const gsr_scene* sc, const gsr_camera* cam, int mode, gsr
                        int* radii_user, void** geom_out, void** bin_out, void** img_out, int* N_out, bool debug, cudaStream_t s) {
     const int P = sc->P, W = cam->width, H = cam->height;
     const size_t gbytes = gsr_geom_bytes(P), ibytes = gsr_image_bytes(W, H, mode);
+    g_last_build = {nullptr, 0, 0};
     void* geom = alloc(user, GSR_BUF_GEOM, gbytes);
     void* img = alloc(user, GSR_BUF_IMAGE, ibytes);
     if (!geom || !img) { set_error("allocation callback returned NULL"); return GSR_ERR_ALLOC; }
@@ -120,8 +144,12 @@ static int build_lists(const gsr_scene* sc, const gsr_camera* cam, int mode, gsr
     const int num_tiles = im.tiles_x * im.tiles_y;
     if (cam->band_row1 > im.tiles_y) { set_error("tile band [%d,%d) exceeds the %d tile rows", cam->band_row0, cam->band_row1, im.tiles_y); return GSR_ERR_INVALID; }
     if (im.tiles_x > kRunFieldMask || im.tiles_y > kRunMaxRows) { set_error("image of %dx%d tiles exceeds the %dx%d tile grid limit", im.tiles_x, im.tiles_y, kRunFieldMask, kRunMaxRows); return GSR_ERR_INVALID; }
-    int rc = check_cuda(cudaMemsetAsync(g.header, 0, sizeof(GeomHeader), s), "memset header");
-    if (rc) return rc;
+    int rc = GSR_OK;
+    // No memset operation in the frame: block_scan_kernel rewrites the whole header, and the preprocess kernel clears
+    // the depth sort's histograms / tile counters / look-back words (one region per pass) on the side.
+    const SortPlan dplan = make_sort_plan(32);
+    if (dplan.passes & 1) { set_error("depth sort plan must have an even pass count"); return GSR_ERR_INVALID; }
+    const size_t dzero = sort_prezero_bytes(P, dplan, g.sort_temp_bytes, false);
 
     PreprocessArgs a;
     a.P = P; a.D = sc->sh_degree; a.M = sc->sh_coeffs;
@@ -136,32 +164,32 @@ static int build_lists(const gsr_scene* sc, const gsr_camera* cam, int mode, gsr
     a.radii = radii_user ? radii_user : g.radii;
     a.prefiltered = cam->prefiltered != 0;
     a.band_row0 = cam->band_row0; a.band_row1 = cam->band_row1;
+    a.zero_ptr = dzero ? (void*)sort_hist_ptr(g.sort_temp) : nullptr; a.zero_bytes = dzero;
     { ProfScope ps(GSR_PROF_PREPROCESS, s); launch_preprocess(a, g, s); }
     if ((rc = check_last("preprocess", debug, s))) return rc;
-    { ProfScope ps(GSR_PROF_SCAN, s); launch_block_scan(g, P, s); }
+    uint32_t* box_dev = nullptr;
+    uint32_t* box = pinned_mailbox(&box_dev);
+    { ProfScope ps(GSR_PROF_SCAN, s); launch_block_scan(g, P, box_dev, s); }
     if ((rc = check_last("block scan", debug, s))) return rc;
 
     // The one host round-trip of the forward (reference: rasterizer_impl.cu:281): the binning buffer is sized by N.
-    // The copy is queued BEFORE the depth sort and waited on through an event, so the host allocates the binning
-    // buffer while the GPU is already sorting the Gaussians by depth.
-    uint32_t* box = pinned_mailbox();
+    // The scan kernel stores the totals straight into mapped host memory and the host waits on an event recorded
+    // BEFORE the depth sort, so the host allocates the binning buffer while the GPU is already sorting by depth.
+    // No cudaMemcpy: a D2H copy, however small, queues behind whatever the application has in flight on the copy
+    // engine (a 25 MB frame read-back delayed this read by up to 0.45 ms).
     static thread_local cudaEvent_t ev_hdr = nullptr;
-    if (box && !ev_hdr) cudaEventCreateWithFlags(&ev_hdr, cudaEventDisableTiming);
-    if (box && ev_hdr) {
-        if ((rc = check_cuda(cudaMemcpyAsync(box, &g.header->magic, 32, cudaMemcpyDeviceToHost, s), "D2H header"))) return rc;
-        if ((rc = check_cuda(cudaEventRecord(ev_hdr, s), "event record"))) return rc;
-    }
+    if (box && box_dev && !ev_hdr) cudaEventCreateWithFlags(&ev_hdr, cudaEventDisableTiming);
+    const bool mailed = box && box_dev && ev_hdr;
+    if (mailed && (rc = check_cuda(cudaEventRecord(ev_hdr, s), "event record"))) return rc;
 
     // (1) stable sort of the Gaussians by depth bits (invisible ones keyed 0xffffffff go last and emit nothing)
     {
         ProfScope ps(GSR_PROF_DEPTH_SORT, s);
         // compact the visible Gaussians (ascending index) into (dkeys_a, order), then 4 radix passes over those only
         launch_compact_keys(g, P, g.dkeys_a, g.order, s);
-        const SortPlan dplan = make_sort_plan(32);
-        if (dplan.passes & 1) { set_error("depth sort plan must have an even pass count"); return GSR_ERR_INVALID; }
         // even pass count: keys a -> b -> a ..., values order -> order_tmp -> order ...; the result ends in (dkeys_a, order)
         rc = launch_onesweep32(g.dkeys_a, g.order, g.dkeys_a, g.order, g.dkeys_b, g.order_tmp, P, dplan, g.sort_temp, g.sort_temp_bytes,
-                               /*hist_ready=*/false, &g.header->sort_error, -1, s, &g.header->num_visible);
+                               /*hist_ready=*/false, &g.header->sort_error, -1, s, &g.header->num_visible, /*prezeroed=*/dzero != 0);
         if (rc) return rc;
         launch_order_block_sums(P, &g.header->num_visible, g.order, g.rects, g.oblock_sums, s);
         launch_scan_u32(g.oblock_sums, g.oblock_offsets, g.nblocks, s);
@@ -169,7 +197,7 @@ static int build_lists(const gsr_scene* sc, const gsr_camera* cam, int mode, gsr
     if ((rc = check_last("depth sort", debug, s))) return rc;
 
     uint32_t hdr[8];
-    if (box && ev_hdr) {
+    if (mailed) {
         if ((rc = check_cuda(cudaEventSynchronize(ev_hdr), "event sync (header)"))) return rc;
         memcpy(hdr, box, 32);
     } else if ((rc = read_u32(&g.header->magic, hdr, 8, s))) return rc;
@@ -185,7 +213,9 @@ static int build_lists(const gsr_scene* sc, const gsr_camera* cam, int mode, gsr
         // (2) emit one run per (Gaussian, tile row) in depth order, (3) stable partition of the runs by row
         const SortPlan plan = make_sort_plan_range(kRunRowShift, (int)higher_msb((unsigned)im.tiles_y));
         uint32_t* hist = sort_hist_ptr(b.sort_temp);
-        if ((rc = check_cuda(cudaMemsetAsync(hist, 0, sizeof(uint32_t) * kSortMaxPasses * kSortMaxRadix, s), "memset hist"))) return rc;
+        const size_t rzero = sort_prezero_bytes(R, plan, b.sort_temp_bytes, false);
+        if (rzero) launch_zero(hist, rzero, s);       // one clearing kernel for histogram + counters + look-back words
+        else if ((rc = check_cuda(cudaMemsetAsync(hist, 0, sizeof(uint32_t) * kSortMaxPasses * kSortMaxRadix, s), "memset hist"))) return rc;
         { ProfScope ps(GSR_PROF_DUPLICATE, s);
           launch_emit_runs(g, P, g.order, g.oblock_offsets, b.rkeyA, b.rvalA, hist, plan, s); }
         if ((rc = check_last("emit runs", debug, s))) return rc;
@@ -196,7 +226,7 @@ static int build_lists(const gsr_scene* sc, const gsr_camera* cam, int mode, gsr
             if (plan.passes > 2 || (plan.passes == 2 && im.tiles_y <= kSortMaxRadix)) { set_error("unexpected row-sort plan"); return GSR_ERR_INVALID; }
             rc = launch_onesweep32(b.rkeyA, b.rvalA, b.rkeyB, b.rvalB, (plan.passes & 1) ? b.rkeyA : b.rkeyC,
                                    (plan.passes & 1) ? b.rvalA : b.vals, R, plan, b.sort_temp, b.sort_temp_bytes,
-                                   /*hist_ready=*/true, &g.header->sort_error, GSR_PROF_SORT_PASS0, s);
+                                   /*hist_ready=*/true, &g.header->sort_error, GSR_PROF_SORT_PASS0, s, nullptr, /*prezeroed=*/rzero != 0);
         }
         if (rc) return rc;
         if ((rc = check_last("radix sort", debug, s))) return rc;
@@ -206,6 +236,7 @@ static int build_lists(const gsr_scene* sc, const gsr_camera* cam, int mode, gsr
     launch_expand_runs(b, rk_sorted, rv_sorted, R, im.tiles_x, im.tiles_y, row_offsets, im.ranges, im.n_intersections, GSR_PROF_RANGES, GSR_PROF_EXPAND, s);
     if ((rc = check_last("expand runs", debug, s))) return rc;
     *geom_out = geom; *bin_out = bin; *img_out = img; *N_out = (int)N;
+    g_last_build = {geom, P, (int)N};
     return GSR_OK;
 }
 
@@ -351,10 +382,7 @@ int gsr_amr_forward(const gsr_scene* sc, const gsr_camera* cam, int fovea_step, 
         // progressive round k: everything was built by step 0 (A/rasterizer_impl.cu:334-462)
         if (!geom || !bin || !img) { set_error("fovea_step >= 1 needs the buffers built by step 0"); return GSR_ERR_WORKSPACE; }
         GeomPtrs g0 = geom_ptrs(geom, P);
-        uint32_t hdr[4];
-        if ((rc = read_u32(&g0.header->magic, hdr, 4, s))) return rc;
-        if (hdr[0] != kGeomMagic || hdr[1] != (uint32_t)P) { set_error("geometry buffer does not belong to this scene (magic %08x, P %u)", hdr[0], hdr[1]); return GSR_ERR_WORKSPACE; }
-        N = (int)hdr[2];
+        if ((rc = geom_header(geom, g0.header, P, &N, s))) return rc;
     } else {
         if (!alloc) { set_error("alloc callback is required"); return GSR_ERR_INVALID; }
         rc = build_lists(sc, cam, GSR_MODE_AMR, alloc, user, radii, &geom, &bin, &img, &N, debug != 0, s);
@@ -403,9 +431,8 @@ int gsr_amr_render_prebuilt(const gsr_scene* sc, const gsr_camera* cam, const vo
     if (P == 0) return GSR_OK;
     if (!geom_buffer || !binning_buffer || !image_buffer) { set_error("prebuilt work buffers are required"); return GSR_ERR_WORKSPACE; }
     GeomPtrs g = geom_ptrs(geom_buffer, P);
-    uint32_t hdr[4];
-    if ((rc = read_u32(&g.header->magic, hdr, 4, s))) return rc;
-    if (hdr[0] != kGeomMagic || hdr[1] != (uint32_t)P) { set_error("geometry buffer does not belong to this scene (magic %08x, P %u)", hdr[0], hdr[1]); return GSR_ERR_WORKSPACE; }
+    int N_unused = 0;
+    if ((rc = geom_header(geom_buffer, g.header, P, &N_unused, s))) return rc;
     ImgPtrs im = img_ptrs(image_buffer, W, H, GSR_MODE_AMR);
     if (cam->band_row1 > im.tiles_y) { set_error("tile band exceeds the tile rows"); return GSR_ERR_INVALID; }
     launch_fovea_levels(im, im.tiles_x * im.tiles_y, -1, gaze, s);

@@ -273,14 +273,15 @@ __global__ void __launch_bounds__(THREADS, MINB) onesweep_kernel(const SweepPara
     uint32_t* s_whist = s_vals + TILE;                                                        // [WARPS][RADIX]
     uint32_t* s_bin_start = s_whist + WARPS * RADIX;                                          // [RADIX]
     uint32_t* s_gofs = s_bin_start + RADIX;                                                   // [RADIX]
-    __shared__ uint32_t s_tile;
     __shared__ uint32_t s_wtot[RADIX / 32];
 
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-    if (tid == 0) s_tile = atomicAdd(p.tile_counter, 1u);
     for (int i = tid; i < WARPS * RADIX; i += THREADS) s_whist[i] = 0;
     __syncthreads();
-    const uint32_t tile = s_tile;
+    // The tile's place in the chained scan is its block index: blocks are dispatched in increasing linear index (the
+    // assumption cub::DeviceScan makes too), so every predecessor is resident or done.  A global ticket counter costs a
+    // serialised same-address atomic round trip per CTA; the watchdog below still bounds any wait.
+    const uint32_t tile = blockIdx.x;
     const long long tile_base = (long long)tile * TILE;
     const long long n_items = p.n_dev ? (long long)__ldg(p.n_dev) : p.n;
     if (tile_base >= n_items) return;          // grid was sized for the upper bound (CTA-uniform exit; nobody waits on this tile)
@@ -451,16 +452,51 @@ template <int RADIX> struct SweepDispatch<uint32_t, RADIX> {
     }
 };
 
+// look-back words one pass needs: tiles x radix of the widest pass of the plan, for the active tile shape
+template <typename KeyT>
+static size_t pass_status_words(long long n, const SortPlan& plan) {
+    size_t words = 0;
+    for (int ps = 0; ps < plan.passes; ++ps) {
+        const int radix = plan.bits[ps] <= 7 ? 128 : (plan.bits[ps] <= 8 ? 256 : 512);
+        const int tile_items = radix == 128 ? SweepDispatch<KeyT, 128>::tile_items()
+                             : radix == 256 ? SweepDispatch<KeyT, 256>::tile_items() : 512 * 9;
+        const size_t w = (size_t)((n + tile_items - 1) / tile_items) * radix;
+        if (w > words) words = w;
+    }
+    return (words + 3) / 4 * 4;
+}
+
+size_t sort_prezero_bytes(long long n, const SortPlan& plan, size_t temp_bytes, bool keys64) {
+    if (n <= 0) return 0;
+    const size_t head = align_up(sizeof(uint32_t) * kSortMaxPasses * kSortMaxRadix) + align_up(256);
+    const size_t words = keys64 ? pass_status_words<uint64_t>(n, plan) : pass_status_words<uint32_t>(n, plan);
+    const size_t need = head + sizeof(uint32_t) * words * plan.passes;
+    return need + kAlign <= temp_bytes ? need : 0;      // kAlign: slack of aligned_base()
+}
+
+__global__ void __launch_bounds__(256) zero_kernel(uint4* __restrict__ p, size_t n16) {
+    for (size_t i = (size_t)blockIdx.x * 256 + threadIdx.x; i < n16; i += (size_t)gridDim.x * 256) p[i] = make_uint4(0u, 0u, 0u, 0u);
+}
+void launch_zero(void* ptr, size_t bytes, cudaStream_t s) {
+    if (bytes == 0) return;
+    const size_t n16 = bytes / 16;
+    const int grid = (int)min((size_t)num_sms() * 8, (n16 + 255) / 256);
+    zero_kernel<<<grid, 256, 0, s>>>(reinterpret_cast<uint4*>(aligned_base(ptr)), n16);
+    count_launch();
+}
+
 template <typename KeyT>
 int launch_onesweep_t(const KeyT* kin0, const uint32_t* vin0, KeyT* kout, uint32_t* vout, KeyT* ktmp, uint32_t* vtmp,
                       long long n, const SortPlan& plan, void* temp, size_t temp_bytes, bool hist_ready, uint32_t* err_flag,
-                      int prof_slot0, cudaStream_t s, const uint32_t* n_dev = nullptr) {
+                      int prof_slot0, cudaStream_t s, const uint32_t* n_dev = nullptr, bool prezeroed = false) {
     if (n <= 0) return GSR_OK;
     if (n >= (1ll << 30)) { set_error("radix sort: n=%lld exceeds 2^30 pairs", n); return GSR_ERR_INVALID; }
     if (temp_bytes < sort_temp_bytes(n)) { set_error("radix sort: temp too small"); return GSR_ERR_ALLOC; }
     SortTemp t = carve_sort_temp(temp);
+    const size_t pass_words = pass_status_words<KeyT>(n, plan);
+    if (prezeroed && sort_prezero_bytes(n, plan, temp_bytes, sizeof(KeyT) == 8) == 0) { set_error("radix sort: prezeroed temp does not fit"); return GSR_ERR_ALLOC; }
     if (!hist_ready) {
-        cudaMemsetAsync(t.hist, 0, sizeof(uint32_t) * kSortMaxPasses * kSortMaxRadix, s);
+        if (!prezeroed) cudaMemsetAsync(t.hist, 0, sizeof(uint32_t) * kSortMaxPasses * kSortMaxRadix, s);
         HistParams<KeyT> hp; hp.keys = kin0; hp.n = n; hp.n_dev = n_dev; hp.hist = t.hist; hp.passes = plan.passes;
         for (int i = 0; i < kSortMaxPasses; ++i) { hp.shift[i] = i < plan.passes ? plan.shift[i] : 0; hp.bits[i] = i < plan.passes ? plan.bits[i] : 1; }
         long long want = (n + 256 * 16 - 1) / (256 * 16);
@@ -470,7 +506,7 @@ int launch_onesweep_t(const KeyT* kin0, const uint32_t* vin0, KeyT* kout, uint32
     }
     hist_scan_kernel<<<plan.passes, kSortMaxRadix, 0, s>>>(t.hist);
     count_launch();
-    cudaMemsetAsync(t.counters, 0, 256, s);
+    if (!prezeroed) cudaMemsetAsync(t.counters, 0, 256, s);
     const KeyT* kin = kin0; const uint32_t* vin = vin0;
     KeyT* kb[2]; uint32_t* vb[2];
     if (plan.passes & 1) { kb[0] = kout; vb[0] = vout; kb[1] = ktmp; vb[1] = vtmp; }
@@ -479,12 +515,12 @@ int launch_onesweep_t(const KeyT* kin0, const uint32_t* vin0, KeyT* kout, uint32
         SweepParams<KeyT> sp;
         sp.keys_in = kin; sp.keys_out = kb[ps & 1]; sp.vals_in = vin; sp.vals_out = vb[ps & 1];
         sp.n = n; sp.n_dev = n_dev; sp.shift = plan.shift[ps]; sp.bits = plan.bits[ps];
-        sp.bin_base = t.hist + ps * kSortMaxRadix; sp.status = t.status; sp.tile_counter = t.counters + ps; sp.err_flag = err_flag;
+        sp.bin_base = t.hist + ps * kSortMaxRadix; sp.tile_counter = t.counters + ps; sp.err_flag = err_flag;
         const int radix = plan.bits[ps] <= 7 ? 128 : (plan.bits[ps] <= 8 ? 256 : 512);
-        const int tile_items = radix == 128 ? SweepDispatch<KeyT, 128>::tile_items()
-                             : radix == 256 ? SweepDispatch<KeyT, 256>::tile_items() : 512 * 9;
-        const long long tiles = (n + tile_items - 1) / tile_items;
-        cudaMemsetAsync(t.status, 0, sizeof(uint32_t) * (size_t)tiles * radix, s);
+        // prezeroed: every pass has its own look-back region, cleared by the caller in one go; otherwise one region,
+        // re-zeroed before each pass
+        sp.status = prezeroed ? t.status + (size_t)ps * pass_words : t.status;
+        if (!prezeroed) cudaMemsetAsync(t.status, 0, sizeof(uint32_t) * pass_words, s);
         {
             ProfScope pr(prof_slot0 >= 0 ? prof_slot0 + ps : -1, s);
             if (radix == 128) SweepDispatch<KeyT, 128>::launch(sp, n, s);
@@ -503,8 +539,8 @@ int launch_onesweep(const uint64_t* kin, const uint32_t* vin, uint64_t* kout, ui
 }
 int launch_onesweep32(const uint32_t* kin, const uint32_t* vin, uint32_t* kout, uint32_t* vout, uint32_t* ktmp, uint32_t* vtmp,
                       long long n, const SortPlan& plan, void* temp, size_t temp_bytes, bool hist_ready, uint32_t* err_flag,
-                      int prof_slot0, cudaStream_t s, const uint32_t* n_dev) {
-    return launch_onesweep_t<uint32_t>(kin, vin, kout, vout, ktmp, vtmp, n, plan, temp, temp_bytes, hist_ready, err_flag, prof_slot0, s, n_dev);
+                      int prof_slot0, cudaStream_t s, const uint32_t* n_dev, bool prezeroed) {
+    return launch_onesweep_t<uint32_t>(kin, vin, kout, vout, ktmp, vtmp, n, plan, temp, temp_bytes, hist_ready, err_flag, prof_slot0, s, n_dev, prezeroed);
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -241,9 +241,11 @@ struct PreprocessArgs {
     int* radii;            // output (caller's or internal)
     bool prefiltered;
     int band_row0, band_row1;   // tile-row band [row0,row1); 0,0 = whole frame
+    void* zero_ptr; size_t zero_bytes;   // 16 B aligned scratch the kernel clears on the side (the depth sort's histograms and
+                                         // look-back words), so that the frame needs no memset operation; may be null / 0
 };
 void launch_preprocess(const PreprocessArgs& a, const GeomPtrs& g, cudaStream_t s);
-void launch_block_scan(const GeomPtrs& g, int P, cudaStream_t s);
+void launch_block_scan(const GeomPtrs& g, int P, uint32_t* mailbox_dev, cudaStream_t s);
 void launch_mark_visible(int P, const float* means3D, const float* view, const float* proj, unsigned char* present, cudaStream_t s);
 
 struct SortPlan {
@@ -267,10 +269,16 @@ void launch_expand_runs(const BinPtrs& b, const uint32_t* rkeys_sorted, const ui
 // b1).  vin == nullptr: values = 0..n-1.
 int launch_onesweep(const uint64_t* kin, const uint32_t* vin, uint64_t* kout, uint32_t* vout, uint64_t* ktmp, uint32_t* vtmp,
                     long long n, const SortPlan& plan, void* temp, size_t temp_bytes, bool hist_ready, uint32_t* err_flag, cudaStream_t s);
+// prezeroed: the caller cleared sort_prezero_bytes() of `temp` (no memset is issued here)
 int launch_onesweep32(const uint32_t* kin, const uint32_t* vin, uint32_t* kout, uint32_t* vout, uint32_t* ktmp, uint32_t* vtmp,
                       long long n, const SortPlan& plan, void* temp, size_t temp_bytes, bool hist_ready, uint32_t* err_flag,
-                      int prof_slot0, cudaStream_t s, const uint32_t* n_dev = nullptr);   // n_dev: actual count on the device (<= n)
+                      int prof_slot0, cudaStream_t s, const uint32_t* n_dev = nullptr,   // n_dev: actual count on the device (<= n)
+                      bool prezeroed = false);
 uint32_t* sort_hist_ptr(void* temp);
+// Bytes at the start of `temp` that launch_onesweep* expects to be zero when called with prezeroed = true (histograms,
+// tile counters and one look-back region PER PASS); 0 if the per-pass regions do not fit the temp area.
+size_t sort_prezero_bytes(long long n, const SortPlan& plan, size_t temp_bytes, bool keys64);
+void launch_zero(void* ptr, size_t bytes, cudaStream_t s);   // bytes % 16 == 0, ptr 16 B aligned
 void set_sort_variant(int v);
 
 void launch_amr_levels(const ImgPtrs& im, int num_tiles, cudaStream_t s);

@@ -47,7 +47,9 @@ struct PreFwdParams {
     uint2* __restrict__ rects;              // (x0 | x1 << 16, y0 | y1 << 16) tile rect, (0,0) when nothing is touched
     uint32_t* __restrict__ block_sums;
     uint32_t* __restrict__ block_sums_r;    // per-CTA sum of tile rows spanned (runs)
-    uint32_t* __restrict__ block_sums_v;    // per-CTA number of visible Gaussians
+    uint32_t* __restrict__ block_sums_v;    // per-CTA number of visible Gaussians; bit 31 = "a Gaussian was culled although
+                                            // prefiltered" (the reference would __trap)
+    uint4* zero_ptr; size_t zero_n16;       // scratch cleared on the side (grid-stride), see PreprocessArgs
     GeomHeader* header;
     int prefiltered;
     int band_row0, band_row1;
@@ -213,7 +215,8 @@ __global__ void __launch_bounds__(kPreBlock, 4) preprocess_fwd_kernel(const PreF
 
     const int idx = blockIdx.x * kPreBlock + tid;
     uint32_t touched = 0, rows = 0;
-    int radius = 0;
+    int radius = 0, trapped = 0;
+    for (size_t i = (size_t)idx; i < p.zero_n16; i += (size_t)gridDim.x * kPreBlock) p.zero_ptr[i] = make_uint4(0u, 0u, 0u, 0u);
 
     if (idx < p.P) {
         const float px = __ldg(p.means3D + 3 * (size_t)idx);
@@ -222,7 +225,7 @@ __global__ void __launch_bounds__(kPreBlock, 4) preprocess_fwd_kernel(const PreF
         // near-plane cull (auxiliary.h:139-164): p_view.z <= 0.2 -> invisible
         const float depth = xform_row(sV[2], sV[6], sV[10], sV[14], px, py, pz);
         bool alive = depth > 0.2f;
-        if (!alive && p.prefiltered) atomicOr(&p.header->sort_error, 0x100u);   // reference: printf + __trap()
+        if (!alive && p.prefiltered) trapped = 1;   // reference: printf + __trap(); here: an error status from the call
 
         float2 pix = make_float2(0.f, 0.f);
         float3 conic = make_float3(0.f, 0.f, 0.f);
@@ -294,14 +297,14 @@ __global__ void __launch_bounds__(kPreBlock, 4) preprocess_fwd_kernel(const PreF
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) { v += __shfl_xor_sync(0xffffffffu, v, o); vr += __shfl_xor_sync(0xffffffffu, vr, o); }
     if ((tid & 31) == 0) { s_warp_sum[tid >> 5] = v; s_warp_sum_r[tid >> 5] = vr; s_warp_sum_v[tid >> 5] = vv; }
-    __syncthreads();
+    const int trap_any = __syncthreads_or(trapped);
     if (tid == 0) {
         uint32_t s = 0, sr = 0, sv = 0;
 #pragma unroll
         for (int w = 0; w < kPreBlock / 32; ++w) { s += s_warp_sum[w]; sr += s_warp_sum_r[w]; sv += s_warp_sum_v[w]; }
         p.block_sums[blockIdx.x] = s;
         p.block_sums_r[blockIdx.x] = sr;
-        p.block_sums_v[blockIdx.x] = sv;
+        p.block_sums_v[blockIdx.x] = sv | (trap_any ? 0x80000000u : 0u);
     }
 }
 
@@ -319,6 +322,7 @@ void launch_preprocess(const PreprocessArgs& a, const GeomPtrs& g, cudaStream_t 
     p.rects = g.rects; p.block_sums_r = g.block_sums_r; p.block_sums_v = g.block_sums_v;
     p.block_sums = g.block_sums; p.header = g.header; p.prefiltered = a.prefiltered ? 1 : 0;
     p.band_row0 = a.band_row0; p.band_row1 = a.band_row1;
+    p.zero_ptr = reinterpret_cast<uint4*>(a.zero_ptr); p.zero_n16 = a.zero_ptr ? a.zero_bytes / 16 : 0;
     preprocess_fwd_kernel<<<g.nblocks, kPreBlock, 0, s>>>(p);
     count_launch();
 }
@@ -328,7 +332,7 @@ void launch_preprocess(const PreprocessArgs& a, const GeomPtrs& g, cudaStream_t 
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(1024) block_scan_kernel(const uint32_t* __restrict__ sums, uint32_t* __restrict__ offsets,
                                                           int n, GeomHeader* header, uint32_t P, const uint32_t* __restrict__ sums_t,
-                                                          const uint32_t* __restrict__ sums_r) {
+                                                          const uint32_t* __restrict__ sums_r, uint32_t* mailbox) {
     // offsets = exclusive scan of sums (+ grand total at [n]).  With a header: sums = visible counts, and the plain totals
     // of sums_t (tiles touched -> num_rendered) and sums_r (tile rows -> num_runs) are taken on the way.
     // One pass: every thread owns a contiguous slice of the (small, cache-resident) array.
@@ -336,9 +340,12 @@ __global__ void __launch_bounds__(1024) block_scan_kernel(const uint32_t* __rest
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const int per = (n + 1023) / 1024;
     const int begin = min(n, tid * per), end = min(n, begin + per);
-    uint32_t local = 0, t = 0, r = 0;
-    for (int i = begin; i < end; ++i) local += sums[i];
+    // with a header, bit 31 of a visible count is the prefiltered-trap flag of that block
+    const uint32_t vmask = header != nullptr ? 0x7fffffffu : 0xffffffffu;
+    uint32_t local = 0, t = 0, r = 0, trap = 0;
+    for (int i = begin; i < end; ++i) { const uint32_t v = sums[i]; local += v & vmask; trap |= v & ~vmask; }
     if (header != nullptr) for (int i = begin; i < end; ++i) { t += sums_t[i]; r += sums_r[i]; }
+    const int trap_any = __syncthreads_or(trap != 0u);
     uint32_t inc = local;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) { uint32_t u = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += u; }
@@ -351,22 +358,30 @@ __global__ void __launch_bounds__(1024) block_scan_kernel(const uint32_t* __rest
 #pragma unroll
     for (int k = 0; k < 32; ++k) { const uint32_t v = s_warp[k]; wbase += (k < wid) ? v : 0u; total += v; tt += s_warp_t[k]; tr += s_warp_r[k]; }
     uint32_t running = wbase + inc - local;
-    for (int i = begin; i < end; ++i) { const uint32_t v = sums[i]; offsets[i] = running; running += v; }
+    for (int i = begin; i < end; ++i) { const uint32_t v = sums[i] & vmask; offsets[i] = running; running += v; }
     if (tid == 0) {
         offsets[n] = total;
-        if (header) {   // sort_error: zeroed by the host memset
+        if (header) {   // every header field is (re)written here: no host memset of the header
+            const uint32_t err = trap_any ? 0x100u : 0u;
             header->magic = kGeomMagic; header->P = P; header->num_rendered = tt; header->num_runs = tr; header->num_visible = total;
+            header->sort_error = err;
+            if (mailbox) {   // mapped pinned host memory: the host reads the totals without a DMA copy (a D2H memcpy would
+                             // queue behind the caller's own frame read-back on the copy engine)
+                volatile uint32_t* m = mailbox;
+                m[0] = kGeomMagic; m[1] = P; m[2] = tt; m[3] = err; m[4] = tr; m[5] = total;
+                __threadfence_system();
+            }
         }
     }
 }
 
-void launch_block_scan(const GeomPtrs& g, int P, cudaStream_t s) {
-    block_scan_kernel<<<1, 1024, 0, s>>>(g.block_sums_v, g.block_offsets, g.nblocks, g.header, (uint32_t)P, g.block_sums, g.block_sums_r);
+void launch_block_scan(const GeomPtrs& g, int P, uint32_t* mailbox_dev, cudaStream_t s) {
+    block_scan_kernel<<<1, 1024, 0, s>>>(g.block_sums_v, g.block_offsets, g.nblocks, g.header, (uint32_t)P, g.block_sums, g.block_sums_r, mailbox_dev);
     count_launch();
 }
 
 void launch_scan_u32(const uint32_t* sums, uint32_t* offsets, int n, cudaStream_t s) {
-    block_scan_kernel<<<1, 1024, 0, s>>>(sums, offsets, n, nullptr, 0u, nullptr, nullptr);
+    block_scan_kernel<<<1, 1024, 0, s>>>(sums, offsets, n, nullptr, 0u, nullptr, nullptr, nullptr);
     count_launch();
 }
 
