@@ -328,39 +328,66 @@ def measure(impl, args, d, cams, rank, world, timer, full):
     frame_host = torch.empty((3, args.height, args.width), dtype=torch.float32).pin_memory()
     h2d = sum(t.numel() * 4 for t in host_cams[0])
 
-    # the frame leaves on a copy stream into a ring of three pinned buffers, so the D2H DMA of frame i overlaps the render
-    # of frame i+1; every copy is complete (event-synchronised) before its buffer is reused and before the timed region
-    # ends.  (A ring of two makes the host wait ~0.1 ms per frame on the hand-off event, tools/e2e_diag2.py.)
+    # Software-pipelined read-back: frame i-1 leaves on a copy stream (ring of three pinned buffers) right AFTER the
+    # call that renders frame i has returned, i.e. while frame i's binning/blend kernels -- already queued -- run.
+    # Started earlier (right behind render i-1) the 25 MB DMA overlaps frame i's preprocess/scan/depth sort, whose
+    # launches and host round trip then queue behind it on PCIe (+0.12 ms/frame, measured per stage).  Every copy is
+    # complete (event-synchronised) before its buffer is reused and before the timed region ends.
     copy_stream = torch.cuda.Stream(device=dev)
     RING = 3
     frames_host = [frame_host] + [torch.empty_like(frame_host).pin_memory() for _ in range(RING - 1)]
     copied = [None] * RING
+    pending = {"img": None, "ready": None, "n": 0}
+    seg = [0.0, 0.0, 0.0, 0.0, 0]          # host seconds: h2d enqueue, forward_api, ring wait, copy enqueue; count
 
-    def step_e2e(i):
-        j = (i + rank) % ncam
-        v, p, c = (t.to(dev, non_blocking=True) for t in host_cams[j])
-        img = impl.forward_api(cams[j], v, p, c)
-        slot = i % RING
+    def read_back():
+        """queue the D2H copy of the pending frame (if any) on the copy stream"""
+        img = pending["img"]
+        if img is None:
+            return
+        slot = pending["n"] % RING
+        pending["n"] += 1
         if copied[slot] is not None:
-            copied[slot].synchronize()                   # the caller has consumed frame i-RING; its buffer is free again
-        copy_stream.wait_stream(torch.cuda.current_stream())
+            copied[slot].synchronize()                   # the caller has consumed the frame that used this buffer
+        copy_stream.wait_event(pending["ready"])
         with torch.cuda.stream(copy_stream):
             frames_host[slot].copy_(img, non_blocking=True)
             img.record_stream(copy_stream)
             ev = torch.cuda.Event(); ev.record(copy_stream)
         copied[slot] = ev
-        torch.cuda.current_stream().wait_event(ev) if i == Wm + K - 1 else None   # last timed step: drain inside the region
+        pending["img"] = None
+
+    def step_e2e(i):
+        t0 = time.perf_counter()
+        j = (i + rank) % ncam
+        v, p, c = (t.to(dev, non_blocking=True) for t in host_cams[j])
+        t1 = time.perf_counter()
+        img = impl.forward_api(cams[j], v, p, c)
+        ready = torch.cuda.Event(); ready.record()
+        t2 = time.perf_counter()
+        read_back()                                      # frame i-1, now that frame i is queued
+        pending["img"], pending["ready"] = img, ready
+        t3 = time.perf_counter()
+        seg[0] += t1 - t0; seg[1] += t2 - t1; seg[3] += t3 - t2; seg[4] += 1
 
     def step_e2e_drained(i):
         step_e2e(i)
-        if i == Wm + K - 1:
+        if i == Wm + K - 1:                              # last timed step: its own frame too, and drain inside the region
+            read_back()
             for e_ in copied:
                 if e_ is not None:
                     e_.synchronize()
+    st0 = torch.cuda.memory_stats()
     ms = timer.run(step_e2e_drained, K, Wm)
+    if os.environ.get("GSR_E2E_DIAG"):
+        st1 = torch.cuda.memory_stats()
+        print("e2e allocator: device_allocs %d device_frees %d reserved %d MB (incl. priming)" % (
+            st1["num_device_alloc"] - st0["num_device_alloc"], st1["num_device_free"] - st0["num_device_free"],
+            st1["reserved_bytes.all.current"] >> 20), file=sys.stderr)
+        print("e2e host ms/step: h2d %.3f forward_api %.3f read_back enqueue %.3f" % tuple(1e3 * x / seg[4] for x in (seg[0], seg[1], seg[3])), file=sys.stderr)
     out["e2e"] = {"value": world * K / (ms / 1e3), "unit": "frames/s", "h2d_bytes_per_step": h2d,
                   "d2h_bytes_per_step": frame_host.numel() * 4, "ms_per_step": ms / K,
-                  "pipeline": "render on the compute stream, frame D2H on a copy stream into a ring of 3 pinned buffers (overlaps the next render); all copies drained inside the timed region"}
+                  "pipeline": "render on the compute stream; the D2H of frame i-1 is queued on a copy stream (ring of 3 pinned buffers) after the call rendering frame i returns, so it overlaps frame i's binning/blend; all copies drained inside the timed region"}
     if not full:
         return out
 
@@ -480,7 +507,8 @@ def main():
     sampler = ClockSampler(local_rank)
     windows = []
     if rank == 0:
-        sampler.start()
+        if not os.environ.get("GSR_BENCH_NO_SMI"):
+            sampler.start()
     sc, d, cams_cpu, cams = make_inputs(args, rank)
     timer = Timer(eff_world, windows)
     peak, peak_src = load_peaks()

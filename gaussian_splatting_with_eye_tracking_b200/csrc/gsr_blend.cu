@@ -53,6 +53,11 @@ __device__ __forceinline__ bool cannot_touch(const float2 xy, const float4 co, f
     return qmin > tau;
 }
 
+// Per-pixel early reject, exact-preserving: power < reject_below(o)  =>  o * expf(power) < (1/255) * 0.98, so the
+// reference's `alpha < 1/255` test (forward.cu:343) is certain to skip the pair and expf need not be evaluated.
+// Same margin as cannot_touch; only called for o >= 1/255.
+__device__ __forceinline__ float reject_below(float o) { return -(__logf(255.0f * o) * 1.0001f + 0.02f); }
+
 __device__ __forceinline__ GaussRec gather(const uint32_t* __restrict__ point_list, const float2* __restrict__ means2D,
                                            const float4* __restrict__ conic_opacity, const float* __restrict__ colors, uint32_t li) {
     GaussRec r;
@@ -88,8 +93,9 @@ struct FwdParams {
 };
 
 __global__ void __launch_bounds__(kBlendThreads) blend_fwd_kernel(const FwdParams p) {
-    // staged entry = 3 x float4: (x, y, conic.x, conic.y) (conic.z, opacity, r, g) (b, 1-based list position, -, -):
-    // one base pointer, immediate offsets, 128-bit broadcast loads
+    // staged entry = 3 x float4: (x, y, conic.x, conic.y) (conic.z, reject threshold, opacity, 1-based list position)
+    // (r, g, b, -): one base pointer, immediate offsets, 128-bit broadcast loads; the colour vector is only read by
+    // pixels the entry contributes to
     __shared__ float4 s_ent[3 * kBlendThreads];
     __shared__ uint32_t s_wcnt[kBlendThreads / 32];
     __shared__ uint32_t s_count;
@@ -122,8 +128,8 @@ __global__ void __launch_bounds__(kBlendThreads) blend_fwd_kernel(const FwdParam
         const int slot = compact_slot(keep, s_wcnt, &s_count);
         if (slot >= 0) {
             s_ent[3 * slot] = make_float4(nxt.xy.x, nxt.xy.y, nxt.co.x, nxt.co.y);
-            s_ent[3 * slot + 1] = make_float4(nxt.co.z, nxt.co.w, nxt.col.x, nxt.col.y);
-            s_ent[3 * slot + 2] = make_float4(nxt.col.z, __uint_as_float((uint32_t)(r * kBlendThreads + tid + 1)), 0.f, 0.f);
+            s_ent[3 * slot + 1] = make_float4(nxt.co.z, reject_below(nxt.co.w), nxt.co.w, __uint_as_float((uint32_t)(r * kBlendThreads + tid + 1)));
+            s_ent[3 * slot + 2] = make_float4(nxt.col.x, nxt.col.y, nxt.col.z, 0.f);
         }
         __syncthreads();
         const int count = (int)s_count;
@@ -139,18 +145,19 @@ __global__ void __launch_bounds__(kBlendThreads) blend_fwd_kernel(const FwdParam
                 const float4 A = e[0], B = e[1];
                 const float dx = __fadd_rn(A.x, -pxf), dy = __fadd_rn(A.y, -pyf);
                 const float power = blend_power(A.z, A.w, B.x, dx, dy);
-                if (power > 0.0f) continue;
-                const float alpha = fminf(0.99f, __fmul_rn(B.y, expf(power)));
+                if (power < B.y || power > 0.0f) continue;       // certain alpha < 1/255 (reject_below) | forward.cu:337
+                const float alpha = fminf(0.99f, __fmul_rn(B.z, expf(power)));
                 if (alpha < kAlphaMin) continue;
                 const float test_T = __fmul_rn(T, __fadd_rn(1.f, -alpha));
                 if (test_T < 0.0001f) { done = true; break; }
-                C0 = __fmaf_rn(T, __fmul_rn(alpha, B.z), C0);
-                C1 = __fmaf_rn(T, __fmul_rn(alpha, B.w), C1);
-                C2 = __fmaf_rn(T, __fmul_rn(alpha, e[2].x), C2);
+                const float4 Cc = e[2];
+                C0 = __fmaf_rn(T, __fmul_rn(alpha, Cc.x), C0);
+                C1 = __fmaf_rn(T, __fmul_rn(alpha, Cc.y), C1);
+                C2 = __fmaf_rn(T, __fmul_rn(alpha, Cc.z), C2);
                 T = test_T;
                 last_j = j;
             }
-            if (last_j >= 0) last_contributor = __float_as_uint(s_ent[3 * last_j + 2].y);
+            if (last_j >= 0) last_contributor = __float_as_uint(s_ent[3 * last_j + 1].w);
         }
     }
     if (inside) {
@@ -239,8 +246,8 @@ __global__ void __launch_bounds__(kBlendThreads) blend_amr_kernel(const AmrParam
         const int slot = compact_slot(keep, s_wcnt, &s_count);
         if (slot >= 0) {
             s_ent[3 * slot] = make_float4(nxt.xy.x, nxt.xy.y, nxt.co.x, nxt.co.y);
-            s_ent[3 * slot + 1] = make_float4(nxt.co.z, nxt.co.w, nxt.col.x, nxt.col.y);
-            s_ent[3 * slot + 2] = make_float4(nxt.col.z, __uint_as_float((uint32_t)(r * kBlendThreads + tid + 1)), 0.f, 0.f);
+            s_ent[3 * slot + 1] = make_float4(nxt.co.z, reject_below(nxt.co.w), nxt.co.w, __uint_as_float((uint32_t)(r * kBlendThreads + tid + 1)));
+            s_ent[3 * slot + 2] = make_float4(nxt.col.x, nxt.col.y, nxt.col.z, 0.f);
         }
         __syncthreads();
         const int count = (int)s_count;
@@ -258,16 +265,16 @@ __global__ void __launch_bounds__(kBlendThreads) blend_amr_kernel(const AmrParam
                     if (done[k]) continue;
                     const float dx = __fadd_rn(A.x, -pxf[k]), dy = __fadd_rn(A.y, -pyf[k]);
                     const float power = blend_power(A.z, A.w, B.x, dx, dy);
-                    if (power > 0.0f) continue;
-                    const float alpha = fminf(0.99f, __fmul_rn(B.y, expf(power)));
+                    if (power < B.y || power > 0.0f) continue;   // certain alpha < 1/255 (reject_below) | forward.cu:337
+                    const float alpha = fminf(0.99f, __fmul_rn(B.z, expf(power)));
                     if (alpha < kAlphaMin) continue;
                     const float test_T = __fmul_rn(T[k], __fadd_rn(1.f, -alpha));
                     if (test_T < 0.0001f) { done[k] = true; continue; }
-                    Cr[k] = __fmaf_rn(T[k], __fmul_rn(alpha, B.z), Cr[k]);
-                    Cg[k] = __fmaf_rn(T[k], __fmul_rn(alpha, B.w), Cg[k]);
-                    Cb[k] = __fmaf_rn(T[k], __fmul_rn(alpha, Cc.x), Cb[k]);
+                    Cr[k] = __fmaf_rn(T[k], __fmul_rn(alpha, Cc.x), Cr[k]);
+                    Cg[k] = __fmaf_rn(T[k], __fmul_rn(alpha, Cc.y), Cg[k]);
+                    Cb[k] = __fmaf_rn(T[k], __fmul_rn(alpha, Cc.z), Cb[k]);
                     T[k] = test_T;
-                    lastc[k] = __float_as_uint(Cc.y);
+                    lastc[k] = __float_as_uint(B.w);
                 }
                 all_done = done[0] && done[1] && done[2] && done[3];
             }
@@ -432,7 +439,7 @@ __global__ void __launch_bounds__(kBlendThreads) blend_bwd_kernel(const BwdParam
         if (slot >= 0) {
             s_a[slot] = make_float4(nxt.xy.x, nxt.xy.y, nxt.co.x, nxt.co.y);
             s_b[slot] = make_float4(nxt.co.z, nxt.co.w, nxt.col.x, nxt.col.y);
-            s_c[slot] = make_float4(nxt.col.z, __uint_as_float((uint32_t)pos_of(r)), __uint_as_float(nxt.id), 0.f);
+            s_c[slot] = make_float4(nxt.col.z, __uint_as_float((uint32_t)pos_of(r)), __uint_as_float(nxt.id), reject_below(nxt.co.w));
         }
         __syncthreads();
         const int count = (int)s_count;
@@ -447,10 +454,13 @@ __global__ void __launch_bounds__(kBlendThreads) blend_bwd_kernel(const BwdParam
             const uint32_t pos = __float_as_uint(Cc.y);
             const float dx = A.x - pxf, dy = A.y - pyf;
             const float power = blend_power(A.z, A.w, B.x, dx, dy);
+            // (!inside pixels carry last_contributor = 0 and positions are 1-based, so no separate `inside` test)
+            // candidates: not behind the pixel's last contributor, not certain to fail the alpha test (reject_below)
+            const bool cand = pos <= last_contributor && !(power < Cc.w) && !(power > 0.0f);
+            if (!__any_sync(0xffffffffu, cand)) continue;
             const float G = expf(power);
             const float alpha = fminf(0.99f, B.y * G);
-            // (!inside pixels carry last_contributor = 0 and positions are 1-based, so no separate `inside` test)
-            const bool act = pos <= last_contributor && !(power > 0.0f) && !(alpha < kAlphaMin);
+            const bool act = cand && !(alpha < kAlphaMin);
             if (!__any_sync(0xffffffffu, act)) continue;
 
             float v[8], v8 = 0.f;

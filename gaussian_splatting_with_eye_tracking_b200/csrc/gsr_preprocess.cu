@@ -369,7 +369,9 @@ __global__ void __launch_bounds__(1024) block_scan_kernel(const uint32_t* __rest
                              // queue behind the caller's own frame read-back on the copy engine)
                 volatile uint32_t* m = mailbox;
                 m[0] = kGeomMagic; m[1] = P; m[2] = tt; m[3] = err; m[4] = tr; m[5] = total;
-                __threadfence_system();
+                // no __threadfence_system(): the host reads after the event recorded behind this kernel, and posted
+                // PCIe writes stay ordered; a system fence here waits out whatever DMA traffic is queued (+50 us
+                // while a 25 MB frame read-back is in flight)
             }
         }
     }
