@@ -62,44 +62,82 @@ def parse_args():
 # helpers
 # ---------------------------------------------------------------------------------------------------------------
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons DURING the timed regions (B200_PROFILING.md recipe)."""
+    """SM clocks / throttle reasons DURING the timed regions (B200_PROFILING.md recipe).  NVML is polled from a thread
+    (25 ms period, so that even a 40-step region holds samples); nvidia-smi -lms is the fallback when NVML cannot be
+    loaded."""
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    REASONS = ((0x8, "hw_slowdown"), (0x40, "hw_thermal_slowdown"), (0x20, "sw_thermal_slowdown"), (0x4, "sw_power_cap"))
 
     def __init__(self, index):
-        self.index, self.rows, self.proc = index, [], None
+        self.index, self.rows, self.proc, self.stop_flag, self.source = index, [], None, False, None
+
+    def _nvml_handle(self):
+        import pynvml
+        pynvml.nvmlInit()
+        try:
+            uuid = str(torch.cuda.get_device_properties(self.index).uuid)
+            return pynvml, pynvml.nvmlDeviceGetHandleByUUID(("GPU-" + uuid) if not uuid.startswith("GPU-") else uuid)
+        except Exception:
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES", "")
+            ids = [v for v in vis.split(",") if v.strip().isdigit()]
+            return pynvml, pynvml.nvmlDeviceGetHandleByIndex(int(ids[self.index]) if self.index < len(ids) else self.index)
+
+    def _poll(self, pynvml, h):
+        mx = float(pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM))
+        get_reasons = getattr(pynvml, "nvmlDeviceGetCurrentClocksEventReasons", None) or pynvml.nvmlDeviceGetCurrentClocksThrottleReasons
+        while not self.stop_flag:
+            try:
+                sm = float(pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM))
+                mask = int(get_reasons(h))
+                self.rows.append((time.time(), sm, mx, [n for bit, n in self.REASONS if mask & bit]))
+            except Exception:
+                pass
+            time.sleep(0.025)
 
     def start(self):
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "200",
+            pynvml, h = self._nvml_handle()
+            pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM)
+            self.source = "nvml"
+            threading.Thread(target=self._poll, args=(pynvml, h), daemon=True).start()
+            return
+        except Exception:
+            pass
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "50",
                                           "-i", str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.source = "nvidia-smi"
             threading.Thread(target=self._read, daemon=True).start()
         except Exception:
             self.proc = None
 
     def _read(self):
         for line in self.proc.stdout:
-            self.rows.append((time.time(), [x.strip() for x in line.split(",")]))
+            r = [x.strip() for x in line.split(",")]
+            if len(r) < 9:
+                continue
+            try:
+                self.rows.append((time.time(), float(r[1]), float(r[2]),
+                                  [n for n, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[5:9])
+                                   if v.lower().startswith("active")]))
+            except ValueError:
+                continue
 
     def stop(self):
+        self.stop_flag = True
         if self.proc:
             self.proc.terminate()
 
     def summary(self, windows):
-        sm, mx, reasons = [], [], set()
-        for t, r in self.rows:
-            if len(r) < 9 or not any(a <= t <= b for a, b in windows):
-                continue
-            try:
-                sm.append(float(r[1])); mx.append(float(r[2]))
-            except ValueError:
-                continue
-            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[5:9]):
-                if v.lower().startswith("active"):
-                    reasons.add(name)
-        if not sm:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
-        return {"sm_mhz": statistics.median(sm), "sm_max_mhz": max(mx), "reasons": sorted(reasons), "samples": len(sm)}
+        rows = [r for r in self.rows if any(a <= r[0] <= b for a, b in windows)]
+        if not rows and windows:      # very short regions: fall back to everything between the first and the last one
+            rows = [r for r in self.rows if windows[0][0] <= r[0] <= windows[-1][1]]
+        if not rows:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0, "source": self.source}
+        reasons = sorted({n for r in rows for n in r[3]})
+        return {"sm_mhz": statistics.median(r[1] for r in rows), "sm_max_mhz": max(r[2] for r in rows), "reasons": reasons,
+                "samples": len(rows), "source": self.source}
 
 
 def dist_env():
@@ -473,6 +511,22 @@ def cpu_baseline(sc, cams):
             "seconds": dt}
 
 
+def c1_prototype_cpu(sc, cams_cpu, frame, W, H):
+    """Config C1: the reference's CPU tile-refinement prototype (AMR_test.py), restated headless in
+    oracle/amr_prototype.py, on the C3 scene's projected means and one frame rendered by this rasterizer.  Bounded
+    sample: the O(tiles x N) counting loop on 100 k points and the griddata fill on a W/4 x H/4 window (both
+    extrapolated to the full frame and flagged); projection, histogram, levels and lattice run at full size."""
+    from oracle import amr_prototype as ap
+    cam = cams_cpu[0]
+    res, t = ap.run(sc["means3D"].numpy(), cam.world_view_transform.numpy(), cam.full_proj_transform.numpy(), frame, W, H,
+                    loop_sample=100_000, fill=True, fill_crop=(W // 4, H // 4))
+    est = t["project"] + t["count_hist"] + t["levels"] + t["lattice"] + t["griddata_fill_extrapolated"]
+    return {"seconds": {k: round(v, 4) for k, v in t.items()}, "frame_seconds_estimate": round(est, 3),
+            "estimate": "project + count_hist + levels + lattice + griddata_fill_extrapolated (fill measured on a 1/16-area window)",
+            "fraction_of_pixels_rendered": round(res["fraction_rendered"], 4), "gaussians_in_image": res["in_image"],
+            "cores": os.cpu_count(), "what": "numpy/scipy restatement of AMR_test.py:109-280 (kind: port)"}
+
+
 def main():
     args = parse_args()
     rank, local_rank, world = dist_env()
@@ -507,8 +561,7 @@ def main():
     sampler = ClockSampler(local_rank)
     windows = []
     if rank == 0:
-        if not os.environ.get("GSR_BENCH_NO_SMI"):
-            sampler.start()
+        sampler.start()
     sc, d, cams_cpu, cams = make_inputs(args, rank)
     timer = Timer(eff_world, windows)
     peak, peak_src = load_peaks()
@@ -566,6 +619,11 @@ def main():
                     extra["reference_cuda_same_run"] = {"error": str(ex)[:300]}
             if not args.no_cpu_baseline:
                 line["cpu_baseline"] = cpu_baseline(sc, cams_cpu)
+                try:
+                    frame = Ours(d).forward_c(cams[0])[1].cpu().numpy()
+                    extra["c1_amr_prototype_cpu"] = c1_prototype_cpu(sc, cams_cpu, frame, args.width, args.height)
+                except Exception as ex:
+                    extra["c1_amr_prototype_cpu"] = {"error": str(ex)[:300]}
         line["extra"] = extra
 
     if rank == 0:

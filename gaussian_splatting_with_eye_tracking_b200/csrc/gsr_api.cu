@@ -279,6 +279,7 @@ int gsr_profile_read(float* ms, int* counts) {
 const char* gsr_last_error(void) { return g_err; }
 int gsr_set_option(int option, int value) {
     if (option == GSR_OPT_SORT_VARIANT && value >= 0 && value <= 5) { set_sort_variant(value); return GSR_OK; }
+    if (option == GSR_OPT_BLEND_VARIANT && value >= 0 && value <= 1) { set_blend_variant(value); return GSR_OK; }
     set_error("unknown option %d / value %d", option, value);
     return GSR_ERR_INVALID;
 }

@@ -68,7 +68,8 @@ __device__ __forceinline__ GaussRec gather(const uint32_t* __restrict__ point_li
     return r;
 }
 
-// CTA-wide stable compaction of `keep` flags; returns slot (or -1) and sets s_count.  Needs 8 warps.
+// CTA-wide stable compaction of `keep` flags; returns slot (or -1) and sets s_count.
+template <int NTHREADS = kBlendThreads>
 __device__ __forceinline__ int compact_slot(bool keep, uint32_t* s_wcnt, uint32_t* s_count) {
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const uint32_t m = __ballot_sync(0xffffffffu, keep);
@@ -76,7 +77,7 @@ __device__ __forceinline__ int compact_slot(bool keep, uint32_t* s_wcnt, uint32_
     __syncthreads();
     uint32_t base = 0, tot = 0;
 #pragma unroll
-    for (int w = 0; w < kBlendThreads / 32; ++w) { const uint32_t c = s_wcnt[w]; base += (w < wid) ? c : 0u; tot += c; }
+    for (int w = 0; w < NTHREADS / 32; ++w) { const uint32_t c = s_wcnt[w]; base += (w < wid) ? c : 0u; tot += c; }
     if (threadIdx.x == 0) *s_count = tot;
     return keep ? (int)(base + __popc(m & ((1u << lane) - 1u))) : -1;
 }
@@ -171,6 +172,121 @@ __global__ void __launch_bounds__(kBlendThreads) blend_fwd_kernel(const FwdParam
     }
 }
 
+// ------------------------------------------------------------------------------------------------
+// forward, two pixels per thread with packed FP32x2 arithmetic (default).  The kernel above is bound by instruction
+// issue (ncu: 79 % issue-active, FMA pipe 49 %); here one FADD2/FMUL2/FFMA2 does the exponent arithmetic of two
+// horizontally adjacent pixels, and one pair of 128-bit shared loads feeds both.  128 threads per 16x16 tile,
+// warp = 8x8 pixels.  Per-pixel results are bit-identical (every half is an IEEE round-to-nearest operation).
+// ------------------------------------------------------------------------------------------------
+constexpr int kBlend2Threads = 128;
+
+__global__ void __launch_bounds__(kBlend2Threads) blend_fwd2_kernel(const FwdParams p) {
+    __shared__ float4 s_ent[3 * kBlend2Threads];
+    __shared__ uint32_t s_wcnt[kBlend2Threads / 32];
+    __shared__ uint32_t s_count;
+
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const uint32_t lx = (wid & 1) * 8 + (lane & 3) * 2, ly = (wid >> 1) * 8 + (lane >> 2);
+    const uint32_t tile_y = blockIdx.y + (uint32_t)p.row0;
+    const uint32_t pix_x = blockIdx.x * 16 + lx, pix_y = tile_y * 16 + ly;
+    const bool inside0 = pix_x < (uint32_t)p.W && pix_y < (uint32_t)p.H;
+    const bool inside1 = pix_x + 1 < (uint32_t)p.W && pix_y < (uint32_t)p.H;
+    const float pyf = (float)pix_y;
+    const f32x2 npx2 = pk(-(float)pix_x, -(float)(pix_x + 1));
+    const float rx0 = (float)(blockIdx.x * 16), ry0 = (float)(tile_y * 16);
+    const float rx1 = rx0 + 15.f, ry1 = ry0 + 15.f;
+
+    const uint2 range = p.ranges[tile_y * p.tiles_x + blockIdx.x];
+    const int todo = (int)(range.y - range.x);
+    const int rounds = (todo + kBlend2Threads - 1) / kBlend2Threads;
+
+    float T0 = 1.0f, T1 = 1.0f, Ca0 = 0.f, Ca1 = 0.f, Ca2 = 0.f, Cb0 = 0.f, Cb1 = 0.f, Cb2 = 0.f;
+    uint32_t last0 = 0, last1 = 0;
+    bool done0 = !inside0, done1 = !inside1;
+
+    GaussRec nxt; bool nxt_valid = false;
+    if (tid < todo) { nxt = gather(p.point_list, p.means2D, p.conic_opacity, p.colors, range.x + tid); nxt_valid = true; }
+
+    for (int r = 0; r < rounds; ++r) {
+        if (__syncthreads_count(done0 && done1) == kBlend2Threads) break;
+        const bool keep = nxt_valid && !cannot_touch(nxt.xy, nxt.co, rx0, ry0, rx1, ry1);
+        const int slot = compact_slot<kBlend2Threads>(keep, s_wcnt, &s_count);
+        if (slot >= 0) {
+            s_ent[3 * slot] = make_float4(nxt.xy.x, nxt.xy.y, nxt.co.x, nxt.co.y);
+            s_ent[3 * slot + 1] = make_float4(nxt.co.z, reject_below(nxt.co.w), nxt.co.w, __uint_as_float((uint32_t)(r * kBlend2Threads + tid + 1)));
+            s_ent[3 * slot + 2] = make_float4(nxt.col.x, nxt.col.y, nxt.col.z, 0.f);
+        }
+        __syncthreads();
+        const int count = (int)s_count;
+        const int nprog = (r + 1) * kBlend2Threads + tid;
+        nxt_valid = nprog < todo;
+        if (nxt_valid) nxt = gather(p.point_list, p.means2D, p.conic_opacity, p.colors, range.x + nprog);
+
+        if (!(done0 && done1)) {
+            const float4* e = s_ent;
+            int lj0 = -1, lj1 = -1;
+            for (int j = 0; j < count; ++j, e += 3) {
+                const float4 A = e[0], B = e[1];
+                const float dy = __fadd_rn(A.y, -pyf);
+                float pw0, pw1;
+                upk(blend_power2(A.z, A.w, B.x, add2(pk(A.x, A.x), npx2), dy), pw0, pw1);
+                // B.y: below it alpha < 1/255 is certain (reject_below); > 0: forward.cu:337
+                const bool c0 = !done0 && !(pw0 < B.y) && !(pw0 > 0.0f);
+                const bool c1 = !done1 && !(pw1 < B.y) && !(pw1 > 0.0f);
+                if (!(c0 || c1)) continue;
+                const float4 Cc = e[2];
+                if (c0) {
+                    const float alpha = fminf(0.99f, __fmul_rn(B.z, expf(pw0)));
+                    if (!(alpha < kAlphaMin)) {
+                        const float test_T = __fmul_rn(T0, __fadd_rn(1.f, -alpha));
+                        if (test_T < 0.0001f) done0 = true;
+                        else {
+                            Ca0 = __fmaf_rn(T0, __fmul_rn(alpha, Cc.x), Ca0);
+                            Ca1 = __fmaf_rn(T0, __fmul_rn(alpha, Cc.y), Ca1);
+                            Ca2 = __fmaf_rn(T0, __fmul_rn(alpha, Cc.z), Ca2);
+                            T0 = test_T; lj0 = j;
+                        }
+                    }
+                }
+                if (c1) {
+                    const float alpha = fminf(0.99f, __fmul_rn(B.z, expf(pw1)));
+                    if (!(alpha < kAlphaMin)) {
+                        const float test_T = __fmul_rn(T1, __fadd_rn(1.f, -alpha));
+                        if (test_T < 0.0001f) done1 = true;
+                        else {
+                            Cb0 = __fmaf_rn(T1, __fmul_rn(alpha, Cc.x), Cb0);
+                            Cb1 = __fmaf_rn(T1, __fmul_rn(alpha, Cc.y), Cb1);
+                            Cb2 = __fmaf_rn(T1, __fmul_rn(alpha, Cc.z), Cb2);
+                            T1 = test_T; lj1 = j;
+                        }
+                    }
+                }
+                if (done0 && done1) break;
+            }
+            if (lj0 >= 0) last0 = __float_as_uint(s_ent[3 * lj0 + 1].w);
+            if (lj1 >= 0) last1 = __float_as_uint(s_ent[3 * lj1 + 1].w);
+        }
+    }
+    const size_t HW = (size_t)p.H * p.W;
+    const float bg0 = __ldg(p.bg), bg1 = __ldg(p.bg + 1), bg2 = __ldg(p.bg + 2);
+    const size_t pix_id = (size_t)p.W * pix_y + pix_x;
+    if (inside0) {
+        p.final_T[pix_id] = T0; p.n_contrib[pix_id] = last0;
+        p.out_color[pix_id] = __fmaf_rn(T0, bg0, Ca0);
+        p.out_color[HW + pix_id] = __fmaf_rn(T0, bg1, Ca1);
+        p.out_color[2 * HW + pix_id] = __fmaf_rn(T0, bg2, Ca2);
+    }
+    if (inside1) {
+        p.final_T[pix_id + 1] = T1; p.n_contrib[pix_id + 1] = last1;
+        p.out_color[pix_id + 1] = __fmaf_rn(T1, bg0, Cb0);
+        p.out_color[HW + pix_id + 1] = __fmaf_rn(T1, bg1, Cb1);
+        p.out_color[2 * HW + pix_id + 1] = __fmaf_rn(T1, bg2, Cb2);
+    }
+}
+
+static int g_blend_variant = 0;
+void set_blend_variant(int v) { g_blend_variant = v; }
+
 void launch_blend_forward(const BlendArgs& a, cudaStream_t s) {
     FwdParams p;
     p.W = a.W; p.H = a.H; p.tiles_x = (a.W + 15) / 16;
@@ -181,7 +297,8 @@ void launch_blend_forward(const BlendArgs& a, cudaStream_t s) {
     if (r1 <= r0) return;
     p.row0 = r0;
     dim3 grid((a.W + 15) / 16, r1 - r0, 1);
-    blend_fwd_kernel<<<grid, kBlendThreads, 0, s>>>(p);
+    if (g_blend_variant == 1) blend_fwd_kernel<<<grid, kBlendThreads, 0, s>>>(p);      // one pixel per thread (A/B reference)
+    else blend_fwd2_kernel<<<grid, kBlend2Threads, 0, s>>>(p);
     count_launch();
 }
 

@@ -280,6 +280,7 @@ uint32_t* sort_hist_ptr(void* temp);
 size_t sort_prezero_bytes(long long n, const SortPlan& plan, size_t temp_bytes, bool keys64);
 void launch_zero(void* ptr, size_t bytes, cudaStream_t s);   // bytes % 16 == 0, ptr 16 B aligned
 void set_sort_variant(int v);
+void set_blend_variant(int v);
 
 void launch_amr_levels(const ImgPtrs& im, int num_tiles, cudaStream_t s);
 void launch_fovea_levels(const ImgPtrs& im, int num_tiles, int fovea_step, const gsr_gaze* gaze, cudaStream_t s);

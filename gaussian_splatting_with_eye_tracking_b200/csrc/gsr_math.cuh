@@ -77,4 +77,23 @@ __device__ __forceinline__ float blend_power(float cx, float cy, float cz, float
     return __fmaf_rn(s, -0.5f, -m);
 }
 
+// ---- packed FP32x2 (sm_100a FADD2 / FMUL2 / FFMA2): two IEEE round-to-nearest operations per issued instruction.
+// Each half is bit-identical to the scalar __f*_rn intrinsic; pk(v, v) compiles to a broadcast operand (no move).
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pk(float lo, float hi) { f32x2 r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi)); return r; }
+__device__ __forceinline__ void upk(f32x2 v, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
+__device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b) { f32x2 r; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) { f32x2 r; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) { f32x2 r; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c)); return r; }
+
+// blend_power for two horizontally adjacent pixels (dx differs, dy shared): same operations, same order, per half.
+// NOTE: every mul2 below feeds an fma2 as a multiplicand or as the addend of a DIFFERENT product, so ptxas has no
+// mul+add pair to contract (it does contract mul.rn.f32x2 + add.rn.f32x2, unlike the scalar .rn forms).
+__device__ __forceinline__ f32x2 blend_power2(float cx, float cy, float cz, f32x2 dx2, float dy) {
+    const float b = __fmul_rn(dy, __fmul_rn(dy, cz));
+    const f32x2 s2 = fma2(dx2, mul2(dx2, pk(cx, cx)), pk(b, b));
+    const f32x2 m2n = mul2(pk(-dy, -dy), mul2(dx2, pk(cy, cy)));     // -(dy * (dx * cy)), negation is exact
+    return fma2(s2, pk(-0.5f, -0.5f), m2n);
+}
+
 }  // namespace gsr

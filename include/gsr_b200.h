@@ -225,7 +225,8 @@ GSR_API void gsr_profile_enable(int on);
 GSR_API int gsr_profile_read(float* ms, int* counts);
 
 /* ---- tuning knobs (results never depend on them) ---- */
-enum { GSR_OPT_SORT_VARIANT = 0 /* onesweep tile shape for u32 keys: 0 = default, 1..5 see gsr_binning.cu */ };
+enum { GSR_OPT_SORT_VARIANT = 0,  /* onesweep tile shape for u32 keys: 0 = default, 1..5 see gsr_binning.cu */
+       GSR_OPT_BLEND_VARIANT = 1  /* forward blend: 0 = two pixels per thread, packed FP32x2 (default); 1 = one pixel per thread */ };
 GSR_API int gsr_set_option(int option, int value);
 
 /* counters: how many kernels this library launched since load (bench.py "gpu_launches") */

@@ -155,3 +155,51 @@ def test_empty_and_offscreen_inputs():
     bg = sc["bg"].numpy()
     assert np.allclose(o["out_color"], bg[:, None, None])          # nothing blended: T = 1 everywhere
     assert (o["ranges"] == 0).all()
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# C1: numpy/scipy restatement of the reference's CPU tile-refinement prototype (oracle/amr_prototype.py)
+# ---------------------------------------------------------------------------------------------------------------
+def test_amr_prototype_counts_levels_lattice_and_fill():
+    from oracle import amr_prototype as ap
+    rng = np.random.default_rng(5)
+    W, H = 96, 64
+    x, y = rng.uniform(0, W, 4000), rng.uniform(0, H, 4000)
+    loop, hist = ap.tile_counts_loop(x, y, W, H), ap.tile_counts_hist(x, y, W, H)
+    assert loop.shape == (W // 16 + 1, H // 16 + 1) and np.array_equal(loop, hist) and loop.sum() == 4000
+    # log10 rule: floor(1.5 * log10(c + 1)) + 1, clamped to 4  (AMR_test.py:191-195)
+    c = np.array([[0, 3, 4, 21], [99, 464, 465, 100000]], dtype=float)
+    assert ap.levels_log10(c).tolist() == [[1, 1, 2, 3], [4, 4, 4, 4]]
+    # percentile rule: bands (0,.25], (.25,.5], (.5,.9], (.9,1]  (AMR_test_cuda.py:209-218)
+    cp = np.arange(1, 101, dtype=float).reshape(10, 10)
+    lp = ap.levels_percentile(cp)
+    assert [int((lp == k).sum()) for k in (1, 2, 3, 4)] == [25, 25, 40, 10]
+    # lattice: stride 2^(4 - level) inside each tile, last row/column of the image excluded as in the prototype
+    lv = np.full((W // 16 + 1, H // 16 + 1), 2)
+    pts = ap.accurate_points(lv, W, H)
+    assert pts.shape[0] == (W // 4) * (H // 4) and set(np.unique(pts[:, 0] % 4)) == {0}
+    # linear fill reproduces an affine image exactly inside the hull of the lattice
+    yy, xx = np.mgrid[0:H, 0:W]
+    img = np.stack([0.01 * xx + 0.02 * yy, 0.5 - 0.003 * xx, 0.1 + 0.0 * yy]).astype(np.float64)
+    out = ap.fill_linear(img, ap.accurate_points(np.full_like(lv, 3), W, H))
+    inside = np.isfinite(out)
+    assert inside.mean() > 0.9 and np.abs(out[inside] - img[inside]).max() < 1e-9
+
+
+def test_amr_prototype_projection_matches_the_rasterizer_oracle():
+    """project_means (AMR_test.py:109-136) against the pixel centres the C oracle's preprocess computes."""
+    from oracle import amr_prototype as ap
+    sc, cam = common.make_case("small")
+    o = common.run_oracle(sc, cam)
+    V = cam.world_view_transform.numpy().astype(np.float32)
+    Pm = cam.full_proj_transform.numpy().astype(np.float32)
+    m3 = sc["means3D"].numpy().astype(np.float32)
+    W, H = int(cam.image_width), int(cam.image_height)
+    x, y = ap.project_means(m3, V, Pm, W, H)
+    vis = o["radii"] > 0
+    m2 = o["means2D"][vis]
+    ins = (m2[:, 0] >= 0) & (m2[:, 0] < W) & (m2[:, 1] >= 0) & (m2[:, 1] < H)
+    # every visible Gaussian whose centre is inside the image is in the prototype's set, at the same pixel position
+    got = {(round(float(a), 2), round(float(b), 2)) for a, b in zip(x, y)}
+    want = {(round(float(a), 2), round(float(b), 2)) for a, b in m2[ins]}
+    assert len(want) > 10 and len(want - got) <= max(1, len(want) // 200)

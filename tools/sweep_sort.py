@@ -19,7 +19,7 @@ def run(cam):
 
 ref = None
 for v in [int(x) for x in (sys.argv[1:] or ["0", "1", "2", "3", "4", "5"])]:
-    _capi.check(_capi.lib.gsr_set_option(0, v), "set_option")
+    _capi.check(_capi.lib.gsr_set_option(0 if v < 10 else 1, v % 10), "set_option")   # 0..5: sort variants, 10/11: blend variants
     for c in cams:
         run(c)
     torch.cuda.synchronize()
