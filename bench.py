@@ -40,8 +40,8 @@ ALG_BYTES_CULLED = 20                 # 12 B mean read + radius / tiles_touched 
 
 
 # dram__bytes_read.sum + dram__bytes_write.sum of one preprocess_fwd_kernel launch from the committed `ncu --set full`
-# capture (profiles/r1_v5_ncu_full_fwd_summary.csv; camera 0 of the C3 workload), keyed by the Gaussian count
-NCU_TRAFFIC_BYTES = {3_000_000: 553_534_208 + 207_832_064}
+# capture (profiles/r1_v11_ncu_full_preprocess_summary.csv; camera 0 of the C3 workload), keyed by the Gaussian count
+NCU_TRAFFIC_BYTES = {3_000_000: 448_445_696 + 221_628_160}
 
 
 def parse_args():

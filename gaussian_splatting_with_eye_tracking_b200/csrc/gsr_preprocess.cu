@@ -230,6 +230,7 @@ __global__ void __launch_bounds__(kPreBlock, 4) preprocess_fwd_kernel(const PreF
         float2 pix = make_float2(0.f, 0.f);
         float3 conic = make_float3(0.f, 0.f, 0.f);
         uint32_t x0 = 0, y0 = 0, x1 = 0, y1 = 0;
+        bool wrote_cov = false;
         if (alive) {
             const float hw = __fadd_rn(xform_row(sPm[3], sPm[7], sPm[11], sPm[15], px, py, pz), 0.0000001f);
             const float hx = xform_row(sPm[0], sPm[4], sPm[8], sPm[12], px, py, pz);
@@ -246,6 +247,7 @@ __global__ void __launch_bounds__(kPreBlock, 4) preprocess_fwd_kernel(const PreF
                             sz = __ldg(p.scales + 3 * (size_t)idx + 2);
                 const float4 q = __ldg(reinterpret_cast<const float4*>(p.rotations) + idx);
                 cov3d_from_scale_rot(sx, sy, sz, p.scale_modifier, q, c3);
+                wrote_cov = true;
 #pragma unroll
                 for (int i = 0; i < 6; ++i) p.cov3D[6 * (size_t)idx + i] = c3[i];
             }
@@ -270,19 +272,26 @@ __global__ void __launch_bounds__(kPreBlock, 4) preprocess_fwd_kernel(const PreF
                 if (!alive) radius = 0;
             }
         }
-        if (alive) {
-            if (p.colors_precomp == nullptr) {
-                float rgb[3]; bool cl[3];
-                const size_t shoff = (size_t)idx * p.M * 3;
-                const bool vec_ok = ((p.M * 3) % 4 == 0) && ((reinterpret_cast<size_t>(p.shs) & 15) == 0);
-                sh_to_rgb(p.D, p.shs + shoff, vec_ok, __fadd_rn(px, -sCam[0]), __fadd_rn(py, -sCam[1]),
-                          __fadd_rn(pz, -sCam[2]), rgb, cl);
-                p.rgb[3 * (size_t)idx] = rgb[0]; p.rgb[3 * (size_t)idx + 1] = rgb[1]; p.rgb[3 * (size_t)idx + 2] = rgb[2];
-                p.clamped[3 * (size_t)idx] = cl[0]; p.clamped[3 * (size_t)idx + 1] = cl[1]; p.clamped[3 * (size_t)idx + 2] = cl[2];
-            }
-            p.depths[idx] = depth;
-            p.means2D[idx] = pix;
-            p.conic_opacity[idx] = make_float4(conic.x, conic.y, conic.z, __ldg(p.opacities + idx));
+        // Every per-Gaussian output is written for EVERY Gaussian (zeros when culled): a warp then always stores whole
+        // 32 B sectors.  Writing only the visible ~46 % left almost every touched sector partially written, and each
+        // of those costs a DRAM read-modify-write (ncu: 553 -> 448 MB read per launch, 761 -> 670 MB in total).
+        float rgb[3] = {0.f, 0.f, 0.f}; bool cl[3] = {false, false, false};
+        if (alive && p.colors_precomp == nullptr) {
+            const size_t shoff = (size_t)idx * p.M * 3;
+            const bool vec_ok = ((p.M * 3) % 4 == 0) && ((reinterpret_cast<size_t>(p.shs) & 15) == 0);
+            sh_to_rgb(p.D, p.shs + shoff, vec_ok, __fadd_rn(px, -sCam[0]), __fadd_rn(py, -sCam[1]),
+                      __fadd_rn(pz, -sCam[2]), rgb, cl);
+        }
+        if (p.colors_precomp == nullptr) {
+            p.rgb[3 * (size_t)idx] = rgb[0]; p.rgb[3 * (size_t)idx + 1] = rgb[1]; p.rgb[3 * (size_t)idx + 2] = rgb[2];
+            p.clamped[3 * (size_t)idx] = cl[0]; p.clamped[3 * (size_t)idx + 1] = cl[1]; p.clamped[3 * (size_t)idx + 2] = cl[2];
+        }
+        p.depths[idx] = alive ? depth : 0.f;
+        p.means2D[idx] = alive ? pix : make_float2(0.f, 0.f);
+        p.conic_opacity[idx] = alive ? make_float4(conic.x, conic.y, conic.z, __ldg(p.opacities + idx)) : make_float4(0.f, 0.f, 0.f, 0.f);
+        if (!wrote_cov && p.cov3D_precomp == nullptr) {
+#pragma unroll
+            for (int i = 0; i < 6; ++i) p.cov3D[6 * (size_t)idx + i] = 0.f;
         }
         p.radii[idx] = radius;
         p.tiles_touched[idx] = touched;
