@@ -608,11 +608,14 @@ __device__ __forceinline__ bool chunk_lookup(uint32_t c, int tiles_y, const uint
 // per chunk: how many of its runs cover each tile column (difference array + scan)
 __global__ void __launch_bounds__(256) chunk_count_kernel(const uint32_t* __restrict__ rkeys, int tiles_x, int tiles_y,
                                                           const uint32_t* __restrict__ chunk_row_start, const uint32_t* __restrict__ row_start,
-                                                          uint32_t* __restrict__ chunk_counts) {
+                                                          uint32_t* __restrict__ chunk_counts, uint4* __restrict__ chunk_info) {
     extern __shared__ int s_diff[];               // [tiles_x + 1], then reused for the scanned counts
     __shared__ int s_wsum[8];
     ChunkCtx cx;
-    if (!chunk_lookup(blockIdx.x, tiles_y, chunk_row_start, row_start, cx)) return;
+    const bool live = chunk_lookup(blockIdx.x, tiles_y, chunk_row_start, row_start, cx);
+    // the chunk's place, for expand_runs_kernel (one 16-byte load there instead of a second binary search)
+    if (threadIdx.x == 0) chunk_info[blockIdx.x] = live ? make_uint4((uint32_t)cx.row, cx.r0, cx.r1, 1u) : make_uint4(0u, 0u, 0u, 0u);
+    if (!live) return;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     for (int i = tid; i <= tiles_x; i += 256) s_diff[i] = 0;
     __syncthreads();
@@ -689,62 +692,71 @@ __global__ void __launch_bounds__(1024) tile_scan_kernel(uint32_t* __restrict__ 
     }
 }
 
-// per chunk: write every run's Gaussian id into the lists of the tiles it covers, at its exact depth-order rank
+// per chunk: write every run's Gaussian id into the lists of the tiles it covers, at its exact depth-order rank.
+// A chunk's 1024 runs form 32 warp-sized groups in run order; group q owns coverage plane q (bit = lane, word =
+// column).  One pass sets the bits (a run covers 1.7 columns on average: one shared atomic per covered column), one
+// pass per column turns the 32 popcounts into each group's slot base, one pass scatters -- two CTA barriers per chunk.
+// The chunk's place (row, run range) comes from one 16-byte record written by chunk_count_kernel and all runs are
+// loaded up front.  The kernel is bound by the L1/LSU pipe (ncu: 75 %; ~4 shared/global lane operations per pair), not
+// by DRAM (7 %).  Measured dead ends: toggle-and-prefix-XOR coverage, staging the pairs in shared memory for coalesced
+// list writes, flattening wide runs across the warp with a shuffle search -- all between 0.135 and 0.153 ms.
 constexpr int kExpandThreads = 256;
+constexpr int kExpandBatches = kRunChunk / kExpandThreads;       // runs per thread
+constexpr int kExpandPlanes = kRunChunk / 32;
+
 __global__ void __launch_bounds__(kExpandThreads) expand_runs_kernel(const uint32_t* __restrict__ rkeys, const uint32_t* __restrict__ rvals,
-                                                                     int tiles_x, int tiles_y, const uint32_t* __restrict__ chunk_row_start,
-                                                                     const uint32_t* __restrict__ row_start, const uint32_t* __restrict__ chunk_counts,
+                                                                     int tiles_x, const uint4* __restrict__ chunk_info,
+                                                                     const uint32_t* __restrict__ chunk_counts,
                                                                      const uint32_t* __restrict__ tile_start, uint32_t* __restrict__ point_list) {
     extern __shared__ uint32_t s_mem[];
     const int stride = tiles_x + 1;
-    uint32_t* s_base = s_mem;                      // [tiles_x] next free slot of every column's list
-    uint32_t* s_wbase = s_base + tiles_x;          // [8][tiles_x] slot base of (warp, column) in the current batch
-    uint32_t* s_bits = s_wbase + 8 * tiles_x;      // [8][tiles_x + 1] coverage bits: warp-major, bit = lane
-    ChunkCtx cx;
-    if (!chunk_lookup(blockIdx.x, tiles_y, chunk_row_start, row_start, cx)) return;
+    uint32_t* s_base = s_mem;                                           // [tiles_x] first slot of this chunk in every column's list
+    uint32_t* s_bits = s_base + tiles_x;                                // [32][tiles_x + 1] coverage bits
+    unsigned short* s_rel = reinterpret_cast<unsigned short*>(s_bits + kExpandPlanes * stride);   // [32][tiles_x] group base - s_base
+    const uint4 info = __ldg(chunk_info + blockIdx.x);                  // (row, first run, end run, valid)
+    if (info.w == 0u) return;
+    const uint32_t row = info.x, r0 = info.y, r1 = info.z;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    uint32_t keys[kExpandBatches], ids[kExpandBatches];
+#pragma unroll
+    for (int b = 0; b < kExpandBatches; ++b) {
+        const uint32_t r = r0 + b * kExpandThreads + tid;
+        keys[b] = (r < r1) ? __ldg(rkeys + r) : 0u;                     // width field 0: covers nothing
+        ids[b] = (r < r1) ? __ldg(rvals + r) : 0u;
+    }
     for (int x = tid; x < tiles_x; x += kExpandThreads)
-        s_base[x] = __ldg(tile_start + (size_t)cx.row * tiles_x + x) + __ldg(chunk_counts + (size_t)blockIdx.x * tiles_x + x);
+        s_base[x] = __ldg(tile_start + (size_t)row * tiles_x + x) + __ldg(chunk_counts + (size_t)blockIdx.x * tiles_x + x);
+    // a warp clears and fills its own planes (b * 8 + wid): no CTA barrier in between
+#pragma unroll
+    for (int b = 0; b < kExpandBatches; ++b) {
+        uint32_t* plane = s_bits + (b * 8 + wid) * stride;
+        for (int x = lane; x < tiles_x; x += 32) plane[x] = 0;
+    }
+    __syncwarp();
+#pragma unroll
+    for (int b = 0; b < kExpandBatches; ++b) {
+        uint32_t* plane = s_bits + (b * 8 + wid) * stride;
+        const uint32_t x0 = (keys[b] >> kRunX0Shift) & kRunFieldMask, w = keys[b] & kRunFieldMask;
+        for (uint32_t i = 0; i < w; ++i) atomicOr(&plane[x0 + i], 1u << lane);
+    }
+    __syncthreads();
+    for (int x = tid; x < tiles_x; x += kExpandThreads) {
+        uint32_t acc = 0;
+#pragma unroll 8
+        for (int q = 0; q < kExpandPlanes; ++q) { s_rel[q * tiles_x + x] = (unsigned short)acc; acc += __popc(s_bits[q * stride + x]); }
+    }
+    __syncthreads();
     const uint32_t lt = (1u << lane) - 1u;
-    uint32_t* mybits = s_bits + wid * stride;
-    uint32_t* mybase = s_wbase + wid * tiles_x;
-    for (uint32_t b0 = cx.r0; b0 < cx.r1; b0 += kExpandThreads) {
-        const uint32_t r = b0 + tid;
-        uint32_t x0 = 0, w = 0, id = 0;
-        if (r < cx.r1) {
-            const uint32_t key = __ldg(rkeys + r);
-            x0 = (key >> kRunX0Shift) & kRunFieldMask; w = key & kRunFieldMask; id = __ldg(rvals + r);
-        }
-        // coverage of this warp's 32 runs: toggle the run's bit at its first column and one past its last, then a
-        // prefix-XOR along the columns turns the toggles into "run covers column" bits (2 atomics per run, not w)
-        for (int x = lane; x <= tiles_x; x += 32) mybits[x] = 0;
-        __syncwarp();
-        if (w) { atomicXor(&mybits[x0], 1u << lane); atomicXor(&mybits[x0 + w], 1u << lane); }
-        __syncwarp();
-        uint32_t carry = 0;
-        for (int xb = 0; xb < tiles_x; xb += 32) {
-            const int x = xb + lane;
-            uint32_t v = (x < tiles_x) ? mybits[x] : 0u;
 #pragma unroll
-            for (int o = 1; o < 32; o <<= 1) { const uint32_t t = __shfl_up_sync(0xffffffffu, v, o); if (lane >= o) v ^= t; }
-            v ^= carry;
-            if (x < tiles_x) mybits[x] = v;
-            carry = __shfl_sync(0xffffffffu, v, 31);
-        }
-        __syncthreads();
-        for (int x = tid; x < tiles_x; x += kExpandThreads) {
-            uint32_t acc = s_base[x];
-#pragma unroll
-            for (int k = 0; k < 8; ++k) { s_wbase[k * tiles_x + x] = acc; acc += __popc(s_bits[k * stride + x]); }
-            s_base[x] = acc;
-        }
-        __syncthreads();
+    for (int b = 0; b < kExpandBatches; ++b) {
+        const int q = b * 8 + wid;
+        const uint32_t* plane = s_bits + q * stride;
+        const unsigned short* rel = s_rel + q * tiles_x;
+        const uint32_t x0 = (keys[b] >> kRunX0Shift) & kRunFieldMask, w = keys[b] & kRunFieldMask, id = ids[b];
         for (uint32_t i = 0; i < w; ++i) {
             const uint32_t x = x0 + i;
-            point_list[mybase[x] + __popc(mybits[x] & lt)] = id;
+            point_list[s_base[x] + rel[x] + __popc(plane[x] & lt)] = id;
         }
-        // no barrier here: a warp only rewrites its own plane before the next batch's first barrier, and s_wbase / s_base
-        // are rewritten after it
     }
 }
 
@@ -755,18 +767,22 @@ void launch_expand_runs(const BinPtrs& b, const uint32_t* rkeys_sorted, const ui
     {
         ProfScope ps(prof_ranges, s);
         chunk_table_kernel<<<1, 1024, 0, s>>>(rkeys_sorted, (uint32_t)R, tiles_y, row_offsets, b.row_start, b.chunk_row_start);
-        chunk_count_kernel<<<grid, 256, sizeof(int) * (tiles_x + 1), s>>>(rkeys_sorted, tiles_x, tiles_y, b.chunk_row_start, b.row_start, b.chunk_counts);
+        chunk_count_kernel<<<grid, 256, sizeof(int) * (tiles_x + 1), s>>>(rkeys_sorted, tiles_x, tiles_y, b.chunk_row_start, b.row_start, b.chunk_counts, b.chunk_info);
         row_scan_kernel<<<dim3((tiles_x + 31) / 32, tiles_y), 1024, 0, s>>>(tiles_x, b.chunk_row_start, b.chunk_counts, b.tile_start);
         tile_scan_kernel<<<1, 1024, 0, s>>>(b.tile_start, num_tiles, ranges, n_intersections);
         count_launch(4);
     }
     {
         ProfScope ps(prof_expand, s);
-        const size_t smem = sizeof(uint32_t) * ((size_t)tiles_x * (1 + 8) + 8 * (size_t)(tiles_x + 1));
+        // [tiles_x] + 32 planes x [tiles_x + 1] u32 + 32 x [tiles_x] u16: 24 KB at 1080p, 200 KB at the 1023-column limit
+        const size_t smem = sizeof(uint32_t) * ((size_t)tiles_x + kExpandPlanes * (size_t)(tiles_x + 1)) + sizeof(unsigned short) * kExpandPlanes * (size_t)tiles_x;
         static bool attr_done = false;
-        if (!attr_done) { cudaFuncSetAttribute(expand_runs_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 17 * 4 * 1024 + 64); attr_done = true; }
-        expand_runs_kernel<<<grid, kExpandThreads, smem, s>>>(rkeys_sorted, rvals_sorted, tiles_x, tiles_y, b.chunk_row_start, b.row_start,
-                                                              b.chunk_counts, b.tile_start, b.vals);
+        if (!attr_done) {
+            cudaFuncSetAttribute(expand_runs_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)(sizeof(uint32_t) * (1023 + kExpandPlanes * 1024) + sizeof(unsigned short) * kExpandPlanes * 1023));
+            attr_done = true;
+        }
+        expand_runs_kernel<<<grid, kExpandThreads, smem, s>>>(rkeys_sorted, rvals_sorted, tiles_x, b.chunk_info, b.chunk_counts, b.tile_start, b.vals);
         count_launch();
     }
 }

@@ -123,7 +123,7 @@ constexpr int kRunChunk = 1024;          // runs per expansion chunk (a chunk ne
 constexpr int kRunRowShift = 20, kRunX0Shift = 10, kRunFieldMask = 1023, kRunMaxRows = 4095;
 
 struct BinLayout {
-    size_t vals, rkeyA, rkeyB, rkeyC, rvalA, rvalB, sort_temp, row_start, chunk_row_start, chunk_counts, tile_start, total;
+    size_t vals, rkeyA, rkeyB, rkeyC, rvalA, rvalB, sort_temp, row_start, chunk_row_start, chunk_counts, chunk_info, tile_start, total;
     long long max_chunks;
     __host__ __device__ BinLayout(long long N, long long R, int tiles_x, int tiles_y) {
         size_t n = (size_t)(N > 0 ? N : 0), r = (size_t)(R > 0 ? R : 0);
@@ -139,6 +139,7 @@ struct BinLayout {
         row_start = o; o = align_up(o + 4 * (size_t)(tiles_y + 2));
         chunk_row_start = o; o = align_up(o + 4 * (size_t)(tiles_y + 2));
         chunk_counts = o; o = align_up(o + 4 * (size_t)max_chunks * (size_t)tiles_x);
+        chunk_info = o; o = align_up(o + 16 * (size_t)max_chunks);     // (row, first run, end run, valid) per chunk
         tile_start = o; o = align_up(o + 4 * ((size_t)tiles_x * tiles_y + 1));
         total = o;
     }
@@ -146,7 +147,7 @@ struct BinLayout {
 
 struct BinPtrs {
     uint32_t *vals, *rkeyA, *rkeyB, *rkeyC, *rvalA, *rvalB; void* sort_temp; size_t sort_temp_bytes;
-    uint32_t *row_start, *chunk_row_start, *chunk_counts, *tile_start; long long max_chunks;
+    uint32_t *row_start, *chunk_row_start, *chunk_counts, *tile_start; uint4* chunk_info; long long max_chunks;
 };
 
 inline BinPtrs bin_ptrs(const void* buf, long long N, long long R, int tiles_x, int tiles_y) {
@@ -159,6 +160,7 @@ inline BinPtrs bin_ptrs(const void* buf, long long N, long long R, int tiles_x, 
     p.sort_temp = (void*)(b + L.sort_temp); p.sort_temp_bytes = sort_temp_bytes(R > 0 ? R : 0);
     p.row_start = (uint32_t*)(b + L.row_start); p.chunk_row_start = (uint32_t*)(b + L.chunk_row_start);
     p.chunk_counts = (uint32_t*)(b + L.chunk_counts); p.tile_start = (uint32_t*)(b + L.tile_start);
+    p.chunk_info = (uint4*)(b + L.chunk_info);
     p.max_chunks = L.max_chunks;
     return p;
 }
