@@ -444,8 +444,10 @@ def measure(impl, args, d, cams, rank, world, timer, full):
         prof = impl.capi.profile_read()
         out["bwd_stages_ms"] = {k: round(v[0] / max(1, v[1]), 5) for k, v in prof.items() if k.startswith("bwd")}
 
-    # ---- data-parallel training step (config C4 shape): every rank one view fwd+bwd, then the bucketed NCCL all-reduce of
-    # the 59 floats/Gaussian of parameter gradients on a side stream (dist.GradientAllReduce)
+    # ---- data-parallel training step (config C4 shape): every rank one view fwd+bwd, then the gradient exchange.
+    # "dense": bucketed NCCL all-reduce of all 59 floats/Gaussian (dist.GradientAllReduce).  "rank1_sh" (ours only): the
+    # SH gradient travels as its rank-1 factor -- 11 floats all-reduced + 3 floats x world gathered -- and is rebuilt
+    # by gsr_sh_grad_from_views (dist.ShGradExchange); the backward then never writes the [P,16,3] tensor.
     from gaussian_splatting_with_eye_tracking_b200 import dist as gdist
     reducer = gdist.GradientAllReduce()
 
@@ -454,9 +456,28 @@ def measure(impl, args, d, cams, rank, world, timer, full):
         reducer.start(grads)
         reducer.wait()
     ms = timer.run(dp_step, Kb, 2)
+    P_ = d["means3D"].shape[0]
     out["dp_train"] = {"ms_per_step": ms / Kb, "views_per_s": world * Kb / (ms / 1e3),
-                       "allreduce_bytes_per_step": 59 * 4 * d["means3D"].shape[0] if world > 1 else 0,
-                       "bucket_bytes": reducer.bucket_bytes}
+                       "allreduce_bytes_per_step": 59 * 4 * P_ if world > 1 else 0, "bucket_bytes": reducer.bucket_bytes, "exchange": "dense"}
+    if is_ours:
+        exch = gdist.ShGradExchange()
+        e_ = impl.e
+
+        def dp_step_rank1(i):
+            cam = cam_of(i)
+            N, img, radii, gb, bb, ib = impl.forward_c(cam)
+            g = impl.host.rasterize_gaussians_backward(d["bg"], d["means3D"], radii, e_, d["scales"], d["rotations"], 1.0, e_,
+                                                       cam.world_view_transform, cam.full_proj_transform, cam.tanfovx, cam.tanfovy, w,
+                                                       d["shs"], d["sh_degree"], cam.camera_center, gb, N, bb, ib, False, compact_sh=True)
+            exch.start([g[3], g[2], g[6], g[7]], g[5], cam.camera_center)     # means3D, opacity, scales, rotations | clamped dRGB
+            return exch.finish(d["means3D"], d["sh_degree"], d["shs"].shape[1])
+        ms = timer.run(dp_step_rank1, Kb, 2)
+        pb = gdist.ShGradExchange.payload_bytes(P_, world)
+        out["dp_train_rank1_sh"] = {"ms_per_step": ms / Kb, "views_per_s": world * Kb / (ms / 1e3),
+                                    "allreduce_bytes_per_step": pb["allreduce"] if world > 1 else 0,
+                                    "allgather_bytes_in_per_step": pb["allgather_in"] if world > 1 else 0,
+                                    "exchange": "rank-1 SH factor (3 floats/Gaussian/view gathered) + 11 floats all-reduced; "
+                                                "no autograd wrapper (the C-shaped backward is called directly)"}
 
     # ---- screen-tile bands (config C5 shape): ONE foveated frame split over the ranks by rows of 32-px tiles, balanced by the
     # previous frame's per-row pair counts; per-tile counts all-reduced so the AMR levels equal the single-GPU ones
@@ -601,7 +622,7 @@ def main():
                                 "traffic": NCU_TRAFFIC_BYTES.get(args.gaussians), "peak_source": peak_src, "launch_ms": st["preprocess"],
                                 "alg_bytes_per_launch": alg, "visible_per_launch": vis, "culled_per_launch": args.gaussians - vis,
                                 "alg_bytes_per_visible": ALG_BYTES_VISIBLE, "alg_bytes_per_culled": ALG_BYTES_CULLED}
-        extra = {k: m[k] for k in ("num_rendered", "stages_ms", "fwd_bwd_ms_per_view", "bwd_stages_ms", "dp_train", "tile_bands", "amr") if k in m}
+        extra = {k: m[k] for k in ("num_rendered", "stages_ms", "fwd_bwd_ms_per_view", "bwd_stages_ms", "dp_train", "dp_train_rank1_sh", "tile_bands", "amr") if k in m}
         extra["pairs_per_gaussian_mean"] = N / args.gaussians
         extra["visible_mean"] = m.get("mean_visible")
         if full and rank == 0 and eff_world == 1:

@@ -45,7 +45,7 @@ class GsrGaze(C.Structure):
 class GsrGrads(C.Structure):
     _fields_ = [(n, C.c_void_p) for n in (
         "dL_dmeans2D", "dL_dcolors", "dL_dopacity", "dL_dmeans3D", "dL_dcov3D", "dL_dsh", "dL_dscales",
-        "dL_drotations", "dL_dconic", "scratch")]
+        "dL_drotations", "dL_dconic", "scratch", "dL_dcolors_clamped")]
 
 
 class GsrGeomView(C.Structure):
@@ -75,6 +75,7 @@ SYMBOLS = {
     "gsr_backward": (C.c_int, [C.POINTER(GsrScene), C.POINTER(GsrCamera), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                C.c_int, C.c_void_p, C.POINTER(GsrGrads), C.c_int, C.c_void_p]),
     "gsr_mark_visible": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "gsr_sh_grad_from_views": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "gsr_amr_forward": (C.c_int, [C.POINTER(GsrScene), C.POINTER(GsrCamera), C.c_int, C.c_void_p, C.c_void_p, C.c_void_p,
                                   C.c_void_p, C.c_int, C.POINTER(GsrGaze), ALLOC_FN, C.c_void_p, C.c_void_p, C.c_void_p,
                                   c_int_p, C.c_int, C.c_void_p]),

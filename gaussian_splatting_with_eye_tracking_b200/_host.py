@@ -155,7 +155,10 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
 
 def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rotations, scale_modifier, cov3D_precomp,
                                  viewmatrix, projmatrix, tan_fovx, tan_fovy, dL_dout_color, sh, degree, campos,
-                                 geomBuffer, R, binningBuffer, imageBuffer, debug, band=None):
+                                 geomBuffer, R, binningBuffer, imageBuffer, debug, band=None, compact_sh=False):
+    """``compact_sh=True`` (extension, view-parallel training): slot 5 of the returned tuple is the [P,3] colour
+    gradient after the SH clamp mask instead of the [P,M,3] SH gradient, which is then not written at all;
+    ``sh_grad_from_views`` rebuilds the SH gradient summed over views from those."""
     H, W = int(dL_dout_color.size(1)), int(dL_dout_color.size(2))
     sc, cam, keep, P, M = _scene_camera(background, means3D, colors, torch.empty(0), scales, rotations, scale_modifier,
                                         cov3D_precomp, viewmatrix, projmatrix, tan_fovx, tan_fovy, H, W, sh, degree,
@@ -169,7 +172,8 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
         dL_dconic = torch.empty((P, 2, 2), **f32)
         dL_dopacity = torch.empty((P, 1), **f32)
         dL_dcov3D = torch.empty((P, 6), **f32)
-        dL_dsh = torch.empty((P, M, 3), **f32)
+        compact = bool(compact_sh) and M > 0
+        dL_dsh = torch.empty((P, 3), **f32) if compact else torch.empty((P, M, 3), **f32)
         dL_dscales = torch.empty((P, 3), **f32)
         dL_drotations = torch.empty((P, 4), **f32)
         if P != 0:
@@ -177,14 +181,31 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
             dpix = _dev_tensor(dL_dout_color, "dL_dout_color")
             radii_t = _dev_tensor(radii, "radii", torch.int32)
             grads = GsrGrads(dL_dmeans2D=_p(dL_dmeans2D), dL_dcolors=_p(dL_dcolors), dL_dopacity=_p(dL_dopacity),
-                             dL_dmeans3D=_p(dL_dmeans3D), dL_dcov3D=_p(dL_dcov3D), dL_dsh=_p(dL_dsh) if M else None,
+                             dL_dmeans3D=_p(dL_dmeans3D), dL_dcov3D=_p(dL_dcov3D),
+                             dL_dsh=_p(dL_dsh) if (M and not compact) else None,
                              dL_dscales=_p(dL_dscales), dL_drotations=_p(dL_drotations), dL_dconic=_p(dL_dconic),
-                             scratch=_p(scratch))
+                             scratch=_p(scratch), dL_dcolors_clamped=_p(dL_dsh) if compact else None)
             rc = lib.gsr_backward(C.byref(sc), C.byref(cam), _p(radii_t), _p(geomBuffer.contiguous()),
                                   _p(binningBuffer.contiguous()), _p(imageBuffer.contiguous()), int(R), _p(dpix),
                                   C.byref(grads), 1 if debug else 0, _stream())
             _capi.check(rc, "gsr_backward")
     return (dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations)
+
+
+def sh_grad_from_views(means3D, cam_positions, dL_dcolors_clamped, degree, M):
+    """SH gradient summed over views from the per-view clamped colour gradients (gsr_sh_grad_from_views).
+    cam_positions [K,3], dL_dcolors_clamped [K,P,3] -> dL_dsh [P,M,3]."""
+    P, K = int(means3D.size(0)), int(cam_positions.size(0))
+    m = _dev_tensor(means3D, "means3D")
+    cams = _dev_tensor(cam_positions, "cam_positions")
+    g = _dev_tensor(dL_dcolors_clamped, "dL_dcolors_clamped")
+    if tuple(g.shape) != (K, P, 3):
+        raise RuntimeError(f"dL_dcolors_clamped must have dimensions ({K}, {P}, 3)")
+    with torch.cuda.device(m.device):
+        out = torch.empty((P, int(M), 3), dtype=torch.float32, device=m.device)
+        rc = lib.gsr_sh_grad_from_views(P, int(degree), int(M), _p(m), K, _p(cams), _p(g), _p(out), _stream())
+        _capi.check(rc, "gsr_sh_grad_from_views")
+    return out
 
 
 def mark_visible(means3D, viewmatrix, projmatrix):

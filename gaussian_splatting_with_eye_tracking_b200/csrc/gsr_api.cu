@@ -322,7 +322,7 @@ int gsr_backward(const gsr_scene* sc, const gsr_camera* cam, const int* radii, c
     if (P == 0) return GSR_OK;
     if (!geom_buffer || !binning_buffer || !image_buffer) { set_error("work buffers are required"); return GSR_ERR_WORKSPACE; }
     if (!gr->dL_dmeans2D || !gr->dL_dcolors || !gr->dL_dopacity || !gr->dL_dmeans3D || !gr->dL_dcov3D || !gr->dL_dscales ||
-        !gr->dL_drotations || !gr->scratch || (sc->sh_coeffs > 0 && sc->shs && !gr->dL_dsh)) {
+        !gr->dL_drotations || !gr->scratch || (sc->sh_coeffs > 0 && sc->shs && !gr->dL_dsh && !gr->dL_dcolors_clamped)) {
         set_error("gradient output pointers are required"); return GSR_ERR_INVALID;
     }
     if (((size_t)gr->scratch & 15) != 0) { set_error("scratch must be 16-byte aligned"); return GSR_ERR_INVALID; }
@@ -446,6 +446,15 @@ int gsr_amr_render_prebuilt(const gsr_scene* sc, const gsr_camera* cam, const vo
     ab.interpolate = interpolate_image != 0;
     { ProfScope ps(GSR_PROF_AMR_BLEND, s); launch_blend_amr(ab, s); }
     return check_last("blend amr (prebuilt)", debug != 0, s);
+}
+
+int gsr_sh_grad_from_views(int P, int sh_degree, int sh_coeffs, const float* means3D, int num_views,
+                           const float* cam_positions, const float* dL_dcolors_clamped, float* dL_dsh, void* stream) {
+    if (P < 0 || num_views < 0 || sh_degree < 0 || sh_degree > 3) { set_error("sh_grad_from_views: bad sizes"); return GSR_ERR_INVALID; }
+    if (P > 0 && (!means3D || !dL_dsh || (num_views > 0 && (!cam_positions || !dL_dcolors_clamped)))) { set_error("sh_grad_from_views: null pointer"); return GSR_ERR_INVALID; }
+    int rc = launch_sh_grad_from_views(P, sh_degree, sh_coeffs, means3D, num_views, cam_positions, dL_dcolors_clamped, dL_dsh, (cudaStream_t)stream);
+    if (rc) return rc;
+    return check_last("sh_grad_from_views", false, (cudaStream_t)stream);
 }
 
 int gsr_view_geom(const void* geom_buffer, int P, gsr_geom_view* out) {

@@ -431,6 +431,7 @@ struct PreBwdParams {
     const int* __restrict__ radii; const unsigned char* __restrict__ clamped;
     const float* __restrict__ scratch;
     float *dL_dmeans2D, *dL_dcolors, *dL_dopacity, *dL_dmeans3D, *dL_dcov3D, *dL_dsh, *dL_dscales, *dL_drot, *dL_dconic;
+    float* dL_drgb_clamped;        // optional [P,3]; with dL_dsh == nullptr the SH rows are not written (gsr_grads)
 };
 
 // SH rows are staged through shared memory (STAGED): a thread's 3M coefficients / gradients are 192 B apart from its
@@ -541,11 +542,15 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreBwdParams 
     }
 
     // ---------------- SH (backward.cu:20-139)
-    if (p.dL_dsh != nullptr) {
+    const bool sh_rows = p.dL_dsh != nullptr;                 // false: only the clamped colour gradient leaves
+    if (p.dL_drgb_clamped != nullptr && valid && !(visible && p.colors_from_sh)) {
+        p.dL_drgb_clamped[i3] = 0.f; p.dL_drgb_clamped[i3 + 1] = 0.f; p.dL_drgb_clamped[i3 + 2] = 0.f;
+    }
+    if (sh_rows || p.colors_from_sh) {
         const int L = 3 * p.M;
         const int warp_idx0 = blockIdx.x * 256 + wid * 32;
         float* wbase = s_sh + wid * 32 * kShStride;
-        float* out = STAGED ? (wbase + lane * kShStride) : (p.dL_dsh + (size_t)idx * L);
+        float* out = STAGED ? (wbase + lane * kShStride) : (sh_rows ? p.dL_dsh + (size_t)idx * L : nullptr);
         const int ncoef = (p.D + 1) * (p.D + 1);
         const int f4_per_row = L >> 2;
         if (STAGED) {
@@ -571,6 +576,7 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreBwdParams 
             const float x = ox * inv_len, y = oy * inv_len, z = oz * inv_len;
             float g[3] = {sB.z, sB.w, sC.x};
             g[0] *= p.clamped[i3] ? 0.f : 1.f; g[1] *= p.clamped[i3 + 1] ? 0.f : 1.f; g[2] *= p.clamped[i3 + 2] ? 0.f : 1.f;
+            if (p.dL_drgb_clamped != nullptr) { p.dL_drgb_clamped[i3] = g[0]; p.dL_drgb_clamped[i3 + 1] = g[1]; p.dL_drgb_clamped[i3 + 2] = g[2]; }
             float w[16];                       // dRGB/dsh_k (same for the three channels)
             float dx_[3] = {0, 0, 0}, dy_[3] = {0, 0, 0}, dz_[3] = {0, 0, 0};   // dRGB/d(dir)
             w[0] = kSH_C0;
@@ -610,9 +616,11 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreBwdParams 
                     }
                 }
             }
-            for (int k = 0; k < p.M; ++k) {
-                const float wk = (k < ncoef && k < 16) ? w[k] : 0.f;
-                out[3 * k] = wk * g[0]; out[3 * k + 1] = wk * g[1]; out[3 * k + 2] = wk * g[2];
+            if (sh_rows) {
+                for (int k = 0; k < p.M; ++k) {
+                    const float wk = (k < ncoef && k < 16) ? w[k] : 0.f;
+                    out[3 * k] = wk * g[0]; out[3 * k + 1] = wk * g[1]; out[3 * k + 2] = wk * g[2];
+                }
             }
             // direction gradient -> mean, through the normalisation (dnormvdv, auxiliary.h:107-118)
             const float ddx = dx_[0] * g[0] + dx_[1] * g[1] + dx_[2] * g[2];
@@ -623,10 +631,10 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreBwdParams 
             dmx += ((sum2 - ox * ox) * ddx - oy * ox * ddy - oz * ox * ddz) * invsum32;
             dmy += (-ox * oy * ddx + (sum2 - oy * oy) * ddy - oz * oy * ddz) * invsum32;
             dmz += (-ox * oz * ddx - oy * oz * ddy + (sum2 - oz * oz) * ddz) * invsum32;
-        } else if (STAGED || valid) {
+        } else if (sh_rows && (STAGED || valid)) {
             for (int k = 0; k < L; ++k) out[k] = 0.f;
         }
-        if (STAGED) {
+        if (STAGED && sh_rows) {
             __syncwarp();
             const int nrows = min(32, p.P - warp_idx0);
             const int total4 = nrows * f4_per_row;
@@ -695,8 +703,9 @@ void launch_preprocess_backward(const PreBwdArgs& a, cudaStream_t s) {
     p.dL_dmeans2D = a.out.dL_dmeans2D; p.dL_dcolors = a.out.dL_dcolors; p.dL_dopacity = a.out.dL_dopacity;
     p.dL_dmeans3D = a.out.dL_dmeans3D; p.dL_dcov3D = a.out.dL_dcov3D; p.dL_dsh = a.out.dL_dsh;
     p.dL_dscales = a.out.dL_dscales; p.dL_drot = a.out.dL_drotations; p.dL_dconic = a.out.dL_dconic;
+    p.dL_drgb_clamped = a.out.dL_dcolors_clamped;
     // staged SH path: needs M % 4 == 0 (128-bit rows), M <= 16 (row fits the staged stride) and 16 B-aligned tensors
-    const bool staged = p.dL_dsh != nullptr && p.M > 0 && p.M <= 16 && (p.M % 4) == 0 && ((size_t)p.dL_dsh & 15) == 0 &&
+    const bool staged = (p.dL_dsh != nullptr || p.colors_from_sh) && p.M > 0 && p.M <= 16 && (p.M % 4) == 0 && ((size_t)p.dL_dsh & 15) == 0 &&
                         (!p.colors_from_sh || ((size_t)p.shs & 15) == 0);
     if (staged) {
         const int smem = 256 * kShStride * (int)sizeof(float);
@@ -707,6 +716,93 @@ void launch_preprocess_backward(const PreBwdArgs& a, cudaStream_t s) {
         preprocess_bwd_kernel<false><<<(a.P + 255) / 256, 256, 0, s>>>(p);
     }
     count_launch();
+}
+
+// ------------------------------------------------------------------------------------------------
+// data-parallel helper: dL_dsh summed over views from the per-view clamped colour gradients (gsr_sh_grad_from_views).
+// Per view the SH gradient of a Gaussian is rank 1: dL_dsh[k][c] = basis_k(dir) * g[c]  (backward.cu:20-139; the same
+// w[] as preprocess_bwd_kernel).  Exchanging g (3 floats) instead of the row (3M floats) cuts the gradient payload of a
+// view-parallel step from 59 to 14 floats per Gaussian; this kernel rebuilds the sum.  Rows leave through shared
+// memory as whole 6 KB warp segments (same staging as the backward).
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) sh_grad_from_views_kernel(int P, int D, int M, const float* __restrict__ means3D, int K,
+                                                                 const float* __restrict__ cams, const float* __restrict__ g_all,
+                                                                 float* __restrict__ dL_dsh) {
+    extern __shared__ float s_rows[];            // [256][kShStride]
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int idx = blockIdx.x * 256 + tid;
+    const bool valid = idx < P;
+    const int ncoef = min(16, min(M, (D + 1) * (D + 1)));
+    float acc[48];
+#pragma unroll
+    for (int i = 0; i < 48; ++i) acc[i] = 0.f;
+    if (valid) {
+        const float mx = __ldg(means3D + 3 * (size_t)idx), my = __ldg(means3D + 3 * (size_t)idx + 1), mz = __ldg(means3D + 3 * (size_t)idx + 2);
+        for (int v = 0; v < K; ++v) {
+            const float* g = g_all + ((size_t)v * P + idx) * 3;
+            const float g0 = __ldg(g), g1 = __ldg(g + 1), g2 = __ldg(g + 2);
+            if (g0 == 0.f && g1 == 0.f && g2 == 0.f) continue;          // culled or fully clamped in this view
+            const float ox = mx - __ldg(cams + 3 * v), oy = my - __ldg(cams + 3 * v + 1), oz = mz - __ldg(cams + 3 * v + 2);
+            const float inv_len = 1.f / sqrtf(ox * ox + oy * oy + oz * oz);
+            const float x = ox * inv_len, y = oy * inv_len, z = oz * inv_len;
+            float w[16];
+            w[0] = kSH_C0;
+#pragma unroll
+            for (int k = 1; k < 16; ++k) w[k] = 0.f;
+            if (D > 0) {
+                w[1] = -kSH_C1 * y; w[2] = kSH_C1 * z; w[3] = -kSH_C1 * x;
+                if (D > 1) {
+                    const float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
+                    w[4] = kSH_C2_0 * xy; w[5] = kSH_C2_1 * yz; w[6] = kSH_C2_2 * (2.f * zz - xx - yy);
+                    w[7] = kSH_C2_3 * xz; w[8] = kSH_C2_4 * (xx - yy);
+                    if (D > 2) {
+                        w[9] = kSH_C3_0 * y * (3.f * xx - yy);
+                        w[10] = kSH_C3_1 * xy * z;
+                        w[11] = kSH_C3_2 * y * (4.f * zz - xx - yy);
+                        w[12] = kSH_C3_3 * z * (2.f * zz - 3.f * xx - 3.f * yy);
+                        w[13] = kSH_C3_4 * x * (4.f * zz - xx - yy);
+                        w[14] = kSH_C3_5 * z * (xx - yy);
+                        w[15] = kSH_C3_6 * x * (xx - 3.f * yy);
+                    }
+                }
+            }
+#pragma unroll
+            for (int k = 0; k < 16; ++k) {
+                const float wk = k < ncoef ? w[k] : 0.f;
+                // product first, then the sum over views: one view reproduces preprocess_bwd_kernel's rows bit for bit
+                acc[3 * k] += wk * g0; acc[3 * k + 1] += wk * g1; acc[3 * k + 2] += wk * g2;
+            }
+        }
+    }
+    const int L = 3 * M;
+    float* row = s_rows + tid * kShStride;
+#pragma unroll
+    for (int i = 0; i < 48; ++i) if (i < L) row[i] = acc[i];
+    __syncwarp();
+    const int warp_idx0 = blockIdx.x * 256 + wid * 32;
+    const int nrows = min(32, P - warp_idx0);
+    if (nrows <= 0) return;
+    const int f4_per_row = L >> 2;
+    const float* wbase = s_rows + wid * 32 * kShStride;
+    float4* gout = reinterpret_cast<float4*>(dL_dsh + (size_t)warp_idx0 * L);
+    for (int e = lane; e < nrows * f4_per_row; e += 32) {
+        const int r = e / f4_per_row, c = (e - r * f4_per_row) * 4;
+        const float* src = wbase + r * kShStride + c;
+        gout[e] = make_float4(src[0], src[1], src[2], src[3]);
+    }
+}
+
+int launch_sh_grad_from_views(int P, int D, int M, const float* means3D, int K, const float* cams, const float* g_all, float* dL_dsh, cudaStream_t s) {
+    if (P <= 0) return GSR_OK;
+    if (M <= 0 || M > 16 || (M % 4) != 0 || ((size_t)dL_dsh & 15) != 0) {
+        set_error("sh_grad_from_views: needs 0 < M <= 16, M %% 4 == 0 and a 16-byte aligned output (M=%d)", M); return GSR_ERR_INVALID;
+    }
+    const int smem = 256 * kShStride * (int)sizeof(float);
+    static bool attr_done = false;
+    if (!attr_done) { cudaFuncSetAttribute(sh_grad_from_views_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem); attr_done = true; }
+    sh_grad_from_views_kernel<<<(P + 255) / 256, 256, smem, s>>>(P, D, M, means3D, K, cams, g_all, dL_dsh);
+    count_launch();
+    return GSR_OK;
 }
 
 }  // namespace gsr

@@ -134,6 +134,73 @@ class GradientAllReduce:
         self.wait()
 
 
+class ShGradExchange:
+    """View-parallel gradient exchange with the SH gradient sent as its rank-1 factor.
+
+    Per view, dL/dsh of a Gaussian is basis(direction)[M] x g[3] with g = the colour gradient after the SH clamp mask
+    (backward.cu:20-139), and the direction depends only on the Gaussian's mean and the view's camera position, which
+    every rank has.  So instead of all-reducing the [P,M,3] tensor (48 of the 59 gradient floats per Gaussian), the
+    ranks all-gather g ([P,3]) and their camera positions and each rebuilds the SUMMED SH gradient locally
+    (``rebuild`` = _host.sh_grad_from_views on the GPU; injectable for the CPU protocol tests).  The remaining
+    gradients (means3D, opacity, scales, rotations: 11 floats) go through the bucketed all-reduce.  Payload per rank
+    and Gaussian: 11 floats all-reduced + 3 floats x world gathered, against 59 floats all-reduced.
+    The sum runs over ranks in rank order on every rank, so the SH gradient is bit-identical everywhere.
+    """
+
+    def __init__(self, rebuild=None, bucket_bytes: int = DEFAULT_BUCKET_BYTES, group=None):
+        self.group = group
+        self.reducer = GradientAllReduce(bucket_bytes, group)
+        self._rebuild = rebuild
+        self._gathered = None
+        self._cams = None
+        self._work = []
+        self._stream = None
+
+    def start(self, dense_grads: Sequence[torch.Tensor], dL_dcolors_clamped: torch.Tensor, campos: torch.Tensor) -> None:
+        """dense_grads: the tensors to SUM in place (means3D, opacity, scales, rotations gradients);
+        dL_dcolors_clamped [P,3] and campos [3] of THIS rank's view."""
+        w = world_size()
+        P = dL_dcolors_clamped.shape[0]
+        dev = dL_dcolors_clamped.device
+        if self._gathered is None or self._gathered.shape != (w, P, 3) or self._gathered.device != dev:
+            self._gathered = torch.empty((w, P, 3), dtype=dL_dcolors_clamped.dtype, device=dev)
+            self._cams = torch.empty((w, 3), dtype=campos.dtype, device=dev)
+        if w == 1:
+            self._gathered[0].copy_(dL_dcolors_clamped); self._cams[0].copy_(campos.reshape(3))
+            return
+        comm = None
+        if dev.type == "cuda":
+            if self._stream is None:
+                self._stream = torch.cuda.Stream(device=dev)
+            comm = self._stream
+            comm.wait_stream(torch.cuda.current_stream(dev))
+        with (torch.cuda.stream(comm) if comm is not None else _null()):
+            self._work = [
+                dist.all_gather_into_tensor(self._gathered.view(-1), dL_dcolors_clamped.contiguous().view(-1), group=self.group, async_op=True),
+                dist.all_gather_into_tensor(self._cams.view(-1), campos.contiguous().view(-1), group=self.group, async_op=True)]
+            if comm is not None:
+                dL_dcolors_clamped.record_stream(comm); campos.record_stream(comm)
+        self.reducer.start(dense_grads)
+
+    def finish(self, means3D: torch.Tensor, degree: int, M: int) -> torch.Tensor:
+        """Wait for the exchange; returns the SH gradient [P,M,3] summed over all views."""
+        for wk in self._work:
+            wk.wait()
+        if self._stream is not None and self._work:
+            torch.cuda.current_stream().wait_stream(self._stream)
+        self._work = []
+        self.reducer.wait()
+        rebuild = self._rebuild
+        if rebuild is None:
+            from . import _host
+            rebuild = _host.sh_grad_from_views
+        return rebuild(means3D, self._cams, self._gathered, degree, M)
+
+    @staticmethod
+    def payload_bytes(P: int, world: int, itemsize: int = 4) -> dict:
+        return {"allreduce": 11 * itemsize * P, "allgather_in": 3 * itemsize * P * world, "dense_allreduce_equivalent": 59 * itemsize * P}
+
+
 class _null:
     def __enter__(self):
         return self

@@ -112,6 +112,11 @@ typedef struct gsr_grads {
     float* dL_drotations; /* [P,4]                          */
     float* dL_dconic;     /* [P,4] scratch (reference: internal dL_dconic, rasterize_points.cu:154) */
     float* scratch;       /* [P,12] floats, packed blend-gradient accumulator; must be 16B aligned   */
+    float* dL_dcolors_clamped; /* optional [P,3]: dL_dcolors after the SH clamp mask (backward.cu:56-58), i.e. the vector
+                                  that multiplies the SH basis; zero rows for culled Gaussians.  When it is given and
+                                  dL_dsh is NULL, the [P,M,3] SH gradient is not written at all: data-parallel training
+                                  exchanges these 3 floats per Gaussian and view and rebuilds the summed SH gradient with
+                                  gsr_sh_grad_from_views (the per-view SH gradient is the rank-1 product basis x this). */
 } gsr_grads;
 
 /* ---- sizes of the three work buffers (bytes, including alignment slack) ---- */
@@ -223,6 +228,14 @@ GSR_API void gsr_profile_enable(int on);
 /* waits for the recorded intervals, ADDS their milliseconds into ms[slot] and their number into counts[slot]
  * (both [GSR_PROF_SLOTS], caller-zeroed), then forgets them.  Returns GSR_OK or GSR_ERR_CUDA. */
 GSR_API int gsr_profile_read(float* ms, int* counts);
+
+/* ---- data-parallel helper: summed SH gradient of `num_views` views from their clamped colour gradients ----
+ * dL_dsh[g][k][c] = sum_v basis_k(normalize(means3D[g] - cam_positions[v])) * dL_dcolors_clamped[v][g][c]
+ * (computeColorFromSH backward, backward.cu:20-139: every coefficient's gradient is its basis value times dL_dRGB).
+ * Views are summed in index order, so every rank that holds the same gathered inputs gets bit-identical sums.
+ * cam_positions [num_views,3], dL_dcolors_clamped [num_views,P,3], dL_dsh [P,sh_coeffs,3] (16-byte aligned), all device. */
+GSR_API int gsr_sh_grad_from_views(int P, int sh_degree, int sh_coeffs, const float* means3D, int num_views,
+                                   const float* cam_positions, const float* dL_dcolors_clamped, float* dL_dsh, void* stream);
 
 /* ---- tuning knobs (results never depend on them) ---- */
 enum { GSR_OPT_SORT_VARIANT = 0,  /* onesweep tile shape for u32 keys: 0 = default, 1..5 see gsr_binning.cu */

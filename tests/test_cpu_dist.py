@@ -108,6 +108,60 @@ def body_band_render_protocol(rank, world):
 
 
 # ---- tests ---------------------------------------------------------------------------------------------------------
+
+def _sh_basis(dirs):
+    """[P,16] real SH basis values with the reference's signs (backward.cu:20-139 / utils/sh_utils.py:57-112)."""
+    import torch_ref as tr
+    x, y, z = dirs[:, 0], dirs[:, 1], dirs[:, 2]
+    xx, yy, zz, xy, yz, xz = x * x, y * y, z * z, x * y, y * z, x * z
+    return torch.stack([
+        torch.full_like(x, tr.C0), -tr.C1 * y, tr.C1 * z, -tr.C1 * x,
+        tr.C2[0] * xy, tr.C2[1] * yz, tr.C2[2] * (2 * zz - xx - yy), tr.C2[3] * xz, tr.C2[4] * (xx - yy),
+        tr.C3[0] * y * (3 * xx - yy), tr.C3[1] * xy * z, tr.C3[2] * y * (4 * zz - xx - yy), tr.C3[3] * z * (2 * zz - 3 * xx - 3 * yy),
+        tr.C3[4] * x * (4 * zz - xx - yy), tr.C3[5] * z * (xx - yy), tr.C3[6] * x * (xx - 3 * yy)], dim=1)
+
+
+def _rebuild_ref(means3D, cams, g_all, degree, M):
+    """torch restatement of gsr_sh_grad_from_views (test double for the CUDA kernel in the CPU protocol test)."""
+    out = torch.zeros(means3D.shape[0], M, 3, dtype=means3D.dtype)
+    ncoef = min(M, (degree + 1) ** 2)
+    for v in range(cams.shape[0]):
+        d = means3D - cams[v]
+        d = d / d.norm(dim=1, keepdim=True)
+        out[:, :ncoef] += _sh_basis(d)[:, :ncoef, None] * g_all[v][:, None, :]
+    return out
+
+
+def body_sh_grad_exchange(rank, world):
+    P, M, deg = 700, 16, 3
+    gen = torch.Generator().manual_seed(7)
+    means = torch.randn(P, 3, generator=gen)
+
+    def view(r):
+        g = torch.Generator().manual_seed(200 + r)
+        cam = torch.randn(3, generator=g) * 4
+        drgb = torch.randn(P, 3, generator=g)
+        drgb[torch.rand(P, generator=g) < 0.5] = 0          # culled in this view
+        dense = [torch.randn(P, 3, generator=g), torch.randn(P, 1, generator=g), torch.randn(P, 3, generator=g), torch.randn(P, 4, generator=g)]
+        return cam, drgb, dense
+    cam, drgb, dense = view(rank)
+    ex = gdist.ShGradExchange(rebuild=_rebuild_ref, bucket_bytes=4096)
+    ex.start(dense, drgb, cam)
+    dsh = ex.finish(means, deg, M)
+    # what a dense all-reduce of per-view SH gradients would have produced
+    want_sh = sum(_rebuild_ref(means, view(r)[0][None], view(r)[1][None], deg, M) for r in range(world))
+    assert torch.allclose(dsh, want_sh, rtol=1e-5, atol=1e-6)
+    for i in range(4):
+        want = sum(view(r)[2][i] for r in range(world))
+        assert torch.allclose(dense[i], want, rtol=1e-6, atol=1e-6), i
+    # every rank ends with the same bits (fixed summation order)
+    mine = dsh.clone()
+    dist.broadcast(dsh, src=0)
+    assert torch.equal(mine, dsh)
+    pb = gdist.ShGradExchange.payload_bytes(P, world)
+    assert pb["allreduce"] + pb["allgather_in"] < pb["dense_allreduce_equivalent"]
+
+
 def test_gradient_allreduce_gloo_world2():
     _run("body_gradient_allreduce")
 
@@ -162,3 +216,11 @@ def test_single_process_paths_are_noops():
     f = torch.rand(3, 8, 8)
     assert gdist.gather_bands(f, [(0, 1)], 32) is f
     assert gdist.view_of_rank(8, 3, 1, 4) == 5
+
+
+def test_sh_grad_exchange_world2():
+    _run("body_sh_grad_exchange", 2)
+
+
+def test_sh_grad_exchange_world3():
+    _run("body_sh_grad_exchange", 3)

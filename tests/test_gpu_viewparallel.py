@@ -1,0 +1,65 @@
+"""View-parallel gradient exchange: the SH gradient leaves the backward as its rank-1 factor
+(the clamped colour gradient, 3 floats per Gaussian) and gsr_sh_grad_from_views rebuilds the summed [P,M,3] tensor.
+Checked against the dense SH gradient of the ordinary backward, through the C ABI."""
+import pytest
+import torch
+
+import common
+
+pytestmark = pytest.mark.gpu
+
+
+def _close(a, b, what):
+    """1e-3 relative with the float-atomics floor of the parity tests (blend-stage sums reorder between runs)."""
+    viol, mx = common.grad_close(common.A(a).reshape(common.A(b).shape), common.A(b), common.GRAD_RTOL, common.GRAD_FLOOR_REF)
+    assert viol <= 0, f"{what}: mismatch beyond 1e-3 relative (max abs diff {mx})"
+
+
+def _backward(sc, cam, dpix, compact):
+    from gaussian_splatting_with_eye_tracking_b200 import _host
+    d, camd = common.cuda_inputs(sc, cam)
+    N, color, radii, geom, binning, img = _host.rasterize_gaussians(*common.fwd_args(d, camd), False)
+    g = _host.rasterize_gaussians_backward(
+        d["bg"], d["means3D"], radii, d["colors_precomp"], d["scales"], d["rotations"], 1.0, d["cov3D_precomp"],
+        camd.world_view_transform, camd.full_proj_transform, cam.tanfovx, cam.tanfovy, dpix.cuda(), d["shs"],
+        d["sh_degree"], camd.camera_center, geom, N, binning, img, False, compact_sh=compact)
+    return d, camd, g
+
+
+@pytest.mark.parametrize("case", ["small", "deg1", "inside"])
+def test_compact_backward_plus_rebuild_equals_dense_sh_gradient(case):
+    from gaussian_splatting_with_eye_tracking_b200 import _host
+    sc, cam = common.make_case(case)
+    dpix = common.upstream_gradient(cam)
+    d, camd, dense = _backward(sc, cam, dpix, False)
+    _, _, comp = _backward(sc, cam, dpix, True)
+    P, M = d["shs"].shape[0], d["shs"].shape[1]
+    assert tuple(comp[5].shape) == (P, 3) and tuple(dense[5].shape) == (P, M, 3)
+    # every other gradient is untouched by the mode (blend atomics reorder: same tolerance as the parity tests)
+    for i in (0, 1, 2, 3, 4, 6, 7):
+        _close(comp[i], dense[i], f"grad[{i}]")
+    rebuilt = _host.sh_grad_from_views(d["means3D"], camd.camera_center.reshape(1, 3), comp[5].reshape(1, P, 3), d["sh_degree"], M)
+    torch.cuda.synchronize()
+    _close(rebuilt, dense[5], "dL_dsh rebuilt from one view")
+    # rows of culled Gaussians are exactly zero in both
+    culled = (comp[5].abs().sum(1) == 0)
+    assert bool((rebuilt[culled] == 0).all())
+
+
+def test_rebuild_sums_views_in_order():
+    from gaussian_splatting_with_eye_tracking_b200 import _host, scenes
+    sc, cam0 = common.make_case("small")
+    cam1 = scenes.look_at_camera((-1.2, 0.5, -3.0), (0, 0, 0), cam0.image_width, cam0.image_height, 0.9)
+    gs, cams, dense = [], [], None
+    for cam in (cam0, cam1):
+        dpix = common.upstream_gradient(cam)
+        d, camd, g_dense = _backward(sc, cam, dpix, False)
+        _, _, g_comp = _backward(sc, cam, dpix, True)
+        gs.append(g_comp[5]); cams.append(camd.camera_center.reshape(3))
+        dense = g_dense[5] if dense is None else dense + g_dense[5]
+    P, M = d["shs"].shape[0], d["shs"].shape[1]
+    both = _host.sh_grad_from_views(d["means3D"], torch.stack(cams), torch.stack(gs), d["sh_degree"], M)
+    _close(both, dense, "dL_dsh summed over two views")
+    # bit-identical on repeat (fixed summation order): what makes the result equal on every rank
+    again = _host.sh_grad_from_views(d["means3D"], torch.stack(cams), torch.stack(gs), d["sh_degree"], M)
+    assert torch.equal(both, again)
