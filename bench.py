@@ -466,11 +466,16 @@ def measure(impl, args, d, cams, rank, world, timer, full):
         def dp_step_rank1(i):
             cam = cam_of(i)
             N, img, radii, gb, bb, ib = impl.forward_c(cam)
-            g = impl.host.rasterize_gaussians_backward(d["bg"], d["means3D"], radii, e_, d["scales"], d["rotations"], 1.0, e_,
-                                                       cam.world_view_transform, cam.full_proj_transform, cam.tanfovx, cam.tanfovy, w,
-                                                       d["shs"], d["sh_degree"], cam.camera_center, gb, N, bb, ib, False, compact_sh=True)
-            exch.start([g[3], g[2], g[6], g[7]], g[5], cam.camera_center)     # means3D, opacity, scales, rotations | clamped dRGB
-            return exch.finish(d["means3D"], d["sh_degree"], d["shs"].shape[1])
+            M_ = d["shs"].shape[1]
+            # the all-gather of the clamped colour gradient + the SH rebuild start between the two backward phases and
+            # overlap the preprocess-stage backward; the 11-float all-reduce follows it
+            g = impl.host.rasterize_gaussians_backward(
+                d["bg"], d["means3D"], radii, e_, d["scales"], d["rotations"], 1.0, e_, cam.world_view_transform,
+                cam.full_proj_transform, cam.tanfovx, cam.tanfovy, w, d["shs"], d["sh_degree"], cam.camera_center, gb, N, bb, ib,
+                False, compact_sh=True,
+                between_phases=lambda drgb: exch.start_gather(drgb, cam.camera_center, d["means3D"], d["sh_degree"], M_))
+            exch.start_reduce([g[3], g[2], g[6], g[7]])            # means3D, opacity, scales, rotations
+            return exch.finish()
         ms = timer.run(dp_step_rank1, Kb, 2)
         pb = gdist.ShGradExchange.payload_bytes(P_, world)
         out["dp_train_rank1_sh"] = {"ms_per_step": ms / Kb, "views_per_s": world * Kb / (ms / 1e3),

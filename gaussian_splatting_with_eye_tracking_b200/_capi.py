@@ -15,6 +15,7 @@ c_int_p = C.POINTER(C.c_int)
 
 # status codes (gsr_b200.h)
 GSR_OK, GSR_ERR_INVALID, GSR_ERR_CUDA, GSR_ERR_ALLOC, GSR_ERR_WORKSPACE, GSR_ERR_SORT = range(6)
+GSR_BWD_ALL, GSR_BWD_BLEND, GSR_BWD_PREPROCESS = 0, 1, 2
 GSR_BUF_GEOM, GSR_BUF_BINNING, GSR_BUF_IMAGE = range(3)
 GSR_MODE_BASELINE, GSR_MODE_AMR = 0, 1
 
@@ -74,6 +75,8 @@ SYMBOLS = {
                               c_int_p, C.c_int, C.c_void_p]),
     "gsr_backward": (C.c_int, [C.POINTER(GsrScene), C.POINTER(GsrCamera), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                C.c_int, C.c_void_p, C.POINTER(GsrGrads), C.c_int, C.c_void_p]),
+    "gsr_backward_phase": (C.c_int, [C.POINTER(GsrScene), C.POINTER(GsrCamera), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                     C.c_int, C.c_void_p, C.POINTER(GsrGrads), C.c_int, C.c_int, C.c_void_p]),
     "gsr_mark_visible": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "gsr_sh_grad_from_views": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "gsr_amr_forward": (C.c_int, [C.POINTER(GsrScene), C.POINTER(GsrCamera), C.c_int, C.c_void_p, C.c_void_p, C.c_void_p,

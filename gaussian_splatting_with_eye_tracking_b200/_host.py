@@ -155,10 +155,14 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
 
 def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rotations, scale_modifier, cov3D_precomp,
                                  viewmatrix, projmatrix, tan_fovx, tan_fovy, dL_dout_color, sh, degree, campos,
-                                 geomBuffer, R, binningBuffer, imageBuffer, debug, band=None, compact_sh=False):
+                                 geomBuffer, R, binningBuffer, imageBuffer, debug, band=None, compact_sh=False,
+                                 between_phases=None):
     """``compact_sh=True`` (extension, view-parallel training): slot 5 of the returned tuple is the [P,3] colour
     gradient after the SH clamp mask instead of the [P,M,3] SH gradient, which is then not written at all;
-    ``sh_grad_from_views`` rebuilds the SH gradient summed over views from those."""
+    ``sh_grad_from_views`` rebuilds the SH gradient summed over views from those.
+    ``between_phases(dL_dcolors_clamped)`` (with compact_sh): called after the blend-stage backward has been queued,
+    when that tensor is final in stream order -- the hook where a view-parallel caller starts its all-gather so that
+    it overlaps the preprocess-stage backward (gsr_backward_phase)."""
     H, W = int(dL_dout_color.size(1)), int(dL_dout_color.size(2))
     sc, cam, keep, P, M = _scene_camera(background, means3D, colors, torch.empty(0), scales, rotations, scale_modifier,
                                         cov3D_precomp, viewmatrix, projmatrix, tan_fovx, tan_fovy, H, W, sh, degree,
@@ -166,16 +170,21 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
     dev = means3D.device
     f32 = dict(dtype=torch.float32, device=dev)
     with torch.cuda.device(dev):
-        dL_dmeans3D = torch.empty((P, 3), **f32)
+        # the four "dense" parameter gradients are carved out of one allocation, back to back (16-byte aligned each for
+        # P % 4 == 0): a view-parallel caller all-reduces them as ONE in-place NCCL call (dist.GradientAllReduce
+        # recognises adjacent tensors) instead of packing them into a bucket and back
+        P4 = (P + 3) // 4 * 4
+        flat = torch.empty((11 * P4,), **f32)
+        dL_dmeans3D = flat[0:3 * P].view(P, 3)
+        dL_dopacity = flat[3 * P4:3 * P4 + P].view(P, 1)
+        dL_dscales = flat[4 * P4:4 * P4 + 3 * P].view(P, 3)
+        dL_drotations = flat[7 * P4:7 * P4 + 4 * P].view(P, 4)
         dL_dmeans2D = torch.empty((P, 3), **f32)
         dL_dcolors = torch.empty((P, 3), **f32)
         dL_dconic = torch.empty((P, 2, 2), **f32)
-        dL_dopacity = torch.empty((P, 1), **f32)
         dL_dcov3D = torch.empty((P, 6), **f32)
         compact = bool(compact_sh) and M > 0
         dL_dsh = torch.empty((P, 3), **f32) if compact else torch.empty((P, M, 3), **f32)
-        dL_dscales = torch.empty((P, 3), **f32)
-        dL_drotations = torch.empty((P, 4), **f32)
         if P != 0:
             scratch = torch.empty((P, 12), **f32)
             dpix = _dev_tensor(dL_dout_color, "dL_dout_color")
@@ -185,10 +194,19 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
                              dL_dsh=_p(dL_dsh) if (M and not compact) else None,
                              dL_dscales=_p(dL_dscales), dL_drotations=_p(dL_drotations), dL_dconic=_p(dL_dconic),
                              scratch=_p(scratch), dL_dcolors_clamped=_p(dL_dsh) if compact else None)
-            rc = lib.gsr_backward(C.byref(sc), C.byref(cam), _p(radii_t), _p(geomBuffer.contiguous()),
-                                  _p(binningBuffer.contiguous()), _p(imageBuffer.contiguous()), int(R), _p(dpix),
-                                  C.byref(grads), 1 if debug else 0, _stream())
-            _capi.check(rc, "gsr_backward")
+            bufs = (_p(geomBuffer.contiguous()), _p(binningBuffer.contiguous()), _p(imageBuffer.contiguous()))
+            if compact and between_phases is not None:
+                rc = lib.gsr_backward_phase(C.byref(sc), C.byref(cam), _p(radii_t), *bufs, int(R), _p(dpix), C.byref(grads),
+                                            _capi.GSR_BWD_BLEND, 1 if debug else 0, _stream())
+                _capi.check(rc, "gsr_backward_phase(blend)")
+                between_phases(dL_dsh)
+                rc = lib.gsr_backward_phase(C.byref(sc), C.byref(cam), _p(radii_t), *bufs, int(R), _p(dpix), C.byref(grads),
+                                            _capi.GSR_BWD_PREPROCESS, 1 if debug else 0, _stream())
+                _capi.check(rc, "gsr_backward_phase(preprocess)")
+            else:
+                rc = lib.gsr_backward(C.byref(sc), C.byref(cam), _p(radii_t), *bufs, int(R), _p(dpix),
+                                      C.byref(grads), 1 if debug else 0, _stream())
+                _capi.check(rc, "gsr_backward")
     return (dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations)
 
 

@@ -314,15 +314,24 @@ int gsr_forward(const gsr_scene* sc, const gsr_camera* cam, gsr_alloc_fn alloc, 
 int gsr_backward(const gsr_scene* sc, const gsr_camera* cam, const int* radii, const void* geom_buffer,
                  const void* binning_buffer, const void* image_buffer, int num_rendered, const float* dL_dpix,
                  const gsr_grads* gr, int debug, void* stream) {
+    return gsr_backward_phase(sc, cam, radii, geom_buffer, binning_buffer, image_buffer, num_rendered, dL_dpix, gr,
+                              GSR_BWD_ALL, debug, stream);
+}
+
+int gsr_backward_phase(const gsr_scene* sc, const gsr_camera* cam, const int* radii, const void* geom_buffer,
+                       const void* binning_buffer, const void* image_buffer, int num_rendered, const float* dL_dpix,
+                       const gsr_grads* gr, int phase, int debug, void* stream) {
     cudaStream_t s = (cudaStream_t)stream;
+    if (phase != GSR_BWD_ALL && phase != GSR_BWD_BLEND && phase != GSR_BWD_PREPROCESS) { set_error("bad backward phase %d", phase); return GSR_ERR_INVALID; }
+    (void)num_rendered;
     int rc = validate(sc, cam, /*forward=*/false);
     if (rc) return rc;
-    if (!gr || !dL_dpix) { set_error("grads/dL_dpix are required"); return GSR_ERR_INVALID; }
+    if (!gr || (!dL_dpix && phase != GSR_BWD_PREPROCESS)) { set_error("grads/dL_dpix are required"); return GSR_ERR_INVALID; }
     const int P = sc->P, W = cam->width, H = cam->height;
     if (P == 0) return GSR_OK;
     if (!geom_buffer || !binning_buffer || !image_buffer) { set_error("work buffers are required"); return GSR_ERR_WORKSPACE; }
     if (!gr->dL_dmeans2D || !gr->dL_dcolors || !gr->dL_dopacity || !gr->dL_dmeans3D || !gr->dL_dcov3D || !gr->dL_dscales ||
-        !gr->dL_drotations || !gr->scratch || (sc->sh_coeffs > 0 && sc->shs && !gr->dL_dsh && !gr->dL_dcolors_clamped)) {
+        !gr->dL_drotations || !gr->scratch || (phase != GSR_BWD_BLEND && sc->sh_coeffs > 0 && sc->shs && !gr->dL_dsh && !gr->dL_dcolors_clamped)) {
         set_error("gradient output pointers are required"); return GSR_ERR_INVALID;
     }
     if (((size_t)gr->scratch & 15) != 0) { set_error("scratch must be 16-byte aligned"); return GSR_ERR_INVALID; }
@@ -330,6 +339,8 @@ int gsr_backward(const gsr_scene* sc, const gsr_camera* cam, const int* radii, c
     ImgPtrs im = img_ptrs(image_buffer, W, H, GSR_MODE_BASELINE);
     if (!radii) radii = g.radii;
 
+    const bool colors_from_sh = (sc->shs != nullptr) && (sc->colors_precomp == nullptr);          // backward.cu:390 `if (shs)`
+    if (phase != GSR_BWD_PREPROCESS) {
     if ((rc = check_cuda(cudaMemsetAsync(gr->scratch, 0, sizeof(float) * 12 * (size_t)P, s), "memset scratch"))) return rc;
     BlendBwdArgs bb;
     bb.W = W; bb.H = H; bb.row0 = cam->band_row0; bb.row1 = cam->band_row1; bb.ranges = im.ranges; bb.point_list = bin_point_list(binning_buffer); bb.means2D = g.means2D;
@@ -338,19 +349,28 @@ int gsr_backward(const gsr_scene* sc, const gsr_camera* cam, const int* radii, c
     bb.scratch = gr->scratch;
     { ProfScope ps(GSR_PROF_BWD_BLEND, s); launch_blend_backward(bb, s); }
     if ((rc = check_last("blend backward", debug != 0, s))) return rc;
+    if (phase == GSR_BWD_BLEND && gr->dL_dcolors_clamped) {
+        // the clamped colour gradient is final once the blend stage is done: emit it now so that a view-parallel
+        // caller can start exchanging it while the preprocess stage still runs
+        launch_clamped_rgb(P, radii, gr->scratch, g.clamped, colors_from_sh, gr->dL_dcolors_clamped, s);
+        if ((rc = check_last("clamped rgb", debug != 0, s))) return rc;
+    }
+    }
+    if (phase == GSR_BWD_BLEND) return GSR_OK;
 
     PreBwdArgs pb;
     pb.P = P; pb.D = sc->sh_degree; pb.M = sc->sh_coeffs;
     pb.means3D = sc->means3D; pb.scales = sc->scales; pb.rotations = sc->rotations; pb.shs = sc->shs;
     pb.cov3D = sc->cov3D_precomp ? sc->cov3D_precomp : g.cov3D;
     pb.cov_from_scales = (sc->cov3D_precomp == nullptr) && sc->scales && sc->rotations;   // backward.cu:394 `if (scales)`
-    pb.colors_from_sh = (sc->shs != nullptr) && (sc->colors_precomp == nullptr);          // backward.cu:390 `if (shs)`
+    pb.colors_from_sh = colors_from_sh;
     pb.scale_modifier = sc->scale_modifier;
     pb.viewmatrix = cam->viewmatrix; pb.projmatrix = cam->projmatrix; pb.cam_pos = cam->cam_pos;
     pb.focal_y = H / (2.0f * cam->tan_fovy); pb.focal_x = W / (2.0f * cam->tan_fovx);
     pb.tan_fovx = cam->tan_fovx; pb.tan_fovy = cam->tan_fovy;
     pb.radii = radii; pb.clamped = g.clamped; pb.scratch = gr->scratch; pb.out = *gr;
     if (sc->sh_coeffs == 0) pb.out.dL_dsh = nullptr;
+    if (phase == GSR_BWD_PREPROCESS) pb.out.dL_dcolors_clamped = nullptr;      // already emitted by the blend phase
     { ProfScope ps(GSR_PROF_BWD_PREPROCESS, s); launch_preprocess_backward(pb, s); }
     return check_last("preprocess backward", debug != 0, s);
 }

@@ -248,6 +248,7 @@ struct PreprocessArgs {
 };
 void launch_preprocess(const PreprocessArgs& a, const GeomPtrs& g, cudaStream_t s);
 void launch_block_scan(const GeomPtrs& g, int P, uint32_t* mailbox_dev, cudaStream_t s);
+void launch_clamped_rgb(int P, const int* radii, const float* scratch, const unsigned char* clamped, bool colors_from_sh, float* out, cudaStream_t s);
 int launch_sh_grad_from_views(int P, int D, int M, const float* means3D, int K, const float* cams, const float* g_all, float* dL_dsh, cudaStream_t s);
 void launch_mark_visible(int P, const float* means3D, const float* view, const float* proj, unsigned char* present, cudaStream_t s);
 

@@ -805,4 +805,27 @@ int launch_sh_grad_from_views(int P, int D, int M, const float* means3D, int K, 
     return GSR_OK;
 }
 
+// clamped colour gradient right after the blend stage (gsr_backward_phase GSR_BWD_BLEND): scratch rows hold dL_dcolor
+// in (1.z, 1.w, 2.x); the SH clamp mask zeroes channels (backward.cu:56-58); culled Gaussians get zero rows.
+__global__ void __launch_bounds__(256) clamped_rgb_kernel(int P, const int* __restrict__ radii, const float* __restrict__ scratch,
+                                                          const unsigned char* __restrict__ clamped, int colors_from_sh,
+                                                          float* __restrict__ out) {
+    const int idx = blockIdx.x * 256 + threadIdx.x;
+    if (idx >= P) return;
+    const size_t i3 = 3 * (size_t)idx;
+    float g0 = 0.f, g1 = 0.f, g2 = 0.f;
+    if (colors_from_sh && radii[idx] > 0) {
+        const float4* sp = reinterpret_cast<const float4*>(scratch) + 3 * (size_t)idx;
+        const float4 sB = sp[1], sC = sp[2];
+        g0 = sB.z * (clamped[i3] ? 0.f : 1.f); g1 = sB.w * (clamped[i3 + 1] ? 0.f : 1.f); g2 = sC.x * (clamped[i3 + 2] ? 0.f : 1.f);
+    }
+    out[i3] = g0; out[i3 + 1] = g1; out[i3 + 2] = g2;
+}
+
+void launch_clamped_rgb(int P, const int* radii, const float* scratch, const unsigned char* clamped, bool colors_from_sh, float* out, cudaStream_t s) {
+    if (P <= 0) return;
+    clamped_rgb_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, radii, scratch, clamped, colors_from_sh ? 1 : 0, out);
+    count_launch();
+}
+
 }  // namespace gsr

@@ -93,7 +93,7 @@ class GradientAllReduce:
         if world_size() == 1 or not grads:
             return
         dev, dt = grads[0].device, grads[0].dtype
-        flats = [g.view(-1) for g in grads]
+        flats = _coalesce_adjacent([g.view(-1) for g in grads])
         plan = plan_buckets([f.numel() for f in flats], self.bucket_bytes, grads[0].element_size())
         comm = self._comm_stream(dev)
         if comm is not None:
@@ -153,52 +153,87 @@ class ShGradExchange:
         self._rebuild = rebuild
         self._gathered = None
         self._cams = None
-        self._work = []
         self._stream = None
+        self._dsh = None
+        self._keep = None
 
-    def start(self, dense_grads: Sequence[torch.Tensor], dL_dcolors_clamped: torch.Tensor, campos: torch.Tensor) -> None:
-        """dense_grads: the tensors to SUM in place (means3D, opacity, scales, rotations gradients);
-        dL_dcolors_clamped [P,3] and campos [3] of THIS rank's view."""
+    def _comm(self, dev):
+        if dev.type != "cuda":
+            return None
+        if self._stream is None:
+            self._stream = torch.cuda.Stream(device=dev)
+        return self._stream
+
+    def start_gather(self, dL_dcolors_clamped: torch.Tensor, campos: torch.Tensor, means3D: torch.Tensor, degree: int, M: int) -> None:
+        """Queue (on the side stream) the all-gather of this rank's clamped colour gradient [P,3] and camera position,
+        followed by the rebuild of the summed SH gradient.  Returns immediately: called between the two backward
+        phases (``_host.rasterize_gaussians_backward(..., between_phases=...)``) it overlaps the preprocess stage."""
         w = world_size()
         P = dL_dcolors_clamped.shape[0]
         dev = dL_dcolors_clamped.device
         if self._gathered is None or self._gathered.shape != (w, P, 3) or self._gathered.device != dev:
             self._gathered = torch.empty((w, P, 3), dtype=dL_dcolors_clamped.dtype, device=dev)
             self._cams = torch.empty((w, 3), dtype=campos.dtype, device=dev)
-        if w == 1:
-            self._gathered[0].copy_(dL_dcolors_clamped); self._cams[0].copy_(campos.reshape(3))
-            return
-        comm = None
-        if dev.type == "cuda":
-            if self._stream is None:
-                self._stream = torch.cuda.Stream(device=dev)
-            comm = self._stream
-            comm.wait_stream(torch.cuda.current_stream(dev))
-        with (torch.cuda.stream(comm) if comm is not None else _null()):
-            self._work = [
-                dist.all_gather_into_tensor(self._gathered.view(-1), dL_dcolors_clamped.contiguous().view(-1), group=self.group, async_op=True),
-                dist.all_gather_into_tensor(self._cams.view(-1), campos.contiguous().view(-1), group=self.group, async_op=True)]
-            if comm is not None:
-                dL_dcolors_clamped.record_stream(comm); campos.record_stream(comm)
-        self.reducer.start(dense_grads)
-
-    def finish(self, means3D: torch.Tensor, degree: int, M: int) -> torch.Tensor:
-        """Wait for the exchange; returns the SH gradient [P,M,3] summed over all views."""
-        for wk in self._work:
-            wk.wait()
-        if self._stream is not None and self._work:
-            torch.cuda.current_stream().wait_stream(self._stream)
-        self._work = []
-        self.reducer.wait()
         rebuild = self._rebuild
         if rebuild is None:
             from . import _host
             rebuild = _host.sh_grad_from_views
-        return rebuild(means3D, self._cams, self._gathered, degree, M)
+        comm = self._comm(dev)
+        if comm is not None:
+            comm.wait_stream(torch.cuda.current_stream(dev))
+        self._keep = (dL_dcolors_clamped, campos)           # alive until finish(): they are read on the side stream
+        with (torch.cuda.stream(comm) if comm is not None else _null()):
+            if w == 1:
+                self._gathered[0].copy_(dL_dcolors_clamped); self._cams[0].copy_(campos.reshape(3))
+            else:
+                works = [dist.all_gather_into_tensor(self._gathered.view(-1), dL_dcolors_clamped.contiguous().view(-1), group=self.group, async_op=True),
+                         dist.all_gather_into_tensor(self._cams.view(-1), campos.contiguous().view(-1), group=self.group, async_op=True)]
+                for wk in works:
+                    wk.wait()                                 # blocks the side stream only (the host for gloo)
+            self._dsh = rebuild(means3D, self._cams, self._gathered, degree, M)
+
+    def start_reduce(self, dense_grads: Sequence[torch.Tensor]) -> None:
+        """Queue the in-place SUM of the remaining gradients (means3D, opacity, scales, rotations)."""
+        self.reducer.start(dense_grads)
+
+    def start(self, dense_grads: Sequence[torch.Tensor], dL_dcolors_clamped: torch.Tensor, campos: torch.Tensor,
+              means3D: torch.Tensor, degree: int, M: int) -> None:
+        self.start_gather(dL_dcolors_clamped, campos, means3D, degree, M)
+        self.start_reduce(dense_grads)
+
+    def finish(self) -> torch.Tensor:
+        """Wait (the current stream, not the host) for the exchange; returns the SH gradient [P,M,3] summed over all views."""
+        if self._stream is not None:
+            torch.cuda.current_stream().wait_stream(self._stream)
+        self.reducer.wait()
+        dsh, self._dsh, self._keep = self._dsh, None, None
+        if dsh is not None and dsh.is_cuda:
+            dsh.record_stream(torch.cuda.current_stream())    # allocated on the side stream, consumed here
+        return dsh
 
     @staticmethod
     def payload_bytes(P: int, world: int, itemsize: int = 4) -> dict:
         return {"allreduce": 11 * itemsize * P, "allgather_in": 3 * itemsize * P * world, "dense_allreduce_equivalent": 59 * itemsize * P}
+
+
+def _coalesce_adjacent(flats: List[torch.Tensor]) -> List[torch.Tensor]:
+    """Merge 1-D tensors that sit back to back in the same storage (e.g. the parameter gradients that
+    _host.rasterize_gaussians_backward carves out of one allocation) into single views, so that they are reduced in place
+    by one collective; gaps (alignment padding) of up to 16 elements are bridged -- summing padding is harmless."""
+    out: List[torch.Tensor] = []
+    for f in flats:
+        if out and f.is_contiguous() and out[-1].is_contiguous() and f.dtype == out[-1].dtype:
+            prev = out[-1]
+            try:
+                same = f.untyped_storage().data_ptr() == prev.untyped_storage().data_ptr()
+            except Exception:
+                same = False
+            gap = f.storage_offset() - (prev.storage_offset() + prev.numel())
+            if same and 0 <= gap <= 16:
+                out[-1] = torch.as_strided(prev, (prev.numel() + gap + f.numel(),), (1,), prev.storage_offset())
+                continue
+        out.append(f)
+    return out
 
 
 class _null:

@@ -136,6 +136,17 @@ GSR_API int gsr_backward(const gsr_scene* scene, const gsr_camera* cam,
                          const float* dL_dpix /* [3,H,W] */, const gsr_grads* grads,
                          int debug, void* stream);
 
+/* The same in two calls, so that a view-parallel caller can overlap its gradient exchange with the second stage:
+ * GSR_BWD_BLEND      blend-stage backward into `scratch`; with grads->dL_dcolors_clamped given, that tensor is final on
+ *                    return of this phase (in stream order)
+ * GSR_BWD_PREPROCESS preprocess-stage backward from `scratch` (dL_dpix may be NULL); dL_dsh == NULL with
+ *                    dL_dcolors_clamped given = SH rows not written, dL_dcolors_clamped not rewritten
+ * GSR_BWD_ALL        both (== gsr_backward) */
+enum { GSR_BWD_ALL = 0, GSR_BWD_BLEND = 1, GSR_BWD_PREPROCESS = 2 };
+GSR_API int gsr_backward_phase(const gsr_scene* scene, const gsr_camera* cam, const int* radii, const void* geom_buffer,
+                               const void* binning_buffer, const void* image_buffer, int num_rendered, const float* dL_dpix,
+                               const gsr_grads* grads, int phase, int debug, void* stream);
+
 GSR_API int gsr_mark_visible(int P, const float* means3D, const float* viewmatrix,
                              const float* projmatrix, unsigned char* present, void* stream);
 

@@ -146,8 +146,9 @@ def body_sh_grad_exchange(rank, world):
         return cam, drgb, dense
     cam, drgb, dense = view(rank)
     ex = gdist.ShGradExchange(rebuild=_rebuild_ref, bucket_bytes=4096)
-    ex.start(dense, drgb, cam)
-    dsh = ex.finish(means, deg, M)
+    ex.start_gather(drgb, cam, means, deg, M)          # (between the two backward phases on the GPU)
+    ex.start_reduce(dense)
+    dsh = ex.finish()
     # what a dense all-reduce of per-view SH gradients would have produced
     want_sh = sum(_rebuild_ref(means, view(r)[0][None], view(r)[1][None], deg, M) for r in range(world))
     assert torch.allclose(dsh, want_sh, rtol=1e-5, atol=1e-6)

@@ -63,3 +63,25 @@ def test_rebuild_sums_views_in_order():
     # bit-identical on repeat (fixed summation order): what makes the result equal on every rank
     again = _host.sh_grad_from_views(d["means3D"], torch.stack(cams), torch.stack(gs), d["sh_degree"], M)
     assert torch.equal(both, again)
+
+
+def test_two_phase_backward_matches_single_call_and_hook_sees_final_tensor():
+    """gsr_backward_phase: BLEND then PREPROCESS == one gsr_backward; the clamped colour gradient is final (in stream
+    order) when the between-phases hook runs, which is where the view-parallel all-gather starts."""
+    from gaussian_splatting_with_eye_tracking_b200 import _host
+    sc, cam = common.make_case("small")
+    dpix = common.upstream_gradient(cam)
+    d, camd, one = _backward(sc, cam, dpix, True)
+    N, color, radii, geom, binning, img = _host.rasterize_gaussians(*common.fwd_args(d, camd), False)
+    seen = {}
+
+    def hook(drgb):
+        seen["at_hook"] = drgb.clone()          # stream-ordered copy at the hook point
+    two = _host.rasterize_gaussians_backward(
+        d["bg"], d["means3D"], radii, d["colors_precomp"], d["scales"], d["rotations"], 1.0, d["cov3D_precomp"],
+        camd.world_view_transform, camd.full_proj_transform, cam.tanfovx, cam.tanfovy, dpix.cuda(), d["shs"],
+        d["sh_degree"], camd.camera_center, geom, N, binning, img, False, compact_sh=True, between_phases=hook)
+    torch.cuda.synchronize()
+    assert torch.equal(seen["at_hook"], two[5])          # not rewritten by the second phase
+    for i in range(8):
+        _close(two[i], one[i], f"grad[{i}] two-phase vs single call")
