@@ -645,6 +645,174 @@ __global__ void __launch_bounds__(kBlendThreads) blend_bwd_kernel(const BwdParam
     }
 }
 
+// ------------------------------------------------------------------------------------------------
+// backward, two pixels per thread (default).  blend_bwd_kernel is bound by instruction issue (ncu: 84 % issue-active);
+// here a thread owns two horizontally adjacent pixels, the gradient chain runs in packed FP32x2, the two pixels'
+// terms are added before the warp butterfly (one reduction and one atomic set per 64 pixels instead of 32), and 128
+// threads cover the tile.  A pixel that an entry does not touch is carried through the same arithmetic with
+// alpha = 0 and G = 0: T, the deferred colour accumulator and every gradient term then come out unchanged / zero
+// exactly (acc' = a*lc + (1-a)*acc applied early followed by a zero-weight entry is the same recurrence), so no
+// per-pixel selects are needed.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kBlend2Threads, 6) blend_bwd2_kernel(const BwdParams p) {
+    __shared__ float4 s_a[kBlend2Threads];
+    __shared__ float4 s_b[kBlend2Threads];
+    __shared__ float4 s_c[kBlend2Threads];     // b, list position (1-based), id, reject threshold
+    __shared__ uint32_t s_wcnt[kBlend2Threads / 32];
+    __shared__ uint32_t s_count;
+    __shared__ uint32_t s_maxc;
+
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const uint32_t lx = (wid & 1) * 8 + (lane & 3) * 2, ly = (wid >> 1) * 8 + (lane >> 2);
+    const uint32_t tile_y = blockIdx.y + (uint32_t)p.row0;
+    const uint32_t pix_x = blockIdx.x * 16 + lx, pix_y = tile_y * 16 + ly;
+    const bool in0 = pix_x < (uint32_t)p.W && pix_y < (uint32_t)p.H;
+    const bool in1 = pix_x + 1 < (uint32_t)p.W && pix_y < (uint32_t)p.H;
+    const size_t pix_id = (size_t)p.W * pix_y + pix_x;
+    const float pyf = (float)pix_y;
+    const f32x2 npx2 = pk(-(float)pix_x, -(float)(pix_x + 1));
+    const float rx0 = (float)(blockIdx.x * 16), ry0 = (float)(tile_y * 16);
+    const float rx1 = rx0 + 15.f, ry1 = ry0 + 15.f;
+    const size_t HW = (size_t)p.H * p.W;
+
+    const uint2 range = p.ranges[tile_y * p.tiles_x + blockIdx.x];
+    const int todo = (int)(range.y - range.x);
+    const int rounds = (todo + kBlend2Threads - 1) / kBlend2Threads;
+
+    const float Tf0 = in0 ? p.final_T[pix_id] : 0.f, Tf1 = in1 ? p.final_T[pix_id + 1] : 0.f;
+    const uint32_t lc0 = in0 ? p.n_contrib[pix_id] : 0u, lc1 = in1 ? p.n_contrib[pix_id + 1] : 0u;
+    float ga0 = 0.f, ga1 = 0.f, ga2 = 0.f, gb0 = 0.f, gb1 = 0.f, gb2 = 0.f;
+    if (in0) { ga0 = p.dL_dpix[pix_id]; ga1 = p.dL_dpix[HW + pix_id]; ga2 = p.dL_dpix[2 * HW + pix_id]; }
+    if (in1) { gb0 = p.dL_dpix[pix_id + 1]; gb1 = p.dL_dpix[HW + pix_id + 1]; gb2 = p.dL_dpix[2 * HW + pix_id + 1]; }
+    const float bgx = p.bg[0], bgy = p.bg[1], bgz = p.bg[2];
+    const f32x2 g0_2 = pk(ga0, gb0), g1_2 = pk(ga1, gb1), g2_2 = pk(ga2, gb2);
+    const f32x2 nTf_bg2 = pk(-Tf0 * (bgx * ga0 + bgy * ga1 + bgz * ga2), -Tf1 * (bgx * gb0 + bgy * gb1 + bgz * gb2));   // -T_final * bg_dot
+    const float ddelx_dx = 0.5f * (float)p.W, ddely_dy = 0.5f * (float)p.H;
+    f32x2 T2 = pk(Tf0, Tf1);
+    f32x2 acc0_2 = pk(0.f, 0.f), acc1_2 = acc0_2, acc2_2 = acc0_2, la2 = acc0_2;      // accum_rec, last_alpha
+    float lcol0 = 0.f, lcol1 = 0.f, lcol2 = 0.f;                                        // last colour (same for both pixels)
+
+    // the CTA only needs list entries up to the largest n_contrib of its pixels
+    if (tid == 0) s_maxc = 0;
+    __syncthreads();
+    {
+        uint32_t m = max(lc0, lc1);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) m = max(m, __shfl_xor_sync(0xffffffffu, m, o));
+        if (lane == 0) atomicMax(&s_maxc, m);
+    }
+    __syncthreads();
+    const int max_c = (int)s_maxc;
+
+    GaussRec nxt; bool nxt_valid = false;
+    auto pos_of = [&](int r) { return todo - r * kBlend2Threads - tid; };      // batch r, back to front, 1-based
+    const int r_first = (todo - max_c) / kBlend2Threads;
+    {
+        const int pos = pos_of(r_first);
+        nxt_valid = pos >= 1 && pos <= max_c;
+        if (nxt_valid) nxt = gather(p.point_list, p.means2D, p.conic_opacity, p.colors, range.x + pos - 1);
+    }
+
+    for (int r = r_first; r < rounds; ++r) {
+        __syncthreads();
+        const bool keep = nxt_valid && !cannot_touch(nxt.xy, nxt.co, rx0, ry0, rx1, ry1);
+        const int slot = compact_slot<kBlend2Threads>(keep, s_wcnt, &s_count);
+        if (slot >= 0) {
+            s_a[slot] = make_float4(nxt.xy.x, nxt.xy.y, nxt.co.x, nxt.co.y);
+            s_b[slot] = make_float4(nxt.co.z, nxt.co.w, nxt.col.x, nxt.col.y);
+            s_c[slot] = make_float4(nxt.col.z, __uint_as_float((uint32_t)pos_of(r)), __uint_as_float(nxt.id), reject_below(nxt.co.w));
+        }
+        __syncthreads();
+        const int count = (int)s_count;
+        {
+            const int pos = pos_of(r + 1);
+            nxt_valid = (r + 1 < rounds) && pos >= 1 && pos <= max_c;
+            if (nxt_valid) nxt = gather(p.point_list, p.means2D, p.conic_opacity, p.colors, range.x + pos - 1);
+        }
+
+        for (int j = 0; j < count; ++j) {
+            const float4 A = s_a[j], B = s_b[j], Cc = s_c[j];
+            const uint32_t pos = __float_as_uint(Cc.y);
+            const float dy = A.y - pyf;
+            const f32x2 dx2 = add2(pk(A.x, A.x), npx2);
+            float pw0, pw1;
+            upk(blend_power2(A.z, A.w, B.x, dx2, dy), pw0, pw1);
+            const bool c0 = pos <= lc0 && !(pw0 < Cc.w) && !(pw0 > 0.0f);
+            const bool c1 = pos <= lc1 && !(pw1 < Cc.w) && !(pw1 > 0.0f);
+            if (!__any_sync(0xffffffffu, c0 || c1)) continue;
+            float G0 = expf(pw0), G1 = expf(pw1);
+            float al0 = fminf(0.99f, B.y * G0), al1 = fminf(0.99f, B.y * G1);
+            const bool a0 = c0 && !(al0 < kAlphaMin), a1 = c1 && !(al1 < kAlphaMin);
+            if (!__any_sync(0xffffffffu, a0 || a1)) continue;
+            if (!a0) { al0 = 0.f; G0 = 0.f; }
+            if (!a1) { al1 = 0.f; G1 = 0.f; }
+            const f32x2 al2 = pk(al0, al1), G2 = pk(G0, G1);
+            const f32x2 inv2 = pk(__frcp_rn(1.f - al0), __frcp_rn(1.f - al1));       // 1 for an untouched pixel
+            T2 = mul2(T2, inv2);
+            const f32x2 dch2 = mul2(al2, T2);                                          // dchannel_dcolor
+            const f32x2 oml2 = add2(pk(1.f, 1.f), la2 ^ 0x8000000080000000ull);         // 1 - last_alpha
+            acc0_2 = fma2(la2, pk(lcol0, lcol0), mul2(oml2, acc0_2));
+            acc1_2 = fma2(la2, pk(lcol1, lcol1), mul2(oml2, acc1_2));
+            acc2_2 = fma2(la2, pk(lcol2, lcol2), mul2(oml2, acc2_2));
+            lcol0 = B.z; lcol1 = B.w; lcol2 = Cc.x;
+            f32x2 dLa2 = mul2(add2(pk(lcol0, lcol0), acc0_2 ^ 0x8000000080000000ull), g0_2);
+            dLa2 = fma2(add2(pk(lcol1, lcol1), acc1_2 ^ 0x8000000080000000ull), g1_2, dLa2);
+            dLa2 = fma2(add2(pk(lcol2, lcol2), acc2_2 ^ 0x8000000080000000ull), g2_2, dLa2);
+            dLa2 = mul2(dLa2, T2);
+            la2 = al2;
+            dLa2 = fma2(nTf_bg2, inv2, dLa2);
+            const f32x2 dLdG2 = mul2(pk(B.y, B.y), dLa2);
+            const f32x2 gdx2 = mul2(G2, dx2), gdy2 = mul2(G2, pk(dy, dy));
+            const f32x2 ncx = pk(-A.z, -A.z), ncy = pk(-A.w, -A.w), ncz = pk(-B.x, -B.x);
+            const f32x2 dGx2 = fma2(gdx2, ncx, mul2(gdy2, ncy));                       // -gdx*cx - gdy*cy
+            const f32x2 dGy2 = fma2(gdy2, ncz, mul2(gdx2, ncy));                       // -gdy*cz - gdx*cy
+            const f32x2 h2 = mul2(pk(-0.5f, -0.5f), dLdG2);
+            float v[8], v8, lo, hi;
+            upk(mul2(mul2(dLdG2, dGx2), pk(ddelx_dx, ddelx_dx)), lo, hi); v[0] = lo + hi;
+            upk(mul2(mul2(dLdG2, dGy2), pk(ddely_dy, ddely_dy)), lo, hi); v[1] = lo + hi;
+            upk(mul2(mul2(gdx2, dx2), h2), lo, hi); v[2] = lo + hi;
+            upk(mul2(mul2(gdx2, pk(dy, dy)), h2), lo, hi); v[3] = lo + hi;
+            upk(mul2(mul2(gdy2, pk(dy, dy)), h2), lo, hi); v[4] = lo + hi;
+            upk(mul2(G2, dLa2), lo, hi); v[5] = lo + hi;
+            upk(mul2(dch2, g0_2), lo, hi); v[6] = lo + hi;
+            upk(mul2(dch2, g1_2), lo, hi); v[7] = lo + hi;
+            upk(mul2(dch2, g2_2), lo, hi); v8 = lo + hi;
+
+            // butterfly reduction (as in blend_bwd_kernel): 9 shuffles for 8 values
+            float w4[4], w2[2], w1;
+            {
+                const bool hi_ = lane & 16;
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const float keepv = hi_ ? v[4 + i] : v[i], send = hi_ ? v[i] : v[4 + i];
+                    w4[i] = keepv + __shfl_xor_sync(0xffffffffu, send, 16);
+                }
+            }
+            {
+                const bool hi_ = lane & 8;
+#pragma unroll
+                for (int i = 0; i < 2; ++i) {
+                    const float keepv = hi_ ? w4[2 + i] : w4[i], send = hi_ ? w4[i] : w4[2 + i];
+                    w2[i] = keepv + __shfl_xor_sync(0xffffffffu, send, 8);
+                }
+            }
+            {
+                const bool hi_ = lane & 4;
+                const float keepv = hi_ ? w2[1] : w2[0], send = hi_ ? w2[0] : w2[1];
+                w1 = keepv + __shfl_xor_sync(0xffffffffu, send, 4);
+            }
+            w1 += __shfl_xor_sync(0xffffffffu, w1, 2);
+            w1 += __shfl_xor_sync(0xffffffffu, w1, 1);
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) v8 += __shfl_xor_sync(0xffffffffu, v8, o);
+
+            float* dst = p.scratch + 12 * (size_t)__float_as_uint(Cc.z);
+            if ((lane & 3) == 0) atomicAdd(dst + ((lane >> 2) & 7), w1);
+            if (lane == 1) atomicAdd(dst + 8, v8);
+        }
+    }
+}
+
 void launch_blend_backward(const BlendBwdArgs& a, cudaStream_t s) {
     BwdParams p;
     p.W = a.W; p.H = a.H; p.tiles_x = (a.W + 15) / 16;
@@ -656,7 +824,8 @@ void launch_blend_backward(const BlendBwdArgs& a, cudaStream_t s) {
     if (r1 <= r0) return;
     p.row0 = r0;
     dim3 grid((a.W + 15) / 16, r1 - r0, 1);
-    blend_bwd_kernel<<<grid, kBlendThreads, 0, s>>>(p);
+    if (g_blend_variant == 1) blend_bwd_kernel<<<grid, kBlendThreads, 0, s>>>(p);      // one pixel per thread (A/B reference)
+    else blend_bwd2_kernel<<<grid, kBlend2Threads, 0, s>>>(p);
     count_launch();
 }
 
