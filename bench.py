@@ -492,14 +492,16 @@ def measure(impl, args, d, cams, rank, world, timer, full):
 
         def band_step(i):
             cam = cams[i % ncam]                      # every rank renders the SAME view
+            # the frame is assembled on rank 0 only (the display node): exactly-sized point-to-point blocks
             frame, counts, levels, _ = gdist.render_amr_frame_bands(impl._args(cam), args.height, args.width, state["bands"], rank,
-                                                                    interpolate_image=True, gather=True)
-            state["bands"] = gdist.balanced_bands(gdist.row_costs_from_counts(counts, tiles_x32, tiles_y32, levels), world)
+                                                                    interpolate_image=True, gather=True, dst=0)
+            if i % 4 == 3:                            # re-balance every 4th frame (it reads the counts back to the host)
+                state["bands"] = gdist.balanced_bands(gdist.row_costs_from_counts(counts, tiles_x32, tiles_y32, levels), world)
             return frame
         try:
             ms = timer.run(band_step, Kb, 2)
             out["tile_bands"] = {"frames_per_s": Kb / (ms / 1e3), "ms_per_frame": ms / Kb, "bands": [list(b) for b in state["bands"]],
-                                 "what": "one AMR-foveated frame per step, all ranks on the same view (strong scaling)"}
+                                 "what": "one AMR-foveated frame per step, all ranks on the same view (strong scaling); assembled on rank 0, bands re-balanced every 4th frame"}
         except RuntimeError as ex:
             out["tile_bands"] = {"error": str(ex)[:200]}
 

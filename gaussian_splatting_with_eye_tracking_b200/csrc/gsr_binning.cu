@@ -276,6 +276,8 @@ __global__ void __launch_bounds__(THREADS, MINB) onesweep_kernel(const SweepPara
     __shared__ uint32_t s_wtot[RADIX / 32];
 
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    // grid sized for the upper bound n: tiles past the device-side count leave at once (nobody waits on them)
+    if (p.n_dev != nullptr && (long long)blockIdx.x * (THREADS * ITEMS) >= (long long)__ldg(p.n_dev)) return;
     for (int i = tid; i < WARPS * RADIX; i += THREADS) s_whist[i] = 0;
     __syncthreads();
     // The tile's place in the chained scan is its block index: blocks are dispatched in increasing linear index (the

@@ -307,37 +307,54 @@ def allreduce_tile_counts(n_intersections: torch.Tensor, group=None) -> torch.Te
     return n_intersections
 
 
-def gather_bands(frame: torch.Tensor, bands: Sequence[Tuple[int, int]], tile_px: int, group=None) -> torch.Tensor:
+def gather_bands(frame: torch.Tensor, bands: Sequence[Tuple[int, int]], tile_px: int, group=None, dst: Optional[int] = None) -> torch.Tensor:
     """Assemble the full [3,H,W] frame from per-rank frames in which only the rank's band rows are valid.
 
-    Uses all_gather of equal-size padded band slabs (NCCL needs equal counts), then copies each slab into place."""
+    ``dst=None``: every rank gets the frame -- all_gather of equal-size padded band slabs (NCCL needs equal counts),
+    then each slab is copied into place.  ``dst=r``: only rank r assembles it (what a display node needs): every
+    other rank sends exactly its band rows, one contiguous [rows, W] block per colour channel, and rank r receives
+    them straight into its own frame (one batched group of point-to-point operations, no padding, no staging
+    copies); the other ranks return their own (partial) frame."""
     world = world_size()
     if world == 1:
         return frame
     C_, H, W = frame.shape
     rank = dist.get_rank(group)
-    max_rows = max(b - a for a, b in bands) * tile_px
-    a, b = bands[rank]
-    y0, y1 = min(a * tile_px, H), min(b * tile_px, H)
+    rows = [(min(a * tile_px, H), min(b * tile_px, H)) for a, b in bands]
+    if dst is not None:
+        ops = []
+        if rank == dst:
+            for r, (y0, y1) in enumerate(rows):
+                if r != dst and y1 > y0:
+                    ops += [dist.P2POp(dist.irecv, frame[c, y0:y1], r, group) for c in range(C_)]
+        else:
+            y0, y1 = rows[rank]
+            if y1 > y0:
+                ops = [dist.P2POp(dist.isend, frame[c, y0:y1], dst, group) for c in range(C_)]
+        if ops:
+            for wk in dist.batch_isend_irecv(ops):
+                wk.wait()
+        return frame
+    max_rows = max(y1 - y0 for y0, y1 in rows)
+    y0, y1 = rows[rank]
     slab = torch.zeros((C_, max_rows, W), dtype=frame.dtype, device=frame.device)
     slab[:, :y1 - y0] = frame[:, y0:y1]
     out = [torch.empty_like(slab) for _ in range(world)]
     dist.all_gather(out, slab, group=group)
     full = torch.empty_like(frame)
-    for r, (ra, rb) in enumerate(bands):
-        ry0, ry1 = min(ra * tile_px, H), min(rb * tile_px, H)
+    for r, (ry0, ry1) in enumerate(rows):
         full[:, ry0:ry1] = out[r][:, :ry1 - ry0]
     return full
 
 
 def render_amr_frame_bands(fwd_args, image_height: int, image_width: int, bands: Sequence[Tuple[int, int]], rank: int,
-                           interpolate_image: bool = True, gaze=None, group=None, gather: bool = True):
+                           interpolate_image: bool = True, gaze=None, group=None, gather: bool = True, dst: Optional[int] = None):
     """One foveated frame split by screen-tile band over the ranks of ``group`` (config C5).
 
     ``fwd_args`` are the first 18 positional arguments of ``_C.rasterize_gaussians`` (bg ... prefiltered).  Every rank
     (1) preprocesses all Gaussians but bins only its rows (``foveaStep=0`` build with ``band``), (2) all-reduces the
     per-tile pair counts so that the AMR percentiles are the global ones, (3) re-levels and renders its band in a single
-    pass, (4) optionally gathers the bands.  Returns (frame, n_intersections, levels, (geom, binning, image) buffers);
+    pass, (4) optionally gathers the bands (on every rank, or only on rank ``dst``).  Returns (frame, n_intersections, levels, (geom, binning, image) buffers);
     the levels are bit-identical to a single-GPU render of the whole frame."""
     from . import _host, views
     dev = fwd_args[1].device
@@ -352,5 +369,5 @@ def render_amr_frame_bands(fwd_args, image_height: int, image_width: int, bands:
     _host.amr_relevel(ib, image_height, image_width)
     frame = _host.amr_render_prebuilt(*fwd_args, gb, bb, ib, interpolate_image, False, gaze=gaze, band=band)
     if gather:
-        frame = gather_bands(frame, bands, 32, group)
+        frame = gather_bands(frame, bands, 32, group, dst)
     return frame, iv["n_intersections"], iv["levels"], (gb, bb, ib)

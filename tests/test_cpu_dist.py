@@ -105,6 +105,11 @@ def body_band_render_protocol(rank, world):
     mine[:, y0:y1] = truth[:, y0:y1]
     out = gdist.gather_bands(mine, bands, tile_px)
     assert torch.equal(out, truth)
+    # display-node form: only rank `dst` assembles the frame, from exactly-sized point-to-point blocks
+    dst = world - 1
+    got = gdist.gather_bands(mine.clone(), bands, tile_px, dst=dst)
+    if rank == dst:
+        assert torch.equal(got, truth)
 
 
 # ---- tests ---------------------------------------------------------------------------------------------------------
