@@ -460,29 +460,37 @@ def measure(impl, args, d, cams, rank, world, timer, full):
     out["dp_train"] = {"ms_per_step": ms / Kb, "views_per_s": world * Kb / (ms / 1e3),
                        "allreduce_bytes_per_step": 59 * 4 * P_ if world > 1 else 0, "bucket_bytes": reducer.bucket_bytes, "exchange": "dense"}
     if is_ours:
-        exch = gdist.ShGradExchange()
         e_ = impl.e
+        M_ = d["shs"].shape[1]
+        res = {}
+        for mode in ("dense_rows", "packed_rows"):
+            exch = gdist.ShGradExchange(packed=(mode == "packed_rows"))
 
-        def dp_step_rank1(i):
-            cam = cam_of(i)
-            N, img, radii, gb, bb, ib = impl.forward_c(cam)
-            M_ = d["shs"].shape[1]
-            # the all-gather of the clamped colour gradient + the SH rebuild start between the two backward phases and
-            # overlap the preprocess-stage backward; the 11-float all-reduce follows it
-            g = impl.host.rasterize_gaussians_backward(
-                d["bg"], d["means3D"], radii, e_, d["scales"], d["rotations"], 1.0, e_, cam.world_view_transform,
-                cam.full_proj_transform, cam.tanfovx, cam.tanfovy, w, d["shs"], d["sh_degree"], cam.camera_center, gb, N, bb, ib,
-                False, compact_sh=True,
-                between_phases=lambda drgb: exch.start_gather(drgb, cam.camera_center, d["means3D"], d["sh_degree"], M_))
-            exch.start_reduce([g[3], g[2], g[6], g[7]])            # means3D, opacity, scales, rotations
-            return exch.finish()
-        ms = timer.run(dp_step_rank1, Kb, 2)
-        pb = gdist.ShGradExchange.payload_bytes(P_, world)
-        out["dp_train_rank1_sh"] = {"ms_per_step": ms / Kb, "views_per_s": world * Kb / (ms / 1e3),
+            def dp_step_rank1(i, exch=exch):
+                cam = cam_of(i)
+                N, img, radii, gb, bb, ib = impl.forward_c(cam)
+                if exch.packed:     # the forward holds the visible count on the host; the ranks agree on the gather size meanwhile
+                    exch.post_visible_count(impl.host.last_counts(gb, P_)[2], dev)
+                # the all-gather of the clamped colour gradient + the SH rebuild start between the two backward phases and
+                # overlap the preprocess-stage backward; the 11-float all-reduce follows it
+                g = impl.host.rasterize_gaussians_backward(
+                    d["bg"], d["means3D"], radii, e_, d["scales"], d["rotations"], 1.0, e_, cam.world_view_transform,
+                    cam.full_proj_transform, cam.tanfovx, cam.tanfovy, w, d["shs"], d["sh_degree"], cam.camera_center, gb, N, bb, ib,
+                    False, compact_sh=True,
+                    between_phases=lambda drgb: exch.start_gather(drgb, cam.camera_center, d["means3D"], d["sh_degree"], M_, radii=radii))
+                exch.start_reduce([g[3], g[2], g[6], g[7]])            # means3D, opacity, scales, rotations
+                return exch.finish()
+            res[mode] = (timer.run(dp_step_rank1, Kb, 2) / Kb, exch.last_cap)
+        ms1, cap = res["packed_rows"]
+        pb = gdist.ShGradExchange.payload_bytes(P_, world, cap=cap)
+        out["dp_train_rank1_sh"] = {"ms_per_step": ms1, "views_per_s": world / (ms1 / 1e3),
                                     "allreduce_bytes_per_step": pb["allreduce"] if world > 1 else 0,
                                     "allgather_bytes_in_per_step": pb["allgather_in"] if world > 1 else 0,
-                                    "exchange": "rank-1 SH factor (3 floats/Gaussian/view gathered) + 11 floats all-reduced; "
-                                                "no autograd wrapper (the C-shaped backward is called directly)"}
+                                    "rows_per_view": cap, "ms_per_step_dense_rows": res["dense_rows"][0],
+                                    "exchange": "rank-1 SH factor: the 3-float rows of the visible Gaussians of every view gathered "
+                                                "(bit mask + prefix words locate them) + 11 floats all-reduced; no autograd wrapper "
+                                                "(the C-shaped backward is called directly); ms_per_step_dense_rows = the same with "
+                                                "all P rows gathered"}
 
     # ---- screen-tile bands (config C5 shape): ONE foveated frame split over the ranks by rows of 32-px tiles, balanced by the
     # previous frame's per-row pair counts; per-tile counts all-reduced so the AMR levels equal the single-GPU ones

@@ -79,6 +79,12 @@ SYMBOLS = {
                                      C.c_int, C.c_void_p, C.POINTER(GsrGrads), C.c_int, C.c_int, C.c_void_p]),
     "gsr_mark_visible": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "gsr_sh_grad_from_views": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "gsr_pack_meta_words": (C.c_size_t, [C.c_int]),
+    "gsr_pack_temp_bytes": (C.c_size_t, [C.c_int]),
+    "gsr_pack_visible_rows": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
+    "gsr_sh_grad_from_packed_views": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_size_t,
+                                                C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]),
+    "gsr_last_counts": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_longlong), C.POINTER(C.c_longlong), C.POINTER(C.c_longlong)]),
     "gsr_amr_forward": (C.c_int, [C.POINTER(GsrScene), C.POINTER(GsrCamera), C.c_int, C.c_void_p, C.c_void_p, C.c_void_p,
                                   C.c_void_p, C.c_int, C.POINTER(GsrGaze), ALLOC_FN, C.c_void_p, C.c_void_p, C.c_void_p,
                                   c_int_p, C.c_int, C.c_void_p]),

@@ -226,6 +226,59 @@ def sh_grad_from_views(means3D, cam_positions, dL_dcolors_clamped, degree, M):
     return out
 
 
+def last_counts(geomBuffer, P):
+    """(pairs, runs, visible Gaussians) of the forward this thread ran last on ``geomBuffer`` (gsr_last_counts): host
+    integers the forward already holds -- no device round trip."""
+    n, r, v = C.c_longlong(0), C.c_longlong(0), C.c_longlong(0)
+    rc = lib.gsr_last_counts(_p(geomBuffer), int(P), C.byref(n), C.byref(r), C.byref(v))
+    _capi.check(rc, "gsr_last_counts")
+    return int(n.value), int(r.value), int(v.value)
+
+
+def pack_meta_words(P):
+    return int(lib.gsr_pack_meta_words(int(P)))
+
+
+def pack_visible_rows(rows, radii, cap, out_rows=None, out_meta=None):
+    """rows [P,3] float32, radii [P] int32 -> (packed [cap,3], meta [pack_meta_words(P)] int32): the rows of the
+    Gaussians with radii > 0 in index order plus the mask / prefix words that locate them (gsr_pack_visible_rows)."""
+    P = int(rows.size(0))
+    r = _dev_tensor(rows, "rows")
+    rad = radii if (radii.dtype == torch.int32 and radii.is_contiguous()) else radii.to(torch.int32).contiguous()
+    if not rad.is_cuda or tuple(r.shape) != (P, 3) or int(rad.numel()) != P:
+        raise RuntimeError("pack_visible_rows: rows must be [P,3] float32 and radii [P] on the GPU")
+    cap = int(cap)
+    with torch.cuda.device(r.device):
+        packed = out_rows if out_rows is not None else torch.empty((cap, 3), dtype=torch.float32, device=r.device)
+        meta = out_meta if out_meta is not None else torch.empty((pack_meta_words(P),), dtype=torch.int32, device=r.device)
+        if packed.numel() < 3 * cap or meta.numel() < pack_meta_words(P) or not packed.is_contiguous() or not meta.is_contiguous():
+            raise RuntimeError("pack_visible_rows: output buffers too small")
+        tb = int(lib.gsr_pack_temp_bytes(P))
+        temp = torch.empty((max(tb, 4),), dtype=torch.uint8, device=r.device)
+        rc = lib.gsr_pack_visible_rows(P, _p(rad), _p(r), cap, _p(packed), _p(meta), _p(temp), tb, _stream())
+        _capi.check(rc, "gsr_pack_visible_rows")
+    return packed, meta
+
+
+def sh_grad_from_packed_views(means3D, cam_positions, meta, rows, degree, M):
+    """As sh_grad_from_views with every view's colour gradient packed by pack_visible_rows:
+    cam_positions [K,3], meta [K,L] int32 (L >= pack_meta_words(P)), rows [K,cap,3] -> dL_dsh [P,M,3]."""
+    P, K = int(means3D.size(0)), int(cam_positions.size(0))
+    m = _dev_tensor(means3D, "means3D")
+    cams = _dev_tensor(cam_positions, "cam_positions")
+    g = _dev_tensor(rows, "rows")
+    if meta.dtype != torch.int32 or not meta.is_cuda or not meta.is_contiguous() or meta.dim() != 2 or int(meta.size(0)) != K:
+        raise RuntimeError("meta must be a contiguous int32 [K, L] GPU tensor")
+    if g.dim() != 3 or int(g.size(0)) != K or int(g.size(2)) != 3:
+        raise RuntimeError(f"rows must have dimensions ({K}, cap, 3)")
+    with torch.cuda.device(m.device):
+        out = torch.empty((P, int(M), 3), dtype=torch.float32, device=m.device)
+        rc = lib.gsr_sh_grad_from_packed_views(P, int(degree), int(M), _p(m), K, _p(cams), _p(meta), int(meta.size(1)),
+                                               _p(g), int(g.size(1)), _p(out), _stream())
+        _capi.check(rc, "gsr_sh_grad_from_packed_views")
+    return out
+
+
 def mark_visible(means3D, viewmatrix, projmatrix):
     P = int(means3D.size(0))
     present = torch.empty((P,), dtype=torch.bool, device=means3D.device)

@@ -91,8 +91,8 @@ static int read_u32(const uint32_t* dev, uint32_t* host, int count, cudaStream_t
 // Header of the geometry buffer this host thread built last: lets the follow-up calls of the 5-step fovea protocol and
 // gsr_amr_render_prebuilt skip the blocking header read-back (and the pipeline bubble behind it) when they are handed
 // that same buffer, which is the only way the reference's Python ever calls them (gaussian_renderer_amr/__init__.py).
-struct LastBuild { const void* geom; int P; int N; };
-static thread_local LastBuild g_last_build = {nullptr, 0, 0};
+struct LastBuild { const void* geom; int P; int N; long long R; long long V; };
+static thread_local LastBuild g_last_build = {nullptr, 0, 0, 0, 0};
 
 static int geom_header(const void* geom, const GeomHeader* header, int P, int* N, cudaStream_t s) {
     if (geom == g_last_build.geom && P == g_last_build.P) { *N = g_last_build.N; return GSR_OK; }
@@ -135,7 +135,7 @@ static int build_lists(const gsr_scene* sc, const gsr_camera* cam, int mode, gsr
                        int* radii_user, void** geom_out, void** bin_out, void** img_out, int* N_out, bool debug, cudaStream_t s) {
     const int P = sc->P, W = cam->width, H = cam->height;
     const size_t gbytes = gsr_geom_bytes(P), ibytes = gsr_image_bytes(W, H, mode);
-    g_last_build = {nullptr, 0, 0};
+    g_last_build = {nullptr, 0, 0, 0, 0};
     void* geom = alloc(user, GSR_BUF_GEOM, gbytes);
     void* img = alloc(user, GSR_BUF_IMAGE, ibytes);
     if (!geom || !img) { set_error("allocation callback returned NULL"); return GSR_ERR_ALLOC; }
@@ -236,7 +236,7 @@ static int build_lists(const gsr_scene* sc, const gsr_camera* cam, int mode, gsr
     launch_expand_runs(b, rk_sorted, rv_sorted, R, im.tiles_x, im.tiles_y, row_offsets, im.ranges, im.n_intersections, GSR_PROF_RANGES, GSR_PROF_EXPAND, s);
     if ((rc = check_last("expand runs", debug, s))) return rc;
     *geom_out = geom; *bin_out = bin; *img_out = img; *N_out = (int)N;
-    g_last_build = {geom, P, (int)N};
+    g_last_build = {geom, P, (int)N, R, (long long)hdr[5]};
     return GSR_OK;
 }
 
@@ -472,9 +472,45 @@ int gsr_sh_grad_from_views(int P, int sh_degree, int sh_coeffs, const float* mea
                            const float* cam_positions, const float* dL_dcolors_clamped, float* dL_dsh, void* stream) {
     if (P < 0 || num_views < 0 || sh_degree < 0 || sh_degree > 3) { set_error("sh_grad_from_views: bad sizes"); return GSR_ERR_INVALID; }
     if (P > 0 && (!means3D || !dL_dsh || (num_views > 0 && (!cam_positions || !dL_dcolors_clamped)))) { set_error("sh_grad_from_views: null pointer"); return GSR_ERR_INVALID; }
-    int rc = launch_sh_grad_from_views(P, sh_degree, sh_coeffs, means3D, num_views, cam_positions, dL_dcolors_clamped, dL_dsh, (cudaStream_t)stream);
+    int rc = launch_sh_grad_from_views(P, sh_degree, sh_coeffs, means3D, num_views, cam_positions, dL_dcolors_clamped, nullptr, 0, 0, dL_dsh, (cudaStream_t)stream);
     if (rc) return rc;
     return check_last("sh_grad_from_views", false, (cudaStream_t)stream);
+}
+
+size_t gsr_pack_meta_words(int P) { return P < 0 ? 0 : 2 * (size_t)((P + 31) / 32); }
+size_t gsr_pack_temp_bytes(int P) { return P < 0 ? 0 : pack_temp_bytes(P); }
+
+int gsr_pack_visible_rows(int P, const int* radii, const float* rows_in, int cap, float* rows_out, uint32_t* meta,
+                          void* temp, size_t temp_bytes, void* stream) {
+    if (P < 0 || cap < 0) { set_error("pack_visible_rows: bad sizes"); return GSR_ERR_INVALID; }
+    if (P == 0) return GSR_OK;
+    if (!radii || !rows_in || !meta || !temp || (cap > 0 && !rows_out)) { set_error("pack_visible_rows: null pointer"); return GSR_ERR_INVALID; }
+    if (temp_bytes < pack_temp_bytes(P)) { set_error("pack_visible_rows: temp too small (%zu < %zu)", temp_bytes, pack_temp_bytes(P)); return GSR_ERR_INVALID; }
+    const int W32 = (P + 31) / 32;
+    int rc = launch_pack_visible_rows(P, radii, rows_in, cap, rows_out, meta, meta + W32, (uint32_t*)temp, (cudaStream_t)stream);
+    if (rc) return rc;
+    return check_last("pack_visible_rows", false, (cudaStream_t)stream);
+}
+
+int gsr_sh_grad_from_packed_views(int P, int sh_degree, int sh_coeffs, const float* means3D, int num_views, const float* cam_positions,
+                                  const uint32_t* meta, size_t meta_stride_words, const float* rows, int cap, float* dL_dsh, void* stream) {
+    if (P < 0 || num_views < 0 || cap < 0 || sh_degree < 0 || sh_degree > 3) { set_error("sh_grad_from_packed_views: bad sizes"); return GSR_ERR_INVALID; }
+    if (P > 0 && (!means3D || !dL_dsh || (num_views > 0 && (!cam_positions || !meta || (cap > 0 && !rows))))) { set_error("sh_grad_from_packed_views: null pointer"); return GSR_ERR_INVALID; }
+    if (meta_stride_words < gsr_pack_meta_words(P) || meta_stride_words > 0x7fffffffull) { set_error("sh_grad_from_packed_views: meta stride too small"); return GSR_ERR_INVALID; }
+    if (num_views == 0) return gsr_sh_grad_from_views(P, sh_degree, sh_coeffs, means3D, 0, nullptr, nullptr, dL_dsh, stream);
+    int rc = launch_sh_grad_from_views(P, sh_degree, sh_coeffs, means3D, num_views, cam_positions, rows, meta, (int)meta_stride_words, cap, dL_dsh, (cudaStream_t)stream);
+    if (rc) return rc;
+    return check_last("sh_grad_from_packed_views", false, (cudaStream_t)stream);
+}
+
+int gsr_last_counts(const void* geom_buffer, int P, long long* num_rendered, long long* num_runs, long long* num_visible) {
+    if (!geom_buffer || geom_buffer != g_last_build.geom || P != g_last_build.P) {
+        set_error("last_counts: not the geometry buffer this thread built last"); return GSR_ERR_INVALID;
+    }
+    if (num_rendered) *num_rendered = g_last_build.N;
+    if (num_runs) *num_runs = g_last_build.R;
+    if (num_visible) *num_visible = g_last_build.V;
+    return GSR_OK;
 }
 
 int gsr_view_geom(const void* geom_buffer, int P, gsr_geom_view* out) {

@@ -249,7 +249,11 @@ struct PreprocessArgs {
 void launch_preprocess(const PreprocessArgs& a, const GeomPtrs& g, cudaStream_t s);
 void launch_block_scan(const GeomPtrs& g, int P, uint32_t* mailbox_dev, cudaStream_t s);
 void launch_clamped_rgb(int P, const int* radii, const float* scratch, const unsigned char* clamped, bool colors_from_sh, float* out, cudaStream_t s);
-int launch_sh_grad_from_views(int P, int D, int M, const float* means3D, int K, const float* cams, const float* g_all, float* dL_dsh, cudaStream_t s);
+int launch_sh_grad_from_views(int P, int D, int M, const float* means3D, int K, const float* cams, const float* g_all,
+                              const uint32_t* meta, int meta_stride, int cap, float* dL_dsh, cudaStream_t s);   // meta == nullptr: dense [K,P,3]
+size_t pack_temp_bytes(int P);
+int launch_pack_visible_rows(int P, const int* radii, const float* src, int cap, float* rows, uint32_t* mask, uint32_t* prefix,
+                             uint32_t* temp, cudaStream_t s);
 void launch_mark_visible(int P, const float* means3D, const float* view, const float* proj, unsigned char* present, cudaStream_t s);
 
 struct SortPlan {

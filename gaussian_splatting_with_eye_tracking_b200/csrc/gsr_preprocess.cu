@@ -725,8 +725,12 @@ void launch_preprocess_backward(const PreBwdArgs& a, cudaStream_t s) {
 // view-parallel step from 59 to 14 floats per Gaussian; this kernel rebuilds the sum.  Rows leave through shared
 // memory as whole 6 KB warp segments (same staging as the backward).
 // ------------------------------------------------------------------------------------------------
+// PACKED: g_all holds, per view, only the rows of the Gaussians whose bit is set in that view's mask ([K][cap][3], index
+// order); meta holds per view `meta_stride` words: mask words [W32], then the number of set bits before each word [W32].
+template <bool PACKED>
 __global__ void __launch_bounds__(256) sh_grad_from_views_kernel(int P, int D, int M, const float* __restrict__ means3D, int K,
                                                                  const float* __restrict__ cams, const float* __restrict__ g_all,
+                                                                 const uint32_t* __restrict__ meta, int meta_stride, int W32, int cap,
                                                                  float* __restrict__ dL_dsh) {
     extern __shared__ float s_rows[];            // [256][kShStride]
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
@@ -739,7 +743,17 @@ __global__ void __launch_bounds__(256) sh_grad_from_views_kernel(int P, int D, i
     if (valid) {
         const float mx = __ldg(means3D + 3 * (size_t)idx), my = __ldg(means3D + 3 * (size_t)idx + 1), mz = __ldg(means3D + 3 * (size_t)idx + 2);
         for (int v = 0; v < K; ++v) {
-            const float* g = g_all + ((size_t)v * P + idx) * 3;
+            const float* g;
+            if (PACKED) {
+                const uint32_t* mv = meta + (size_t)v * meta_stride;
+                const uint32_t word = __ldg(mv + (idx >> 5));
+                if (!((word >> (idx & 31)) & 1u)) continue;
+                const uint32_t slot = __ldg(mv + W32 + (idx >> 5)) + __popc(word & ((1u << (idx & 31)) - 1u));
+                if (slot >= (uint32_t)cap) continue;                    // cannot happen with a consistent pack; never read out of bounds
+                g = g_all + ((size_t)v * cap + slot) * 3;
+            } else {
+                g = g_all + ((size_t)v * P + idx) * 3;
+            }
             const float g0 = __ldg(g), g1 = __ldg(g + 1), g2 = __ldg(g + 2);
             if (g0 == 0.f && g1 == 0.f && g2 == 0.f) continue;          // culled or fully clamped in this view
             const float ox = mx - __ldg(cams + 3 * v), oy = my - __ldg(cams + 3 * v + 1), oz = mz - __ldg(cams + 3 * v + 2);
@@ -792,16 +806,112 @@ __global__ void __launch_bounds__(256) sh_grad_from_views_kernel(int P, int D, i
     }
 }
 
-int launch_sh_grad_from_views(int P, int D, int M, const float* means3D, int K, const float* cams, const float* g_all, float* dL_dsh, cudaStream_t s) {
+int launch_sh_grad_from_views(int P, int D, int M, const float* means3D, int K, const float* cams, const float* g_all,
+                              const uint32_t* meta, int meta_stride, int cap, float* dL_dsh, cudaStream_t s) {
     if (P <= 0) return GSR_OK;
     if (M <= 0 || M > 16 || (M % 4) != 0 || ((size_t)dL_dsh & 15) != 0) {
         set_error("sh_grad_from_views: needs 0 < M <= 16, M %% 4 == 0 and a 16-byte aligned output (M=%d)", M); return GSR_ERR_INVALID;
     }
     const int smem = 256 * kShStride * (int)sizeof(float);
     static bool attr_done = false;
-    if (!attr_done) { cudaFuncSetAttribute(sh_grad_from_views_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem); attr_done = true; }
-    sh_grad_from_views_kernel<<<(P + 255) / 256, 256, smem, s>>>(P, D, M, means3D, K, cams, g_all, dL_dsh);
+    if (!attr_done) {
+        cudaFuncSetAttribute(sh_grad_from_views_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        cudaFuncSetAttribute(sh_grad_from_views_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        attr_done = true;
+    }
+    if (meta) sh_grad_from_views_kernel<true><<<(P + 255) / 256, 256, smem, s>>>(P, D, M, means3D, K, cams, g_all, meta, meta_stride, (P + 31) / 32, cap, dL_dsh);
+    else sh_grad_from_views_kernel<false><<<(P + 255) / 256, 256, smem, s>>>(P, D, M, means3D, K, cams, g_all, nullptr, 0, 0, 0, dL_dsh);
     count_launch();
+    return GSR_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// gsr_pack_visible_rows: rows of src [P,3] of the Gaussians with radii > 0, in index order, plus the bit mask and the
+// per-word exclusive popcount prefix that let a reader find a Gaussian's row (see sh_grad_from_views_kernel<true>).
+// Three small launches: per-1024 counts + mask words, one-CTA scan of the counts, scatter.
+// ------------------------------------------------------------------------------------------------
+constexpr int kPackBlock = 1024;
+
+__global__ void __launch_bounds__(kPackBlock) pack_mask_kernel(int P, const int* __restrict__ radii, uint32_t* __restrict__ mask,
+                                                                uint32_t* __restrict__ prefix, uint32_t* __restrict__ block_counts) {
+    __shared__ uint32_t s_cnt[kPackBlock / 32];
+    const int idx = blockIdx.x * kPackBlock + threadIdx.x, lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const bool vis = idx < P && radii[idx] > 0;
+    const uint32_t word = __ballot_sync(0xffffffffu, vis);
+    if (lane == 0) s_cnt[wid] = __popc(word);
+    __syncthreads();
+    if (wid == 0) {
+        const uint32_t c = s_cnt[lane];
+        uint32_t inc = c;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { const uint32_t t = __shfl_up_sync(0xffffffffu, inc, d); if (lane >= d) inc += t; }
+        s_cnt[lane] = inc - c;                                    // exclusive, local to the block
+        if (lane == 31) block_counts[blockIdx.x] = inc;
+    }
+    __syncthreads();
+    if (lane == 0 && (idx >> 5) < (P + 31) / 32) { mask[idx >> 5] = word; prefix[idx >> 5] = s_cnt[wid]; }
+}
+
+__global__ void __launch_bounds__(1024) pack_scan_kernel(uint32_t* __restrict__ block_counts, int n) {
+    // in-place exclusive scan of n block counts by one CTA (n = P/1024: a few thousand)
+    __shared__ uint32_t s_w[32];
+    __shared__ uint32_t s_carry;
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    if (tid == 0) s_carry = 0;
+    __syncthreads();
+    for (int base = 0; base < n; base += 1024) {
+        const int i = base + tid;
+        const uint32_t v = i < n ? block_counts[i] : 0u;
+        uint32_t inc = v;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { const uint32_t t = __shfl_up_sync(0xffffffffu, inc, d); if (lane >= d) inc += t; }
+        if (lane == 31) s_w[wid] = inc;
+        __syncthreads();
+        if (wid == 0) {
+            const uint32_t w = s_w[lane];
+            uint32_t winc = w;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) { const uint32_t t = __shfl_up_sync(0xffffffffu, winc, d); if (lane >= d) winc += t; }
+            s_w[lane] = winc - w;
+        }
+        __syncthreads();
+        const uint32_t carry = s_carry;
+        if (i < n) block_counts[i] = carry + s_w[wid] + inc - v;
+        __syncthreads();
+        if (tid == 1023) s_carry = carry + s_w[31] + inc;
+        __syncthreads();
+    }
+    if (tid == 0) block_counts[n] = s_carry;                      // total, for the caller's consistency check
+}
+
+__global__ void __launch_bounds__(kPackBlock) pack_scatter_kernel(int P, const float* __restrict__ src, const uint32_t* __restrict__ mask,
+                                                                   uint32_t* __restrict__ prefix, const uint32_t* __restrict__ block_offsets,
+                                                                   int cap, float* __restrict__ rows) {
+    const int idx = blockIdx.x * kPackBlock + threadIdx.x, lane = threadIdx.x & 31;
+    if (idx >= ((P + 31) / 32) * 32) return;                      // whole warps stay: the word's lane 0 finalises the prefix
+    const uint32_t word = mask[idx >> 5];
+    const uint32_t base = block_offsets[blockIdx.x] + prefix[idx >> 5];
+    __syncwarp();
+    if (lane == 0) prefix[idx >> 5] = base;                       // now global: set bits before this word
+    if (idx < P && ((word >> lane) & 1u)) {
+        const uint32_t slot = base + __popc(word & ((1u << lane) - 1u));
+        if (slot < (uint32_t)cap) {
+            const size_t i3 = 3 * (size_t)idx, o3 = 3 * (size_t)slot;
+            rows[o3] = src[i3]; rows[o3 + 1] = src[i3 + 1]; rows[o3 + 2] = src[i3 + 2];
+        }
+    }
+}
+
+size_t pack_temp_bytes(int P) { return sizeof(uint32_t) * ((size_t)(P + kPackBlock - 1) / kPackBlock + 1); }
+
+int launch_pack_visible_rows(int P, const int* radii, const float* src, int cap, float* rows, uint32_t* mask, uint32_t* prefix,
+                             uint32_t* temp, cudaStream_t s) {
+    if (P <= 0) return GSR_OK;
+    const int nb = (P + kPackBlock - 1) / kPackBlock;
+    pack_mask_kernel<<<nb, kPackBlock, 0, s>>>(P, radii, mask, prefix, temp);
+    pack_scan_kernel<<<1, 1024, 0, s>>>(temp, nb);
+    pack_scatter_kernel<<<nb, kPackBlock, 0, s>>>(P, src, mask, prefix, temp, cap, rows);
+    count_launch(); count_launch(); count_launch();
     return GSR_OK;
 }
 

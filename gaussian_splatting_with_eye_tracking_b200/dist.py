@@ -147,15 +147,29 @@ class ShGradExchange:
     The sum runs over ranks in rank order on every rank, so the SH gradient is bit-identical everywhere.
     """
 
-    def __init__(self, rebuild=None, bucket_bytes: int = DEFAULT_BUCKET_BYTES, group=None):
+    def __init__(self, rebuild=None, bucket_bytes: int = DEFAULT_BUCKET_BYTES, group=None, packed: bool = False,
+                 pack=None, rebuild_packed=None):
+        """``packed``: only the rows of the Gaussians visible in a view (radii > 0) travel, with a bit mask and a
+        per-word prefix that locate them (``pack`` = _host.pack_visible_rows, ``rebuild_packed`` =
+        _host.sh_grad_from_packed_views; both injectable for the CPU protocol tests).  The ranks must then call
+        ``post_visible_count`` after their forward: the all-gather is sized by the largest count."""
         self.group = group
         self.reducer = GradientAllReduce(bucket_bytes, group)
         self._rebuild = rebuild
+        self.packed = bool(packed)
+        self._pack = pack
+        self._rebuild_packed = rebuild_packed
         self._gathered = None
         self._cams = None
         self._stream = None
         self._dsh = None
         self._keep = None
+        self._send_rows = None
+        self._send_meta = None
+        self._meta_all = None
+        self._counts = None
+        self._counts_event = None
+        self.last_cap = 0
 
     def _comm(self, dev):
         if dev.type != "cuda":
@@ -164,13 +178,55 @@ class ShGradExchange:
             self._stream = torch.cuda.Stream(device=dev)
         return self._stream
 
-    def start_gather(self, dL_dcolors_clamped: torch.Tensor, campos: torch.Tensor, means3D: torch.Tensor, degree: int, M: int) -> None:
+    # ---- packed mode: agree on the capacity of the row gather ----
+    def post_visible_count(self, num_visible: int, device) -> None:
+        """Start (side stream) the exchange of this rank's visible-Gaussian count; call right after the forward, which
+        holds the number on the host (_host.last_counts).  start_gather reads the result -- long finished by then."""
+        w = world_size()
+        dev = torch.device(device)
+        if w == 1:
+            self._counts, self._counts_event = torch.tensor([int(num_visible)], dtype=torch.int64), None
+            return
+        if dev.type != "cuda":
+            mine = torch.tensor([int(num_visible)], dtype=torch.int64)
+            allc = torch.empty((w,), dtype=torch.int64)
+            dist.all_gather_into_tensor(allc, mine, group=self.group)
+            self._counts, self._counts_event = allc, None
+            return
+        if self._counts is None or not self._counts.is_pinned() or self._counts.numel() != w + 1:
+            self._counts = torch.empty((w + 1,), dtype=torch.int64).pin_memory()
+        if self._counts_event is not None:
+            self._counts_event.synchronize()            # the previous exchange still owns the pinned words
+        self._counts[w] = int(num_visible)
+        comm = self._comm(dev)
+        with torch.cuda.stream(comm):
+            mine = self._counts[w:].to(dev, non_blocking=True)
+            allc = torch.empty((w,), dtype=torch.int64, device=dev)
+            dist.all_gather_into_tensor(allc, mine, group=self.group)
+            self._counts[:w].copy_(allc, non_blocking=True)
+            self._counts_event = torch.cuda.Event()
+            self._counts_event.record(comm)
+
+    def _capacity(self, P: int) -> int:
+        if self._counts is None:
+            raise RuntimeError("ShGradExchange(packed=True): call post_visible_count() after the forward")
+        if self._counts_event is not None:
+            self._counts_event.synchronize()
+        w = world_size()
+        most = int(self._counts[:w].max()) if w > 1 else int(self._counts[0])
+        return min(int(P), max(256, (most + 255) // 256 * 256))
+
+    def start_gather(self, dL_dcolors_clamped: torch.Tensor, campos: torch.Tensor, means3D: torch.Tensor, degree: int, M: int,
+                     radii: Optional[torch.Tensor] = None) -> None:
         """Queue (on the side stream) the all-gather of this rank's clamped colour gradient [P,3] and camera position,
         followed by the rebuild of the summed SH gradient.  Returns immediately: called between the two backward
-        phases (``_host.rasterize_gaussians_backward(..., between_phases=...)``) it overlaps the preprocess stage."""
+        phases (``_host.rasterize_gaussians_backward(..., between_phases=...)``) it overlaps the preprocess stage.
+        Packed mode needs ``radii`` (the forward's) and a posted visible count."""
         w = world_size()
         P = dL_dcolors_clamped.shape[0]
         dev = dL_dcolors_clamped.device
+        if self.packed:
+            return self._start_gather_packed(dL_dcolors_clamped, campos, means3D, degree, M, radii, w, P, dev)
         if self._gathered is None or self._gathered.shape != (w, P, 3) or self._gathered.device != dev:
             self._gathered = torch.empty((w, P, 3), dtype=dL_dcolors_clamped.dtype, device=dev)
             self._cams = torch.empty((w, 3), dtype=campos.dtype, device=dev)
@@ -192,13 +248,48 @@ class ShGradExchange:
                     wk.wait()                                 # blocks the side stream only (the host for gloo)
             self._dsh = rebuild(means3D, self._cams, self._gathered, degree, M)
 
+    def _start_gather_packed(self, g, campos, means3D, degree, M, radii, w, P, dev):
+        if radii is None:
+            raise RuntimeError("ShGradExchange(packed=True).start_gather needs the forward's radii")
+        cap = self._capacity(P)
+        self.last_cap = cap
+        L = packed_meta_words(P)
+        if self._send_rows is None or self._send_rows.shape != (P, 3) or self._send_rows.device != dev:
+            self._send_rows = torch.empty((P, 3), dtype=torch.float32, device=dev)
+            self._send_meta = torch.empty((L + 4,), dtype=torch.int32, device=dev)      # + camera position (3 float words) + pad
+            self._gathered = torch.empty((w * P * 3,), dtype=torch.float32, device=dev)  # worst case; a [w,cap,3] prefix is used
+            self._meta_all = torch.empty((w, L + 4), dtype=torch.int32, device=dev)
+        pack, rebuild = self._pack, self._rebuild_packed
+        if pack is None or rebuild is None:
+            from . import _host
+            pack = pack or _host.pack_visible_rows
+            rebuild = rebuild or _host.sh_grad_from_packed_views
+        comm = self._comm(dev)
+        if comm is not None:
+            comm.wait_stream(torch.cuda.current_stream(dev))
+        self._keep = (g, campos, radii)
+        with (torch.cuda.stream(comm) if comm is not None else _null()):
+            rows = self._send_rows[:cap]
+            pack(g, radii, cap, rows, self._send_meta[:L])
+            self._send_meta[L:L + 3].view(torch.float32).copy_(campos.reshape(3))
+            rows_all = self._gathered[: w * cap * 3]
+            if w == 1:
+                rows_all.copy_(rows.reshape(-1)); self._meta_all[0].copy_(self._send_meta)
+            else:
+                works = [dist.all_gather_into_tensor(rows_all, rows.reshape(-1), group=self.group, async_op=True),
+                         dist.all_gather_into_tensor(self._meta_all.view(-1), self._send_meta, group=self.group, async_op=True)]
+                for wk in works:
+                    wk.wait()
+            cams = self._meta_all[:, L:L + 3].contiguous().view(torch.float32)
+            self._dsh = rebuild(means3D, cams, self._meta_all, rows_all.view(w, cap, 3), degree, M)
+
     def start_reduce(self, dense_grads: Sequence[torch.Tensor]) -> None:
         """Queue the in-place SUM of the remaining gradients (means3D, opacity, scales, rotations)."""
         self.reducer.start(dense_grads)
 
     def start(self, dense_grads: Sequence[torch.Tensor], dL_dcolors_clamped: torch.Tensor, campos: torch.Tensor,
-              means3D: torch.Tensor, degree: int, M: int) -> None:
-        self.start_gather(dL_dcolors_clamped, campos, means3D, degree, M)
+              means3D: torch.Tensor, degree: int, M: int, radii: Optional[torch.Tensor] = None) -> None:
+        self.start_gather(dL_dcolors_clamped, campos, means3D, degree, M, radii)
         self.start_reduce(dense_grads)
 
     def finish(self) -> torch.Tensor:
@@ -212,8 +303,15 @@ class ShGradExchange:
         return dsh
 
     @staticmethod
-    def payload_bytes(P: int, world: int, itemsize: int = 4) -> dict:
-        return {"allreduce": 11 * itemsize * P, "allgather_in": 3 * itemsize * P * world, "dense_allreduce_equivalent": 59 * itemsize * P}
+    def payload_bytes(P: int, world: int, itemsize: int = 4, cap: Optional[int] = None) -> dict:
+        """Bytes per rank and step; ``cap`` = rows per view in packed mode (None: dense [P,3] rows)."""
+        gathered = 3 * itemsize * P * world if cap is None else (3 * itemsize * cap + 4 * (packed_meta_words(P) + 4)) * world
+        return {"allreduce": 11 * itemsize * P, "allgather_in": gathered, "dense_allreduce_equivalent": 59 * itemsize * P}
+
+
+def packed_meta_words(P: int) -> int:
+    """Words of (mask, prefix) metadata per view in the packed row exchange (= gsr_pack_meta_words)."""
+    return 2 * ((int(P) + 31) // 32)
 
 
 def _coalesce_adjacent(flats: List[torch.Tensor]) -> List[torch.Tensor]:

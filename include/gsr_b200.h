@@ -248,6 +248,24 @@ GSR_API int gsr_profile_read(float* ms, int* counts);
 GSR_API int gsr_sh_grad_from_views(int P, int sh_degree, int sh_coeffs, const float* means3D, int num_views,
                                    const float* cam_positions, const float* dL_dcolors_clamped, float* dL_dsh, void* stream);
 
+/* ---- the same exchange with only the visible Gaussians' rows on the wire ----
+ * gsr_pack_visible_rows: rows_out[slot] = rows_in[g] ([.,3] floats) for the Gaussians with radii[g] > 0, slots in index
+ *   order; meta [gsr_pack_meta_words(P)] = ceil(P/32) mask words (bit g%32 of word g/32) followed by ceil(P/32) words
+ *   "set bits before this word".  Rows whose slot >= cap are dropped (size cap from num_visible, gsr_last_counts).
+ *   temp: gsr_pack_temp_bytes(P) bytes of device scratch.  Every view's (rows, meta) then travels instead of [P,3].
+ * gsr_sh_grad_from_packed_views: gsr_sh_grad_from_views reading view v's rows at rows + v*cap*3 and its meta at
+ *   meta + v*meta_stride_words; a Gaussian whose bit is clear in a view contributes nothing from it.
+ * gsr_last_counts: totals of the forward this host thread ran last on `geom_buffer` (from the header mailbox, no
+ *   device round trip): pairs, (Gaussian, tile-row) runs, visible Gaussians.  GSR_ERR_INVALID for any other buffer. */
+GSR_API size_t gsr_pack_meta_words(int P);
+GSR_API size_t gsr_pack_temp_bytes(int P);
+GSR_API int gsr_pack_visible_rows(int P, const int* radii, const float* rows_in, int cap, float* rows_out, uint32_t* meta,
+                                  void* temp, size_t temp_bytes, void* stream);
+GSR_API int gsr_sh_grad_from_packed_views(int P, int sh_degree, int sh_coeffs, const float* means3D, int num_views,
+                                          const float* cam_positions, const uint32_t* meta, size_t meta_stride_words,
+                                          const float* rows, int cap, float* dL_dsh, void* stream);
+GSR_API int gsr_last_counts(const void* geom_buffer, int P, long long* num_rendered, long long* num_runs, long long* num_visible);
+
 /* ---- tuning knobs (results never depend on them) ---- */
 enum { GSR_OPT_SORT_VARIANT = 0,  /* onesweep tile shape for u32 keys: 0 = default, 1..5 see gsr_binning.cu */
        GSR_OPT_BLEND_VARIANT = 1  /* forward blend: 0 = two pixels per thread, packed FP32x2 (default); 1 = one pixel per thread */ };

@@ -168,6 +168,91 @@ def body_sh_grad_exchange(rank, world):
     assert pb["allreduce"] + pb["allgather_in"] < pb["dense_allreduce_equivalent"]
 
 
+def _pack_ref(rows, radii, cap, out_rows, out_meta):
+    """torch restatement of gsr_pack_visible_rows (mask words, exclusive per-word popcount prefix, rows in index order)."""
+    P = rows.shape[0]
+    W32 = (P + 31) // 32
+    vis = (radii > 0)
+    bits = torch.zeros(W32 * 32, dtype=torch.int64); bits[:P] = vis.to(torch.int64)
+    words = (bits.view(W32, 32) << torch.arange(32)).sum(1)
+    counts = bits.view(W32, 32).sum(1)
+    prefix = torch.cumsum(counts, 0) - counts
+    words = torch.where(words >= 2 ** 31, words - 2 ** 32, words)
+    out_meta[:W32] = words.to(torch.int32); out_meta[W32:2 * W32] = prefix.to(torch.int32)
+    packed = rows[vis][:cap]
+    out_rows[: packed.shape[0]] = packed
+    return out_rows, out_meta
+
+
+def _rebuild_packed_ref(means3D, cams, meta_all, rows_all, degree, M):
+    P = means3D.shape[0]
+    W32 = (P + 31) // 32
+    K, cap = rows_all.shape[0], rows_all.shape[1]
+    dense = torch.zeros(K, P, 3, dtype=rows_all.dtype)
+    idx = torch.arange(P)
+    for v in range(K):
+        words = meta_all[v, :W32].to(torch.int64) & 0xffffffff
+        prefix = meta_all[v, W32:2 * W32].to(torch.int64)
+        w = words[idx >> 5]
+        bit = (w >> (idx & 31)) & 1
+        below = w & ((torch.ones_like(idx) << (idx & 31)) - 1)
+        pop = torch.tensor([bin(int(x)).count("1") for x in below])
+        slot = prefix[idx >> 5] + pop
+        sel = (bit == 1) & (slot < cap)
+        dense[v, sel] = rows_all[v, slot[sel]]
+    return _rebuild_ref(means3D, cams, dense, degree, M)
+
+
+def body_sh_grad_exchange_packed(rank, world):
+    P, M, deg = 717, 16, 3          # not a multiple of 32: ragged last mask word
+    gen = torch.Generator().manual_seed(7)
+    means = torch.randn(P, 3, generator=gen)
+
+    def view(r):
+        g = torch.Generator().manual_seed(300 + r)
+        cam = torch.randn(3, generator=g) * 4
+        radii = (torch.rand(P, generator=g) < (0.3 + 0.2 * r)).to(torch.int32) * 5       # different counts per rank
+        drgb = torch.randn(P, 3, generator=g) * (radii > 0)[:, None]
+        drgb[torch.rand(P, generator=g) < 0.1] = 0          # visible, but no colour gradient
+        dense = [torch.randn(P, 3, generator=g), torch.randn(P, 1, generator=g), torch.randn(P, 3, generator=g), torch.randn(P, 4, generator=g)]
+        return cam, drgb, dense, radii
+    for step in range(2):            # buffers and the pinned count words are reused across steps
+        cam, drgb, dense, radii = view(rank)
+        ex = body_sh_grad_exchange_packed.ex = getattr(body_sh_grad_exchange_packed, "ex", None) or gdist.ShGradExchange(
+            packed=True, pack=_pack_ref, rebuild_packed=_rebuild_packed_ref, bucket_bytes=4096)
+        ex.post_visible_count(int((radii > 0).sum()), "cpu")
+        ex.start_gather(drgb, cam, means, deg, M, radii=radii)
+        ex.start_reduce(dense)
+        dsh = ex.finish()
+        most = max(int((view(r)[3] > 0).sum()) for r in range(world))
+        assert ex.last_cap == min(P, max(256, (most + 255) // 256 * 256))
+        want_sh = sum(_rebuild_ref(means, view(r)[0][None], view(r)[1][None], deg, M) for r in range(world))
+        assert torch.allclose(dsh, want_sh, rtol=1e-5, atol=1e-6)
+        for i in range(4):
+            want = sum(view(r)[2][i] for r in range(world))
+            assert torch.allclose(dense[i], want, rtol=1e-6, atol=1e-6), i
+        mine = dsh.clone()
+        dist.broadcast(dsh, src=0)
+        assert torch.equal(mine, dsh)
+    pb = gdist.ShGradExchange.payload_bytes(P, world, cap=ex.last_cap)
+    assert pb["allgather_in"] <= gdist.ShGradExchange.payload_bytes(P, world)["allgather_in"] + 4 * world * (gdist.packed_meta_words(P) + 4)
+    # without a posted count the packed exchange refuses to guess a capacity
+    ex2 = gdist.ShGradExchange(packed=True, pack=_pack_ref, rebuild_packed=_rebuild_packed_ref)
+    try:
+        ex2.start_gather(drgb, cam, means, deg, M, radii=radii)
+        raise AssertionError("expected RuntimeError")
+    except RuntimeError:
+        pass
+
+
+def test_sh_grad_exchange_packed_gloo_world2():
+    _run("body_sh_grad_exchange_packed", 2)
+
+
+def test_sh_grad_exchange_packed_gloo_world3():
+    _run("body_sh_grad_exchange_packed", 3)
+
+
 def test_gradient_allreduce_gloo_world2():
     _run("body_gradient_allreduce")
 

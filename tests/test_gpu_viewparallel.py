@@ -85,3 +85,66 @@ def test_two_phase_backward_matches_single_call_and_hook_sees_final_tensor():
     assert torch.equal(seen["at_hook"], two[5])          # not rewritten by the second phase
     for i in range(8):
         _close(two[i], one[i], f"grad[{i}] two-phase vs single call")
+
+
+def test_last_counts_match_the_forward_outputs():
+    from gaussian_splatting_with_eye_tracking_b200 import _host
+    sc, cam = common.make_case("small")
+    d, camd = common.cuda_inputs(sc, cam)
+    N, color, radii, geom, binning, img = _host.rasterize_gaussians(*common.fwd_args(d, camd), False)
+    n, r, v = _host.last_counts(geom, d["means3D"].shape[0])
+    assert n == N and v == int((radii > 0).sum()) and 0 < v <= r <= n
+    with pytest.raises(RuntimeError):
+        _host.last_counts(binning, d["means3D"].shape[0])          # not the geometry buffer of the last forward
+
+
+@pytest.mark.parametrize("P", [1, 31, 32, 1000, 1025, 70001])
+def test_pack_visible_rows_layout(P):
+    """mask word g/32 bit g%32, prefix = set bits before the word, rows in index order (bit-exact copies)."""
+    from gaussian_splatting_with_eye_tracking_b200 import _host
+    gen = torch.Generator().manual_seed(P)
+    radii = ((torch.rand(P, generator=gen) < 0.4).to(torch.int32) * 7).cuda()
+    rows = torch.randn(P, 3, generator=gen).cuda()
+    V = int((radii > 0).sum())
+    for cap in (V, V + 13, max(0, V - 5)):
+        packed, meta = _host.pack_visible_rows(rows, radii, cap)
+        torch.cuda.synchronize()
+        W32 = (P + 31) // 32
+        assert meta.numel() == 2 * W32 == _host.pack_meta_words(P)
+        bits = torch.zeros(W32 * 32, dtype=torch.int64); bits[:P] = (radii > 0).cpu().to(torch.int64)
+        words = (bits.view(W32, 32) << torch.arange(32)).sum(1)
+        counts = bits.view(W32, 32).sum(1)
+        assert torch.equal(meta[:W32].cpu().to(torch.int64) & 0xffffffff, words)
+        assert torch.equal(meta[W32:].cpu().to(torch.int64), torch.cumsum(counts, 0) - counts)
+        want = rows[radii > 0][:cap]
+        assert torch.equal(packed[: want.shape[0]], want)
+
+
+def test_packed_rebuild_is_bit_identical_to_dense_rebuild():
+    from gaussian_splatting_with_eye_tracking_b200 import _host, scenes
+    sc, cam0 = common.make_case("small")
+    cam1 = scenes.look_at_camera((-1.2, 0.5, -3.0), (0, 0, 0), cam0.image_width, cam0.image_height, 0.9)
+    gs, cams, radiis = [], [], []
+    for cam in (cam0, cam1):
+        dpix = common.upstream_gradient(cam)
+        d, camd = common.cuda_inputs(sc, cam)
+        N, color, radii, geom, binning, img = _host.rasterize_gaussians(*common.fwd_args(d, camd), False)
+        g = _host.rasterize_gaussians_backward(
+            d["bg"], d["means3D"], radii, d["colors_precomp"], d["scales"], d["rotations"], 1.0, d["cov3D_precomp"],
+            camd.world_view_transform, camd.full_proj_transform, cam.tanfovx, cam.tanfovy, dpix.cuda(), d["shs"],
+            d["sh_degree"], camd.camera_center, geom, N, binning, img, False, compact_sh=True)
+        assert _host.last_counts(geom, radii.numel())[2] == int((radii > 0).sum())
+        gs.append(g[5]); cams.append(camd.camera_center.reshape(3)); radiis.append(radii)
+    P, M = d["shs"].shape[0], d["shs"].shape[1]
+    dense = _host.sh_grad_from_views(d["means3D"], torch.stack(cams), torch.stack(gs), d["sh_degree"], M)
+    cap = (max(int((r > 0).sum()) for r in radiis) + 255) // 256 * 256
+    cap = min(cap, P)
+    L = _host.pack_meta_words(P)
+    rows_all = torch.zeros(2, cap, 3, device="cuda")
+    meta_all = torch.zeros(2, L + 4, dtype=torch.int32, device="cuda")          # strided meta, as the exchange lays it out
+    for v in range(2):
+        _host.pack_visible_rows(gs[v], radiis[v], cap, rows_all[v], meta_all[v, :L])
+    packed = _host.sh_grad_from_packed_views(d["means3D"], torch.stack(cams), meta_all, rows_all, d["sh_degree"], M)
+    torch.cuda.synchronize()
+    assert torch.equal(packed, dense)
+    assert float(dense.abs().max()) > 0
