@@ -463,10 +463,11 @@ def measure(impl, args, d, cams, rank, world, timer, full):
         e_ = impl.e
         M_ = d["shs"].shape[1]
         res = {}
-        for mode in ("dense_rows", "packed_rows"):
-            exch = gdist.ShGradExchange(packed=(mode == "packed_rows"))
+        modes = {"dense_rows": (False, 1), "packed_rows": (True, 1), "packed_rows_2_ranges": (True, 2), "packed_rows_4_ranges": (True, 4)}
+        for mode, (packed_, nch) in modes.items():
+            exch = gdist.ShGradExchange(packed=packed_)
 
-            def dp_step_rank1(i, exch=exch):
+            def dp_step_rank1(i, exch=exch, nch=nch):
                 cam = cam_of(i)
                 N, img, radii, gb, bb, ib = impl.forward_c(cam)
                 if exch.packed:     # the forward holds the visible count on the host; the ranks agree on the gather size meanwhile
@@ -477,20 +478,25 @@ def measure(impl, args, d, cams, rank, world, timer, full):
                     d["bg"], d["means3D"], radii, e_, d["scales"], d["rotations"], 1.0, e_, cam.world_view_transform,
                     cam.full_proj_transform, cam.tanfovx, cam.tanfovy, w, d["shs"], d["sh_degree"], cam.camera_center, gb, N, bb, ib,
                     False, compact_sh=True,
-                    between_phases=lambda drgb: exch.start_gather(drgb, cam.camera_center, d["means3D"], d["sh_degree"], M_, radii=radii))
-                exch.start_reduce([g[3], g[2], g[6], g[7]])            # means3D, opacity, scales, rotations
+                    between_phases=lambda drgb: exch.start_gather(drgb, cam.camera_center, d["means3D"], d["sh_degree"], M_, radii=radii),
+                    preprocess_chunks=nch,
+                    after_chunk=(lambda first, count, rows: exch.start_reduce_chunk(rows)) if nch > 1 else None)
+                if nch == 1:
+                    exch.start_reduce([g[3], g[2], g[6], g[7]])        # means3D, opacity, scales, rotations
                 return exch.finish()
             res[mode] = (timer.run(dp_step_rank1, Kb, 2) / Kb, exch.last_cap)
-        ms1, cap = res["packed_rows"]
+        best = min((m for m in res if m != "dense_rows"), key=lambda m: res[m][0])
+        ms1, cap = res[best]
         pb = gdist.ShGradExchange.payload_bytes(P_, world, cap=cap)
         out["dp_train_rank1_sh"] = {"ms_per_step": ms1, "views_per_s": world / (ms1 / 1e3),
                                     "allreduce_bytes_per_step": pb["allreduce"] if world > 1 else 0,
                                     "allgather_bytes_in_per_step": pb["allgather_in"] if world > 1 else 0,
-                                    "rows_per_view": cap, "ms_per_step_dense_rows": res["dense_rows"][0],
+                                    "rows_per_view": cap, "variant": best, "ms_per_step_by_variant": {m: round(v[0], 4) for m, v in res.items()},
                                     "exchange": "rank-1 SH factor: the 3-float rows of the visible Gaussians of every view gathered "
                                                 "(bit mask + prefix words locate them) + 11 floats all-reduced; no autograd wrapper "
-                                                "(the C-shaped backward is called directly); ms_per_step_dense_rows = the same with "
-                                                "all P rows gathered"}
+                                                "(the C-shaped backward is called directly).  Variants: dense_rows = all P rows "
+                                                "gathered; k_ranges = preprocess-stage backward split into k ranges of Gaussians, each "
+                                                "range's 11 floats reduced while the next is computed"}
 
     # ---- screen-tile bands (config C5 shape): ONE foveated frame split over the ranks by rows of 32-px tiles, balanced by the
     # previous frame's per-row pair counts; per-tile counts all-reduced so the AMR levels equal the single-GPU ones
@@ -563,8 +569,31 @@ def c1_prototype_cpu(sc, cams_cpu, frame, W, H):
             "cores": os.cpu_count(), "what": "numpy/scipy restatement of AMR_test.py:109-280 (kind: port)"}
 
 
+_REAL_STDOUT = None
+
+
+def claim_stdout():
+    """stdout carries exactly ONE JSON line: libraries that chatter there (NCCL prints its version to stdout at every
+    debug level above NONE) are sent to stderr by re-pointing fd 1; emit() writes the line to the original fd."""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(line):
+    data = (json.dumps(line) + "\n").encode()
+    sys.stdout.flush()
+    if _REAL_STDOUT is None:
+        os.write(1, data)
+    else:
+        os.write(_REAL_STDOUT, data)
+
+
 def main():
     args = parse_args()
+    claim_stdout()
     rank, local_rank, world = dist_env()
     if args.impl == "reference-cpu":
         if rank != 0:
@@ -581,7 +610,7 @@ def main():
                 "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                 "config": {"workload": f"C3: {args.gaussians} Gaussians, {args.width}x{args.height}, SH deg 3"},
                 "cpu_baseline": best, "e2e": {"value": best["value"], "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-        print(json.dumps(line))
+        emit(line)
         return
 
     torch.cuda.set_device(local_rank)
@@ -613,7 +642,7 @@ def main():
     if args.impl == "reference":
         from oracle import ref_cuda
         if not ref_cuda.available(False):
-            print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/libref_raster.so missing (build with make -C oracle ref)"}))
+            emit({"impl": "reference", "unavailable": "oracle/_ref/libref_raster.so missing (build with make -C oracle ref)"})
             return
         impl = Ref(d)
         m = measure(impl, args, d, cams, 0, 1, timer, full)
@@ -665,7 +694,7 @@ def main():
     if rank == 0:
         sampler.stop()
         line["clocks"] = sampler.summary(windows)
-        print(json.dumps(line))
+        emit(line)
     if world > 1 and args.impl == "ours":
         dist.barrier()
         dist.destroy_process_group()

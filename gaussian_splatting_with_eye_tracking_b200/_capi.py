@@ -77,6 +77,8 @@ SYMBOLS = {
                                C.c_int, C.c_void_p, C.POINTER(GsrGrads), C.c_int, C.c_void_p]),
     "gsr_backward_phase": (C.c_int, [C.POINTER(GsrScene), C.POINTER(GsrCamera), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                      C.c_int, C.c_void_p, C.POINTER(GsrGrads), C.c_int, C.c_int, C.c_void_p]),
+    "gsr_backward_preprocess_range": (C.c_int, [C.POINTER(GsrScene), C.POINTER(GsrCamera), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                                C.c_int, C.POINTER(GsrGrads), C.c_int, C.c_int, C.c_int, C.c_void_p]),
     "gsr_mark_visible": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "gsr_sh_grad_from_views": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "gsr_pack_meta_words": (C.c_size_t, [C.c_int]),

@@ -156,13 +156,17 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
 def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rotations, scale_modifier, cov3D_precomp,
                                  viewmatrix, projmatrix, tan_fovx, tan_fovy, dL_dout_color, sh, degree, campos,
                                  geomBuffer, R, binningBuffer, imageBuffer, debug, band=None, compact_sh=False,
-                                 between_phases=None):
+                                 between_phases=None, preprocess_chunks=1, after_chunk=None):
     """``compact_sh=True`` (extension, view-parallel training): slot 5 of the returned tuple is the [P,3] colour
     gradient after the SH clamp mask instead of the [P,M,3] SH gradient, which is then not written at all;
     ``sh_grad_from_views`` rebuilds the SH gradient summed over views from those.
     ``between_phases(dL_dcolors_clamped)`` (with compact_sh): called after the blend-stage backward has been queued,
     when that tensor is final in stream order -- the hook where a view-parallel caller starts its all-gather so that
-    it overlaps the preprocess-stage backward (gsr_backward_phase)."""
+    it overlaps the preprocess-stage backward (gsr_backward_phase).
+    ``preprocess_chunks`` > 1 (with between_phases): the preprocess stage runs as that many launches over consecutive
+    ranges of Gaussians (gsr_backward_preprocess_range) and ``after_chunk(first, count, (dL_dmeans3D, dL_dopacity,
+    dL_dscales, dL_drotations))`` is called after each with views of that range's rows, final in stream order -- where
+    the caller starts reducing them while the next range is still being computed."""
     H, W = int(dL_dout_color.size(1)), int(dL_dout_color.size(2))
     sc, cam, keep, P, M = _scene_camera(background, means3D, colors, torch.empty(0), scales, rotations, scale_modifier,
                                         cov3D_precomp, viewmatrix, projmatrix, tan_fovx, tan_fovy, H, W, sh, degree,
@@ -200,9 +204,22 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
                                             _capi.GSR_BWD_BLEND, 1 if debug else 0, _stream())
                 _capi.check(rc, "gsr_backward_phase(blend)")
                 between_phases(dL_dsh)
-                rc = lib.gsr_backward_phase(C.byref(sc), C.byref(cam), _p(radii_t), *bufs, int(R), _p(dpix), C.byref(grads),
-                                            _capi.GSR_BWD_PREPROCESS, 1 if debug else 0, _stream())
-                _capi.check(rc, "gsr_backward_phase(preprocess)")
+                nch = max(1, min(int(preprocess_chunks), (P + 255) // 256))
+                if nch == 1:
+                    rc = lib.gsr_backward_phase(C.byref(sc), C.byref(cam), _p(radii_t), *bufs, int(R), _p(dpix), C.byref(grads),
+                                                _capi.GSR_BWD_PREPROCESS, 1 if debug else 0, _stream())
+                    _capi.check(rc, "gsr_backward_phase(preprocess)")
+                    if after_chunk is not None:
+                        after_chunk(0, P, (dL_dmeans3D, dL_dopacity, dL_dscales, dL_drotations))
+                else:
+                    per = ((P + nch - 1) // nch + 255) // 256 * 256
+                    for first in range(0, P, per):
+                        count = min(per, P - first)
+                        rc = lib.gsr_backward_preprocess_range(C.byref(sc), C.byref(cam), _p(radii_t), *bufs, int(R), C.byref(grads),
+                                                               first, count, 1 if debug else 0, _stream())
+                        _capi.check(rc, "gsr_backward_preprocess_range")
+                        if after_chunk is not None:
+                            after_chunk(first, count, tuple(t[first:first + count] for t in (dL_dmeans3D, dL_dopacity, dL_dscales, dL_drotations)))
             else:
                 rc = lib.gsr_backward(C.byref(sc), C.byref(cam), _p(radii_t), *bufs, int(R), _p(dpix),
                                       C.byref(grads), 1 if debug else 0, _stream())

@@ -318,9 +318,26 @@ int gsr_backward(const gsr_scene* sc, const gsr_camera* cam, const int* radii, c
                               GSR_BWD_ALL, debug, stream);
 }
 
+static int backward_impl(const gsr_scene* sc, const gsr_camera* cam, const int* radii, const void* geom_buffer,
+                         const void* binning_buffer, const void* image_buffer, int num_rendered, const float* dL_dpix,
+                         const gsr_grads* gr, int phase, int first, int count, int debug, void* stream);
+
 int gsr_backward_phase(const gsr_scene* sc, const gsr_camera* cam, const int* radii, const void* geom_buffer,
                        const void* binning_buffer, const void* image_buffer, int num_rendered, const float* dL_dpix,
                        const gsr_grads* gr, int phase, int debug, void* stream) {
+    return backward_impl(sc, cam, radii, geom_buffer, binning_buffer, image_buffer, num_rendered, dL_dpix, gr, phase, 0, -1, debug, stream);
+}
+
+int gsr_backward_preprocess_range(const gsr_scene* sc, const gsr_camera* cam, const int* radii, const void* geom_buffer,
+                                  const void* binning_buffer, const void* image_buffer, int num_rendered,
+                                  const gsr_grads* gr, int first, int count, int debug, void* stream) {
+    if (first < 0 || count < 0 || (first % 256) != 0) { set_error("backward_preprocess_range: first must be a non-negative multiple of 256, count >= 0"); return GSR_ERR_INVALID; }
+    return backward_impl(sc, cam, radii, geom_buffer, binning_buffer, image_buffer, num_rendered, nullptr, gr, GSR_BWD_PREPROCESS, first, count, debug, stream);
+}
+
+static int backward_impl(const gsr_scene* sc, const gsr_camera* cam, const int* radii, const void* geom_buffer,
+                         const void* binning_buffer, const void* image_buffer, int num_rendered, const float* dL_dpix,
+                         const gsr_grads* gr, int phase, int first, int count, int debug, void* stream) {
     cudaStream_t s = (cudaStream_t)stream;
     if (phase != GSR_BWD_ALL && phase != GSR_BWD_BLEND && phase != GSR_BWD_PREPROCESS) { set_error("bad backward phase %d", phase); return GSR_ERR_INVALID; }
     (void)num_rendered;
@@ -371,6 +388,7 @@ int gsr_backward_phase(const gsr_scene* sc, const gsr_camera* cam, const int* ra
     pb.radii = radii; pb.clamped = g.clamped; pb.scratch = gr->scratch; pb.out = *gr;
     if (sc->sh_coeffs == 0) pb.out.dL_dsh = nullptr;
     if (phase == GSR_BWD_PREPROCESS) pb.out.dL_dcolors_clamped = nullptr;      // already emitted by the blend phase
+    pb.first = first; pb.count = count;
     { ProfScope ps(GSR_PROF_BWD_PREPROCESS, s); launch_preprocess_backward(pb, s); }
     return check_last("preprocess backward", debug != 0, s);
 }

@@ -331,6 +331,7 @@ struct PreBwdArgs {
     const int* radii; const unsigned char* clamped;
     const float* scratch;
     gsr_grads out;
+    int first = 0, count = -1;     // count >= 0: only Gaussians [first, first + count), first a multiple of 256
 };
 void launch_preprocess_backward(const PreBwdArgs& a, cudaStream_t s);
 

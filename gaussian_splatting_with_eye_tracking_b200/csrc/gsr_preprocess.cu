@@ -421,7 +421,8 @@ void launch_mark_visible(int P, const float* means3D, const float* view, const f
 // non-deterministic float atomics), so arithmetic here is plain FP32 without pinned contraction.
 // ------------------------------------------------------------------------------------------------
 struct PreBwdParams {
-    int P, D, M;
+    int P, D, M;                   // P = one past the last Gaussian this launch handles
+    int block0;                    // first 256-Gaussian block of this launch (range launches, gsr_backward_preprocess_range)
     const float* __restrict__ means3D; const float* __restrict__ scales; const float* __restrict__ rotations;
     const float* __restrict__ shs; const float* __restrict__ cov3D;
     int cov_from_scales, colors_from_sh;
@@ -448,7 +449,7 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreBwdParams 
     if (tid < 16) { V[tid] = p.viewmatrix[tid]; Pm[tid] = p.projmatrix[tid]; }
     if (tid < 3) cam[tid] = p.cam_pos[tid];
     __syncthreads();
-    const int idx = blockIdx.x * 256 + tid;
+    const int idx = (blockIdx.x + p.block0) * 256 + tid;
     const bool valid = idx < p.P;
     if (!STAGED && !valid) return;
     const size_t i3 = 3 * (size_t)idx;
@@ -548,7 +549,7 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreBwdParams 
     }
     if (sh_rows || p.colors_from_sh) {
         const int L = 3 * p.M;
-        const int warp_idx0 = blockIdx.x * 256 + wid * 32;
+        const int warp_idx0 = (blockIdx.x + p.block0) * 256 + wid * 32;
         float* wbase = s_sh + wid * 32 * kShStride;
         float* out = STAGED ? (wbase + lane * kShStride) : (sh_rows ? p.dL_dsh + (size_t)idx * L : nullptr);
         const int ncoef = (p.D + 1) * (p.D + 1);
@@ -692,8 +693,11 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreBwdParams 
 
 void launch_preprocess_backward(const PreBwdArgs& a, cudaStream_t s) {
     if (a.P <= 0) return;
+    const int first = a.count >= 0 ? a.first : 0;
+    const int end = a.count >= 0 ? min(a.P, a.first + a.count) : a.P;
+    if (end <= first) return;
     PreBwdParams p;
-    p.P = a.P; p.D = a.D; p.M = a.M;
+    p.P = end; p.block0 = first / 256; p.D = a.D; p.M = a.M;
     p.means3D = a.means3D; p.scales = a.scales; p.rotations = a.rotations; p.shs = a.shs; p.cov3D = a.cov3D;
     p.cov_from_scales = a.cov_from_scales ? 1 : 0; p.colors_from_sh = a.colors_from_sh ? 1 : 0;
     p.scale_modifier = a.scale_modifier;
@@ -711,9 +715,9 @@ void launch_preprocess_backward(const PreBwdArgs& a, cudaStream_t s) {
         const int smem = 256 * kShStride * (int)sizeof(float);
         static bool attr_done = false;
         if (!attr_done) { cudaFuncSetAttribute(preprocess_bwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem); attr_done = true; }
-        preprocess_bwd_kernel<true><<<(a.P + 255) / 256, 256, smem, s>>>(p);
+        preprocess_bwd_kernel<true><<<(end - first + 255) / 256, 256, smem, s>>>(p);
     } else {
-        preprocess_bwd_kernel<false><<<(a.P + 255) / 256, 256, 0, s>>>(p);
+        preprocess_bwd_kernel<false><<<(end - first + 255) / 256, 256, 0, s>>>(p);
     }
     count_launch();
 }

@@ -117,6 +117,29 @@ class GradientAllReduce:
                 work = dist.all_reduce(buf, op=dist.ReduceOp.SUM, group=self.group, async_op=True)
                 self._pending.append((work, buf, scatter, flats))
 
+    def start_inplace(self, tensors: Sequence[torch.Tensor]) -> None:
+        """Queue the in-place SUM of a few contiguous tensors as ONE grouped collective (no bucket copies); may be called
+        several times before wait() -- the chunks of a range-split backward are reduced as they become final."""
+        if world_size() == 1 or not tensors:
+            return
+        dev = tensors[0].device
+        if not all(t.is_contiguous() for t in tensors):
+            raise RuntimeError("start_inplace needs contiguous tensors")
+        flats = _coalesce_adjacent([t.view(-1) for t in tensors])
+        comm = self._comm_stream(dev)
+        if comm is not None:
+            comm.wait_stream(torch.cuda.current_stream(dev))
+        with (torch.cuda.stream(comm) if comm is not None else _null()):
+            if dev.type == "cuda" and len(flats) > 1:
+                with dist._coalescing_manager(group=self.group, device=dev, async_ops=True) as cm:      # one ncclGroup launch
+                    for f in flats:
+                        dist.all_reduce(f, op=dist.ReduceOp.SUM, group=self.group)
+                self._pending.append((cm, None, None, flats))
+            else:
+                for f in flats:
+                    work = dist.all_reduce(f, op=dist.ReduceOp.SUM, group=self.group, async_op=True)
+                    self._pending.append((work, f, None, flats))
+
     def wait(self) -> None:
         """Block the CURRENT stream (not the host, for NCCL) until every bucket is reduced and scattered back."""
         for work, buf, scatter, flats in self._pending:
@@ -286,6 +309,11 @@ class ShGradExchange:
     def start_reduce(self, dense_grads: Sequence[torch.Tensor]) -> None:
         """Queue the in-place SUM of the remaining gradients (means3D, opacity, scales, rotations)."""
         self.reducer.start(dense_grads)
+
+    def start_reduce_chunk(self, chunk_grads: Sequence[torch.Tensor]) -> None:
+        """As start_reduce for one range of a range-split backward (``after_chunk`` of
+        _host.rasterize_gaussians_backward): the range's rows of the four tensors, reduced in place as one grouped call."""
+        self.reducer.start_inplace(chunk_grads)
 
     def start(self, dense_grads: Sequence[torch.Tensor], dL_dcolors_clamped: torch.Tensor, campos: torch.Tensor,
               means3D: torch.Tensor, degree: int, M: int, radii: Optional[torch.Tensor] = None) -> None:

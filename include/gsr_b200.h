@@ -146,6 +146,12 @@ enum { GSR_BWD_ALL = 0, GSR_BWD_BLEND = 1, GSR_BWD_PREPROCESS = 2 };
 GSR_API int gsr_backward_phase(const gsr_scene* scene, const gsr_camera* cam, const int* radii, const void* geom_buffer,
                                const void* binning_buffer, const void* image_buffer, int num_rendered, const float* dL_dpix,
                                const gsr_grads* grads, int phase, int debug, void* stream);
+/* The GSR_BWD_PREPROCESS phase for the Gaussians [first, first + count) only (first a multiple of 256): a view-parallel
+ * caller runs the stage as a few consecutive ranges and starts reducing a range's rows of dL_dmeans3D / dL_dopacity /
+ * dL_dscales / dL_drotations while the next range is computed.  The ranges of one backward must cover [0, P) once. */
+GSR_API int gsr_backward_preprocess_range(const gsr_scene* scene, const gsr_camera* cam, const int* radii, const void* geom_buffer,
+                                          const void* binning_buffer, const void* image_buffer, int num_rendered,
+                                          const gsr_grads* grads, int first, int count, int debug, void* stream);
 
 GSR_API int gsr_mark_visible(int P, const float* means3D, const float* viewmatrix,
                              const float* projmatrix, unsigned char* present, void* stream);

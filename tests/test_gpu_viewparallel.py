@@ -148,3 +148,34 @@ def test_packed_rebuild_is_bit_identical_to_dense_rebuild():
     torch.cuda.synchronize()
     assert torch.equal(packed, dense)
     assert float(dense.abs().max()) > 0
+
+
+@pytest.mark.parametrize("chunks", [2, 3, 7])
+def test_range_split_preprocess_backward_matches_single_launch(chunks):
+    """gsr_backward_preprocess_range: consecutive ranges cover [0, P) once; every range's rows are final at its hook."""
+    from gaussian_splatting_with_eye_tracking_b200 import _host
+    sc, cam = common.make_case("small")
+    dpix = common.upstream_gradient(cam)
+    d, camd, one = _backward(sc, cam, dpix, True)
+    N, color, radii, geom, binning, img = _host.rasterize_gaussians(*common.fwd_args(d, camd), False)
+    P = d["means3D"].shape[0]
+    seen, snaps = [], []
+
+    def after(first, count, rows):
+        seen.append((first, count))
+        assert [tuple(r.shape) for r in rows] == [(count, 3), (count, 1), (count, 3), (count, 4)]
+        assert all(r.is_contiguous() for r in rows)
+        snaps.append([r.clone() for r in rows])
+    split = _host.rasterize_gaussians_backward(
+        d["bg"], d["means3D"], radii, d["colors_precomp"], d["scales"], d["rotations"], 1.0, d["cov3D_precomp"],
+        camd.world_view_transform, camd.full_proj_transform, cam.tanfovx, cam.tanfovy, dpix.cuda(), d["shs"],
+        d["sh_degree"], camd.camera_center, geom, N, binning, img, False, compact_sh=True,
+        between_phases=lambda drgb: None, preprocess_chunks=chunks, after_chunk=after)
+    torch.cuda.synchronize()
+    assert seen[0][0] == 0 and sum(c for _, c in seen) == P and all(f % 256 == 0 for f, _ in seen)
+    assert all(seen[i][0] + seen[i][1] == seen[i + 1][0] for i in range(len(seen) - 1))
+    for (first, count), snap in zip(seen, snaps):          # rows were final when the hook ran
+        for r, full in zip(snap, (split[3], split[2], split[6], split[7])):
+            assert torch.equal(r, full[first:first + count])
+    for i in range(8):
+        _close(split[i], one[i], f"grad[{i}] range-split vs single launch")
