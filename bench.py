@@ -463,7 +463,9 @@ def measure(impl, args, d, cams, rank, world, timer, full):
         e_ = impl.e
         M_ = d["shs"].shape[1]
         res = {}
-        modes = {"dense_rows": (False, 1), "packed_rows": (True, 1), "packed_rows_2_ranges": (True, 2), "packed_rows_4_ranges": (True, 4)}
+        modes = {"dense_rows": (False, 1), "packed_rows": (True, 1)}
+        if os.environ.get("GSR_BENCH_DP_RANGES"):           # measured: splitting the preprocess stage into ranges does not pay
+            modes.update({"packed_rows_2_ranges": (True, 2), "packed_rows_4_ranges": (True, 4)})
         for mode, (packed_, nch) in modes.items():
             exch = gdist.ShGradExchange(packed=packed_)
 
@@ -620,7 +622,8 @@ def main():
     if world > 1 and args.impl == "ours":
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         os.environ["NCCL_DEBUG"] = os.environ.get("GSR_NCCL_DEBUG", "WARN")     # keep stdout to the one JSON line (NCCL prints its version there)
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        from gaussian_splatting_with_eye_tracking_b200 import dist as gdist_
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank), pg_options=gdist_.nccl_options())
     eff_world = world if args.impl == "ours" else 1
 
     sampler = ClockSampler(local_rank)

@@ -25,6 +25,22 @@ GRAD_FLOATS_PER_GAUSSIAN = 59          # 3 + 48 + 1 + 3 + 4
 DEFAULT_BUCKET_BYTES = 128 << 20       # NVSwitch: size buckets for launch latency and overlap, not link count
 
 
+def comm_stream(device) -> "torch.cuda.Stream":
+    """Side stream for exchange work.  High priority: its small kernels (row packing, the SH rebuild) and the NCCL calls
+    queued behind them are dispatched ahead of the still-pending CTAs of the backward kernel they are meant to overlap;
+    at default priority they only start once that kernel has handed out all its CTAs, i.e. after it.
+    GSR_COMM_PRIORITY=0 restores default priority (diagnostics)."""
+    pr = int(os.environ.get("GSR_COMM_PRIORITY", "-1"))
+    return torch.cuda.Stream(device=device, priority=pr)
+
+
+def nccl_options():
+    """ProcessGroupNCCL options with NCCL's own stream at high priority (same reason as comm_stream)."""
+    opts = dist.ProcessGroupNCCL.Options()
+    opts.is_high_priority_stream = os.environ.get("GSR_COMM_PRIORITY", "-1") != "0"
+    return opts
+
+
 def init(backend: Optional[str] = None) -> Tuple[int, int]:
     """Initialise the default process group from the torchrun environment.  Returns (rank, world)."""
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -38,6 +54,7 @@ def init(backend: Optional[str] = None) -> Tuple[int, int]:
             local = int(os.environ.get("LOCAL_RANK", rank))
             torch.cuda.set_device(local)
             kw["device_id"] = torch.device("cuda", local)
+            kw["pg_options"] = nccl_options()
         dist.init_process_group(backend, **kw)
     return rank, world
 
@@ -84,7 +101,7 @@ class GradientAllReduce:
         if device.type != "cuda":
             return None
         if self._stream is None:
-            self._stream = torch.cuda.Stream(device=device)
+            self._stream = comm_stream(device)
         return self._stream
 
     def start(self, grads: Sequence[torch.Tensor]) -> None:
@@ -185,7 +202,8 @@ class ShGradExchange:
         self._gathered = None
         self._cams = None
         self._stream = None
-        self._dsh = None
+        self._rebuild_call = None
+        self._side_allocs = []
         self._keep = None
         self._send_rows = None
         self._send_meta = None
@@ -198,7 +216,7 @@ class ShGradExchange:
         if dev.type != "cuda":
             return None
         if self._stream is None:
-            self._stream = torch.cuda.Stream(device=dev)
+            self._stream = comm_stream(dev)
         return self._stream
 
     # ---- packed mode: agree on the capacity of the row gather ----
@@ -269,7 +287,7 @@ class ShGradExchange:
                          dist.all_gather_into_tensor(self._cams.view(-1), campos.contiguous().view(-1), group=self.group, async_op=True)]
                 for wk in works:
                     wk.wait()                                 # blocks the side stream only (the host for gloo)
-            self._dsh = rebuild(means3D, self._cams, self._gathered, degree, M)
+        self._rebuild_call = lambda: rebuild(means3D, self._cams, self._gathered, degree, M)
 
     def _start_gather_packed(self, g, campos, means3D, degree, M, radii, w, P, dev):
         if radii is None:
@@ -304,7 +322,8 @@ class ShGradExchange:
                 for wk in works:
                     wk.wait()
             cams = self._meta_all[:, L:L + 3].contiguous().view(torch.float32)
-            self._dsh = rebuild(means3D, cams, self._meta_all, rows_all.view(w, cap, 3), degree, M)
+            self._side_allocs = [cams]
+        self._rebuild_call = lambda: rebuild(means3D, cams, self._meta_all, rows_all.view(w, cap, 3), degree, M)
 
     def start_reduce(self, dense_grads: Sequence[torch.Tensor]) -> None:
         """Queue the in-place SUM of the remaining gradients (means3D, opacity, scales, rotations)."""
@@ -324,10 +343,17 @@ class ShGradExchange:
         """Wait (the current stream, not the host) for the exchange; returns the SH gradient [P,M,3] summed over all views."""
         if self._stream is not None:
             torch.cuda.current_stream().wait_stream(self._stream)
+        # The rebuild runs HERE, on the caller's stream behind the backward, not on the side stream: it is HBM-bound
+        # like the preprocess-stage backward (running both at once only slows the backward down, measured), while the
+        # all-reduce queued by start_reduce is NVLink-bound -- so the rebuild overlaps the all-reduce instead.
+        dsh = self._rebuild_call() if self._rebuild_call is not None else None
         self.reducer.wait()
-        dsh, self._dsh, self._keep = self._dsh, None, None
-        if dsh is not None and dsh.is_cuda:
-            dsh.record_stream(torch.cuda.current_stream())    # allocated on the side stream, consumed here
+        self._rebuild_call, self._keep = None, None
+        # (the persistent gather buffers are safe: the next start_gather makes the side stream wait for this one)
+        for t in self._side_allocs:
+            if t.is_cuda:
+                t.record_stream(torch.cuda.current_stream())  # allocated on the side stream, read by the rebuild here
+        self._side_allocs = []
         return dsh
 
     @staticmethod
