@@ -22,6 +22,7 @@ from __future__ import annotations
 
 import argparse
 import json
+import math
 import os
 import statistics
 import subprocess
@@ -592,6 +593,86 @@ def emit(line):
     else:
         os.write(_REAL_STDOUT, data)
 
+def train_step_bench(impl, ref_impl, d, cams, args, timer_iters=12):
+    """One full training iteration (train.py:83-121 shape): render -> (1-l)*L1 + l*(1-SSIM) -> backward ->
+    Adam over the six parameter groups.  ours: rasterizer autograd API + loss_utils.l1_ssim_loss + optim.FusedAdam;
+    reference: the unmodified reference CUDA rasterizer + the plain-torch loss chain of utils/loss_utils.py (F.conv2d, autograd)
+    + torch.optim.Adam(eps=1e-15).  Device time (CUDA events), one view per iteration, ring cameras."""
+    import torch.nn.functional as F
+    from gaussian_splatting_with_eye_tracking_b200 import loss_utils, optim
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import train_surround
+    dev = d["means3D"].device
+    H, W = args.height, args.width
+    g = torch.Generator().manual_seed(4004)
+    gts = [torch.rand(3, H, W, generator=g).to(dev) for _ in range(2)]
+    lrs = {"means3D": 1.6e-4, "shs": 2.5e-3, "opacities": 0.05, "scales": 5e-3, "rotations": 1e-3}
+    keys = ("means3D", "shs", "opacities", "scales", "rotations")
+    out = {}
+
+    def timed(fn):
+        for i in range(3):
+            fn(i)
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for i in range(timer_iters):
+            fn(i)
+        b.record(); b.synchronize()
+        return a.elapsed_time(b) / timer_iters
+
+    # ---- ours
+    leaves = {k: torch.nn.Parameter(d[k].detach().clone()) for k in keys}
+    m2d = torch.zeros_like(leaves["means3D"], requires_grad=True)
+    opt = optim.FusedAdam([{"params": [leaves[k]], "lr": lrs[k], "name": k} for k in keys], lr=0.0, eps=1e-15)
+
+    def ours(i):
+        cam = cams[i % len(cams)]
+        rs = impl.dgr.GaussianRasterizationSettings(cam.image_height, cam.image_width, cam.tanfovx, cam.tanfovy, d["bg"], 1.0,
+                                                    cam.world_view_transform, cam.full_proj_transform, d["sh_degree"],
+                                                    cam.camera_center, False, False)
+        m2d.grad = None
+        img, _ = impl.dgr.GaussianRasterizer(rs)(means3D=leaves["means3D"], means2D=m2d, opacities=leaves["opacities"], shs=leaves["shs"],
+                                                 scales=leaves["scales"], rotations=leaves["rotations"])
+        loss_utils.l1_ssim_loss(img, gts[i % 2], 0.2).backward()
+        opt.step()
+        opt.zero_grad(set_to_none=True)
+    n0 = impl.launches()
+    out["ours_ms_per_iteration"] = timed(ours)
+    out["ours_launches_per_iteration"] = (impl.launches() - n0) / (timer_iters + 3)
+    del opt, leaves, m2d
+    # ---- reference chain
+    if ref_impl is not None:
+        rl = {k: torch.nn.Parameter(d[k].detach().clone()) for k in keys}
+        ropt = torch.optim.Adam([{"params": [rl[k]], "lr": lrs[k], "name": k} for k in keys], lr=0.0, eps=1e-15)
+        w1 = torch.tensor([math.exp(-(x - 5) ** 2 / 4.5) for x in range(11)])
+        w1 = (w1 / w1.sum()).to(dev)
+        win = (w1[:, None] @ w1[None, :]).expand(3, 1, 11, 11).contiguous()
+        e = ref_impl.e
+
+        def ref(i):
+            cam = cams[i % len(cams)]
+            a = (d["bg"], rl["means3D"].data, e, rl["opacities"].data, rl["scales"].data, rl["rotations"].data, 1.0, e, cam.world_view_transform,
+                 cam.full_proj_transform, cam.tanfovx, cam.tanfovy, cam.image_height, cam.image_width, rl["shs"].data, d["sh_degree"], cam.camera_center)
+            N, img, radii, gb, bb, ib = ref_impl.r.forward(*a)
+            x = img.detach().requires_grad_(True)
+            train_surround.torch_loss(x, gts[i % 2], 0.2, win).backward()
+            gr = ref_impl.r.backward(d["bg"], rl["means3D"].data, radii, e, rl["scales"].data, rl["rotations"].data, 1.0, e, cam.world_view_transform,
+                                     cam.full_proj_transform, cam.tanfovx, cam.tanfovy, x.grad, rl["shs"].data, d["sh_degree"], cam.camera_center,
+                                     gb, N, bb, ib)
+            for k, gk in zip(keys, ("dL_dmeans3D", "dL_dsh", "dL_dopacity", "dL_dscales", "dL_drotations")):
+                rl[k].grad = gr[gk].view_as(rl[k])
+            ropt.step()
+            ropt.zero_grad(set_to_none=True)
+        out["reference_ms_per_iteration"] = timed(ref)
+        out["speedup"] = out["reference_ms_per_iteration"] / out["ours_ms_per_iteration"]
+        del ropt, rl
+    torch.cuda.empty_cache()
+    out["kernels"] = train_surround.measure(args.gaussians, W, H, dev, hbm_gbs=load_peaks()[0])
+    out["what"] = ("render + L1/SSIM loss + backward + Adam, one view per iteration; reference = unmodified reference CUDA rasterizer + "
+                   "torch conv2d/autograd loss + torch.optim.Adam")
+    return out
+
 
 def main():
     args = parse_args()
@@ -685,6 +766,10 @@ def main():
                                                           "fwd_bwd": r["fwd_bwd_ms_per_view"] / m["fwd_bwd_ms_per_view"]}
                 except Exception as ex:     # reported, never fatal for our own line
                     extra["reference_cuda_same_run"] = {"error": str(ex)[:300]}
+            try:
+                extra["train_step"] = train_step_bench(impl, Ref(d) if ref_cuda.available(False) else None, d, cams, args)
+            except Exception as ex:
+                extra["train_step"] = {"error": str(ex)[:300]}
             if not args.no_cpu_baseline:
                 line["cpu_baseline"] = cpu_baseline(sc, cams_cpu)
                 try:

@@ -49,6 +49,11 @@ class GsrGrads(C.Structure):
         "dL_drotations", "dL_dconic", "scratch", "dL_dcolors_clamped")]
 
 
+class GsrAdamTensor(C.Structure):
+    _fields_ = [("param", C.c_void_p), ("grad", C.c_void_p), ("exp_avg", C.c_void_p), ("exp_avg_sq", C.c_void_p),
+                ("n", C.c_longlong), ("lr", C.c_float), ("step", C.c_int)]
+
+
 class GsrGeomView(C.Structure):
     _fields_ = [("P", C.c_int)] + [(n, C.c_void_p) for n in (
         "depths", "clamped", "radii", "means2D", "cov3D", "conic_opacity", "rgb", "tiles_touched", "block_offsets",
@@ -100,6 +105,12 @@ SYMBOLS = {
     "gsr_sort_pairs": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_longlong,
                                  C.c_int, C.c_void_p, C.c_size_t, C.c_void_p]),
     "gsr_higher_msb": (C.c_uint, [C.c_uint]),
+    "gsr_l1_ssim_partials": (C.c_size_t, [C.c_int, C.c_int, C.c_int]),
+    "gsr_l1_ssim_forward": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_float, C.c_float, C.c_float,
+                                      C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "gsr_l1_ssim_backward": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_float, C.c_float, C.c_void_p,
+                                       C.c_void_p, C.c_void_p, C.c_void_p]),
+    "gsr_adam_step": (C.c_int, [C.POINTER(GsrAdamTensor), C.c_int, C.c_float, C.c_float, C.c_float, C.c_void_p]),
     "gsr_launch_count": (C.c_ulonglong, []),
     "gsr_set_option": (C.c_int, [C.c_int, C.c_int]),
     "gsr_profile_enable": (None, [C.c_int]),

@@ -272,6 +272,34 @@ GSR_API int gsr_sh_grad_from_packed_views(int P, int sh_degree, int sh_coeffs, c
                                           const float* rows, int cap, float* dL_dsh, void* stream);
 GSR_API int gsr_last_counts(const void* geom_buffer, int P, long long* num_rendered, long long* num_runs, long long* num_visible);
 
+/* ---- training-step surround: the loss and the optimizer either side of the rasterizer ----
+ * gsr_l1_ssim_forward  <- utils/loss_utils.py:17-18 (l1_loss) + :39-63 (ssim, window 11, sigma 1.5, zero padding, mean),
+ *                         combined as train.py:87-88.  image, gt: [channels,height,width] floats.
+ *                         out[3] = { w_l1*L1 + w_ssim*SSIM + w_const, L1, SSIM }   (train.py: w_l1 = 1-l, w_ssim = -l, w_const = l)
+ *                         maps: [3,channels,height,width] scratch the backward reads (d ssim / d{mu1, E[xx], E[xy]} per window
+ *                         centre), or NULL when no gradient is wanted.  partials: 2*gsr_l1_ssim_partials(...) floats of scratch;
+ *                         the final sum runs in a fixed order in double (deterministic).
+ * gsr_l1_ssim_backward <- autograd of the above w.r.t. image: dL_dimage [channels,height,width];
+ *                         dloss = device scalar upstream gradient of out[0], or NULL for 1.
+ * gsr_adam_step        <- torch.optim.Adam.step() as configured by scene/gaussian_model.py:149-175 (betas, eps=1e-15, no weight
+ *                         decay, no amsgrad), every tensor of every group in ONE launch (per 8 tensors); `step` is the 1-based
+ *                         step count of that tensor AFTER this update, lr its group's learning rate. */
+typedef struct gsr_adam_tensor {
+    float* param;            /* [n] updated in place */
+    const float* grad;       /* [n]                  */
+    float* exp_avg;          /* [n] updated in place */
+    float* exp_avg_sq;       /* [n] updated in place */
+    long long n;
+    float lr;
+    int step;
+} gsr_adam_tensor;
+GSR_API size_t gsr_l1_ssim_partials(int channels, int height, int width);
+GSR_API int gsr_l1_ssim_forward(int channels, int height, int width, const float* image, const float* gt, float w_l1, float w_ssim,
+                                float w_const, float* maps, float* partials, float* out, void* stream);
+GSR_API int gsr_l1_ssim_backward(int channels, int height, int width, const float* image, const float* gt, float w_l1, float w_ssim,
+                                 const float* maps, const float* dloss, float* dL_dimage, void* stream);
+GSR_API int gsr_adam_step(const gsr_adam_tensor* tensors, int count, float beta1, float beta2, float eps, void* stream);
+
 /* ---- tuning knobs (results never depend on them) ---- */
 enum { GSR_OPT_SORT_VARIANT = 0,  /* onesweep tile shape for u32 keys: 0 = default, 1..5 see gsr_binning.cu */
        GSR_OPT_BLEND_VARIANT = 1  /* forward blend: 0 = two pixels per thread, packed FP32x2 (default); 1 = one pixel per thread */ };
