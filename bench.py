@@ -465,12 +465,21 @@ def measure(impl, args, d, cams, rank, world, timer, full):
         M_ = d["shs"].shape[1]
         res = {}
         modes = {"dense_rows": (False, 1), "packed_rows": (True, 1)}
+        peer_err, peer_red = None, None
+        if world > 1 and not os.environ.get("GSR_BENCH_NO_PEER"):
+            try:                 # the 11 dense floats summed over NVLink peer memory (gsr_peer_allreduce_sum) instead of NCCL
+                peer_red = gdist.PeerAllReduce(11 * ((P_ + 3) // 4 * 4), dev)
+                modes["packed_rows_peer_sum"] = (True, 1)
+                modes["dense_rows_peer_sum"] = (False, 1)
+            except Exception as ex:
+                peer_err = str(ex)[:300]
         if os.environ.get("GSR_BENCH_DP_RANGES"):           # measured: splitting the preprocess stage into ranges does not pay
             modes.update({"packed_rows_2_ranges": (True, 2), "packed_rows_4_ranges": (True, 4)})
         for mode, (packed_, nch) in modes.items():
-            exch = gdist.ShGradExchange(packed=packed_)
+            use_peer = mode.endswith("peer_sum")
+            exch = gdist.ShGradExchange(packed=packed_, peer=peer_red if use_peer else None)
 
-            def dp_step_rank1(i, exch=exch, nch=nch):
+            def dp_step_rank1(i, exch=exch, nch=nch, use_peer=use_peer):
                 cam = cam_of(i)
                 N, img, radii, gb, bb, ib = impl.forward_c(cam)
                 if exch.packed:     # the forward holds the visible count on the host; the ranks agree on the gather size meanwhile
@@ -483,7 +492,8 @@ def measure(impl, args, d, cams, rank, world, timer, full):
                     False, compact_sh=True,
                     between_phases=lambda drgb: exch.start_gather(drgb, cam.camera_center, d["means3D"], d["sh_degree"], M_, radii=radii),
                     preprocess_chunks=nch,
-                    after_chunk=(lambda first, count, rows: exch.start_reduce_chunk(rows)) if nch > 1 else None)
+                    after_chunk=(lambda first, count, rows: exch.start_reduce_chunk(rows)) if nch > 1 else None,
+                    dense_out=peer_red.data if use_peer else None)
                 if nch == 1:
                     exch.start_reduce([g[3], g[2], g[6], g[7]])        # means3D, opacity, scales, rotations
                 return exch.finish()
@@ -494,12 +504,13 @@ def measure(impl, args, d, cams, rank, world, timer, full):
         out["dp_train_rank1_sh"] = {"ms_per_step": ms1, "views_per_s": world / (ms1 / 1e3),
                                     "allreduce_bytes_per_step": pb["allreduce"] if world > 1 else 0,
                                     "allgather_bytes_in_per_step": pb["allgather_in"] if world > 1 else 0,
-                                    "rows_per_view": cap, "variant": best, "ms_per_step_by_variant": {m: round(v[0], 4) for m, v in res.items()},
+                                    "rows_per_view": cap, "variant": best, **({"peer_sum_error": peer_err} if peer_err else {}), "ms_per_step_by_variant": {m: round(v[0], 4) for m, v in res.items()},
                                     "exchange": "rank-1 SH factor: the 3-float rows of the visible Gaussians of every view gathered "
                                                 "(bit mask + prefix words locate them) + 11 floats all-reduced; no autograd wrapper "
                                                 "(the C-shaped backward is called directly).  Variants: dense_rows = all P rows "
                                                 "gathered; k_ranges = preprocess-stage backward split into k ranges of Gaussians, each "
-                                                "range's 11 floats reduced while the next is computed"}
+                                                "range's 11 floats reduced while the next is computed; *_peer_sum = the 11 floats summed in place over NVLink peer "
+                                                "memory by gsr_peer_allreduce_sum (two-shot pull/push, one kernel) instead of ncclAllReduce"}
 
     # ---- screen-tile bands (config C5 shape): ONE foveated frame split over the ranks by rows of 32-px tiles, balanced by the
     # previous frame's per-row pair counts; per-tile counts all-reduced so the AMR levels equal the single-GPU ones

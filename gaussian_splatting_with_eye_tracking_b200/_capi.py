@@ -51,7 +51,7 @@ class GsrGrads(C.Structure):
 
 class GsrAdamTensor(C.Structure):
     _fields_ = [("param", C.c_void_p), ("grad", C.c_void_p), ("exp_avg", C.c_void_p), ("exp_avg_sq", C.c_void_p),
-                ("n", C.c_longlong), ("lr", C.c_float), ("step", C.c_int)]
+                ("n", C.c_longlong), ("lr", C.c_double), ("step", C.c_int)]
 
 
 class GsrGeomView(C.Structure):
@@ -110,7 +110,10 @@ SYMBOLS = {
                                       C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "gsr_l1_ssim_backward": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_float, C.c_float, C.c_void_p,
                                        C.c_void_p, C.c_void_p, C.c_void_p]),
-    "gsr_adam_step": (C.c_int, [C.POINTER(GsrAdamTensor), C.c_int, C.c_float, C.c_float, C.c_float, C.c_void_p]),
+    "gsr_adam_step": (C.c_int, [C.POINTER(GsrAdamTensor), C.c_int, C.c_double, C.c_double, C.c_double, C.c_void_p]),
+    "gsr_peer_flag_bytes": (C.c_size_t, [C.c_int]),
+    "gsr_peer_barrier": (C.c_int, [C.c_void_p, C.c_size_t, C.c_int, C.c_int, C.c_uint, C.c_void_p]),
+    "gsr_peer_allreduce_sum": (C.c_int, [C.c_void_p, C.c_size_t, C.c_longlong, C.c_size_t, C.c_int, C.c_int, C.c_uint, C.c_void_p]),
     "gsr_launch_count": (C.c_ulonglong, []),
     "gsr_set_option": (C.c_int, [C.c_int, C.c_int]),
     "gsr_profile_enable": (None, [C.c_int]),

@@ -156,7 +156,7 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
 def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rotations, scale_modifier, cov3D_precomp,
                                  viewmatrix, projmatrix, tan_fovx, tan_fovy, dL_dout_color, sh, degree, campos,
                                  geomBuffer, R, binningBuffer, imageBuffer, debug, band=None, compact_sh=False,
-                                 between_phases=None, preprocess_chunks=1, after_chunk=None):
+                                 between_phases=None, preprocess_chunks=1, after_chunk=None, dense_out=None):
     """``compact_sh=True`` (extension, view-parallel training): slot 5 of the returned tuple is the [P,3] colour
     gradient after the SH clamp mask instead of the [P,M,3] SH gradient, which is then not written at all;
     ``sh_grad_from_views`` rebuilds the SH gradient summed over views from those.
@@ -166,7 +166,10 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
     ``preprocess_chunks`` > 1 (with between_phases): the preprocess stage runs as that many launches over consecutive
     ranges of Gaussians (gsr_backward_preprocess_range) and ``after_chunk(first, count, (dL_dmeans3D, dL_dopacity,
     dL_dscales, dL_drotations))`` is called after each with views of that range's rows, final in stream order -- where
-    the caller starts reducing them while the next range is still being computed."""
+    the caller starts reducing them while the next range is still being computed.
+    ``dense_out``: caller-owned float32 buffer of at least 11 * ceil4(P) elements that receives the four dense gradients
+    (means3D, opacity, scales, rotations, back to back) instead of a fresh allocation -- a view-parallel caller passes
+    peer-mapped memory here so that dist.PeerAllReduce sums them in place over NVLink."""
     H, W = int(dL_dout_color.size(1)), int(dL_dout_color.size(2))
     sc, cam, keep, P, M = _scene_camera(background, means3D, colors, torch.empty(0), scales, rotations, scale_modifier,
                                         cov3D_precomp, viewmatrix, projmatrix, tan_fovx, tan_fovy, H, W, sh, degree,
@@ -178,7 +181,13 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
         # P % 4 == 0): a view-parallel caller all-reduces them as ONE in-place NCCL call (dist.GradientAllReduce
         # recognises adjacent tensors) instead of packing them into a bucket and back
         P4 = (P + 3) // 4 * 4
-        flat = torch.empty((11 * P4,), **f32)
+        if dense_out is None:
+            flat = torch.empty((11 * P4,), **f32)
+        else:
+            if (not dense_out.is_cuda or dense_out.dtype != torch.float32 or not dense_out.is_contiguous()
+                    or dense_out.numel() < 11 * P4 or dense_out.data_ptr() % 16):
+                raise RuntimeError("dense_out must be a contiguous, 16-byte aligned float32 CUDA buffer of >= 11*ceil4(P) elements")
+            flat = dense_out.view(-1)[:11 * P4]
         dL_dmeans3D = flat[0:3 * P].view(P, 3)
         dL_dopacity = flat[3 * P4:3 * P4 + P].view(P, 1)
         dL_dscales = flat[4 * P4:4 * P4 + 3 * P].view(P, 3)

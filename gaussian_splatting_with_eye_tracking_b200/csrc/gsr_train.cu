@@ -263,15 +263,15 @@ struct AdamPack {
     float bc2_sqrt[kAdamMaxGroups];       // sqrt(1 - beta2^t)
     int block_end[kAdamMaxGroups];        // exclusive end of the tensor's CTA range
     int count;
-    float beta1, beta2, eps;
+    float beta1, beta2, omb1, omb2, eps;   // omb = 1 - beta, rounded from double (1.f - 0.999f is off by 4.7e-5 relative)
 };
 
-__device__ __forceinline__ void adam_one(float& p, float g, float& m, float& v, float b1, float b2, float eps, float step_size, float bc2_sqrt) {
+__device__ __forceinline__ void adam_one(float& p, float g, float& m, float& v, float omb1, float b2, float omb2, float eps, float step_size, float bc2_sqrt) {
     // torch/optim/adam.py (_single_tensor_adam / _multi_tensor_adam, no amsgrad, no weight decay, maximize=False):
     //   exp_avg.lerp_(grad, 1-beta1); exp_avg_sq.mul_(beta2).addcmul_(grad, grad, value=1-beta2)
     //   denom = exp_avg_sq.sqrt() / bias_correction2_sqrt + eps;  param.addcdiv_(exp_avg, denom, value=-step_size)
-    m = fmaf(1.f - b1, g - m, m);
-    v = fmaf(1.f - b2, g * g, v * b2);
+    m = fmaf(omb1, g - m, m);
+    v = fmaf(omb2, g * g, v * b2);
     const float denom = __fdiv_rn(__fsqrt_rn(v), bc2_sqrt) + eps;
     p = p - step_size * __fdiv_rn(m, denom);
 }
@@ -295,10 +295,10 @@ __global__ void __launch_bounds__(kAdamThreads) adam_multi_kernel(const AdamPack
         }
 #pragma unroll
         for (int k = 0; k < kAdamVecPerThread; ++k) {
-            adam_one(P4[k].x, G4[k].x, M4[k].x, V4[k].x, a.beta1, a.beta2, a.eps, ss, bs);
-            adam_one(P4[k].y, G4[k].y, M4[k].y, V4[k].y, a.beta1, a.beta2, a.eps, ss, bs);
-            adam_one(P4[k].z, G4[k].z, M4[k].z, V4[k].z, a.beta1, a.beta2, a.eps, ss, bs);
-            adam_one(P4[k].w, G4[k].w, M4[k].w, V4[k].w, a.beta1, a.beta2, a.eps, ss, bs);
+            adam_one(P4[k].x, G4[k].x, M4[k].x, V4[k].x, a.omb1, a.beta2, a.omb2, a.eps, ss, bs);
+            adam_one(P4[k].y, G4[k].y, M4[k].y, V4[k].y, a.omb1, a.beta2, a.omb2, a.eps, ss, bs);
+            adam_one(P4[k].z, G4[k].z, M4[k].z, V4[k].z, a.omb1, a.beta2, a.omb2, a.eps, ss, bs);
+            adam_one(P4[k].w, G4[k].w, M4[k].w, V4[k].w, a.omb1, a.beta2, a.omb2, a.eps, ss, bs);
         }
 #pragma unroll
         for (int k = 0; k < kAdamVecPerThread; ++k) {
@@ -308,7 +308,7 @@ __global__ void __launch_bounds__(kAdamThreads) adam_multi_kernel(const AdamPack
     } else {
         for (long long i = base + threadIdx.x; i < min(n, base + (long long)kAdamChunk); i += kAdamThreads) {
             float pp = p[i], mm = m[i], vv = v[i];
-            adam_one(pp, g[i], mm, vv, a.beta1, a.beta2, a.eps, ss, bs);
+            adam_one(pp, g[i], mm, vv, a.omb1, a.beta2, a.omb2, a.eps, ss, bs);
             p[i] = pp; m[i] = mm; v[i] = vv;
         }
     }
@@ -358,12 +358,12 @@ int gsr_l1_ssim_backward(int channels, int height, int width, const float* image
     return check_last("l1_ssim_backward", false, s);
 }
 
-int gsr_adam_step(const gsr_adam_tensor* tensors, int count, float beta1, float beta2, float eps, void* stream) {
+int gsr_adam_step(const gsr_adam_tensor* tensors, int count, double beta1, double beta2, double eps, void* stream) {
     if (count < 0 || (count > 0 && !tensors)) { set_error("adam_step: bad arguments"); return GSR_ERR_INVALID; }
     cudaStream_t s = (cudaStream_t)stream;
     int i = 0, launched = 0;
     while (i < count) {
-        AdamPack a; a.count = 0; a.beta1 = beta1; a.beta2 = beta2; a.eps = eps;
+        AdamPack a; a.count = 0; a.beta1 = (float)beta1; a.beta2 = (float)beta2; a.omb1 = (float)(1.0 - beta1); a.omb2 = (float)(1.0 - beta2); a.eps = (float)eps;
         long long blocks = 0;
         for (; i < count && a.count < kAdamMaxGroups; ++i) {
             const gsr_adam_tensor& t = tensors[i];
@@ -375,8 +375,8 @@ int gsr_adam_step(const gsr_adam_tensor* tensors, int count, float beta1, float 
             const int k = a.count++;
             a.p[k] = t.param; a.g[k] = t.grad; a.m[k] = t.exp_avg; a.v[k] = t.exp_avg_sq; a.n[k] = t.n;
             // the bias corrections in double like Python floats (torch: 1 - beta ** step), then one rounding to float
-            const double bc1 = 1.0 - pow((double)beta1, (double)t.step), bc2 = 1.0 - pow((double)beta2, (double)t.step);
-            a.step_size[k] = (float)((double)t.lr / bc1);
+            const double bc1 = 1.0 - pow(beta1, (double)t.step), bc2 = 1.0 - pow(beta2, (double)t.step);
+            a.step_size[k] = (float)(t.lr / bc1);
             a.bc2_sqrt[k] = (float)sqrt(bc2);
             blocks += nb; a.block_end[k] = (int)blocks;
         }

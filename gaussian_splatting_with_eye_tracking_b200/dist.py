@@ -174,6 +174,68 @@ class GradientAllReduce:
         self.wait()
 
 
+class PeerAllReduce:
+    """In-place SUM of one float32 buffer over NVLink peer memory (gsr_peer_allreduce_sum): every rank's buffer is mapped
+    into every other rank's address space (torch symmetric memory = cuMem + fabric/IPC handles; plumbing only), and one
+    kernel per rank pulls its 1/world slice from all peers, adds in rank order and pushes the sum back to all of them.
+    The four dense gradients of the view-parallel backward are written straight into ``data``
+    (``_host.rasterize_gaussians_backward(..., dense_out=peer.data)``), so there is no bucket copy on either side.
+    (world-1)/world of the payload crosses NVLink in each direction per GPU, concurrently, against 2x that, serialised
+    over ring or tree steps, for ncclAllReduce; the result is bit-identical on all ranks."""
+
+    def __init__(self, numel: int, device, group=None):
+        from ._capi import lib
+        self._lib = lib
+        self.group = group
+        self.world = world_size()
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self.numel = (int(numel) + 3) // 4 * 4
+        self.flag_bytes = int(lib.gsr_peer_flag_bytes(self.world))
+        total = self.numel + self.flag_bytes // 4
+        dev = torch.device(device)
+        if self.world > 1:
+            import torch.distributed._symmetric_memory as symm
+            self.buf = symm.empty(total, dtype=torch.float32, device=dev)
+            grp = group if group is not None else dist.group.WORLD
+            try:
+                self.hdl = symm.rendezvous(self.buf, grp.group_name)
+            except TypeError:
+                self.hdl = symm.rendezvous(self.buf, grp)
+            self.bases_dev = int(self.hdl.buffer_ptrs_dev)
+            self._bases_keep = None
+        else:
+            self.buf = torch.empty(total, dtype=torch.float32, device=dev)
+            self._bases_keep = torch.tensor([self.buf.data_ptr()], dtype=torch.int64, device=dev)
+            self.bases_dev = self._bases_keep.data_ptr()
+            self.hdl = None
+        self.buf[self.numel:].zero_()                # flag words: zero on every rank before anyone signals
+        torch.cuda.synchronize(dev)
+        if self.world > 1:
+            dist.barrier(group)
+        self.epoch = 1
+
+    @property
+    def data(self) -> torch.Tensor:
+        return self.buf[: self.numel]
+
+    def all_reduce(self, numel: Optional[int] = None) -> None:
+        """Queue barrier + reduce + barrier on the CURRENT stream; ``numel`` (multiple of 4) limits the sum to a prefix."""
+        import ctypes as C
+        from ._capi import check
+        n = self.numel if numel is None else int(numel)
+        if n % 4 or n > self.numel:
+            raise RuntimeError("PeerAllReduce.all_reduce: numel must be a multiple of 4 within the buffer")
+        with torch.cuda.device(self.buf.device):
+            check(self._lib.gsr_peer_allreduce_sum(C.c_void_p(self.bases_dev), 0, n, self.numel * 4, self.world, self.rank,
+                                                   self.epoch, C.c_void_p(torch.cuda.current_stream().cuda_stream)),
+                  "gsr_peer_allreduce_sum")
+        self.epoch += 2
+
+    def timed_out(self) -> bool:
+        """True if a barrier's watchdog fired (a rank never arrived).  Synchronises; diagnostics only."""
+        return bool(self.buf[self.numel + self.world].view(torch.int32).item())
+
+
 class ShGradExchange:
     """View-parallel gradient exchange with the SH gradient sent as its rank-1 factor.
 
@@ -188,13 +250,15 @@ class ShGradExchange:
     """
 
     def __init__(self, rebuild=None, bucket_bytes: int = DEFAULT_BUCKET_BYTES, group=None, packed: bool = False,
-                 pack=None, rebuild_packed=None):
+                 pack=None, rebuild_packed=None, peer: Optional["PeerAllReduce"] = None):
         """``packed``: only the rows of the Gaussians visible in a view (radii > 0) travel, with a bit mask and a
         per-word prefix that locate them (``pack`` = _host.pack_visible_rows, ``rebuild_packed`` =
         _host.sh_grad_from_packed_views; both injectable for the CPU protocol tests).  The ranks must then call
         ``post_visible_count`` after their forward: the all-gather is sized by the largest count."""
         self.group = group
         self.reducer = GradientAllReduce(bucket_bytes, group)
+        self.peer = peer               # the 11 dense floats summed in place over NVLink peer memory instead of NCCL
+        self._peer_stream = None
         self._rebuild = rebuild
         self.packed = bool(packed)
         self._pack = pack
@@ -327,6 +391,20 @@ class ShGradExchange:
 
     def start_reduce(self, dense_grads: Sequence[torch.Tensor]) -> None:
         """Queue the in-place SUM of the remaining gradients (means3D, opacity, scales, rotations)."""
+        if self.peer is not None:
+            lo = min(t.data_ptr() for t in dense_grads)
+            hi = max(t.data_ptr() + t.numel() * 4 for t in dense_grads)
+            base = self.peer.data.data_ptr()
+            if lo != base or hi > base + self.peer.numel * 4:
+                raise RuntimeError("ShGradExchange(peer=...): the dense gradients must be written into peer.data "
+                                   "(rasterize_gaussians_backward(..., dense_out=peer.data))")
+            dev = dense_grads[0].device
+            if self._peer_stream is None:
+                self._peer_stream = comm_stream(dev)
+            self._peer_stream.wait_stream(torch.cuda.current_stream(dev))
+            with torch.cuda.stream(self._peer_stream):
+                self.peer.all_reduce(((hi - base) // 4 + 3) // 4 * 4)
+            return
         self.reducer.start(dense_grads)
 
     def start_reduce_chunk(self, chunk_grads: Sequence[torch.Tensor]) -> None:
@@ -348,6 +426,8 @@ class ShGradExchange:
         # all-reduce queued by start_reduce is NVLink-bound -- so the rebuild overlaps the all-reduce instead.
         dsh = self._rebuild_call() if self._rebuild_call is not None else None
         self.reducer.wait()
+        if self._peer_stream is not None:
+            torch.cuda.current_stream().wait_stream(self._peer_stream)
         self._rebuild_call, self._keep = None, None
         # (the persistent gather buffers are safe: the next start_gather makes the side stream wait for this one)
         for t in self._side_allocs:

@@ -290,7 +290,7 @@ typedef struct gsr_adam_tensor {
     float* exp_avg;          /* [n] updated in place */
     float* exp_avg_sq;       /* [n] updated in place */
     long long n;
-    float lr;
+    double lr;               /* doubles like the Python floats torch derives its step size from */
     int step;
 } gsr_adam_tensor;
 GSR_API size_t gsr_l1_ssim_partials(int channels, int height, int width);
@@ -298,7 +298,20 @@ GSR_API int gsr_l1_ssim_forward(int channels, int height, int width, const float
                                 float w_const, float* maps, float* partials, float* out, void* stream);
 GSR_API int gsr_l1_ssim_backward(int channels, int height, int width, const float* image, const float* gt, float w_l1, float w_ssim,
                                  const float* maps, const float* dloss, float* dL_dimage, void* stream);
-GSR_API int gsr_adam_step(const gsr_adam_tensor* tensors, int count, float beta1, float beta2, float eps, void* stream);
+GSR_API int gsr_adam_step(const gsr_adam_tensor* tensors, int count, double beta1, double beta2, double eps, void* stream);
+
+/* ---- view-parallel gradient sum over NVLink peer memory (replaces the NCCL all-reduce of the 11 dense
+ * floats per Gaussian that follows the preprocess-stage backward) ----
+ * peer_bases: DEVICE array of `world` base pointers, entry k = rank k's buffer as addressable from THIS device (peer-mapped
+ * by the host: torch symmetric memory / cudaIpc; all on one device in the single-GPU tests).  Every buffer holds the data
+ * ([n_floats] at data_offset, 16-byte aligned) and gsr_peer_flag_bytes(world) of flag words at flag_offset, zeroed once
+ * before first use.  gsr_peer_allreduce_sum = barrier(epoch) + one kernel in which rank r loads the r-th 1/world slice
+ * from every peer in rank order, adds, and stores the sum into every peer's buffer + barrier(epoch + 1): in place, the same
+ * bits on every rank.  `epoch` must grow by 2 per call (by 1 per gsr_peer_barrier), identically on all ranks, from 1. */
+GSR_API size_t gsr_peer_flag_bytes(int world);
+GSR_API int gsr_peer_barrier(void* const* peer_bases, size_t flag_offset, int world, int rank, unsigned epoch, void* stream);
+GSR_API int gsr_peer_allreduce_sum(void* const* peer_bases, size_t data_offset, long long n_floats, size_t flag_offset, int world,
+                                   int rank, unsigned epoch, void* stream);
 
 /* ---- tuning knobs (results never depend on them) ---- */
 enum { GSR_OPT_SORT_VARIANT = 0,  /* onesweep tile shape for u32 keys: 0 = default, 1..5 see gsr_binning.cu */

@@ -9,8 +9,8 @@ import pytest
 import torch
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-sys.path.insert(0, os.path.join(ROOT, "oracle"))
-import loss_oracle as lo  # noqa: E402
+sys.path.insert(0, ROOT)
+from oracle import loss_oracle as lo  # noqa: E402
 
 GOLDEN = os.path.join(ROOT, "tests", "golden")
 CASES = ["small", "tiny", "edge32", "mono"]

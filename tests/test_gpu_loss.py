@@ -12,8 +12,8 @@ import torch
 import torch.nn.functional as F
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-sys.path.insert(0, os.path.join(ROOT, "oracle"))
-import loss_oracle as lo  # noqa: E402
+sys.path.insert(0, ROOT)
+from oracle import loss_oracle as lo  # noqa: E402
 
 pytestmark = pytest.mark.gpu
 GOLDEN = os.path.join(ROOT, "tests", "golden")
