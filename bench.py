@@ -512,6 +512,60 @@ def measure(impl, args, d, cams, rank, world, timer, full):
                                                 "range's 11 floats reduced while the next is computed; *_peer_sum = the 11 floats summed in place over NVLink peer "
                                                 "memory by gsr_peer_allreduce_sum (two-shot pull/push, one kernel) instead of ncclAllReduce"}
 
+    # ---- the WHOLE data-parallel training iteration (config C4 shape, train.py:83-121): render -> L1/SSIM loss -> backward ->
+    # gradient exchange -> Adam.  The SH coefficients' Adam update (48 of 59 floats) needs only the locally rebuilt SH gradient,
+    # so it runs under the dense sum that is still on NVLink ("sh_adam_first"); "exchange_then_adam" waits for everything first.
+    # Learning rates are ~0 so the scene (and with it the per-frame workload) stays put; the kernels' work does not depend on them.
+    if is_ours:
+        from gaussian_splatting_with_eye_tracking_b200 import loss_utils, optim
+        gen = torch.Generator().manual_seed(4004 + rank)
+        gts = [torch.rand(3, args.height, args.width, generator=gen).to(dev) for _ in range(2)]
+        keys = ("means3D", "shs", "opacities", "scales", "rotations")
+        fullms = {}
+        variants = [("sh_adam_first", True, peer_red is not None), ("exchange_then_adam", False, peer_red is not None)]
+        if world > 1 and peer_red is not None:
+            variants.append(("sh_adam_first_nccl_sum", True, False))
+        for vname, sh_first, use_peer in variants:
+            prm = {k: torch.nn.Parameter(d[k].detach().clone()) for k in keys}
+            opt = optim.FusedAdam([{"params": [prm[k]], "lr": 1e-12, "name": k} for k in keys], lr=0.0, eps=1e-15)
+            exch = gdist.ShGradExchange(packed=True, peer=peer_red if use_peer else None)
+
+            def full_step(i, prm=prm, opt=opt, exch=exch, sh_first=sh_first, use_peer=use_peer):
+                cam = cam_of(i)
+                m3, sh_, op_, sc_, ro_ = (prm[k].data for k in keys)
+                N, img, radii, gb, bb, ib = impl.host.rasterize_gaussians(
+                    d["bg"], m3, e_, op_, sc_, ro_, 1.0, e_, cam.world_view_transform, cam.full_proj_transform, cam.tanfovx, cam.tanfovy,
+                    cam.image_height, cam.image_width, sh_, d["sh_degree"], cam.camera_center, False, False)
+                exch.post_visible_count(impl.host.last_counts(gb, P_)[2], dev)
+                x = img.requires_grad_(True)
+                loss_utils.l1_ssim_loss(x, gts[i % 2], 0.2).backward()
+                g = impl.host.rasterize_gaussians_backward(
+                    d["bg"], m3, radii, e_, sc_, ro_, 1.0, e_, cam.world_view_transform, cam.full_proj_transform, cam.tanfovx, cam.tanfovy,
+                    x.grad, sh_, d["sh_degree"], cam.camera_center, gb, N, bb, ib, False, compact_sh=True,
+                    between_phases=lambda drgb: exch.start_gather(drgb, cam.camera_center, m3, d["sh_degree"], M_, radii=radii),
+                    dense_out=peer_red.data if use_peer else None)
+                exch.start_reduce([g[3], g[2], g[6], g[7]])
+                if sh_first:
+                    prm["shs"].grad = exch.finish_sh()
+                    opt.step()                                   # SH coefficients only: the other gradients are still None
+                    prm["shs"].grad = None
+                    exch.finish_dense()
+                else:
+                    prm["shs"].grad = exch.finish()
+                prm["means3D"].grad, prm["opacities"].grad, prm["scales"].grad, prm["rotations"].grad = g[3], g[2], g[6], g[7]
+                opt.step()
+                for p_ in prm.values():
+                    p_.grad = None
+            fullms[vname] = timer.run(full_step, Kb, 2) / Kb
+            del opt, prm, exch
+            torch.cuda.empty_cache()
+        bestv = min(fullms, key=fullms.get)
+        out["dp_train_full_step"] = {"ms_per_step": fullms[bestv], "views_per_s": world / (fullms[bestv] / 1e3), "variant": bestv,
+                                     "ms_per_step_by_variant": {k: round(v, 4) for k, v in fullms.items()},
+                                     "what": "render + fused L1/SSIM loss + backward + view-parallel exchange (packed rank-1 SH rows gathered, 11 dense "
+                                             "floats summed over NVLink peer memory when world > 1) + multi-tensor Adam, one view per rank and step; "
+                                             "weak-scaling efficiency = this line at N=1 / at N"}
+
     # ---- screen-tile bands (config C5 shape): ONE foveated frame split over the ranks by rows of 32-px tiles, balanced by the
     # previous frame's per-row pair counts; per-tile counts all-reduced so the AMR levels equal the single-GPU ones
     if is_ours:
@@ -617,7 +671,8 @@ def train_step_bench(impl, ref_impl, d, cams, args, timer_iters=12):
     H, W = args.height, args.width
     g = torch.Generator().manual_seed(4004)
     gts = [torch.rand(3, H, W, generator=g).to(dev) for _ in range(2)]
-    lrs = {"means3D": 1.6e-4, "shs": 2.5e-3, "opacities": 0.05, "scales": 5e-3, "rotations": 1e-3}
+    # learning rates ~0: the scene (hence the per-frame workload) stays put over the timed iterations; Adam's work does not depend on them
+    lrs = {"means3D": 1.6e-12, "shs": 2.5e-12, "opacities": 5e-12, "scales": 5e-12, "rotations": 1e-12}
     keys = ("means3D", "shs", "opacities", "scales", "rotations")
     out = {}
 
@@ -761,7 +816,7 @@ def main():
                                 "traffic": NCU_TRAFFIC_BYTES.get(args.gaussians), "peak_source": peak_src, "launch_ms": st["preprocess"],
                                 "alg_bytes_per_launch": alg, "visible_per_launch": vis, "culled_per_launch": args.gaussians - vis,
                                 "alg_bytes_per_visible": ALG_BYTES_VISIBLE, "alg_bytes_per_culled": ALG_BYTES_CULLED}
-        extra = {k: m[k] for k in ("num_rendered", "stages_ms", "fwd_bwd_ms_per_view", "bwd_stages_ms", "dp_train", "dp_train_rank1_sh", "tile_bands", "amr") if k in m}
+        extra = {k: m[k] for k in ("num_rendered", "stages_ms", "fwd_bwd_ms_per_view", "bwd_stages_ms", "dp_train", "dp_train_rank1_sh", "dp_train_full_step", "tile_bands", "amr") if k in m}
         extra["pairs_per_gaussian_mean"] = N / args.gaussians
         extra["visible_mean"] = m.get("mean_visible")
         if full and rank == 0 and eff_world == 1:

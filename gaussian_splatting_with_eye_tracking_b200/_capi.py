@@ -114,6 +114,7 @@ SYMBOLS = {
     "gsr_peer_flag_bytes": (C.c_size_t, [C.c_int]),
     "gsr_peer_barrier": (C.c_int, [C.c_void_p, C.c_size_t, C.c_int, C.c_int, C.c_uint, C.c_void_p]),
     "gsr_peer_allreduce_sum": (C.c_int, [C.c_void_p, C.c_size_t, C.c_longlong, C.c_size_t, C.c_int, C.c_int, C.c_uint, C.c_void_p]),
+    "gsr_peer_allreduce_sum_mc": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_longlong, C.c_size_t, C.c_int, C.c_int, C.c_uint, C.c_void_p]),
     "gsr_launch_count": (C.c_ulonglong, []),
     "gsr_set_option": (C.c_int, [C.c_int, C.c_int]),
     "gsr_profile_enable": (None, [C.c_int]),

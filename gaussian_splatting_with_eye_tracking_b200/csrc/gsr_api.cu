@@ -280,6 +280,7 @@ const char* gsr_last_error(void) { return g_err; }
 int gsr_set_option(int option, int value) {
     if (option == GSR_OPT_SORT_VARIANT && value >= 0 && value <= 5) { set_sort_variant(value); return GSR_OK; }
     if (option == GSR_OPT_BLEND_VARIANT && value >= 0 && value <= 1) { set_blend_variant(value); return GSR_OK; }
+    if (option == GSR_OPT_PEER_CTAS_PER_SM && value >= 0 && (value & 0xff) <= 32 && value < 0x300) { set_peer_ctas_per_sm(value); return GSR_OK; }
     set_error("unknown option %d / value %d", option, value);
     return GSR_ERR_INVALID;
 }

@@ -289,6 +289,7 @@ size_t sort_prezero_bytes(long long n, const SortPlan& plan, size_t temp_bytes, 
 void launch_zero(void* ptr, size_t bytes, cudaStream_t s);   // bytes % 16 == 0, ptr 16 B aligned
 void set_sort_variant(int v);
 void set_blend_variant(int v);
+void set_peer_ctas_per_sm(int v);   // gsr_peer.cu: grid cap of the reduce kernels in CTAs per SM; 0 = default
 
 void launch_amr_levels(const ImgPtrs& im, int num_tiles, cudaStream_t s);
 void launch_fovea_levels(const ImgPtrs& im, int num_tiles, int fovea_step, const gsr_gaze* gaze, cudaStream_t s);

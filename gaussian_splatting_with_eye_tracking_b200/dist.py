@@ -183,7 +183,9 @@ class PeerAllReduce:
     (world-1)/world of the payload crosses NVLink in each direction per GPU, concurrently, against 2x that, serialised
     over ring or tree steps, for ncclAllReduce; the result is bit-identical on all ranks."""
 
-    def __init__(self, numel: int, device, group=None):
+    def __init__(self, numel: int, device, group=None, multicast: Optional[bool] = None):
+        """``multicast``: form the sum inside the NVSwitch (gsr_peer_allreduce_sum_mc); None = when the mapping exists and
+        world > 2 (at world 2 the unicast kernel moves the same bytes and keeps the rank-ordered sum)."""
         from ._capi import lib
         self._lib = lib
         self.group = group
@@ -203,11 +205,17 @@ class PeerAllReduce:
                 self.hdl = symm.rendezvous(self.buf, grp)
             self.bases_dev = int(self.hdl.buffer_ptrs_dev)
             self._bases_keep = None
+            mc = int(getattr(self.hdl, "multicast_ptr", 0) or 0)
+            want = (self.world > 2) if multicast is None else bool(multicast)
+            if multicast and not mc:
+                raise RuntimeError("PeerAllReduce(multicast=True): no multicast mapping on this system")
+            self.multicast_ptr = mc if want else 0
         else:
             self.buf = torch.empty(total, dtype=torch.float32, device=dev)
             self._bases_keep = torch.tensor([self.buf.data_ptr()], dtype=torch.int64, device=dev)
             self.bases_dev = self._bases_keep.data_ptr()
             self.hdl = None
+            self.multicast_ptr = 0
         self.buf[self.numel:].zero_()                # flag words: zero on every rank before anyone signals
         torch.cuda.synchronize(dev)
         if self.world > 1:
@@ -226,9 +234,14 @@ class PeerAllReduce:
         if n % 4 or n > self.numel:
             raise RuntimeError("PeerAllReduce.all_reduce: numel must be a multiple of 4 within the buffer")
         with torch.cuda.device(self.buf.device):
-            check(self._lib.gsr_peer_allreduce_sum(C.c_void_p(self.bases_dev), 0, n, self.numel * 4, self.world, self.rank,
-                                                   self.epoch, C.c_void_p(torch.cuda.current_stream().cuda_stream)),
-                  "gsr_peer_allreduce_sum")
+            st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+            if self.multicast_ptr:
+                check(self._lib.gsr_peer_allreduce_sum_mc(C.c_void_p(self.bases_dev), C.c_void_p(self.multicast_ptr), 0, n,
+                                                          self.numel * 4, self.world, self.rank, self.epoch, st),
+                      "gsr_peer_allreduce_sum_mc")
+            else:
+                check(self._lib.gsr_peer_allreduce_sum(C.c_void_p(self.bases_dev), 0, n, self.numel * 4, self.world, self.rank,
+                                                       self.epoch, st), "gsr_peer_allreduce_sum")
         self.epoch += 2
 
     def timed_out(self) -> bool:
@@ -417,23 +430,35 @@ class ShGradExchange:
         self.start_gather(dL_dcolors_clamped, campos, means3D, degree, M, radii)
         self.start_reduce(dense_grads)
 
-    def finish(self) -> torch.Tensor:
-        """Wait (the current stream, not the host) for the exchange; returns the SH gradient [P,M,3] summed over all views."""
+    def finish_sh(self) -> torch.Tensor:
+        """Wait (the current stream, not the host) for the row gather and rebuild the SH gradient [P,M,3] summed over all
+        views -- WITHOUT waiting for the dense sum: a training step runs Adam on the SH coefficients (48 of the 59 floats
+        per Gaussian, ~80 % of the optimizer's HBM traffic) right after this, under the dense sum still on NVLink, and only
+        then calls finish_dense()."""
         if self._stream is not None:
             torch.cuda.current_stream().wait_stream(self._stream)
         # The rebuild runs HERE, on the caller's stream behind the backward, not on the side stream: it is HBM-bound
         # like the preprocess-stage backward (running both at once only slows the backward down, measured), while the
         # all-reduce queued by start_reduce is NVLink-bound -- so the rebuild overlaps the all-reduce instead.
         dsh = self._rebuild_call() if self._rebuild_call is not None else None
-        self.reducer.wait()
-        if self._peer_stream is not None:
-            torch.cuda.current_stream().wait_stream(self._peer_stream)
         self._rebuild_call, self._keep = None, None
         # (the persistent gather buffers are safe: the next start_gather makes the side stream wait for this one)
         for t in self._side_allocs:
             if t.is_cuda:
                 t.record_stream(torch.cuda.current_stream())  # allocated on the side stream, read by the rebuild here
         self._side_allocs = []
+        return dsh
+
+    def finish_dense(self) -> None:
+        """Wait (the current stream) for the sum of the dense gradients queued by start_reduce / start_reduce_chunk."""
+        self.reducer.wait()
+        if self._peer_stream is not None:
+            torch.cuda.current_stream().wait_stream(self._peer_stream)
+
+    def finish(self) -> torch.Tensor:
+        """finish_sh() + finish_dense(): returns the SH gradient [P,M,3] summed over all views; all gradients final."""
+        dsh = self.finish_sh()
+        self.finish_dense()
         return dsh
 
     @staticmethod

@@ -310,12 +310,18 @@ GSR_API int gsr_adam_step(const gsr_adam_tensor* tensors, int count, double beta
  * bits on every rank.  `epoch` must grow by 2 per call (by 1 per gsr_peer_barrier), identically on all ranks, from 1. */
 GSR_API size_t gsr_peer_flag_bytes(int world);
 GSR_API int gsr_peer_barrier(void* const* peer_bases, size_t flag_offset, int world, int rank, unsigned epoch, void* stream);
+/* the same with the sum formed inside the NVSwitch: multicast_base = the multicast (cuMulticast) mapping of the same buffers;
+ * multimem.ld_reduce + multimem.st, (1 + 1/world) x payload per direction instead of 2 (world-1)/world.  Identical bits on
+ * all ranks; the switch's add order is not the rank order of the unicast variant. */
+GSR_API int gsr_peer_allreduce_sum_mc(void* const* peer_bases, void* multicast_base, size_t data_offset, long long n_floats,
+                                      size_t flag_offset, int world, int rank, unsigned epoch, void* stream);
 GSR_API int gsr_peer_allreduce_sum(void* const* peer_bases, size_t data_offset, long long n_floats, size_t flag_offset, int world,
                                    int rank, unsigned epoch, void* stream);
 
 /* ---- tuning knobs (results never depend on them) ---- */
 enum { GSR_OPT_SORT_VARIANT = 0,  /* onesweep tile shape for u32 keys: 0 = default, 1..5 see gsr_binning.cu */
-       GSR_OPT_BLEND_VARIANT = 1  /* forward blend: 0 = two pixels per thread, packed FP32x2 (default); 1 = one pixel per thread */ };
+       GSR_OPT_BLEND_VARIANT = 1, /* forward blend: 0 = two pixels per thread, packed FP32x2 (default); 1 = one pixel per thread */
+       GSR_OPT_PEER_CTAS_PER_SM = 2 /* gsr_peer_allreduce_sum*: grid cap in CTAs per SM, 0 = default */ };
 GSR_API int gsr_set_option(int option, int value);
 
 /* counters: how many kernels this library launched since load (bench.py "gpu_launches") */
