@@ -819,7 +819,7 @@ def main():
         extra = {k: m[k] for k in ("num_rendered", "stages_ms", "fwd_bwd_ms_per_view", "bwd_stages_ms", "dp_train", "dp_train_rank1_sh", "dp_train_full_step", "tile_bands", "amr") if k in m}
         extra["pairs_per_gaussian_mean"] = N / args.gaussians
         extra["visible_mean"] = m.get("mean_visible")
-        if full and rank == 0 and eff_world == 1:
+        if full and rank == 0 and eff_world == 1 and not os.environ.get("GSR_BENCH_SKIP_REF"):
             from oracle import ref_cuda
             if ref_cuda.available(False):
                 a2 = argparse.Namespace(**vars(args)); a2.steps = max(5, args.steps // 4); a2.warmup = 3
