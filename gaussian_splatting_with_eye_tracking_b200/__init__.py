@@ -8,7 +8,9 @@ _capi.py         ctypes binding of that ABI (loads libgsr_b200.so; raises if it 
 _host.py         PyTorch host shim with the reference's `_C` call signatures
 rasterizer.py    GaussianRasterizationSettings / GaussianRasterizer / autograd functions (baseline + AMR)
 scenes.py        deterministic synthetic Gaussian clouds and cameras
-dist.py          data-parallel views (NCCL gradient all-reduce) and screen-tile-band split
+dist.py          data-parallel views (NCCL / NVLink peer-memory gradient exchange) and screen-tile-band split
+loss_utils.py    l1_loss / ssim / l1_ssim_loss of the reference's utils/loss_utils.py as one kernel per direction
+optim.py         FusedAdam: torch.optim.Adam's state layout, every parameter group in one launch
 
 The drop-in packages `diff_gaussian_rasterization` and `diff_gaussian_rasterization_amr` at the repository root
 re-export this API under the reference's import names.
