@@ -318,7 +318,9 @@ GSR_API int gsr_peer_allreduce_sum_mc(void* const* peer_bases, void* multicast_b
 GSR_API int gsr_peer_allreduce_sum(void* const* peer_bases, size_t data_offset, long long n_floats, size_t flag_offset, int world,
                                    int rank, unsigned epoch, void* stream);
 
-/* ---- tuning knobs (results never depend on them) ---- */
+/* ---- tuning knobs (results never depend on them, with ONE exception: GSR_OPT_PEER_CTAS_PER_SM values >= 0x100 put the
+ * unicast peer kernel into a link-diagnostic mode -- 0x1xx = remote loads only, 0x2xx = remote stores only -- that does NOT
+ * compute the sum; tools/peer_diag.py uses it to time the two directions and nothing else may) ---- */
 enum { GSR_OPT_SORT_VARIANT = 0,  /* onesweep tile shape for u32 keys: 0 = default, 1..5 see gsr_binning.cu */
        GSR_OPT_BLEND_VARIANT = 1, /* forward blend: 0 = two pixels per thread, packed FP32x2 (default); 1 = one pixel per thread */
        GSR_OPT_PEER_CTAS_PER_SM = 2 /* gsr_peer_allreduce_sum*: grid cap in CTAs per SM, 0 = default */ };

@@ -168,6 +168,30 @@ def body_sh_grad_exchange(rank, world):
     assert pb["allreduce"] + pb["allgather_in"] < pb["dense_allreduce_equivalent"]
 
 
+def body_sh_grad_exchange_split_finish(rank, world):
+    """finish_sh() hands out the summed SH gradient before the dense sum is waited for (the training step runs the SH
+    coefficients' Adam update in between); finish_dense() then completes the four dense tensors.  Two steps in a row on one
+    exchange object: no state leaks from one to the next."""
+    P, M, deg = 300, 16, 3
+    means = torch.randn(P, 3, generator=torch.Generator().manual_seed(8))
+    ex = gdist.ShGradExchange(rebuild=_rebuild_ref, bucket_bytes=1 << 20)
+    for step in range(2):
+        def view(r):
+            g = torch.Generator().manual_seed(300 + 10 * step + r)
+            return (torch.randn(3, generator=g) * 4, torch.randn(P, 3, generator=g),
+                    [torch.randn(P, 3, generator=g), torch.randn(P, 1, generator=g), torch.randn(P, 3, generator=g), torch.randn(P, 4, generator=g)])
+        cam, drgb, dense = view(rank)
+        ex.start_gather(drgb, cam, means, deg, M)
+        ex.start_reduce(dense)
+        dsh = ex.finish_sh()
+        want_sh = sum(_rebuild_ref(means, view(r)[0][None], view(r)[1][None], deg, M) for r in range(world))
+        assert torch.allclose(dsh, want_sh, rtol=1e-5, atol=1e-6)
+        ex.finish_dense()
+        for i in range(4):
+            assert torch.allclose(dense[i], sum(view(r)[2][i] for r in range(world)), rtol=1e-6, atol=1e-6), (step, i)
+        assert ex.finish_sh() is None                    # nothing pending any more
+
+
 def _pack_ref(rows, radii, cap, out_rows, out_meta):
     """torch restatement of gsr_pack_visible_rows (mask words, exclusive per-word popcount prefix, rows in index order)."""
     P = rows.shape[0]
@@ -315,3 +339,28 @@ def test_sh_grad_exchange_world2():
 
 def test_sh_grad_exchange_world3():
     _run("body_sh_grad_exchange", 3)
+
+
+def test_sh_grad_exchange_split_finish_world2():
+    _run("body_sh_grad_exchange_split_finish", 2)
+
+
+def test_peer_sum_refuses_gradients_outside_its_buffer():
+    """ShGradExchange(peer=...) sums in place in peer-mapped memory: gradients living anywhere else are a caller bug, reported
+    before anything is queued (the backward must be given dense_out=peer.data)."""
+    class FakePeer:                                      # only the fields start_reduce looks at
+        numel = 44
+        data = torch.zeros(44)
+    ex = gdist.ShGradExchange(peer=FakePeer())
+    with pytest.raises(RuntimeError, match="dense_out=peer.data"):
+        ex.start_reduce([torch.zeros(4, 3), torch.zeros(4, 1), torch.zeros(4, 3), torch.zeros(4, 4)])
+
+
+def test_peer_abi_argument_validation_without_a_gpu():
+    from gaussian_splatting_with_eye_tracking_b200 import _capi
+    lib = _capi.lib
+    assert lib.gsr_peer_flag_bytes(8) == 256 and lib.gsr_peer_flag_bytes(0) == 0
+    assert lib.gsr_peer_allreduce_sum(None, 0, 8, 64, 2, 0, 1, None) == _capi.GSR_ERR_INVALID         # no pointer table
+    assert lib.gsr_peer_allreduce_sum_mc(None, None, 0, 8, 64, 2, 0, 1, None) == _capi.GSR_ERR_INVALID
+    assert lib.gsr_peer_barrier(None, 0, 2, 0, 1, None) == _capi.GSR_ERR_INVALID
+    assert b"peer" in lib.gsr_last_error()
