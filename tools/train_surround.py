@@ -48,7 +48,7 @@ def measure(P=3_000_000, W=1920, H=1080, dev=None, hbm_gbs=None):
     def ours():
         x.grad = None
         loss_utils.l1_ssim_loss(x, gt, 0.2).backward()
-    w1 = torch.tensor([float(v) for v in __import__("math").e ** (-(torch.arange(11.0) - 5) ** 2 / 4.5)])
+    w1 = torch.exp(-(torch.arange(11.0) - 5) ** 2 / 4.5)            # gaussian(11, 1.5), utils/loss_utils.py:23-25
     w1 = (w1 / w1.sum()).to(dev)
     win = (w1[:, None] @ w1[None, :]).expand(3, 1, 11, 11).contiguous()
 
