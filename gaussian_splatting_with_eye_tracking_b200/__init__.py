@@ -11,6 +11,8 @@ scenes.py        deterministic synthetic Gaussian clouds and cameras (SURVEY 8(d
 dist.py          data-parallel views (NCCL / NVLink peer-memory gradient exchange) and screen-tile-band split
 loss_utils.py    l1_loss / ssim / l1_ssim_loss of the reference's utils/loss_utils.py as one kernel per direction
 optim.py         FusedAdam: torch.optim.Adam's state layout, every parameter group in one launch
+scene_io.py      the reference's point-cloud PLY and cameras.json, plyfile-free
+model.py         GaussianModel with the reference class's interface (densify / prune / reset bookkeeping, schedules)
 
 The drop-in packages `diff_gaussian_rasterization` and `diff_gaussian_rasterization_amr` at the repository root
 re-export this API under the reference's import names.

@@ -1,0 +1,304 @@
+"""The Gaussian parameter container the training step works on ("densify/prune bookkeeping"), with the
+reference's ``GaussianModel`` interface (scene/gaussian_model.py) so that ``train.py`` and ``gaussian_renderer`` can hold one:
+same attribute names (``_xyz``, ``_features_dc``, ``_features_rest``, ``_scaling``, ``_rotation``, ``_opacity``,
+``max_radii2D``, ``xyz_gradient_accum``, ``denom``, ``optimizer``), same getters, same methods, same results.
+
+What differs is how the bookkeeping is done.  The reference re-materialises every parameter and both Adam moments three
+times per densification (clone: ``cat``; split: ``cat`` then boolean-mask prune; final prune: boolean mask), and every
+``tensor[mask]`` is its own ``nonzero`` + gather with a device-to-host round trip for the output size -- 18 of them per
+prune.  Here every restructuring step computes ONE row-index vector and applies it to all parameters, moments and
+statistics with ``index_select`` (`_regather`), and appended rows are concatenated in the same pass.  The row order, the
+values and the optimizer state are those of the reference (pinned by tests/golden/model_ref.npz, made by running the
+reference's own class on CPU).
+
+Device-agnostic host logic (PyTorch tensor ops only; no kernels of its own).  On CUDA parameters the optimizer is
+``optim.FusedAdam``; there is no silent CPU substitute -- CPU use (the tests) has to name an optimizer class.
+"""
+from __future__ import annotations
+
+import math
+from types import SimpleNamespace
+from typing import Dict, Optional
+
+import torch
+from torch import nn
+
+from . import scene_io
+
+SH_C0 = 0.28209479177387814
+GROUPS = ("xyz", "f_dc", "f_rest", "opacity", "scaling", "rotation")        # optimizer group order (gaussian_model.py:151-158)
+
+
+def optimization_defaults(**over) -> SimpleNamespace:
+    """OptimizationParams (arguments/__init__.py:72-90)."""
+    d = dict(iterations=30_000, position_lr_init=0.00016, position_lr_final=0.0000016, position_lr_delay_mult=0.01,
+             position_lr_max_steps=30_000, feature_lr=0.0025, opacity_lr=0.05, scaling_lr=0.005, rotation_lr=0.001,
+             percent_dense=0.01, lambda_dssim=0.2, densification_interval=100, opacity_reset_interval=3000,
+             densify_from_iter=500, densify_until_iter=15_000, densify_grad_threshold=0.0002)
+    d.update(over)
+    return SimpleNamespace(**d)
+
+
+def inverse_sigmoid(x: torch.Tensor) -> torch.Tensor:
+    return torch.log(x / (1 - x))                                          # utils/general_utils.py:18-19
+
+
+def expon_lr(step: int, lr_init: float, lr_final: float, lr_delay_steps: int = 0, lr_delay_mult: float = 1.0,
+             max_steps: int = 1_000_000) -> float:
+    """get_expon_lr_func(...)(step) (utils/general_utils.py:29-62): log-linear interpolation with an optional sine warm-up."""
+    if step < 0 or (lr_init == 0.0 and lr_final == 0.0):
+        return 0.0
+    delay = 1.0
+    if lr_delay_steps > 0:
+        delay = lr_delay_mult + (1 - lr_delay_mult) * math.sin(0.5 * math.pi * min(max(step / lr_delay_steps, 0.0), 1.0))
+    t = min(max(step / max_steps, 0.0), 1.0)
+    return delay * math.exp(math.log(lr_init) * (1 - t) + math.log(lr_final) * t)
+
+
+def quaternion_to_matrix(q: torch.Tensor) -> torch.Tensor:
+    """build_rotation (utils/general_utils.py:78-99): normalises, (r, x, y, z) order, [N,3,3]."""
+    q = q / torch.sqrt((q * q).sum(dim=1, keepdim=True))
+    r, x, y, z = q.unbind(dim=1)
+    rows = (1 - 2 * (y * y + z * z), 2 * (x * y - r * z), 2 * (x * z + r * y),
+            2 * (x * y + r * z), 1 - 2 * (x * x + z * z), 2 * (y * z - r * x),
+            2 * (x * z - r * y), 2 * (y * z + r * x), 1 - 2 * (x * x + y * y))
+    return torch.stack(rows, dim=1).reshape(-1, 3, 3)
+
+
+def mean_knn_dist2(points: torch.Tensor, k: int = 3, chunk: int = 4096) -> torch.Tensor:
+    """Mean squared distance to the k nearest neighbours -- what ``simple_knn._C.distCUDA2`` returns
+    (submodules/simple-knn, not part of this build: SURVEY 9).  Exact, chunked brute force; parity unpinned (the
+    reference's routine is CUDA-only and absent here)."""
+    P = points.shape[0]
+    out = torch.empty(P, dtype=points.dtype, device=points.device)
+    for a in range(0, P, chunk):
+        d = torch.cdist(points[a:a + chunk], points).pow(2)
+        kk = min(k + 1, P)
+        near = d.topk(kk, dim=1, largest=False).values[:, 1:]              # drop the point itself
+        out[a:a + chunk] = near.mean(dim=1) if near.shape[1] else 0.0
+    return out
+
+
+class GaussianModel:
+    def __init__(self, sh_degree: int, optimizer_cls=None):
+        self.active_sh_degree = 0
+        self.max_sh_degree = sh_degree
+        self._p: Dict[str, torch.Tensor] = {g: torch.empty(0) for g in GROUPS}
+        self.max_radii2D = torch.empty(0)
+        self.xyz_gradient_accum = torch.empty(0)
+        self.denom = torch.empty(0)
+        self.optimizer = None
+        self.percent_dense = 0
+        self.spatial_lr_scale = 0
+        self._optimizer_cls = optimizer_cls
+        self._lr_args = None
+        # activation handles under the reference's names (setup_functions, :26-42)
+        self.scaling_activation, self.scaling_inverse_activation = torch.exp, torch.log
+        self.opacity_activation, self.inverse_opacity_activation = torch.sigmoid, inverse_sigmoid
+        self.rotation_activation = torch.nn.functional.normalize
+
+    # ---- the six parameter tensors under the reference's attribute names
+    def _get(name):                                                         # noqa: N805
+        return property(lambda self: self._p[name], lambda self, v: self._p.__setitem__(name, v))
+    _xyz, _features_dc, _features_rest = _get("xyz"), _get("f_dc"), _get("f_rest")
+    _opacity, _scaling, _rotation = _get("opacity"), _get("scaling"), _get("rotation")
+    del _get
+
+    @property
+    def get_xyz(self):
+        return self._p["xyz"]
+
+    @property
+    def get_features(self):
+        return torch.cat((self._p["f_dc"], self._p["f_rest"]), dim=1)
+
+    @property
+    def get_opacity(self):
+        return torch.sigmoid(self._p["opacity"])
+
+    @property
+    def get_scaling(self):
+        return torch.exp(self._p["scaling"])
+
+    @property
+    def get_rotation(self):
+        return torch.nn.functional.normalize(self._p["rotation"])
+
+    def get_covariance(self, scaling_modifier=1):
+        """Upper triangle of R S S^T R^T, [P,6] (build_covariance_from_scaling_rotation, :27-31)."""
+        L = quaternion_to_matrix(self._p["rotation"]) * (scaling_modifier * self.get_scaling)[:, None, :]   # R @ diag(s)
+        S = L @ L.transpose(1, 2)
+        return torch.stack((S[:, 0, 0], S[:, 0, 1], S[:, 0, 2], S[:, 1, 1], S[:, 1, 2], S[:, 2, 2]), dim=1)
+
+    def oneupSHdegree(self):
+        self.active_sh_degree = min(self.active_sh_degree + 1, self.max_sh_degree)
+
+    # ---- construction
+    def _adopt(self, raw: Dict[str, torch.Tensor]) -> None:
+        names = {"xyz": "xyz", "f_dc": "features_dc", "f_rest": "features_rest", "opacity": "opacity", "scaling": "scaling",
+                 "rotation": "rotation"}
+        for g in GROUPS:
+            self._p[g] = nn.Parameter(raw[names[g]].detach().clone().contiguous().requires_grad_(True))
+        self.max_radii2D = torch.zeros(self.get_xyz.shape[0], device=self.get_xyz.device)
+
+    def create_from_pcd(self, pcd, spatial_lr_scale: float, device="cuda"):
+        """:122-146.  ``pcd`` has ``points`` [P,3] and ``colors`` [P,3] in [0,1] (BasicPointCloud)."""
+        self.spatial_lr_scale = spatial_lr_scale
+        dev = torch.device(device)
+        pts = torch.as_tensor(pcd.points, dtype=torch.float32).to(dev)
+        col = torch.as_tensor(pcd.colors, dtype=torch.float32).to(dev)
+        P, K = pts.shape[0], (self.max_sh_degree + 1) ** 2
+        sh = torch.zeros(P, K, 3, device=dev)
+        sh[:, 0] = (col - 0.5) / SH_C0                                     # RGB2SH (utils/sh_utils.py:114-115)
+        d2 = mean_knn_dist2(pts).clamp_min(1e-7)
+        rot = torch.zeros(P, 4, device=dev)
+        rot[:, 0] = 1
+        self._adopt({"xyz": pts, "features_dc": sh[:, :1], "features_rest": sh[:, 1:],
+                     "opacity": inverse_sigmoid(torch.full((P, 1), 0.1, device=dev)),
+                     "scaling": torch.log(torch.sqrt(d2))[:, None].repeat(1, 3), "rotation": rot})
+
+    def load_ply(self, path, device="cuda"):
+        raw = scene_io.load_ply(path, self.max_sh_degree, device=device)
+        self._adopt(raw)
+        self.active_sh_degree = self.max_sh_degree                         # :256
+
+    def save_ply(self, path):
+        scene_io.save_ply(path, *(self._p[g] for g in ("xyz", "f_dc", "f_rest", "opacity", "scaling", "rotation")))
+
+    # ---- optimizer
+    def training_setup(self, training_args):
+        self.percent_dense = training_args.percent_dense
+        P, dev = self.get_xyz.shape[0], self.get_xyz.device
+        self.xyz_gradient_accum = torch.zeros((P, 1), device=dev)
+        self.denom = torch.zeros((P, 1), device=dev)
+        a = training_args
+        lrs = {"xyz": a.position_lr_init * self.spatial_lr_scale, "f_dc": a.feature_lr, "f_rest": a.feature_lr / 20.0,
+               "opacity": a.opacity_lr, "scaling": a.scaling_lr, "rotation": a.rotation_lr}
+        groups = [{"params": [self._p[g]], "lr": lrs[g], "name": g} for g in GROUPS]
+        cls = self._optimizer_cls
+        if cls is None:
+            if dev.type != "cuda":
+                raise RuntimeError("GaussianModel: parameters are not on a CUDA device and no optimizer_cls was given "
+                                   "(optim.FusedAdam has no CPU path)")
+            from .optim import FusedAdam
+            cls = FusedAdam
+        self.optimizer = cls(groups, lr=0.0, eps=1e-15)
+        self._lr_args = dict(lr_init=a.position_lr_init * self.spatial_lr_scale, lr_final=a.position_lr_final * self.spatial_lr_scale,
+                             lr_delay_mult=a.position_lr_delay_mult, max_steps=a.position_lr_max_steps)
+
+    def update_learning_rate(self, iteration):
+        for group in self.optimizer.param_groups:
+            if group["name"] == "xyz":
+                group["lr"] = expon_lr(iteration, **self._lr_args)
+                return group["lr"]
+
+    def capture(self):
+        return (self.active_sh_degree, *(self._p[g] for g in ("xyz", "f_dc", "f_rest", "scaling", "rotation", "opacity")),
+                self.max_radii2D, self.xyz_gradient_accum, self.denom, self.optimizer.state_dict(), self.spatial_lr_scale)
+
+    def restore(self, model_args, training_args):
+        (self.active_sh_degree, self._p["xyz"], self._p["f_dc"], self._p["f_rest"], self._p["scaling"], self._p["rotation"],
+         self._p["opacity"], self.max_radii2D, accum, denom, opt_dict, self.spatial_lr_scale) = model_args
+        self.training_setup(training_args)
+        self.xyz_gradient_accum, self.denom = accum, denom
+        self.optimizer.load_state_dict(opt_dict)
+
+    # ---- restructuring: one row-index vector for everything
+    def _regather(self, index: Optional[torch.Tensor], append: Optional[Dict[str, torch.Tensor]] = None,
+                  zero_moments: Optional[str] = None, replace: Optional[Dict[str, torch.Tensor]] = None) -> None:
+        """new = cat(old[index] (all rows when index is None), append[name]) for every group's parameter and Adam moments
+        (appended rows get zero moments).  ``replace``: {name: tensor} swaps that group's values for a same-shaped tensor
+        and zeroes its moments (replace_tensor_to_optimizer)."""
+        for group in self.optimizer.param_groups:
+            name, old = group["name"], group["params"][0]
+            state = self.optimizer.state.pop(old, None)
+            if replace is not None:
+                if name not in replace:
+                    if state is not None:
+                        self.optimizer.state[old] = state
+                    continue
+                new = replace[name]
+                if state is not None:
+                    state["exp_avg"], state["exp_avg_sq"] = torch.zeros_like(new), torch.zeros_like(new)
+            else:
+                ext = None if append is None else append[name]
+                pick = (lambda t: t) if index is None else (lambda t: t.index_select(0, index))
+                grow = (lambda t, e: t) if ext is None else (lambda t, e: torch.cat((t, e), dim=0))
+                new = grow(pick(old.detach()), ext)
+                if state is not None:
+                    for k in ("exp_avg", "exp_avg_sq"):
+                        state[k] = grow(pick(state[k]), None if ext is None else torch.zeros_like(ext))
+            p = nn.Parameter(new.requires_grad_(True))
+            group["params"][0] = p
+            self._p[name] = p
+            if state is not None:
+                self.optimizer.state[p] = state
+
+    def replace_tensor_to_optimizer(self, tensor, name):
+        self._regather(None, replace={name: tensor})
+        return {name: self._p[name]}
+
+    def reset_opacity(self):
+        """:210-213: opacities capped at 0.01, their moments restarted."""
+        capped = inverse_sigmoid(torch.min(self.get_opacity, torch.ones_like(self.get_opacity) * 0.01))
+        self._regather(None, replace={"opacity": capped.detach()})
+
+    def prune_points(self, mask):
+        """Remove the rows where ``mask`` is True (:292-307)."""
+        keep = torch.nonzero(~mask, as_tuple=False).squeeze(1)            # ONE nonzero for all 18 tensors and 3 statistics
+        self._regather(keep)
+        self.xyz_gradient_accum = self.xyz_gradient_accum.index_select(0, keep)
+        self.denom = self.denom.index_select(0, keep)
+        self.max_radii2D = self.max_radii2D.index_select(0, keep)
+
+    def densification_postfix(self, new_xyz, new_features_dc, new_features_rest, new_opacities, new_scaling, new_rotation):
+        """Append rows; the accumulated statistics restart for ALL rows (:342-347)."""
+        self._regather(None, append={"xyz": new_xyz, "f_dc": new_features_dc, "f_rest": new_features_rest,
+                                     "opacity": new_opacities, "scaling": new_scaling, "rotation": new_rotation})
+        P, dev = self.get_xyz.shape[0], self.get_xyz.device
+        self.xyz_gradient_accum = torch.zeros((P, 1), device=dev)
+        self.denom = torch.zeros((P, 1), device=dev)
+        self.max_radii2D = torch.zeros(P, device=dev)
+
+    def _rows(self, idx):
+        return [self._p[g].detach().index_select(0, idx) for g in ("xyz", "f_dc", "f_rest", "opacity", "scaling", "rotation")]
+
+    def densify_and_clone(self, grads, grad_threshold, scene_extent):
+        """Small Gaussians with a large view-space gradient are duplicated in place (:377-392)."""
+        sel = (torch.norm(grads, dim=-1) >= grad_threshold) & (self.get_scaling.max(dim=1).values <= self.percent_dense * scene_extent)
+        self.densification_postfix(*self._rows(torch.nonzero(sel, as_tuple=False).squeeze(1)))
+
+    def densify_and_split(self, grads, grad_threshold, scene_extent, N=2):
+        """Large Gaussians with a large gradient are replaced by N samples of themselves, scaled down by 0.8 N (:349-375).
+        ``grads`` covers the rows that existed before the clone step; rows appended since count as zero."""
+        P, dev = self.get_xyz.shape[0], self.get_xyz.device
+        padded = torch.zeros(P, device=dev)
+        padded[:grads.shape[0]] = grads.squeeze()
+        sel = (padded >= grad_threshold) & (self.get_scaling.max(dim=1).values > self.percent_dense * scene_extent)
+        idx = torch.nonzero(sel, as_tuple=False).squeeze(1)
+        xyz, fdc, frest, opac, scal, rot = self._rows(idx)
+        stds = torch.exp(scal).repeat(N, 1)
+        samples = torch.normal(mean=torch.zeros((stds.size(0), 3), device=dev), std=stds)
+        R = quaternion_to_matrix(rot).repeat(N, 1, 1)
+        new_xyz = torch.bmm(R, samples.unsqueeze(-1)).squeeze(-1) + xyz.repeat(N, 1)
+        new_scaling = torch.log(torch.exp(scal).repeat(N, 1) / (0.8 * N))
+        self.densification_postfix(new_xyz, fdc.repeat(N, 1, 1), frest.repeat(N, 1, 1), opac.repeat(N, 1), new_scaling, rot.repeat(N, 1))
+        self.prune_points(torch.cat((sel, torch.zeros(N * idx.numel(), device=dev, dtype=torch.bool))))
+
+    def densify_and_prune(self, max_grad, min_opacity, extent, max_screen_size):
+        """:394-409.  (As in the reference, ``max_radii2D`` has just been restarted by the two steps above, so the
+        screen-size criterion never fires here; kept for identical results.)"""
+        grads = self.xyz_gradient_accum / self.denom
+        grads[grads.isnan()] = 0.0
+        self.densify_and_clone(grads, max_grad, extent)
+        self.densify_and_split(grads, max_grad, extent)
+        prune = (self.get_opacity < min_opacity).squeeze()
+        if max_screen_size:
+            prune = prune | (self.max_radii2D > max_screen_size) | (self.get_scaling.max(dim=1).values > 0.1 * extent)
+        self.prune_points(prune)
+
+    def add_densification_stats(self, viewspace_point_tensor, update_filter):
+        """:411-413: per visible Gaussian, the norm of the screen-space positional gradient and a visit count."""
+        g = viewspace_point_tensor.grad if viewspace_point_tensor.grad is not None else viewspace_point_tensor
+        self.xyz_gradient_accum[update_filter] += torch.norm(g[update_filter, :2], dim=-1, keepdim=True)
+        self.denom[update_filter] += 1

@@ -1,0 +1,105 @@
+"""model.GaussianModel (densify/prune bookkeeping, optimizer state surgery, schedules) against the reference's
+own class: tests/golden/model_ref.npz holds every tensor the reference's GaussianModel produced on CPU along one scripted
+sequence (tests/golden/model_script.py, made by make_model_golden.py); our class walks the same script with the same seeds.
+Row order, gathered values and Adam moments must be identical; computed values (exp/log/normal samples) to float rounding."""
+import os
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+sys.path.insert(0, GOLDEN)
+import model_script as ms  # noqa: E402
+
+
+@pytest.fixture(scope="module")
+def ours():
+    from gaussian_splatting_with_eye_tracking_b200 import model
+    gm = model.GaussianModel(3, optimizer_cls=torch.optim.Adam)          # CPU: the optimizer class has to be named
+    raw = ms.make_raw()
+    for g, attr in ms.GROUP_ATTR.items():
+        setattr(gm, attr, torch.nn.Parameter(raw[g].clone().requires_grad_(True)))
+    gm.max_radii2D = torch.zeros(raw["xyz"].shape[0])
+    gm.spatial_lr_scale = 1.3
+    return ms.run_sequence(gm, ms.namespace_args())
+
+
+def test_sequence_matches_the_reference_class(ours):
+    z = np.load(os.path.join(GOLDEN, "model_ref.npz"))
+    assert set(ours) == set(z.files)
+    assert int(ours["n_after_densify"]) == int(z["n_after_densify"]) == 652 and int(ours["sh_degree"]) == int(z["sh_degree"]) == 2
+    np.testing.assert_allclose(ours["lr_probe"], z["lr_probe"], rtol=1e-12)
+    np.testing.assert_allclose(ours["lr_groups"], z["lr_groups"], rtol=1e-12)
+    for k in z.files:
+        a, b = ours[k], z[k]
+        assert a.shape == b.shape, k
+        if k.startswith(("stats_",)) or k.endswith(("_accum", "_denom", "_radii")):
+            assert np.array_equal(a, b), k                               # pure bookkeeping: bit-identical
+        else:
+            np.testing.assert_allclose(a, b, rtol=2e-6, atol=1e-7, err_msg=k)
+    # the rows the densification only moved (everything but split children's xyz/scaling) are bit-identical
+    for name in ("f_dc", "f_rest", "opacity", "rotation"):
+        for suffix in ("", "_m", "_v"):
+            assert np.array_equal(ours[f"dens_{name}{suffix}"], z[f"dens_{name}{suffix}"]), (name, suffix)
+
+
+def test_clone_split_and_prune_all_fired(ours):
+    """The script must exercise every branch, or the comparison above proves little."""
+    P0 = ours["stats_xyz"].shape[0]
+    dens = ours["dens_xyz"]
+    assert dens.shape[0] != P0
+    m = ours["dens_xyz_m"]
+    zero_rows = int((np.abs(m).sum(axis=1) == 0).sum())                  # appended rows start with zero moments
+    assert 0 < zero_rows < dens.shape[0]
+    # reset_opacity caps the activated opacity at 0.01 and restarts its moments
+    assert float(1 / (1 + np.exp(-ours["reset_opacity"])).max()) <= 0.01 + 1e-6
+    assert not ours["reset_opacity_m"].any() and not ours["reset_opacity_v"].any()
+    assert ours["final_opacity_m"].any()
+
+
+def test_model_without_cuda_needs_a_named_optimizer():
+    from gaussian_splatting_with_eye_tracking_b200 import model
+    gm = model.GaussianModel(3)
+    raw = ms.make_raw(8)
+    for g, attr in ms.GROUP_ATTR.items():
+        setattr(gm, attr, torch.nn.Parameter(raw[g]))
+    with pytest.raises(RuntimeError, match="optimizer_cls"):
+        gm.training_setup(model.optimization_defaults())
+
+
+def test_schedule_ply_and_point_cloud_initialisation(tmp_path):
+    from gaussian_splatting_with_eye_tracking_b200 import model
+    a = model.optimization_defaults()
+    assert model.expon_lr(0, a.position_lr_init, a.position_lr_final, lr_delay_mult=0.01, max_steps=30_000) == pytest.approx(1.6e-4)
+    assert model.expon_lr(30_000, a.position_lr_init, a.position_lr_final, max_steps=30_000) == pytest.approx(1.6e-6)
+    assert model.expon_lr(-1, 1.0, 1.0) == 0.0 and model.expon_lr(5, 0.0, 0.0) == 0.0
+    # create_from_pcd (gaussian_model.py:122-146): SH dc from colours, isotropic log-scale from the 3-NN distance, identity rotation, opacity 0.1
+    g = torch.Generator().manual_seed(3)
+    pts, col = torch.rand(50, 3, generator=g), torch.rand(50, 3, generator=g)
+    gm = model.GaussianModel(3, optimizer_cls=torch.optim.Adam)
+    gm.create_from_pcd(type("PCD", (), {"points": pts.numpy(), "colors": col.numpy()})(), 2.5, device="cpu")
+    d = torch.cdist(pts, pts).pow(2)
+    want = d.sort(dim=1).values[:, 1:4].mean(dim=1).clamp_min(1e-7)
+    assert torch.allclose(gm.get_scaling, torch.sqrt(want)[:, None].expand(-1, 3), rtol=1e-5)
+    assert torch.allclose(gm.get_opacity, torch.full((50, 1), 0.1), atol=1e-6)
+    assert torch.allclose(gm.get_features[:, 0], (col - 0.5) / model.SH_C0) and not gm.get_features[:, 1:].any()
+    assert gm.get_features.shape == (50, 16, 3) and torch.equal(gm.get_rotation, torch.tensor([[1.0, 0, 0, 0]]).expand(50, 4))
+    # save / load round trip through the reference's PLY layout; capture / restore keep the optimizer state
+    gm.training_setup(a)
+    for grp in gm.optimizer.param_groups:
+        grp["params"][0].grad = torch.ones_like(grp["params"][0])
+    gm.optimizer.step()
+    path = str(tmp_path / "point_cloud" / "iteration_30000" / "point_cloud.ply")
+    gm.save_ply(path)
+    gm2 = model.GaussianModel(3, optimizer_cls=torch.optim.Adam)
+    gm2.load_ply(path, device="cpu")
+    assert gm2.active_sh_degree == 3
+    for attr in ms.GROUP_ATTR.values():
+        assert torch.equal(getattr(gm2, attr), getattr(gm, attr).detach()), attr
+    gm3 = model.GaussianModel(3, optimizer_cls=torch.optim.Adam)
+    gm3.restore(gm.capture(), a)
+    assert torch.equal(gm3.optimizer.state[gm3._xyz]["exp_avg"], gm.optimizer.state[gm._xyz]["exp_avg"])
+    assert gm3.spatial_lr_scale == 2.5 and torch.equal(gm3.get_xyz, gm.get_xyz)
