@@ -11,9 +11,12 @@ SURVEY 8(d)), cycling through 8 cameras on a ring.  Rank 0 prints ONE JSON line:
   e2e        the same through the public Python API (GaussianRasterizer module) with the per-step inputs (camera
              matrices) copied from pinned host memory and the rendered frame copied back to pinned host memory
   roofline   preprocess_fwd_kernel (dominant HBM-bound kernel): algorithmic bytes per launch / CUDA-event time
-  cpu_baseline  the CPU oracle port rendering one frame of the same workload on all host cores
+  cpu_baseline  the CPU oracle port rendering frames of the same workload on all host cores (bounded sample, ~12 s)
   extra      fwd+bwd ms/view, AMR single-pass / 5-step / gaze-foveated FPS, per-stage device times, the reference
-             CUDA rasterizer timed in the same run, DP training-step throughput (NCCL all-reduce when N > 1)
+             CUDA rasterizer timed in the same run; train_step (N = 1): render + fused L1/SSIM loss + backward + FusedAdam
+             next to the reference chain; dp_train / dp_train_rank1_sh / dp_train_full_step: the view-parallel training
+             step with its gradient exchange (NCCL all-reduce, rank-1 SH rows, peer-memory sum); tile_bands: one foveated
+             frame split over the ranks
 
 --impl reference runs the UNMODIFIED reference CUDA rasterizer (oracle/_ref, rebuilt for sm_100a from
 /root/reference sources) on the same config with the same protocol; --impl reference-cpu times the CPU oracle.
