@@ -1,7 +1,9 @@
 """ctypes binding of include/gsr_b200.h.
 
 This module is the only place that touches the shared library.  It fails loudly: if libgsr_b200.so is missing and
-cannot be built, importing it raises -- there is no CPU or PyTorch fallback anywhere in the product path.
+cannot be built, the first call into it raises -- there is no CPU or PyTorch fallback anywhere in the product path.
+(The library is mapped on first use, not at import, so that a process which never calls the product -- bench.py's
+reference arm -- does not carry it.)
 """
 from __future__ import annotations
 
@@ -142,8 +144,28 @@ def _load() -> C.CDLL:
     return lib
 
 
-lib = _load()
+class _LazyLib:
+    """The shared library, dlopen'ed on FIRST USE rather than at import: a process that only imports the package for
+    its host-side helpers (scenes.py in bench.py's reference arm) never maps libgsr_b200.so.  The first attribute access
+    loads (or builds) the library and raises if that is impossible -- there is still no fallback of any kind."""
+    _real = None
+
+    def _get(self) -> C.CDLL:
+        if _LazyLib._real is None:
+            _LazyLib._real = _load()
+        return _LazyLib._real
+
+    def __getattr__(self, name):
+        return getattr(self._get(), name)
+
+
+lib = _LazyLib()
 LIB_PATH = _build.LIB_PATH
+
+
+def loaded() -> bool:
+    """True once libgsr_b200.so has been mapped into this process."""
+    return _LazyLib._real is not None
 
 
 class GsrError(RuntimeError):

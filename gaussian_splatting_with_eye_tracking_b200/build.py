@@ -40,16 +40,35 @@ def is_stale() -> bool:
 
 
 def build(force: bool = False, verbose: bool = False) -> str:
-    """Compile csrc/*.cu into libgsr_b200.so (no-op when up to date).  Returns the library path."""
+    """Compile csrc/*.cu into libgsr_b200.so (no-op when up to date).  Returns the library path.
+
+    Safe under torchrun: an exclusive file lock serialises the ranks (the first one in builds, the others find the
+    library fresh when they get the lock), and every build writes to its own temporary file before the atomic rename."""
     if not force and not is_stale():
         return LIB_PATH
-    cmd = [find_nvcc(), *NVCC_FLAGS, "-o", LIB_PATH + ".tmp", *[os.path.join(CSRC, f) for f in SOURCES]]
-    if verbose:
-        print(" ".join(cmd), file=sys.stderr)
-    res = subprocess.run(cmd, capture_output=True, text=True)
-    if res.returncode != 0:
-        raise RuntimeError("nvcc failed:\n" + res.stdout + res.stderr)
-    os.replace(LIB_PATH + ".tmp", LIB_PATH)
+    import fcntl
+    import tempfile
+    with open(LIB_PATH + ".lock", "w") as lock:
+        fcntl.flock(lock, fcntl.LOCK_EX)
+        try:
+            if not force and not is_stale():        # another process built it while we waited
+                return LIB_PATH
+            fd, tmp = tempfile.mkstemp(prefix="libgsr_b200.", suffix=".so.tmp", dir=PKG_DIR)
+            os.close(fd)
+            cmd = [find_nvcc(), *NVCC_FLAGS, "-o", tmp, *[os.path.join(CSRC, f) for f in SOURCES]]
+            if verbose:
+                print(" ".join(cmd), file=sys.stderr)
+            res = subprocess.run(cmd, capture_output=True, text=True)
+            if res.returncode != 0:
+                try:
+                    os.unlink(tmp)
+                except OSError:
+                    pass
+                raise RuntimeError("nvcc failed:\n" + res.stdout + res.stderr)
+            os.chmod(tmp, 0o755)
+            os.replace(tmp, LIB_PATH)
+        finally:
+            fcntl.flock(lock, fcntl.LOCK_UN)
     return LIB_PATH
 
 
