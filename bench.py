@@ -266,45 +266,82 @@ class Ours:
 
 
 class Ref:
+    """The UNMODIFIED reference, through its STOCK Python packages and torch binding: baseline/_ref/diff_gaussian_rasterization
+    (built by the reference's own setup.py, see baseline/build_ref.py).  forward_c = `_C.rasterize_gaussians` (the call
+    /root/reference/submodules/diff-gaussian-rasterization/diff_gaussian_rasterization/__init__.py:92 makes), forward_api =
+    `GaussianRasterizer(...)(...)`, fwd_bwd = autograd through `_RasterizeGaussians`.  The AMR fork is driven through its
+    stock binding too where the device can dereference pageable host memory (its setAMRLevelsKernel is handed a host stack
+    array); elsewhere the same unmodified kernels run through oracle/_ref's shim, which registers that stack."""
     name = "reference"
 
-    def __init__(self, d):
-        from oracle import ref_cuda
+    def __init__(self, d, alias):
+        from baseline import ref_loader
         self.d = d
-        self.r = ref_cuda.RefRasterizer(False)
-        self.ra = ref_cuda.RefRasterizer(True) if ref_cuda.available(True) else None
+        self.dgr = ref_loader.load("diff_gaussian_rasterization", alias=alias)
+        self.C = self.dgr._C
         self.e = torch.empty(0, device=d["means3D"].device)
+        self.amr_via, self.dgra, self.shim = None, None, None
+        dev_index = d["means3D"].device.index or 0
+        if ref_loader.available("diff_gaussian_rasterization_amr") and ref_loader.pageable_memory_access(dev_index):
+            self.dgra = ref_loader.load("diff_gaussian_rasterization_amr", alias=alias)
+            self.amr_via = "stock binding (baseline/_ref/diff_gaussian_rasterization_amr)"
+        else:
+            try:
+                from oracle import ref_cuda
+                if ref_cuda.available(True):
+                    self.shim = ref_cuda.RefRasterizer(True)
+                    self.amr_via = ("oracle/_ref shim around the unmodified AMR kernels (the stock binding would fault here: "
+                                    "host stack array passed to setAMRLevelsKernel, no pageable-memory access on this device)")
+            except Exception:
+                self.shim = None
 
     def _args(self, cam, view=None, proj=None, campos=None):
         d = self.d
         return (d["bg"], d["means3D"], self.e, d["opacities"], d["scales"], d["rotations"], 1.0, self.e,
                 view if view is not None else cam.world_view_transform, proj if proj is not None else cam.full_proj_transform,
                 cam.tanfovx, cam.tanfovy, cam.image_height, cam.image_width, d["shs"], d["sh_degree"],
-                campos if campos is not None else cam.camera_center)
+                campos if campos is not None else cam.camera_center, False)
 
     def forward_c(self, cam):
-        return self.r.forward(*self._args(cam))
+        return self.C.rasterize_gaussians(*self._args(cam), False)
+
+    def _settings(self, mod, cam, view=None, proj=None, campos=None):
+        d = self.d
+        return mod.GaussianRasterizationSettings(cam.image_height, cam.image_width, cam.tanfovx, cam.tanfovy, d["bg"], 1.0,
+                                                 view if view is not None else cam.world_view_transform,
+                                                 proj if proj is not None else cam.full_proj_transform, d["sh_degree"],
+                                                 campos if campos is not None else cam.camera_center, False, False)
 
     def forward_api(self, cam, view, proj, campos):
-        return self.r.forward(*self._args(cam, view, proj, campos))[1]
+        d = self.d
+        with torch.no_grad():
+            img, _ = self.dgr.GaussianRasterizer(self._settings(self.dgr, cam, view, proj, campos))(
+                means3D=d["means3D"], means2D=torch.zeros_like(d["means3D"]), opacities=d["opacities"], shs=d["shs"],
+                scales=d["scales"], rotations=d["rotations"])
+        return img
 
     def make_leaves(self):
-        pass
+        d = self.d
+        self.leaves = [d[k].detach().clone().requires_grad_(True) for k in ("means3D", "shs", "opacities", "scales", "rotations")]
+        self.m2d = torch.zeros_like(self.leaves[0], requires_grad=True)
 
     def fwd_bwd(self, cam, w):
-        d = self.d
-        N, img, radii, gb, bb, ib = self.r.forward(*self._args(cam))
+        m3, sh, op, sc, ro = self.leaves
+        for t in self.leaves + [self.m2d]:
+            t.grad = None
+        img, _ = self.dgr.GaussianRasterizer(self._settings(self.dgr, cam))(means3D=m3, means2D=self.m2d, opacities=op, shs=sh,
+                                                                           scales=sc, rotations=ro)
         loss = (img * w).sum()
-        g = self.r.backward(d["bg"], d["means3D"], radii, self.e, d["scales"], d["rotations"], 1.0, self.e, cam.world_view_transform,
-                            cam.full_proj_transform, cam.tanfovx, cam.tanfovy, w, d["shs"], d["sh_degree"], cam.camera_center,
-                            gb, N, bb, ib)
-        return loss, [g[k] for k in ("dL_dmeans3D", "dL_dsh", "dL_dopacity", "dL_dscales", "dL_drotations")]
+        loss.backward()
+        return loss, [t.grad for t in self.leaves]
 
     def amr(self, cam, step, precomp, gb, bb, ib, interp, gaze=None):
-        if self.ra is None or gaze is not None:
+        if gaze is not None or self.amr_via is None:
             raise RuntimeError("not available in the reference")
+        if self.dgra is not None:
+            return self.dgra._C.rasterize_gaussians(*self._args(cam), step, precomp, gb, bb, ib, interp, False)
         g = lambda t: None if (t is None or t.numel() == 0) else t  # noqa: E731
-        return self.ra.forward(*self._args(cam), False, step, precomp, g(gb), g(bb), g(ib), interp)
+        return self.shim.forward(*self._args(cam)[:17], False, step, precomp, g(gb), g(bb), g(ib), interp)
 
     def launches(self):
         return 0
@@ -452,17 +489,18 @@ def measure(impl, args, d, cams, rank, world, timer, full):
     # "dense": bucketed NCCL all-reduce of all 59 floats/Gaussian (dist.GradientAllReduce).  "rank1_sh" (ours only): the
     # SH gradient travels as its rank-1 factor -- 11 floats all-reduced + 3 floats x world gathered -- and is rebuilt
     # by gsr_sh_grad_from_views (dist.ShGradExchange); the backward then never writes the [P,16,3] tensor.
-    from gaussian_splatting_with_eye_tracking_b200 import dist as gdist
-    reducer = gdist.GradientAllReduce()
-
-    def dp_step(i):
-        _, grads = impl.fwd_bwd(cam_of(i), w)
-        reducer.start(grads)
-        reducer.wait()
-    ms = timer.run(dp_step, Kb, 2)
     P_ = d["means3D"].shape[0]
-    out["dp_train"] = {"ms_per_step": ms / Kb, "views_per_s": world * Kb / (ms / 1e3),
-                       "allreduce_bytes_per_step": 59 * 4 * P_ if world > 1 else 0, "bucket_bytes": reducer.bucket_bytes, "exchange": "dense"}
+    if is_ours:
+        from gaussian_splatting_with_eye_tracking_b200 import dist as gdist
+        reducer = gdist.GradientAllReduce()
+
+        def dp_step(i):
+            _, grads = impl.fwd_bwd(cam_of(i), w)
+            reducer.start(grads)
+            reducer.wait()
+        ms = timer.run(dp_step, Kb, 2)
+        out["dp_train"] = {"ms_per_step": ms / Kb, "views_per_s": world * Kb / (ms / 1e3),
+                           "allreduce_bytes_per_step": 59 * 4 * P_ if world > 1 else 0, "bucket_bytes": reducer.bucket_bytes, "exchange": "dense"}
     if is_ours:
         e_ = impl.e
         M_ = d["shs"].shape[1]
@@ -731,14 +769,15 @@ def train_step_bench(impl, ref_impl, d, cams, args, timer_iters=12):
             cam = cams[i % len(cams)]
             a = (d["bg"], rl["means3D"].data, e, rl["opacities"].data, rl["scales"].data, rl["rotations"].data, 1.0, e, cam.world_view_transform,
                  cam.full_proj_transform, cam.tanfovx, cam.tanfovy, cam.image_height, cam.image_width, rl["shs"].data, d["sh_degree"], cam.camera_center)
-            N, img, radii, gb, bb, ib = ref_impl.r.forward(*a)
+            N, img, radii, gb, bb, ib = ref_impl.C.rasterize_gaussians(*a, False, False)
             x = img.detach().requires_grad_(True)
             train_surround.torch_loss(x, gts[i % 2], 0.2, win).backward()
-            gr = ref_impl.r.backward(d["bg"], rl["means3D"].data, radii, e, rl["scales"].data, rl["rotations"].data, 1.0, e, cam.world_view_transform,
-                                     cam.full_proj_transform, cam.tanfovx, cam.tanfovy, x.grad, rl["shs"].data, d["sh_degree"], cam.camera_center,
-                                     gb, N, bb, ib)
-            for k, gk in zip(keys, ("dL_dmeans3D", "dL_dsh", "dL_dopacity", "dL_dscales", "dL_drotations")):
-                rl[k].grad = gr[gk].view_as(rl[k])
+            gr = ref_impl.C.rasterize_gaussians_backward(d["bg"], rl["means3D"].data, radii, e, rl["scales"].data, rl["rotations"].data, 1.0, e,
+                                                         cam.world_view_transform, cam.full_proj_transform, cam.tanfovx, cam.tanfovy, x.grad,
+                                                         rl["shs"].data, d["sh_degree"], cam.camera_center, gb, N, bb, ib, False)
+            # (dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations)
+            for k, gk in zip(keys, (gr[3], gr[5], gr[2], gr[6], gr[7])):
+                rl[k].grad = gk.view_as(rl[k])
             ropt.step()
             ropt.zero_grad(set_to_none=True)
         out["reference_ms_per_iteration"] = timed(ref)
@@ -775,14 +814,26 @@ def main():
 
     torch.cuda.set_device(local_rank)
     import torch.distributed as dist
-    if args.impl == "reference" and world > 1 and rank != 0:
-        return                                            # reference arm: rank 0 alone runs and prints
-    if world > 1 and args.impl == "ours":
+    if world > 1:
+        # one process per GPU for BOTH arms: ours exchanges gradients over NCCL in the training legs; the reference arm runs N
+        # independent replicas (the reference has no multi-GPU path, hence no collective) and uses the group only for the
+        # barrier and the max-over-ranks of the timings.  NCCL's INFO log goes to a per-rank file so that the communicator
+        # size is checkable while stdout stays the one JSON line.
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        os.environ["NCCL_DEBUG"] = os.environ.get("GSR_NCCL_DEBUG", "WARN")     # keep stdout to the one JSON line (NCCL prints its version there)
-        from gaussian_splatting_with_eye_tracking_b200 import dist as gdist_
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank), pg_options=gdist_.nccl_options())
-    eff_world = world if args.impl == "ours" else 1
+        os.environ.setdefault("NCCL_DEBUG", os.environ.get("GSR_NCCL_DEBUG", "INFO"))
+        os.environ.setdefault("NCCL_DEBUG_SUBSYS", "INIT")
+        log_dir = os.path.join(ROOT, "gpurun_out")
+        try:
+            os.makedirs(log_dir, exist_ok=True)
+            os.environ.setdefault("NCCL_DEBUG_FILE", os.path.join(log_dir, f"nccl_{args.impl}_n{world}_rank%h_%p.log"))
+        except OSError:
+            pass
+        if args.impl == "ours":
+            from gaussian_splatting_with_eye_tracking_b200 import dist as gdist_
+            dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank), pg_options=gdist_.nccl_options())
+        else:
+            dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    eff_world = world
 
     sampler = ClockSampler(local_rank)
     windows = []
@@ -801,17 +852,23 @@ def main():
                        "parallelism": f"dp{eff_world} (views per rank, scene replicated)"}}
 
     if args.impl == "reference":
-        from oracle import ref_cuda
-        if not ref_cuda.available(False):
-            emit({"impl": "reference", "unavailable": "oracle/_ref/libref_raster.so missing (build with make -C oracle ref)"})
+        from baseline import ref_loader
+        if not ref_loader.available("diff_gaussian_rasterization"):
+            if rank == 0:
+                emit({"impl": "reference", "unavailable": "baseline/_ref/diff_gaussian_rasterization missing (python baseline/build_ref.py, where /root/reference exists)"})
             return
-        impl = Ref(d)
-        m = measure(impl, args, d, cams, 0, 1, timer, full)
+        impl = Ref(d, alias=False)
+        m = measure(impl, args, d, cams, rank, eff_world, timer, full and eff_world == 1)
         line.update(impl="reference", value=m["value"], ms_per_step=m["ms_per_step"], e2e=m["e2e"], gpu_launches=0)
+        line["config"]["parallelism"] = f"{eff_world} independent replica(s), one view per rank and step, no collective (the reference has no multi-GPU path)"
         line["cpu_baseline"] = {"value": m["value"], "unit": "frames/s", "cores": 0, "kind": "reference",
-                                "sample": "UNMODIFIED reference CUDA rasterizer (oracle/_ref, sm_100a rebuild) on the GPU -- the reference "
+                                "sample": "UNMODIFIED reference CUDA rasterizer through its stock torch binding and Python package "
+                                          "(baseline/_ref, built by the reference's own setup.py for sm_100a) on the GPU -- the reference "
                                           "has no CPU rasterizer; see --impl reference-cpu for the CPU oracle port"}
-        line["extra"] = {k: m[k] for k in ("num_rendered", "fwd_bwd_ms_per_view", "dp_train", "amr") if k in m}
+        line["extra"] = {k: m[k] for k in ("num_rendered", "fwd_bwd_ms_per_view", "amr", "c2", "sustained") if k in m}
+        line["extra"]["amr_via"] = impl.amr_via
+        line["extra"]["python_package"] = os.path.relpath(impl.dgr.__file__, ROOT)
+        line["extra"]["libgsr_b200_mapped"] = any("libgsr_b200" in ln for ln in open("/proc/self/maps"))
     else:
         impl = Ours(d)
         m = measure(impl, args, d, cams, rank, eff_world, timer, full)
@@ -831,20 +888,21 @@ def main():
         extra["pairs_per_gaussian_mean"] = N / args.gaussians
         extra["visible_mean"] = m.get("mean_visible")
         if full and rank == 0 and eff_world == 1 and not os.environ.get("GSR_BENCH_SKIP_REF"):
-            from oracle import ref_cuda
-            if ref_cuda.available(False):
+            from baseline import ref_loader
+            ref_ok = ref_loader.available("diff_gaussian_rasterization")
+            if ref_ok:
                 a2 = argparse.Namespace(**vars(args)); a2.steps = max(5, args.steps // 4); a2.warmup = 3
                 try:
-                    r = measure(Ref(d), a2, d, cams, 0, 1, timer, True)
+                    r = measure(Ref(d, alias=True), a2, d, cams, 0, 1, timer, True)
                     extra["reference_cuda_same_run"] = {"fps": r["value"], "e2e_fps": r["e2e"]["value"],
                                                         "fwd_bwd_ms_per_view": r.get("fwd_bwd_ms_per_view"), "amr": r.get("amr"),
-                                                        "what": "unmodified reference kernels rebuilt for sm_100a (oracle/_ref)"}
+                                                        "what": "unmodified reference through its stock torch binding (baseline/_ref), same process"}
                     extra["speedup_vs_reference_cuda"] = {"fwd_fps": m["value"] / r["value"], "e2e_fps": m["e2e"]["value"] / r["e2e"]["value"],
                                                           "fwd_bwd": r["fwd_bwd_ms_per_view"] / m["fwd_bwd_ms_per_view"]}
                 except Exception as ex:     # reported, never fatal for our own line
                     extra["reference_cuda_same_run"] = {"error": str(ex)[:300]}
             try:
-                extra["train_step"] = train_step_bench(impl, Ref(d) if ref_cuda.available(False) else None, d, cams, args)
+                extra["train_step"] = train_step_bench(impl, Ref(d, alias=True) if ref_ok else None, d, cams, args)
             except Exception as ex:
                 extra["train_step"] = {"error": str(ex)[:300]}
             if not args.no_cpu_baseline:

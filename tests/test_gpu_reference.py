@@ -80,15 +80,24 @@ def _ref_amr(sc, cam, stepped, interpolate):
     return out
 
 
+def _ref_amr_or_optout(sc, cam, stepped, interpolate):
+    """The AMR pin must not vanish silently: when oracle/_ref/libref_raster_amr.so exists but cannot run, the test FAILS
+    unless GSR_ALLOW_AMR_REF_SKIP=1 says the box is known not to address registered host memory."""
+    import os
+    try:
+        return _ref_amr(sc, cam, stepped, interpolate)
+    except RuntimeError as ex:
+        if os.environ.get("GSR_ALLOW_AMR_REF_SKIP") == "1":
+            pytest.skip(str(ex))
+        raise
+
+
 @needs_ref_amr
 @pytest.mark.parametrize("case", ["small", "ragged", "dense"])
 @pytest.mark.parametrize("stepped", [False, True])
 def test_amr_vs_reference_cuda(case, stepped, cuda_device):
     sc, cam = common.make_case(case)
-    try:
-        ref = _ref_amr(sc, cam, stepped, False)
-    except RuntimeError as ex:      # device cannot address registered host memory: the unmodified fork cannot run here
-        pytest.skip(str(ex))
+    ref = _ref_amr_or_optout(sc, cam, stepped, False)
     ours = common.run_ours_amr(sc, cam, stepped, False)
     common.assert_ints_equal(ours["radii"], ref["radii"], "radii")
     assert ours["N"] == ref["N"]
@@ -107,10 +116,76 @@ def test_amr_vs_reference_cuda(case, stepped, cuda_device):
 @needs_ref_amr
 def test_amr_interpolated_vs_reference_cuda(cuda_device):
     sc, cam = common.make_case("small")
-    try:
-        ref = _ref_amr(sc, cam, False, True)
-    except RuntimeError as ex:
-        pytest.skip(str(ex))
+    ref = _ref_amr_or_optout(sc, cam, False, True)
     ours = common.run_ours_amr(sc, cam, False, True)
     dmax = np.abs(A(ours["out_color"]) - A(ref["out_color"])).max()
     assert dmax <= common.IMG_TOL, f"interpolated AMR image max-abs {dmax}"
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# BASELINE.json sizes against the LIVE reference (not invariants): C2 = 100 k Gaussians, 800x800, forward + backward;
+# C3 = 3 M Gaussians, 1920x1080, forward on two ring cameras + backward on one; AMR levels / lists at C3.
+# This is where the exact-preserving tile cull of the blend kernels (cannot_touch / reject_below, gsr_blend.cu) decides
+# ~30 M pairs per frame: a flipped n_contrib or a single differing pixel bit fails here.
+# Reference code matched: cuda_rasterizer/forward.cu:261-374 (blend), rasterizer_impl.cu:198-336 (lists), backward.cu.
+# ---------------------------------------------------------------------------------------------------------------
+def _full_scene(name, cam_index):
+    from gaussian_splatting_with_eye_tracking_b200 import scenes
+    if name == "C2":
+        return scenes.make_object_scene(P=100_000), scenes.object_cameras(8, 800, 800)[cam_index]
+    if name == "C3":
+        return scenes.make_unbounded_scene(P=3_000_000, seed=2002), scenes.unbounded_cameras(8, 1920, 1080)[cam_index]
+    raise KeyError(name)
+
+
+def _assert_forward_identical(ours, ref, sc):
+    vis = A(ref["radii"]) > 0
+    common.assert_ints_equal(ours["radii"], ref["radii"], "radii")
+    assert ours["N"] == ref["N"]
+    common.assert_ints_equal(ours["tiles_touched"], ref["tiles_touched"], "tiles_touched")
+    common.assert_bits_equal(ours["depths"], ref["depths"], "depths", vis)
+    common.assert_bits_equal(ours["means2D"], ref["means2D"], "means2D", vis)
+    common.assert_bits_equal(ours["conic_opacity"], ref["conic_opacity"], "conic_opacity", vis)
+    common.assert_bits_equal(ours["rgb"], ref["rgb"], "rgb", vis)
+    assert torch.equal(ours["point_list"].view(torch.int32), ref["point_list"].view(torch.int32)), "sorted Gaussian indices differ"
+    assert torch.equal(ours["keys"].view(torch.int64), ref["keys"].view(torch.int64)), "sorted (tile, depth) keys differ"
+    common.assert_ints_equal(ours["ranges"], ref["ranges"], "tile ranges")
+    common.assert_ints_equal(ours["n_contrib"], ref["n_contrib"], "n_contrib")
+    common.assert_bits_equal(ours["accum_alpha"], ref["accum_alpha"], "final_T (bitwise)")
+    common.assert_bits_equal(ours["out_color"], ref["out_color"], "image (bitwise)")
+
+
+@needs_ref
+@pytest.mark.parametrize("name,cam_index", [("C2", 1), ("C2", 6), ("C3", 2), ("C3", 5)])
+def test_full_size_forward_vs_reference_cuda(name, cam_index, cuda_device):
+    sc, cam = _full_scene(name, cam_index)
+    ours = common.run_ours(sc, cam)
+    ref = common.run_reference(sc, cam)
+    _assert_forward_identical(ours, ref, sc)
+
+
+@needs_ref
+@pytest.mark.parametrize("name,cam_index", [("C2", 1), ("C3", 2)])
+def test_full_size_backward_vs_reference_cuda(name, cam_index, cuda_device):
+    sc, cam = _full_scene(name, cam_index)
+    dpix = common.upstream_gradient(cam)
+    ours = common.run_ours(sc, cam, dpix)["grads"]
+    ours = {k: v.clone() for k, v in ours.items()}
+    torch.cuda.empty_cache()
+    ref = common.run_reference(sc, cam, dpix)["grads"]
+    common.assert_grads_close(ours, ref, floor_factor=common.GRAD_FLOOR_REF)
+
+
+@needs_ref_amr
+def test_full_size_amr_vs_reference_cuda(cuda_device):
+    sc, cam = _full_scene("C3", 2)
+    ref = _ref_amr_or_optout(sc, cam, False, False)
+    ours = common.run_ours_amr(sc, cam, False, False)
+    assert ours["N"] == ref["N"]
+    assert torch.equal(ours["point_list"].view(torch.int32), ref["point_list"].view(torch.int32)), "AMR sorted indices differ"
+    common.assert_ints_equal(ours["ranges"], ref["ranges"], "ranges")
+    common.assert_ints_equal(ours["n_intersections"], ref["n_intersections"], "n_intersections")
+    common.assert_ints_equal(ours["levels"], ref["levels"], "AMR tile levels")
+    dmax = np.abs(A(ours["out_color"]) - A(ref["out_color"])).max()
+    assert dmax <= common.IMG_TOL, f"AMR single-pass image at C3: max-abs {dmax}"
+    common.assert_bits_equal(ours["out_color"], ref["out_color"], "AMR image (bitwise)")
