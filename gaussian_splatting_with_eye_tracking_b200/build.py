@@ -12,7 +12,7 @@ import sys
 PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(PKG_DIR, "csrc")
 LIB_PATH = os.path.join(PKG_DIR, "libgsr_b200.so")
-SOURCES = ["gsr_api.cu", "gsr_preprocess.cu", "gsr_binning.cu", "gsr_blend.cu", "gsr_train.cu", "gsr_peer.cu"]
+SOURCES = ["gsr_api.cu", "gsr_preprocess.cu", "gsr_binning.cu", "gsr_depthsort.cu", "gsr_blend.cu", "gsr_train.cu", "gsr_peer.cu"]
 HEADERS = ["gsr_common.cuh", "gsr_math.cuh", os.path.join("..", "..", "include", "gsr_b200.h")]
 
 NVCC_FLAGS = [

@@ -67,7 +67,10 @@ static uint32_t* pinned_mailbox(uint32_t** dev_alias = nullptr) {
     static thread_local uint32_t* box_dev = nullptr;
     if (!box) {
         if (cudaHostAlloc((void**)&box, 64, cudaHostAllocMapped) != cudaSuccess) { box = nullptr; cudaGetLastError(); }
-        else if (cudaHostGetDevicePointer((void**)&box_dev, box, 0) != cudaSuccess) { box_dev = nullptr; cudaGetLastError(); }
+        else {
+            memset(box, 0, 64);
+            if (cudaHostGetDevicePointer((void**)&box_dev, box, 0) != cudaSuccess) { box_dev = nullptr; cudaGetLastError(); }
+        }
     }
     if (dev_alias) *dev_alias = box_dev;
     return box;
@@ -93,6 +96,23 @@ static int read_u32(const uint32_t* dev, uint32_t* host, int count, cudaStream_t
 // that same buffer, which is the only way the reference's Python ever calls them (gaussian_renderer_amr/__init__.py).
 struct LastBuild { const void* geom; int P; int N; long long R; long long V; };
 static thread_local LastBuild g_last_build = {nullptr, 0, 0, 0, 0};
+static int g_force_sort_fallback = 0;      // GSR_OPT_FORCE_SORT_FALLBACK: run the onesweep depth sort even when the buckets fit (tests)
+
+// The radix-sort watchdog (a look-back that never saw its predecessor) cannot stop a frame that is already queued; the
+// last binning kernel posts the flag to the mailbox and the NEXT call of this host thread into the library -- the
+// backward of the same frame, the next forward, gsr_last_counts -- returns GSR_ERR_SORT instead of working on lists that
+// may be corrupt.  With debug != 0 the forward itself reports it.
+static int check_sort_mailbox(const char* where) {
+    uint32_t* box = pinned_mailbox();
+    if (!box) return GSR_OK;
+    const uint32_t w = ((volatile uint32_t*)box)[8];
+    if ((w & 0x80000001u) == 0x80000001u) {
+        box[8] = 0;
+        set_error("%s: the radix-sort watchdog fired in the previous frame of this thread (tile lists may be corrupt)", where);
+        return GSR_ERR_SORT;
+    }
+    return GSR_OK;
+}
 
 static int geom_header(const void* geom, const GeomHeader* header, int P, int* N, cudaStream_t s) {
     if (geom == g_last_build.geom && P == g_last_build.P) { *N = g_last_build.N; return GSR_OK; }
@@ -136,6 +156,7 @@ static int build_lists(const gsr_scene* sc, const gsr_camera* cam, int mode, gsr
     const int P = sc->P, W = cam->width, H = cam->height;
     const size_t gbytes = gsr_geom_bytes(P), ibytes = gsr_image_bytes(W, H, mode);
     g_last_build = {nullptr, 0, 0, 0, 0};
+    { int rc0 = check_sort_mailbox("forward"); if (rc0) return rc0; }
     void* geom = alloc(user, GSR_BUF_GEOM, gbytes);
     void* img = alloc(user, GSR_BUF_IMAGE, ibytes);
     if (!geom || !img) { set_error("allocation callback returned NULL"); return GSR_ERR_ALLOC; }
@@ -145,11 +166,13 @@ static int build_lists(const gsr_scene* sc, const gsr_camera* cam, int mode, gsr
     if (cam->band_row1 > im.tiles_y) { set_error("tile band [%d,%d) exceeds the %d tile rows", cam->band_row0, cam->band_row1, im.tiles_y); return GSR_ERR_INVALID; }
     if (im.tiles_x > kRunFieldMask || im.tiles_y > kRunMaxRows) { set_error("image of %dx%d tiles exceeds the %dx%d tile grid limit", im.tiles_x, im.tiles_y, kRunFieldMask, kRunMaxRows); return GSR_ERR_INVALID; }
     int rc = GSR_OK;
-    // No memset operation in the frame: block_scan_kernel rewrites the whole header, and the preprocess kernel clears
-    // the depth sort's histograms / tile counters / look-back words (one region per pass) on the side.
-    const SortPlan dplan = make_sort_plan(32);
-    if (dplan.passes & 1) { set_error("depth sort plan must have an even pass count"); return GSR_ERR_INVALID; }
-    const size_t dzero = sort_prezero_bytes(P, dplan, g.sort_temp_bytes, false);
+    // One 256-byte memset node per frame: the header's counters are accumulated with atomics by the preprocess and sort
+    // kernels.  Everything else the frame needs cleared (bin histogram, bucket cursors) is cleared on the side by the
+    // preprocess kernel.
+    if ((rc = check_cuda(cudaMemsetAsync(g.header, 0, sizeof(GeomHeader), s), "memset header"))) return rc;
+    uint32_t* box_dev = nullptr;
+    uint32_t* box = pinned_mailbox(&box_dev);
+    if (box) { box[0] = 0; box[6] = 0; }
 
     PreprocessArgs a;
     a.P = P; a.D = sc->sh_degree; a.M = sc->sh_coeffs;
@@ -164,35 +187,31 @@ static int build_lists(const gsr_scene* sc, const gsr_camera* cam, int mode, gsr
     a.radii = radii_user ? radii_user : g.radii;
     a.prefiltered = cam->prefiltered != 0;
     a.band_row0 = cam->band_row0; a.band_row1 = cam->band_row1;
-    a.zero_ptr = dzero ? (void*)sort_hist_ptr(g.sort_temp) : nullptr; a.zero_bytes = dzero;
+    a.zero_ptr = nullptr; a.zero_bytes = 0; a.mailbox = box_dev;
     { ProfScope ps(GSR_PROF_PREPROCESS, s); launch_preprocess(a, g, s); }
     if ((rc = check_last("preprocess", debug, s))) return rc;
-    uint32_t* box_dev = nullptr;
-    uint32_t* box = pinned_mailbox(&box_dev);
-    { ProfScope ps(GSR_PROF_SCAN, s); launch_block_scan(g, P, box_dev, s); }
-    if ((rc = check_last("block scan", debug, s))) return rc;
+    // histogram of the depth keys + bucket plan (replaces the scan kernel's slot in the profile)
+    { ProfScope ps(GSR_PROF_SCAN, s); launch_bucket_hist(g, P, box_dev, s); }
+    if ((rc = check_last("bucket histogram", debug, s))) return rc;
 
     // The one host round-trip of the forward (reference: rasterizer_impl.cu:281): the binning buffer is sized by N.
-    // The scan kernel stores the totals straight into mapped host memory and the host waits on an event recorded
-    // BEFORE the depth sort, so the host allocates the binning buffer while the GPU is already sorting by depth.
+    // The last CTAs of the two kernels above store the totals straight into mapped host memory and the host waits on an
+    // event recorded BEFORE the depth sort, so the host allocates the binning buffer while the GPU is already sorting.
     // No cudaMemcpy: a D2H copy, however small, queues behind whatever the application has in flight on the copy
     // engine (a 25 MB frame read-back delayed this read by up to 0.45 ms).
-    static thread_local cudaEvent_t ev_hdr = nullptr;
-    if (box && box_dev && !ev_hdr) cudaEventCreateWithFlags(&ev_hdr, cudaEventDisableTiming);
+    static thread_local cudaEvent_t ev_hdr_by_dev[64] = {};
+    int dev_now = 0; cudaGetDevice(&dev_now);
+    cudaEvent_t* ev_slot = (dev_now >= 0 && dev_now < 64) ? &ev_hdr_by_dev[dev_now] : nullptr;   // events belong to a device
+    if (box && box_dev && ev_slot && !*ev_slot) cudaEventCreateWithFlags(ev_slot, cudaEventDisableTiming);
+    cudaEvent_t ev_hdr = ev_slot ? *ev_slot : nullptr;
     const bool mailed = box && box_dev && ev_hdr;
     if (mailed && (rc = check_cuda(cudaEventRecord(ev_hdr, s), "event record"))) return rc;
 
-    // (1) stable sort of the Gaussians by depth bits (invisible ones keyed 0xffffffff go last and emit nothing)
+    // (1) order the visible Gaussians by (depth bits, index): scatter into range buckets, sort every bucket in shared memory
     {
         ProfScope ps(GSR_PROF_DEPTH_SORT, s);
-        // compact the visible Gaussians (ascending index) into (dkeys_a, order), then 4 radix passes over those only
-        launch_compact_keys(g, P, g.dkeys_a, g.order, s);
-        // even pass count: keys a -> b -> a ..., values order -> order_tmp -> order ...; the result ends in (dkeys_a, order)
-        rc = launch_onesweep32(g.dkeys_a, g.order, g.dkeys_a, g.order, g.dkeys_b, g.order_tmp, P, dplan, g.sort_temp, g.sort_temp_bytes,
-                               /*hist_ready=*/false, &g.header->sort_error, -1, s, &g.header->num_visible, /*prezeroed=*/dzero != 0);
-        if (rc) return rc;
-        launch_order_block_sums(P, &g.header->num_visible, g.order, g.rects, g.oblock_sums, s);
-        launch_scan_u32(g.oblock_sums, g.oblock_offsets, g.nblocks, s);
+        launch_bucket_scatter(g, P, s);
+        launch_bucket_sort(g, P, /*presorted=*/false, s);
     }
     if ((rc = check_last("depth sort", debug, s))) return rc;
 
@@ -200,9 +219,31 @@ static int build_lists(const gsr_scene* sc, const gsr_camera* cam, int mode, gsr
     if (mailed) {
         if ((rc = check_cuda(cudaEventSynchronize(ev_hdr), "event sync (header)"))) return rc;
         memcpy(hdr, box, 32);
-    } else if ((rc = read_u32(&g.header->magic, hdr, 8, s))) return rc;
+    } else {
+        if ((rc = read_u32(&g.header->magic, hdr, 6, s))) return rc;
+        uint32_t mode = 0;
+        if ((rc = read_u32(&g.header->sort_mode, &mode, 1, s))) return rc;
+        hdr[6] = mode >= 2 ? 2u : mode; hdr[7] = 0;
+    }
+    if (hdr[0] != kGeomMagic || hdr[1] != (uint32_t)P || hdr[6] == 0) { set_error("frame totals did not arrive (magic %08x, P %u, mode %u)", hdr[0], hdr[1], hdr[6]); return GSR_ERR_WORKSPACE; }
     if (hdr[3] & 0x100u) { set_error("a Gaussian was culled although prefiltered=true (reference would __trap)"); return GSR_ERR_INVALID; }
-    const long long N = hdr[2], R = hdr[4];
+    const long long N = hdr[2], R = hdr[4], V = hdr[5];
+    if (hdr[6] == 2u || g_force_sort_fallback) {
+        // A histogram bin holds more keys than one CTA sorts (or the test hook asks for it): the round-1 chain instead --
+        // ordered compaction of the visible Gaussians, 4 stable onesweep passes over the 32 depth bits -- then the run
+        // offsets on uniform buckets.  The bucket kernels queued above have left at once (sort_mode != 1).
+        ProfScope ps(GSR_PROF_DEPTH_SORT, s);
+        const SortPlan dplan = make_sort_plan(32);
+        if (dplan.passes & 1) { set_error("depth sort plan must have an even pass count"); return GSR_ERR_INVALID; }
+        launch_scan_u32(g.block_sums_v, g.block_offsets, g.nblocks, s);
+        launch_compact_keys(g, P, g.dkeys_a, g.order, s);
+        rc = launch_onesweep32(g.dkeys_a, g.order, g.dkeys_a, g.order, g.dkeys_b, g.order_tmp, P, dplan, g.sort_temp, g.sort_temp_bytes,
+                               /*hist_ready=*/false, &g.header->sort_error, -1, s, &g.header->num_visible, /*prezeroed=*/false);
+        if (rc) return rc;
+        launch_uniform_buckets(g, P, s);
+        launch_bucket_sort(g, P, /*presorted=*/true, s);
+        if ((rc = check_last("depth sort (fallback)", debug, s))) return rc;
+    }
     void* bin = alloc(user, GSR_BUF_BINNING, gsr_binning_bytes(N, R, W, H, mode));
     if (!bin) { set_error("allocation callback returned NULL (binning)"); return GSR_ERR_ALLOC; }
     BinPtrs b = bin_ptrs(bin, N, R, im.tiles_x, im.tiles_y);
@@ -217,7 +258,7 @@ static int build_lists(const gsr_scene* sc, const gsr_camera* cam, int mode, gsr
         if (rzero) launch_zero(hist, rzero, s);       // one clearing kernel for histogram + counters + look-back words
         else if ((rc = check_cuda(cudaMemsetAsync(hist, 0, sizeof(uint32_t) * kSortMaxPasses * kSortMaxRadix, s), "memset hist"))) return rc;
         { ProfScope ps(GSR_PROF_DUPLICATE, s);
-          launch_emit_runs(g, P, g.order, g.oblock_offsets, b.rkeyA, b.rvalA, hist, plan, s); }
+          launch_emit_runs(g, V, b.rkeyA, b.rvalA, hist, plan, s); }
         if ((rc = check_last("emit runs", debug, s))) return rc;
         {
             ProfScope ps(GSR_PROF_SORT, s);
@@ -233,8 +274,10 @@ static int build_lists(const gsr_scene* sc, const gsr_camera* cam, int mode, gsr
         if (plan.passes == 1 && plan.shift[0] == kRunRowShift) row_offsets = hist;   // exclusive digit offsets == first run of every row
     }
     // (4) expand the row-sorted runs into the per-tile lists; also yields tile ranges and AMR intersection counts
-    launch_expand_runs(b, rk_sorted, rv_sorted, R, im.tiles_x, im.tiles_y, row_offsets, im.ranges, im.n_intersections, GSR_PROF_RANGES, GSR_PROF_EXPAND, s);
+    launch_expand_runs(b, rk_sorted, rv_sorted, R, im.tiles_x, im.tiles_y, row_offsets, im.ranges, im.n_intersections, g.header, box_dev,
+                       GSR_PROF_RANGES, GSR_PROF_EXPAND, s);
     if ((rc = check_last("expand runs", debug, s))) return rc;
+    if (debug && (rc = check_sort_mailbox("forward (debug)"))) return rc;      // debug synchronised: the word has arrived
     *geom_out = geom; *bin_out = bin; *img_out = img; *N_out = (int)N;
     g_last_build = {geom, P, (int)N, R, (long long)hdr[5]};
     return GSR_OK;
@@ -280,6 +323,8 @@ const char* gsr_last_error(void) { return g_err; }
 int gsr_set_option(int option, int value) {
     if (option == GSR_OPT_SORT_VARIANT && value >= 0 && value <= 5) { set_sort_variant(value); return GSR_OK; }
     if (option == GSR_OPT_BLEND_VARIANT && value >= 0 && value <= 1) { set_blend_variant(value); return GSR_OK; }
+    if (option == GSR_OPT_FAKE_SORT_ERROR && (value == 0 || value == 1)) { set_fake_sort_error(value); return GSR_OK; }
+    if (option == GSR_OPT_FORCE_SORT_FALLBACK && (value == 0 || value == 1)) { g_force_sort_fallback = value; return GSR_OK; }
     if (option == GSR_OPT_PEER_CTAS_PER_SM && value >= 0 && (value & 0xff) <= 32 && value < 0x300) { set_peer_ctas_per_sm(value); return GSR_OK; }
     set_error("unknown option %d / value %d", option, value);
     return GSR_ERR_INVALID;
@@ -347,6 +392,7 @@ static int backward_impl(const gsr_scene* sc, const gsr_camera* cam, const int* 
     if (!gr || (!dL_dpix && phase != GSR_BWD_PREPROCESS)) { set_error("grads/dL_dpix are required"); return GSR_ERR_INVALID; }
     const int P = sc->P, W = cam->width, H = cam->height;
     if (P == 0) return GSR_OK;
+    if ((rc = check_sort_mailbox("backward"))) return rc;
     if (!geom_buffer || !binning_buffer || !image_buffer) { set_error("work buffers are required"); return GSR_ERR_WORKSPACE; }
     if (!gr->dL_dmeans2D || !gr->dL_dcolors || !gr->dL_dopacity || !gr->dL_dmeans3D || !gr->dL_dcov3D || !gr->dL_dscales ||
         !gr->dL_drotations || !gr->scratch || (phase != GSR_BWD_BLEND && sc->sh_coeffs > 0 && sc->shs && !gr->dL_dsh && !gr->dL_dcolors_clamped)) {
@@ -526,6 +572,7 @@ int gsr_last_counts(const void* geom_buffer, int P, long long* num_rendered, lon
     if (!geom_buffer || geom_buffer != g_last_build.geom || P != g_last_build.P) {
         set_error("last_counts: not the geometry buffer this thread built last"); return GSR_ERR_INVALID;
     }
+    { int rc0 = check_sort_mailbox("last_counts"); if (rc0) return rc0; }
     if (num_rendered) *num_rendered = g_last_build.N;
     if (num_runs) *num_runs = g_last_build.R;
     if (num_visible) *num_visible = g_last_build.V;
@@ -569,9 +616,16 @@ int gsr_sort_pairs(const uint64_t* keys_in, uint64_t* keys_out, const uint32_t* 
     const SortPlan plan = make_sort_plan(end_bit);
     // the watchdog flag lives in the last word of the counters block
     uint32_t* err = (uint32_t*)(aligned_base(temp) + align_up(sizeof(uint32_t) * kSortMaxPasses * kSortMaxRadix)) + 32;
-    int rc = launch_onesweep(keys_in, vals_in, keys_out, vals_out, keys_tmp, vals_tmp, n, plan, temp, temp_bytes, false, err, s);
+    int rc = check_cuda(cudaMemsetAsync(err, 0, sizeof(uint32_t), s), "memset sort flag");
     if (rc) return rc;
-    return check_last("sort_pairs", false, s);
+    rc = launch_onesweep(keys_in, vals_in, keys_out, vals_out, keys_tmp, vals_tmp, n, plan, temp, temp_bytes, false, err, s);
+    if (rc) return rc;
+    if ((rc = check_last("sort_pairs", false, s))) return rc;
+    // stand-alone operator: report the watchdog synchronously (a caller of a sort wants sorted data or an error)
+    uint32_t flag = 0;
+    if ((rc = read_u32(err, &flag, 1, s))) return rc;
+    if (flag & 1u) { set_error("sort_pairs: the radix-sort watchdog fired (a look-back never saw its predecessor)"); return GSR_ERR_SORT; }
+    return GSR_OK;
 }
 
 }  // extern "C"

@@ -94,10 +94,12 @@ __global__ void __launch_bounds__(kPreBlock) order_block_sums_kernel(const uint3
 //   rank of Gaussian j in tile (row, x) = number of runs of that row, earlier in depth order, that cover column x.
 // ------------------------------------------------------------------------------------------------
 struct EmitRunsParams {
-    const uint32_t* __restrict__ n_dev;          // number of depth-sorted (visible) Gaussians
+    const GeomHeader* __restrict__ hdr;          // num_visible, num_buckets
     const uint32_t* __restrict__ order;          // depth-sorted Gaussian ids
     const uint2* __restrict__ rects;
-    const uint32_t* __restrict__ block_offsets;  // [nblocks+1] exclusive run offsets of the sorted 256-blocks
+    const uint32_t* __restrict__ bucket_start;   // [num_buckets + 1] first sorted position of every sort bucket
+    const uint32_t* __restrict__ bucket_base;    // [num_buckets + 1] exclusive run offsets of the buckets
+    const uint32_t* __restrict__ runoff;         // [num_visible] exclusive run offset of a sorted position inside its bucket
     uint32_t* __restrict__ rkeys;                // out: (row << 20) | (x0 << 10) | w
     uint32_t* __restrict__ rvals;                // out: Gaussian id
     uint32_t* hist;                              // [passes][kSortMaxRadix] global digit counts of the row field
@@ -106,32 +108,33 @@ struct EmitRunsParams {
 
 __global__ void __launch_bounds__(kPreBlock) emit_runs_kernel(const EmitRunsParams p) {
     extern __shared__ uint32_t s_hist[];            // [passes][kSortMaxRadix]
-    __shared__ uint32_t s_wsum[kPreBlock / 32];
-    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-    const uint32_t base = __ldg(p.block_offsets + blockIdx.x);
-    if (__ldg(p.block_offsets + blockIdx.x + 1) == base) return;        // nothing visible in this block (CTA-uniform)
-    for (int i = tid; i < p.passes * kSortMaxRadix; i += kPreBlock) s_hist[i] = 0;
-    const uint32_t j = blockIdx.x * kPreBlock + tid;
-    uint32_t g = 0, x0 = 0, w = 0, y0 = 0, h = 0;
-    if (j < __ldg(p.n_dev)) {
-        g = p.order[j];
-        const uint2 r = p.rects[g];
-        x0 = r.x & 0xffffu; w = (r.x >> 16) - x0; y0 = r.y & 0xffffu; h = (r.y >> 16) - y0;
+    __shared__ uint32_t s_b0;
+    const int tid = threadIdx.x;
+    const uint32_t V = p.hdr->num_visible;
+    const uint32_t j0 = blockIdx.x * kPreBlock;
+    if (j0 >= V) return;                             // grid is sized for P (CTA-uniform exit)
+    if (tid == 0) {                                  // sort bucket of this block's first position
+        uint32_t lo = 0, hi = p.hdr->num_buckets;    // invariant: bucket_start[lo] <= j0 < bucket_start[hi]
+        while (hi - lo > 1) { const uint32_t mid = (lo + hi) >> 1; if (__ldg(p.bucket_start + mid) <= j0) lo = mid; else hi = mid; }
+        s_b0 = lo;
     }
-    uint32_t inc = h;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) { uint32_t u = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += u; }
-    if (lane == 31) s_wsum[wid] = inc;
+    for (int i = tid; i < p.passes * kSortMaxRadix; i += kPreBlock) s_hist[i] = 0;
     __syncthreads();
-    uint32_t off = base + inc - h;
-#pragma unroll
-    for (int k = 0; k < kPreBlock / 32; ++k) off += (k < wid) ? s_wsum[k] : 0u;
-    for (uint32_t k = 0; k < h; ++k) {
-        const uint32_t key = ((y0 + k) << kRunRowShift) | (x0 << kRunX0Shift) | w;
-        p.rkeys[off + k] = key;
-        p.rvals[off + k] = g;
-        atomicAdd(&s_hist[(key >> p.shift0) & ((1u << p.bits0) - 1u)], 1u);
-        if (p.passes > 1) atomicAdd(&s_hist[kSortMaxRadix + ((key >> p.shift1) & ((1u << p.bits1) - 1u))], 1u);
+    const uint32_t j = j0 + tid;
+    if (j < V) {
+        uint32_t b = s_b0;
+        while (j >= __ldg(p.bucket_start + b + 1)) ++b;      // a 256-block spans few buckets (empty ones are skipped over)
+        const uint32_t off = __ldg(p.bucket_base + b) + __ldg(p.runoff + j);
+        const uint32_t g = p.order[j];
+        const uint2 r = p.rects[g];
+        const uint32_t x0 = r.x & 0xffffu, w = (r.x >> 16) - x0, y0 = r.y & 0xffffu, h = (r.y >> 16) - y0;
+        for (uint32_t k = 0; k < h; ++k) {
+            const uint32_t key = ((y0 + k) << kRunRowShift) | (x0 << kRunX0Shift) | w;
+            p.rkeys[off + k] = key;
+            p.rvals[off + k] = g;
+            atomicAdd(&s_hist[(key >> p.shift0) & ((1u << p.bits0) - 1u)], 1u);
+            if (p.passes > 1) atomicAdd(&s_hist[kSortMaxRadix + ((key >> p.shift1) & ((1u << p.bits1) - 1u))], 1u);
+        }
     }
     __syncthreads();
     for (int i = tid; i < p.passes * kSortMaxRadix; i += kPreBlock) {
@@ -160,15 +163,15 @@ void launch_order_block_sums(int P, const uint32_t* n_dev, const uint32_t* order
     count_launch();
 }
 
-void launch_emit_runs(const GeomPtrs& g, int P, const uint32_t* order, const uint32_t* block_offsets, uint32_t* rkeys, uint32_t* rvals,
-                      uint32_t* hist, const SortPlan& plan, cudaStream_t s) {
+void launch_emit_runs(const GeomPtrs& g, long long V, uint32_t* rkeys, uint32_t* rvals, uint32_t* hist, const SortPlan& plan, cudaStream_t s) {
     EmitRunsParams p;
-    p.n_dev = &g.header->num_visible; p.order = order; p.rects = g.rects; p.block_offsets = block_offsets; p.rkeys = rkeys; p.rvals = rvals; p.hist = hist;
+    p.hdr = g.header; p.order = g.order; p.rects = g.rects; p.bucket_start = g.bucket_start; p.bucket_base = g.bucket_base; p.runoff = g.runoff;
+    p.rkeys = rkeys; p.rvals = rvals; p.hist = hist;
     p.passes = plan.passes;
     p.shift0 = plan.shift[0]; p.bits0 = plan.bits[0];
     p.shift1 = plan.passes > 1 ? plan.shift[1] : 0; p.bits1 = plan.passes > 1 ? plan.bits[1] : 1;
-    if (g.nblocks < 1) return;
-    emit_runs_kernel<<<g.nblocks, kPreBlock, sizeof(uint32_t) * plan.passes * kSortMaxRadix, s>>>(p);
+    if (V < 1) return;                 // the host knows the visible count by now: the grid covers exactly the sorted positions
+    emit_runs_kernel<<<(unsigned)((V + kPreBlock - 1) / kPreBlock), kPreBlock, sizeof(uint32_t) * plan.passes * kSortMaxRadix, s>>>(p);
     count_launch();
 }
 
@@ -676,9 +679,13 @@ __global__ void __launch_bounds__(1024) row_scan_kernel(int tiles_x, const uint3
 
 // exclusive scan of the per-tile totals -> tile_start (in place), ranges, AMR intersection counts
 __global__ void __launch_bounds__(1024) tile_scan_kernel(uint32_t* __restrict__ tile_start, int num_tiles, uint2* __restrict__ ranges,
-                                                         uint32_t* __restrict__ n_intersections) {
+                                                         uint32_t* __restrict__ n_intersections, const GeomHeader* hdr, uint32_t* mailbox,
+                                                         uint32_t fake_error) {
     __shared__ uint32_t s_warp[32];
     const int tid = threadIdx.x;
+    // Every radix pass of the frame (depth-sort fallback, row partition of the runs) is behind us in stream order: post the
+    // watchdog word where the host finds it at its next call on this thread (gsr_api.cu: check_sort_mailbox).
+    if (tid == 0 && mailbox != nullptr) *((volatile uint32_t*)mailbox + 8) = 0x80000000u | ((hdr->sort_error | fake_error) & 1u);
     const int per = (num_tiles + 1023) / 1024;
     const int begin = min(num_tiles, tid * per), end = min(num_tiles, begin + per);
     uint32_t local = 0;
@@ -762,8 +769,12 @@ __global__ void __launch_bounds__(kExpandThreads) expand_runs_kernel(const uint3
     }
 }
 
+static uint32_t g_fake_sort_error = 0;
+void set_fake_sort_error(int v) { g_fake_sort_error = v ? 1u : 0u; }
+
 void launch_expand_runs(const BinPtrs& b, const uint32_t* rkeys_sorted, const uint32_t* rvals_sorted, long long R, int tiles_x, int tiles_y,
-                        const uint32_t* row_offsets, uint2* ranges, uint32_t* n_intersections, int prof_ranges, int prof_expand, cudaStream_t s) {
+                        const uint32_t* row_offsets, uint2* ranges, uint32_t* n_intersections, const GeomHeader* hdr, uint32_t* mailbox_dev,
+                        int prof_ranges, int prof_expand, cudaStream_t s) {
     const int num_tiles = tiles_x * tiles_y;
     const unsigned grid = (unsigned)b.max_chunks;
     {
@@ -771,7 +782,7 @@ void launch_expand_runs(const BinPtrs& b, const uint32_t* rkeys_sorted, const ui
         chunk_table_kernel<<<1, 1024, 0, s>>>(rkeys_sorted, (uint32_t)R, tiles_y, row_offsets, b.row_start, b.chunk_row_start);
         chunk_count_kernel<<<grid, 256, sizeof(int) * (tiles_x + 1), s>>>(rkeys_sorted, tiles_x, tiles_y, b.chunk_row_start, b.row_start, b.chunk_counts, b.chunk_info);
         row_scan_kernel<<<dim3((tiles_x + 31) / 32, tiles_y), 1024, 0, s>>>(tiles_x, b.chunk_row_start, b.chunk_counts, b.tile_start);
-        tile_scan_kernel<<<1, 1024, 0, s>>>(b.tile_start, num_tiles, ranges, n_intersections);
+        tile_scan_kernel<<<1, 1024, 0, s>>>(b.tile_start, num_tiles, ranges, n_intersections, hdr, mailbox_dev, g_fake_sort_error);
         count_launch(4);
     }
     {

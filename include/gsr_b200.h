@@ -323,7 +323,10 @@ GSR_API int gsr_peer_allreduce_sum(void* const* peer_bases, size_t data_offset, 
  * compute the sum; tools/peer_diag.py uses it to time the two directions and nothing else may) ---- */
 enum { GSR_OPT_SORT_VARIANT = 0,  /* onesweep tile shape for u32 keys: 0 = default, 1..5 see gsr_binning.cu */
        GSR_OPT_BLEND_VARIANT = 1, /* forward blend: 0 = two pixels per thread, packed FP32x2 (default); 1 = one pixel per thread */
-       GSR_OPT_PEER_CTAS_PER_SM = 2 /* gsr_peer_allreduce_sum*: grid cap in CTAs per SM, 0 = default */ };
+       GSR_OPT_PEER_CTAS_PER_SM = 2, /* gsr_peer_allreduce_sum*: grid cap in CTAs per SM, 0 = default */
+       GSR_OPT_FAKE_SORT_ERROR = 4, /* 1: the next frames post a tripped radix-sort watchdog (test hook for GSR_ERR_SORT) */
+       GSR_OPT_FORCE_SORT_FALLBACK = 3 /* 1: depth-sort with the global onesweep chain even when the range buckets fit (the
+                                          path taken when a depth-histogram bin overflows a bucket); results are identical */ };
 GSR_API int gsr_set_option(int option, int value);
 
 /* counters: how many kernels this library launched since load (bench.py "gpu_launches") */
