@@ -80,3 +80,85 @@ def pageable_memory_access(device_index: int) -> bool:
         return bool(v.value)
     except OSError:
         return False
+
+
+class RegisteredStackWorker:
+    """Runs callables on ONE worker thread whose whole stack is cudaHostRegister'ed (portable | mapped).
+
+    Why: the reference's AMR fork hands a host STACK array to setAMRLevelsKernel
+    (diff-gaussian-rasterization-amr/cuda_rasterizer/rasterizer_impl.cu:610,644).  On a device without pageable-memory
+    access the stock binding therefore faults -- unless the calling thread's stack is registered with the driver, which
+    makes that very host pointer valid on the device (unified addressing; needs
+    cudaDevAttrCanUseHostPointerForRegisteredMem).  Nothing of the reference is modified: the same `_C` call is simply
+    issued from this thread.  Test/baseline infrastructure only."""
+
+    def __init__(self, device_index: int = 0, stack_bytes: int = 32 << 20):
+        import queue
+        import threading
+        self._q, self._res = queue.Queue(), queue.Queue()
+        self.error = None
+        self._dev = int(device_index)
+        old = threading.stack_size(stack_bytes)
+        try:
+            self._t = threading.Thread(target=self._run, daemon=True)
+            self._t.start()
+        finally:
+            threading.stack_size(old)
+        ok = self._res.get()
+        if ok is not True:
+            self.error = str(ok)
+            raise RuntimeError(f"cannot register the worker stack: {ok}")
+
+    def _register_own_stack(self):
+        libc = C.CDLL(None)
+        rt = C.CDLL("libcudart.so.12")
+        attr = C.create_string_buffer(128)                      # pthread_attr_t (56 bytes on x86-64 glibc)
+        libc.pthread_self.restype = C.c_void_p
+        if libc.pthread_getattr_np(C.c_void_p(libc.pthread_self()), attr) != 0:
+            return "pthread_getattr_np failed"
+        addr, size = C.c_void_p(0), C.c_size_t(0)
+        if libc.pthread_attr_getstack(attr, C.byref(addr), C.byref(size)) != 0:
+            return "pthread_attr_getstack failed"
+        libc.pthread_attr_destroy(attr)
+        can = C.c_int(0)
+        rt.cudaSetDevice(C.c_int(self._dev))
+        rt.cudaDeviceGetAttribute(C.byref(can), C.c_int(91), C.c_int(self._dev))     # cudaDevAttrCanUseHostPointerForRegisteredMem
+        if not can.value:
+            return "device cannot use host pointers of registered memory"
+        # touch every page first (the stack is lazily mapped), then pin it: portable (1) | mapped (2)
+        page = 4096
+        buf = (C.c_char * size.value).from_address(addr.value)
+        guard = 64 * 1024                                       # leave the guard region at the low end alone
+        for off in range(guard, size.value - 256 * 1024, page):  # do not scribble over the live frames at the top
+            buf[off] = b"\0"
+        e = rt.cudaHostRegister(C.c_void_p(addr.value + guard), C.c_size_t(size.value - guard), C.c_uint(1 | 2))
+        if e != 0:
+            rt.cudaGetLastError()
+            return f"cudaHostRegister(stack) failed with error {e}"
+        return True
+
+    def _run(self):
+        try:
+            self._res.put(self._register_own_stack())
+        except Exception as ex:  # noqa: BLE001
+            self._res.put(repr(ex))
+            return
+        while True:
+            item = self._q.get()
+            if item is None:
+                return
+            fn, args, kw = item
+            try:
+                self._res.put((True, fn(*args, **kw)))
+            except BaseException as ex:  # noqa: BLE001
+                self._res.put((False, ex))
+
+    def call(self, fn, *args, **kw):
+        self._q.put((fn, args, kw))
+        ok, val = self._res.get()
+        if not ok:
+            raise val
+        return val
+
+    def close(self):
+        self._q.put(None)

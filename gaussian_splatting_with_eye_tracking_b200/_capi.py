@@ -100,6 +100,7 @@ SYMBOLS = {
     "gsr_amr_relevel": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
     "gsr_amr_render_prebuilt": (C.c_int, [C.POINTER(GsrScene), C.POINTER(GsrCamera), C.c_void_p, C.c_void_p, C.c_void_p, C.c_int,
                                           C.POINTER(GsrGaze), C.c_void_p, C.c_int, C.c_void_p]),
+    "gsr_blend_stats": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "gsr_view_geom": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(GsrGeomView)]),
     "gsr_view_binning": (C.c_int, [C.c_void_p, C.c_longlong, C.POINTER(GsrBinningView)]),
     "gsr_view_image": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.POINTER(GsrImageView)]),

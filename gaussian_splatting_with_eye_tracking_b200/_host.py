@@ -261,6 +261,18 @@ def last_counts(geomBuffer, P):
     return int(n.value), int(r.value), int(v.value)
 
 
+def blend_stats(geomBuffer, binningBuffer, imageBuffer, P, image_height, image_width):
+    """(pair_tests_forward, hits, pair_tests_backward) of a baseline frame just built by rasterize_gaussians: the
+    algorithmic work of the blend stage, counted by one extra kernel (gsr_blend_stats).  Measurement only."""
+    dev = geomBuffer.device
+    with torch.cuda.device(dev):
+        tot = torch.empty(3, dtype=torch.int64, device=dev)
+        rc = lib.gsr_blend_stats(int(P), int(image_width), int(image_height), _p(geomBuffer), _p(binningBuffer), _p(imageBuffer),
+                                 _p(tot), _stream())
+        _capi.check(rc, "gsr_blend_stats")
+    return tuple(int(x) for x in tot.tolist())
+
+
 def pack_meta_words(P):
     return int(lib.gsr_pack_meta_words(int(P)))
 

@@ -166,10 +166,10 @@ static int build_lists(const gsr_scene* sc, const gsr_camera* cam, int mode, gsr
     if (cam->band_row1 > im.tiles_y) { set_error("tile band [%d,%d) exceeds the %d tile rows", cam->band_row0, cam->band_row1, im.tiles_y); return GSR_ERR_INVALID; }
     if (im.tiles_x > kRunFieldMask || im.tiles_y > kRunMaxRows) { set_error("image of %dx%d tiles exceeds the %dx%d tile grid limit", im.tiles_x, im.tiles_y, kRunFieldMask, kRunMaxRows); return GSR_ERR_INVALID; }
     int rc = GSR_OK;
-    // One 256-byte memset node per frame: the header's counters are accumulated with atomics by the preprocess and sort
-    // kernels.  Everything else the frame needs cleared (bin histogram, bucket cursors) is cleared on the side by the
-    // preprocess kernel.
+    // Two small memset nodes per frame (header: 256 B, statistics slots: 16 KB): both are accumulated with atomics.  The
+    // depth bins are cleared on the side by the preprocess kernel.
     if ((rc = check_cuda(cudaMemsetAsync(g.header, 0, sizeof(GeomHeader), s), "memset header"))) return rc;
+    if ((rc = check_cuda(cudaMemsetAsync(g.stat_slots, 0, sizeof(FrameStatSlot) * kStatSlots, s), "memset statistics"))) return rc;
     uint32_t* box_dev = nullptr;
     uint32_t* box = pinned_mailbox(&box_dev);
     if (box) { box[0] = 0; box[6] = 0; }
@@ -187,12 +187,12 @@ static int build_lists(const gsr_scene* sc, const gsr_camera* cam, int mode, gsr
     a.radii = radii_user ? radii_user : g.radii;
     a.prefiltered = cam->prefiltered != 0;
     a.band_row0 = cam->band_row0; a.band_row1 = cam->band_row1;
-    a.zero_ptr = nullptr; a.zero_bytes = 0; a.mailbox = box_dev;
+    a.zero_ptr = nullptr; a.zero_bytes = 0;
     { ProfScope ps(GSR_PROF_PREPROCESS, s); launch_preprocess(a, g, s); }
     if ((rc = check_last("preprocess", debug, s))) return rc;
     // histogram of the depth keys + bucket plan (replaces the scan kernel's slot in the profile)
-    { ProfScope ps(GSR_PROF_SCAN, s); launch_bucket_hist(g, P, box_dev, s); }
-    if ((rc = check_last("bucket histogram", debug, s))) return rc;
+    { ProfScope ps(GSR_PROF_SCAN, s); launch_bin_hist(g, P, box_dev, s); }
+    if ((rc = check_last("depth histogram", debug, s))) return rc;
 
     // The one host round-trip of the forward (reference: rasterizer_impl.cu:281): the binning buffer is sized by N.
     // The last CTAs of the two kernels above store the totals straight into mapped host memory and the host waits on an
@@ -207,11 +207,11 @@ static int build_lists(const gsr_scene* sc, const gsr_camera* cam, int mode, gsr
     const bool mailed = box && box_dev && ev_hdr;
     if (mailed && (rc = check_cuda(cudaEventRecord(ev_hdr, s), "event record"))) return rc;
 
-    // (1) order the visible Gaussians by (depth bits, index): scatter into range buckets, sort every bucket in shared memory
+    // (1) order the visible Gaussians by (depth bits, index): counting sort into fine depth bins, exact order inside each
     {
         ProfScope ps(GSR_PROF_DEPTH_SORT, s);
-        launch_bucket_scatter(g, P, s);
-        launch_bucket_sort(g, P, /*presorted=*/false, s);
+        { ProfScope p1(GSR_PROF_SORT_PASS0 + 1, s); launch_bin_scatter(g, P, s); }
+        { ProfScope p2(GSR_PROF_SORT_PASS0 + 2, s); launch_bin_sort(g, P, s); }
     }
     if ((rc = check_last("depth sort", debug, s))) return rc;
 
@@ -229,9 +229,9 @@ static int build_lists(const gsr_scene* sc, const gsr_camera* cam, int mode, gsr
     if (hdr[3] & 0x100u) { set_error("a Gaussian was culled although prefiltered=true (reference would __trap)"); return GSR_ERR_INVALID; }
     const long long N = hdr[2], R = hdr[4], V = hdr[5];
     if (hdr[6] == 2u || g_force_sort_fallback) {
-        // A histogram bin holds more keys than one CTA sorts (or the test hook asks for it): the round-1 chain instead --
-        // ordered compaction of the visible Gaussians, 4 stable onesweep passes over the 32 depth bits -- then the run
-        // offsets on uniform buckets.  The bucket kernels queued above have left at once (sort_mode != 1).
+        // A depth bin holds more records than one warp orders (or the test hook asks for it): the round-1 chain instead --
+        // ordered compaction of the visible Gaussians, 4 stable onesweep passes over the 32 depth bits, block sums + scan --
+        // then the run offsets per sorted position.  The bin kernels queued above have left at once (sort_mode != 1).
         ProfScope ps(GSR_PROF_DEPTH_SORT, s);
         const SortPlan dplan = make_sort_plan(32);
         if (dplan.passes & 1) { set_error("depth sort plan must have an even pass count"); return GSR_ERR_INVALID; }
@@ -240,8 +240,9 @@ static int build_lists(const gsr_scene* sc, const gsr_camera* cam, int mode, gsr
         rc = launch_onesweep32(g.dkeys_a, g.order, g.dkeys_a, g.order, g.dkeys_b, g.order_tmp, P, dplan, g.sort_temp, g.sort_temp_bytes,
                                /*hist_ready=*/false, &g.header->sort_error, -1, s, &g.header->num_visible, /*prezeroed=*/false);
         if (rc) return rc;
-        launch_uniform_buckets(g, P, s);
-        launch_bucket_sort(g, P, /*presorted=*/true, s);
+        launch_order_block_sums(P, &g.header->num_visible, g.order, g.rects, g.oblock_sums, s);
+        launch_scan_u32(g.oblock_sums, g.oblock_offsets, g.nblocks, s);
+        launch_runoff_from_blocks(g, P, s);
         if ((rc = check_last("depth sort (fallback)", debug, s))) return rc;
     }
     void* bin = alloc(user, GSR_BUF_BINNING, gsr_binning_bytes(N, R, W, H, mode));
@@ -577,6 +578,21 @@ int gsr_last_counts(const void* geom_buffer, int P, long long* num_rendered, lon
     if (num_runs) *num_runs = g_last_build.R;
     if (num_visible) *num_visible = g_last_build.V;
     return GSR_OK;
+}
+
+int gsr_blend_stats(int P, int W, int H, const void* geom_buffer, const void* binning_buffer, const void* image_buffer,
+                    unsigned long long* totals_dev, void* stream) {
+    if (P <= 0 || W <= 0 || H <= 0 || !geom_buffer || !binning_buffer || !image_buffer || !totals_dev) { set_error("blend_stats: bad arguments"); return GSR_ERR_INVALID; }
+    cudaStream_t s = (cudaStream_t)stream;
+    GeomPtrs g = geom_ptrs(geom_buffer, P);
+    ImgPtrs im = img_ptrs(image_buffer, W, H, GSR_MODE_BASELINE);
+    int rc = check_cuda(cudaMemsetAsync(totals_dev, 0, 3 * sizeof(unsigned long long), s), "memset totals");
+    if (rc) return rc;
+    BlendArgs ba;
+    ba.W = W; ba.H = H; ba.row0 = 0; ba.row1 = 0; ba.ranges = im.ranges; ba.point_list = bin_point_list(binning_buffer); ba.means2D = g.means2D;
+    ba.conic_opacity = g.conic_opacity; ba.colors = nullptr; ba.bg = nullptr; ba.final_T = nullptr; ba.n_contrib = nullptr; ba.out_color = nullptr;
+    launch_blend_count(ba, totals_dev, s);
+    return check_last("blend_stats", false, s);
 }
 
 int gsr_view_geom(const void* geom_buffer, int P, gsr_geom_view* out) {

@@ -94,47 +94,50 @@ __global__ void __launch_bounds__(kPreBlock) order_block_sums_kernel(const uint3
 //   rank of Gaussian j in tile (row, x) = number of runs of that row, earlier in depth order, that cover column x.
 // ------------------------------------------------------------------------------------------------
 struct EmitRunsParams {
-    const GeomHeader* __restrict__ hdr;          // num_visible, num_buckets
+    const GeomHeader* __restrict__ hdr;          // num_visible
     const uint32_t* __restrict__ order;          // depth-sorted Gaussian ids
     const uint2* __restrict__ rects;
-    const uint32_t* __restrict__ bucket_start;   // [num_buckets + 1] first sorted position of every sort bucket
-    const uint32_t* __restrict__ bucket_base;    // [num_buckets + 1] exclusive run offsets of the buckets
-    const uint32_t* __restrict__ runoff;         // [num_visible] exclusive run offset of a sorted position inside its bucket
+    const uint32_t* __restrict__ runoff;         // [num_visible + 1] first run of every sorted position (exclusive prefix of the tile rows)
     uint32_t* __restrict__ rkeys;                // out: (row << 20) | (x0 << 10) | w
     uint32_t* __restrict__ rvals;                // out: Gaussian id
     uint32_t* hist;                              // [passes][kSortMaxRadix] global digit counts of the row field
     int passes, shift0, bits0, shift1, bits1;    // at most two passes (<= 4095 tile rows)
 };
 
+// One THREAD PER RUN: the runs of a block of 256 depth-sorted Gaussians are consecutive in the output, so thread r of the
+// block writes run base + r -- fully coalesced stores (one thread per Gaussian looping over its rows wrote 32 different
+// sectors per store instruction, 1 cycle each in the L1) and no divergence on tall Gaussians.  The Gaussian of a run is
+// found by binary search in the block's 257 offsets (shared memory).
 __global__ void __launch_bounds__(kPreBlock) emit_runs_kernel(const EmitRunsParams p) {
     extern __shared__ uint32_t s_hist[];            // [passes][kSortMaxRadix]
-    __shared__ uint32_t s_b0;
+    __shared__ uint32_t s_off[kPreBlock + 1];
+    __shared__ uint32_t s_id[kPreBlock];
+    __shared__ uint32_t s_x[kPreBlock], s_y0[kPreBlock];
     const int tid = threadIdx.x;
     const uint32_t V = p.hdr->num_visible;
     const uint32_t j0 = blockIdx.x * kPreBlock;
-    if (j0 >= V) return;                             // grid is sized for P (CTA-uniform exit)
-    if (tid == 0) {                                  // sort bucket of this block's first position
-        uint32_t lo = 0, hi = p.hdr->num_buckets;    // invariant: bucket_start[lo] <= j0 < bucket_start[hi]
-        while (hi - lo > 1) { const uint32_t mid = (lo + hi) >> 1; if (__ldg(p.bucket_start + mid) <= j0) lo = mid; else hi = mid; }
-        s_b0 = lo;
-    }
-    for (int i = tid; i < p.passes * kSortMaxRadix; i += kPreBlock) s_hist[i] = 0;
-    __syncthreads();
+    if (j0 >= V) return;                             // (CTA-uniform)
     const uint32_t j = j0 + tid;
-    if (j < V) {
-        uint32_t b = s_b0;
-        while (j >= __ldg(p.bucket_start + b + 1)) ++b;      // a 256-block spans few buckets (empty ones are skipped over)
-        const uint32_t off = __ldg(p.bucket_base + b) + __ldg(p.runoff + j);
+    const int cnt = (int)min((uint32_t)kPreBlock, V - j0);
+    for (int i = tid; i < p.passes * kSortMaxRadix; i += kPreBlock) s_hist[i] = 0;
+    if (tid < cnt) {
         const uint32_t g = p.order[j];
         const uint2 r = p.rects[g];
-        const uint32_t x0 = r.x & 0xffffu, w = (r.x >> 16) - x0, y0 = r.y & 0xffffu, h = (r.y >> 16) - y0;
-        for (uint32_t k = 0; k < h; ++k) {
-            const uint32_t key = ((y0 + k) << kRunRowShift) | (x0 << kRunX0Shift) | w;
-            p.rkeys[off + k] = key;
-            p.rvals[off + k] = g;
-            atomicAdd(&s_hist[(key >> p.shift0) & ((1u << p.bits0) - 1u)], 1u);
-            if (p.passes > 1) atomicAdd(&s_hist[kSortMaxRadix + ((key >> p.shift1) & ((1u << p.bits1) - 1u))], 1u);
-        }
+        s_id[tid] = g; s_x[tid] = ((r.x & 0xffffu) << kRunX0Shift) | ((r.x >> 16) - (r.x & 0xffffu)); s_y0[tid] = r.y & 0xffffu;
+        s_off[tid] = __ldg(p.runoff + j);
+    }
+    if (tid == 0) s_off[cnt] = __ldg(p.runoff + j0 + cnt);
+    __syncthreads();
+    const uint32_t base = s_off[0], total = s_off[cnt] - base;
+    for (uint32_t r = tid; r < total; r += kPreBlock) {
+        const uint32_t at = base + r;
+        int lo = 0, hi = cnt;                        // invariant: s_off[lo] <= at < s_off[hi]
+        while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (s_off[mid] <= at) lo = mid; else hi = mid; }
+        const uint32_t key = ((s_y0[lo] + (at - s_off[lo])) << kRunRowShift) | s_x[lo];
+        p.rkeys[at] = key;
+        p.rvals[at] = s_id[lo];
+        atomicAdd(&s_hist[(key >> p.shift0) & ((1u << p.bits0) - 1u)], 1u);
+        if (p.passes > 1) atomicAdd(&s_hist[kSortMaxRadix + ((key >> p.shift1) & ((1u << p.bits1) - 1u))], 1u);
     }
     __syncthreads();
     for (int i = tid; i < p.passes * kSortMaxRadix; i += kPreBlock) {
@@ -165,7 +168,7 @@ void launch_order_block_sums(int P, const uint32_t* n_dev, const uint32_t* order
 
 void launch_emit_runs(const GeomPtrs& g, long long V, uint32_t* rkeys, uint32_t* rvals, uint32_t* hist, const SortPlan& plan, cudaStream_t s) {
     EmitRunsParams p;
-    p.hdr = g.header; p.order = g.order; p.rects = g.rects; p.bucket_start = g.bucket_start; p.bucket_base = g.bucket_base; p.runoff = g.runoff;
+    p.hdr = g.header; p.order = g.order; p.rects = g.rects; p.runoff = g.runoff;
     p.rkeys = rkeys; p.rvals = rvals; p.hist = hist;
     p.passes = plan.passes;
     p.shift0 = plan.shift[0]; p.bits0 = plan.bits[0];
@@ -702,69 +705,60 @@ __global__ void __launch_bounds__(1024) tile_scan_kernel(uint32_t* __restrict__ 
 }
 
 // per chunk: write every run's Gaussian id into the lists of the tiles it covers, at its exact depth-order rank.
-// A chunk's 1024 runs form 32 warp-sized groups in run order; group q owns coverage plane q (bit = lane, word =
-// column).  One pass sets the bits (a run covers 1.7 columns on average: one shared atomic per covered column), one
-// pass per column turns the 32 popcounts into each group's slot base, one pass scatters -- two CTA barriers per chunk.
-// The chunk's place (row, run range) comes from one 16-byte record written by chunk_count_kernel and all runs are
-// loaded up front.  The kernel is bound by the L1/LSU pipe (ncu: 75 %; ~4 shared/global lane operations per pair), not
-// by DRAM (7 %).  Measured dead ends: toggle-and-prefix-XOR coverage, staging the pairs in shared memory for coalesced
-// list writes, flattening wide runs across the warp with a shuffle search -- all between 0.135 and 0.153 ms.
+// A chunk's 1024 runs form 32 warp-sized groups in run order; the coverage of column x is 32 words (word q = group q, bit =
+// lane = run q*32 + lane), stored COLUMN-MAJOR.  Phase 1: every run sets its bit in the words of the columns it covers
+// (shared atomicOr).  Phase 2: a WARP PER COLUMN decodes that column's 1024-bit map: lane q takes word q, a warp scan of
+// the popcounts gives its first slot, and the set bits are enumerated into consecutive list slots -- the lanes of a warp
+// write one contiguous stretch of one tile's list (a few sectors per store), where the round-1 kernel had every lane
+// scatter into a different tile (32 sectors per store instruction, 1 cycle each in the L1: that, not DRAM, was its limit).
+// No per-(group, column) offset table, no rank look-ups.
 constexpr int kExpandThreads = 256;
 constexpr int kExpandBatches = kRunChunk / kExpandThreads;       // runs per thread
-constexpr int kExpandPlanes = kRunChunk / 32;
+constexpr int kExpandPlanes = kRunChunk / 32;                    // words per column
+constexpr int kExpandStride = kExpandPlanes + 1;                 // odd stride: phase-1 atomics of neighbouring columns hit different banks
 
 __global__ void __launch_bounds__(kExpandThreads) expand_runs_kernel(const uint32_t* __restrict__ rkeys, const uint32_t* __restrict__ rvals,
                                                                      int tiles_x, const uint4* __restrict__ chunk_info,
                                                                      const uint32_t* __restrict__ chunk_counts,
                                                                      const uint32_t* __restrict__ tile_start, uint32_t* __restrict__ point_list) {
     extern __shared__ uint32_t s_mem[];
-    const int stride = tiles_x + 1;
-    uint32_t* s_base = s_mem;                                           // [tiles_x] first slot of this chunk in every column's list
-    uint32_t* s_bits = s_base + tiles_x;                                // [32][tiles_x + 1] coverage bits
-    unsigned short* s_rel = reinterpret_cast<unsigned short*>(s_bits + kExpandPlanes * stride);   // [32][tiles_x] group base - s_base
+    uint32_t* s_ids = s_mem;                                            // [kRunChunk] Gaussian id of run r
+    uint32_t* s_bits = s_ids + kRunChunk;                               // [tiles_x][kExpandStride] coverage words
     const uint4 info = __ldg(chunk_info + blockIdx.x);                  // (row, first run, end run, valid)
     if (info.w == 0u) return;
     const uint32_t row = info.x, r0 = info.y, r1 = info.z;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-    uint32_t keys[kExpandBatches], ids[kExpandBatches];
+    uint32_t keys[kExpandBatches];
 #pragma unroll
     for (int b = 0; b < kExpandBatches; ++b) {
         const uint32_t r = r0 + b * kExpandThreads + tid;
         keys[b] = (r < r1) ? __ldg(rkeys + r) : 0u;                     // width field 0: covers nothing
-        ids[b] = (r < r1) ? __ldg(rvals + r) : 0u;
+        s_ids[b * kExpandThreads + tid] = (r < r1) ? __ldg(rvals + r) : 0u;
     }
-    for (int x = tid; x < tiles_x; x += kExpandThreads)
-        s_base[x] = __ldg(tile_start + (size_t)row * tiles_x + x) + __ldg(chunk_counts + (size_t)blockIdx.x * tiles_x + x);
-    // a warp clears and fills its own planes (b * 8 + wid): no CTA barrier in between
+    for (int i = tid; i < tiles_x * kExpandStride; i += kExpandThreads) s_bits[i] = 0;
+    __syncthreads();
 #pragma unroll
     for (int b = 0; b < kExpandBatches; ++b) {
-        uint32_t* plane = s_bits + (b * 8 + wid) * stride;
-        for (int x = lane; x < tiles_x; x += 32) plane[x] = 0;
-    }
-    __syncwarp();
-#pragma unroll
-    for (int b = 0; b < kExpandBatches; ++b) {
-        uint32_t* plane = s_bits + (b * 8 + wid) * stride;
+        const int q = b * (kExpandThreads / 32) + wid;                  // group of run b*256 + tid
         const uint32_t x0 = (keys[b] >> kRunX0Shift) & kRunFieldMask, w = keys[b] & kRunFieldMask;
-        for (uint32_t i = 0; i < w; ++i) atomicOr(&plane[x0 + i], 1u << lane);
+        for (uint32_t i = 0; i < w; ++i) atomicOr(&s_bits[(x0 + i) * kExpandStride + q], 1u << lane);
     }
     __syncthreads();
-    for (int x = tid; x < tiles_x; x += kExpandThreads) {
-        uint32_t acc = 0;
-#pragma unroll 8
-        for (int q = 0; q < kExpandPlanes; ++q) { s_rel[q * tiles_x + x] = (unsigned short)acc; acc += __popc(s_bits[q * stride + x]); }
-    }
-    __syncthreads();
-    const uint32_t lt = (1u << lane) - 1u;
+    const uint32_t* cc = chunk_counts + (size_t)blockIdx.x * tiles_x;
+    const uint32_t* ts = tile_start + (size_t)row * tiles_x;
+    for (int x = wid; x < tiles_x; x += kExpandThreads / 32) {
+        uint32_t word = s_bits[x * kExpandStride + lane];
+        const uint32_t c = __popc(word);
+        uint32_t inc = c;
 #pragma unroll
-    for (int b = 0; b < kExpandBatches; ++b) {
-        const int q = b * 8 + wid;
-        const uint32_t* plane = s_bits + q * stride;
-        const unsigned short* rel = s_rel + q * tiles_x;
-        const uint32_t x0 = (keys[b] >> kRunX0Shift) & kRunFieldMask, w = keys[b] & kRunFieldMask, id = ids[b];
-        for (uint32_t i = 0; i < w; ++i) {
-            const uint32_t x = x0 + i;
-            point_list[s_base[x] + rel[x] + __popc(plane[x] & lt)] = id;
+        for (int o = 1; o < 32; o <<= 1) { const uint32_t u = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += u; }
+        if (__shfl_sync(0xffffffffu, inc, 31) == 0u) continue;          // nothing of this chunk in column x (warp-uniform)
+        uint32_t slot = __ldg(ts + x) + __ldg(cc + x) + inc - c;        // first list slot of this lane's runs
+        const uint32_t* ids = s_ids + lane * 32;
+        while (word) {
+            const int bpos = __ffs(word) - 1;
+            word &= word - 1u;
+            point_list[slot++] = ids[bpos];
         }
     }
 }
@@ -787,12 +781,12 @@ void launch_expand_runs(const BinPtrs& b, const uint32_t* rkeys_sorted, const ui
     }
     {
         ProfScope ps(prof_expand, s);
-        // [tiles_x] + 32 planes x [tiles_x + 1] u32 + 32 x [tiles_x] u16: 24 KB at 1080p, 200 KB at the 1023-column limit
-        const size_t smem = sizeof(uint32_t) * ((size_t)tiles_x + kExpandPlanes * (size_t)(tiles_x + 1)) + sizeof(unsigned short) * kExpandPlanes * (size_t)tiles_x;
+        // [1024] ids + [tiles_x][33] coverage words: 20 KB at 1080p, 139 KB at the 1023-column limit
+        const size_t smem = sizeof(uint32_t) * ((size_t)kRunChunk + (size_t)tiles_x * kExpandStride);
         static bool attr_done = false;
         if (!attr_done) {
             cudaFuncSetAttribute(expand_runs_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 (int)(sizeof(uint32_t) * (1023 + kExpandPlanes * 1024) + sizeof(unsigned short) * kExpandPlanes * 1023));
+                                 (int)(sizeof(uint32_t) * (kRunChunk + 1023 * kExpandStride)));
             attr_done = true;
         }
         expand_runs_kernel<<<grid, kExpandThreads, smem, s>>>(rkeys_sorted, rvals_sorted, tiles_x, b.chunk_info, b.chunk_counts, b.tile_start, b.vals);

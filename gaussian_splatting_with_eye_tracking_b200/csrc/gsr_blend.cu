@@ -284,6 +284,72 @@ __global__ void __launch_bounds__(kBlend2Threads) blend_fwd2_kernel(const FwdPar
     }
 }
 
+// ------------------------------------------------------------------------------------------------
+// measurement only: the ALGORITHMIC work of the blend stage ("pair-test" = one pixel x one list entry the
+// reference's loop examines, forward.cu:328-361; "hit" = a pair-test that passes both skips and is accumulated).  One
+// pixel per thread, no cull, no staging tricks: per pixel the number of entries examined before `done` (or the whole
+// list), the number accumulated, and n_contrib (what the backward walks, backward.cu:486-488).  Never on the frame path.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) blend_count_kernel(const FwdParams p, unsigned long long* __restrict__ totals) {
+    __shared__ float4 s_a[256];
+    __shared__ float2 s_b[256];
+    __shared__ unsigned long long s_tot[3];
+    const int tid = threadIdx.x;
+    if (tid < 3) s_tot[tid] = 0ull;
+    const uint32_t tile_y = blockIdx.y + (uint32_t)p.row0;
+    const uint32_t pix_x = blockIdx.x * 16 + (tid & 15), pix_y = tile_y * 16 + (tid >> 4);
+    const bool inside = pix_x < (uint32_t)p.W && pix_y < (uint32_t)p.H;
+    const float pxf = (float)pix_x, pyf = (float)pix_y;
+    const uint2 range = p.ranges[tile_y * p.tiles_x + blockIdx.x];
+    const int todo = (int)(range.y - range.x);
+    float T = 1.0f;
+    bool done = !inside;
+    uint32_t examined = 0, hits = 0, last = 0;
+    for (int base = 0; base < todo; base += 256) {
+        if (__syncthreads_count(done) == 256) break;
+        if (base + tid < todo) {
+            const uint32_t id = __ldg(p.point_list + range.x + base + tid);
+            const float2 xy = __ldg(p.means2D + id); const float4 co = __ldg(p.conic_opacity + id);
+            s_a[tid] = make_float4(xy.x, xy.y, co.x, co.y); s_b[tid] = make_float2(co.z, co.w);
+        }
+        __syncthreads();
+        const int cnt = min(256, todo - base);
+        for (int j = 0; !done && j < cnt; ++j) {
+            ++examined;
+            const float4 A = s_a[j]; const float2 B = s_b[j];
+            const float dx = __fadd_rn(A.x, -pxf), dy = __fadd_rn(A.y, -pyf);
+            const float power = blend_power(A.z, A.w, B.x, dx, dy);
+            if (power > 0.0f) continue;
+            const float alpha = fminf(0.99f, __fmul_rn(B.y, expf(power)));
+            if (alpha < kAlphaMin) continue;
+            const float test_T = __fmul_rn(T, __fadd_rn(1.f, -alpha));
+            if (test_T < 0.0001f) { done = true; continue; }
+            T = test_T; ++hits; last = (uint32_t)(base + j + 1);
+        }
+    }
+    __syncthreads();
+    if (inside) {
+        atomicAdd(&s_tot[0], (unsigned long long)examined);
+        atomicAdd(&s_tot[1], (unsigned long long)hits);
+        atomicAdd(&s_tot[2], (unsigned long long)last);
+    }
+    __syncthreads();
+    if (tid < 3 && s_tot[tid]) atomicAdd(&totals[tid], s_tot[tid]);
+}
+
+void launch_blend_count(const BlendArgs& a, unsigned long long* totals, cudaStream_t s) {
+    FwdParams p;
+    p.W = a.W; p.H = a.H; p.tiles_x = (a.W + 15) / 16;
+    p.ranges = a.ranges; p.point_list = a.point_list; p.means2D = a.means2D; p.conic_opacity = a.conic_opacity;
+    p.colors = a.colors; p.bg = a.bg; p.final_T = a.final_T; p.n_contrib = a.n_contrib; p.out_color = a.out_color;
+    const int tiles_y = (a.H + 15) / 16;
+    const int r0 = a.row1 > 0 ? a.row0 : 0, r1 = a.row1 > 0 ? a.row1 : tiles_y;
+    if (r1 <= r0) return;
+    p.row0 = r0;
+    blend_count_kernel<<<dim3((a.W + 15) / 16, r1 - r0, 1), 256, 0, s>>>(p, totals);
+    count_launch();
+}
+
 static int g_blend_variant = 0;
 void set_blend_variant(int v) { g_blend_variant = v; }
 

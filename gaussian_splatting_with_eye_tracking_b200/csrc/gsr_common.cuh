@@ -42,38 +42,35 @@ struct GeomHeader {      // lives at the start of the (aligned) geometry buffer,
     uint32_t sort_error;     // bit 0: radix-sort watchdog; bit 8: a Gaussian was culled although prefiltered
     uint32_t num_runs;       // = sum over visible Gaussians of the tile rows their rect spans ((Gaussian, row) runs)
     uint32_t num_visible;    // Gaussians with tiles_touched > 0: only these are depth-sorted
-    // ---- bucketed depth sort (gsr_depthsort.cu).  Words [6..15] are accumulated with atomics by preprocess_fwd_kernel and
-    // the sort kernels, so the first 64 bytes of the header are cleared (one 256-byte memset node) before every frame.
-    uint32_t compact_cursor; // next free slot of the unordered (depth key, id) compaction == num_visible when preprocess ends
-    uint32_t key_max;        // largest depth key (float bits) among the visible Gaussians
-    uint32_t key_min_inv;    // ~smallest depth key (kept inverted so that zero-initialisation + atomicMax works)
-    uint32_t done_pre;       // CTAs of preprocess_fwd_kernel that have finished (last one finalises header + mailbox)
-    uint32_t done_hist;      // same for bucket_hist_kernel (last one plans the buckets)
-    uint32_t done_sort;      // same for bucket_sort_kernel (last one scans the per-bucket run counts)
+    // ---- depth sort (gsr_depthsort.cu)
+    uint32_t done_hist;      // CTAs of bin_hist_kernel that have finished (the last one scans the histograms, posts the totals)
+    uint32_t key_min;        // smallest depth key (float bits) among the visible Gaussians
     uint32_t shift;          // bin = (key - key_min) >> shift
-    uint32_t num_buckets;
-    uint32_t sort_mode;      // 1 = bucket plan valid; 2 = a bin exceeds the bucket capacity -> host runs the onesweep fallback
-    uint32_t bucket_quantum; // Cq: bucket b holds the bins whose exclusive prefix lies in [b*Cq, (b+1)*Cq)
-    uint32_t pad[48];
+    uint32_t sort_mode;      // 1 = bins valid; 2 = a bin exceeds kBinCap -> the host runs the onesweep fallback; 3 = fallback done
+    uint32_t max_bin;        // records in the fullest bin (diagnostics)
+    uint32_t pad[53];
 };
 static_assert(sizeof(GeomHeader) == 256, "header is one alignment unit");
 
-// ---------------------------------------------------------------- bucketed depth sort sizing
-constexpr int kBucketThreads = 512, kBucketItems = 12;
-constexpr int kBucketCap = kBucketThreads * kBucketItems;     // 6144 (key, id) pairs sorted by one CTA in shared memory
-constexpr int kBucketMinQuantum = 1024;                       // a bin larger than kBucketCap - 1024 sends the frame to the fallback
-__host__ __device__ inline int depth_bins(int P) {            // histogram resolution: ~128 Gaussians per bin, 1 Ki .. 64 Ki bins
+// Frame statistics accumulated by preprocess_fwd_kernel with atomics.  Same-address global atomics serialise (~30 ns each
+// on B200), so the 11 719 CTAs of a 3 M-Gaussian frame are spread over kStatSlots slots, one 128-byte line each.
+constexpr int kStatSlots = 128;
+struct FrameStatSlot { uint32_t key_max, key_min_inv /* ~min, so that 0-init + atomicMax works */, num_rendered, flags, pad[28]; };
+static_assert(sizeof(FrameStatSlot) == 128, "one line per slot");
+
+// ---------------------------------------------------------------- depth sort sizing
+constexpr int kBinCap = 512;                                  // records one warp orders by all-pairs ranking; fuller bin -> fallback
+__host__ __device__ inline int depth_bins(int P) {            // ~32 Gaussians of the scene per bin, 1 Ki .. 64 Ki bins
     int n = 1024;
-    while (n < 65536 && n * 128 < P) n <<= 1;
+    while (n < 65536 && n * 32 < P) n <<= 1;
     return n;
 }
-__host__ __device__ inline int max_buckets(int P) { return P / kBucketMinQuantum + 8; }
 
 struct GeomLayout {
     size_t header, depths, clamped, radii, means2D, cov3D, conic_opacity, rgb, tiles_touched, rects,
            block_sums, block_sums_r, block_sums_v, block_offsets, dkeys_a, dkeys_b, order_tmp, order, oblock_sums, oblock_offsets, sort_temp,
-           bids, runoff, bhist, bucket_start, bucket_cursor, bucket_runs, bucket_base, total;
-    int nblocks, nbins, maxb;
+           stat_slots, brec, runoff, bin_cur, bin_runs, total;
+    int nblocks, nbins;
     __host__ __device__ explicit GeomLayout(int P) {
         nblocks = (P + kPreBlock - 1) / kPreBlock;
         size_t o = 0;
@@ -99,16 +96,14 @@ struct GeomLayout {
         oblock_sums = o;   o = align_up(o + sizeof(uint32_t) * (size_t)(nblocks + 1));
         oblock_offsets = o; o = align_up(o + sizeof(uint32_t) * (size_t)(nblocks + 1));
         sort_temp = o;     o = align_up(o + sort_temp_bytes(P));
-        // bucketed depth sort: unordered compaction (dkeys_a, order_tmp) -> bucket-partitioned (dkeys_b, bids) -> order, runoff
-        nbins = depth_bins(P); maxb = max_buckets(P);
-        bids = o;          o = align_up(o + sizeof(uint32_t) * (size_t)P);
-        runoff = o;        o = align_up(o + sizeof(uint32_t) * (size_t)P);
-        // bhist .. bucket_cursor are contiguous: cleared on the side by preprocess_fwd_kernel (zero_ptr)
-        bhist = o;         o = align_up(o + sizeof(uint32_t) * (size_t)nbins);
-        bucket_cursor = o; o = align_up(o + sizeof(uint32_t) * (size_t)(maxb + 1));
-        bucket_start = o;  o = align_up(o + sizeof(uint32_t) * (size_t)(maxb + 1));
-        bucket_runs = o;   o = align_up(o + sizeof(uint32_t) * (size_t)(maxb + 1));
-        bucket_base = o;   o = align_up(o + sizeof(uint32_t) * (size_t)(maxb + 1));
+        // depth sort: per-block compaction (dkeys_a = keys, order_tmp = ids, dkeys_b = tile rows) -> brec (binned records)
+        // -> order, runoff.  stat_slots are cleared by a memset node, bin_cur / bin_runs on the side by preprocess_fwd_kernel.
+        nbins = depth_bins(P);
+        stat_slots = o;    o = align_up(o + sizeof(FrameStatSlot) * kStatSlots);
+        brec = o;          o = align_up(o + sizeof(uint4) * (size_t)P);
+        runoff = o;        o = align_up(o + sizeof(uint32_t) * ((size_t)P + 1));
+        bin_cur = o;       o = align_up(o + sizeof(uint32_t) * (size_t)nbins);
+        bin_runs = o;      o = align_up(o + sizeof(uint32_t) * (size_t)nbins);
         total = o;
     }
 };
@@ -119,8 +114,8 @@ struct GeomPtrs {
     float4* conic_opacity; float* rgb; uint32_t* tiles_touched; uint2* rects; uint32_t* block_sums; uint32_t* block_sums_r; uint32_t* block_sums_v;
     uint32_t* block_offsets;
     uint32_t *dkeys_a, *dkeys_b, *order_tmp, *order, *oblock_sums, *oblock_offsets; void* sort_temp; size_t sort_temp_bytes;
-    uint32_t *bids, *runoff, *bhist, *bucket_start, *bucket_cursor, *bucket_runs, *bucket_base; size_t bucket_zero_bytes;
-    int nblocks, nbins, maxb;
+    FrameStatSlot* stat_slots; uint4* brec; uint32_t *runoff, *bin_cur, *bin_runs; size_t bin_zero_bytes;
+    int nblocks, nbins;
 };
 
 inline char* aligned_base(const void* p) { return (char*)align_up((size_t)p); }
@@ -147,11 +142,10 @@ inline GeomPtrs geom_ptrs(const void* buf, int P) {
     g.order_tmp = (uint32_t*)(b + L.order_tmp); g.order = (uint32_t*)(b + L.order);
     g.oblock_sums = (uint32_t*)(b + L.oblock_sums); g.oblock_offsets = (uint32_t*)(b + L.oblock_offsets);
     g.sort_temp = (void*)(b + L.sort_temp); g.sort_temp_bytes = sort_temp_bytes(P);
-    g.bids = (uint32_t*)(b + L.bids); g.runoff = (uint32_t*)(b + L.runoff); g.bhist = (uint32_t*)(b + L.bhist);
-    g.bucket_start = (uint32_t*)(b + L.bucket_start); g.bucket_cursor = (uint32_t*)(b + L.bucket_cursor);
-    g.bucket_runs = (uint32_t*)(b + L.bucket_runs); g.bucket_base = (uint32_t*)(b + L.bucket_base);
-    g.bucket_zero_bytes = L.bucket_start - L.bhist;       // bhist + bucket_cursor (256-byte aligned pieces)
-    g.nblocks = L.nblocks; g.nbins = L.nbins; g.maxb = L.maxb;
+    g.stat_slots = (FrameStatSlot*)(b + L.stat_slots); g.brec = (uint4*)(b + L.brec); g.runoff = (uint32_t*)(b + L.runoff);
+    g.bin_cur = (uint32_t*)(b + L.bin_cur); g.bin_runs = (uint32_t*)(b + L.bin_runs);
+    g.bin_zero_bytes = L.total - L.bin_cur;               // bin_cur + bin_runs, contiguous, 256-byte aligned pieces
+    g.nblocks = L.nblocks; g.nbins = L.nbins;
     return g;
 }
 
@@ -282,17 +276,16 @@ struct PreprocessArgs {
     int* radii;            // output (caller's or internal)
     bool prefiltered;
     int band_row0, band_row1;   // tile-row band [row0,row1); 0,0 = whole frame
-    uint32_t* mailbox;     // device alias of mapped pinned host words the last CTA posts the frame totals to; may be null
     void* zero_ptr; size_t zero_bytes;   // 16 B aligned scratch the kernel clears on the side (the depth sort's histograms and
                                          // look-back words), so that the frame needs no memset operation; may be null / 0
 };
 void launch_preprocess(const PreprocessArgs& a, const GeomPtrs& g, cudaStream_t s);
 void launch_block_scan(const GeomPtrs& g, int P, uint32_t* mailbox_dev, cudaStream_t s);
-// bucketed depth sort (gsr_depthsort.cu): histogram + bucket plan, scatter, per-bucket shared-memory sort (+ run offsets)
-void launch_bucket_hist(const GeomPtrs& g, int P, uint32_t* mailbox_dev, cudaStream_t s);
-void launch_bucket_scatter(const GeomPtrs& g, int P, cudaStream_t s);
-void launch_bucket_sort(const GeomPtrs& g, int P, bool presorted, cudaStream_t s);
-void launch_uniform_buckets(const GeomPtrs& g, int P, cudaStream_t s);
+// depth sort (gsr_depthsort.cu): bin histogram + scans, scatter into the bins, exact order inside every bin (+ run offsets)
+void launch_bin_hist(const GeomPtrs& g, int P, uint32_t* mailbox_dev, cudaStream_t s);
+void launch_bin_scatter(const GeomPtrs& g, int P, cudaStream_t s);
+void launch_bin_sort(const GeomPtrs& g, int P, cudaStream_t s);
+void launch_runoff_from_blocks(const GeomPtrs& g, int P, cudaStream_t s);      // fallback: run offsets of an onesweep-sorted order
 void launch_clamped_rgb(int P, const int* radii, const float* scratch, const unsigned char* clamped, bool colors_from_sh, float* out, cudaStream_t s);
 int launch_sh_grad_from_views(int P, int D, int M, const float* means3D, int K, const float* cams, const float* g_all,
                               const uint32_t* meta, int meta_stride, int cap, float* dL_dsh, cudaStream_t s);   // meta == nullptr: dense [K,P,3]
@@ -349,6 +342,7 @@ struct BlendArgs {
     float* final_T; uint32_t* n_contrib; float* out_color;
 };
 void launch_blend_forward(const BlendArgs& a, cudaStream_t s);
+void launch_blend_count(const BlendArgs& a, unsigned long long* totals /* device, [3], caller-zeroed */, cudaStream_t s);
 
 struct AmrBlendArgs {
     BlendArgs b;

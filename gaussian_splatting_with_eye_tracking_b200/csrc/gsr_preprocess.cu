@@ -51,9 +51,10 @@ struct PreFwdParams {
                                             // prefiltered" (the reference would __trap)
     uint4* zero_ptr; size_t zero_n16;       // scratch cleared on the side (grid-stride), see PreprocessArgs
     uint4* zero_ptr2; size_t zero_n16_2;
-    uint32_t* __restrict__ ckeys;           // unordered compaction of the visible Gaussians: depth key (float bits) ...
-    uint32_t* __restrict__ cids;            // ... and index; slots are reserved per CTA with one atomic on header->compact_cursor
-    uint32_t* mailbox;                      // mapped pinned host words the LAST CTA posts the frame totals to (may be null)
+    uint32_t* __restrict__ ckeys;           // per-block compaction of the visible Gaussians: depth key (float bits) ...
+    uint32_t* __restrict__ cids;            // ... index ...
+    uint32_t* __restrict__ crows;           // ... and number of tile rows the rect spans (= runs the Gaussian emits)
+    FrameStatSlot* stat_slots;              // [kStatSlots] key range, pair total, prefiltered-trap flag
     GeomHeader* header;
     int prefiltered;
     int band_row0, band_row1;
@@ -211,8 +212,8 @@ __device__ __forceinline__ float3 cov2d_from_cov3d(float tx, float ty, float tz,
 
 __global__ void __launch_bounds__(kPreBlock, 4) preprocess_fwd_kernel(const PreFwdParams p) {
     __shared__ float sV[16], sPm[16], sCam[3];
-    __shared__ uint32_t s_warp_sum[kPreBlock / 32], s_warp_sum_r[kPreBlock / 32], s_warp_sum_v[kPreBlock / 32];
-    __shared__ uint32_t s_warp_kmx[kPreBlock / 32], s_warp_kmn[kPreBlock / 32], s_base;
+    __shared__ uint32_t s_warp_sum[kPreBlock / 32], s_warp_sum_v[kPreBlock / 32];
+    __shared__ uint32_t s_warp_kmx[kPreBlock / 32], s_warp_kmn[kPreBlock / 32];
     const int tid = threadIdx.x;
     if (tid < 16) { sV[tid] = p.viewmatrix[tid]; sPm[tid] = p.projmatrix[tid]; }
     if (tid < 3) sCam[tid] = p.cam_pos[tid];
@@ -307,64 +308,36 @@ __global__ void __launch_bounds__(kPreBlock, 4) preprocess_fwd_kernel(const PreF
         rows = y1 - y0;
     }
 
-    // ---- CTA totals, slot reservation for the compaction, frame totals.
-    // There is no scan kernel any more: every CTA reserves the slots of its visible Gaussians with ONE atomic on
-    // header->compact_cursor (the compaction is unordered -- the bucketed depth sort orders by (depth key, index), so the
-    // arrival order of the CTAs does not matter), adds its pair / run counts and key range to the header, and the CTA
-    // that finishes last writes the totals where the host reads them (mapped pinned memory: no D2H copy).
-    uint32_t v = touched, vr = rows;
+    // ---- block-local compaction + frame statistics.
+    // There is no scan kernel and no global cursor: the visible Gaussians of this 256-block go to the FRONT of the block's
+    // own segment of (ckeys, cids, crows) and the block's count to block_sums_v -- the depth sort (gsr_depthsort.cu) walks
+    // blocks, not a dense array.  The key range and the pair total go to one of kStatSlots statistics lines (same-address
+    // atomics serialise at ~30 ns each: one hot word for 11 719 CTAs would cost more than the kernel itself).
+    uint32_t v = touched;
     const uint32_t vis_mask = __ballot_sync(0xffffffffu, touched != 0);
     uint32_t kmx = touched ? key : 0u, kmn = touched ? ~key : 0u;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
-        v += __shfl_xor_sync(0xffffffffu, v, o); vr += __shfl_xor_sync(0xffffffffu, vr, o);
+        v += __shfl_xor_sync(0xffffffffu, v, o);
         kmx = max(kmx, __shfl_xor_sync(0xffffffffu, kmx, o)); kmn = max(kmn, __shfl_xor_sync(0xffffffffu, kmn, o));
     }
-    if ((tid & 31) == 0) {
-        s_warp_sum[tid >> 5] = v; s_warp_sum_r[tid >> 5] = vr; s_warp_sum_v[tid >> 5] = __popc(vis_mask);
-        s_warp_kmx[tid >> 5] = kmx; s_warp_kmn[tid >> 5] = kmn;
-    }
+    if ((tid & 31) == 0) { s_warp_sum[tid >> 5] = v; s_warp_sum_v[tid >> 5] = __popc(vis_mask); s_warp_kmx[tid >> 5] = kmx; s_warp_kmn[tid >> 5] = kmn; }
     const int trap_any = __syncthreads_or(trapped);
-    if (tid == 0) {
-        uint32_t s = 0, sr = 0, sv = 0, mx = 0, mn = 0;
-#pragma unroll
-        for (int w = 0; w < kPreBlock / 32; ++w) {
-            s += s_warp_sum[w]; sr += s_warp_sum_r[w]; sv += s_warp_sum_v[w];
-            mx = max(mx, s_warp_kmx[w]); mn = max(mn, s_warp_kmn[w]);
-        }
-        p.block_sums_v[blockIdx.x] = sv;               // kept for the onesweep fallback's ordered compaction
-        uint32_t base = 0;
-        if (sv) {
-            base = atomicAdd(&p.header->compact_cursor, sv);
-            atomicAdd(&p.header->num_rendered, s);
-            atomicAdd(&p.header->num_runs, sr);
-            atomicMax(&p.header->key_max, mx);
-            atomicMax(&p.header->key_min_inv, mn);
-        }
-        if (trap_any) atomicOr(&p.header->sort_error, 0x100u);
-        s_base = base;
-    }
-    __syncthreads();
     if (touched) {
-        uint32_t pos = s_base + __popc(vis_mask & ((1u << (tid & 31)) - 1u));
+        uint32_t pos = __popc(vis_mask & ((1u << (tid & 31)) - 1u));
 #pragma unroll
         for (int w = 0; w < kPreBlock / 32; ++w) pos += (w < (tid >> 5)) ? s_warp_sum_v[w] : 0u;
-        p.ckeys[pos] = key;
-        p.cids[pos] = (uint32_t)idx;
+        const size_t at = (size_t)blockIdx.x * kPreBlock + pos;
+        p.ckeys[at] = key; p.cids[at] = (uint32_t)idx; p.crows[at] = rows;
     }
     if (tid == 0) {
-        __threadfence();
-        const uint32_t ticket = atomicAdd(&p.header->done_pre, 1u);
-        if (ticket == gridDim.x - 1) {                 // every other CTA's header atomics are visible now
-            __threadfence();
-            const uint32_t nvis = atomicAdd(&p.header->compact_cursor, 0u), nren = atomicAdd(&p.header->num_rendered, 0u),
-                           nrun = atomicAdd(&p.header->num_runs, 0u), err = atomicAdd(&p.header->sort_error, 0u);
-            p.header->magic = kGeomMagic; p.header->P = (uint32_t)p.P; p.header->num_visible = nvis;
-            if (p.mailbox) {   // posted PCIe writes stay ordered; the host reads after an event recorded behind a later kernel
-                volatile uint32_t* m = p.mailbox;
-                m[0] = kGeomMagic; m[1] = (uint32_t)p.P; m[2] = nren; m[3] = err; m[4] = nrun; m[5] = nvis;
-            }
-        }
+        uint32_t s = 0, sv = 0, mx = 0, mn = 0;
+#pragma unroll
+        for (int w = 0; w < kPreBlock / 32; ++w) { s += s_warp_sum[w]; sv += s_warp_sum_v[w]; mx = max(mx, s_warp_kmx[w]); mn = max(mn, s_warp_kmn[w]); }
+        p.block_sums_v[blockIdx.x] = sv;
+        FrameStatSlot* slot = p.stat_slots + (blockIdx.x & (kStatSlots - 1));
+        if (sv) { atomicMax(&slot->key_max, mx); atomicMax(&slot->key_min_inv, mn); atomicAdd(&slot->num_rendered, s); }
+        if (trap_any) atomicOr(&slot->flags, 1u);
     }
 }
 
@@ -383,8 +356,8 @@ void launch_preprocess(const PreprocessArgs& a, const GeomPtrs& g, cudaStream_t 
     p.block_sums = g.block_sums; p.header = g.header; p.prefiltered = a.prefiltered ? 1 : 0;
     p.band_row0 = a.band_row0; p.band_row1 = a.band_row1;
     p.zero_ptr = reinterpret_cast<uint4*>(a.zero_ptr); p.zero_n16 = a.zero_ptr ? a.zero_bytes / 16 : 0;
-    p.zero_ptr2 = reinterpret_cast<uint4*>(g.bhist); p.zero_n16_2 = g.bucket_zero_bytes / 16;
-    p.ckeys = g.dkeys_a; p.cids = g.order_tmp; p.mailbox = a.mailbox;
+    p.zero_ptr2 = reinterpret_cast<uint4*>(g.bin_cur); p.zero_n16_2 = g.bin_zero_bytes / 16;
+    p.ckeys = g.dkeys_a; p.cids = g.order_tmp; p.crows = g.dkeys_b; p.stat_slots = g.stat_slots;
     preprocess_fwd_kernel<<<g.nblocks, kPreBlock, 0, s>>>(p);
     count_launch();
 }

@@ -318,6 +318,15 @@ GSR_API int gsr_peer_allreduce_sum_mc(void* const* peer_bases, void* multicast_b
 GSR_API int gsr_peer_allreduce_sum(void* const* peer_bases, size_t data_offset, long long n_floats, size_t flag_offset, int world,
                                    int rank, unsigned epoch, void* stream);
 
+/* ---- measurement: algorithmic work of the blend stage of a frame built by gsr_forward.
+ * totals_dev[0] = pair-tests of the forward  (sum over pixels of the list entries the reference's loop examines before the
+ *                 pixel is done, cuda_rasterizer/forward.cu:328-361),
+ * totals_dev[1] = hits (pair-tests that pass both skips and are accumulated; what the backward differentiates),
+ * totals_dev[2] = sum over pixels of n_contrib (entries the backward walks, backward.cu:486-488).
+ * One extra kernel, one pixel per thread, no culling; never part of a frame.  totals_dev: 3 x u64 in device memory. */
+GSR_API int gsr_blend_stats(int P, int W, int H, const void* geom_buffer, const void* binning_buffer, const void* image_buffer,
+                            unsigned long long* totals_dev, void* stream);
+
 /* ---- tuning knobs (results never depend on them, with ONE exception: GSR_OPT_PEER_CTAS_PER_SM values >= 0x100 put the
  * unicast peer kernel into a link-diagnostic mode -- 0x1xx = remote loads only, 0x2xx = remote stores only -- that does NOT
  * compute the sum; tools/peer_diag.py uses it to time the two directions and nothing else may) ---- */

@@ -172,8 +172,24 @@ def test_full_size_backward_vs_reference_cuda(name, cam_index, cuda_device):
     ours = common.run_ours(sc, cam, dpix)["grads"]
     ours = {k: v.clone() for k, v in ours.items()}
     torch.cuda.empty_cache()
-    ref = common.run_reference(sc, cam, dpix)["grads"]
-    common.assert_grads_close(ours, ref, floor_factor=common.GRAD_FLOOR_REF)
+    ref = {k: v.clone() for k, v in common.run_reference(sc, cam, dpix)["grads"].items()}
+    torch.cuda.empty_cache()
+    ref2 = common.run_reference(sc, cam, dpix)["grads"]
+    # The reference accumulates every Gaussian's gradient with float atomicAdd in scheduling order
+    # (cuda_rasterizer/backward.cu:523-554): at this size its OWN two runs differ by more than the small-scene floor of
+    # 1e-5 |g|max.  Bar: 1e-3 relative + max(1e-5 |g|max, 4 x the reference's own run-to-run spread of that tensor).
+    for k in ["dL_dmeans2D", "dL_dopacity", "dL_dmeans3D", "dL_dcov3D", "dL_dsh", "dL_dscales", "dL_drotations", "dL_dcolors"]:
+        a, b, b2 = A(ours[k]).astype(np.float64), A(ref[k]).astype(np.float64), A(ref2[k]).astype(np.float64)
+        a = a.reshape(b.shape)
+        gmax = max(np.abs(a).max(initial=0.0), np.abs(b).max(initial=0.0))
+        spread = np.abs(b - b2).max(initial=0.0)
+        floor = max(common.GRAD_FLOOR_REF * gmax, 4.0 * spread) + 1e-12
+        err = np.abs(a - b) - common.GRAD_RTOL * np.maximum(np.abs(a), np.abs(b)) - floor
+        assert err.max(initial=-1.0) <= 0, (f"{k}: max abs diff {np.abs(a - b).max()} with |g|max {gmax}, reference run-to-run spread {spread}")
+        # and in aggregate: relative L2 distance far inside the 1e-3 bar
+        denom = np.linalg.norm(b.ravel())
+        if denom > 0:
+            assert np.linalg.norm((a - b).ravel()) / denom <= 1e-4, f"{k}: relative L2 {np.linalg.norm((a - b).ravel()) / denom}"
 
 
 @needs_ref_amr
