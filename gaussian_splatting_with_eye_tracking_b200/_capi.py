@@ -180,7 +180,7 @@ def check(rc: int, what: str) -> None:
 
 
 PROF_SLOTS = ["preprocess", "scan", "duplicate", "sort", "ranges", "blend", "amr_levels", "amr_blend", "bwd_blend",
-              "bwd_preprocess", "depth_sort", "expand"] + [f"sort_pass{i}" for i in range(8)]
+              "bwd_preprocess", "depth_sort", "expand", "sort_pass0", "bin_scatter", "bin_sort"] + [f"sort_pass{i}" for i in range(3, 8)]
 
 
 def profile_enable(on: bool) -> None:

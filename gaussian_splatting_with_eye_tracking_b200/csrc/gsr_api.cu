@@ -8,6 +8,8 @@
 #include <cstring>
 #include <mutex>
 #include <vector>
+#include <cstdlib>
+#include <nvtx3/nvToolsExt.h>     // header-only NVTX 3: a no-op unless a tool (Nsight Systems / Compute) is attached
 
 namespace gsr {
 
@@ -47,12 +49,27 @@ static cudaEvent_t prof_event() {
     if (!g_prof_pool.empty()) { cudaEvent_t e = g_prof_pool.back(); g_prof_pool.pop_back(); return e; }
     cudaEvent_t e = nullptr; cudaEventCreate(&e); return e;
 }
+// NVTX ranges per stage: off by default, on with GSR_NVTX=1 in the environment or
+// gsr_set_option(GSR_OPT_NVTX, 1).  Range names are the profile slot names.
+static int g_nvtx_on = -1;
+static const char* const kSlotNames[GSR_PROF_SLOTS] = {
+    "gsr:preprocess", "gsr:depth_histogram", "gsr:emit_runs", "gsr:row_partition", "gsr:tile_ranges", "gsr:blend_fwd", "gsr:amr_levels",
+    "gsr:amr_blend", "gsr:blend_bwd", "gsr:preprocess_bwd", "gsr:depth_sort", "gsr:expand_runs", "gsr:sort_pass0", "gsr:bin_scatter",
+    "gsr:bin_sort", "gsr:sort_pass3", "gsr:sort_pass4", "gsr:sort_pass5", "gsr:sort_pass6", "gsr:sort_pass7"};
+static bool nvtx_on() {
+    if (g_nvtx_on < 0) { const char* e = getenv("GSR_NVTX"); g_nvtx_on = (e && e[0] && e[0] != '0') ? 1 : 0; }
+    return g_nvtx_on == 1;
+}
+void set_nvtx(int v) { g_nvtx_on = v ? 1 : 0; }
+
 void prof_begin(int slot, cudaStream_t s) {
+    if (slot >= 0 && slot < GSR_PROF_SLOTS && nvtx_on()) nvtxRangePushA(kSlotNames[slot]);
     if (!g_prof_on || slot < 0) return;
     std::lock_guard<std::mutex> lk(g_prof_mu);
     cudaEvent_t e = prof_event(); cudaEventRecord(e, s); g_prof_open[slot] = e;
 }
 void prof_end(int slot, cudaStream_t s) {
+    if (slot >= 0 && slot < GSR_PROF_SLOTS && nvtx_on()) nvtxRangePop();
     if (!g_prof_on || slot < 0) return;
     std::lock_guard<std::mutex> lk(g_prof_mu);
     if (!g_prof_open[slot]) return;
@@ -324,6 +341,7 @@ const char* gsr_last_error(void) { return g_err; }
 int gsr_set_option(int option, int value) {
     if (option == GSR_OPT_SORT_VARIANT && value >= 0 && value <= 5) { set_sort_variant(value); return GSR_OK; }
     if (option == GSR_OPT_BLEND_VARIANT && value >= 0 && value <= 1) { set_blend_variant(value); return GSR_OK; }
+    if (option == GSR_OPT_NVTX && (value == 0 || value == 1)) { set_nvtx(value); return GSR_OK; }
     if (option == GSR_OPT_FAKE_SORT_ERROR && (value == 0 || value == 1)) { set_fake_sort_error(value); return GSR_OK; }
     if (option == GSR_OPT_FORCE_SORT_FALLBACK && (value == 0 || value == 1)) { g_force_sort_fallback = value; return GSR_OK; }
     if (option == GSR_OPT_PEER_CTAS_PER_SM && value >= 0 && (value & 0xff) <= 32 && value < 0x300) { set_peer_ctas_per_sm(value); return GSR_OK; }

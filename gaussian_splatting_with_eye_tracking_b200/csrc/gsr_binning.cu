@@ -96,7 +96,7 @@ __global__ void __launch_bounds__(kPreBlock) order_block_sums_kernel(const uint3
 struct EmitRunsParams {
     const GeomHeader* __restrict__ hdr;          // num_visible
     const uint32_t* __restrict__ order;          // depth-sorted Gaussian ids
-    const uint2* __restrict__ rects;
+    const uint2* __restrict__ srect;             // [num_visible] ((x0 << 10) | width, y0) of every sorted position
     const uint32_t* __restrict__ runoff;         // [num_visible + 1] first run of every sorted position (exclusive prefix of the tile rows)
     uint32_t* __restrict__ rkeys;                // out: (row << 20) | (x0 << 10) | w
     uint32_t* __restrict__ rvals;                // out: Gaussian id
@@ -121,9 +121,8 @@ __global__ void __launch_bounds__(kPreBlock) emit_runs_kernel(const EmitRunsPara
     const int cnt = (int)min((uint32_t)kPreBlock, V - j0);
     for (int i = tid; i < p.passes * kSortMaxRadix; i += kPreBlock) s_hist[i] = 0;
     if (tid < cnt) {
-        const uint32_t g = p.order[j];
-        const uint2 r = p.rects[g];
-        s_id[tid] = g; s_x[tid] = ((r.x & 0xffffu) << kRunX0Shift) | ((r.x >> 16) - (r.x & 0xffffu)); s_y0[tid] = r.y & 0xffffu;
+        const uint2 r = __ldg(p.srect + j);
+        s_id[tid] = __ldg(p.order + j); s_x[tid] = r.x; s_y0[tid] = r.y;
         s_off[tid] = __ldg(p.runoff + j);
     }
     if (tid == 0) s_off[cnt] = __ldg(p.runoff + j0 + cnt);
@@ -168,7 +167,7 @@ void launch_order_block_sums(int P, const uint32_t* n_dev, const uint32_t* order
 
 void launch_emit_runs(const GeomPtrs& g, long long V, uint32_t* rkeys, uint32_t* rvals, uint32_t* hist, const SortPlan& plan, cudaStream_t s) {
     EmitRunsParams p;
-    p.hdr = g.header; p.order = g.order; p.rects = g.rects; p.runoff = g.runoff;
+    p.hdr = g.header; p.order = g.order; p.srect = g.srect; p.runoff = g.runoff;
     p.rkeys = rkeys; p.rvals = rvals; p.hist = hist;
     p.passes = plan.passes;
     p.shift0 = plan.shift[0]; p.bits0 = plan.bits[0];

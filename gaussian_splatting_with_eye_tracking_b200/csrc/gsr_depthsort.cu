@@ -76,15 +76,22 @@ __global__ void __launch_bounds__(kHistThreads) bin_hist_kernel(GeomHeader* hdr,
     for (int w = 0; w < kStatSlots / 32; ++w) { tot_pairs += s_c[w]; tot_trap |= s_d[w]; }
 
     // ---- two REDs per visible Gaussian.  Four 256-blocks per iteration; a block's records sit at the front of its segment.
+    // The next block's count is fetched before the current block's records are touched (the loop is a chain of dependent
+    // L2 round trips otherwise).
     const int sub = tid >> 8, t = tid & 255;
-    for (int b = (int)blockIdx.x * 4 + sub; b < nblocks; b += (int)gridDim.x * 4) {
-        const uint32_t cnt = __ldg(block_vis + b);
+    const int bstep = (int)gridDim.x * 4;
+    int b = (int)blockIdx.x * 4 + sub;
+    uint32_t cnt = b < nblocks ? __ldg(block_vis + b) : 0u;
+    while (b < nblocks) {
+        const int bn = b + bstep;
+        const uint32_t cnt_next = bn < nblocks ? __ldg(block_vis + bn) : 0u;
         if ((uint32_t)t < cnt) {
             const size_t i = (size_t)b * kPreBlock + t;
             const uint32_t bin = (__ldg(ckeys + i) - kmin) >> shift;
             atomicAdd(&bin_cur[bin], 1u);
-            atomicAdd(&bin_runs[bin], __ldg(crows + i));
+            atomicAdd(&bin_runs[bin], __ldg(crows + i) & 0xffffu);
         }
+        b = bn; cnt = cnt_next;
     }
     __syncthreads();
     if (tid == 0) { __threadfence(); s_last = (atomicAdd(&hdr->done_hist, 1u) == gridDim.x - 1) ? 1u : 0u; }
@@ -93,11 +100,26 @@ __global__ void __launch_bounds__(kHistThreads) bin_hist_kernel(GeomHeader* hdr,
     __threadfence();
 
     // ---- last CTA: exclusive scans of both histograms (in place), largest bin, totals.  Every thread owns nbins / 1024
-    // consecutive bins: one pass for the sums, one block scan, one pass that writes the prefixes.
+    // consecutive bins (a multiple of 4 from 4 Ki bins on: 128-bit loads, four in flight per array).
     const int per = nbins / kHistThreads;               // nbins is a power of two >= 1024
     const int i0 = tid * per;
     uint32_t sc = 0, sr = 0, mx = 0;
-    for (int i = 0; i < per; ++i) { const uint32_t c = __ldcg(bin_cur + i0 + i); sc += c; sr += __ldcg(bin_runs + i0 + i); mx = max(mx, c); }
+    if ((per & 15) == 0) {
+        const uint4* c4 = reinterpret_cast<const uint4*>(bin_cur + i0);
+        const uint4* r4 = reinterpret_cast<const uint4*>(bin_runs + i0);
+        for (int i = 0; i < per / 4; i += 4) {
+            uint4 c[4], r[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) { c[k] = __ldcg(c4 + i + k); r[k] = __ldcg(r4 + i + k); }
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                sc += c[k].x + c[k].y + c[k].z + c[k].w; sr += r[k].x + r[k].y + r[k].z + r[k].w;
+                mx = max(mx, max(max(c[k].x, c[k].y), max(c[k].z, c[k].w)));
+            }
+        }
+    } else {
+        for (int i = 0; i < per; ++i) { const uint32_t c = __ldcg(bin_cur + i0 + i); sc += c; sr += __ldcg(bin_runs + i0 + i); mx = max(mx, c); }
+    }
     uint32_t ic = sc, ir = sr;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
@@ -113,14 +135,31 @@ __global__ void __launch_bounds__(kHistThreads) bin_hist_kernel(GeomHeader* hdr,
     uint32_t bc = 0, br = 0, V = 0, R = 0, maxbin = 0;
 #pragma unroll
     for (int w = 0; w < 32; ++w) {
-        const uint32_t a = s_a[w], b = s_b[w];
-        bc += (w < wid) ? a : 0u; br += (w < wid) ? b : 0u; V += a; R += b; maxbin = max(maxbin, s_c[w]);
+        const uint32_t a = s_a[w], b2 = s_b[w];
+        bc += (w < wid) ? a : 0u; br += (w < wid) ? b2 : 0u; V += a; R += b2; maxbin = max(maxbin, s_c[w]);
     }
     uint32_t rc = bc + ic - sc, rr = br + ir - sr;
-    for (int i = 0; i < per; ++i) {
-        const uint32_t c = __ldcg(bin_cur + i0 + i), r = __ldcg(bin_runs + i0 + i);
-        bin_cur[i0 + i] = rc; bin_runs[i0 + i] = rr;   // bin start (the scatter's cursor) and the bin's first run
-        rc += c; rr += r;
+    if ((per & 15) == 0) {
+        uint4* c4 = reinterpret_cast<uint4*>(bin_cur + i0);
+        uint4* r4 = reinterpret_cast<uint4*>(bin_runs + i0);
+        for (int i = 0; i < per / 4; i += 4) {
+            uint4 c[4], r[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) { c[k] = __ldcg(c4 + i + k); r[k] = __ldcg(r4 + i + k); }
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                uint4 oc, orr;
+                oc.x = rc; rc += c[k].x; oc.y = rc; rc += c[k].y; oc.z = rc; rc += c[k].z; oc.w = rc; rc += c[k].w;
+                orr.x = rr; rr += r[k].x; orr.y = rr; rr += r[k].y; orr.z = rr; rr += r[k].z; orr.w = rr; rr += r[k].w;
+                c4[i + k] = oc; r4[i + k] = orr;       // bin start (the scatter's cursor) and the bin's first run
+            }
+        }
+    } else {
+        for (int i = 0; i < per; ++i) {
+            const uint32_t c = __ldcg(bin_cur + i0 + i), r = __ldcg(bin_runs + i0 + i);
+            bin_cur[i0 + i] = rc; bin_runs[i0 + i] = rr;
+            rc += c; rr += r;
+        }
     }
     if (tid == 0) {
         const bool ok = maxbin <= (uint32_t)kBinCap;
@@ -151,18 +190,24 @@ void launch_bin_hist(const GeomPtrs& g, int P, uint32_t* mailbox_dev, cudaStream
 __global__ void __launch_bounds__(kHistThreads) bin_scatter_kernel(const GeomHeader* __restrict__ hdr, int nblocks,
                                                                    const uint32_t* __restrict__ block_vis, const uint32_t* __restrict__ ckeys,
                                                                    const uint32_t* __restrict__ cids, const uint32_t* __restrict__ crows,
-                                                                   uint32_t* bin_cur, uint4* __restrict__ brec) {
+                                                                   const uint32_t* __restrict__ cxw, uint32_t* bin_cur, uint4* __restrict__ brec) {
     if (hdr->sort_mode != 1u) return;
     const uint32_t kmin = hdr->key_min, shift = hdr->shift;
     const int sub = threadIdx.x >> 8, t = threadIdx.x & 255;
-    for (int b = (int)blockIdx.x * 4 + sub; b < nblocks; b += (int)gridDim.x * 4) {
-        const uint32_t cnt = __ldg(block_vis + b);
+    const int bstep = (int)gridDim.x * 4;
+    int b = (int)blockIdx.x * 4 + sub;
+    uint32_t cnt = b < nblocks ? __ldg(block_vis + b) : 0u;
+    while (b < nblocks) {
+        const int bn = b + bstep;
+        const uint32_t cnt_next = bn < nblocks ? __ldg(block_vis + bn) : 0u;
         if ((uint32_t)t < cnt) {
             const size_t i = (size_t)b * kPreBlock + t;
             const uint32_t key = __ldg(ckeys + i);
+            const uint4 rec = make_uint4(key, __ldg(cids + i), __ldg(crows + i), __ldg(cxw + i));
             const uint32_t pos = atomicAdd(&bin_cur[(key - kmin) >> shift], 1u);
-            brec[pos] = make_uint4(key, __ldg(cids + i), __ldg(crows + i), 0u);
+            brec[pos] = rec;
         }
+        b = bn; cnt = cnt_next;
     }
 }
 
@@ -171,7 +216,7 @@ void launch_bin_scatter(const GeomPtrs& g, int P, cudaStream_t s) {
     const int cap = ds_num_sms() * 2;
     if (grid > cap) grid = cap;
     if (grid < 1) grid = 1;
-    bin_scatter_kernel<<<grid, kHistThreads, 0, s>>>(g.header, g.nblocks, g.block_sums_v, g.dkeys_a, g.order_tmp, g.dkeys_b, g.bin_cur, g.brec);
+    bin_scatter_kernel<<<grid, kHistThreads, 0, s>>>(g.header, g.nblocks, g.block_sums_v, g.dkeys_a, g.order_tmp, g.dkeys_b, g.order, g.bin_cur, g.brec);
     count_launch();
 }
 
@@ -180,16 +225,16 @@ void launch_bin_scatter(const GeomPtrs& g, int P, cudaStream_t s) {
 // ------------------------------------------------------------------------------------------------
 constexpr int kBinSortWarps = 8;
 
+// No shared memory, so that 64 warps per SM are in flight: a bin costs three dependent L2 round trips (cursor words,
+// records, stores) and ~20 of them queue behind each other in a warp -- the kernel is latency-bound, not work-bound.
+// `scratch` (one uint4 per record, indexed like brec) is only touched by bins with more than 32 records.
 __global__ void __launch_bounds__(kBinSortWarps * 32) bin_sort_kernel(const GeomHeader* __restrict__ hdr, const uint32_t* __restrict__ bin_end,
                                                                       const uint32_t* __restrict__ bin_runs, int nbins, const uint4* __restrict__ brec,
-                                                                      uint32_t* __restrict__ order, uint32_t* __restrict__ runoff) {
-    // per warp: the bin's composites (unsorted) and its (id, rows) in sorted order
-    extern __shared__ __align__(16) unsigned char s_raw[];
+                                                                      uint4* scratch, uint32_t* __restrict__ order, uint32_t* __restrict__ runoff,
+                                                                      uint2* __restrict__ srect) {
     if (hdr->sort_mode != 1u) return;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int warp_global = blockIdx.x * kBinSortWarps + wid, warps_total = gridDim.x * kBinSortWarps;
-    unsigned long long* comp = reinterpret_cast<unsigned long long*>(s_raw) + (size_t)wid * kBinCap;
-    uint2* sorted = reinterpret_cast<uint2*>(s_raw + sizeof(unsigned long long) * kBinSortWarps * kBinCap) + (size_t)wid * kBinCap;
     // bins are dealt round-robin: neighbouring (similarly loaded) bins go to different warps
     for (int bin = warp_global; bin < nbins; bin += warps_total) {
         const uint32_t end = __ldg(bin_end + bin), start = bin ? __ldg(bin_end + bin - 1) : 0u;   // after the scatter a cursor = its bin's end
@@ -197,60 +242,55 @@ __global__ void __launch_bounds__(kBinSortWarps * 32) bin_sort_kernel(const Geom
         if (n <= 0) continue;
         uint32_t run0 = __ldg(bin_runs + bin);
         if (n <= 32) {
-            // ---- register path: one record per lane, rank by n shuffled comparisons
+            // ---- one record per lane: rank by n shuffled comparisons of the 64-bit composite (depth key, id), then pull the
+            // record of rank `lane` from the lane that holds it
             uint4 r = make_uint4(0xffffffffu, 0xffffffffu, 0u, 0u);
             if (lane < n) r = __ldg(brec + start + lane);
             const unsigned long long c = ((unsigned long long)r.x << 32) | r.y;
             int rank = 0;
-            for (int j = 0; j < n; ++j) {
-                const unsigned long long o = __shfl_sync(0xffffffffu, c, j);
-                rank += (o < c) ? 1 : 0;
-            }
-            __syncwarp();
-            if (lane < n) sorted[rank] = make_uint2(r.y, r.z);
-            __syncwarp();
-            uint2 v = make_uint2(0u, 0u);
-            if (lane < n) v = sorted[lane];
-            uint32_t inc = v.y;
+            for (int j = 0; j < n; ++j) rank += (__shfl_sync(0xffffffffu, c, j) < c) ? 1 : 0;
+            int src = 0;
+            for (int j = 0; j < n; ++j) src = (__shfl_sync(0xffffffffu, rank, j) == lane) ? j : src;
+            const uint32_t id = __shfl_sync(0xffffffffu, r.y, src), yh = __shfl_sync(0xffffffffu, r.z, src), xw = __shfl_sync(0xffffffffu, r.w, src);
+            const uint32_t h = lane < n ? (yh & 0xffffu) : 0u;
+            uint32_t inc = h;
 #pragma unroll
             for (int o = 1; o < 32; o <<= 1) { const uint32_t u = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += u; }
-            if (lane < n) { order[start + lane] = v.x; runoff[start + lane] = run0 + inc - v.y; }
+            if (lane < n) { order[start + lane] = id; runoff[start + lane] = run0 + inc - h; srect[start + lane] = make_uint2(xw, yh >> 16); }
         } else {
-            // ---- shared-memory path (33 .. kBinCap records): all-pairs rank, records strided over the lanes
-            for (int i = lane; i < n; i += 32) { const uint4 r = __ldg(brec + start + i); comp[i] = ((unsigned long long)r.x << 32) | r.y; }
-            __syncwarp();
+            // ---- 33 .. kBinCap records: all-pairs rank with the records read through the L1, sorted records parked in
+            // `scratch`, then the scan in sorted order
             for (int i = lane; i < n; i += 32) {
-                const unsigned long long c = comp[i];
-                int rank = 0;
-                for (int j = 0; j < n; ++j) rank += (comp[j] < c) ? 1 : 0;       // broadcast reads
                 const uint4 r = __ldg(brec + start + i);
-                sorted[rank] = make_uint2(r.y, r.z);
+                const unsigned long long c = ((unsigned long long)r.x << 32) | r.y;
+                int rank = 0;
+                for (int j = 0; j < n; ++j) { const uint4 o = __ldg(brec + start + j); rank += ((((unsigned long long)o.x << 32) | o.y) < c) ? 1 : 0; }
+                scratch[start + rank] = r;
             }
             __syncwarp();
             for (int base = 0; base < n; base += 32) {
                 const int i = base + lane;
-                uint2 v = make_uint2(0u, 0u);
-                if (i < n) v = sorted[i];
-                uint32_t inc = v.y;
+                uint4 r = make_uint4(0u, 0u, 0u, 0u);
+                if (i < n) r = __ldcg(scratch + start + i);
+                const uint32_t h = r.z & 0xffffu;
+                uint32_t inc = h;
 #pragma unroll
                 for (int o = 1; o < 32; o <<= 1) { const uint32_t u = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += u; }
-                if (i < n) { order[start + i] = v.x; runoff[start + i] = run0 + inc - v.y; }
+                if (i < n) { order[start + i] = r.y; runoff[start + i] = run0 + inc - h; srect[start + i] = make_uint2(r.w, r.z >> 16); }
                 run0 += __shfl_sync(0xffffffffu, inc, 31);
             }
         }
-        __syncwarp();
     }
 }
 
 void launch_bin_sort(const GeomPtrs& g, int P, cudaStream_t s) {
-    int grid = (g.nbins + kBinSortWarps * 8 - 1) / (kBinSortWarps * 8);        // ~8 bins per warp
-    const int cap = ds_num_sms() * 3;                                           // 3 CTAs (3 x 64 KB) per SM
+    int grid = (g.nbins + kBinSortWarps * 4 - 1) / (kBinSortWarps * 4);        // >= 4 bins per warp
+    const int cap = ds_num_sms() * 8;                                           // 8 CTAs x 8 warps per SM
     if (grid > cap) grid = cap;
     if (grid < 1) grid = 1;
-    const size_t smem = (sizeof(unsigned long long) + sizeof(uint2)) * kBinSortWarps * kBinCap;
-    static bool attr_done = false;
-    if (!attr_done) { cudaFuncSetAttribute(bin_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); attr_done = true; }
-    bin_sort_kernel<<<grid, kBinSortWarps * 32, smem, s>>>(g.header, g.bin_cur, g.bin_runs, g.nbins, g.brec, g.order, g.runoff);
+    // scratch for the rare large bins: the per-block compaction arrays are dead by now (dkeys_a .. order_tmp hold 2 x 4 B x P,
+    // contiguous in the layout; a uint4 per record needs 16 B x V <= 16 B x P): use the cov3D-independent sort temp instead
+    bin_sort_kernel<<<grid, kBinSortWarps * 32, 0, s>>>(g.header, g.bin_cur, g.bin_runs, g.nbins, g.brec, g.brec_sorted, g.order, g.runoff, g.srect);
     count_launch();
 }
 
@@ -259,13 +299,19 @@ void launch_bin_sort(const GeomPtrs& g, int P, cudaStream_t s) {
 // 256-block of sorted positions; this finishes the scan inside the block)
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(kPreBlock) runoff_from_blocks_kernel(GeomHeader* hdr, const uint32_t* __restrict__ order, const uint2* __restrict__ rects,
-                                                                       const uint32_t* __restrict__ block_offsets, uint32_t* __restrict__ runoff) {
+                                                                       const uint32_t* __restrict__ block_offsets, uint32_t* __restrict__ runoff,
+                                                                       uint2* __restrict__ srect) {
     __shared__ uint32_t s_w[kPreBlock / 32];
     const uint32_t V = hdr->num_visible;
     const uint32_t j = blockIdx.x * kPreBlock + threadIdx.x;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     uint32_t h = 0;
-    if (j < V) { const uint32_t ry = rects[order[j]].y; h = (ry >> 16) - (ry & 0xffffu); }
+    if (j < V) {
+        const uint2 r = rects[order[j]];
+        const uint32_t x0 = r.x & 0xffffu, y0 = r.y & 0xffffu;
+        h = (r.y >> 16) - y0;
+        srect[j] = make_uint2((x0 << kRunX0Shift) | ((r.x >> 16) - x0), y0);
+    }
     uint32_t inc = h;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) { const uint32_t u = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += u; }
@@ -280,7 +326,7 @@ __global__ void __launch_bounds__(kPreBlock) runoff_from_blocks_kernel(GeomHeade
 }
 
 void launch_runoff_from_blocks(const GeomPtrs& g, int P, cudaStream_t s) {
-    runoff_from_blocks_kernel<<<P / kPreBlock + 1, kPreBlock, 0, s>>>(g.header, g.order, g.rects, g.oblock_offsets, g.runoff);
+    runoff_from_blocks_kernel<<<P / kPreBlock + 1, kPreBlock, 0, s>>>(g.header, g.order, g.rects, g.oblock_offsets, g.runoff, g.srect);
     count_launch();
 }
 

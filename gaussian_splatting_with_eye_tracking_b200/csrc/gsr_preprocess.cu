@@ -53,7 +53,9 @@ struct PreFwdParams {
     uint4* zero_ptr2; size_t zero_n16_2;
     uint32_t* __restrict__ ckeys;           // per-block compaction of the visible Gaussians: depth key (float bits) ...
     uint32_t* __restrict__ cids;            // ... index ...
-    uint32_t* __restrict__ crows;           // ... and number of tile rows the rect spans (= runs the Gaussian emits)
+    uint32_t* __restrict__ crows;           // ... (y0 << 16) | tile rows the rect spans (= runs the Gaussian emits) ...
+    uint32_t* __restrict__ cxw;             // ... and (x0 << 10) | width in tiles: what the run emission needs, so that it never
+                                            // gathers rects[] through the sorted order
     FrameStatSlot* stat_slots;              // [kStatSlots] key range, pair total, prefiltered-trap flag
     GeomHeader* header;
     int prefiltered;
@@ -220,7 +222,7 @@ __global__ void __launch_bounds__(kPreBlock, 4) preprocess_fwd_kernel(const PreF
     __syncthreads();
 
     const int idx = blockIdx.x * kPreBlock + tid;
-    uint32_t touched = 0, rows = 0, key = 0;
+    uint32_t touched = 0, rows = 0, key = 0, ry0 = 0, rxw = 0;
     int radius = 0, trapped = 0;
     for (size_t i = (size_t)idx; i < p.zero_n16; i += (size_t)gridDim.x * kPreBlock) p.zero_ptr[i] = make_uint4(0u, 0u, 0u, 0u);
     for (size_t i = (size_t)idx; i < p.zero_n16_2; i += (size_t)gridDim.x * kPreBlock) p.zero_ptr2[i] = make_uint4(0u, 0u, 0u, 0u);
@@ -305,7 +307,7 @@ __global__ void __launch_bounds__(kPreBlock, 4) preprocess_fwd_kernel(const PreF
         p.tiles_touched[idx] = touched;
         if (!alive) { x0 = x1 = y0 = y1 = 0; }
         p.rects[idx] = make_uint2(x0 | (x1 << 16), y0 | (y1 << 16));
-        rows = y1 - y0;
+        rows = y1 - y0; ry0 = y0; rxw = (x0 << kRunX0Shift) | (x1 - x0);
     }
 
     // ---- block-local compaction + frame statistics.
@@ -328,7 +330,7 @@ __global__ void __launch_bounds__(kPreBlock, 4) preprocess_fwd_kernel(const PreF
 #pragma unroll
         for (int w = 0; w < kPreBlock / 32; ++w) pos += (w < (tid >> 5)) ? s_warp_sum_v[w] : 0u;
         const size_t at = (size_t)blockIdx.x * kPreBlock + pos;
-        p.ckeys[at] = key; p.cids[at] = (uint32_t)idx; p.crows[at] = rows;
+        p.ckeys[at] = key; p.cids[at] = (uint32_t)idx; p.crows[at] = (ry0 << 16) | rows; p.cxw[at] = rxw;
     }
     if (tid == 0) {
         uint32_t s = 0, sv = 0, mx = 0, mn = 0;
@@ -357,7 +359,7 @@ void launch_preprocess(const PreprocessArgs& a, const GeomPtrs& g, cudaStream_t 
     p.band_row0 = a.band_row0; p.band_row1 = a.band_row1;
     p.zero_ptr = reinterpret_cast<uint4*>(a.zero_ptr); p.zero_n16 = a.zero_ptr ? a.zero_bytes / 16 : 0;
     p.zero_ptr2 = reinterpret_cast<uint4*>(g.bin_cur); p.zero_n16_2 = g.bin_zero_bytes / 16;
-    p.ckeys = g.dkeys_a; p.cids = g.order_tmp; p.crows = g.dkeys_b; p.stat_slots = g.stat_slots;
+    p.ckeys = g.dkeys_a; p.cids = g.order_tmp; p.crows = g.dkeys_b; p.cxw = g.order; p.stat_slots = g.stat_slots;
     preprocess_fwd_kernel<<<g.nblocks, kPreBlock, 0, s>>>(p);
     count_launch();
 }

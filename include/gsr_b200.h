@@ -333,6 +333,7 @@ GSR_API int gsr_blend_stats(int P, int W, int H, const void* geom_buffer, const 
 enum { GSR_OPT_SORT_VARIANT = 0,  /* onesweep tile shape for u32 keys: 0 = default, 1..5 see gsr_binning.cu */
        GSR_OPT_BLEND_VARIANT = 1, /* forward blend: 0 = two pixels per thread, packed FP32x2 (default); 1 = one pixel per thread */
        GSR_OPT_PEER_CTAS_PER_SM = 2, /* gsr_peer_allreduce_sum*: grid cap in CTAs per SM, 0 = default */
+       GSR_OPT_NVTX = 5,            /* 1: NVTX range per stage (names "gsr:<stage>"); also enabled by GSR_NVTX=1 in the environment */
        GSR_OPT_FAKE_SORT_ERROR = 4, /* 1: the next frames post a tripped radix-sort watchdog (test hook for GSR_ERR_SORT) */
        GSR_OPT_FORCE_SORT_FALLBACK = 3 /* 1: depth-sort with the global onesweep chain even when the range buckets fit (the
                                           path taken when a depth-histogram bin overflows a bucket); results are identical */ };
