@@ -41,6 +41,9 @@ import torch  # noqa: E402
 # preprocess_fwd_kernel, the dominant HBM-bound kernel: algorithmic bytes per unit
 ALG_BYTES_VISIBLE = 311               # 236 B of parameters read + 75 B of per-Gaussian results written
 ALG_BYTES_CULLED = 20                 # 12 B mean read + radius / tiles_touched written
+# blend kernels: FP32-pipe instructions per unit of algorithmic work
+FP32_INSTR_PER_PAIR_TEST = 20         # forward: one pixel x one examined list entry (+ 1 MUFU.EX2)
+FP32_INSTR_PER_HIT_BWD = 55           # backward: one pair-test that passes both skips (+ 1 MUFU, 9 reductions)
 
 
 # dram__bytes_read.sum + dram__bytes_write.sum of one preprocess_fwd_kernel launch from the committed `ncu --set full`
@@ -154,11 +157,11 @@ class Timer:
     def __init__(self, world, windows, prime=16):
         self.world, self.windows, self.prime = world, windows, prime
 
-    def run(self, fn, steps, warmup):
+    def run(self, fn, steps, warmup, prime=None):
         import torch.distributed as dist
         # allocator priming, outside the W warm-up steps: every ring camera once, so that torch's caching allocator
         # has seen the largest per-camera work buffers (N differs per view) and the timed region holds no cudaMalloc
-        for i in range(self.prime):
+        for i in range(self.prime if prime is None else prime):
             fn(i)
         for i in range(warmup):
             fn(i)
@@ -363,6 +366,191 @@ def amr_frame(impl, cam, mode, gaze=None):
 # ---------------------------------------------------------------------------------------------------------------
 # measurements
 # ---------------------------------------------------------------------------------------------------------------
+def dp_rank1_variants(impl, d, cam_of, w, timer, Kb, world, dev, only=None):
+    """The view-parallel rasterizer step (forward + backward of one view per rank + gradient exchange, no loss / optimizer) in
+    its exchange variants; returns ({variant: (ms_per_step, rows_per_view)}, peer_reducer, peer_error)."""
+    from gaussian_splatting_with_eye_tracking_b200 import dist as gdist
+    P_ = d["means3D"].shape[0]
+    e_ = impl.e
+    M_ = d["shs"].shape[1]
+    res = {}
+    modes = {"dense_rows": (False, 1), "packed_rows": (True, 1)}
+    peer_err, peer_red = None, None
+    if world > 1 and not os.environ.get("GSR_BENCH_NO_PEER"):
+        try:                 # the 11 dense floats summed over NVLink peer memory (gsr_peer_allreduce_sum) instead of NCCL
+            peer_red = gdist.PeerAllReduce(11 * ((P_ + 3) // 4 * 4), dev)
+            modes["packed_rows_peer_sum"] = (True, 1)
+            modes["dense_rows_peer_sum"] = (False, 1)
+        except Exception as ex:
+            peer_err = str(ex)[:300]
+    if os.environ.get("GSR_BENCH_DP_RANGES"):           # measured: splitting the preprocess stage into ranges does not pay (DESIGN 6)
+        modes.update({"packed_rows_2_ranges": (True, 2), "packed_rows_4_ranges": (True, 4)})
+    if only is not None:
+        modes = {k: v for k, v in modes.items() if k in only}
+    for mode, (packed_, nch) in modes.items():
+        use_peer = mode.endswith("peer_sum")
+        exch = gdist.ShGradExchange(packed=packed_, peer=peer_red if use_peer else None)
+
+        def dp_step_rank1(i, exch=exch, nch=nch, use_peer=use_peer):
+            cam = cam_of(i)
+            N, img, radii, gb, bb, ib = impl.forward_c(cam)
+            if exch.packed:     # the forward holds the visible count on the host; the ranks agree on the gather size meanwhile
+                exch.post_visible_count(impl.host.last_counts(gb, P_)[2], dev)
+            # the all-gather of the clamped colour gradient + the SH rebuild start between the two backward phases and
+            # overlap the preprocess-stage backward; the 11-float all-reduce follows it
+            g = impl.host.rasterize_gaussians_backward(
+                d["bg"], d["means3D"], radii, e_, d["scales"], d["rotations"], 1.0, e_, cam.world_view_transform,
+                cam.full_proj_transform, cam.tanfovx, cam.tanfovy, w, d["shs"], d["sh_degree"], cam.camera_center, gb, N, bb, ib,
+                False, compact_sh=True,
+                between_phases=lambda drgb: exch.start_gather(drgb, cam.camera_center, d["means3D"], d["sh_degree"], M_, radii=radii),
+                preprocess_chunks=nch,
+                after_chunk=(lambda first, count, rows: exch.start_reduce_chunk(rows)) if nch > 1 else None,
+                dense_out=peer_red.data if use_peer else None)
+            if nch == 1:
+                exch.start_reduce([g[3], g[2], g[6], g[7]])        # means3D, opacity, scales, rotations
+            return exch.finish()
+        res[mode] = (timer.run(dp_step_rank1, Kb, 2) / Kb, exch.last_cap)
+    return res, peer_red, peer_err
+
+
+def c2_leg(make_impl, timer, rank, K):
+    """Config C2 (BASELINE.json configs[1]): 100 k Gaussians, SH degree 3, one 800x800 view, forward and forward+backward ms/view
+    on one GPU (NeRF-synthetic scale).  At this size the launch chain and the host round trip, not the kernels, set the time."""
+    from gaussian_splatting_with_eye_tracking_b200 import scenes
+    dev = torch.device("cuda", torch.cuda.current_device())
+    sc = scenes.make_object_scene(P=100_000)
+    cams = [c.to(dev) for c in scenes.object_cameras(8, 800, 800)]
+    d2 = {k: (v.to(dev).contiguous() if isinstance(v, torch.Tensor) else v) for k, v in sc.items()}
+    impl = make_impl(d2)
+    cam_of = lambda i: cams[(i + rank) % len(cams)]          # noqa: E731
+    Kc = max(20, K)
+    ms_f = timer.run(lambda i: impl.forward_c(cam_of(i)), Kc, 5, prime=8)
+    g = torch.Generator().manual_seed(3003)
+    w = (torch.rand(3, 800, 800, generator=g) * 2 - 1).to(dev)
+    impl.make_leaves()
+    ms_b = timer.run(lambda i: impl.fwd_bwd(cam_of(i), w), Kc, 5, prime=8)
+    out = {"gaussians": 100_000, "width": 800, "height": 800, "fwd_ms_per_view": ms_f / Kc, "fwd_fps": 1e3 * Kc / ms_f,
+           "fwd_bwd_ms_per_view": ms_b / Kc, "num_rendered": int(impl.forward_c(cams[0])[0])}
+    return out, sc
+
+
+def c2_cpu_oracle(sc):
+    """B-cpu-raster at C2: the C oracle (OpenMP, all host cores), one view forward and forward+backward."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import common
+    from gaussian_splatting_with_eye_tracking_b200 import scenes
+    from oracle import oracle as orc
+    cam = scenes.object_cameras(8, 800, 800)[0]
+    s_, c_ = common.to_oracle(sc, cam)
+    dpix = common.upstream_gradient(cam).numpy()
+    t0 = time.perf_counter(); st = orc.forward(s_, c_); t1 = time.perf_counter()
+    orc.backward(s_, c_, st, dpix); t2 = time.perf_counter()
+    return {"fwd_ms_per_view": 1e3 * (t1 - t0), "fwd_bwd_ms_per_view": 1e3 * (t2 - t0), "cores": orc.num_threads(), "kind": "port",
+            "sample": "1 view (camera 0), 100000 Gaussians, 800x800, C oracle (OpenMP)"}
+
+
+def c4_leg(impl_cls, args, rank, world, timer, dev):
+    """Config C4 (BASELINE.json configs[3]): 6 M-Gaussian training step, one 1080p view per rank, gradients of all views summed on
+    every rank.  Rasterizer forward + backward + exchange ONLY (no loss, no optimizer in numerator or denominator).
+    `n1_ms` = the same forward + backward with no exchange, measured in this run on this rank (what one GPU needs for one view);
+    `dp_step_efficiency` = n1_ms / dp_ms."""
+    from gaussian_splatting_with_eye_tracking_b200 import scenes
+    P6 = int(os.environ.get("GSR_BENCH_C4_GAUSSIANS", 6_000_000))
+    sc = scenes.make_unbounded_scene(P=P6, seed=2003)
+    cams = [c.to(dev) for c in scenes.unbounded_cameras(8, 1920, 1080)]
+    d6 = {k: (v.to(dev).contiguous() if isinstance(v, torch.Tensor) else v) for k, v in sc.items()}
+    del sc
+    impl = impl_cls(d6)
+    cam_of = lambda i: cams[(i + rank) % len(cams)]          # noqa: E731
+    g = torch.Generator().manual_seed(3003)
+    w = (torch.rand(3, 1080, 1920, generator=g) * 2 - 1).to(dev)
+    Kc = 6
+    e_ = impl.e
+
+    def n1_step(i):            # forward + backward through the C-shaped calls, SH gradient written in full, nothing exchanged
+        cam = cam_of(i)
+        N, img, radii, gb, bb, ib = impl.forward_c(cam)
+        return impl.host.rasterize_gaussians_backward(
+            d6["bg"], d6["means3D"], radii, e_, d6["scales"], d6["rotations"], 1.0, e_, cam.world_view_transform, cam.full_proj_transform,
+            cam.tanfovx, cam.tanfovy, w, d6["shs"], d6["sh_degree"], cam.camera_center, gb, N, bb, ib, False)
+    n1 = timer.run(n1_step, Kc, 2, prime=8) / Kc
+    only = ("packed_rows", "packed_rows_peer_sum") if world > 1 else ("packed_rows",)
+    res, peer_red, peer_err = dp_rank1_variants(impl, d6, cam_of, w, timer, Kc, world, dev, only=only)
+    best = min(res, key=lambda m: res[m][0])
+    out = {"gaussians": P6, "width": 1920, "height": 1080, "views_per_step": world, "n1_ms": n1, "dp_ms": res[best][0], "variant": best,
+           "dp_ms_by_variant": {m: round(v[0], 4) for m, v in res.items()}, "dp_step_efficiency": n1 / res[best][0],
+           "views_per_s": world / (res[best][0] / 1e3),
+           "what": "rasterizer forward + backward of one view per rank + exchange of the gradients of all views (rank-1 SH rows gathered, "
+                   "11 dense floats summed); efficiency = same step without exchange on this rank / this"}
+    if peer_err:
+        out["peer_sum_error"] = peer_err
+    del impl, d6, peer_red
+    torch.cuda.empty_cache()
+    return out
+
+
+def c5_leg(impl_cls, args, rank, world, timer, dev, n_frames):
+    """Config C5 (BASELINE.json configs[4]): 4K eye-tracked foveated render along a recorded gaze trajectory, 6 M Gaussians, the
+    frame split into screen-tile bands over the ranks.  The reference ships no gaze recording: scenes.gaze_trajectory is the
+    synthetic 90 Hz pursuit + saccade track of SURVEY 8(d); the camera orbits 0.5 degrees per frame.  Every frame is assembled on
+    rank 0.  frames/s over the trajectory and the p99 frame time (CUDA events per frame, max over ranks of the total)."""
+    import torch.distributed as dist
+    from gaussian_splatting_with_eye_tracking_b200 import dist as gdist, scenes
+    W4, H4 = 3840, 2160
+    P6 = int(os.environ.get("GSR_BENCH_C4_GAUSSIANS", 6_000_000))
+    sc = scenes.make_unbounded_scene(P=P6, seed=2003)
+    d6 = {k: (v.to(dev).contiguous() if isinstance(v, torch.Tensor) else v) for k, v in sc.items()}
+    del sc
+    impl = impl_cls(d6)
+    traj = scenes.gaze_trajectory(n_frames=n_frames, width=W4, height=H4)
+    radii = scenes.fovea_radii(W4)
+    cams = [scenes.look_at_camera((4.5 * math.sin(math.radians(0.5 * i)), 0.3, -4.5 * math.cos(math.radians(0.5 * i))), (0.0, 0.0, 0.0), W4, H4, 1.20).to(dev)
+            for i in range(n_frames)]
+    tiles_x32, tiles_y32 = (W4 + 31) // 32, (H4 + 31) // 32
+    state = {"bands": gdist.balanced_bands([1.0] * tiles_y32, world)}
+    evs = []
+
+    def frame(i):
+        j = i % n_frames
+        gz = (traj[j][0], traj[j][1], radii)
+        fr, counts, levels, _ = gdist.render_amr_frame_bands(impl._args(cams[j]), H4, W4, state["bands"], rank, interpolate_image=True,
+                                                             gaze=gz, gather=True, dst=0)
+        if i % 8 == 7:      # re-balance the bands from this frame's per-row costs (reads the counts back to the host)
+            state["bands"] = gdist.balanced_bands(gdist.row_costs_from_counts(counts, tiles_x32, tiles_y32, levels), world)
+        ev = torch.cuda.Event(enable_timing=True); ev.record(); evs.append(ev)
+        return fr
+    for i in range(8):
+        frame(i)
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    evs.clear()
+    e0 = torch.cuda.Event(enable_timing=True); e0.record()
+    t0 = time.time()
+    for i in range(n_frames):
+        frame(i)
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    timer.windows.append((t0, time.time()))
+    total = e0.elapsed_time(evs[-1])
+    per = [evs[0].elapsed_time(evs[0]) if False else 0.0]
+    per = [e0.elapsed_time(evs[0])] + [evs[k - 1].elapsed_time(evs[k]) for k in range(1, len(evs))]
+    if world > 1:
+        t = torch.tensor([total], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        total = float(t.item())
+    per.sort()
+    out = {"gaussians": P6, "width": W4, "height": H4, "frames": n_frames, "frames_per_s": 1e3 * n_frames / total, "ms_per_frame_mean": total / n_frames,
+           "ms_per_frame_p50": per[len(per) // 2], "ms_per_frame_p99": per[min(len(per) - 1, int(0.99 * len(per)))], "ranks": world,
+           "bands": [list(b) for b in state["bands"]],
+           "what": "AMR-foveated 4K frame per step along the synthetic 90 Hz gaze trajectory (gaze-driven level cap, radii W/2..W/16), camera orbit "
+                   "0.5 deg/frame, tile bands over the ranks, assembled on rank 0; p50/p99 are rank 0's per-frame event intervals"}
+    del impl, d6
+    torch.cuda.empty_cache()
+    return out
+
+
 def measure(impl, args, d, cams, rank, world, timer, full):
     """All GPU numbers of one implementation.  `full` = also AMR / fwd+bwd / DP arms."""
     import torch.distributed as dist
@@ -398,7 +586,21 @@ def measure(impl, args, d, cams, rank, world, timer, full):
         out["stage_counts"] = {k: v[1] for k, v in prof.items()}
         out["mean_num_rendered"] = nr / K
         out["mean_visible"] = sum(int((impl.forward_c(cam_of(Wm + i))[2] > 0).sum()) for i in range(min(K, ncam))) / min(K, ncam)
+        # algorithmic work of the blend stage: pair-tests / hits counted on the device per ring camera
+        # (gsr_blend_stats, one extra kernel, outside every timed region), weighted by the cameras the K profiled steps visited
+        per_cam = {}
+        for j in sorted({(Wm + i + rank) % ncam for i in range(K)}):
+            N_, _, _, gb_, bb_, ib_ = impl.forward_c(cams[j])
+            per_cam[j] = impl.host.blend_stats(gb_, bb_, ib_, d["means3D"].shape[0], args.height, args.width)
+        visits = [(Wm + i + rank) % ncam for i in range(K)]
+        out["blend_work"] = {k: sum(per_cam[j][q] for j in visits) / K for q, k in enumerate(("pair_tests_fwd", "hits", "pair_tests_bwd"))}
     del last["r"]
+
+    # ---- sustained: >= 2 s of back-to-back frames of the same workload (the K-step region above is a ~20 ms burst at boost clock)
+    n_sus = max(K, int(2.2 / max(1e-6, out["ms_per_step"] / 1e3)))
+    ms = timer.run(lambda i: impl.forward_c(cam_of(i)), n_sus, 2, prime=0)
+    out["sustained"] = {"value": world * n_sus / (ms / 1e3), "unit": "frames/s", "frames_per_rank": n_sus, "seconds": ms / 1e3,
+                        "window": timer.windows[-1]}
 
     # ---- e2e: public API, camera from pinned host memory, frame back to pinned host memory
     dev = d["means3D"].device
@@ -504,41 +706,7 @@ def measure(impl, args, d, cams, rank, world, timer, full):
     if is_ours:
         e_ = impl.e
         M_ = d["shs"].shape[1]
-        res = {}
-        modes = {"dense_rows": (False, 1), "packed_rows": (True, 1)}
-        peer_err, peer_red = None, None
-        if world > 1 and not os.environ.get("GSR_BENCH_NO_PEER"):
-            try:                 # the 11 dense floats summed over NVLink peer memory (gsr_peer_allreduce_sum) instead of NCCL
-                peer_red = gdist.PeerAllReduce(11 * ((P_ + 3) // 4 * 4), dev)
-                modes["packed_rows_peer_sum"] = (True, 1)
-                modes["dense_rows_peer_sum"] = (False, 1)
-            except Exception as ex:
-                peer_err = str(ex)[:300]
-        if os.environ.get("GSR_BENCH_DP_RANGES"):           # measured: splitting the preprocess stage into ranges does not pay
-            modes.update({"packed_rows_2_ranges": (True, 2), "packed_rows_4_ranges": (True, 4)})
-        for mode, (packed_, nch) in modes.items():
-            use_peer = mode.endswith("peer_sum")
-            exch = gdist.ShGradExchange(packed=packed_, peer=peer_red if use_peer else None)
-
-            def dp_step_rank1(i, exch=exch, nch=nch, use_peer=use_peer):
-                cam = cam_of(i)
-                N, img, radii, gb, bb, ib = impl.forward_c(cam)
-                if exch.packed:     # the forward holds the visible count on the host; the ranks agree on the gather size meanwhile
-                    exch.post_visible_count(impl.host.last_counts(gb, P_)[2], dev)
-                # the all-gather of the clamped colour gradient + the SH rebuild start between the two backward phases and
-                # overlap the preprocess-stage backward; the 11-float all-reduce follows it
-                g = impl.host.rasterize_gaussians_backward(
-                    d["bg"], d["means3D"], radii, e_, d["scales"], d["rotations"], 1.0, e_, cam.world_view_transform,
-                    cam.full_proj_transform, cam.tanfovx, cam.tanfovy, w, d["shs"], d["sh_degree"], cam.camera_center, gb, N, bb, ib,
-                    False, compact_sh=True,
-                    between_phases=lambda drgb: exch.start_gather(drgb, cam.camera_center, d["means3D"], d["sh_degree"], M_, radii=radii),
-                    preprocess_chunks=nch,
-                    after_chunk=(lambda first, count, rows: exch.start_reduce_chunk(rows)) if nch > 1 else None,
-                    dense_out=peer_red.data if use_peer else None)
-                if nch == 1:
-                    exch.start_reduce([g[3], g[2], g[6], g[7]])        # means3D, opacity, scales, rotations
-                return exch.finish()
-            res[mode] = (timer.run(dp_step_rank1, Kb, 2) / Kb, exch.last_cap)
+        res, peer_red, peer_err = dp_rank1_variants(impl, d, cam_of, w, timer, Kb, world, dev)
         best = min((m for m in res if m != "dense_rows"), key=lambda m: res[m][0])
         ms1, cap = res[best]
         pb = gdist.ShGradExchange.payload_bytes(P_, world, cap=cap)
@@ -866,6 +1034,11 @@ def main():
                                           "(baseline/_ref, built by the reference's own setup.py for sm_100a) on the GPU -- the reference "
                                           "has no CPU rasterizer; see --impl reference-cpu for the CPU oracle port"}
         line["extra"] = {k: m[k] for k in ("num_rendered", "fwd_bwd_ms_per_view", "amr", "c2", "sustained") if k in m}
+        if full and eff_world == 1:
+            try:
+                line["extra"]["c2"] = c2_leg(lambda d2: Ref(d2, alias=False), timer, 0, args.steps)[0]
+            except Exception as ex:
+                line["extra"]["c2"] = {"error": f"{type(ex).__name__}: {str(ex)[:300]}"}
         line["extra"]["amr_via"] = impl.amr_via
         line["extra"]["python_package"] = os.path.relpath(impl.dgr.__file__, ROOT)
         line["extra"]["libgsr_b200_mapped"] = any("libgsr_b200" in ln for ln in open("/proc/self/maps"))
@@ -875,16 +1048,59 @@ def main():
         line.update(value=m["value"], ms_per_step=m["ms_per_step"], e2e=m["e2e"], gpu_launches=m["gpu_launches"])
         N = m["mean_num_rendered"]
         st = m["stages_ms"]
+        sm_count = torch.cuda.get_device_properties(torch.cuda.current_device()).multi_processor_count
+        f_sm_ghz = 1.965                    # boost clock of the K-step burst (the clocks object below records what NVML saw)
+        hbm_roof = None
         if "preprocess" in st:
             vis = m["mean_visible"]
             alg = ALG_BYTES_VISIBLE * vis + ALG_BYTES_CULLED * (args.gaussians - vis)
             ach = alg / (st["preprocess"] * 1e-3) / 1e9
-            line["roofline"] = {"kernel": "preprocess_fwd_kernel (projection, cov3D->cov2D, SH->RGB, radius, tile rect; one launch per step)",
-                                "bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-                                "traffic": NCU_TRAFFIC_BYTES.get(args.gaussians), "peak_source": peak_src, "launch_ms": st["preprocess"],
-                                "alg_bytes_per_launch": alg, "visible_per_launch": vis, "culled_per_launch": args.gaussians - vis,
-                                "alg_bytes_per_visible": ALG_BYTES_VISIBLE, "alg_bytes_per_culled": ALG_BYTES_CULLED}
-        extra = {k: m[k] for k in ("num_rendered", "stages_ms", "fwd_bwd_ms_per_view", "bwd_stages_ms", "dp_train", "dp_train_rank1_sh", "dp_train_full_step", "tile_bands", "amr") if k in m}
+            hbm_roof = {"kernel": "preprocess_fwd_kernel (projection, cov3D->cov2D, SH->RGB, radius, tile rect, per-block compaction; one launch per step)",
+                        "bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                        "traffic": NCU_TRAFFIC_BYTES.get(args.gaussians), "peak_source": peak_src, "launch_ms": st["preprocess"],
+                        "share_of_step": st["preprocess"] / m["ms_per_step"],
+                        "alg_bytes_per_launch": alg, "visible_per_launch": vis, "culled_per_launch": args.gaussians - vis,
+                        "alg_bytes_per_visible": ALG_BYTES_VISIBLE, "alg_bytes_per_culled": ALG_BYTES_CULLED}
+        # The kernel with the largest share of the step is the forward blend, bound by FP32 instruction issue (no dense
+        # contraction on this path: tensor cores unused).  Its roofline per SURVEY 8(d): algorithmic work = pair-tests (one pixel x
+        # one list entry the reference's loop examines, counted on the device by gsr_blend_stats) x 20 FP32-pipe instructions,
+        # against sm_count x 128 FP32 lanes x f_SM.
+        bw = m.get("blend_work")
+        if bw and "blend" in st:
+            peak_lanes = sm_count * 128 * f_sm_ghz          # G lane-instructions / s
+            ach_f = bw["pair_tests_fwd"] * FP32_INSTR_PER_PAIR_TEST / (st["blend"] * 1e-3) / 1e9
+            line["roofline"] = {"kernel": "blend_fwd2_kernel (per-tile front-to-back alpha blending; one launch per step; largest share of the step)",
+                                "bound": "fp32", "achieved": ach_f / 1e3, "peak": peak_lanes / 1e3, "unit": "T lane-instr/s", "frac": ach_f / peak_lanes,
+                                "traffic": None, "launch_ms": st["blend"], "share_of_step": st["blend"] / m["ms_per_step"],
+                                "pair_tests_per_launch": bw["pair_tests_fwd"], "hits_per_launch": bw["hits"],
+                                "fp32_instr_per_pair_test": FP32_INSTR_PER_PAIR_TEST,
+                                "peak_source": f"{sm_count} SMs x 128 FP32 lanes x {f_sm_ghz} GHz (cudaGetDeviceProperties SM count, max SM clock)",
+                                "note": "algorithmic pair-tests: the kernel's exact tile cull skips part of them, so frac may exceed what the issued instructions alone would give"}
+            line["roofline_hbm"] = hbm_roof
+        elif hbm_roof:
+            line["roofline"] = hbm_roof
+        bst = m.get("bwd_stages_ms") or {}
+        if bw and "bwd_blend" in bst:
+            peak_lanes = sm_count * 128 * f_sm_ghz
+            ach_b = bw["hits"] * FP32_INSTR_PER_HIT_BWD / (bst["bwd_blend"] * 1e-3) / 1e9
+            line["roofline_blend_bwd"] = {"kernel": "blend_bwd2_kernel", "bound": "fp32", "achieved": ach_b / 1e3, "peak": peak_lanes / 1e3,
+                                          "unit": "T lane-instr/s", "frac": ach_b / peak_lanes, "launch_ms": bst["bwd_blend"],
+                                          "hits_per_launch": bw["hits"], "pair_tests_per_launch": bw["pair_tests_bwd"],
+                                          "fp32_instr_per_hit": FP32_INSTR_PER_HIT_BWD}
+        extra = {k: m[k] for k in ("num_rendered", "stages_ms", "fwd_bwd_ms_per_view", "bwd_stages_ms", "blend_work", "sustained", "dp_train", "dp_train_rank1_sh", "dp_train_full_step", "tile_bands", "amr") if k in m}
+        if full:
+            dev_ = torch.device("cuda", torch.cuda.current_device())
+            torch.cuda.empty_cache()
+            for name, fn in (("c4", lambda: c4_leg(Ours, args, rank, eff_world, timer, dev_)),
+                             ("c5", lambda: c5_leg(Ours, args, rank, eff_world, timer, dev_, int(os.environ.get("GSR_BENCH_C5_FRAMES", 900))))):
+                if os.environ.get("GSR_BENCH_SKIP_" + name.upper()):
+                    continue
+                try:
+                    extra[name] = fn()
+                except Exception as ex:     # reported, never fatal for the headline
+                    extra[name] = {"error": f"{type(ex).__name__}: {str(ex)[:300]}"}
+                    if eff_world > 1:
+                        raise                # a rank that drops out of a collective leg would hang the others
         extra["pairs_per_gaussian_mean"] = N / args.gaussians
         extra["visible_mean"] = m.get("mean_visible")
         if full and rank == 0 and eff_world == 1 and not os.environ.get("GSR_BENCH_SKIP_REF"):
@@ -902,6 +1118,18 @@ def main():
                 except Exception as ex:     # reported, never fatal for our own line
                     extra["reference_cuda_same_run"] = {"error": str(ex)[:300]}
             try:
+                c2, sc2 = c2_leg(lambda d2: Ours(d2), timer, 0, args.steps)
+                if ref_ok:
+                    c2r, _ = c2_leg(lambda d2: Ref(d2, alias=True), timer, 0, args.steps)
+                    c2["reference"] = {k: c2r[k] for k in ("fwd_ms_per_view", "fwd_fps", "fwd_bwd_ms_per_view")}
+                    c2["speedup_fwd"] = c2r["fwd_ms_per_view"] / c2["fwd_ms_per_view"]
+                    c2["speedup_fwd_bwd"] = c2r["fwd_bwd_ms_per_view"] / c2["fwd_bwd_ms_per_view"]
+                if not args.no_cpu_baseline:
+                    c2["cpu_oracle"] = c2_cpu_oracle(sc2)
+                extra["c2"] = c2
+            except Exception as ex:
+                extra["c2"] = {"error": f"{type(ex).__name__}: {str(ex)[:300]}"}
+            try:
                 extra["train_step"] = train_step_bench(impl, Ref(d, alias=True) if ref_ok else None, d, cams, args)
             except Exception as ex:
                 extra["train_step"] = {"error": str(ex)[:300]}
@@ -916,6 +1144,10 @@ def main():
 
     if rank == 0:
         sampler.stop()
+        sus = line.get("extra", {}).get("sustained")
+        if isinstance(sus, dict) and "window" in sus:
+            w0, w1 = sus.pop("window")
+            sus["clocks"] = sampler.summary([(w0, w1)])
         line["clocks"] = sampler.summary(windows)
         emit(line)
     if world > 1 and args.impl == "ours":

@@ -47,8 +47,9 @@ struct GeomHeader {      // lives at the start of the (aligned) geometry buffer,
     uint32_t key_min;        // smallest depth key (float bits) among the visible Gaussians
     uint32_t shift;          // bin = (key - key_min) >> shift
     uint32_t sort_mode;      // 1 = bins valid; 2 = a bin exceeds kBinCap -> the host runs the onesweep fallback; 3 = fallback done
-    uint32_t max_bin;        // records in the fullest bin (diagnostics)
-    uint32_t pad[53];
+    uint32_t max_bin;        // records in the fullest bin
+    uint32_t comp32;         // 1: (position of the key inside its bin, id) fits one 32-bit composite
+    uint32_t pad[52];
 };
 static_assert(sizeof(GeomHeader) == 256, "header is one alignment unit");
 
@@ -60,16 +61,16 @@ static_assert(sizeof(FrameStatSlot) == 128, "one line per slot");
 
 // ---------------------------------------------------------------- depth sort sizing
 constexpr int kBinCap = 512;                                  // records one warp orders by all-pairs ranking; fuller bin -> fallback
-__host__ __device__ inline int depth_bins(int P) {            // ~32 Gaussians of the scene per bin, 1 Ki .. 64 Ki bins
+__host__ __device__ inline int depth_bins(int P) {            // <= 32 Gaussians of the scene per bin, 1 Ki .. 256 Ki bins (power of two)
     int n = 1024;
-    while (n < 65536 && n * 32 < P) n <<= 1;
+    while (n < 262144 && n * 32 < P) n <<= 1;
     return n;
 }
 
 struct GeomLayout {
     size_t header, depths, clamped, radii, means2D, cov3D, conic_opacity, rgb, tiles_touched, rects,
            block_sums, block_sums_r, block_sums_v, block_offsets, dkeys_a, dkeys_b, order_tmp, order, oblock_sums, oblock_offsets, sort_temp,
-           stat_slots, brec, brec_sorted, runoff, srect, bin_cur, bin_runs, total;
+           stat_slots, brec, seg_tot, runoff, srect, bin_cur, bin_runs, total;
     int nblocks, nbins;
     __host__ __device__ explicit GeomLayout(int P) {
         nblocks = (P + kPreBlock - 1) / kPreBlock;
@@ -101,7 +102,7 @@ struct GeomLayout {
         nbins = depth_bins(P);
         stat_slots = o;    o = align_up(o + sizeof(FrameStatSlot) * kStatSlots);
         brec = o;          o = align_up(o + sizeof(uint4) * (size_t)P);
-        brec_sorted = o;   o = align_up(o + sizeof(uint4) * (size_t)P);     // touched only by bins with more than 32 records
+        seg_tot = o;       o = align_up(o + sizeof(uint2) * 256);            // (records, runs) per scan segment of 1024 bins
         runoff = o;        o = align_up(o + sizeof(uint32_t) * ((size_t)P + 1));
         srect = o;         o = align_up(o + sizeof(uint2) * (size_t)P);
         bin_cur = o;       o = align_up(o + sizeof(uint32_t) * (size_t)nbins);
@@ -116,7 +117,7 @@ struct GeomPtrs {
     float4* conic_opacity; float* rgb; uint32_t* tiles_touched; uint2* rects; uint32_t* block_sums; uint32_t* block_sums_r; uint32_t* block_sums_v;
     uint32_t* block_offsets;
     uint32_t *dkeys_a, *dkeys_b, *order_tmp, *order, *oblock_sums, *oblock_offsets; void* sort_temp; size_t sort_temp_bytes;
-    FrameStatSlot* stat_slots; uint4 *brec, *brec_sorted; uint32_t *runoff, *bin_cur, *bin_runs; uint2* srect; size_t bin_zero_bytes;
+    FrameStatSlot* stat_slots; uint4* brec; uint2* seg_tot; uint32_t *runoff, *bin_cur, *bin_runs; uint2* srect; size_t bin_zero_bytes;
     int nblocks, nbins;
 };
 
@@ -144,7 +145,7 @@ inline GeomPtrs geom_ptrs(const void* buf, int P) {
     g.order_tmp = (uint32_t*)(b + L.order_tmp); g.order = (uint32_t*)(b + L.order);
     g.oblock_sums = (uint32_t*)(b + L.oblock_sums); g.oblock_offsets = (uint32_t*)(b + L.oblock_offsets);
     g.sort_temp = (void*)(b + L.sort_temp); g.sort_temp_bytes = sort_temp_bytes(P);
-    g.stat_slots = (FrameStatSlot*)(b + L.stat_slots); g.brec = (uint4*)(b + L.brec); g.brec_sorted = (uint4*)(b + L.brec_sorted); g.runoff = (uint32_t*)(b + L.runoff);
+    g.stat_slots = (FrameStatSlot*)(b + L.stat_slots); g.brec = (uint4*)(b + L.brec); g.seg_tot = (uint2*)(b + L.seg_tot); g.runoff = (uint32_t*)(b + L.runoff);
     g.bin_cur = (uint32_t*)(b + L.bin_cur); g.bin_runs = (uint32_t*)(b + L.bin_runs); g.srect = (uint2*)(b + L.srect);
     g.bin_zero_bytes = L.total - L.bin_cur;               // bin_cur + bin_runs, contiguous, 256-byte aligned pieces
     g.nblocks = L.nblocks; g.nbins = L.nbins;
