@@ -183,10 +183,10 @@ static int build_lists(const gsr_scene* sc, const gsr_camera* cam, int mode, gsr
     if (cam->band_row1 > im.tiles_y) { set_error("tile band [%d,%d) exceeds the %d tile rows", cam->band_row0, cam->band_row1, im.tiles_y); return GSR_ERR_INVALID; }
     if (im.tiles_x > kRunFieldMask || im.tiles_y > kRunMaxRows) { set_error("image of %dx%d tiles exceeds the %dx%d tile grid limit", im.tiles_x, im.tiles_y, kRunFieldMask, kRunMaxRows); return GSR_ERR_INVALID; }
     int rc = GSR_OK;
-    // Two small memset nodes per frame (header: 256 B, statistics slots: 16 KB): both are accumulated with atomics.  The
-    // depth bins are cleared on the side by the preprocess kernel.
+    // Two memset nodes per frame: the header (256 B) and the statistics slots + depth bins (2 - 8 MB, contiguous), all
+    // accumulated with atomics by the preprocess kernel.
     if ((rc = check_cuda(cudaMemsetAsync(g.header, 0, sizeof(GeomHeader), s), "memset header"))) return rc;
-    if ((rc = check_cuda(cudaMemsetAsync(g.stat_slots, 0, sizeof(FrameStatSlot) * kStatSlots, s), "memset statistics"))) return rc;
+    if ((rc = check_cuda(cudaMemsetAsync(g.stat_slots, 0, g.frame_zero_bytes, s), "memset bins"))) return rc;
     uint32_t* box_dev = nullptr;
     uint32_t* box = pinned_mailbox(&box_dev);
     if (box) { box[0] = 0; box[6] = 0; }
@@ -208,8 +208,8 @@ static int build_lists(const gsr_scene* sc, const gsr_camera* cam, int mode, gsr
     { ProfScope ps(GSR_PROF_PREPROCESS, s); launch_preprocess(a, g, s); }
     if ((rc = check_last("preprocess", debug, s))) return rc;
     // histogram of the depth keys + bucket plan (replaces the scan kernel's slot in the profile)
-    { ProfScope ps(GSR_PROF_SCAN, s); launch_bin_hist(g, P, box_dev, s); }
-    if ((rc = check_last("depth histogram", debug, s))) return rc;
+    { ProfScope ps(GSR_PROF_SCAN, s); launch_bin_scan(g, P, box_dev, s); }
+    if ((rc = check_last("depth-bin scan", debug, s))) return rc;
 
     // The one host round-trip of the forward (reference: rasterizer_impl.cu:281): the binning buffer is sized by N.
     // The last CTAs of the two kernels above store the totals straight into mapped host memory and the host waits on an

@@ -106,14 +106,21 @@ struct EmitRunsParams {
 
 // One THREAD PER RUN: the runs of a block of 256 depth-sorted Gaussians are consecutive in the output, so thread r of the
 // block writes run base + r -- fully coalesced stores (one thread per Gaussian looping over its rows wrote 32 different
-// sectors per store instruction, 1 cycle each in the L1) and no divergence on tall Gaussians.  The Gaussian of a run is
-// found by binary search in the block's 257 offsets (shared memory).
+// sectors per store instruction, 1 cycle each in the L1) and no divergence on tall Gaussians.  The Gaussian of a run comes
+// from a marker + prefix-max pass over tiles of 1024 runs in shared memory: every Gaussian marks the slot of its first
+// run with its index, an inclusive max-scan spreads the index over the Gaussian's runs (~30 instructions per run; a binary
+// search per run in the block's offsets cost ~150 and made the kernel issue-bound).
+constexpr int kEmitTile = 4 * kPreBlock;
+
 __global__ void __launch_bounds__(kPreBlock) emit_runs_kernel(const EmitRunsParams p) {
     extern __shared__ uint32_t s_hist[];            // [passes][kSortMaxRadix]
     __shared__ uint32_t s_off[kPreBlock + 1];
     __shared__ uint32_t s_id[kPreBlock];
     __shared__ uint32_t s_x[kPreBlock], s_y0[kPreBlock];
-    const int tid = threadIdx.x;
+    __shared__ __align__(16) uint32_t s_g[kEmitTile];
+    __shared__ uint32_t s_wmax[kPreBlock / 32];
+    __shared__ uint32_t s_carry;
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const uint32_t V = p.hdr->num_visible;
     const uint32_t j0 = blockIdx.x * kPreBlock;
     if (j0 >= V) return;                             // (CTA-uniform)
@@ -128,17 +135,47 @@ __global__ void __launch_bounds__(kPreBlock) emit_runs_kernel(const EmitRunsPara
     if (tid == 0) s_off[cnt] = __ldg(p.runoff + j0 + cnt);
     __syncthreads();
     const uint32_t base = s_off[0], total = s_off[cnt] - base;
-    for (uint32_t r = tid; r < total; r += kPreBlock) {
-        const uint32_t at = base + r;
-        int lo = 0, hi = cnt;                        // invariant: s_off[lo] <= at < s_off[hi]
-        while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (s_off[mid] <= at) lo = mid; else hi = mid; }
-        const uint32_t key = ((s_y0[lo] + (at - s_off[lo])) << kRunRowShift) | s_x[lo];
-        p.rkeys[at] = key;
-        p.rvals[at] = s_id[lo];
-        atomicAdd(&s_hist[(key >> p.shift0) & ((1u << p.bits0) - 1u)], 1u);
-        if (p.passes > 1) atomicAdd(&s_hist[kSortMaxRadix + ((key >> p.shift1) & ((1u << p.bits1) - 1u))], 1u);
+    const uint32_t my_st = tid < cnt ? s_off[tid] - base : 0u, my_en = tid < cnt ? s_off[tid + 1] - base : 0u;
+    for (uint32_t tile0 = 0; tile0 < total; tile0 += kEmitTile) {
+        reinterpret_cast<uint4*>(s_g)[tid] = make_uint4(0u, 0u, 0u, 0u);
+        if (tid == 0) s_carry = 0;
+        __syncthreads();
+        if (my_en > my_st) {                                          // Gaussians with at least one run
+            if (my_st >= tile0 && my_st < tile0 + kEmitTile) s_g[my_st - tile0] = (uint32_t)tid + 1u;
+            else if (my_st < tile0 && my_en > tile0) s_carry = (uint32_t)tid + 1u;      // the one whose runs straddle the tile start
+        }
+        __syncthreads();
+        // inclusive prefix-max over the tile: 4 consecutive slots per thread, warp scan, 8 warp totals
+        uint4 v = reinterpret_cast<const uint4*>(s_g)[tid];
+        v.y = max(v.y, v.x); v.z = max(v.z, v.y); v.w = max(v.w, v.z);
+        uint32_t m = v.w;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const uint32_t u = __shfl_up_sync(0xffffffffu, m, o); if (lane >= o) m = max(m, u); }
+        if (lane == 31) s_wmax[wid] = m;
+        uint32_t ex = __shfl_up_sync(0xffffffffu, m, 1);
+        if (lane == 0) ex = 0;
+        __syncthreads();
+        uint32_t pre = s_carry;
+#pragma unroll
+        for (int w = 0; w < kPreBlock / 32; ++w) pre = max(pre, (w < wid) ? s_wmax[w] : 0u);
+        pre = max(pre, ex);
+        reinterpret_cast<uint4*>(s_g)[tid] = make_uint4(max(v.x, pre), max(v.y, pre), max(v.z, pre), max(v.w, pre));   // own slots only
+        __syncthreads();
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const uint32_t r = tile0 + k * kPreBlock + tid;
+            if (r < total) {
+                const uint32_t lo = s_g[k * kPreBlock + tid] - 1u;
+                const uint32_t at = base + r;
+                const uint32_t key = ((s_y0[lo] + (at - s_off[lo])) << kRunRowShift) | s_x[lo];
+                p.rkeys[at] = key;
+                p.rvals[at] = s_id[lo];
+                atomicAdd(&s_hist[(key >> p.shift0) & ((1u << p.bits0) - 1u)], 1u);
+                if (p.passes > 1) atomicAdd(&s_hist[kSortMaxRadix + ((key >> p.shift1) & ((1u << p.bits1) - 1u))], 1u);
+            }
+        }
+        __syncthreads();
     }
-    __syncthreads();
     for (int i = tid; i < p.passes * kSortMaxRadix; i += kPreBlock) {
         const uint32_t c = s_hist[i];
         if (c) atomicAdd(&p.hist[i], c);

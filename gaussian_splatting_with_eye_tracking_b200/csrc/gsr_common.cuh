@@ -43,34 +43,39 @@ struct GeomHeader {      // lives at the start of the (aligned) geometry buffer,
     uint32_t num_runs;       // = sum over visible Gaussians of the tile rows their rect spans ((Gaussian, row) runs)
     uint32_t num_visible;    // Gaussians with tiles_touched > 0: only these are depth-sorted
     // ---- depth sort (gsr_depthsort.cu)
-    uint32_t done_hist;      // CTAs of bin_hist_kernel that have finished (the last one scans the histograms, posts the totals)
-    uint32_t key_min;        // smallest depth key (float bits) among the visible Gaussians
-    uint32_t shift;          // bin = (key - key_min) >> shift
-    uint32_t sort_mode;      // 1 = bins valid; 2 = a bin exceeds kBinCap -> the host runs the onesweep fallback; 3 = fallback done
+    uint32_t done_hist;      // CTAs of bin_scan_kernel that have finished (the last one posts the frame totals)
+    uint32_t shift;          // bin = (key - kDepthKey0) >> shift
+    uint32_t sort_mode;      // 1 = bins valid; 2 = a bin exceeds kBinCap / a key beyond the binned range -> the host runs the
+                             // onesweep fallback; 3 = fallback done
     uint32_t max_bin;        // records in the fullest bin
     uint32_t comp32;         // 1: (position of the key inside its bin, id) fits one 32-bit composite
-    uint32_t pad[52];
+    uint32_t pad[53];
 };
 static_assert(sizeof(GeomHeader) == 256, "header is one alignment unit");
 
 // Frame statistics accumulated by preprocess_fwd_kernel with atomics.  Same-address global atomics serialise (~30 ns each
 // on B200), so the 11 719 CTAs of a 3 M-Gaussian frame are spread over kStatSlots slots, one 128-byte line each.
 constexpr int kStatSlots = 128;
-struct FrameStatSlot { uint32_t key_max, key_min_inv /* ~min, so that 0-init + atomicMax works */, num_rendered, flags, pad[28]; };
+struct FrameStatSlot { uint32_t num_rendered, flags /* 1: culled although prefiltered, 2: depth key beyond the binned range */, pad[30]; };
 static_assert(sizeof(FrameStatSlot) == 128, "one line per slot");
 
 // ---------------------------------------------------------------- depth sort sizing
+// Depth keys are the float bits of the view-space depth, > 0.2 by the near-plane cull (auxiliary.h:139-164).  The bins cover
+// keys [kDepthKey0, kDepthKey0 + 2^28) -- depths up to ~1e6 -- at a FIXED resolution, so that the preprocess kernel itself can
+// count them (no key-range pass): 2^shift keys per bin, shift chosen so that (key position inside the bin, Gaussian index)
+// fits one 32-bit word for the scene size.
+constexpr uint32_t kDepthKey0 = 0x3E4CCCCDu;                  // bits of 0.2f
+constexpr int kDepthSpanLog2 = 28;
 constexpr int kBinCap = 512;                                  // records one warp orders by all-pairs ranking; fuller bin -> fallback
-__host__ __device__ inline int depth_bins(int P) {            // <= 32 Gaussians of the scene per bin, 1 Ki .. 256 Ki bins (power of two)
-    int n = 1024;
-    while (n < 262144 && n * 32 < P) n <<= 1;
-    return n;
-}
+constexpr int kSegBins = 1024;                                // bins per scan segment
+__host__ __device__ inline int index_bits(int P) { int b = 1; while (b < 31 && (1ll << b) < (long long)P) ++b; return b; }
+__host__ __device__ inline int depth_shift(int P) { int sh = 32 - index_bits(P); return sh > 10 ? 10 : (sh < 8 ? 8 : sh); }
+__host__ __device__ inline int depth_bins(int P) { return 1 << (kDepthSpanLog2 - depth_shift(P)); }       // 256 Ki .. 1 Mi
 
 struct GeomLayout {
     size_t header, depths, clamped, radii, means2D, cov3D, conic_opacity, rgb, tiles_touched, rects,
            block_sums, block_sums_r, block_sums_v, block_offsets, dkeys_a, dkeys_b, order_tmp, order, oblock_sums, oblock_offsets, sort_temp,
-           stat_slots, brec, seg_tot, runoff, srect, bin_cur, bin_runs, total;
+           stat_slots, brec, crank, seg_tot, runoff, srect, bins64, bin_cnt, total;
     int nblocks, nbins;
     __host__ __device__ explicit GeomLayout(int P) {
         nblocks = (P + kPreBlock - 1) / kPreBlock;
@@ -97,16 +102,17 @@ struct GeomLayout {
         oblock_sums = o;   o = align_up(o + sizeof(uint32_t) * (size_t)(nblocks + 1));
         oblock_offsets = o; o = align_up(o + sizeof(uint32_t) * (size_t)(nblocks + 1));
         sort_temp = o;     o = align_up(o + sort_temp_bytes(P));
-        // depth sort: per-block compaction (dkeys_a = keys, order_tmp = ids, dkeys_b = tile rows) -> brec (binned records)
-        // -> order, runoff.  stat_slots are cleared by a memset node, bin_cur / bin_runs on the side by preprocess_fwd_kernel.
+        // depth sort: per-block compaction (dkeys_a = keys, order_tmp = ids, dkeys_b = rows, order = x-pack, crank = rank inside the
+        // bin) -> brec (binned records) -> order, runoff, srect.  stat_slots + bins64 are cleared by ONE memset node per frame.
         nbins = depth_bins(P);
-        stat_slots = o;    o = align_up(o + sizeof(FrameStatSlot) * kStatSlots);
         brec = o;          o = align_up(o + sizeof(uint4) * (size_t)P);
-        seg_tot = o;       o = align_up(o + sizeof(uint2) * 256);            // (records, runs) per scan segment of 1024 bins
+        crank = o;         o = align_up(o + sizeof(uint32_t) * (size_t)P);
+        seg_tot = o;       o = align_up(o + sizeof(uint2) * (size_t)(nbins / kSegBins));   // (records, runs) per scan segment
         runoff = o;        o = align_up(o + sizeof(uint32_t) * ((size_t)P + 1));
         srect = o;         o = align_up(o + sizeof(uint2) * (size_t)P);
-        bin_cur = o;       o = align_up(o + sizeof(uint32_t) * (size_t)nbins);
-        bin_runs = o;      o = align_up(o + sizeof(uint32_t) * (size_t)nbins);
+        bin_cnt = o;       o = align_up(o + sizeof(uint32_t) * (size_t)nbins);
+        stat_slots = o;    o = align_up(o + sizeof(FrameStatSlot) * kStatSlots);
+        bins64 = o;        o = align_up(o + sizeof(unsigned long long) * (size_t)nbins);      // directly behind stat_slots
         total = o;
     }
 };
@@ -117,7 +123,8 @@ struct GeomPtrs {
     float4* conic_opacity; float* rgb; uint32_t* tiles_touched; uint2* rects; uint32_t* block_sums; uint32_t* block_sums_r; uint32_t* block_sums_v;
     uint32_t* block_offsets;
     uint32_t *dkeys_a, *dkeys_b, *order_tmp, *order, *oblock_sums, *oblock_offsets; void* sort_temp; size_t sort_temp_bytes;
-    FrameStatSlot* stat_slots; uint4* brec; uint2* seg_tot; uint32_t *runoff, *bin_cur, *bin_runs; uint2* srect; size_t bin_zero_bytes;
+    FrameStatSlot* stat_slots; uint4* brec; uint2* seg_tot; uint32_t *runoff, *crank, *bin_cnt; unsigned long long* bins64; uint2* srect;
+    size_t frame_zero_bytes;      // stat_slots .. end of bins64: what the per-frame memset node clears
     int nblocks, nbins;
 };
 
@@ -146,8 +153,8 @@ inline GeomPtrs geom_ptrs(const void* buf, int P) {
     g.oblock_sums = (uint32_t*)(b + L.oblock_sums); g.oblock_offsets = (uint32_t*)(b + L.oblock_offsets);
     g.sort_temp = (void*)(b + L.sort_temp); g.sort_temp_bytes = sort_temp_bytes(P);
     g.stat_slots = (FrameStatSlot*)(b + L.stat_slots); g.brec = (uint4*)(b + L.brec); g.seg_tot = (uint2*)(b + L.seg_tot); g.runoff = (uint32_t*)(b + L.runoff);
-    g.bin_cur = (uint32_t*)(b + L.bin_cur); g.bin_runs = (uint32_t*)(b + L.bin_runs); g.srect = (uint2*)(b + L.srect);
-    g.bin_zero_bytes = L.total - L.bin_cur;               // bin_cur + bin_runs, contiguous, 256-byte aligned pieces
+    g.crank = (uint32_t*)(b + L.crank); g.bin_cnt = (uint32_t*)(b + L.bin_cnt); g.bins64 = (unsigned long long*)(b + L.bins64); g.srect = (uint2*)(b + L.srect);
+    g.frame_zero_bytes = L.total - L.stat_slots;
     g.nblocks = L.nblocks; g.nbins = L.nbins;
     return g;
 }
@@ -284,8 +291,8 @@ struct PreprocessArgs {
 };
 void launch_preprocess(const PreprocessArgs& a, const GeomPtrs& g, cudaStream_t s);
 void launch_block_scan(const GeomPtrs& g, int P, uint32_t* mailbox_dev, cudaStream_t s);
-// depth sort (gsr_depthsort.cu): bin histogram + scans, scatter into the bins, exact order inside every bin (+ run offsets)
-void launch_bin_hist(const GeomPtrs& g, int P, uint32_t* mailbox_dev, cudaStream_t s);
+// depth sort (gsr_depthsort.cu): scan of the bins counted by preprocess, scatter into the bins, exact order inside every bin (+ run offsets)
+void launch_bin_scan(const GeomPtrs& g, int P, uint32_t* mailbox_dev, cudaStream_t s);
 void launch_bin_scatter(const GeomPtrs& g, int P, cudaStream_t s);
 void launch_bin_sort(const GeomPtrs& g, int P, cudaStream_t s);
 void launch_runoff_from_blocks(const GeomPtrs& g, int P, cudaStream_t s);      // fallback: run offsets of an onesweep-sorted order

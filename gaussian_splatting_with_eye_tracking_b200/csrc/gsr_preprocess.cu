@@ -50,13 +50,15 @@ struct PreFwdParams {
     uint32_t* __restrict__ block_sums_v;    // per-CTA number of visible Gaussians; bit 31 = "a Gaussian was culled although
                                             // prefiltered" (the reference would __trap)
     uint4* zero_ptr; size_t zero_n16;       // scratch cleared on the side (grid-stride), see PreprocessArgs
-    uint4* zero_ptr2; size_t zero_n16_2;
     uint32_t* __restrict__ ckeys;           // per-block compaction of the visible Gaussians: depth key (float bits) ...
     uint32_t* __restrict__ cids;            // ... index ...
     uint32_t* __restrict__ crows;           // ... (y0 << 16) | tile rows the rect spans (= runs the Gaussian emits) ...
     uint32_t* __restrict__ cxw;             // ... and (x0 << 10) | width in tiles: what the run emission needs, so that it never
                                             // gathers rects[] through the sorted order
-    FrameStatSlot* stat_slots;              // [kStatSlots] key range, pair total, prefiltered-trap flag
+    uint32_t* __restrict__ crank;           // ... and its slot inside its depth bin (return value of the counting atomic)
+    FrameStatSlot* stat_slots;              // [kStatSlots] pair total, flags
+    unsigned long long* bins64;             // [nbins] (runs << 32) | records per depth bin, cleared by the frame's memset node
+    int nbins, depth_shift;
     GeomHeader* header;
     int prefiltered;
     int band_row0, band_row1;
@@ -215,7 +217,6 @@ __device__ __forceinline__ float3 cov2d_from_cov3d(float tx, float ty, float tz,
 __global__ void __launch_bounds__(kPreBlock, 4) preprocess_fwd_kernel(const PreFwdParams p) {
     __shared__ float sV[16], sPm[16], sCam[3];
     __shared__ uint32_t s_warp_sum[kPreBlock / 32], s_warp_sum_v[kPreBlock / 32];
-    __shared__ uint32_t s_warp_kmx[kPreBlock / 32], s_warp_kmn[kPreBlock / 32];
     const int tid = threadIdx.x;
     if (tid < 16) { sV[tid] = p.viewmatrix[tid]; sPm[tid] = p.projmatrix[tid]; }
     if (tid < 3) sCam[tid] = p.cam_pos[tid];
@@ -225,7 +226,6 @@ __global__ void __launch_bounds__(kPreBlock, 4) preprocess_fwd_kernel(const PreF
     uint32_t touched = 0, rows = 0, key = 0, ry0 = 0, rxw = 0;
     int radius = 0, trapped = 0;
     for (size_t i = (size_t)idx; i < p.zero_n16; i += (size_t)gridDim.x * kPreBlock) p.zero_ptr[i] = make_uint4(0u, 0u, 0u, 0u);
-    for (size_t i = (size_t)idx; i < p.zero_n16_2; i += (size_t)gridDim.x * kPreBlock) p.zero_ptr2[i] = make_uint4(0u, 0u, 0u, 0u);
 
     if (idx < p.P) {
         const float px = __ldg(p.means3D + 3 * (size_t)idx);
@@ -310,36 +310,40 @@ __global__ void __launch_bounds__(kPreBlock, 4) preprocess_fwd_kernel(const PreF
         rows = y1 - y0; ry0 = y0; rxw = (x0 << kRunX0Shift) | (x1 - x0);
     }
 
-    // ---- block-local compaction + frame statistics.
+    // ---- block-local compaction, depth-bin count, frame statistics.
     // There is no scan kernel and no global cursor: the visible Gaussians of this 256-block go to the FRONT of the block's
-    // own segment of (ckeys, cids, crows) and the block's count to block_sums_v -- the depth sort (gsr_depthsort.cu) walks
-    // blocks, not a dense array.  The key range and the pair total go to one of kStatSlots statistics lines (same-address
-    // atomics serialise at ~30 ns each: one hot word for 11 719 CTAs would cost more than the kernel itself).
+    // own segment of the compaction arrays and the block's count to block_sums_v -- the depth sort (gsr_depthsort.cu) walks
+    // blocks, not a dense array.  Every visible Gaussian also counts itself into its depth bin here (one 64-bit atomic:
+    // +1 record, +rows runs; the returned count is its slot inside the bin), spread over the kernel's whole HBM-bound run
+    // time instead of a pass of its own.  The pair total goes to one of kStatSlots statistics lines (same-address atomics
+    // serialise at ~30 ns each: one hot word for 11 719 CTAs would cost more than the kernel itself).
     uint32_t v = touched;
     const uint32_t vis_mask = __ballot_sync(0xffffffffu, touched != 0);
-    uint32_t kmx = touched ? key : 0u, kmn = touched ? ~key : 0u;
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-        v += __shfl_xor_sync(0xffffffffu, v, o);
-        kmx = max(kmx, __shfl_xor_sync(0xffffffffu, kmx, o)); kmn = max(kmn, __shfl_xor_sync(0xffffffffu, kmn, o));
+    uint32_t rank_in_bin = 0, beyond = 0;
+    if (touched) {
+        uint32_t bin = (key - kDepthKey0) >> p.depth_shift;
+        if (key < kDepthKey0 || bin >= (uint32_t)p.nbins) { bin = (uint32_t)p.nbins - 1u; beyond = 1u; }
+        rank_in_bin = (uint32_t)atomicAdd(p.bins64 + bin, ((unsigned long long)rows << 32) | 1ull);
     }
-    if ((tid & 31) == 0) { s_warp_sum[tid >> 5] = v; s_warp_sum_v[tid >> 5] = __popc(vis_mask); s_warp_kmx[tid >> 5] = kmx; s_warp_kmn[tid >> 5] = kmn; }
-    const int trap_any = __syncthreads_or(trapped);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if ((tid & 31) == 0) { s_warp_sum[tid >> 5] = v; s_warp_sum_v[tid >> 5] = __popc(vis_mask); }
+    const int flags_any = __syncthreads_or((trapped ? 1 : 0) | (beyond ? 2 : 0));
     if (touched) {
         uint32_t pos = __popc(vis_mask & ((1u << (tid & 31)) - 1u));
 #pragma unroll
         for (int w = 0; w < kPreBlock / 32; ++w) pos += (w < (tid >> 5)) ? s_warp_sum_v[w] : 0u;
         const size_t at = (size_t)blockIdx.x * kPreBlock + pos;
-        p.ckeys[at] = key; p.cids[at] = (uint32_t)idx; p.crows[at] = (ry0 << 16) | rows; p.cxw[at] = rxw;
+        p.ckeys[at] = key; p.cids[at] = (uint32_t)idx; p.crows[at] = (ry0 << 16) | rows; p.cxw[at] = rxw; p.crank[at] = rank_in_bin;
     }
     if (tid == 0) {
-        uint32_t s = 0, sv = 0, mx = 0, mn = 0;
+        uint32_t s = 0, sv = 0;
 #pragma unroll
-        for (int w = 0; w < kPreBlock / 32; ++w) { s += s_warp_sum[w]; sv += s_warp_sum_v[w]; mx = max(mx, s_warp_kmx[w]); mn = max(mn, s_warp_kmn[w]); }
+        for (int w = 0; w < kPreBlock / 32; ++w) { s += s_warp_sum[w]; sv += s_warp_sum_v[w]; }
         p.block_sums_v[blockIdx.x] = sv;
         FrameStatSlot* slot = p.stat_slots + (blockIdx.x & (kStatSlots - 1));
-        if (sv) { atomicMax(&slot->key_max, mx); atomicMax(&slot->key_min_inv, mn); atomicAdd(&slot->num_rendered, s); }
-        if (trap_any) atomicOr(&slot->flags, 1u);
+        if (sv) atomicAdd(&slot->num_rendered, s);
+        if (flags_any) atomicOr(&slot->flags, (uint32_t)flags_any);
     }
 }
 
@@ -358,8 +362,8 @@ void launch_preprocess(const PreprocessArgs& a, const GeomPtrs& g, cudaStream_t 
     p.block_sums = g.block_sums; p.header = g.header; p.prefiltered = a.prefiltered ? 1 : 0;
     p.band_row0 = a.band_row0; p.band_row1 = a.band_row1;
     p.zero_ptr = reinterpret_cast<uint4*>(a.zero_ptr); p.zero_n16 = a.zero_ptr ? a.zero_bytes / 16 : 0;
-    p.zero_ptr2 = reinterpret_cast<uint4*>(g.bin_cur); p.zero_n16_2 = g.bin_zero_bytes / 16;
-    p.ckeys = g.dkeys_a; p.cids = g.order_tmp; p.crows = g.dkeys_b; p.cxw = g.order; p.stat_slots = g.stat_slots;
+    p.ckeys = g.dkeys_a; p.cids = g.order_tmp; p.crows = g.dkeys_b; p.cxw = g.order; p.crank = g.crank; p.stat_slots = g.stat_slots;
+    p.bins64 = g.bins64; p.nbins = g.nbins; p.depth_shift = depth_shift(a.P);
     preprocess_fwd_kernel<<<g.nblocks, kPreBlock, 0, s>>>(p);
     count_launch();
 }
