@@ -69,8 +69,12 @@ constexpr int kDepthSpanLog2 = 28;
 constexpr int kBinCap = 512;                                  // records one warp orders by all-pairs ranking; fuller bin -> fallback
 constexpr int kSegBins = 1024;                                // bins per scan segment
 __host__ __device__ inline int index_bits(int P) { int b = 1; while (b < 31 && (1ll << b) < (long long)P) ++b; return b; }
-__host__ __device__ inline int depth_shift(int P) { int sh = 32 - index_bits(P); return sh > 10 ? 10 : (sh < 8 ? 8 : sh); }
-__host__ __device__ inline int depth_bins(int P) { return 1 << (kDepthSpanLog2 - depth_shift(P)); }       // 256 Ki .. 1 Mi
+// ~10 records per populated bin at the densities of trained scenes (measured on the 3 M-Gaussian bench scene: shift 8 -> mean 10,
+// max 83; shift 10 -> mean 33, max 270 and the all-pairs ranking of the full bins dominates the frame)
+__host__ __device__ inline int depth_shift(int P) { int sh = 30 - index_bits(P); return sh > 10 ? 10 : (sh < 6 ? 6 : sh); }
+__host__ __device__ inline int depth_bins(int P) { return 1 << (kDepthSpanLog2 - depth_shift(P)); }       // 256 Ki .. 4 Mi
+constexpr unsigned long long kBinPairBudget = 48ull << 20;    // sum of n^2 over the bins with more than 32 records above which the
+                                                              // frame takes the onesweep fallback (the all-pairs ranking would cost more)
 
 struct GeomLayout {
     size_t header, depths, clamped, radii, means2D, cov3D, conic_opacity, rgb, tiles_touched, rects,
@@ -107,7 +111,7 @@ struct GeomLayout {
         nbins = depth_bins(P);
         brec = o;          o = align_up(o + sizeof(uint4) * (size_t)P);
         crank = o;         o = align_up(o + sizeof(uint32_t) * (size_t)P);
-        seg_tot = o;       o = align_up(o + sizeof(uint2) * (size_t)(nbins / kSegBins));   // (records, runs) per scan segment
+        seg_tot = o;       o = align_up(o + sizeof(uint4) * (size_t)(nbins / kSegBins));   // (records, runs, n^2 of the full bins) per scan segment
         runoff = o;        o = align_up(o + sizeof(uint32_t) * ((size_t)P + 1));
         srect = o;         o = align_up(o + sizeof(uint2) * (size_t)P);
         bin_cnt = o;       o = align_up(o + sizeof(uint32_t) * (size_t)nbins);
@@ -123,7 +127,7 @@ struct GeomPtrs {
     float4* conic_opacity; float* rgb; uint32_t* tiles_touched; uint2* rects; uint32_t* block_sums; uint32_t* block_sums_r; uint32_t* block_sums_v;
     uint32_t* block_offsets;
     uint32_t *dkeys_a, *dkeys_b, *order_tmp, *order, *oblock_sums, *oblock_offsets; void* sort_temp; size_t sort_temp_bytes;
-    FrameStatSlot* stat_slots; uint4* brec; uint2* seg_tot; uint32_t *runoff, *crank, *bin_cnt; unsigned long long* bins64; uint2* srect;
+    FrameStatSlot* stat_slots; uint4* brec; uint4* seg_tot; uint32_t *runoff, *crank, *bin_cnt; unsigned long long* bins64; uint2* srect;
     size_t frame_zero_bytes;      // stat_slots .. end of bins64: what the per-frame memset node clears
     int nblocks, nbins;
 };
@@ -152,7 +156,7 @@ inline GeomPtrs geom_ptrs(const void* buf, int P) {
     g.order_tmp = (uint32_t*)(b + L.order_tmp); g.order = (uint32_t*)(b + L.order);
     g.oblock_sums = (uint32_t*)(b + L.oblock_sums); g.oblock_offsets = (uint32_t*)(b + L.oblock_offsets);
     g.sort_temp = (void*)(b + L.sort_temp); g.sort_temp_bytes = sort_temp_bytes(P);
-    g.stat_slots = (FrameStatSlot*)(b + L.stat_slots); g.brec = (uint4*)(b + L.brec); g.seg_tot = (uint2*)(b + L.seg_tot); g.runoff = (uint32_t*)(b + L.runoff);
+    g.stat_slots = (FrameStatSlot*)(b + L.stat_slots); g.brec = (uint4*)(b + L.brec); g.seg_tot = (uint4*)(b + L.seg_tot); g.runoff = (uint32_t*)(b + L.runoff);
     g.crank = (uint32_t*)(b + L.crank); g.bin_cnt = (uint32_t*)(b + L.bin_cnt); g.bins64 = (unsigned long long*)(b + L.bins64); g.srect = (uint2*)(b + L.srect);
     g.frame_zero_bytes = L.total - L.stat_slots;
     g.nblocks = L.nblocks; g.nbins = L.nbins;

@@ -47,37 +47,39 @@ static int ds_num_sms() {
 constexpr int kIlp = 4;                        // 256-blocks a thread of the scatter has in flight
 
 __global__ void __launch_bounds__(kSegBins) bin_scan_kernel(GeomHeader* hdr, const FrameStatSlot* __restrict__ slots, int P, int nbins,
-                                                            unsigned long long* bins64, uint32_t* __restrict__ bin_cnt, uint2* seg_tot,
+                                                            unsigned long long* bins64, uint32_t* __restrict__ bin_cnt, uint4* seg_tot,
                                                             uint32_t* runoff, int shift, int id_bits, uint32_t* mailbox) {
-    __shared__ uint32_t s_a[32], s_b[32], s_c[32];
+    __shared__ uint32_t s_a[32], s_b[32], s_c[32], s_d[32];
     __shared__ uint32_t s_last;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const int i = blockIdx.x * kSegBins + tid;
     const unsigned long long packed = bins64[i];
     const uint32_t c = (uint32_t)packed, r = (uint32_t)(packed >> 32);
     uint32_t ic = c, ir = r, mx = c;
+    uint32_t sq = c > 32u ? min(c, 0xffffu) * min(c, 0xffffu) : 0u;        // all-pairs cost of a bin the warp cannot rank in registers
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
         const uint32_t u = __shfl_up_sync(0xffffffffu, ic, o), v = __shfl_up_sync(0xffffffffu, ir, o);
         if (lane >= o) { ic += u; ir += v; }
     }
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    for (int o = 16; o > 0; o >>= 1) { mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o)); sq += __shfl_xor_sync(0xffffffffu, sq, o); }
     if (lane == 31) { s_a[wid] = ic; s_b[wid] = ir; }
-    if (lane == 0) s_c[wid] = mx;
+    if (lane == 0) { s_c[wid] = mx; s_d[wid] = sq; }
     __syncthreads();
-    uint32_t bc = 0, br = 0, tc = 0, tr = 0, maxbin = 0;
+    uint32_t bc = 0, br = 0, tc = 0, tr = 0, maxbin = 0, tsq = 0;
 #pragma unroll
     for (int w = 0; w < 32; ++w) {
         const uint32_t a = s_a[w], b = s_b[w];
         bc += (w < wid) ? a : 0u; br += (w < wid) ? b : 0u; tc += a; tr += b; maxbin = max(maxbin, s_c[w]);
+        tsq = (tsq + s_d[w] < tsq) ? 0xffffffffu : tsq + s_d[w];           // saturating
     }
     if (tc != 0u) {                                    // (segments without records keep their zeros: nobody reads them)
         bins64[i] = ((unsigned long long)(br + ir - r) << 32) | (unsigned long long)(bc + ic - c);   // (first run, first slot), relative
         bin_cnt[i] = c;
     } else bin_cnt[i] = 0u;
     if (tid == 0) {
-        seg_tot[blockIdx.x] = make_uint2(tc, tr);
+        seg_tot[blockIdx.x] = make_uint4(tc, tr, tsq, 0u);
         if (maxbin) atomicMax(&hdr->max_bin, maxbin);
         __threadfence();
         s_last = (atomicAdd(&hdr->done_hist, 1u) == gridDim.x - 1) ? 1u : 0u;
@@ -87,7 +89,12 @@ __global__ void __launch_bounds__(kSegBins) bin_scan_kernel(GeomHeader* hdr, con
     __threadfence();
     // ---- last CTA: frame totals
     uint32_t v = 0, rr = 0, pairs = 0, flags = 0;
-    for (int k = tid; k < (int)gridDim.x; k += kSegBins) { const uint2 t2 = __ldcg(seg_tot + k); v += t2.x; rr += t2.y; }
+    unsigned long long cost = 0;
+    for (int k = tid; k < (int)gridDim.x; k += kSegBins) { const uint4 t2 = __ldcg(seg_tot + k); v += t2.x; rr += t2.y; cost += t2.z; }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) cost += __shfl_xor_sync(0xffffffffu, cost, o);
+    __shared__ unsigned long long s_cost[32];
+    if (lane == 0) s_cost[wid] = cost;                 // summed by thread 0 behind the block-wide OR below
     if (tid < kStatSlots) { pairs = slots[tid].num_rendered; flags = slots[tid].flags; }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
@@ -101,7 +108,9 @@ __global__ void __launch_bounds__(kSegBins) bin_scan_kernel(GeomHeader* hdr, con
         uint32_t V = 0, R = 0, N = 0;
         for (int w = 0; w < 32; ++w) { V += s_a[w]; R += s_b[w]; N += s_c[w]; }
         const uint32_t mb = atomicMax(&hdr->max_bin, 0u);
-        const bool ok = mb <= (uint32_t)kBinCap && !(flags_any & 2);
+        unsigned long long pair_cost = 0;
+        for (int w = 0; w < 32; ++w) pair_cost += s_cost[w];
+        const bool ok = mb <= (uint32_t)kBinCap && !(flags_any & 2) && pair_cost <= kBinPairBudget;
         const uint32_t err = (flags_any & 1) ? 0x100u : 0u;
         hdr->magic = kGeomMagic; hdr->P = (uint32_t)P; hdr->num_rendered = N; hdr->num_runs = R; hdr->num_visible = V;
         hdr->sort_error = err; hdr->shift = (uint32_t)shift; hdr->sort_mode = ok ? 1u : 2u;
@@ -122,7 +131,7 @@ void launch_bin_scan(const GeomPtrs& g, int P, uint32_t* mailbox_dev, cudaStream
 }
 
 // exclusive prefix of the segment totals, by every consumer CTA for itself (<= 1024 segments): s_seg[k] = (records, runs) before segment k
-__device__ __forceinline__ void seg_base(const uint2* __restrict__ seg_tot, int nseg, uint2* s_seg) {
+__device__ __forceinline__ void seg_base(const uint4* __restrict__ seg_tot, int nseg, uint2* s_seg) {
     __shared__ uint2 s_w[32];
     __shared__ uint2 s_run;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
@@ -131,7 +140,7 @@ __device__ __forceinline__ void seg_base(const uint2* __restrict__ seg_tot, int 
     for (int base = 0; base < nseg; base += nthr) {
         const int k = base + tid;
         uint2 t = make_uint2(0u, 0u);
-        if (k < nseg) t = __ldcg(seg_tot + k);
+        if (k < nseg) { const uint4 t4 = __ldcg(seg_tot + k); t = make_uint2(t4.x, t4.y); }
         uint2 inc = t;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
@@ -161,7 +170,7 @@ __global__ void __launch_bounds__(1024) bin_scatter_kernel(const GeomHeader* __r
                                                            const uint32_t* __restrict__ block_vis, const uint32_t* __restrict__ ckeys,
                                                            const uint32_t* __restrict__ cids, const uint32_t* __restrict__ crows,
                                                            const uint32_t* __restrict__ cxw, const uint32_t* __restrict__ crank,
-                                                           const unsigned long long* __restrict__ bins64, const uint2* __restrict__ seg_tot,
+                                                           const unsigned long long* __restrict__ bins64, const uint4* __restrict__ seg_tot,
                                                            uint4* __restrict__ brec) {
     extern __shared__ uint2 s_seg[];                  // [nseg]
     if (hdr->sort_mode != 1u) return;
@@ -212,7 +221,7 @@ constexpr int kBinSortWarps = 8;
 // it -- the exclusive prefix of the tile rows in sorted order -- is accumulated in the same loop, so no inverse permutation
 // and no scan is needed.
 __global__ void __launch_bounds__(kBinSortWarps * 32) bin_sort_kernel(const GeomHeader* __restrict__ hdr, const unsigned long long* __restrict__ bins64,
-                                                                      const uint32_t* __restrict__ bin_cnt, const uint2* __restrict__ seg_tot,
+                                                                      const uint32_t* __restrict__ bin_cnt, const uint4* __restrict__ seg_tot,
                                                                       int nbins, const uint4* __restrict__ brec, uint32_t* __restrict__ order,
                                                                       uint32_t* __restrict__ runoff, uint2* __restrict__ srect) {
     extern __shared__ uint2 s_seg[];                  // [nbins / kSegBins]
@@ -272,6 +281,7 @@ __global__ void __launch_bounds__(kBinSortWarps * 32) bin_sort_kernel(const Geom
                 for (int i = lane; i < n; i += 32) {
                     const uint4 q = __ldg(brec + start + i);
                     uint32_t rank = 0, before = 0;
+#pragma unroll 4
                     for (int j = 0; j < n; ++j) {
                         const uint4 o = __ldg(brec + start + j);
                         const bool lt = o.x < q.x || (!comp32 && o.x == q.x && o.w < q.w);
