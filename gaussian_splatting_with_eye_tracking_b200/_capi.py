@@ -48,7 +48,9 @@ class GsrGaze(C.Structure):
 class GsrGrads(C.Structure):
     _fields_ = [(n, C.c_void_p) for n in (
         "dL_dmeans2D", "dL_dcolors", "dL_dopacity", "dL_dmeans3D", "dL_dcov3D", "dL_dsh", "dL_dscales",
-        "dL_drotations", "dL_dconic", "scratch", "dL_dcolors_clamped")]
+        "dL_drotations", "dL_dconic", "scratch", "dL_dcolors_clamped")] + [
+        ("push_bases", C.c_void_p), ("push_offset", C.c_size_t), ("push_rank", C.c_int), ("push_world", C.c_int),
+        ("push_rows_per_rank", C.c_int)]
 
 
 class GsrAdamTensor(C.Structure):
@@ -116,6 +118,9 @@ SYMBOLS = {
     "gsr_adam_step": (C.c_int, [C.POINTER(GsrAdamTensor), C.c_int, C.c_double, C.c_double, C.c_double, C.c_void_p]),
     "gsr_peer_flag_bytes": (C.c_size_t, [C.c_int]),
     "gsr_peer_barrier": (C.c_int, [C.c_void_p, C.c_size_t, C.c_int, C.c_int, C.c_uint, C.c_void_p]),
+    "gsr_peer_owner_sum": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t, C.c_int, C.c_int, C.c_void_p, C.c_size_t, C.c_size_t,
+                                     C.c_int, C.c_int, C.c_uint, C.c_void_p]),
+    "gsr_peer_error": (C.c_int, []),
     "gsr_peer_allreduce_sum": (C.c_int, [C.c_void_p, C.c_size_t, C.c_longlong, C.c_size_t, C.c_int, C.c_int, C.c_uint, C.c_void_p]),
     "gsr_peer_allreduce_sum_mc": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_longlong, C.c_size_t, C.c_int, C.c_int, C.c_uint, C.c_void_p]),
     "gsr_launch_count": (C.c_ulonglong, []),

@@ -341,6 +341,7 @@ const char* gsr_last_error(void) { return g_err; }
 int gsr_set_option(int option, int value) {
     if (option == GSR_OPT_SORT_VARIANT && value >= 0 && value <= 5) { set_sort_variant(value); return GSR_OK; }
     if (option == GSR_OPT_BLEND_VARIANT && value >= 0 && value <= 1) { set_blend_variant(value); return GSR_OK; }
+    if (option == GSR_OPT_PEER_TIMEOUT_MS && value >= 0) { set_peer_timeout_ms(value); return GSR_OK; }
     if (option == GSR_OPT_NVTX && (value == 0 || value == 1)) { set_nvtx(value); return GSR_OK; }
     if (option == GSR_OPT_FAKE_SORT_ERROR && (value == 0 || value == 1)) { set_fake_sort_error(value); return GSR_OK; }
     if (option == GSR_OPT_FORCE_SORT_FALLBACK && (value == 0 || value == 1)) { g_force_sort_fallback = value; return GSR_OK; }
@@ -418,6 +419,12 @@ static int backward_impl(const gsr_scene* sc, const gsr_camera* cam, const int* 
         set_error("gradient output pointers are required"); return GSR_ERR_INVALID;
     }
     if (((size_t)gr->scratch & 15) != 0) { set_error("scratch must be 16-byte aligned"); return GSR_ERR_INVALID; }
+    if (gr->push_bases && (gr->push_world < 1 || gr->push_rank < 0 || gr->push_rank >= gr->push_world || gr->push_rows_per_rank <= 0 ||
+                           (gr->push_rows_per_rank % 256) != 0 || (gr->push_offset & 15) != 0 ||
+                           (long long)gr->push_rows_per_rank * gr->push_world < (long long)P)) {
+        set_error("bad push_* fields (world %d, rank %d, rows per rank %d for P = %d)", gr->push_world, gr->push_rank, gr->push_rows_per_rank, P);
+        return GSR_ERR_INVALID;
+    }
     GeomPtrs g = geom_ptrs(geom_buffer, P);
     ImgPtrs im = img_ptrs(image_buffer, W, H, GSR_MODE_BASELINE);
     if (!radii) radii = g.radii;

@@ -79,7 +79,7 @@ constexpr unsigned long long kBinPairBudget = 48ull << 20;    // sum of n^2 over
 struct GeomLayout {
     size_t header, depths, clamped, radii, means2D, cov3D, conic_opacity, rgb, tiles_touched, rects,
            block_sums, block_sums_r, block_sums_v, block_offsets, dkeys_a, dkeys_b, order_tmp, order, oblock_sums, oblock_offsets, sort_temp,
-           stat_slots, brec, crank, seg_tot, runoff, srect, bins64, bin_cnt, total;
+           stat_slots, brec, crank, seg_tot, seg_pre, runoff, srect, bins64, bin_cnt, total;
     int nblocks, nbins;
     __host__ __device__ explicit GeomLayout(int P) {
         nblocks = (P + kPreBlock - 1) / kPreBlock;
@@ -111,7 +111,8 @@ struct GeomLayout {
         nbins = depth_bins(P);
         brec = o;          o = align_up(o + sizeof(uint4) * (size_t)P);
         crank = o;         o = align_up(o + sizeof(uint32_t) * (size_t)P);
-        seg_tot = o;       o = align_up(o + sizeof(uint4) * (size_t)(nbins / kSegBins));   // (records, runs, n^2 of the full bins) per scan segment
+        seg_tot = o;       o = align_up(o + sizeof(uint4) * (size_t)(nbins / kSegBins));   // (records, runs, n^2 of the full bins, fullest bin) per scan segment
+        seg_pre = o;       o = align_up(o + sizeof(uint2) * (size_t)(nbins / kSegBins));   // exclusive prefix of (records, runs) over the segments
         runoff = o;        o = align_up(o + sizeof(uint32_t) * ((size_t)P + 1));
         srect = o;         o = align_up(o + sizeof(uint2) * (size_t)P);
         bin_cnt = o;       o = align_up(o + sizeof(uint32_t) * (size_t)nbins);
@@ -127,7 +128,7 @@ struct GeomPtrs {
     float4* conic_opacity; float* rgb; uint32_t* tiles_touched; uint2* rects; uint32_t* block_sums; uint32_t* block_sums_r; uint32_t* block_sums_v;
     uint32_t* block_offsets;
     uint32_t *dkeys_a, *dkeys_b, *order_tmp, *order, *oblock_sums, *oblock_offsets; void* sort_temp; size_t sort_temp_bytes;
-    FrameStatSlot* stat_slots; uint4* brec; uint4* seg_tot; uint32_t *runoff, *crank, *bin_cnt; unsigned long long* bins64; uint2* srect;
+    FrameStatSlot* stat_slots; uint4* brec; uint4* seg_tot; uint2* seg_pre; uint32_t *runoff, *crank, *bin_cnt; unsigned long long* bins64; uint2* srect;
     size_t frame_zero_bytes;      // stat_slots .. end of bins64: what the per-frame memset node clears
     int nblocks, nbins;
 };
@@ -156,7 +157,7 @@ inline GeomPtrs geom_ptrs(const void* buf, int P) {
     g.order_tmp = (uint32_t*)(b + L.order_tmp); g.order = (uint32_t*)(b + L.order);
     g.oblock_sums = (uint32_t*)(b + L.oblock_sums); g.oblock_offsets = (uint32_t*)(b + L.oblock_offsets);
     g.sort_temp = (void*)(b + L.sort_temp); g.sort_temp_bytes = sort_temp_bytes(P);
-    g.stat_slots = (FrameStatSlot*)(b + L.stat_slots); g.brec = (uint4*)(b + L.brec); g.seg_tot = (uint4*)(b + L.seg_tot); g.runoff = (uint32_t*)(b + L.runoff);
+    g.stat_slots = (FrameStatSlot*)(b + L.stat_slots); g.brec = (uint4*)(b + L.brec); g.seg_tot = (uint4*)(b + L.seg_tot); g.seg_pre = (uint2*)(b + L.seg_pre); g.runoff = (uint32_t*)(b + L.runoff);
     g.crank = (uint32_t*)(b + L.crank); g.bin_cnt = (uint32_t*)(b + L.bin_cnt); g.bins64 = (unsigned long long*)(b + L.bins64); g.srect = (uint2*)(b + L.srect);
     g.frame_zero_bytes = L.total - L.stat_slots;
     g.nblocks = L.nblocks; g.nbins = L.nbins;
@@ -343,6 +344,7 @@ void launch_zero(void* ptr, size_t bytes, cudaStream_t s);   // bytes % 16 == 0,
 void set_sort_variant(int v);
 void set_blend_variant(int v);
 void set_peer_ctas_per_sm(int v);   // gsr_peer.cu: grid cap of the reduce kernels in CTAs per SM; 0 = default
+void set_peer_timeout_ms(int v);    // gsr_peer.cu: barrier watchdog
 
 void launch_amr_levels(const ImgPtrs& im, int num_tiles, cudaStream_t s);
 void launch_fovea_levels(const ImgPtrs& im, int num_tiles, int fovea_step, const gsr_gaze* gaze, cudaStream_t s);

@@ -41,22 +41,20 @@ static int ds_num_sms() {
 
 // ------------------------------------------------------------------------------------------------
 // scan: one CTA per segment of 1024 bins -- exclusive prefix of records / runs INSIDE the segment + the segment's totals.
-// Consumers add the exclusive prefix of the segment totals themselves (seg_base()).  The CTA that finishes last sums the
-// totals and the statistics slots and posts the frame's counts where the host reads them.
+// Consumers add the exclusive prefix of the segment totals themselves (seg_base()).  No atomics, no "last CTA" ticket: a
+// thousand CTAs bumping one counter would serialise for longer than the scan takes (same-address atomics: ~30 ns each); the
+// frame totals are taken by the one-CTA bin_totals_kernel behind it.
 // ------------------------------------------------------------------------------------------------
 constexpr int kIlp = 4;                        // 256-blocks a thread of the scatter has in flight
 
-__global__ void __launch_bounds__(kSegBins) bin_scan_kernel(GeomHeader* hdr, const FrameStatSlot* __restrict__ slots, int P, int nbins,
-                                                            unsigned long long* bins64, uint32_t* __restrict__ bin_cnt, uint4* seg_tot,
-                                                            uint32_t* runoff, int shift, int id_bits, uint32_t* mailbox) {
+__global__ void __launch_bounds__(kSegBins) bin_scan_kernel(unsigned long long* bins64, uint32_t* __restrict__ bin_cnt, uint4* __restrict__ seg_tot) {
     __shared__ uint32_t s_a[32], s_b[32], s_c[32], s_d[32];
-    __shared__ uint32_t s_last;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const int i = blockIdx.x * kSegBins + tid;
     const unsigned long long packed = bins64[i];
     const uint32_t c = (uint32_t)packed, r = (uint32_t)(packed >> 32);
     uint32_t ic = c, ir = r, mx = c;
-    uint32_t sq = c > 32u ? min(c, 0xffffu) * min(c, 0xffffu) : 0u;        // all-pairs cost of a bin the warp cannot rank in registers
+    uint32_t sq = c > 32u ? min(c, 0xffffu) * min(c, 0xffffu) : 0u;        // all-pairs cost of a bin too full for one thread
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
         const uint32_t u = __shfl_up_sync(0xffffffffu, ic, o), v = __shfl_up_sync(0xffffffffu, ir, o);
@@ -74,89 +72,77 @@ __global__ void __launch_bounds__(kSegBins) bin_scan_kernel(GeomHeader* hdr, con
         bc += (w < wid) ? a : 0u; br += (w < wid) ? b : 0u; tc += a; tr += b; maxbin = max(maxbin, s_c[w]);
         tsq = (tsq + s_d[w] < tsq) ? 0xffffffffu : tsq + s_d[w];           // saturating
     }
-    if (tc != 0u) {                                    // (segments without records keep their zeros: nobody reads them)
-        bins64[i] = ((unsigned long long)(br + ir - r) << 32) | (unsigned long long)(bc + ic - c);   // (first run, first slot), relative
-        bin_cnt[i] = c;
-    } else bin_cnt[i] = 0u;
-    if (tid == 0) {
-        seg_tot[blockIdx.x] = make_uint4(tc, tr, tsq, 0u);
-        if (maxbin) atomicMax(&hdr->max_bin, maxbin);
-        __threadfence();
-        s_last = (atomicAdd(&hdr->done_hist, 1u) == gridDim.x - 1) ? 1u : 0u;
-    }
-    __syncthreads();
-    if (!s_last) return;
-    __threadfence();
-    // ---- last CTA: frame totals
-    uint32_t v = 0, rr = 0, pairs = 0, flags = 0;
-    unsigned long long cost = 0;
-    for (int k = tid; k < (int)gridDim.x; k += kSegBins) { const uint4 t2 = __ldcg(seg_tot + k); v += t2.x; rr += t2.y; cost += t2.z; }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) cost += __shfl_xor_sync(0xffffffffu, cost, o);
+    if (tc != 0u) bins64[i] = ((unsigned long long)(br + ir - r) << 32) | (unsigned long long)(bc + ic - c);   // (first run, first slot), relative
+    bin_cnt[i] = c;
+    if (tid == 0) seg_tot[blockIdx.x] = make_uint4(tc, tr, tsq, maxbin);
+}
+
+// frame totals: one CTA sums the segment totals and the statistics slots and posts the counts where the host reads them
+__global__ void __launch_bounds__(1024) bin_totals_kernel(GeomHeader* hdr, const FrameStatSlot* __restrict__ slots, int P, int nseg,
+                                                          const uint4* __restrict__ seg_tot, uint2* __restrict__ seg_pre, uint32_t* runoff,
+                                                          int shift, int id_bits, uint32_t* mailbox) {
+    __shared__ uint32_t s_a[32], s_b[32], s_c[32], s_d[32];
     __shared__ unsigned long long s_cost[32];
-    if (lane == 0) s_cost[wid] = cost;                 // summed by thread 0 behind the block-wide OR below
-    if (tid < kStatSlots) { pairs = slots[tid].num_rendered; flags = slots[tid].flags; }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-        v += __shfl_xor_sync(0xffffffffu, v, o); rr += __shfl_xor_sync(0xffffffffu, rr, o);
-        pairs += __shfl_xor_sync(0xffffffffu, pairs, o); flags |= __shfl_xor_sync(0xffffffffu, flags, o);
-    }
-    __syncthreads();
-    if (lane == 0) { s_a[wid] = v; s_b[wid] = rr; s_c[wid] = pairs; }
-    const int flags_any = __syncthreads_or((int)flags);
-    if (tid == 0) {
-        uint32_t V = 0, R = 0, N = 0;
-        for (int w = 0; w < 32; ++w) { V += s_a[w]; R += s_b[w]; N += s_c[w]; }
-        const uint32_t mb = atomicMax(&hdr->max_bin, 0u);
-        unsigned long long pair_cost = 0;
-        for (int w = 0; w < 32; ++w) pair_cost += s_cost[w];
-        const bool ok = mb <= (uint32_t)kBinCap && !(flags_any & 2) && pair_cost <= kBinPairBudget;
-        const uint32_t err = (flags_any & 1) ? 0x100u : 0u;
-        hdr->magic = kGeomMagic; hdr->P = (uint32_t)P; hdr->num_rendered = N; hdr->num_runs = R; hdr->num_visible = V;
-        hdr->sort_error = err; hdr->shift = (uint32_t)shift; hdr->sort_mode = ok ? 1u : 2u;
-        hdr->comp32 = (shift + id_bits <= 32) ? 1u : 0u;
-        runoff[V] = R;                                 // read by the run emission of the last block of sorted positions
-        if (mailbox) {   // mapped pinned host memory: the host reads the totals without a DMA copy; posted PCIe writes stay
-                         // ordered and the host reads after an event recorded behind this kernel
-            volatile uint32_t* m = mailbox;
-            m[0] = kGeomMagic; m[1] = (uint32_t)P; m[2] = N; m[3] = err; m[4] = R; m[5] = V; m[6] = ok ? 1u : 2u; m[7] = mb;
-        }
-    }
-}
-
-void launch_bin_scan(const GeomPtrs& g, int P, uint32_t* mailbox_dev, cudaStream_t s) {
-    bin_scan_kernel<<<g.nbins / kSegBins, kSegBins, 0, s>>>(g.header, g.stat_slots, P, g.nbins, g.bins64, g.bin_cnt, g.seg_tot, g.runoff,
-                                                           depth_shift(P), index_bits(P), mailbox_dev);
-    count_launch();
-}
-
-// exclusive prefix of the segment totals, by every consumer CTA for itself (<= 1024 segments): s_seg[k] = (records, runs) before segment k
-__device__ __forceinline__ void seg_base(const uint4* __restrict__ seg_tot, int nseg, uint2* s_seg) {
     __shared__ uint2 s_w[32];
     __shared__ uint2 s_run;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-    const int nthr = blockDim.x, nw = nthr / 32;
+    // exclusive prefix of the segment totals (records, runs): what the scatter and the per-bin sort add to segment-relative offsets
     if (tid == 0) s_run = make_uint2(0u, 0u);
-    for (int base = 0; base < nseg; base += nthr) {
+    for (int base = 0; base < nseg; base += 1024) {
         const int k = base + tid;
         uint2 t = make_uint2(0u, 0u);
-        if (k < nseg) { const uint4 t4 = __ldcg(seg_tot + k); t = make_uint2(t4.x, t4.y); }
+        if (k < nseg) { const uint4 t4 = seg_tot[k]; t = make_uint2(t4.x, t4.y); }
         uint2 inc = t;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
-            const uint32_t u = __shfl_up_sync(0xffffffffu, inc.x, o), v = __shfl_up_sync(0xffffffffu, inc.y, o);
-            if (lane >= o) { inc.x += u; inc.y += v; }
+            const uint32_t u = __shfl_up_sync(0xffffffffu, inc.x, o), v2 = __shfl_up_sync(0xffffffffu, inc.y, o);
+            if (lane >= o) { inc.x += u; inc.y += v2; }
         }
         __syncthreads();
         if (lane == 31) s_w[wid] = inc;
         __syncthreads();
         uint2 b = s_run, tot = make_uint2(0u, 0u);
-        for (int w = 0; w < nw; ++w) { const uint2 x = s_w[w]; if (w < wid) { b.x += x.x; b.y += x.y; } tot.x += x.x; tot.y += x.y; }
-        if (k < nseg) s_seg[k] = make_uint2(b.x + inc.x - t.x, b.y + inc.y - t.y);
+        for (int w = 0; w < 32; ++w) { const uint2 x = s_w[w]; if (w < wid) { b.x += x.x; b.y += x.y; } tot.x += x.x; tot.y += x.y; }
+        if (k < nseg) seg_pre[k] = make_uint2(b.x + inc.x - t.x, b.y + inc.y - t.y);
         __syncthreads();
         if (tid == 0) { s_run.x += tot.x; s_run.y += tot.y; }
     }
     __syncthreads();
+    uint32_t v = 0, rr = 0, pairs = 0, flags = 0, mb = 0;
+    unsigned long long cost = 0;
+    for (int k = tid; k < nseg; k += 1024) { const uint4 t = seg_tot[k]; v += t.x; rr += t.y; cost += t.z; mb = max(mb, t.w); }
+    if (tid < kStatSlots) { pairs = slots[tid].num_rendered; flags = slots[tid].flags; }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        v += __shfl_xor_sync(0xffffffffu, v, o); rr += __shfl_xor_sync(0xffffffffu, rr, o); cost += __shfl_xor_sync(0xffffffffu, cost, o);
+        pairs += __shfl_xor_sync(0xffffffffu, pairs, o); flags |= __shfl_xor_sync(0xffffffffu, flags, o);
+        mb = max(mb, __shfl_xor_sync(0xffffffffu, mb, o));
+    }
+    if (lane == 0) { s_a[wid] = v; s_b[wid] = rr; s_c[wid] = pairs; s_d[wid] = mb; s_cost[wid] = cost; }
+    const int flags_any = __syncthreads_or((int)flags);
+    if (tid == 0) {
+        uint32_t V = 0, R = 0, N = 0, maxbin = 0;
+        unsigned long long pair_cost = 0;
+        for (int w = 0; w < 32; ++w) { V += s_a[w]; R += s_b[w]; N += s_c[w]; maxbin = max(maxbin, s_d[w]); pair_cost += s_cost[w]; }
+        const bool ok = maxbin <= (uint32_t)kBinCap && !(flags_any & 2) && pair_cost <= kBinPairBudget;
+        const uint32_t err = (flags_any & 1) ? 0x100u : 0u;
+        hdr->magic = kGeomMagic; hdr->P = (uint32_t)P; hdr->num_rendered = N; hdr->num_runs = R; hdr->num_visible = V;
+        hdr->sort_error = err; hdr->shift = (uint32_t)shift; hdr->sort_mode = ok ? 1u : 2u; hdr->max_bin = maxbin;
+        hdr->comp32 = (shift + id_bits <= 32) ? 1u : 0u;
+        runoff[V] = R;                                 // read by the run emission of the last block of sorted positions
+        if (mailbox) {   // mapped pinned host memory: the host reads the totals without a DMA copy; posted PCIe writes stay
+                         // ordered and the host reads after an event recorded behind this kernel
+            volatile uint32_t* m = mailbox;
+            m[0] = kGeomMagic; m[1] = (uint32_t)P; m[2] = N; m[3] = err; m[4] = R; m[5] = V; m[6] = ok ? 1u : 2u; m[7] = maxbin;
+        }
+    }
+}
+
+void launch_bin_scan(const GeomPtrs& g, int P, uint32_t* mailbox_dev, cudaStream_t s) {
+    const int nseg = g.nbins / kSegBins;
+    bin_scan_kernel<<<nseg, kSegBins, 0, s>>>(g.bins64, g.bin_cnt, g.seg_tot);
+    bin_totals_kernel<<<1, 1024, 0, s>>>(g.header, g.stat_slots, P, nseg, g.seg_tot, g.seg_pre, g.runoff, depth_shift(P), index_bits(P), mailbox_dev);
+    count_launch(2);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -165,21 +151,19 @@ __device__ __forceinline__ void seg_base(const uint4* __restrict__ seg_tot, int 
 // record = (composite, (y0 << 16) | rows, (x0 << 10) | width, id).  composite = position of the key inside its bin (low `shift`
 // key bits) above the id bits when that fits 32 bits (hdr->comp32), so that one 32-bit compare orders (depth, index);
 // otherwise the full key (ties then compare the id word).  Slot = first slot of the bin + the count the preprocess kernel's
-// atomic returned: no atomics here.
-__global__ void __launch_bounds__(1024) bin_scatter_kernel(const GeomHeader* __restrict__ hdr, int nblocks, int nseg, int id_bits,
-                                                           const uint32_t* __restrict__ block_vis, const uint32_t* __restrict__ ckeys,
-                                                           const uint32_t* __restrict__ cids, const uint32_t* __restrict__ crows,
-                                                           const uint32_t* __restrict__ cxw, const uint32_t* __restrict__ crank,
-                                                           const unsigned long long* __restrict__ bins64, const uint4* __restrict__ seg_tot,
-                                                           uint4* __restrict__ brec) {
-    extern __shared__ uint2 s_seg[];                  // [nseg]
+// atomic returned: no atomics here.  One 256-Gaussian block per CTA iteration, kIlp blocks in flight.
+__global__ void __launch_bounds__(kPreBlock) bin_scatter_kernel(const GeomHeader* __restrict__ hdr, int nblocks, int nseg, int id_bits,
+                                                                const uint32_t* __restrict__ block_vis, const uint32_t* __restrict__ ckeys,
+                                                                const uint32_t* __restrict__ cids, const uint32_t* __restrict__ crows,
+                                                                const uint32_t* __restrict__ cxw, const uint32_t* __restrict__ crank,
+                                                                const unsigned long long* __restrict__ bins64, const uint2* __restrict__ seg_pre,
+                                                                uint4* __restrict__ brec) {
     if (hdr->sort_mode != 1u) return;
-    seg_base(seg_tot, nseg, s_seg);
     const uint32_t shift = hdr->shift, comp32 = hdr->comp32;
     const uint32_t low = (1u << shift) - 1u;
-    const int sub = threadIdx.x >> 8, t = threadIdx.x & 255;
-    const int bstep = (int)gridDim.x * 4;
-    for (int b0 = (int)blockIdx.x * 4 + sub; b0 < nblocks; b0 += bstep * kIlp) {
+    const int t = threadIdx.x;
+    const int bstep = (int)gridDim.x;
+    for (int b0 = (int)blockIdx.x; b0 < nblocks; b0 += bstep * kIlp) {
         uint4 rec[kIlp]; uint32_t bin[kIlp], slot[kIlp]; bool on[kIlp];
 #pragma unroll
         for (int k = 0; k < kIlp; ++k) { const int b = b0 + k * bstep; on[k] = b < nblocks && (uint32_t)t < __ldg(block_vis + b); }
@@ -193,118 +177,102 @@ __global__ void __launch_bounds__(1024) bin_scatter_kernel(const GeomHeader* __r
             rec[k] = make_uint4(comp32 ? (((rel & low) << id_bits) | id) : key, __ldg(crows + i), __ldg(cxw + i), id);
         }
 #pragma unroll
-        for (int k = 0; k < kIlp; ++k) if (on[k]) slot[k] += s_seg[bin[k] / kSegBins].x + (uint32_t)__ldg(bins64 + bin[k]);
+        for (int k = 0; k < kIlp; ++k) if (on[k]) slot[k] += __ldg(seg_pre + bin[k] / kSegBins).x + (uint32_t)__ldg(bins64 + bin[k]);
 #pragma unroll
         for (int k = 0; k < kIlp; ++k) if (on[k]) brec[slot[k]] = rec[k];
     }
 }
 
 void launch_bin_scatter(const GeomPtrs& g, int P, cudaStream_t s) {
-    int grid = (g.nblocks + 4 * kIlp - 1) / (4 * kIlp);
-    const int cap = ds_num_sms() * 2;
+    int grid = (g.nblocks + kIlp - 1) / kIlp;
+    const int cap = ds_num_sms() * 8;
     if (grid > cap) grid = cap;
     if (grid < 1) grid = 1;
     const int nseg = g.nbins / kSegBins;
-    bin_scatter_kernel<<<grid, 1024, sizeof(uint2) * nseg, s>>>(g.header, g.nblocks, nseg, index_bits(P), g.block_sums_v, g.dkeys_a, g.order_tmp,
-                                                              g.dkeys_b, g.order, g.crank, g.bins64, g.seg_tot, g.brec);
+    bin_scatter_kernel<<<grid, kPreBlock, 0, s>>>(g.header, g.nblocks, nseg, index_bits(P), g.block_sums_v, g.dkeys_a, g.order_tmp,
+                                                  g.dkeys_b, g.order, g.crank, g.bins64, g.seg_pre, g.brec);
     count_launch();
 }
 
 // ------------------------------------------------------------------------------------------------
 // exact order inside every bin + run offsets
 // ------------------------------------------------------------------------------------------------
-constexpr int kBinSortWarps = 8;
+constexpr int kBinSortThreads = 256;
+constexpr int kBinThreadMax = 48;              // a bin up to this size is ordered by its own thread; fuller ones by the whole warp
 
-// A warp takes 32 consecutive bins per step (one coalesced look-up of their counts) and then one non-empty bin at a time, the
-// next bin's records already in flight.  Every lane ranks its record against the bin's others and PUSHES its outputs to slot
-// start + rank (the bin's slots are one short contiguous stretch); the number of runs emitted by the records ordered before
-// it -- the exclusive prefix of the tile rows in sorted order -- is accumulated in the same loop, so no inverse permutation
-// and no scan is needed.
-__global__ void __launch_bounds__(kBinSortWarps * 32) bin_sort_kernel(const GeomHeader* __restrict__ hdr, const unsigned long long* __restrict__ bins64,
-                                                                      const uint32_t* __restrict__ bin_cnt, const uint4* __restrict__ seg_tot,
-                                                                      int nbins, const uint4* __restrict__ brec, uint32_t* __restrict__ order,
-                                                                      uint32_t* __restrict__ runoff, uint2* __restrict__ srect) {
-    extern __shared__ uint2 s_seg[];                  // [nbins / kSegBins]
+// A THREAD per bin (a populated bin holds ~10 records): for each of its records the thread counts the records of the bin
+// that order before it -- composites re-read through the L1, n^2 compares -- and, in the same loop, the runs those records
+// emit; it then writes the record's id, the absolute offset of its first run and its rect to slot start + rank.  A warp per
+// bin (the round-2 first attempt) left each warp with a chain of ~20 dependent L2 round trips and 30 % of its lanes busy;
+// here a million threads are in flight and the latencies overlap.  Bins with more than kBinThreadMax records are taken by
+// the whole warp afterwards, one at a time (all-pairs with the candidates strided over the lanes).
+__global__ void __launch_bounds__(kBinSortThreads) bin_sort_kernel(const GeomHeader* __restrict__ hdr, const unsigned long long* __restrict__ bins64,
+                                                                   const uint32_t* __restrict__ bin_cnt, const uint2* __restrict__ seg_pre,
+                                                                   int nbins, const uint4* __restrict__ brec, uint32_t* __restrict__ order,
+                                                                   uint32_t* __restrict__ runoff, uint2* __restrict__ srect) {
     if (hdr->sort_mode != 1u) return;
-    seg_base(seg_tot, nbins / kSegBins, s_seg);
     const bool comp32 = hdr->comp32 != 0u;
-    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    const int warp_global = blockIdx.x * kBinSortWarps + wid, warps_total = gridDim.x * kBinSortWarps;
-    const int ngroups = nbins / 32;
-    // groups of 32 bins are dealt round-robin: neighbouring (similarly loaded) groups go to different warps
-    for (int grp = warp_global; grp < ngroups; grp += warps_total) {
-        const int bin = grp * 32 + lane;
-        const uint32_t cnt = __ldg(bin_cnt + bin);
-        uint32_t mask = __ballot_sync(0xffffffffu, cnt != 0u);
-        if (mask == 0u) continue;
-        uint32_t my_start = 0, my_run0 = 0;
-        if (cnt) {
+    const int lane = threadIdx.x & 31;
+    for (int bin0 = blockIdx.x * kBinSortThreads; bin0 < nbins; bin0 += gridDim.x * kBinSortThreads) {
+        const int bin = bin0 + threadIdx.x;             // nbins is a multiple of 1024: always in range
+        const int n = (int)__ldg(bin_cnt + bin);
+        uint32_t start = 0, run0 = 0;
+        if (n) {
             const unsigned long long sr = __ldg(bins64 + bin);
-            const uint2 sb = s_seg[bin / kSegBins];
-            my_start = sb.x + (uint32_t)sr; my_run0 = sb.y + (uint32_t)(sr >> 32);
+            const uint2 sb = __ldg(seg_pre + bin / kSegBins);
+            start = sb.x + (uint32_t)sr; run0 = sb.y + (uint32_t)(sr >> 32);
         }
-        int k = __ffs(mask) - 1;
-        int n = (int)__shfl_sync(0xffffffffu, cnt, k);
-        uint32_t start = __shfl_sync(0xffffffffu, my_start, k), run0 = __shfl_sync(0xffffffffu, my_run0, k);
-        uint4 r = make_uint4(0xffffffffu, 0u, 0u, 0xffffffffu);
-        if (lane < n && n <= 32) r = __ldg(brec + start + lane);
-        while (true) {
-            mask &= mask - 1u;
-            // the next non-empty bin of the group: its records are requested before this bin's are ranked
-            int k2 = 0, n2 = 0; uint32_t start2 = 0, run02 = 0;
-            uint4 r2 = make_uint4(0xffffffffu, 0u, 0u, 0xffffffffu);
-            if (mask) {
-                k2 = __ffs(mask) - 1;
-                n2 = (int)__shfl_sync(0xffffffffu, cnt, k2);
-                start2 = __shfl_sync(0xffffffffu, my_start, k2); run02 = __shfl_sync(0xffffffffu, my_run0, k2);
-                if (lane < n2 && n2 <= 32) r2 = __ldg(brec + start2 + lane);
-            }
-            if (n <= 32) {
-                const uint32_t h = r.y & 0xffffu;
+        if (n > 0 && n <= kBinThreadMax) {
+            for (int i = 0; i < n; ++i) {
+                const uint4 q = __ldg(brec + start + i);
                 uint32_t rank = 0, before = 0;
                 if (comp32) {
+#pragma unroll 4
                     for (int j = 0; j < n; ++j) {
-                        const uint32_t oc = __shfl_sync(0xffffffffu, r.x, j), oh = __shfl_sync(0xffffffffu, h, j);
-                        const bool lt = oc < r.x;
-                        rank += lt ? 1u : 0u; before += lt ? oh : 0u;
+                        const uint2 o = __ldg(reinterpret_cast<const uint2*>(brec + start + j));
+                        const bool lt = o.x < q.x;
+                        rank += lt ? 1u : 0u; before += lt ? (o.y & 0xffffu) : 0u;
                     }
                 } else {
                     for (int j = 0; j < n; ++j) {
-                        const uint32_t ok = __shfl_sync(0xffffffffu, r.x, j), oi = __shfl_sync(0xffffffffu, r.w, j), oh = __shfl_sync(0xffffffffu, h, j);
-                        const bool lt = ok < r.x || (ok == r.x && oi < r.w);
-                        rank += lt ? 1u : 0u; before += lt ? oh : 0u;
-                    }
-                }
-                if (lane < n) { const uint32_t at = start + rank; order[at] = r.w; runoff[at] = run0 + before; srect[at] = make_uint2(r.z, r.y >> 16); }
-            } else {
-                // 33 .. kBinCap records: the same all-pairs loop with the bin's records re-read through the L1
-                for (int i = lane; i < n; i += 32) {
-                    const uint4 q = __ldg(brec + start + i);
-                    uint32_t rank = 0, before = 0;
-#pragma unroll 4
-                    for (int j = 0; j < n; ++j) {
                         const uint4 o = __ldg(brec + start + j);
-                        const bool lt = o.x < q.x || (!comp32 && o.x == q.x && o.w < q.w);
+                        const bool lt = o.x < q.x || (o.x == q.x && o.w < q.w);
                         rank += lt ? 1u : 0u; before += lt ? (o.y & 0xffffu) : 0u;
                     }
-                    const uint32_t at = start + rank;
-                    order[at] = q.w; runoff[at] = run0 + before; srect[at] = make_uint2(q.z, q.y >> 16);
                 }
+                const uint32_t at = start + rank;
+                order[at] = q.w; runoff[at] = run0 + before; srect[at] = make_uint2(q.z, q.y >> 16);
             }
-            if (!mask) break;
-            k = k2; n = n2; start = start2; run0 = run02; r = r2;
+        }
+        // fuller bins: the warp takes them one by one
+        uint32_t big = __ballot_sync(0xffffffffu, n > kBinThreadMax);
+        while (big) {
+            const int k = __ffs(big) - 1;
+            big &= big - 1u;
+            const int nk = __shfl_sync(0xffffffffu, n, k);
+            const uint32_t st = __shfl_sync(0xffffffffu, start, k), r0 = __shfl_sync(0xffffffffu, run0, k);
+            for (int i = lane; i < nk; i += 32) {
+                const uint4 q = __ldg(brec + st + i);
+                uint32_t rank = 0, before = 0;
+#pragma unroll 4
+                for (int j = 0; j < nk; ++j) {
+                    const uint4 o = __ldg(brec + st + j);
+                    const bool lt = o.x < q.x || (!comp32 && o.x == q.x && o.w < q.w);
+                    rank += lt ? 1u : 0u; before += lt ? (o.y & 0xffffu) : 0u;
+                }
+                const uint32_t at = st + rank;
+                order[at] = q.w; runoff[at] = r0 + before; srect[at] = make_uint2(q.z, q.y >> 16);
+            }
         }
     }
 }
 
 void launch_bin_sort(const GeomPtrs& g, int P, cudaStream_t s) {
-    const int ngroups = g.nbins / 32;
-    int grid = (ngroups + kBinSortWarps * 2 - 1) / (kBinSortWarps * 2);
-    const int cap = ds_num_sms() * 8;                                           // 8 CTAs x 8 warps per SM
+    int grid = g.nbins / kBinSortThreads;
+    const int cap = ds_num_sms() * 8 * 4;                                       // a few waves of 8 CTAs per SM
     if (grid > cap) grid = cap;
     if (grid < 1) grid = 1;
-    bin_sort_kernel<<<grid, kBinSortWarps * 32, sizeof(uint2) * (g.nbins / kSegBins), s>>>(g.header, g.bins64, g.bin_cnt, g.seg_tot, g.nbins, g.brec,
-                                                                                          g.order, g.runoff, g.srect);
+    bin_sort_kernel<<<grid, kBinSortThreads, 0, s>>>(g.header, g.bins64, g.bin_cnt, g.seg_pre, g.nbins, g.brec, g.order, g.runoff, g.srect);
     count_launch();
 }
 

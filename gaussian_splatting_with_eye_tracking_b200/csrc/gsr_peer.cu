@@ -33,25 +33,46 @@ __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
 }
 
 // One CTA, one thread per peer.  flags = `world` words inside every rank's buffer at flag_offset; word s of rank d's
-// flags is written only by rank s.  Epochs only grow, so nothing is ever reset.  A rank that never arrives trips the
-// watchdog (~2 s) instead of hanging the device: flags[world] (error word, local) is set and the kernel returns.
-__global__ void peer_barrier_kernel(char* const* __restrict__ bases, size_t flag_offset, int world, int rank, uint32_t epoch) {
+// flags is written only by rank s.  Epochs only grow, so nothing is ever reset.
+// A rank that has not arrived after the watchdog time (default 10 minutes, like a collective library's; a rank may be busy
+// with a checkpoint, an evaluation pass or a cold start -- GSR_OPT_PEER_TIMEOUT_MS) must never lead to a silent sum of stale
+// data: the barrier then (1) sets the local error word flags[world], which makes every data kernel behind it on this rank
+// write NaN instead of sums, and (2) raises the process-wide host-visible error word that gsr_peer_error() reports -- the
+// host shim checks it whenever it waits for an exchange.  The device is not hung and the context survives.
+__global__ void peer_barrier_kernel(char* const* __restrict__ bases, size_t flag_offset, int world, int rank, uint32_t epoch,
+                                    long long timeout_ns, uint32_t* host_err) {
     const int p = threadIdx.x;
     if (p >= world) return;
     __threadfence_system();
     uint32_t* theirs = (uint32_t*)(bases[p] + flag_offset);
     uint32_t* mine = (uint32_t*)(bases[rank] + flag_offset);
     st_release_sys(theirs + rank, epoch);
-    const long long t0 = clock64();
+    unsigned long long t0;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+    unsigned spins = 0;
     while ((int32_t)(ld_acquire_sys(mine + p) - epoch) < 0) {
-        if (clock64() - t0 > 4000000000LL) { mine[world] = 1u; break; }
+        if ((++spins & 1023u) == 0u) {
+            unsigned long long t1;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+            if ((long long)(t1 - t0) > timeout_ns) {
+                mine[world] = 1u;
+                if (host_err) { *((volatile uint32_t*)host_err) = 1u; __threadfence_system(); }
+                break;
+            }
+        }
         __nanosleep(100);
     }
 }
 
+__device__ __forceinline__ bool peer_poisoned(char* const* bases, size_t flag_offset, int world, int rank) {
+    return ((volatile const uint32_t*)(bases[rank] + flag_offset))[world] != 0u;
+}
+
 template <int WORLD>
 __global__ void __launch_bounds__(kPeerThreads)
-peer_reduce_kernel(char* const* __restrict__ bases, size_t data_offset, long long n4, int rank, int diag) {
+peer_reduce_kernel(char* const* __restrict__ bases, size_t data_offset, long long n4, int rank, int diag, size_t flag_offset) {
+    const bool poisoned = peer_poisoned(bases, flag_offset, WORLD, rank);      // a barrier of this rank timed out
+    const float nanv = __int_as_float(0x7fc00000);
     PeerPtrs P, Q;
 #pragma unroll
     for (int k = 0; k < WORLD; ++k) {
@@ -76,6 +97,7 @@ peer_reduce_kernel(char* const* __restrict__ bases, size_t data_offset, long lon
             s.x += a[k].x; s.y += a[k].y; s.z += a[k].z; s.w += a[k].w;
             if (two) { t.x += b[k].x; t.y += b[k].y; t.z += b[k].z; t.w += b[k].w; }
         }
+        if (poisoned) { s = make_float4(nanv, nanv, nanv, nanv); t = s; }
 #pragma unroll
         for (int k = 0; k < WORLD; ++k) {
             __stcg(Q.p[k] + i, s);
@@ -91,7 +113,9 @@ peer_reduce_kernel(char* const* __restrict__ bases, size_t data_offset, long lon
 // by the host).  The switch fixes the order of its adds, so all ranks still receive identical bits, but that order is not
 // the rank order of the unicast kernel (last-bit differences between the two variants).
 __global__ void __launch_bounds__(kPeerThreads)
-peer_reduce_mc_kernel(float4* __restrict__ mc, long long n4, int world, int rank) {
+peer_reduce_mc_kernel(float4* __restrict__ mc, long long n4, int world, int rank, char* const* __restrict__ bases, size_t flag_offset) {
+    const bool poisoned = peer_poisoned(bases, flag_offset, world, rank);
+    const float nanv = __int_as_float(0x7fc00000);
     const long long per = (n4 + world - 1) / world;
     const long long lo = per * rank, hi = min(n4, lo + per);
     const long long stride = (long long)gridDim.x * kPeerThreads;
@@ -103,6 +127,7 @@ peer_reduce_mc_kernel(float4* __restrict__ mc, long long n4, int world, int rank
             if (j < hi)
                 asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
                              : "=f"(v[u].x), "=f"(v[u].y), "=f"(v[u].z), "=f"(v[u].w) : "l"(mc + j) : "memory");
+            if (poisoned) v[u] = make_float4(nanv, nanv, nanv, nanv);
         }
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
@@ -111,6 +136,87 @@ peer_reduce_mc_kernel(float4* __restrict__ mc, long long n4, int world, int rank
                 asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};"
                              :: "l"(mc + j), "f"(v[u].x), "f"(v[u].y), "f"(v[u].z), "f"(v[u].w) : "memory");
         }
+    }
+    __threadfence_system();
+}
+
+long long g_peer_timeout_ms = 600000;
+long long peer_timeout_ns() { return g_peer_timeout_ms * 1000000LL; }
+// process-wide error word in mapped pinned host memory (portable: valid on every device under unified addressing)
+uint32_t* peer_error_word() {
+    static uint32_t* w = nullptr;
+    static bool tried = false;
+    if (!tried) {
+        tried = true;
+        if (cudaHostAlloc((void**)&w, 64, cudaHostAllocMapped | cudaHostAllocPortable) != cudaSuccess) { w = nullptr; cudaGetLastError(); }
+        else *w = 0u;
+    }
+    return w;
+}
+
+// ---- fused exchange, second half (gsr_peer_owner_sum): rank r sums the rows staged for its slice of Gaussians and delivers the
+// totals to every rank.  A thread owns 4 consecutive Gaussians so that every array of the dense block is written with 128-bit
+// stores: means3D 3 x float4, opacity 1, scales 3, rotations 4.
+struct OwnerSumParams {
+    char* const* bases; float* mc;            // mc != nullptr: multicast mapping of the buffers (one multimem.st per value)
+    size_t staging_offset, final_offset, flag_offset;
+    int P, P4, rows_per_rank, world, rank;
+    const uint32_t* masks; size_t mask_stride;
+};
+
+template <bool MC>
+__device__ __forceinline__ void deliver(const OwnerSumParams& p, size_t float_index, float4 v) {
+    if (MC) {
+        asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};"
+                     :: "l"(p.mc + (p.final_offset >> 2) + float_index), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+    } else {
+        for (int k = 0; k < p.world; ++k) __stcg(reinterpret_cast<float4*>(p.bases[k] + p.final_offset) + (float_index >> 2), v);
+    }
+}
+
+template <bool MC>
+__global__ void __launch_bounds__(kPeerThreads) peer_owner_sum_kernel(const OwnerSumParams p) {
+    const bool poisoned = peer_poisoned(p.bases, p.flag_offset, p.world, p.rank);
+    const float nanv = __int_as_float(0x7fc00000);
+    const float4* staging = reinterpret_cast<const float4*>(p.bases[p.rank] + p.staging_offset);
+    const int first = p.rank * p.rows_per_rank;
+    const int count = max(0, min(p.rows_per_rank, p.P4 - first));       // multiple of 4
+    const size_t P4 = (size_t)p.P4;
+    for (int g4 = (blockIdx.x * kPeerThreads + threadIdx.x) * 4; g4 < count; g4 += gridDim.x * kPeerThreads * 4) {
+        const int idx = first + g4;                                       // 4 Gaussians idx .. idx + 3, same mask word
+        float row[4][11];
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+#pragma unroll
+            for (int c = 0; c < 11; ++c) row[q][c] = poisoned ? nanv : 0.f;
+        if (!poisoned) {
+            for (int k = 0; k < p.world; ++k) {                           // rank order: the same float expression on every run
+                const uint32_t word = __ldg(p.masks + (size_t)k * p.mask_stride + (idx >> 5));
+                const uint32_t bits = (word >> (idx & 31)) & 0xfu;
+                if (!bits) continue;
+                const float4* src = staging + ((size_t)k * p.rows_per_rank + g4) * 3;
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    if (!((bits >> q) & 1u)) continue;
+                    const float4 a = __ldcg(src + 3 * q), b = __ldcg(src + 3 * q + 1), c = __ldcg(src + 3 * q + 2);
+                    row[q][0] += a.x; row[q][1] += a.y; row[q][2] += a.z; row[q][3] += a.w;
+                    row[q][4] += b.x; row[q][5] += b.y; row[q][6] += b.z; row[q][7] += b.w;
+                    row[q][8] += c.x; row[q][9] += c.y; row[q][10] += c.z;
+                }
+            }
+        }
+        // dense block: [means3D 3 x P4 | opacity P4 | scales 3 x P4 | rotations 4 x P4]
+        const size_t i = (size_t)idx;
+        deliver<MC>(p, 3 * i,      make_float4(row[0][0], row[0][1], row[0][2], row[1][0]));
+        deliver<MC>(p, 3 * i + 4,  make_float4(row[1][1], row[1][2], row[2][0], row[2][1]));
+        deliver<MC>(p, 3 * i + 8,  make_float4(row[2][2], row[3][0], row[3][1], row[3][2]));
+        deliver<MC>(p, 3 * P4 + i, make_float4(row[0][3], row[1][3], row[2][3], row[3][3]));
+        deliver<MC>(p, 4 * P4 + 3 * i,     make_float4(row[0][4], row[0][5], row[0][6], row[1][4]));
+        deliver<MC>(p, 4 * P4 + 3 * i + 4, make_float4(row[1][5], row[1][6], row[2][4], row[2][5]));
+        deliver<MC>(p, 4 * P4 + 3 * i + 8, make_float4(row[2][6], row[3][4], row[3][5], row[3][6]));
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+            deliver<MC>(p, 7 * P4 + 4 * (i + q), make_float4(row[q][7], row[q][8], row[q][9], row[q][10]));
     }
     __threadfence_system();
 }
@@ -129,6 +235,8 @@ void preload(int world) {
     cudaFuncAttributes fa;
     cudaFuncGetAttributes(&fa, peer_barrier_kernel);
     cudaFuncGetAttributes(&fa, peer_reduce_mc_kernel);
+    cudaFuncGetAttributes(&fa, peer_owner_sum_kernel<true>);
+    cudaFuncGetAttributes(&fa, peer_owner_sum_kernel<false>);
     switch (world) {
         case 2: preload_reduce<2>(); break; case 3: preload_reduce<3>(); break; case 4: preload_reduce<4>(); break;
         case 5: preload_reduce<5>(); break; case 6: preload_reduce<6>(); break; case 7: preload_reduce<7>(); break;
@@ -138,15 +246,16 @@ void preload(int world) {
 }
 
 template <int WORLD>
-void launch_reduce(char* const* bases, size_t off, long long n4, int rank, cudaStream_t s) {
+void launch_reduce(char* const* bases, size_t off, long long n4, int rank, size_t flag_off, cudaStream_t s) {
     const long long per = (n4 + WORLD - 1) / WORLD;
     long long blocks = (per + 2LL * kPeerThreads - 1) / (2LL * kPeerThreads);
     blocks = std::max(1LL, std::min(blocks, 148LL * (g_peer_ctas_per_sm ? g_peer_ctas_per_sm : 2)));
-    peer_reduce_kernel<WORLD><<<(unsigned)blocks, kPeerThreads, 0, s>>>(bases, off, n4, rank, g_peer_diag_mode);
+    peer_reduce_kernel<WORLD><<<(unsigned)blocks, kPeerThreads, 0, s>>>(bases, off, n4, rank, g_peer_diag_mode, flag_off);
 }
 
 }  // namespace
 void set_peer_ctas_per_sm(int v) { g_peer_ctas_per_sm = v & 0xff; g_peer_diag_mode = (v >> 8) & 3; }
+void set_peer_timeout_ms(int v) { g_peer_timeout_ms = v > 0 ? v : 600000; }
 }  // namespace gsr
 
 using namespace gsr;
@@ -160,9 +269,45 @@ int gsr_peer_barrier(void* const* peer_bases, size_t flag_offset, int world, int
         set_error("peer_barrier: bad arguments (world %d, rank %d)", world, rank); return GSR_ERR_INVALID;
     }
     preload(world);
-    peer_barrier_kernel<<<1, 32, 0, (cudaStream_t)stream>>>((char* const*)peer_bases, flag_offset, world, rank, epoch);
+    peer_barrier_kernel<<<1, 32, 0, (cudaStream_t)stream>>>((char* const*)peer_bases, flag_offset, world, rank, epoch, peer_timeout_ns(), peer_error_word());
     count_launch();
     return check_last("peer_barrier", false, (cudaStream_t)stream);
+}
+
+int gsr_peer_error(void) {
+    uint32_t* w = peer_error_word();
+    if (!w) return 0;
+    const uint32_t v = *((volatile uint32_t*)w);
+    if (v) *((volatile uint32_t*)w) = 0u;
+    return v ? 1 : 0;
+}
+
+int gsr_peer_owner_sum(void* const* peer_bases, void* multicast_base, size_t staging_offset, size_t final_offset, int P,
+                       int rows_per_rank, const uint32_t* view_masks, size_t mask_stride_words, size_t flag_offset,
+                       int world, int rank, unsigned epoch, void* stream) {
+    if (world < 1 || world > kMaxPeers || rank < 0 || rank >= world || !peer_bases || !view_masks) {
+        set_error("peer_owner_sum: bad arguments (world %d, rank %d)", world, rank); return GSR_ERR_INVALID;
+    }
+    if (P < 0 || rows_per_rank <= 0 || (rows_per_rank % 256) != 0 || (long long)rows_per_rank * world < (long long)P ||
+        (staging_offset & 15) || (final_offset & 15) || (flag_offset & 3) || ((uintptr_t)multicast_base & 15) ||
+        mask_stride_words < (size_t)((P + 31) / 32)) {
+        set_error("peer_owner_sum: bad sizes / alignment (P %d, rows per rank %d)", P, rows_per_rank); return GSR_ERR_INVALID;
+    }
+    cudaStream_t s = (cudaStream_t)stream;
+    char* const* bases = (char* const*)peer_bases;
+    preload(world);
+    peer_barrier_kernel<<<1, 32, 0, s>>>(bases, flag_offset, world, rank, epoch, peer_timeout_ns(), peer_error_word());
+    OwnerSumParams p;
+    p.bases = bases; p.mc = (float*)multicast_base; p.staging_offset = staging_offset; p.final_offset = final_offset; p.flag_offset = flag_offset;
+    p.P = P; p.P4 = (P + 3) / 4 * 4; p.rows_per_rank = rows_per_rank; p.world = world; p.rank = rank;
+    p.masks = view_masks; p.mask_stride = mask_stride_words;
+    long long blocks = ((long long)rows_per_rank / 4 + kPeerThreads - 1) / kPeerThreads;
+    blocks = std::max(1LL, std::min(blocks, 148LL * (g_peer_ctas_per_sm ? g_peer_ctas_per_sm : 2)));
+    if (multicast_base) peer_owner_sum_kernel<true><<<(unsigned)blocks, kPeerThreads, 0, s>>>(p);
+    else peer_owner_sum_kernel<false><<<(unsigned)blocks, kPeerThreads, 0, s>>>(p);
+    peer_barrier_kernel<<<1, 32, 0, s>>>(bases, flag_offset, world, rank, epoch + 1u, peer_timeout_ns(), peer_error_word());
+    count_launch(3);
+    return check_last("peer_owner_sum", false, s);
 }
 
 int gsr_peer_allreduce_sum_mc(void* const* peer_bases, void* multicast_base, size_t data_offset, long long n_floats,
@@ -177,12 +322,12 @@ int gsr_peer_allreduce_sum_mc(void* const* peer_bases, void* multicast_base, siz
     cudaStream_t s = (cudaStream_t)stream;
     char* const* bases = (char* const*)peer_bases;
     preload(world);
-    peer_barrier_kernel<<<1, 32, 0, s>>>(bases, flag_offset, world, rank, epoch);
+    peer_barrier_kernel<<<1, 32, 0, s>>>(bases, flag_offset, world, rank, epoch, peer_timeout_ns(), peer_error_word());
     const long long n4 = n_floats / 4, per = (n4 + world - 1) / world;
     long long blocks = (per + 4LL * kPeerThreads - 1) / (4LL * kPeerThreads);
     blocks = std::max(1LL, std::min(blocks, 148LL * (g_peer_ctas_per_sm ? g_peer_ctas_per_sm : 1)));
-    peer_reduce_mc_kernel<<<(unsigned)blocks, kPeerThreads, 0, s>>>((float4*)((char*)multicast_base + data_offset), n4, world, rank);
-    peer_barrier_kernel<<<1, 32, 0, s>>>(bases, flag_offset, world, rank, epoch + 1u);
+    peer_reduce_mc_kernel<<<(unsigned)blocks, kPeerThreads, 0, s>>>((float4*)((char*)multicast_base + data_offset), n4, world, rank, bases, flag_offset);
+    peer_barrier_kernel<<<1, 32, 0, s>>>(bases, flag_offset, world, rank, epoch + 1u, peer_timeout_ns(), peer_error_word());
     count_launch(3);
     return check_last("peer_allreduce_sum_mc", false, s);
 }
@@ -199,19 +344,19 @@ int gsr_peer_allreduce_sum(void* const* peer_bases, size_t data_offset, long lon
     cudaStream_t s = (cudaStream_t)stream;
     char* const* bases = (char* const*)peer_bases;
     preload(world);
-    peer_barrier_kernel<<<1, 32, 0, s>>>(bases, flag_offset, world, rank, epoch);
+    peer_barrier_kernel<<<1, 32, 0, s>>>(bases, flag_offset, world, rank, epoch, peer_timeout_ns(), peer_error_word());
     const long long n4 = n_floats / 4;
     switch (world) {
         case 1: break;                                   // a single rank's sum is its own buffer
-        case 2: launch_reduce<2>(bases, data_offset, n4, rank, s); break;
-        case 3: launch_reduce<3>(bases, data_offset, n4, rank, s); break;
-        case 4: launch_reduce<4>(bases, data_offset, n4, rank, s); break;
-        case 5: launch_reduce<5>(bases, data_offset, n4, rank, s); break;
-        case 6: launch_reduce<6>(bases, data_offset, n4, rank, s); break;
-        case 7: launch_reduce<7>(bases, data_offset, n4, rank, s); break;
-        default: launch_reduce<8>(bases, data_offset, n4, rank, s); break;
+        case 2: launch_reduce<2>(bases, data_offset, n4, rank, flag_offset, s); break;
+        case 3: launch_reduce<3>(bases, data_offset, n4, rank, flag_offset, s); break;
+        case 4: launch_reduce<4>(bases, data_offset, n4, rank, flag_offset, s); break;
+        case 5: launch_reduce<5>(bases, data_offset, n4, rank, flag_offset, s); break;
+        case 6: launch_reduce<6>(bases, data_offset, n4, rank, flag_offset, s); break;
+        case 7: launch_reduce<7>(bases, data_offset, n4, rank, flag_offset, s); break;
+        default: launch_reduce<8>(bases, data_offset, n4, rank, flag_offset, s); break;
     }
-    peer_barrier_kernel<<<1, 32, 0, s>>>(bases, flag_offset, world, rank, epoch + 1u);
+    peer_barrier_kernel<<<1, 32, 0, s>>>(bases, flag_offset, world, rank, epoch + 1u, peer_timeout_ns(), peer_error_word());
     count_launch(world > 1 ? 3 : 2);
     return check_last("peer_allreduce_sum", false, s);
 }

@@ -465,6 +465,8 @@ struct PreBwdParams {
     const float* __restrict__ scratch;
     float *dL_dmeans2D, *dL_dcolors, *dL_dopacity, *dL_dmeans3D, *dL_dcov3D, *dL_dsh, *dL_dscales, *dL_drot, *dL_dconic;
     float* dL_drgb_clamped;        // optional [P,3]; with dL_dsh == nullptr the SH rows are not written (gsr_grads)
+    // fused view-parallel exchange (gsr_grads.push_*): rows of the 11 dense floats go to the owner rank's staging area
+    char* const* push_bases; size_t push_offset; int push_rank, push_rows_per_rank;
 };
 
 // SH rows are staged through shared memory (STAGED): a thread's 3M coefficients / gradients are 192 B apart from its
@@ -495,7 +497,7 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreBwdParams 
     // blend-stage gradients leave in the reference's tensor shapes
     if (valid) {
         p.dL_dmeans2D[i3] = sA.x; p.dL_dmeans2D[i3 + 1] = sA.y; p.dL_dmeans2D[i3 + 2] = 0.f;
-        p.dL_dopacity[idx] = sB.y;
+        if (p.push_bases == nullptr) p.dL_dopacity[idx] = sB.y;
         p.dL_dcolors[i3] = sB.z; p.dL_dcolors[i3 + 1] = sB.w; p.dL_dcolors[i3 + 2] = sC.x;
         if (p.dL_dconic) reinterpret_cast<float4*>(p.dL_dconic)[idx] = make_float4(sA.z, sA.w, 0.f, sB.x);
     }
@@ -716,9 +718,23 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreBwdParams 
         // note: like the reference, dL_dscale is the gradient w.r.t. (modifier * scale); no extra factor is applied
     }
 
-    p.dL_dmeans3D[i3] = dmx; p.dL_dmeans3D[i3 + 1] = dmy; p.dL_dmeans3D[i3 + 2] = dmz;
 #pragma unroll
     for (int i = 0; i < 6; ++i) p.dL_dcov3D[6 * (size_t)idx + i] = dcov[i];
+    if (p.push_bases != nullptr) {
+        // one 48-byte row per VISIBLE Gaussian into the owner's staging area (peer memory): consecutive Gaussians -> consecutive
+        // rows, so a warp writes whole 128-byte lines across NVLink.  The owner knows from the gathered visibility masks which
+        // ranks wrote a row, so invisible Gaussians send nothing.
+        if (visible) {
+            const int owner = idx / p.push_rows_per_rank, local = idx - owner * p.push_rows_per_rank;
+            float4* dst = reinterpret_cast<float4*>(p.push_bases[owner] + p.push_offset) + ((size_t)p.push_rank * p.push_rows_per_rank + local) * 3;
+            dst[0] = make_float4(dmx, dmy, dmz, sB.y);
+            dst[1] = make_float4(dscale[0], dscale[1], dscale[2], drot.x);
+            dst[2] = make_float4(drot.y, drot.z, drot.w, 0.f);
+            __threadfence_system();
+        }
+        return;
+    }
+    p.dL_dmeans3D[i3] = dmx; p.dL_dmeans3D[i3 + 1] = dmy; p.dL_dmeans3D[i3 + 2] = dmz;
     p.dL_dscales[i3] = dscale[0]; p.dL_dscales[i3 + 1] = dscale[1]; p.dL_dscales[i3 + 2] = dscale[2];
     reinterpret_cast<float4*>(p.dL_drot)[idx] = drot;
 }
@@ -740,6 +756,8 @@ void launch_preprocess_backward(const PreBwdArgs& a, cudaStream_t s) {
     p.dL_dmeans3D = a.out.dL_dmeans3D; p.dL_dcov3D = a.out.dL_dcov3D; p.dL_dsh = a.out.dL_dsh;
     p.dL_dscales = a.out.dL_dscales; p.dL_drot = a.out.dL_drotations; p.dL_dconic = a.out.dL_dconic;
     p.dL_drgb_clamped = a.out.dL_dcolors_clamped;
+    p.push_bases = (char* const*)a.out.push_bases; p.push_offset = a.out.push_offset; p.push_rank = a.out.push_rank;
+    p.push_rows_per_rank = a.out.push_rows_per_rank;
     // staged SH path: needs M % 4 == 0 (128-bit rows), M <= 16 (row fits the staged stride) and 16 B-aligned tensors
     const bool staged = (p.dL_dsh != nullptr || p.colors_from_sh) && p.M > 0 && p.M <= 16 && (p.M % 4) == 0 && ((size_t)p.dL_dsh & 15) == 0 &&
                         (!p.colors_from_sh || ((size_t)p.shs & 15) == 0);

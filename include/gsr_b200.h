@@ -117,6 +117,17 @@ typedef struct gsr_grads {
                                   dL_dsh is NULL, the [P,M,3] SH gradient is not written at all: data-parallel training
                                   exchanges these 3 floats per Gaussian and view and rebuilds the summed SH gradient with
                                   gsr_sh_grad_from_views (the per-view SH gradient is the rank-1 product basis x this). */
+    /* ---- view-parallel training, fused gradient exchange (optional; push_bases == NULL: off).  The preprocess-stage
+     * backward then does NOT write dL_dmeans3D / dL_dopacity / dL_dscales / dL_drotations locally: for every Gaussian visible
+     * in this view it stores the 11 floats as one 48-byte row straight into the staging area of the rank that OWNS the
+     * Gaussian (peer memory over NVLink, under the kernel's own HBM-bound run time):
+     *     owner = idx / push_rows_per_rank,   row address = push_bases[owner] + push_offset
+     *                                                       + ((push_rank * push_rows_per_rank) + idx % push_rows_per_rank) * 48
+     * gsr_peer_owner_sum then sums the staged rows of every owner's Gaussians in rank order and delivers the totals to all
+     * ranks.  push_rows_per_rank must be a multiple of 256. */
+    void* const* push_bases;   /* DEVICE array of `push_world` peer-mapped base pointers (as for gsr_peer_allreduce_sum) */
+    size_t push_offset;        /* byte offset of the staging area inside every rank's buffer, 16-byte aligned */
+    int push_rank, push_world, push_rows_per_rank;
 } gsr_grads;
 
 /* ---- sizes of the three work buffers (bytes, including alignment slack) ---- */
@@ -315,6 +326,19 @@ GSR_API int gsr_peer_barrier(void* const* peer_bases, size_t flag_offset, int wo
  * all ranks; the switch's add order is not the rank order of the unicast variant. */
 GSR_API int gsr_peer_allreduce_sum_mc(void* const* peer_bases, void* multicast_base, size_t data_offset, long long n_floats,
                                       size_t flag_offset, int world, int rank, unsigned epoch, void* stream);
+/* Second half of the fused exchange (see gsr_grads.push_*): barrier(epoch), then rank r sums, for every Gaussian of its slice
+ * [r * rows_per_rank, (r+1) * rows_per_rank), the rows staged by the ranks in whose view the Gaussian was visible (visibility =
+ * bit idx of rank k's mask words, view_masks + k * mask_stride_words: the words gsr_pack_visible_rows produced and the ranks
+ * gathered; rank order, so every run gives the same bits), and writes the totals into EVERY rank's dense gradient block at
+ * final_offset -- [means3D 3 x P4 | opacity P4 | scales 3 x P4 | rotations 4 x P4] floats, P4 = P rounded up to 4, the layout
+ * the torch host carves the four tensors from -- through the multicast mapping when multicast_base != NULL (one store per
+ * value, replicated by the NVSwitch) or with one store per peer; barrier(epoch + 1).  Gaussians visible in no view get zeros. */
+GSR_API int gsr_peer_owner_sum(void* const* peer_bases, void* multicast_base, size_t staging_offset, size_t final_offset, int P,
+                               int rows_per_rank, const uint32_t* view_masks, size_t mask_stride_words, size_t flag_offset,
+                               int world, int rank, unsigned epoch, void* stream);
+/* 1 if a peer barrier of this process timed out since the last call (the word is cleared); the kernels that follow a timed-out
+ * barrier write NaN instead of sums, so a rank that ran ahead can never train on stale gradients silently. */
+GSR_API int gsr_peer_error(void);
 GSR_API int gsr_peer_allreduce_sum(void* const* peer_bases, size_t data_offset, long long n_floats, size_t flag_offset, int world,
                                    int rank, unsigned epoch, void* stream);
 
@@ -333,6 +357,8 @@ GSR_API int gsr_blend_stats(int P, int W, int H, const void* geom_buffer, const 
 enum { GSR_OPT_SORT_VARIANT = 0,  /* onesweep tile shape for u32 keys: 0 = default, 1..5 see gsr_binning.cu */
        GSR_OPT_BLEND_VARIANT = 1, /* forward blend: 0 = two pixels per thread, packed FP32x2 (default); 1 = one pixel per thread */
        GSR_OPT_PEER_CTAS_PER_SM = 2, /* gsr_peer_allreduce_sum*: grid cap in CTAs per SM, 0 = default */
+       GSR_OPT_PEER_TIMEOUT_MS = 6, /* peer barrier watchdog in milliseconds (default 600 000 = 10 min, NCCL-like); on expiry the
+                                       barrier posts gsr_peer_error and the data kernel behind it writes NaN */
        GSR_OPT_NVTX = 5,            /* 1: NVTX range per stage (names "gsr:<stage>"); also enabled by GSR_NVTX=1 in the environment */
        GSR_OPT_FAKE_SORT_ERROR = 4, /* 1: the next frames post a tripped radix-sort watchdog (test hook for GSR_ERR_SORT) */
        GSR_OPT_FORCE_SORT_FALLBACK = 3 /* 1: depth-sort with the global onesweep chain even when the range buckets fit (the
