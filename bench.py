@@ -378,9 +378,10 @@ def dp_rank1_variants(impl, d, cam_of, w, timer, Kb, world, dev, only=None):
     peer_err, peer_red = None, None
     if world > 1 and not os.environ.get("GSR_BENCH_NO_PEER"):
         try:                 # the 11 dense floats summed over NVLink peer memory (gsr_peer_allreduce_sum) instead of NCCL
-            peer_red = gdist.PeerAllReduce(11 * ((P_ + 3) // 4 * 4), dev)
+            peer_red = gdist.PeerAllReduce(11 * ((P_ + 3) // 4 * 4), dev, staging_gaussians=P_)
             modes["packed_rows_peer_sum"] = (True, 1)
             modes["dense_rows_peer_sum"] = (False, 1)
+            modes["packed_rows_fused_push"] = (True, 1)
         except Exception as ex:
             peer_err = str(ex)[:300]
     if os.environ.get("GSR_BENCH_DP_RANGES"):           # measured: splitting the preprocess stage into ranges does not pay
@@ -388,10 +389,11 @@ def dp_rank1_variants(impl, d, cam_of, w, timer, Kb, world, dev, only=None):
     if only is not None:
         modes = {k: v for k, v in modes.items() if k in only}
     for mode, (packed_, nch) in modes.items():
-        use_peer = mode.endswith("peer_sum")
-        exch = gdist.ShGradExchange(packed=packed_, peer=peer_red if use_peer else None)
+        fused = mode.endswith("fused_push")
+        use_peer = mode.endswith("peer_sum") or fused
+        exch = gdist.ShGradExchange(packed=packed_, peer=peer_red if use_peer else None, fused=fused)
 
-        def dp_step_rank1(i, exch=exch, nch=nch, use_peer=use_peer):
+        def dp_step_rank1(i, exch=exch, nch=nch, use_peer=use_peer, fused=fused):
             cam = cam_of(i)
             N, img, radii, gb, bb, ib = impl.forward_c(cam)
             if exch.packed:     # the forward holds the visible count on the host; the ranks agree on the gather size meanwhile
@@ -405,7 +407,7 @@ def dp_rank1_variants(impl, d, cam_of, w, timer, Kb, world, dev, only=None):
                 between_phases=lambda drgb: exch.start_gather(drgb, cam.camera_center, d["means3D"], d["sh_degree"], M_, radii=radii),
                 preprocess_chunks=nch,
                 after_chunk=(lambda first, count, rows: exch.start_reduce_chunk(rows)) if nch > 1 else None,
-                dense_out=peer_red.data if use_peer else None)
+                dense_out=peer_red.data if use_peer else None, push=peer_red.push_args if fused else None)
             if nch == 1:
                 exch.start_reduce([g[3], g[2], g[6], g[7]])        # means3D, opacity, scales, rotations
             return exch.finish()
@@ -474,7 +476,7 @@ def c4_leg(impl_cls, args, rank, world, timer, dev):
             d6["bg"], d6["means3D"], radii, e_, d6["scales"], d6["rotations"], 1.0, e_, cam.world_view_transform, cam.full_proj_transform,
             cam.tanfovx, cam.tanfovy, w, d6["shs"], d6["sh_degree"], cam.camera_center, gb, N, bb, ib, False)
     n1 = timer.run(n1_step, Kc, 2, prime=8) / Kc
-    only = ("packed_rows", "packed_rows_peer_sum") if world > 1 else ("packed_rows",)
+    only = ("packed_rows", "packed_rows_peer_sum", "packed_rows_fused_push") if world > 1 else ("packed_rows",)
     res, peer_red, peer_err = dp_rank1_variants(impl, d6, cam_of, w, timer, Kc, world, dev, only=only)
     best = min(res, key=lambda m: res[m][0])
     out = {"gaussians": P6, "width": 1920, "height": 1080, "views_per_step": world, "n1_ms": n1, "dp_ms": res[best][0], "variant": best,

@@ -156,7 +156,7 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
 def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rotations, scale_modifier, cov3D_precomp,
                                  viewmatrix, projmatrix, tan_fovx, tan_fovy, dL_dout_color, sh, degree, campos,
                                  geomBuffer, R, binningBuffer, imageBuffer, debug, band=None, compact_sh=False,
-                                 between_phases=None, preprocess_chunks=1, after_chunk=None, dense_out=None):
+                                 between_phases=None, preprocess_chunks=1, after_chunk=None, dense_out=None, push=None):
     """``compact_sh=True`` (extension, view-parallel training): slot 5 of the returned tuple is the [P,3] colour
     gradient after the SH clamp mask instead of the [P,M,3] SH gradient, which is then not written at all;
     ``sh_grad_from_views`` rebuilds the SH gradient summed over views from those.
@@ -169,7 +169,10 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
     the caller starts reducing them while the next range is still being computed.
     ``dense_out``: caller-owned float32 buffer of at least 11 * ceil4(P) elements that receives the four dense gradients
     (means3D, opacity, scales, rotations, back to back) instead of a fresh allocation -- a view-parallel caller passes
-    peer-mapped memory here so that dist.PeerAllReduce sums them in place over NVLink."""
+    peer-mapped memory here so that dist.PeerAllReduce sums them in place over NVLink.
+    ``push`` = (peer_bases_dev_ptr, staging_offset_bytes, rank, world, rows_per_rank): fused exchange (gsr_grads.push_*) -- the
+    preprocess stage stores the 11 dense floats of every visible Gaussian into the OWNER rank's staging area instead of
+    writing the four dense tensors; dist.PeerAllReduce.owner_sum then fills them (in ``dense_out``) on every rank."""
     H, W = int(dL_dout_color.size(1)), int(dL_dout_color.size(2))
     sc, cam, keep, P, M = _scene_camera(background, means3D, colors, torch.empty(0), scales, rotations, scale_modifier,
                                         cov3D_precomp, viewmatrix, projmatrix, tan_fovx, tan_fovy, H, W, sh, degree,
@@ -207,6 +210,9 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
                              dL_dsh=_p(dL_dsh) if (M and not compact) else None,
                              dL_dscales=_p(dL_dscales), dL_drotations=_p(dL_drotations), dL_dconic=_p(dL_dconic),
                              scratch=_p(scratch), dL_dcolors_clamped=_p(dL_dsh) if compact else None)
+            if push is not None:
+                grads.push_bases = C.c_void_p(int(push[0])); grads.push_offset = int(push[1]); grads.push_rank = int(push[2])
+                grads.push_world = int(push[3]); grads.push_rows_per_rank = int(push[4])
             bufs = (_p(geomBuffer.contiguous()), _p(binningBuffer.contiguous()), _p(imageBuffer.contiguous()))
             if compact and between_phases is not None:
                 rc = lib.gsr_backward_phase(C.byref(sc), C.byref(cam), _p(radii_t), *bufs, int(R), _p(dpix), C.byref(grads),

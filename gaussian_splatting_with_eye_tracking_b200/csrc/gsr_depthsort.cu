@@ -47,7 +47,7 @@ static int ds_num_sms() {
 // ------------------------------------------------------------------------------------------------
 constexpr int kIlp = 4;                        // 256-blocks a thread of the scatter has in flight
 
-__global__ void __launch_bounds__(kSegBins) bin_scan_kernel(unsigned long long* bins64, uint32_t* __restrict__ bin_cnt, uint4* __restrict__ seg_tot) {
+__global__ void __launch_bounds__(kSegBins) bin_scan_kernel(unsigned long long* bins64, uint4* __restrict__ seg_tot) {
     __shared__ uint32_t s_a[32], s_b[32], s_c[32], s_d[32];
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const int i = blockIdx.x * kSegBins + tid;
@@ -73,7 +73,6 @@ __global__ void __launch_bounds__(kSegBins) bin_scan_kernel(unsigned long long* 
         tsq = (tsq + s_d[w] < tsq) ? 0xffffffffu : tsq + s_d[w];           // saturating
     }
     if (tc != 0u) bins64[i] = ((unsigned long long)(br + ir - r) << 32) | (unsigned long long)(bc + ic - c);   // (first run, first slot), relative
-    bin_cnt[i] = c;
     if (tid == 0) seg_tot[blockIdx.x] = make_uint4(tc, tr, tsq, maxbin);
 }
 
@@ -140,7 +139,7 @@ __global__ void __launch_bounds__(1024) bin_totals_kernel(GeomHeader* hdr, const
 
 void launch_bin_scan(const GeomPtrs& g, int P, uint32_t* mailbox_dev, cudaStream_t s) {
     const int nseg = g.nbins / kSegBins;
-    bin_scan_kernel<<<nseg, kSegBins, 0, s>>>(g.bins64, g.bin_cnt, g.seg_tot);
+    bin_scan_kernel<<<nseg, kSegBins, 0, s>>>(g.bins64, g.seg_tot);
     bin_totals_kernel<<<1, 1024, 0, s>>>(g.header, g.stat_slots, P, nseg, g.seg_tot, g.seg_pre, g.runoff, depth_shift(P), index_bits(P), mailbox_dev);
     count_launch(2);
 }
@@ -198,81 +197,87 @@ void launch_bin_scatter(const GeomPtrs& g, int P, cudaStream_t s) {
 // exact order inside every bin + run offsets
 // ------------------------------------------------------------------------------------------------
 constexpr int kBinSortThreads = 256;
-constexpr int kBinThreadMax = 48;              // a bin up to this size is ordered by its own thread; fuller ones by the whole warp
+constexpr int kBinsPerCta = 128;               // consecutive bins one CTA orders (their records are one contiguous stretch of brec)
+constexpr int kBinChunk = 2048;                // records staged in shared memory at a time (whole bins; a bin holds <= kBinCap)
 
-// A THREAD per bin (a populated bin holds ~10 records): for each of its records the thread counts the records of the bin
-// that order before it -- composites re-read through the L1, n^2 compares -- and, in the same loop, the runs those records
-// emit; it then writes the record's id, the absolute offset of its first run and its rect to slot start + rank.  A warp per
-// bin (the round-2 first attempt) left each warp with a chain of ~20 dependent L2 round trips and 30 % of its lanes busy;
-// here a million threads are in flight and the latencies overlap.  Bins with more than kBinThreadMax records are taken by
-// the whole warp afterwards, one at a time (all-pairs with the candidates strided over the lanes).
+// A CTA per 128 consecutive bins.  Their records are contiguous in brec: the CTA stages them in shared memory with coalesced
+// 128-bit loads (whole bins, up to 2048 records at a time) and then works a THREAD PER RECORD: the thread finds its bin in the
+// CTA's table of bin starts (binary search), counts the records of that bin that order before its own -- (composite, rows) pairs
+// read from shared memory, n compares -- and, in the same loop, the runs those records emit; the record's id, the absolute
+// offset of its first run and its rect go to slot start + rank.  (Per-thread or per-warp bins reading global memory are bound by
+// the L1's one-sector-per-clock rate on scattered accesses: two earlier forms of this kernel took 70 - 250 us.)
 __global__ void __launch_bounds__(kBinSortThreads) bin_sort_kernel(const GeomHeader* __restrict__ hdr, const unsigned long long* __restrict__ bins64,
-                                                                   const uint32_t* __restrict__ bin_cnt, const uint2* __restrict__ seg_pre,
+                                                                   const uint4* __restrict__ seg_tot, const uint2* __restrict__ seg_pre,
                                                                    int nbins, const uint4* __restrict__ brec, uint32_t* __restrict__ order,
                                                                    uint32_t* __restrict__ runoff, uint2* __restrict__ srect) {
+    __shared__ uint32_t s_start[kBinsPerCta + 1];     // first record of every bin of this CTA (absolute), + end
+    __shared__ uint32_t s_run0[kBinsPerCta];          // first run of every bin (absolute)
+    __shared__ uint2 s_rec[kBinChunk];                // (composite, rows) of the staged records
+    __shared__ uint32_t s_tie[kBinChunk];             // id word (tie break when the composite is the full key)
+    __shared__ int s_b1;
     if (hdr->sort_mode != 1u) return;
     const bool comp32 = hdr->comp32 != 0u;
-    const int lane = threadIdx.x & 31;
-    for (int bin0 = blockIdx.x * kBinSortThreads; bin0 < nbins; bin0 += gridDim.x * kBinSortThreads) {
-        const int bin = bin0 + threadIdx.x;             // nbins is a multiple of 1024: always in range
-        const int n = (int)__ldg(bin_cnt + bin);
-        uint32_t start = 0, run0 = 0;
-        if (n) {
-            const unsigned long long sr = __ldg(bins64 + bin);
-            const uint2 sb = __ldg(seg_pre + bin / kSegBins);
-            start = sb.x + (uint32_t)sr; run0 = sb.y + (uint32_t)(sr >> 32);
+    const int tid = threadIdx.x;
+    const int bin0 = blockIdx.x * kBinsPerCta;
+    const int seg = bin0 / kSegBins;
+    const uint4 st = __ldg(seg_tot + seg);
+    if (st.x == 0u) return;                           // empty segment (its bins64 words were never rewritten)
+    const uint2 sp = __ldg(seg_pre + seg);
+    if (tid < kBinsPerCta) {
+        const unsigned long long sr = __ldg(bins64 + bin0 + tid);
+        s_start[tid] = sp.x + (uint32_t)sr; s_run0[tid] = sp.y + (uint32_t)(sr >> 32);
+    }
+    if (tid == kBinsPerCta) {                         // end of the CTA's last bin: start of the next bin, or the segment's end
+        const int nb = bin0 + kBinsPerCta;
+        s_start[kBinsPerCta] = (nb % kSegBins) ? sp.x + (uint32_t)__ldg(bins64 + nb) : sp.x + st.x;
+    }
+    __syncthreads();
+    if (s_start[kBinsPerCta] == s_start[0]) return;   // no records in these bins
+    int b0 = 0;
+    while (b0 < kBinsPerCta) {
+        // chunk = bins [b0, b1): as many whole bins as fit kBinChunk records (at least one: a bin holds <= kBinCap < kBinChunk)
+        if (tid == 0) {
+            const uint32_t lim = s_start[b0] + kBinChunk;
+            int lo = b0 + 1, hi = kBinsPerCta;        // largest b1 in [b0 + 1, 128] with s_start[b1] <= lim
+            while (lo < hi) { const int mid = (lo + hi + 1) >> 1; if (s_start[mid] <= lim) lo = mid; else hi = mid - 1; }
+            s_b1 = lo;
         }
-        if (n > 0 && n <= kBinThreadMax) {
-            for (int i = 0; i < n; ++i) {
-                const uint4 q = __ldg(brec + start + i);
-                uint32_t rank = 0, before = 0;
-                if (comp32) {
-#pragma unroll 4
-                    for (int j = 0; j < n; ++j) {
-                        const uint2 o = __ldg(reinterpret_cast<const uint2*>(brec + start + j));
-                        const bool lt = o.x < q.x;
-                        rank += lt ? 1u : 0u; before += lt ? (o.y & 0xffffu) : 0u;
-                    }
-                } else {
-                    for (int j = 0; j < n; ++j) {
-                        const uint4 o = __ldg(brec + start + j);
-                        const bool lt = o.x < q.x || (o.x == q.x && o.w < q.w);
-                        rank += lt ? 1u : 0u; before += lt ? (o.y & 0xffffu) : 0u;
-                    }
+        __syncthreads();
+        const int b1 = s_b1;
+        const uint32_t c0 = s_start[b0], cn = s_start[b1] - c0;
+        for (uint32_t i = tid; i < cn; i += kBinSortThreads) {
+            const uint4 q = __ldg(brec + c0 + i);
+            s_rec[i] = make_uint2(q.x, q.y & 0xffffu); s_tie[i] = q.w;
+        }
+        __syncthreads();
+        for (uint32_t i = tid; i < cn; i += kBinSortThreads) {
+            const uint32_t at0 = c0 + i;
+            int lo = b0, hi = b1;                     // bin of record at0: s_start[lo] <= at0 < s_start[lo + 1]
+            while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (s_start[mid] <= at0) lo = mid; else hi = mid; }
+            const uint32_t s = s_start[lo] - c0, e = s_start[lo + 1] - c0;
+            const uint2 me = s_rec[i];
+            uint32_t rank = 0, before = 0;
+            if (comp32) {
+                for (uint32_t j = s; j < e; ++j) { const uint2 o = s_rec[j]; const bool lt = o.x < me.x; rank += lt ? 1u : 0u; before += lt ? o.y : 0u; }
+            } else {
+                const uint32_t myid = s_tie[i];
+                for (uint32_t j = s; j < e; ++j) {
+                    const uint2 o = s_rec[j];
+                    const bool lt = o.x < me.x || (o.x == me.x && s_tie[j] < myid);
+                    rank += lt ? 1u : 0u; before += lt ? o.y : 0u;
                 }
-                const uint32_t at = start + rank;
-                order[at] = q.w; runoff[at] = run0 + before; srect[at] = make_uint2(q.z, q.y >> 16);
             }
+            const uint4 q = __ldg(brec + at0);        // L1 hit: id, rect words
+            const uint32_t at = c0 + s + rank;
+            order[at] = q.w; runoff[at] = s_run0[lo] + before; srect[at] = make_uint2(q.z, q.y >> 16);
         }
-        // fuller bins: the warp takes them one by one
-        uint32_t big = __ballot_sync(0xffffffffu, n > kBinThreadMax);
-        while (big) {
-            const int k = __ffs(big) - 1;
-            big &= big - 1u;
-            const int nk = __shfl_sync(0xffffffffu, n, k);
-            const uint32_t st = __shfl_sync(0xffffffffu, start, k), r0 = __shfl_sync(0xffffffffu, run0, k);
-            for (int i = lane; i < nk; i += 32) {
-                const uint4 q = __ldg(brec + st + i);
-                uint32_t rank = 0, before = 0;
-#pragma unroll 4
-                for (int j = 0; j < nk; ++j) {
-                    const uint4 o = __ldg(brec + st + j);
-                    const bool lt = o.x < q.x || (!comp32 && o.x == q.x && o.w < q.w);
-                    rank += lt ? 1u : 0u; before += lt ? (o.y & 0xffffu) : 0u;
-                }
-                const uint32_t at = st + rank;
-                order[at] = q.w; runoff[at] = r0 + before; srect[at] = make_uint2(q.z, q.y >> 16);
-            }
-        }
+        __syncthreads();
+        b0 = b1;
     }
 }
 
 void launch_bin_sort(const GeomPtrs& g, int P, cudaStream_t s) {
-    int grid = g.nbins / kBinSortThreads;
-    const int cap = ds_num_sms() * 8 * 4;                                       // a few waves of 8 CTAs per SM
-    if (grid > cap) grid = cap;
-    if (grid < 1) grid = 1;
-    bin_sort_kernel<<<grid, kBinSortThreads, 0, s>>>(g.header, g.bins64, g.bin_cnt, g.seg_pre, g.nbins, g.brec, g.order, g.runoff, g.srect);
+    bin_sort_kernel<<<g.nbins / kBinsPerCta, kBinSortThreads, 0, s>>>(g.header, g.bins64, g.seg_tot, g.seg_pre, g.nbins, g.brec, g.order, g.runoff, g.srect);
     count_launch();
 }
 

@@ -183,9 +183,12 @@ class PeerAllReduce:
     (world-1)/world of the payload crosses NVLink in each direction per GPU, concurrently, against 2x that, serialised
     over ring or tree steps, for ncclAllReduce; the result is bit-identical on all ranks."""
 
-    def __init__(self, numel: int, device, group=None, multicast: Optional[bool] = None):
+    def __init__(self, numel: int, device, group=None, multicast: Optional[bool] = None, staging_gaussians: int = 0):
         """``multicast``: form the sum inside the NVSwitch (gsr_peer_allreduce_sum_mc); None = when the mapping exists and
-        world > 2 (at world 2 the unicast kernel moves the same bytes and keeps the rank-ordered sum)."""
+        world > 2 (at world 2 the unicast kernel moves the same bytes and keeps the rank-ordered sum).
+        ``staging_gaussians`` = P reserves, behind the data, the staging area of the FUSED exchange: `world` slots of
+        rows_per_rank x 48 bytes -- the preprocess-stage backward of every rank stores the gradient rows of the Gaussians
+        this rank owns straight into its slot (``push_args``), ``owner_sum`` adds them up and delivers the totals."""
         from ._capi import lib
         self._lib = lib
         self.group = group
@@ -193,7 +196,10 @@ class PeerAllReduce:
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
         self.numel = (int(numel) + 3) // 4 * 4
         self.flag_bytes = int(lib.gsr_peer_flag_bytes(self.world))
-        total = self.numel + self.flag_bytes // 4
+        self.staging_P = int(staging_gaussians)
+        self.rows_per_rank = ((self.staging_P + self.world - 1) // self.world + 255) // 256 * 256 if self.staging_P else 0
+        self.staging_floats = self.world * self.rows_per_rank * 12
+        total = self.numel + self.staging_floats + self.flag_bytes // 4
         dev = torch.device(device)
         if self.world > 1:
             import torch.distributed._symmetric_memory as symm
@@ -216,7 +222,7 @@ class PeerAllReduce:
             self.bases_dev = self._bases_keep.data_ptr()
             self.hdl = None
             self.multicast_ptr = 0
-        self.buf[self.numel:].zero_()                # flag words: zero on every rank before anyone signals
+        self.buf[self.numel + self.staging_floats:].zero_()                # flag words: zero on every rank before anyone signals
         torch.cuda.synchronize(dev)
         if self.world > 1:
             dist.barrier(group)
@@ -237,16 +243,51 @@ class PeerAllReduce:
             st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
             if self.multicast_ptr:
                 check(self._lib.gsr_peer_allreduce_sum_mc(C.c_void_p(self.bases_dev), C.c_void_p(self.multicast_ptr), 0, n,
-                                                          self.numel * 4, self.world, self.rank, self.epoch, st),
+                                                          self.flag_offset, self.world, self.rank, self.epoch, st),
                       "gsr_peer_allreduce_sum_mc")
             else:
-                check(self._lib.gsr_peer_allreduce_sum(C.c_void_p(self.bases_dev), 0, n, self.numel * 4, self.world, self.rank,
+                check(self._lib.gsr_peer_allreduce_sum(C.c_void_p(self.bases_dev), 0, n, self.flag_offset, self.world, self.rank,
                                                        self.epoch, st), "gsr_peer_allreduce_sum")
         self.epoch += 2
 
+    @property
+    def flag_offset(self) -> int:
+        return (self.numel + self.staging_floats) * 4
+
+    @property
+    def push_args(self):
+        """What ``_host.rasterize_gaussians_backward(..., push=...)`` needs: (peer base table, staging offset, rank, world, rows per rank)."""
+        if not self.rows_per_rank:
+            raise RuntimeError("PeerAllReduce was built without a staging area (staging_gaussians=P)")
+        return (self.bases_dev, self.numel * 4, self.rank, self.world, self.rows_per_rank)
+
+    def owner_sum(self, P: int, view_masks: torch.Tensor) -> None:
+        """Second half of the fused exchange, queued on the CURRENT stream (gsr_peer_owner_sum): barrier, this rank sums the rows
+        staged for its slice of Gaussians (visibility of Gaussian i in rank k's view = bit i of ``view_masks[k]``, int32
+        [world, >= ceil(P/32)] on the device) and writes the totals into the dense block at the start of EVERY rank's ``data``,
+        barrier."""
+        import ctypes as C
+        from ._capi import check
+        if int(P) != self.staging_P or view_masks.dtype != torch.int32 or not view_masks.is_contiguous() or view_masks.dim() != 2 \
+                or view_masks.shape[0] != self.world or view_masks.shape[1] < (int(P) + 31) // 32:
+            raise RuntimeError("PeerAllReduce.owner_sum: P / view_masks do not match the staging area")
+        with torch.cuda.device(self.buf.device):
+            st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+            check(self._lib.gsr_peer_owner_sum(C.c_void_p(self.bases_dev), C.c_void_p(self.multicast_ptr) if self.multicast_ptr else None,
+                                               self.numel * 4, 0, int(P), self.rows_per_rank, C.c_void_p(view_masks.data_ptr()),
+                                               int(view_masks.shape[1]), self.flag_offset, self.world, self.rank, self.epoch, st),
+                  "gsr_peer_owner_sum")
+        self.epoch += 2
+
+    def check_error(self) -> None:
+        """Raises if a peer barrier of this process timed out (gsr_peer_error): a rank never arrived within the watchdog time, the
+        sums behind that barrier were written as NaN.  Reads a host word -- no synchronisation."""
+        if self._lib.gsr_peer_error():
+            raise RuntimeError("peer-memory gradient exchange: a barrier timed out (a rank did not arrive); the affected sums are NaN")
+
     def timed_out(self) -> bool:
         """True if a barrier's watchdog fired (a rank never arrived).  Synchronises; diagnostics only."""
-        return bool(self.buf[self.numel + self.world].view(torch.int32).item())
+        return bool(self.buf[self.numel + self.staging_floats + self.world].view(torch.int32).item())
 
 
 class ShGradExchange:
@@ -263,7 +304,7 @@ class ShGradExchange:
     """
 
     def __init__(self, rebuild=None, bucket_bytes: int = DEFAULT_BUCKET_BYTES, group=None, packed: bool = False,
-                 pack=None, rebuild_packed=None, peer: Optional["PeerAllReduce"] = None):
+                 pack=None, rebuild_packed=None, peer: Optional["PeerAllReduce"] = None, fused: bool = False):
         """``packed``: only the rows of the Gaussians visible in a view (radii > 0) travel, with a bit mask and a
         per-word prefix that locate them (``pack`` = _host.pack_visible_rows, ``rebuild_packed`` =
         _host.sh_grad_from_packed_views; both injectable for the CPU protocol tests).  The ranks must then call
@@ -272,6 +313,13 @@ class ShGradExchange:
         self.reducer = GradientAllReduce(bucket_bytes, group)
         self.peer = peer               # the 11 dense floats summed in place over NVLink peer memory instead of NCCL
         self._peer_stream = None
+        # fused: the preprocess-stage backward pushes every visible Gaussian's 11 floats to the owner rank's staging area
+        # (peer.push_args) and start_reduce only queues the owner sum + broadcast; needs packed rows (their masks tell the
+        # owner which ranks staged a row) and a peer buffer with a staging area
+        self.fused = bool(fused)
+        if self.fused and (peer is None or not packed or not peer.rows_per_rank):
+            raise RuntimeError("ShGradExchange(fused=True) needs packed=True and a PeerAllReduce with staging_gaussians=P")
+        self._gather_event = None
         self._rebuild = rebuild
         self.packed = bool(packed)
         self._pack = pack
@@ -398,12 +446,25 @@ class ShGradExchange:
                          dist.all_gather_into_tensor(self._meta_all.view(-1), self._send_meta, group=self.group, async_op=True)]
                 for wk in works:
                     wk.wait()
+            if comm is not None:
+                self._gather_event = torch.cuda.Event()
+                self._gather_event.record(comm)          # the masks of all views are on this rank from here on
             cams = self._meta_all[:, L:L + 3].contiguous().view(torch.float32)
             self._side_allocs = [cams]
         self._rebuild_call = lambda: rebuild(means3D, cams, self._meta_all, rows_all.view(w, cap, 3), degree, M)
 
     def start_reduce(self, dense_grads: Sequence[torch.Tensor]) -> None:
         """Queue the in-place SUM of the remaining gradients (means3D, opacity, scales, rotations)."""
+        if self.fused:
+            dev = dense_grads[0].device
+            if self._peer_stream is None:
+                self._peer_stream = comm_stream(dev)
+            self._peer_stream.wait_stream(torch.cuda.current_stream(dev))      # this rank's pushes are queued behind the backward
+            if self._gather_event is not None:
+                self._peer_stream.wait_event(self._gather_event)
+            with torch.cuda.stream(self._peer_stream):
+                self.peer.owner_sum(self.peer.staging_P, self._meta_all)
+            return
         if self.peer is not None:
             lo = min(t.data_ptr() for t in dense_grads)
             hi = max(t.data_ptr() + t.numel() * 4 for t in dense_grads)
@@ -454,6 +515,8 @@ class ShGradExchange:
         self.reducer.wait()
         if self._peer_stream is not None:
             torch.cuda.current_stream().wait_stream(self._peer_stream)
+        if self.peer is not None:
+            self.peer.check_error()
 
     def finish(self) -> torch.Tensor:
         """finish_sh() + finish_dense(): returns the SH gradient [P,M,3] summed over all views; all gradients final."""

@@ -1,0 +1,136 @@
+"""The fused view-parallel gradient exchange: the preprocess-stage backward pushes the 11 dense floats of every
+visible Gaussian into the OWNER rank's staging area (gsr_grads.push_*), gsr_peer_owner_sum adds the staged rows in rank order and
+delivers the totals to every rank.  Exercised on ONE device: the `world` rank buffers all live on cuda:0 and each "rank" runs on
+its own stream -- the kernels only see a table of base pointers, so this is the code path of the multi-GPU run
+(tests/test_gpu_peer_multi.py and bench.py's packed_rows_fused_push variant run it across real devices).
+
+Also here: the peer-barrier watchdog: a rank that does not arrive must never produce a silent sum of stale data."""
+import ctypes as C
+import time
+
+import numpy as np
+import pytest
+import torch
+
+import common
+
+pytestmark = pytest.mark.gpu
+
+
+def _views(n, W=160, H=120):
+    from gaussian_splatting_with_eye_tracking_b200 import scenes
+    import math
+    return [scenes.look_at_camera((3.2 * math.sin(2 * math.pi * k / n + 0.3), 0.4 - 0.1 * k, -3.2 * math.cos(2 * math.pi * k / n + 0.3)),
+                                  (0, 0, 0), W, H, 0.9) for k in range(n)]
+
+
+def _backward(d, camd, cam, dpix, radii, gb, N, bb, ib, **kw):
+    from gaussian_splatting_with_eye_tracking_b200 import _host
+    return _host.rasterize_gaussians_backward(
+        d["bg"], d["means3D"], radii, d["colors_precomp"], d["scales"], d["rotations"], 1.0, d["cov3D_precomp"], camd.world_view_transform,
+        camd.full_proj_transform, cam.tanfovx, cam.tanfovy, dpix, d["shs"], d["sh_degree"], camd.camera_center, gb, N, bb, ib, False, **kw)
+
+
+@pytest.mark.parametrize("world", [1, 2, 3, 8])
+def test_pushed_rows_plus_owner_sum_equal_the_rank_ordered_sum(world, cuda_device):
+    from gaussian_splatting_with_eye_tracking_b200 import _capi, _host
+    lib = _capi.lib
+    dev = cuda_device
+    sc, _ = common.make_case("small")
+    P = sc["means3D"].shape[0]
+    P4 = (P + 3) // 4 * 4
+    rows = ((P + world - 1) // world + 255) // 256 * 256
+    numel = 11 * P4
+    staging = world * rows * 12
+    fb = int(lib.gsr_peer_flag_bytes(world))
+    bufs = [torch.full((numel + staging + fb // 4,), float("nan"), dtype=torch.float32, device=dev) for _ in range(world)]
+    for b in bufs:
+        b[numel + staging:].zero_()
+    bases = torch.tensor([b.data_ptr() for b in bufs], dtype=torch.int64, device=dev)
+    W32 = (P + 31) // 32
+    masks = torch.zeros((world, W32 + 3), dtype=torch.int32, device=dev)
+    want = [torch.zeros(P, 3), torch.zeros(P, 1), torch.zeros(P, 3), torch.zeros(P, 4)]
+    for r, cam in enumerate(_views(world)):
+        d, camd = common.cuda_inputs(sc, cam, dev)
+        dpix = common.upstream_gradient(cam, seed=3003 + r).to(dev)
+        N, img, radii, gb, bb, ib = _host.rasterize_gaussians(*common.fwd_args(d, camd), False)
+        ref = _backward(d, camd, cam, dpix, radii, gb, N, bb, ib)
+        for acc, k in zip(want, (3, 2, 6, 7)):
+            acc += ref[k].cpu().reshape(acc.shape)              # rank order, float32
+        vis = (radii > 0).cpu().numpy()
+        bits = np.zeros(W32 * 32, dtype=np.uint8); bits[:P] = vis
+        masks[r, :W32] = torch.from_numpy(np.packbits(bits.reshape(-1, 32)[:, ::-1], axis=1).view(">u4").astype(np.uint32).view(np.int32).reshape(-1)).to(dev)
+        _backward(d, camd, cam, dpix, radii, gb, N, bb, ib, dense_out=bufs[r][:numel],
+                  push=(bases.data_ptr(), numel * 4, r, world, rows))
+    torch.cuda.synchronize()
+    streams = [torch.cuda.Stream(device=dev) for _ in range(world)]
+    for r in range(world):
+        with torch.cuda.stream(streams[r]):
+            _capi.check(lib.gsr_peer_owner_sum(C.c_void_p(bases.data_ptr()), None, numel * 4, 0, P, rows, C.c_void_p(masks.data_ptr()),
+                                               masks.shape[1], (numel + staging) * 4, world, r, 1, C.c_void_p(streams[r].cuda_stream)),
+                        "gsr_peer_owner_sum")
+    torch.cuda.synchronize()
+    assert lib.gsr_peer_error() == 0
+    for b in bufs:
+        flat = b[:numel].cpu()
+        got = [flat[0:3 * P].view(P, 3), flat[3 * P4:3 * P4 + P].view(P, 1), flat[4 * P4:4 * P4 + 3 * P].view(P, 3), flat[7 * P4:7 * P4 + 4 * P].view(P, 4)]
+        for g, w_ in zip(got, want):
+            assert torch.equal(g, w_), "owner sum differs from the rank-ordered float32 sum"
+
+
+def test_fused_exchange_through_the_host_classes_single_rank(cuda_device):
+    """world = 1 through dist.PeerAllReduce / ShGradExchange(fused=True): the dense gradients and the rebuilt SH gradient equal a
+    plain backward bit for bit."""
+    from gaussian_splatting_with_eye_tracking_b200 import _host, dist as gdist
+    dev = cuda_device
+    sc, cam = common.make_case("small")
+    d, camd = common.cuda_inputs(sc, cam, dev)
+    P, M = d["means3D"].shape[0], d["shs"].shape[1]
+    dpix = common.upstream_gradient(cam).to(dev)
+    N, img, radii, gb, bb, ib = _host.rasterize_gaussians(*common.fwd_args(d, camd), False)
+    ref = _backward(d, camd, cam, dpix, radii, gb, N, bb, ib)
+    peer = gdist.PeerAllReduce(11 * ((P + 3) // 4 * 4), dev, staging_gaussians=P)
+    exch = gdist.ShGradExchange(packed=True, peer=peer, fused=True)
+    for _ in range(2):                                         # twice: epochs advance, buffers are reused
+        exch.post_visible_count(_host.last_counts(gb, P)[2], dev)
+        g = _backward(d, camd, cam, dpix, radii, gb, N, bb, ib, compact_sh=True,
+                      between_phases=lambda drgb: exch.start_gather(drgb, camd.camera_center, d["means3D"], d["sh_degree"], M, radii=radii),
+                      dense_out=peer.data, push=peer.push_args)
+        exch.start_reduce([g[3], g[2], g[6], g[7]])
+        dsh = exch.finish()
+        torch.cuda.synchronize()
+        for k in (3, 2, 6, 7):
+            assert torch.equal(g[k], ref[k]), f"dense gradient {k}"
+        assert torch.equal(dsh, ref[5])
+
+
+def test_peer_watchdog_poisons_and_reports(cuda_device):
+    """One of two ranks never arrives: after the (shortened) watchdog time the waiting rank's sum is NaN, not stale data, and
+    gsr_peer_error() reports it; the late rank then completes and the pair is usable again."""
+    from gaussian_splatting_with_eye_tracking_b200 import _capi
+    lib = _capi.lib
+    dev = cuda_device
+    n = 1024
+    fb = int(lib.gsr_peer_flag_bytes(2))
+    bufs = [torch.ones(n + fb // 4, dtype=torch.float32, device=dev) for _ in range(2)]
+    for b in bufs:
+        b[n:].zero_()
+    bases = torch.tensor([b.data_ptr() for b in bufs], dtype=torch.int64, device=dev)
+    streams = [torch.cuda.Stream(device=dev) for _ in range(2)]
+    _capi.check(lib.gsr_set_option(6, 200), "gsr_set_option")              # GSR_OPT_PEER_TIMEOUT_MS = 200 ms
+    try:
+        assert lib.gsr_peer_error() == 0
+        with torch.cuda.stream(streams[0]):                                  # rank 0 alone
+            _capi.check(lib.gsr_peer_allreduce_sum(C.c_void_p(bases.data_ptr()), 0, n, n * 4, 2, 0, 1, C.c_void_p(streams[0].cuda_stream)), "sum")
+        t0 = time.time()
+        streams[0].synchronize()
+        assert 0.15 < time.time() - t0 < 5.0
+        assert lib.gsr_peer_error() == 1 and lib.gsr_peer_error() == 0      # reported once, then cleared
+        half = n // 2
+        assert bool(torch.isnan(bufs[0][:half]).all()) and bool(torch.isnan(bufs[1][:half]).all()), "rank 0's slice must be poisoned on both ranks"
+    finally:
+        _capi.check(lib.gsr_set_option(6, 0), "gsr_set_option")             # back to the default (10 min)
+        with torch.cuda.stream(streams[1]):                                  # the late rank drains its side
+            lib.gsr_peer_allreduce_sum(C.c_void_p(bases.data_ptr()), 0, n, n * 4, 2, 1, 1, C.c_void_p(streams[1].cuda_stream))
+        torch.cuda.synchronize()
+        lib.gsr_peer_error()
