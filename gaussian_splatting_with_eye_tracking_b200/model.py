@@ -65,16 +65,28 @@ def quaternion_to_matrix(q: torch.Tensor) -> torch.Tensor:
     return torch.stack(rows, dim=1).reshape(-1, 3, 3)
 
 
-def mean_knn_dist2(points: torch.Tensor, k: int = 3, chunk: int = 4096) -> torch.Tensor:
+def mean_knn_dist2(points: torch.Tensor, k: int = 3, chunk: int = 1024) -> torch.Tensor:
     """Mean squared distance to the k nearest neighbours -- what ``simple_knn._C.distCUDA2`` returns
-    (submodules/simple-knn, not part of this build: SURVEY 9).  Exact, chunked brute force; parity unpinned (the
-    reference's routine is CUDA-only and absent here)."""
+    (submodules/simple-knn, not part of this build: SURVEY 9).  Chunked brute force on explicit coordinate differences of the
+    CENTRED cloud: ``torch.cdist`` switches to the matmul expansion |x|^2 + |y|^2 - 2xy above 25 rows, which cancels
+    catastrophically in float32 for clouds far from the origin (7 % median error, negative distances, measured by the round-1
+    advisor).  Pinned against a float64 brute force in tests/test_cpu_model.py; parity with the reference's CUDA routine itself
+    stays unpinned (it is absent here).  Memory: chunk x P x 4 bytes per temporary."""
     P = points.shape[0]
     out = torch.empty(P, dtype=points.dtype, device=points.device)
+    if P == 0:
+        return out
+    pts = points - points.mean(dim=0, keepdim=True)
+    kk = min(k + 1, P)
+    px, py, pz = pts[:, 0].contiguous(), pts[:, 1].contiguous(), pts[:, 2].contiguous()
     for a in range(0, P, chunk):
-        d = torch.cdist(points[a:a + chunk], points).pow(2)
-        kk = min(k + 1, P)
-        near = d.topk(kk, dim=1, largest=False).values[:, 1:]              # drop the point itself
+        q = pts[a:a + chunk]
+        d = (q[:, 0:1] - px[None, :]).square_()
+        d += (q[:, 1:2] - py[None, :]).square_()
+        d += (q[:, 2:3] - pz[None, :]).square_()
+        rows = torch.arange(q.shape[0], device=points.device)
+        d[rows, a + rows] = -1.0                                          # the point itself sorts first, whatever duplicates exist
+        near = d.topk(kk, dim=1, largest=False).values[:, 1:]
         out[a:a + chunk] = near.mean(dim=1) if near.shape[1] else 0.0
     return out
 

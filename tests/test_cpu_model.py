@@ -103,3 +103,27 @@ def test_schedule_ply_and_point_cloud_initialisation(tmp_path):
     gm3.restore(gm.capture(), a)
     assert torch.equal(gm3.optimizer.state[gm3._xyz]["exp_avg"], gm.optimizer.state[gm._xyz]["exp_avg"])
     assert gm3.spatial_lr_scale == 2.5 and torch.equal(gm3.get_xyz, gm.get_xyz)
+
+
+def test_mean_knn_dist2_against_float64_brute_force_far_from_the_origin():
+    """torch.cdist's matmul expansion lost all precision for a cloud offset by (40, -25, 60) with nearest-neighbour
+    distances around 5e-2.  The replacement is pinned on a float64 brute force: near the origin, far from it, with duplicates."""
+    import numpy as np
+    from gaussian_splatting_with_eye_tracking_b200.model import mean_knn_dist2
+    g = torch.Generator().manual_seed(5)
+    base = torch.rand(3000, 3, generator=g) * 0.5
+    for off in ((0.0, 0.0, 0.0), (40.0, -25.0, 60.0), (-900.0, 300.0, 1200.0)):
+        pts = base + torch.tensor(off)
+        pts[10] = pts[11]                                                  # an exact duplicate: distance 0 counts as a neighbour
+        got = mean_knn_dist2(pts).double().numpy()
+        p64 = pts.double().numpy()
+        want = np.empty(len(p64))
+        for i in range(len(p64)):
+            d2 = ((p64 - p64[i]) ** 2).sum(1)
+            d2[i] = np.inf
+            want[i] = np.sort(d2)[:3].mean()
+        rel = np.abs(got - want) / np.maximum(want, 1e-12)
+        assert (got >= 0).all()
+        # float32 coordinates of the offset cloud carry ~1e-4 absolute error at |x| ~ 1000: compare at that resolution
+        tol = 2e-5 if max(abs(o) for o in off) < 100 else 3e-3
+        assert np.median(rel) < tol and rel.max() < 50 * tol, (off, float(np.median(rel)), float(rel.max()))
