@@ -611,7 +611,7 @@ __device__ __forceinline__ uint32_t cta1024_exclusive_scan(uint32_t v, uint32_t*
 }
 
 // row_start[r] = first sorted run of tile row r (binary search on the row field); chunk_row_start[r] = first chunk of row r
-__global__ void __launch_bounds__(1024) chunk_table_kernel(const uint32_t* __restrict__ rkeys, uint32_t R, int tiles_y,
+__global__ void __launch_bounds__(1024) chunk_table_kernel(const uint32_t* __restrict__ rkeys, uint32_t R, int tiles_y, int chunk,
                                                            const uint32_t* __restrict__ row_offsets,   // sort's digit offsets or nullptr
                                                            uint32_t* __restrict__ row_start, uint32_t* __restrict__ chunk_row_start) {
     __shared__ uint32_t s_warp[32];
@@ -627,7 +627,7 @@ __global__ void __launch_bounds__(1024) chunk_table_kernel(const uint32_t* __res
     for (int base = 0; base <= tiles_y; base += 1024) {
         const int r = base + tid;
         uint32_t nch = 0;
-        if (r < tiles_y) { const uint32_t len = row_start[r + 1] - row_start[r]; nch = (len + kRunChunk - 1) / kRunChunk; }
+        if (r < tiles_y) { const uint32_t len = row_start[r + 1] - row_start[r]; nch = (len + chunk - 1) / chunk; }
         uint32_t tot;
         const uint32_t ex = cta1024_exclusive_scan(nch, s_warp, &tot);
         if (r <= tiles_y) chunk_row_start[r] = carry + ex;      // entry [tiles_y] = total number of chunks
@@ -637,26 +637,26 @@ __global__ void __launch_bounds__(1024) chunk_table_kernel(const uint32_t* __res
 
 struct ChunkCtx { int row; uint32_t r0, r1; };
 // which rows' runs does chunk c cover?  (binary search over the <= 4096 rows; CTA-uniform)
-__device__ __forceinline__ bool chunk_lookup(uint32_t c, int tiles_y, const uint32_t* __restrict__ chunk_row_start,
+__device__ __forceinline__ bool chunk_lookup(uint32_t c, int tiles_y, int chunk, const uint32_t* __restrict__ chunk_row_start,
                                              const uint32_t* __restrict__ row_start, ChunkCtx& cx) {
     if (c >= __ldg(chunk_row_start + tiles_y)) return false;
     int lo = 0, hi = tiles_y;                  // invariant: chunk_row_start[lo] <= c < chunk_row_start[hi]
     while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (__ldg(chunk_row_start + mid) <= c) lo = mid; else hi = mid; }
     cx.row = lo;
     const uint32_t k = c - __ldg(chunk_row_start + lo);
-    cx.r0 = __ldg(row_start + lo) + k * kRunChunk;
-    cx.r1 = min(cx.r0 + (uint32_t)kRunChunk, __ldg(row_start + lo + 1));
+    cx.r0 = __ldg(row_start + lo) + k * (uint32_t)chunk;
+    cx.r1 = min(cx.r0 + (uint32_t)chunk, __ldg(row_start + lo + 1));
     return true;
 }
 
 // per chunk: how many of its runs cover each tile column (difference array + scan)
-__global__ void __launch_bounds__(256) chunk_count_kernel(const uint32_t* __restrict__ rkeys, int tiles_x, int tiles_y,
+__global__ void __launch_bounds__(256) chunk_count_kernel(const uint32_t* __restrict__ rkeys, int tiles_x, int tiles_y, int chunk,
                                                           const uint32_t* __restrict__ chunk_row_start, const uint32_t* __restrict__ row_start,
                                                           uint32_t* __restrict__ chunk_counts, uint4* __restrict__ chunk_info) {
     extern __shared__ int s_diff[];               // [tiles_x + 1], then reused for the scanned counts
     __shared__ int s_wsum[8];
     ChunkCtx cx;
-    const bool live = chunk_lookup(blockIdx.x, tiles_y, chunk_row_start, row_start, cx);
+    const bool live = chunk_lookup(blockIdx.x, tiles_y, chunk, chunk_row_start, row_start, cx);
     // the chunk's place, for expand_runs_kernel (one 16-byte load there instead of a second binary search)
     if (threadIdx.x == 0) chunk_info[blockIdx.x] = live ? make_uint4((uint32_t)cx.row, cx.r0, cx.r1, 1u) : make_uint4(0u, 0u, 0u, 0u);
     if (!live) return;
@@ -749,52 +749,62 @@ __global__ void __launch_bounds__(1024) tile_scan_kernel(uint32_t* __restrict__ 
 // scatter into a different tile (32 sectors per store instruction, 1 cycle each in the L1: that, not DRAM, was its limit).
 // No per-(group, column) offset table, no rank look-ups.
 constexpr int kExpandThreads = 256;
-constexpr int kExpandBatches = kRunChunk / kExpandThreads;       // runs per thread
-constexpr int kExpandPlanes = kRunChunk / 32;                    // words per column
-constexpr int kExpandStride = kExpandPlanes + 1;                 // odd stride: phase-1 atomics of neighbouring columns hit different banks
-
+// CHUNK = 1024 or 2048 runs per CTA.  The per-column decode has a fixed cost per column and chunk (scan, look-ups), so the larger
+// chunk halves it per run; it needs [CHUNK] ids + tiles_x x (CHUNK/32 + pad) coverage words of shared memory (40 KB at 1080p for
+// 2048) and is used up to 600 tile columns.
+template <int CHUNK>
 __global__ void __launch_bounds__(kExpandThreads) expand_runs_kernel(const uint32_t* __restrict__ rkeys, const uint32_t* __restrict__ rvals,
                                                                      int tiles_x, const uint4* __restrict__ chunk_info,
                                                                      const uint32_t* __restrict__ chunk_counts,
                                                                      const uint32_t* __restrict__ tile_start, uint32_t* __restrict__ point_list) {
-    extern __shared__ uint32_t s_mem[];
-    uint32_t* s_ids = s_mem;                                            // [kRunChunk] Gaussian id of run r
-    uint32_t* s_bits = s_ids + kRunChunk;                               // [tiles_x][kExpandStride] coverage words
+    constexpr int BATCHES = CHUNK / kExpandThreads;                     // runs per thread
+    constexpr int PLANES = CHUNK / 32;                                  // coverage words per column
+    constexpr int WPL = PLANES / 32;                                    // words per lane in the decode
+    constexpr int STRIDE = PLANES + (WPL == 1 ? 1 : 2);                 // 33: odd; 66: lane's two words 8-byte aligned, columns 2 banks apart
+    extern __shared__ __align__(16) uint32_t s_mem[];
+    uint32_t* s_ids = s_mem;                                            // [CHUNK] Gaussian id of run r
+    uint32_t* s_bits = s_ids + CHUNK;                                   // [tiles_x][STRIDE] coverage words
     const uint4 info = __ldg(chunk_info + blockIdx.x);                  // (row, first run, end run, valid)
     if (info.w == 0u) return;
     const uint32_t row = info.x, r0 = info.y, r1 = info.z;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-    uint32_t keys[kExpandBatches];
+    uint32_t keys[BATCHES];
 #pragma unroll
-    for (int b = 0; b < kExpandBatches; ++b) {
+    for (int b = 0; b < BATCHES; ++b) {
         const uint32_t r = r0 + b * kExpandThreads + tid;
         keys[b] = (r < r1) ? __ldg(rkeys + r) : 0u;                     // width field 0: covers nothing
         s_ids[b * kExpandThreads + tid] = (r < r1) ? __ldg(rvals + r) : 0u;
     }
-    for (int i = tid; i < tiles_x * kExpandStride; i += kExpandThreads) s_bits[i] = 0;
+    for (int i = tid; i < tiles_x * STRIDE; i += kExpandThreads) s_bits[i] = 0;
     __syncthreads();
 #pragma unroll
-    for (int b = 0; b < kExpandBatches; ++b) {
-        const int q = b * (kExpandThreads / 32) + wid;                  // group of run b*256 + tid
+    for (int b = 0; b < BATCHES; ++b) {
+        const int q = b * (kExpandThreads / 32) + wid;                  // group (coverage word) of run b*256 + tid
         const uint32_t x0 = (keys[b] >> kRunX0Shift) & kRunFieldMask, w = keys[b] & kRunFieldMask;
-        for (uint32_t i = 0; i < w; ++i) atomicOr(&s_bits[(x0 + i) * kExpandStride + q], 1u << lane);
+        for (uint32_t i = 0; i < w; ++i) atomicOr(&s_bits[(x0 + i) * STRIDE + q], 1u << lane);
     }
     __syncthreads();
     const uint32_t* cc = chunk_counts + (size_t)blockIdx.x * tiles_x;
     const uint32_t* ts = tile_start + (size_t)row * tiles_x;
     for (int x = wid; x < tiles_x; x += kExpandThreads / 32) {
-        uint32_t word = s_bits[x * kExpandStride + lane];
-        const uint32_t c = __popc(word);
+        uint32_t word[WPL];
+        uint32_t c = 0;
+#pragma unroll
+        for (int k = 0; k < WPL; ++k) { word[k] = s_bits[x * STRIDE + lane * WPL + k]; c += __popc(word[k]); }
         uint32_t inc = c;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) { const uint32_t u = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += u; }
         if (__shfl_sync(0xffffffffu, inc, 31) == 0u) continue;          // nothing of this chunk in column x (warp-uniform)
         uint32_t slot = __ldg(ts + x) + __ldg(cc + x) + inc - c;        // first list slot of this lane's runs
-        const uint32_t* ids = s_ids + lane * 32;
-        while (word) {
-            const int bpos = __ffs(word) - 1;
-            word &= word - 1u;
-            point_list[slot++] = ids[bpos];
+#pragma unroll
+        for (int k = 0; k < WPL; ++k) {
+            const uint32_t* ids = s_ids + (lane * WPL + k) * 32;
+            uint32_t wd = word[k];
+            while (wd) {
+                const int bpos = __ffs(wd) - 1;
+                wd &= wd - 1u;
+                point_list[slot++] = ids[bpos];
+            }
         }
     }
 }
@@ -806,26 +816,31 @@ void launch_expand_runs(const BinPtrs& b, const uint32_t* rkeys_sorted, const ui
                         const uint32_t* row_offsets, uint2* ranges, uint32_t* n_intersections, const GeomHeader* hdr, uint32_t* mailbox_dev,
                         int prof_ranges, int prof_expand, cudaStream_t s) {
     const int num_tiles = tiles_x * tiles_y;
-    const unsigned grid = (unsigned)b.max_chunks;
+    const int chunk = tiles_x <= 600 ? 2048 : kRunChunk;                // runs per expansion chunk (tables are sized for kRunChunk: an upper bound)
+    const unsigned grid = (unsigned)(R / chunk + tiles_y + 1);
     {
         ProfScope ps(prof_ranges, s);
-        chunk_table_kernel<<<1, 1024, 0, s>>>(rkeys_sorted, (uint32_t)R, tiles_y, row_offsets, b.row_start, b.chunk_row_start);
-        chunk_count_kernel<<<grid, 256, sizeof(int) * (tiles_x + 1), s>>>(rkeys_sorted, tiles_x, tiles_y, b.chunk_row_start, b.row_start, b.chunk_counts, b.chunk_info);
+        chunk_table_kernel<<<1, 1024, 0, s>>>(rkeys_sorted, (uint32_t)R, tiles_y, chunk, row_offsets, b.row_start, b.chunk_row_start);
+        chunk_count_kernel<<<grid, 256, sizeof(int) * (tiles_x + 1), s>>>(rkeys_sorted, tiles_x, tiles_y, chunk, b.chunk_row_start, b.row_start, b.chunk_counts, b.chunk_info);
         row_scan_kernel<<<dim3((tiles_x + 31) / 32, tiles_y), 1024, 0, s>>>(tiles_x, b.chunk_row_start, b.chunk_counts, b.tile_start);
         tile_scan_kernel<<<1, 1024, 0, s>>>(b.tile_start, num_tiles, ranges, n_intersections, hdr, mailbox_dev, g_fake_sort_error);
         count_launch(4);
     }
     {
         ProfScope ps(prof_expand, s);
-        // [1024] ids + [tiles_x][33] coverage words: 20 KB at 1080p, 139 KB at the 1023-column limit
-        const size_t smem = sizeof(uint32_t) * ((size_t)kRunChunk + (size_t)tiles_x * kExpandStride);
         static bool attr_done = false;
         if (!attr_done) {
-            cudaFuncSetAttribute(expand_runs_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 (int)(sizeof(uint32_t) * (kRunChunk + 1023 * kExpandStride)));
+            cudaFuncSetAttribute(expand_runs_kernel<1024>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(uint32_t) * (1024 + 1023 * 33)));
+            cudaFuncSetAttribute(expand_runs_kernel<2048>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(uint32_t) * (2048 + 600 * 66)));
             attr_done = true;
         }
-        expand_runs_kernel<<<grid, kExpandThreads, smem, s>>>(rkeys_sorted, rvals_sorted, tiles_x, b.chunk_info, b.chunk_counts, b.tile_start, b.vals);
+        if (chunk == 2048) {
+            const size_t smem = sizeof(uint32_t) * (2048 + (size_t)tiles_x * 66);      // 40 KB at 1080p
+            expand_runs_kernel<2048><<<grid, kExpandThreads, smem, s>>>(rkeys_sorted, rvals_sorted, tiles_x, b.chunk_info, b.chunk_counts, b.tile_start, b.vals);
+        } else {
+            const size_t smem = sizeof(uint32_t) * (1024 + (size_t)tiles_x * 33);      // 139 KB at the 1023-column limit
+            expand_runs_kernel<1024><<<grid, kExpandThreads, smem, s>>>(rkeys_sorted, rvals_sorted, tiles_x, b.chunk_info, b.chunk_counts, b.tile_start, b.vals);
+        }
         count_launch();
     }
 }
