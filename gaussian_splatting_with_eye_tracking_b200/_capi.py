@@ -116,6 +116,7 @@ SYMBOLS = {
     "gsr_l1_ssim_backward": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_float, C.c_float, C.c_void_p,
                                        C.c_void_p, C.c_void_p, C.c_void_p]),
     "gsr_adam_step": (C.c_int, [C.POINTER(GsrAdamTensor), C.c_int, C.c_double, C.c_double, C.c_double, C.c_void_p]),
+    "gsr_pack_rgb8": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
     "gsr_peer_flag_bytes": (C.c_size_t, [C.c_int]),
     "gsr_peer_barrier": (C.c_int, [C.c_void_p, C.c_size_t, C.c_int, C.c_int, C.c_uint, C.c_void_p]),
     "gsr_peer_owner_sum": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t, C.c_int, C.c_int, C.c_void_p, C.c_size_t, C.c_size_t,

@@ -320,6 +320,36 @@ __global__ void __launch_bounds__(kAdamThreads) adam_multi_kernel(const AdamPack
 
 using namespace gsr;
 
+namespace gsr {
+// 4 pixels per thread: three 16-byte-ish channel reads (scalar when unaligned / at the tail), one 12-byte store group
+__global__ void __launch_bounds__(256) pack_rgb8_kernel(const float* __restrict__ img, long long px, unsigned char* __restrict__ out) {
+    const long long g = (long long)blockIdx.x * 256 + threadIdx.x;
+    const long long p0 = g * 4;
+    if (p0 >= px) return;
+    const int n = (int)min(4LL, px - p0);
+    unsigned char v[12];
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        const float* src = img + (size_t)c * px + p0;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const float x = k < n ? __ldg(src + k) : 0.f;
+            const float y = fminf(fmaxf(x, 0.f), 1.f) * 255.f;          // clamp(min=0,max=1): NaN -> propagates in torch; here NaN -> 0
+            v[3 * k + c] = (unsigned char)(int)y;                        // .byte(): truncation toward zero
+        }
+    }
+    unsigned char* dst = out + p0 * 3;
+    if (n == 4 && ((size_t)dst & 3) == 0) {
+        uint32_t* d4 = reinterpret_cast<uint32_t*>(dst);
+        d4[0] = v[0] | (v[1] << 8) | (v[2] << 16) | ((uint32_t)v[3] << 24);
+        d4[1] = v[4] | (v[5] << 8) | (v[6] << 16) | ((uint32_t)v[7] << 24);
+        d4[2] = v[8] | (v[9] << 8) | (v[10] << 16) | ((uint32_t)v[11] << 24);
+    } else {
+        for (int k = 0; k < 3 * n; ++k) dst[k] = v[k];
+    }
+}
+}  // namespace gsr
+
 extern "C" {
 
 size_t gsr_l1_ssim_partials(int channels, int height, int width) {
@@ -385,6 +415,18 @@ int gsr_adam_step(const gsr_adam_tensor* tensors, int count, double beta1, doubl
         count_launch(); ++launched;
     }
     return launched ? check_last("adam_step", false, s) : GSR_OK;
+}
+
+// ---- presenter: float [3,H,W] frame -> the viewer's uint8 [H,W,3] layout.
+// Replaces `(torch.clamp(net_image, min=0, max=1.0) * 255).byte().permute(1, 2, 0).contiguous()` (train.py:60): four passes
+// over the frame in the reference, one here (12 B read + 3 B written per pixel).  `.byte()` truncates toward zero.
+int gsr_pack_rgb8(const float* image_chw, int width, int height, unsigned char* out_hwc, void* stream) {
+    if (width <= 0 || height <= 0 || !image_chw || !out_hwc) { set_error("pack_rgb8: bad arguments"); return GSR_ERR_INVALID; }
+    const long long px = (long long)width * height;
+    const long long groups = (px + 3) / 4;
+    pack_rgb8_kernel<<<(unsigned)((groups + 255) / 256), 256, 0, (cudaStream_t)stream>>>(image_chw, px, out_hwc);
+    count_launch();
+    return check_last("pack_rgb8", false, (cudaStream_t)stream);
 }
 
 }  // extern "C"

@@ -311,6 +311,10 @@ GSR_API int gsr_l1_ssim_backward(int channels, int height, int width, const floa
                                  const float* maps, const float* dloss, float* dL_dimage, void* stream);
 GSR_API int gsr_adam_step(const gsr_adam_tensor* tensors, int count, double beta1, double beta2, double eps, void* stream);
 
+/* ---- presenter (replaces train.py:60): float32 [3,H,W] frame -> uint8 [H,W,3], clamp to [0,1], x255, truncate.
+ * The 8-bit interleaved layout is what the reference's network viewer protocol carries (gaussian_renderer/network_gui.py:50-55). */
+GSR_API int gsr_pack_rgb8(const float* image_chw, int width, int height, unsigned char* out_hwc, void* stream);
+
 /* ---- view-parallel gradient sum over NVLink peer memory (replaces the NCCL all-reduce of the 11 dense
  * floats per Gaussian that follows the preprocess-stage backward) ----
  * peer_bases: DEVICE array of `world` base pointers, entry k = rank k's buffer as addressable from THIS device (peer-mapped
