@@ -415,6 +415,38 @@ def dp_rank1_variants(impl, d, cam_of, w, timer, Kb, world, dev, only=None):
     return res, peer_red, peer_err
 
 
+def raw_params_leg(impl, d, cams, args, timer, rank, K):
+    """the reference's caller materialises activated copies of every parameter per frame (scene/gaussian_model.py
+    :95-115 -- sigmoid, exp, normalize, torch.cat of the SH tensors) before the rasterizer reads them again; the raw-parameter
+    entry reads the model's raw tensors directly.  Both timed through the public Python API on the same model and views."""
+    import math
+    from gaussian_splatting_with_eye_tracking_b200 import model, rasterizer
+    pc = model.GaussianModel(d["sh_degree"])
+    op = d["opacities"].clamp(1e-6, 1 - 1e-6)
+    pc._adopt({"xyz": d["means3D"], "features_dc": d["shs"][:, :1].contiguous(), "features_rest": d["shs"][:, 1:].contiguous(),
+               "opacity": torch.log(op / (1 - op)), "scaling": torch.log(d["scales"]), "rotation": d["rotations"] * 1.7})
+    pc.active_sh_degree = d["sh_degree"]
+    P_ = d["means3D"].shape[0]
+    cam_of = lambda i: cams[(i + rank) % len(cams)]          # noqa: E731
+
+    def activated(i):
+        cam = cam_of(i)
+        rs = rasterizer.GaussianRasterizationSettings(cam.image_height, cam.image_width, math.tan(cam.FoVx * 0.5), math.tan(cam.FoVy * 0.5), d["bg"], 1.0,
+                                                      cam.world_view_transform, cam.full_proj_transform, d["sh_degree"], cam.camera_center, False, False)
+        with torch.no_grad():
+            return impl.dgr.GaussianRasterizer(rs)(means3D=pc.get_xyz, means2D=None, opacities=pc.get_opacity, shs=pc.get_features,
+                                                   scales=pc.get_scaling, rotations=pc.get_rotation)[0]
+
+    def raw(i):
+        with torch.no_grad():
+            return rasterizer.render_raw(cam_of(i), pc, d["bg"])["render"]
+    ms_a = timer.run(activated, K, 3, prime=8)
+    ms_r = timer.run(raw, K, 3, prime=8)
+    return {"activated_getters_ms_per_frame": ms_a / K, "raw_entry_ms_per_frame": ms_r / K, "speedup": ms_a / ms_r,
+            "caller_bytes_saved_per_frame": 2 * 236 * P_, "what": "forward through the Python API: reference-style getters (sigmoid, exp, normalize, cat) + rasterizer "
+            "vs rasterize_gaussians_raw on the raw tensors; 236 B/Gaussian of activated copies are neither written nor re-read"}
+
+
 def c2_leg(make_impl, timer, rank, K):
     """Config C2 (BASELINE.json configs[1]): 100 k Gaussians, SH degree 3, one 800x800 view, forward and forward+backward ms/view
     on one GPU (NeRF-synthetic scale).  At this size the launch chain and the host round trip, not the kernels, set the time."""
@@ -1119,6 +1151,10 @@ def main():
                                                           "fwd_bwd": r["fwd_bwd_ms_per_view"] / m["fwd_bwd_ms_per_view"]}
                 except Exception as ex:     # reported, never fatal for our own line
                     extra["reference_cuda_same_run"] = {"error": str(ex)[:300]}
+            try:
+                extra["raw_params"] = raw_params_leg(impl, d, cams, args, timer, 0, args.steps)
+            except Exception as ex:
+                extra["raw_params"] = {"error": f"{type(ex).__name__}: {str(ex)[:300]}"}
             try:
                 c2, sc2 = c2_leg(lambda d2: Ours(d2), timer, 0, args.steps)
                 if ref_ok:

@@ -23,8 +23,11 @@ from .rasterizer import (  # noqa: F401
     GaussianRasterizerBaseline,
     RasterizeGaussiansAMR,
     RasterizeGaussiansBaseline,
+    RasterizeGaussiansRaw,
     rasterize_gaussians_amr,
     rasterize_gaussians_baseline,
+    rasterize_gaussians_raw,
+    render_raw,
 )
 
 __all__ = [

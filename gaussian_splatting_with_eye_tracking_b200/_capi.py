@@ -29,7 +29,7 @@ class GsrScene(C.Structure):
         ("P", C.c_int), ("sh_degree", C.c_int), ("sh_coeffs", C.c_int),
         ("means3D", C.c_void_p), ("shs", C.c_void_p), ("colors_precomp", C.c_void_p), ("opacities", C.c_void_p),
         ("scales", C.c_void_p), ("rotations", C.c_void_p), ("cov3D_precomp", C.c_void_p),
-        ("scale_modifier", C.c_float),
+        ("scale_modifier", C.c_float), ("raw_params", C.c_int), ("shs_rest", C.c_void_p),
     ]
 
 

@@ -98,7 +98,10 @@ _ALLOC_CB = _capi.ALLOC_FN(_alloc_trampoline)
 
 
 def _scene_camera(background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp, viewmatrix,
-                  projmatrix, tan_fovx, tan_fovy, image_height, image_width, sh, degree, campos, prefiltered, band=None):
+                  projmatrix, tan_fovx, tan_fovy, image_height, image_width, sh, degree, campos, prefiltered, band=None, sh_rest=None):
+    """``sh_rest`` is not None: raw-parameter entry (gsr_scene.raw_params) -- opacity / scales / rotations are the RAW tensors of
+    scene/gaussian_model.py (logit, log-scale, un-normalised quaternion), ``sh`` = features_dc [P,1,3], ``sh_rest`` =
+    features_rest [P,M-1,3]; the kernels apply the activations on load."""
     if means3D.ndimension() != 2 or means3D.size(1) != 3:
         raise RuntimeError("means3D must have dimensions (num_points, 3)")
     P = int(means3D.size(0))
@@ -115,9 +118,17 @@ def _scene_camera(background, means3D, colors, opacity, scales, rotations, scale
     keep.proj = _dev_tensor(projmatrix, "projmatrix")
     keep.campos = _dev_tensor(campos, "campos")
     M = int(sh.size(1)) if (sh is not None and sh.dim() >= 2 and sh.size(0) != 0) else 0
+    keep.sh_rest = None
+    raw = sh_rest is not None
+    if raw:
+        if M != 1:
+            raise RuntimeError("raw-parameter entry: sh must be features_dc [P,1,3]")
+        keep.sh_rest = _dev_tensor(sh_rest, "features_rest")
+        M = 1 + (int(sh_rest.size(1)) if keep.sh_rest is not None else 0)
     sc = GsrScene(P=P, sh_degree=int(degree), sh_coeffs=M, means3D=_p(keep.means3D), shs=_p(keep.sh),
                   colors_precomp=_p(keep.colors), opacities=_p(keep.opacity), scales=_p(keep.scales),
-                  rotations=_p(keep.rotations), cov3D_precomp=_p(keep.cov3D), scale_modifier=float(scale_modifier))
+                  rotations=_p(keep.rotations), cov3D_precomp=_p(keep.cov3D), scale_modifier=float(scale_modifier),
+                  raw_params=1 if raw else 0, shs_rest=_p(keep.sh_rest))
     cam = GsrCamera(width=int(image_width), height=int(image_height), tan_fovx=float(tan_fovx), tan_fovy=float(tan_fovy),
                     background=_p(keep.bg), viewmatrix=_p(keep.view), projmatrix=_p(keep.proj), cam_pos=_p(keep.campos),
                     prefiltered=1 if prefiltered else 0, band_row0=int(band[0]) if band else 0,
@@ -134,12 +145,13 @@ def _stream():
 # ----------------------------------------------------------------------------------------------------------------
 def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp,
                         viewmatrix, projmatrix, tan_fovx, tan_fovy, image_height, image_width, sh, degree, campos,
-                        prefiltered, debug, band=None):
-    """``band`` = (row0, row1): bin and blend only tile rows [row0, row1) (extension for multi-GPU tile bands;
+                        prefiltered, debug, band=None, sh_rest=None):
+    """``sh_rest`` (extension): raw-parameter entry, see ``_scene_camera``.
+    ``band`` = (row0, row1): bin and blend only tile rows [row0, row1) (extension for multi-GPU tile bands;
     rows of out_color outside the band are left unwritten).  None = the reference's whole-frame behaviour."""
     sc, cam, keep, P, _ = _scene_camera(background, means3D, colors, opacity, scales, rotations, scale_modifier,
                                         cov3D_precomp, viewmatrix, projmatrix, tan_fovx, tan_fovy, image_height,
-                                        image_width, sh, degree, campos, prefiltered, band)
+                                        image_width, sh, degree, campos, prefiltered, band, sh_rest)
     dev = means3D.device if means3D.is_cuda else torch.device("cuda")
     with torch.cuda.device(dev):
         out_color = torch.empty((3, int(image_height), int(image_width)), dtype=torch.float32, device=dev)
@@ -156,7 +168,7 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
 def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rotations, scale_modifier, cov3D_precomp,
                                  viewmatrix, projmatrix, tan_fovx, tan_fovy, dL_dout_color, sh, degree, campos,
                                  geomBuffer, R, binningBuffer, imageBuffer, debug, band=None, compact_sh=False,
-                                 between_phases=None, preprocess_chunks=1, after_chunk=None, dense_out=None, push=None):
+                                 between_phases=None, preprocess_chunks=1, after_chunk=None, dense_out=None, push=None, sh_rest=None):
     """``compact_sh=True`` (extension, view-parallel training): slot 5 of the returned tuple is the [P,3] colour
     gradient after the SH clamp mask instead of the [P,M,3] SH gradient, which is then not written at all;
     ``sh_grad_from_views`` rebuilds the SH gradient summed over views from those.
@@ -176,7 +188,7 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
     H, W = int(dL_dout_color.size(1)), int(dL_dout_color.size(2))
     sc, cam, keep, P, M = _scene_camera(background, means3D, colors, torch.empty(0), scales, rotations, scale_modifier,
                                         cov3D_precomp, viewmatrix, projmatrix, tan_fovx, tan_fovy, H, W, sh, degree,
-                                        campos, False, band)
+                                        campos, False, band, sh_rest)
     dev = means3D.device
     f32 = dict(dtype=torch.float32, device=dev)
     with torch.cuda.device(dev):

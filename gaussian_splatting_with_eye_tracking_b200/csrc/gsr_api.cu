@@ -160,6 +160,10 @@ static int validate(const gsr_scene* sc, const gsr_camera* cam, bool forward = t
             return GSR_ERR_INVALID;
         }
     }
+    if (sc->raw_params && sc->P > 0) {
+        if (sc->cov3D_precomp || !sc->scales || !sc->rotations) { set_error("raw_params needs scales and rotations (no precomputed covariance)"); return GSR_ERR_INVALID; }
+        if (!sc->colors_precomp && (!sc->shs_rest && sc->sh_coeffs > 1)) { set_error("raw_params needs shs (features_dc) and shs_rest (features_rest)"); return GSR_ERR_INVALID; }
+    }
     if (!cam->background || !cam->viewmatrix || !cam->projmatrix || !cam->cam_pos) { set_error("camera pointers are required"); return GSR_ERR_INVALID; }
     if (cam->band_row0 < 0 || cam->band_row1 < 0 || (cam->band_row1 > 0 && cam->band_row0 >= cam->band_row1) || (cam->band_row1 == 0 && cam->band_row0 != 0)) {
         set_error("bad tile band [%d,%d)", cam->band_row0, cam->band_row1); return GSR_ERR_INVALID;
@@ -195,6 +199,7 @@ static int build_lists(const gsr_scene* sc, const gsr_camera* cam, int mode, gsr
     a.P = P; a.D = sc->sh_degree; a.M = sc->sh_coeffs;
     a.means3D = sc->means3D; a.scales = sc->scales; a.rotations = sc->rotations; a.opacities = sc->opacities;
     a.shs = sc->shs; a.cov3D_precomp = sc->cov3D_precomp; a.colors_precomp = sc->colors_precomp;
+    a.shs_rest = sc->raw_params ? sc->shs_rest : nullptr; a.raw = sc->raw_params != 0;
     a.scale_modifier = sc->scale_modifier;
     a.viewmatrix = cam->viewmatrix; a.projmatrix = cam->projmatrix; a.cam_pos = cam->cam_pos;
     a.W = W; a.H = H; a.tan_fovx = cam->tan_fovx; a.tan_fovy = cam->tan_fovy;
@@ -419,6 +424,10 @@ static int backward_impl(const gsr_scene* sc, const gsr_camera* cam, const int* 
         set_error("gradient output pointers are required"); return GSR_ERR_INVALID;
     }
     if (((size_t)gr->scratch & 15) != 0) { set_error("scratch must be 16-byte aligned"); return GSR_ERR_INVALID; }
+    if (sc->raw_params && sc->shs_rest && phase != GSR_BWD_BLEND &&
+        (sc->sh_coeffs > 16 || (sc->sh_coeffs % 4) != 0 || (gr->dL_dsh && ((size_t)gr->dL_dsh & 15) != 0))) {
+        set_error("raw-parameter backward needs M in {4, 8, 12, 16} and a 16-byte aligned dL_dsh (M = %d)", sc->sh_coeffs); return GSR_ERR_INVALID;
+    }
     if (gr->push_bases && (gr->push_world < 1 || gr->push_rank < 0 || gr->push_rank >= gr->push_world || gr->push_rows_per_rank <= 0 ||
                            (gr->push_rows_per_rank % 256) != 0 || (gr->push_offset & 15) != 0 ||
                            (long long)gr->push_rows_per_rank * gr->push_world < (long long)P)) {
@@ -451,6 +460,7 @@ static int backward_impl(const gsr_scene* sc, const gsr_camera* cam, const int* 
     PreBwdArgs pb;
     pb.P = P; pb.D = sc->sh_degree; pb.M = sc->sh_coeffs;
     pb.means3D = sc->means3D; pb.scales = sc->scales; pb.rotations = sc->rotations; pb.shs = sc->shs;
+    pb.shs_rest = sc->raw_params ? sc->shs_rest : nullptr; pb.raw = sc->raw_params != 0;
     pb.cov3D = sc->cov3D_precomp ? sc->cov3D_precomp : g.cov3D;
     pb.cov_from_scales = (sc->cov3D_precomp == nullptr) && sc->scales && sc->rotations;   // backward.cu:394 `if (scales)`
     pb.colors_from_sh = colors_from_sh;

@@ -283,6 +283,7 @@ struct ProfScope {
 struct PreprocessArgs {
     int P, D, M;
     const float *means3D, *scales, *rotations, *opacities, *shs, *cov3D_precomp, *colors_precomp;
+    const float* shs_rest = nullptr; bool raw = false;       // raw-parameter entry (gsr_scene.raw_params)
     float scale_modifier;
     const float *viewmatrix, *projmatrix, *cam_pos;
     int W, H; float tan_fovx, tan_fovy, focal_x, focal_y;
@@ -381,6 +382,7 @@ void launch_blend_backward(const BlendBwdArgs& a, cudaStream_t s);
 struct PreBwdArgs {
     int P, D, M;
     const float *means3D, *scales, *rotations, *shs, *cov3D /*precomp or internal*/;
+    const float* shs_rest = nullptr; bool raw = false;
     bool cov_from_scales, colors_from_sh;
     float scale_modifier;
     const float *viewmatrix, *projmatrix, *cam_pos;

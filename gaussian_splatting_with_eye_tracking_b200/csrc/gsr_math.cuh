@@ -62,6 +62,15 @@ __device__ __forceinline__ void get_rect(float px, float py, int radius, int til
     y1 = min((uint32_t)grid_y, (uint32_t)max(0, by));
 }
 
+// activations of the raw-parameter entry (gsr_scene.raw_params; scene/gaussian_model.py:33-41): the expressions torch evaluates
+__device__ __forceinline__ float act_sigmoid(float x) { return __fdiv_rn(1.0f, __fadd_rn(1.0f, expf(-x))); }
+__device__ __forceinline__ float act_exp(float x) { return expf(x); }
+__device__ __forceinline__ float4 act_normalize(float4 q) {      // F.normalize: x / max(||x||_2, 1e-12)
+    const float n = __fsqrt_rn(__fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(q.x, q.x), __fmul_rn(q.y, q.y)), __fmul_rn(q.z, q.z)), __fmul_rn(q.w, q.w)));
+    const float d = fmaxf(n, 1e-12f);
+    return make_float4(__fdiv_rn(q.x, d), __fdiv_rn(q.y, d), __fdiv_rn(q.z, d), __fdiv_rn(q.w, d));
+}
+
 // screen-tile band (multi-GPU tile bands): keep only rows [row0,row1) of a rect; row1 == 0 means "no band"
 __device__ __forceinline__ void clip_band(uint32_t& y0, uint32_t& y1, int row0, int row1) {
     if (row1 > 0) {

@@ -29,6 +29,8 @@ struct PreFwdParams {
     const float* __restrict__ shs;
     const float* __restrict__ cov3D_precomp;
     const float* __restrict__ colors_precomp;
+    const float* __restrict__ shs_rest;     // raw-parameter entry: shs = features_dc [P,1,3], shs_rest = features_rest [P,M-1,3]
+    int raw;                                // 1: opacities / scales / rotations are raw (logit / log / un-normalised)
     float scale_modifier;
     const float* __restrict__ viewmatrix;
     const float* __restrict__ projmatrix;
@@ -66,14 +68,19 @@ struct PreFwdParams {
 
 // SH -> RGB (forward.cu:20-71).  `sh` points at this Gaussian's [M][3] coefficients.
 __device__ __forceinline__ void sh_to_rgb(int deg, const float* __restrict__ sh, bool vec4_ok,
-                                          float dx, float dy, float dz, float out[3], bool clamp_flag[3]) {
+                                          float dx, float dy, float dz, float out[3], bool clamp_flag[3],
+                                          const float* __restrict__ sh_rest = nullptr) {
     // direction = (pos - campos) / |pos - campos|
     const float len = __fsqrt_rn(sum3(dx, dx, dy, dy, dz, dz));
     const float x = __fdiv_rn(dx, len), y = __fdiv_rn(dy, len), z = __fdiv_rn(dz, len);
 
     float c[48];
     const int ncoef = (deg + 1) * (deg + 1);
-    if (vec4_ok && deg == 3) {
+    if (sh_rest != nullptr) {           // split layout: 3 floats of features_dc, then the row of features_rest
+        c[0] = __ldg(sh); c[1] = __ldg(sh + 1); c[2] = __ldg(sh + 2);
+#pragma unroll
+        for (int i = 3; i < 48; ++i) c[i] = (i < 3 * ncoef) ? __ldg(sh_rest + i - 3) : 0.f;
+    } else if (vec4_ok && deg == 3) {
         const float4* s4 = reinterpret_cast<const float4*>(sh);
 #pragma unroll
         for (int i = 0; i < 12; ++i) {
@@ -252,9 +259,10 @@ __global__ void __launch_bounds__(kPreBlock, 4) preprocess_fwd_kernel(const PreF
 #pragma unroll
                 for (int i = 0; i < 6; ++i) c3[i] = __ldg(p.cov3D_precomp + 6 * (size_t)idx + i);
             } else {
-                const float sx = __ldg(p.scales + 3 * (size_t)idx), sy = __ldg(p.scales + 3 * (size_t)idx + 1),
-                            sz = __ldg(p.scales + 3 * (size_t)idx + 2);
-                const float4 q = __ldg(reinterpret_cast<const float4*>(p.rotations) + idx);
+                float sx = __ldg(p.scales + 3 * (size_t)idx), sy = __ldg(p.scales + 3 * (size_t)idx + 1),
+                      sz = __ldg(p.scales + 3 * (size_t)idx + 2);
+                float4 q = __ldg(reinterpret_cast<const float4*>(p.rotations) + idx);
+                if (p.raw) { sx = act_exp(sx); sy = act_exp(sy); sz = act_exp(sz); q = act_normalize(q); }
                 cov3d_from_scale_rot(sx, sy, sz, p.scale_modifier, q, c3);
                 wrote_cov = true;
 #pragma unroll
@@ -288,8 +296,12 @@ __global__ void __launch_bounds__(kPreBlock, 4) preprocess_fwd_kernel(const PreF
         if (alive && p.colors_precomp == nullptr) {
             const size_t shoff = (size_t)idx * p.M * 3;
             const bool vec_ok = ((p.M * 3) % 4 == 0) && ((reinterpret_cast<size_t>(p.shs) & 15) == 0);
-            sh_to_rgb(p.D, p.shs + shoff, vec_ok, __fadd_rn(px, -sCam[0]), __fadd_rn(py, -sCam[1]),
-                      __fadd_rn(pz, -sCam[2]), rgb, cl);
+            if (p.shs_rest != nullptr)
+                sh_to_rgb(p.D, p.shs + 3 * (size_t)idx, false, __fadd_rn(px, -sCam[0]), __fadd_rn(py, -sCam[1]), __fadd_rn(pz, -sCam[2]), rgb, cl,
+                          p.shs_rest + (size_t)idx * (p.M - 1) * 3);
+            else
+                sh_to_rgb(p.D, p.shs + shoff, vec_ok, __fadd_rn(px, -sCam[0]), __fadd_rn(py, -sCam[1]),
+                          __fadd_rn(pz, -sCam[2]), rgb, cl);
         }
         if (p.colors_precomp == nullptr) {
             p.rgb[3 * (size_t)idx] = rgb[0]; p.rgb[3 * (size_t)idx + 1] = rgb[1]; p.rgb[3 * (size_t)idx + 2] = rgb[2];
@@ -298,7 +310,9 @@ __global__ void __launch_bounds__(kPreBlock, 4) preprocess_fwd_kernel(const PreF
         p.depths[idx] = alive ? depth : 0.f;
         key = __float_as_uint(depth);
         p.means2D[idx] = alive ? pix : make_float2(0.f, 0.f);
-        p.conic_opacity[idx] = alive ? make_float4(conic.x, conic.y, conic.z, __ldg(p.opacities + idx)) : make_float4(0.f, 0.f, 0.f, 0.f);
+        float opac = 0.f;
+        if (alive) { opac = __ldg(p.opacities + idx); if (p.raw) opac = act_sigmoid(opac); }
+        p.conic_opacity[idx] = alive ? make_float4(conic.x, conic.y, conic.z, opac) : make_float4(0.f, 0.f, 0.f, 0.f);
         if (!wrote_cov && p.cov3D_precomp == nullptr) {
 #pragma unroll
             for (int i = 0; i < 6; ++i) p.cov3D[6 * (size_t)idx + i] = 0.f;
@@ -352,6 +366,7 @@ void launch_preprocess(const PreprocessArgs& a, const GeomPtrs& g, cudaStream_t 
     p.P = a.P; p.D = a.D; p.M = a.M;
     p.means3D = a.means3D; p.scales = a.scales; p.rotations = a.rotations; p.opacities = a.opacities;
     p.shs = a.shs; p.cov3D_precomp = a.cov3D_precomp; p.colors_precomp = a.colors_precomp;
+    p.shs_rest = a.shs_rest; p.raw = a.raw ? 1 : 0;
     p.scale_modifier = a.scale_modifier;
     p.viewmatrix = a.viewmatrix; p.projmatrix = a.projmatrix; p.cam_pos = a.cam_pos;
     p.W = a.W; p.H = a.H; p.tan_fovx = a.tan_fovx; p.tan_fovy = a.tan_fovy; p.focal_x = a.focal_x; p.focal_y = a.focal_y;
@@ -457,6 +472,7 @@ struct PreBwdParams {
     int block0;                    // first 256-Gaussian block of this launch (range launches, gsr_backward_preprocess_range)
     const float* __restrict__ means3D; const float* __restrict__ scales; const float* __restrict__ rotations;
     const float* __restrict__ shs; const float* __restrict__ cov3D;
+    const float* __restrict__ shs_rest; int raw;      // raw-parameter entry (see PreFwdParams)
     int cov_from_scales, colors_from_sh;
     float scale_modifier;
     const float* __restrict__ viewmatrix; const float* __restrict__ projmatrix; const float* __restrict__ cam_pos;
@@ -597,7 +613,15 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreBwdParams 
                 const int k = i + sel;
                 if (sel < rpi && k < nv) {
                     const int src_lane = __fns(m, 0, k + 1);
-                    const float4 v = __ldg(reinterpret_cast<const float4*>(p.shs + (size_t)(warp_idx0 + src_lane) * L) + part);
+                    float4 v;
+                    if (p.shs_rest != nullptr) {       // split layout: coefficient c of the row = dc[c] (c < 3) or rest[c - 3]
+                        const float* dc = p.shs + 3 * (size_t)(warp_idx0 + src_lane);
+                        const float* rs = p.shs_rest + (size_t)(warp_idx0 + src_lane) * (L - 3);
+                        float t[4];
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) { const int c = 4 * part + e; t[e] = c < 3 ? __ldg(dc + c) : __ldg(rs + c - 3); }
+                        v = make_float4(t[0], t[1], t[2], t[3]);
+                    } else v = __ldg(reinterpret_cast<const float4*>(p.shs + (size_t)(warp_idx0 + src_lane) * L) + part);
                     float* dst = wbase + src_lane * kShStride + 4 * part;
                     dst[0] = v.x; dst[1] = v.y; dst[2] = v.z; dst[3] = v.w;
                 }
@@ -685,9 +709,11 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreBwdParams 
 
     // ---------------- cov3D -> scale, rotation (backward.cu:278-341)
     if (visible && p.cov_from_scales) {
-        const float4 q = reinterpret_cast<const float4*>(p.rotations)[idx];
+        float4 q = reinterpret_cast<const float4*>(p.rotations)[idx];
+        float sc0 = p.scales[i3], sc1 = p.scales[i3 + 1], sc2 = p.scales[i3 + 2];
+        if (p.raw) { q = act_normalize(q); sc0 = act_exp(sc0); sc1 = act_exp(sc1); sc2 = act_exp(sc2); }
         const float r = q.x, x = q.y, y = q.z, z = q.w;
-        const float s0 = p.scale_modifier * p.scales[i3], s1 = p.scale_modifier * p.scales[i3 + 1], s2 = p.scale_modifier * p.scales[i3 + 2];
+        const float s0 = p.scale_modifier * sc0, s1 = p.scale_modifier * sc1, s2 = p.scale_modifier * sc2;
         // R[c][r] as in the forward (glm column-major)
         const float R00 = 1.f - 2.f * (y * y + z * z), R01 = 2.f * (x * y - r * z), R02 = 2.f * (x * z + r * y);
         const float R10 = 2.f * (x * y + r * z), R11 = 1.f - 2.f * (x * x + z * z), R12 = 2.f * (y * z - r * x);
@@ -747,6 +773,7 @@ void launch_preprocess_backward(const PreBwdArgs& a, cudaStream_t s) {
     PreBwdParams p;
     p.P = end; p.block0 = first / 256; p.D = a.D; p.M = a.M;
     p.means3D = a.means3D; p.scales = a.scales; p.rotations = a.rotations; p.shs = a.shs; p.cov3D = a.cov3D;
+    p.shs_rest = a.shs_rest; p.raw = a.raw ? 1 : 0;
     p.cov_from_scales = a.cov_from_scales ? 1 : 0; p.colors_from_sh = a.colors_from_sh ? 1 : 0;
     p.scale_modifier = a.scale_modifier;
     p.viewmatrix = a.viewmatrix; p.projmatrix = a.projmatrix; p.cam_pos = a.cam_pos;
@@ -760,7 +787,7 @@ void launch_preprocess_backward(const PreBwdArgs& a, cudaStream_t s) {
     p.push_rows_per_rank = a.out.push_rows_per_rank;
     // staged SH path: needs M % 4 == 0 (128-bit rows), M <= 16 (row fits the staged stride) and 16 B-aligned tensors
     const bool staged = (p.dL_dsh != nullptr || p.colors_from_sh) && p.M > 0 && p.M <= 16 && (p.M % 4) == 0 && ((size_t)p.dL_dsh & 15) == 0 &&
-                        (!p.colors_from_sh || ((size_t)p.shs & 15) == 0);
+                        (!p.colors_from_sh || p.shs_rest != nullptr || ((size_t)p.shs & 15) == 0);
     if (staged) {
         const int smem = 256 * kShStride * (int)sizeof(float);
         static bool attr_done = false;

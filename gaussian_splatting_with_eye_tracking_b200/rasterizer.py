@@ -98,6 +98,63 @@ def rasterize_gaussians_baseline(means3D, means2D, sh, colors_precomp, opacities
                                             cov3Ds_precomp, raster_settings)
 
 
+# ----------------------------------------------------------------------------------------------------------------
+# raw-parameter entry (extension): the model's RAW tensors go straight to the kernels
+# ----------------------------------------------------------------------------------------------------------------
+class RasterizeGaussiansRaw(torch.autograd.Function):
+    """Rasterize from the raw parameters of scene/gaussian_model.py -- ``_opacity`` (logits), ``_scaling`` (log-scales),
+    ``_rotation`` (un-normalised quaternions), ``_features_dc`` [P,1,3] and ``_features_rest`` [P,M-1,3] -- without the activated
+    copies the reference's caller materialises every frame (gaussian_model.py:95-115: sigmoid, exp, normalize, torch.cat =
+    236 B/Gaussian read and written again before the rasterizer starts).  The kernels activate on load; the backward returns
+    the gradients of the activated quantities and they are chained through the activations here (11 floats per Gaussian)."""
+
+    @staticmethod
+    def forward(ctx, means3D, means2D, features_dc, features_rest, raw_opacity, raw_scaling, raw_rotation, raster_settings):
+        rs = raster_settings
+        e = means3D.new_empty(0)
+        args = (rs.bg, means3D, e, raw_opacity, raw_scaling, raw_rotation, rs.scale_modifier, e, rs.viewmatrix, rs.projmatrix, rs.tanfovx,
+                rs.tanfovy, rs.image_height, rs.image_width, features_dc, rs.sh_degree, rs.campos, rs.prefiltered, rs.debug)
+        num_rendered, color, radii, geomBuffer, binningBuffer, imgBuffer = _host.rasterize_gaussians(*args, sh_rest=features_rest)
+        ctx.raster_settings, ctx.num_rendered = rs, num_rendered
+        ctx.save_for_backward(means3D, features_dc, features_rest, raw_opacity, raw_scaling, raw_rotation, radii, geomBuffer, binningBuffer, imgBuffer)
+        return color, radii
+
+    @staticmethod
+    def backward(ctx, grad_out_color, _grad_radii=None):
+        rs = ctx.raster_settings
+        means3D, f_dc, f_rest, raw_op, raw_sc, raw_rot, radii, geomBuffer, binningBuffer, imgBuffer = ctx.saved_tensors
+        e = means3D.new_empty(0)
+        (g_means2D, _g_col, g_op, g_means3D, _g_cov, g_sh, g_sc, g_rot) = _host.rasterize_gaussians_backward(
+            rs.bg, means3D, radii, e, raw_sc, raw_rot, rs.scale_modifier, e, rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy,
+            grad_out_color, f_dc, rs.sh_degree, rs.campos, geomBuffer, ctx.num_rendered, binningBuffer, imgBuffer, rs.debug, sh_rest=f_rest)
+        sig = torch.sigmoid(raw_op)
+        g_raw_op = g_op.view_as(raw_op) * sig * (1.0 - sig)
+        g_raw_sc = g_sc * torch.exp(raw_sc)
+        n = raw_rot.norm(dim=1, keepdim=True).clamp_min(1e-12)
+        qh = raw_rot / n
+        g_raw_rot = (g_rot - qh * (qh * g_rot).sum(dim=1, keepdim=True)) / n
+        return g_means3D, g_means2D, g_sh[:, :1], g_sh[:, 1:], g_raw_op, g_raw_sc, g_raw_rot, None
+
+
+def rasterize_gaussians_raw(means3D, means2D, features_dc, features_rest, raw_opacity, raw_scaling, raw_rotation, raster_settings):
+    return RasterizeGaussiansRaw.apply(means3D, means2D, features_dc, features_rest, raw_opacity, raw_scaling, raw_rotation, raster_settings)
+
+
+def render_raw(viewpoint_camera, pc, bg_color, scaling_modifier=1.0, debug=False):
+    """``gaussian_renderer.render`` (gaussian_renderer/__init__.py:18-113) on the raw-parameter entry: same result dictionary, no
+    activated parameter copies.  ``pc`` is a GaussianModel (``_xyz, _features_dc, _features_rest, _opacity, _scaling, _rotation``)."""
+    import math
+    screenspace_points = torch.zeros_like(pc._xyz, requires_grad=True)
+    rs = GaussianRasterizationSettings(
+        image_height=int(viewpoint_camera.image_height), image_width=int(viewpoint_camera.image_width),
+        tanfovx=math.tan(viewpoint_camera.FoVx * 0.5), tanfovy=math.tan(viewpoint_camera.FoVy * 0.5), bg=bg_color,
+        scale_modifier=scaling_modifier, viewmatrix=viewpoint_camera.world_view_transform, projmatrix=viewpoint_camera.full_proj_transform,
+        sh_degree=pc.active_sh_degree, campos=viewpoint_camera.camera_center, prefiltered=False, debug=debug)
+    image, radii = rasterize_gaussians_raw(pc._xyz, screenspace_points, pc._features_dc, pc._features_rest, pc._opacity, pc._scaling,
+                                           pc._rotation, rs)
+    return {"render": image, "viewspace_points": screenspace_points, "visibility_filter": radii > 0, "radii": radii}
+
+
 def _check_optional_inputs(shs, colors_precomp, scales, rotations, cov3D_precomp):
     # same two checks, same messages as the reference (diff_gaussian_rasterization/__init__.py:191-195)
     if (shs is None) == (colors_precomp is None):

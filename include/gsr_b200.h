@@ -78,6 +78,18 @@ typedef struct gsr_scene {
     const float* rotations;      /* [P,4] (r,x,y,z), not normalised by the kernel, or NULL */
     const float* cov3D_precomp;  /* [P,6]  or NULL                                         */
     float scale_modifier;
+    /* ---- raw-parameter entry (optional, raw_params == 0: off).  The reference's caller materialises activated
+     * copies of every parameter per frame (scene/gaussian_model.py:95-115: sigmoid, exp, normalize and torch.cat of the two SH
+     * tensors = 236 B/Gaussian read + 236 B written before the rasterizer reads them again).  With raw_params = 1 the kernels
+     * apply the activations on load:
+     *     opacities  = raw logits            -> 1 / (1 + exp(-x))
+     *     scales     = log-scales            -> exp(x)
+     *     rotations  = raw quaternions       -> x / max(|x|, 1e-12)
+     *     shs        = features_dc   [P,1,3],   shs_rest = features_rest [P,M-1,3]   (sh_coeffs = M as before)
+     * Gradients are still returned w.r.t. the ACTIVATED quantities and the concatenated [P,M,3] SH layout; the host chains them
+     * through the activations (a few floats per Gaussian). */
+    int raw_params;
+    const float* shs_rest;
 } gsr_scene;
 
 typedef struct gsr_camera {
