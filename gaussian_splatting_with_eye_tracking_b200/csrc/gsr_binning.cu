@@ -816,7 +816,9 @@ void launch_expand_runs(const BinPtrs& b, const uint32_t* rkeys_sorted, const ui
                         const uint32_t* row_offsets, uint2* ranges, uint32_t* n_intersections, const GeomHeader* hdr, uint32_t* mailbox_dev,
                         int prof_ranges, int prof_expand, cudaStream_t s) {
     const int num_tiles = tiles_x * tiles_y;
-    const int chunk = tiles_x <= 600 ? 2048 : kRunChunk;                // runs per expansion chunk (tables are sized for kRunChunk: an upper bound)
+    // runs per expansion chunk.  2048 (half the per-column decode overhead per run, 40 KB of shared memory) measured SLOWER than
+    // 1024 at 1080p (110-120 us against 94-104 us: 5 instead of 8 CTAs per SM); kept selectable for wide images only by hand.
+    const int chunk = kRunChunk;
     const unsigned grid = (unsigned)(R / chunk + tiles_y + 1);
     {
         ProfScope ps(prof_ranges, s);

@@ -74,8 +74,28 @@ def test_pushed_rows_plus_owner_sum_equal_the_rank_ordered_sum(world, cuda_devic
     for b in bufs:
         flat = b[:numel].cpu()
         got = [flat[0:3 * P].view(P, 3), flat[3 * P4:3 * P4 + P].view(P, 1), flat[4 * P4:4 * P4 + 3 * P].view(P, 3), flat[7 * P4:7 * P4 + 4 * P].view(P, 4)]
+        # (the blend-stage backward accumulates with float atomics, so two runs of the same view differ in the last bits: the staged
+        # rows come from a second run of each view -- compare at the gradient bar, bit-exactness of the SUM itself is covered below)
         for g, w_ in zip(got, want):
-            assert torch.equal(g, w_), "owner sum differs from the rank-ordered float32 sum"
+            viol, mx = common.grad_close(g, w_, common.GRAD_RTOL, common.GRAD_FLOOR_REF)
+            assert viol <= 0, f"owner sum differs from the rank-ordered sum (max abs diff {mx})"
+    # every rank holds the SAME bits
+    for b in bufs[1:]:
+        assert torch.equal(b[:numel], bufs[0][:numel])
+    # and the sum is exactly the rank-ordered float32 sum of what was staged
+    P4_ = P4
+    stag = [b[numel:numel + staging].view(world, rows, 12).cpu() for b in bufs]        # stag[owner][src rank][local row]
+    mk = masks[:, :W32].cpu().numpy().view(np.uint32)
+    vis = np.stack([np.unpackbits(mk[r].view(np.uint8).reshape(-1, 4)[:, ::-1], axis=1).reshape(-1, 32)[:, ::-1].reshape(-1)[:P] for r in range(world)])
+    flat0 = bufs[0][:numel].cpu()
+    m3 = flat0[0:3 * P].view(P, 3)
+    for idx in range(0, P, max(1, P // 257)):
+        owner, local = idx // rows, idx % rows
+        acc = torch.zeros(3)
+        for r in range(world):
+            if vis[r, idx]:
+                acc = acc + stag[owner][r, local, 0:3]
+        assert torch.equal(m3[idx], acc), idx
 
 
 def test_fused_exchange_through_the_host_classes_single_rank(cuda_device):
@@ -99,9 +119,11 @@ def test_fused_exchange_through_the_host_classes_single_rank(cuda_device):
         exch.start_reduce([g[3], g[2], g[6], g[7]])
         dsh = exch.finish()
         torch.cuda.synchronize()
-        for k in (3, 2, 6, 7):
-            assert torch.equal(g[k], ref[k]), f"dense gradient {k}"
-        assert torch.equal(dsh, ref[5])
+        for k in (3, 2, 6, 7):          # two backward runs differ in the last bits (float atomics in the blend stage)
+            viol, mx = common.grad_close(g[k], ref[k], common.GRAD_RTOL, common.GRAD_FLOOR_REF)
+            assert viol <= 0, f"dense gradient {k}: max abs diff {mx}"
+        viol, mx = common.grad_close(dsh, ref[5], common.GRAD_RTOL, common.GRAD_FLOOR_REF)
+        assert viol <= 0, f"SH gradient: max abs diff {mx}"
 
 
 def test_peer_watchdog_poisons_and_reports(cuda_device):
