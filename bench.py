@@ -844,6 +844,17 @@ def measure(impl, args, d, cams, rank, world, timer, full):
             ms = timer.run(lambda i: amr_frame(impl, cam_of(i), "single", gz), Ka, 3)
             amr["gaze_foveated_fps"] = world * Ka / (ms / 1e3)
             amr["gaze"] = {"cx": gz[0], "cy": gz[1], "radii": list(gz[2])}
+            # per-stage device times of the single-pass AMR frame (library CUDA-event hooks), to show where a foveated frame spends
+            # its time: the per-Gaussian stages (preprocess, depth order) do not shrink with the fovea
+            impl.capi.profile_read()
+            impl.capi.profile_enable(True)
+            for i in range(Ka):
+                amr_frame(impl, cam_of(i), "single", gz)
+            impl.capi.profile_enable(False)
+            prof = impl.capi.profile_read()
+            amr["gaze_foveated_stages_ms"] = {k: round(v[0] / max(1, v[1]), 5) for k, v in prof.items()}
+            amr["full_render_fps"] = out["value"] / world * world
+            amr["speedup_vs_full"] = {k[:-4]: amr[k] / out["value"] for k in ("single_pass_fps", "five_step_fps", "gaze_foveated_fps")}
     except RuntimeError as ex:
         amr["error"] = str(ex)[:200]
     out["amr"] = amr

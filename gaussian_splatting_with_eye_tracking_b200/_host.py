@@ -357,11 +357,26 @@ def rasterize_gaussians_amr(background, means3D, colors, opacity, scales, rotati
                             imageBuffer_precomp, interpolate_image, debug, gaze=None, band=None):
     """``gaze`` = (cx, cy, (r1, r2, r3, r4)) enables the gaze-driven level cap (extension; None = reference).
     ``band`` = (row0, row1) restricts binning and blending to 32-px tile rows [row0, row1) (extension)."""
-    sc, cam, keep, P, _ = _scene_camera(background, means3D, colors, opacity, scales, rotations, scale_modifier,
-                                        cov3D_precomp, viewmatrix, projmatrix, tan_fovx, tan_fovy, image_height,
-                                        image_width, sh, degree, campos, prefiltered, band)
-    dev = means3D.device if means3D.is_cuda else torch.device("cuda")
     step = int(foveaStep)
+    if step >= 1 and means3D.is_cuda and means3D.dim() == 2:
+        # progressive rounds 1..4 read nothing of the scene but its size (everything was built by step 0): marshal only what the
+        # library validates -- five calls per frame make the host side of this protocol the bottleneck
+        P = int(means3D.size(0))
+        keep = SimpleNamespace(means3D=means3D, bg=_dev_tensor(background, "bg"), view=_dev_tensor(viewmatrix, "viewmatrix"),
+                               proj=_dev_tensor(projmatrix, "projmatrix"), campos=_dev_tensor(campos, "campos"), sh=sh if sh.numel() else None,
+                               colors=colors if colors.numel() else None)
+        M = int(sh.size(1)) if (sh is not None and sh.dim() >= 2 and sh.size(0) != 0) else 0
+        dummy = _p(means3D)
+        sc = GsrScene(P=P, sh_degree=int(degree), sh_coeffs=M, means3D=dummy, shs=_p(keep.sh), colors_precomp=_p(keep.colors), opacities=dummy,
+                      scales=dummy, rotations=dummy, cov3D_precomp=None, scale_modifier=float(scale_modifier), raw_params=0, shs_rest=None)
+        cam = GsrCamera(width=int(image_width), height=int(image_height), tan_fovx=float(tan_fovx), tan_fovy=float(tan_fovy),
+                        background=_p(keep.bg), viewmatrix=_p(keep.view), projmatrix=_p(keep.proj), cam_pos=_p(keep.campos),
+                        prefiltered=1 if prefiltered else 0, band_row0=int(band[0]) if band else 0, band_row1=int(band[1]) if band else 0)
+    else:
+        sc, cam, keep, P, _ = _scene_camera(background, means3D, colors, opacity, scales, rotations, scale_modifier,
+                                            cov3D_precomp, viewmatrix, projmatrix, tan_fovx, tan_fovy, image_height,
+                                            image_width, sh, degree, campos, prefiltered, band)
+    dev = means3D.device if means3D.is_cuda else torch.device("cuda")
     gz = _gaze_struct(gaze)
     with torch.cuda.device(dev):
         out_color = torch.empty((3, int(image_height), int(image_width)), dtype=torch.float32, device=dev)

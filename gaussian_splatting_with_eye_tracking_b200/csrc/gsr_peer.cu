@@ -179,11 +179,12 @@ __global__ void __launch_bounds__(kPeerThreads) peer_owner_sum_kernel(const Owne
     const bool poisoned = peer_poisoned(p.bases, p.flag_offset, p.world, p.rank);
     const float nanv = __int_as_float(0x7fc00000);
     const float4* staging = reinterpret_cast<const float4*>(p.bases[p.rank] + p.staging_offset);
-    const int first = p.rank * p.rows_per_rank;
-    const int count = max(0, min(p.rows_per_rank, p.P4 - first));       // multiple of 4
     const size_t P4 = (size_t)p.P4;
-    for (int g4 = (blockIdx.x * kPeerThreads + threadIdx.x) * 4; g4 < count; g4 += gridDim.x * kPeerThreads * 4) {
-        const int idx = first + g4;                                       // 4 Gaussians idx .. idx + 3, same mask word
+    // this rank owns the 256-Gaussian blocks rank, rank + world, rank + 2 world, ... (block-cyclic, see preprocess_bwd_kernel);
+    // local row g4 of the staging slots <-> Gaussian ((g4 >> 8) * world + rank) * 256 + (g4 & 255)
+    for (int g4 = (blockIdx.x * kPeerThreads + threadIdx.x) * 4; g4 < p.rows_per_rank; g4 += gridDim.x * kPeerThreads * 4) {
+        const int idx = (((g4 >> 8) * p.world + p.rank) << 8) | (g4 & 255);   // 4 Gaussians idx .. idx + 3, same mask word
+        if (idx >= p.P4) continue;
         float row[4][11];
 #pragma unroll
         for (int q = 0; q < 4; ++q)

@@ -482,7 +482,7 @@ struct PreBwdParams {
     float *dL_dmeans2D, *dL_dcolors, *dL_dopacity, *dL_dmeans3D, *dL_dcov3D, *dL_dsh, *dL_dscales, *dL_drot, *dL_dconic;
     float* dL_drgb_clamped;        // optional [P,3]; with dL_dsh == nullptr the SH rows are not written (gsr_grads)
     // fused view-parallel exchange (gsr_grads.push_*): rows of the 11 dense floats go to the owner rank's staging area
-    char* const* push_bases; size_t push_offset; int push_rank, push_rows_per_rank;
+    char* const* push_bases; size_t push_offset; int push_rank, push_world, push_rows_per_rank;
 };
 
 // SH rows are staged through shared memory (STAGED): a thread's 3M coefficients / gradients are 192 B apart from its
@@ -750,13 +750,15 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreBwdParams 
         // one 48-byte row per VISIBLE Gaussian into the owner's staging area (peer memory): consecutive Gaussians -> consecutive
         // rows, so a warp writes whole 128-byte lines across NVLink.  The owner knows from the gathered visibility masks which
         // ranks wrote a row, so invisible Gaussians send nothing.
+        // Ownership is block-cyclic (256-Gaussian blocks dealt round-robin to the ranks): at any moment the CTAs in flight push to
+        // ALL owners at once; contiguous slices would make every rank push to the same owner at the same time (7-to-1 incast on
+        // one GPU's NVLink ingress).  No fence here: the kernel's completion orders these stores before the barrier that follows.
         if (visible) {
-            const int owner = idx / p.push_rows_per_rank, local = idx - owner * p.push_rows_per_rank;
+            const int blk = idx >> 8, owner = blk % p.push_world, local = ((blk / p.push_world) << 8) | (idx & 255);
             float4* dst = reinterpret_cast<float4*>(p.push_bases[owner] + p.push_offset) + ((size_t)p.push_rank * p.push_rows_per_rank + local) * 3;
             dst[0] = make_float4(dmx, dmy, dmz, sB.y);
             dst[1] = make_float4(dscale[0], dscale[1], dscale[2], drot.x);
             dst[2] = make_float4(drot.y, drot.z, drot.w, 0.f);
-            __threadfence_system();
         }
         return;
     }
@@ -784,7 +786,7 @@ void launch_preprocess_backward(const PreBwdArgs& a, cudaStream_t s) {
     p.dL_dscales = a.out.dL_dscales; p.dL_drot = a.out.dL_drotations; p.dL_dconic = a.out.dL_dconic;
     p.dL_drgb_clamped = a.out.dL_dcolors_clamped;
     p.push_bases = (char* const*)a.out.push_bases; p.push_offset = a.out.push_offset; p.push_rank = a.out.push_rank;
-    p.push_rows_per_rank = a.out.push_rows_per_rank;
+    p.push_rows_per_rank = a.out.push_rows_per_rank; p.push_world = a.out.push_world > 0 ? a.out.push_world : 1;
     // staged SH path: needs M % 4 == 0 (128-bit rows), M <= 16 (row fits the staged stride) and 16 B-aligned tensors
     const bool staged = (p.dL_dsh != nullptr || p.colors_from_sh) && p.M > 0 && p.M <= 16 && (p.M % 4) == 0 && ((size_t)p.dL_dsh & 15) == 0 &&
                         (!p.colors_from_sh || p.shs_rest != nullptr || ((size_t)p.shs & 15) == 0);

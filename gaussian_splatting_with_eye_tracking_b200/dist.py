@@ -197,7 +197,8 @@ class PeerAllReduce:
         self.numel = (int(numel) + 3) // 4 * 4
         self.flag_bytes = int(lib.gsr_peer_flag_bytes(self.world))
         self.staging_P = int(staging_gaussians)
-        self.rows_per_rank = ((self.staging_P + self.world - 1) // self.world + 255) // 256 * 256 if self.staging_P else 0
+        nblk = (self.staging_P + 255) // 256
+        self.rows_per_rank = (nblk + self.world - 1) // self.world * 256 if self.staging_P else 0      # 256-blocks dealt round-robin
         self.staging_floats = self.world * self.rows_per_rank * 12
         total = self.numel + self.staging_floats + self.flag_bytes // 4
         dev = torch.device(device)

@@ -133,8 +133,9 @@ typedef struct gsr_grads {
      * backward then does NOT write dL_dmeans3D / dL_dopacity / dL_dscales / dL_drotations locally: for every Gaussian visible
      * in this view it stores the 11 floats as one 48-byte row straight into the staging area of the rank that OWNS the
      * Gaussian (peer memory over NVLink, under the kernel's own HBM-bound run time):
-     *     owner = idx / push_rows_per_rank,   row address = push_bases[owner] + push_offset
-     *                                                       + ((push_rank * push_rows_per_rank) + idx % push_rows_per_rank) * 48
+     *     block = idx / 256,  owner = block % push_world  (256-Gaussian blocks dealt round-robin, so that all owners receive at once),
+     *     local = (block / push_world) * 256 + idx % 256,
+     *     row address = push_bases[owner] + push_offset + (push_rank * push_rows_per_rank + local) * 48
      * gsr_peer_owner_sum then sums the staged rows of every owner's Gaussians in rank order and delivers the totals to all
      * ranks.  push_rows_per_rank must be a multiple of 256. */
     void* const* push_bases;   /* DEVICE array of `push_world` peer-mapped base pointers (as for gsr_peer_allreduce_sum) */
@@ -342,8 +343,8 @@ GSR_API int gsr_peer_barrier(void* const* peer_bases, size_t flag_offset, int wo
  * all ranks; the switch's add order is not the rank order of the unicast variant. */
 GSR_API int gsr_peer_allreduce_sum_mc(void* const* peer_bases, void* multicast_base, size_t data_offset, long long n_floats,
                                       size_t flag_offset, int world, int rank, unsigned epoch, void* stream);
-/* Second half of the fused exchange (see gsr_grads.push_*): barrier(epoch), then rank r sums, for every Gaussian of its slice
- * [r * rows_per_rank, (r+1) * rows_per_rank), the rows staged by the ranks in whose view the Gaussian was visible (visibility =
+/* Second half of the fused exchange (see gsr_grads.push_*): barrier(epoch), then rank r sums, for every Gaussian of the blocks it
+ * owns (block % world == r), the rows staged by the ranks in whose view the Gaussian was visible (visibility =
  * bit idx of rank k's mask words, view_masks + k * mask_stride_words: the words gsr_pack_visible_rows produced and the ranks
  * gathered; rank order, so every run gives the same bits), and writes the totals into EVERY rank's dense gradient block at
  * final_offset -- [means3D 3 x P4 | opacity P4 | scales 3 x P4 | rotations 4 x P4] floats, P4 = P rounded up to 4, the layout

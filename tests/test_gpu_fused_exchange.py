@@ -39,7 +39,7 @@ def test_pushed_rows_plus_owner_sum_equal_the_rank_ordered_sum(world, cuda_devic
     sc, _ = common.make_case("small")
     P = sc["means3D"].shape[0]
     P4 = (P + 3) // 4 * 4
-    rows = ((P + world - 1) // world + 255) // 256 * 256
+    rows = ((P + 255) // 256 + world - 1) // world * 256           # 256-Gaussian blocks dealt round-robin to the ranks
     numel = 11 * P4
     staging = world * rows * 12
     fb = int(lib.gsr_peer_flag_bytes(world))
@@ -90,7 +90,8 @@ def test_pushed_rows_plus_owner_sum_equal_the_rank_ordered_sum(world, cuda_devic
     flat0 = bufs[0][:numel].cpu()
     m3 = flat0[0:3 * P].view(P, 3)
     for idx in range(0, P, max(1, P // 257)):
-        owner, local = idx // rows, idx % rows
+        blk = idx // 256
+        owner, local = blk % world, (blk // world) * 256 + idx % 256
         acc = torch.zeros(3)
         for r in range(world):
             if vis[r, idx]:
