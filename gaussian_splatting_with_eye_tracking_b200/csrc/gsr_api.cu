@@ -483,6 +483,17 @@ int gsr_mark_visible(int P, const float* means3D, const float* viewmatrix, const
     return check_last("mark_visible", false, (cudaStream_t)stream);
 }
 
+// The AMR kernels write only the lattice pixels they render: everything else of the frame (or of this call's tile band) must read 0
+// (reference: out_color = torch::full(0), A/rasterize_points.cu:116).  With a tile band only the band's pixel rows are cleared --
+// rows outside it are not this call's to write (a rank of a banded 4K frame would otherwise clear 100 MB to use 12).
+static int zero_out_color(float* out_color, int W, int H, int band_row0, int band_row1, cudaStream_t s) {
+    if (band_row1 <= 0) return check_cuda(cudaMemsetAsync(out_color, 0, sizeof(float) * 3 * (size_t)W * H, s), "memset out_color");
+    const int y0 = min(H, band_row0 * 32), y1 = min(H, band_row1 * 32);
+    if (y1 <= y0) return GSR_OK;
+    return check_cuda(cudaMemset2DAsync(out_color + (size_t)y0 * W, sizeof(float) * (size_t)W * H, 0, sizeof(float) * (size_t)W * (y1 - y0), 3, s),
+                      "memset out_color (band)");
+}
+
 int gsr_amr_forward(const gsr_scene* sc, const gsr_camera* cam, int fovea_step, const float* out_color_precomp,
                     void* geom_precomp, void* binning_precomp, void* image_precomp, int interpolate_image,
                     const gsr_gaze* gaze, gsr_alloc_fn alloc, void* user, float* out_color, int* radii,
@@ -495,7 +506,7 @@ int gsr_amr_forward(const gsr_scene* sc, const gsr_camera* cam, int fovea_step, 
     const int P = sc->P, W = cam->width, H = cam->height;
     // the AMR kernels write only the lattice pixels they render: everything else must read 0
     // (reference: out_color = torch::full(0), A/rasterize_points.cu:116)
-    if ((rc = check_cuda(cudaMemsetAsync(out_color, 0, sizeof(float) * 3 * (size_t)W * H, s), "memset out_color"))) return rc;
+    if ((rc = zero_out_color(out_color, W, H, cam->band_row0, cam->band_row1, s))) return rc;
     if (P == 0) return GSR_OK;
 
     void *geom = geom_precomp, *bin = binning_precomp, *img = image_precomp;
@@ -549,7 +560,7 @@ int gsr_amr_render_prebuilt(const gsr_scene* sc, const gsr_camera* cam, const vo
     if (rc) return rc;
     if (!out_color) { set_error("out_color is required"); return GSR_ERR_INVALID; }
     const int P = sc->P, W = cam->width, H = cam->height;
-    if ((rc = check_cuda(cudaMemsetAsync(out_color, 0, sizeof(float) * 3 * (size_t)W * H, s), "memset out_color"))) return rc;
+    if ((rc = zero_out_color(out_color, W, H, cam->band_row0, cam->band_row1, s))) return rc;
     if (P == 0) return GSR_OK;
     if (!geom_buffer || !binning_buffer || !image_buffer) { set_error("prebuilt work buffers are required"); return GSR_ERR_WORKSPACE; }
     GeomPtrs g = geom_ptrs(geom_buffer, P);

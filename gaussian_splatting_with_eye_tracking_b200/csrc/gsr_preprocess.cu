@@ -705,7 +705,8 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreBwdParams 
             }
         }
     }
-    if (!valid) return;
+    const bool push_staged = STAGED && p.push_bases != nullptr;     // whole warps stay for the cooperative row push below
+    if (!valid && !push_staged) return;
 
     // ---------------- cov3D -> scale, rotation (backward.cu:278-341)
     if (visible && p.cov_from_scales) {
@@ -744,17 +745,34 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreBwdParams 
         // note: like the reference, dL_dscale is the gradient w.r.t. (modifier * scale); no extra factor is applied
     }
 
+    if (valid) {
 #pragma unroll
-    for (int i = 0; i < 6; ++i) p.dL_dcov3D[6 * (size_t)idx + i] = dcov[i];
+        for (int i = 0; i < 6; ++i) p.dL_dcov3D[6 * (size_t)idx + i] = dcov[i];
+    }
     if (p.push_bases != nullptr) {
-        // one 48-byte row per VISIBLE Gaussian into the owner's staging area (peer memory): consecutive Gaussians -> consecutive
-        // rows, so a warp writes whole 128-byte lines across NVLink.  The owner knows from the gathered visibility masks which
-        // ranks wrote a row, so invisible Gaussians send nothing.
-        // Ownership is block-cyclic (256-Gaussian blocks dealt round-robin to the ranks): at any moment the CTAs in flight push to
-        // ALL owners at once; contiguous slices would make every rank push to the same owner at the same time (7-to-1 incast on
-        // one GPU's NVLink ingress).  No fence here: the kernel's completion orders these stores before the barrier that follows.
-        if (visible) {
-            const int blk = idx >> 8, owner = blk % p.push_world, local = ((blk / p.push_world) << 8) | (idx & 255);
+        // One 48-byte row per Gaussian into the owner's staging area (peer memory over NVLink).  Ownership is block-cyclic
+        // (256-Gaussian blocks dealt round-robin to the ranks): at any moment the CTAs in flight push to ALL owners at once;
+        // contiguous slices would make every rank push to the same owner at the same time (7-to-1 incast on one GPU's ingress).
+        // A warp's 32 rows are consecutive at the owner: they are transposed through shared memory and leave as three fully
+        // contiguous 512-byte stores (per-lane 16-byte pieces 48 bytes apart travel as 96 small NVLink packets per warp: measured
+        // slower than the all-reduce they replace).  Rows of invisible Gaussians go out as zeros -- whole lines, no read-modify-
+        // write at the owner; a warp without any visible Gaussian sends nothing (the owner skips it by the visibility masks).
+        // No fence here: the kernel's completion orders these stores before the barrier that follows.
+        const int blk = idx >> 8, owner = blk % p.push_world, local = ((blk / p.push_world) << 8) | (idx & 255);
+        if (push_staged) {
+            const uint32_t any_vis = __ballot_sync(0xffffffffu, visible);
+            if (any_vis) {
+                float4* wrow = reinterpret_cast<float4*>(s_sh + wid * 32 * kShStride);      // the warp's SH staging rows are dead by now
+                __syncwarp();
+                wrow[3 * lane] = visible ? make_float4(dmx, dmy, dmz, sB.y) : make_float4(0.f, 0.f, 0.f, 0.f);
+                wrow[3 * lane + 1] = visible ? make_float4(dscale[0], dscale[1], dscale[2], drot.x) : make_float4(0.f, 0.f, 0.f, 0.f);
+                wrow[3 * lane + 2] = visible ? make_float4(drot.y, drot.z, drot.w, 0.f) : make_float4(0.f, 0.f, 0.f, 0.f);
+                __syncwarp();
+                float4* dst = reinterpret_cast<float4*>(p.push_bases[owner] + p.push_offset) + ((size_t)p.push_rank * p.push_rows_per_rank + (local - lane)) * 3;
+#pragma unroll
+                for (int k = 0; k < 3; ++k) dst[k * 32 + lane] = wrow[k * 32 + lane];
+            }
+        } else if (visible) {
             float4* dst = reinterpret_cast<float4*>(p.push_bases[owner] + p.push_offset) + ((size_t)p.push_rank * p.push_rows_per_rank + local) * 3;
             dst[0] = make_float4(dmx, dmy, dmz, sB.y);
             dst[1] = make_float4(dscale[0], dscale[1], dscale[2], drot.x);
