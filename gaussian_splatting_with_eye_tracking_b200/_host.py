@@ -356,7 +356,8 @@ def rasterize_gaussians_amr(background, means3D, colors, opacity, scales, rotati
                             prefiltered, foveaStep, out_color_precomp, geomBuffer_precomp, binningBuffer_precomp,
                             imageBuffer_precomp, interpolate_image, debug, gaze=None, band=None):
     """``gaze`` = (cx, cy, (r1, r2, r3, r4)) enables the gaze-driven level cap (extension; None = reference).
-    ``band`` = (row0, row1) restricts binning and blending to 32-px tile rows [row0, row1) (extension)."""
+    ``band`` = (row0, row1) restricts binning and blending to 32-px tile rows [row0, row1) (extension); rows of out_color
+    outside the band are left unwritten (only the band's rows are cleared and rendered)."""
     step = int(foveaStep)
     if step >= 1 and means3D.is_cuda and means3D.dim() == 2:
         # progressive rounds 1..4 read nothing of the scene but its size (everything was built by step 0): marshal only what the

@@ -345,7 +345,7 @@ int gsr_profile_read(float* ms, int* counts) {
 const char* gsr_last_error(void) { return g_err; }
 int gsr_set_option(int option, int value) {
     if (option == GSR_OPT_SORT_VARIANT && value >= 0 && value <= 5) { set_sort_variant(value); return GSR_OK; }
-    if (option == GSR_OPT_BLEND_VARIANT && value >= 0 && value <= 1) { set_blend_variant(value); return GSR_OK; }
+    if (option == GSR_OPT_BLEND_VARIANT && value >= 0 && value <= 2) { set_blend_variant(value); return GSR_OK; }
     if (option == GSR_OPT_PEER_TIMEOUT_MS && value >= 0) { set_peer_timeout_ms(value); return GSR_OK; }
     if (option == GSR_OPT_NVTX && (value == 0 || value == 1)) { set_nvtx(value); return GSR_OK; }
     if (option == GSR_OPT_FAKE_SORT_ERROR && (value == 0 || value == 1)) { set_fake_sort_error(value); return GSR_OK; }

@@ -350,6 +350,141 @@ void launch_blend_count(const BlendArgs& a, unsigned long long* totals, cudaStre
     count_launch();
 }
 
+// ------------------------------------------------------------------------------------------------
+// forward, ASYNC-STAGED variant (GSR_OPT_BLEND_VARIANT = 2; A/B only): the same kernel as blend_fwd2_kernel
+// with the per-batch gather issued as cp.async (global -> shared without passing through registers, committed one batch ahead,
+// waited with cp.async.wait_group) instead of __ldg into a register double buffer.  north_star (3) names "staging Gaussian
+// batches into shared memory via TMA/cp.async": a list entry is a 4-byte id followed by an indexed gather of 8 + 16 + 12 bytes
+// from three arrays, so there is no tile for a TMA descriptor; cp.async is the applicable form.  The exact tile cull and the
+// compaction still need the values: they are read back from the raw staging area, culled, and compacted into s_ent.
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void cp_async_4(void* smem, const void* gmem) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((uint32_t)__cvta_generic_to_shared(smem)), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async_8(void* smem, const void* gmem) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"((uint32_t)__cvta_generic_to_shared(smem)), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async_16(void* smem, const void* gmem) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(smem)), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+
+__global__ void __launch_bounds__(kBlend2Threads) blend_fwd3_kernel(const FwdParams p) {
+    __shared__ float4 s_ent[3 * kBlend2Threads];
+    __shared__ __align__(16) float4 s_co[2][kBlend2Threads];       // raw staging, double buffered
+    __shared__ __align__(8) float2 s_xy[2][kBlend2Threads];
+    __shared__ float s_col[2][3 * kBlend2Threads];
+    __shared__ uint32_t s_wcnt[kBlend2Threads / 32];
+    __shared__ uint32_t s_count;
+
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const uint32_t lx = (wid & 1) * 8 + (lane & 3) * 2, ly = (wid >> 1) * 8 + (lane >> 2);
+    const uint32_t tile_y = blockIdx.y + (uint32_t)p.row0;
+    const uint32_t pix_x = blockIdx.x * 16 + lx, pix_y = tile_y * 16 + ly;
+    const bool inside0 = pix_x < (uint32_t)p.W && pix_y < (uint32_t)p.H;
+    const bool inside1 = pix_x + 1 < (uint32_t)p.W && pix_y < (uint32_t)p.H;
+    const float pyf = (float)pix_y;
+    const f32x2 npx2 = pk(-(float)pix_x, -(float)(pix_x + 1));
+    const float rx0 = (float)(blockIdx.x * 16), ry0 = (float)(tile_y * 16);
+    const float rx1 = rx0 + 15.f, ry1 = ry0 + 15.f;
+
+    const uint2 range = p.ranges[tile_y * p.tiles_x + blockIdx.x];
+    const int todo = (int)(range.y - range.x);
+    const int rounds = (todo + kBlend2Threads - 1) / kBlend2Threads;
+
+    float T0 = 1.0f, T1 = 1.0f, Ca0 = 0.f, Ca1 = 0.f, Ca2 = 0.f, Cb0 = 0.f, Cb1 = 0.f, Cb2 = 0.f;
+    uint32_t last0 = 0, last1 = 0;
+    bool done0 = !inside0, done1 = !inside1;
+
+    auto issue = [&](int r, uint32_t id) {            // batch r's gather for this thread's entry, into buffer r & 1
+        const int b = r & 1;
+        cp_async_8(&s_xy[b][tid], p.means2D + id);
+        cp_async_16(&s_co[b][tid], p.conic_opacity + id);
+        cp_async_4(&s_col[b][3 * tid], p.colors + 3 * (size_t)id);
+        cp_async_4(&s_col[b][3 * tid + 1], p.colors + 3 * (size_t)id + 1);
+        cp_async_4(&s_col[b][3 * tid + 2], p.colors + 3 * (size_t)id + 2);
+    };
+    uint32_t id_next = 0;
+    if (tid < todo) issue(0, __ldg(p.point_list + range.x + tid));
+    cp_async_commit();
+    if (kBlend2Threads + tid < todo) id_next = __ldg(p.point_list + range.x + kBlend2Threads + tid);
+
+    for (int r = 0; r < rounds; ++r) {
+        cp_async_wait_all();                            // this thread's copies of batch r have landed
+        if (__syncthreads_count(done0 && done1) == kBlend2Threads) break;
+        const bool valid = r * kBlend2Threads + tid < todo;
+        const int b = r & 1;
+        if ((r + 1) * kBlend2Threads + tid < todo) issue(r + 1, id_next);      // overlaps the blending of batch r
+        cp_async_commit();
+        if ((r + 2) * kBlend2Threads + tid < todo) id_next = __ldg(p.point_list + range.x + (r + 2) * kBlend2Threads + tid);
+        GaussRec cur;
+        if (valid) { cur.xy = s_xy[b][tid]; cur.co = s_co[b][tid]; cur.col = make_float3(s_col[b][3 * tid], s_col[b][3 * tid + 1], s_col[b][3 * tid + 2]); }
+        const bool keep = valid && !cannot_touch(cur.xy, cur.co, rx0, ry0, rx1, ry1);
+        const int slot = compact_slot<kBlend2Threads>(keep, s_wcnt, &s_count);
+        if (slot >= 0) {
+            s_ent[3 * slot] = make_float4(cur.xy.x, cur.xy.y, cur.co.x, cur.co.y);
+            s_ent[3 * slot + 1] = make_float4(cur.co.z, reject_below(cur.co.w), cur.co.w, __uint_as_float((uint32_t)(r * kBlend2Threads + tid + 1)));
+            s_ent[3 * slot + 2] = make_float4(cur.col.x, cur.col.y, cur.col.z, 0.f);
+        }
+        __syncthreads();
+        const int count = (int)s_count;
+        if (!(done0 && done1)) {
+            const float4* e = s_ent;
+            int lj0 = -1, lj1 = -1;
+            for (int j = 0; j < count; ++j, e += 3) {
+                const float4 A = e[0], B = e[1];
+                const float dy = __fadd_rn(A.y, -pyf);
+                float pw0, pw1;
+                upk(blend_power2(A.z, A.w, B.x, add2(pk(A.x, A.x), npx2), dy), pw0, pw1);
+                const bool c0 = !done0 && !(pw0 < B.y) && !(pw0 > 0.0f);
+                const bool c1 = !done1 && !(pw1 < B.y) && !(pw1 > 0.0f);
+                if (!(c0 || c1)) continue;
+                const float4 Cc = e[2];
+                if (c0) {
+                    const float alpha = fminf(0.99f, __fmul_rn(B.z, expf(pw0)));
+                    if (!(alpha < kAlphaMin)) {
+                        const float test_T = __fmul_rn(T0, __fadd_rn(1.f, -alpha));
+                        if (test_T < 0.0001f) done0 = true;
+                        else {
+                            Ca0 = __fmaf_rn(T0, __fmul_rn(alpha, Cc.x), Ca0); Ca1 = __fmaf_rn(T0, __fmul_rn(alpha, Cc.y), Ca1);
+                            Ca2 = __fmaf_rn(T0, __fmul_rn(alpha, Cc.z), Ca2);
+                            T0 = test_T; lj0 = j;
+                        }
+                    }
+                }
+                if (c1) {
+                    const float alpha = fminf(0.99f, __fmul_rn(B.z, expf(pw1)));
+                    if (!(alpha < kAlphaMin)) {
+                        const float test_T = __fmul_rn(T1, __fadd_rn(1.f, -alpha));
+                        if (test_T < 0.0001f) done1 = true;
+                        else {
+                            Cb0 = __fmaf_rn(T1, __fmul_rn(alpha, Cc.x), Cb0); Cb1 = __fmaf_rn(T1, __fmul_rn(alpha, Cc.y), Cb1);
+                            Cb2 = __fmaf_rn(T1, __fmul_rn(alpha, Cc.z), Cb2);
+                            T1 = test_T; lj1 = j;
+                        }
+                    }
+                }
+                if (done0 && done1) break;
+            }
+            if (lj0 >= 0) last0 = __float_as_uint(s_ent[3 * lj0 + 1].w);
+            if (lj1 >= 0) last1 = __float_as_uint(s_ent[3 * lj1 + 1].w);
+        }
+    }
+    cp_async_wait_all();
+    const size_t HW = (size_t)p.H * p.W;
+    const float bg0 = __ldg(p.bg), bg1 = __ldg(p.bg + 1), bg2 = __ldg(p.bg + 2);
+    const size_t pix_id = (size_t)p.W * pix_y + pix_x;
+    if (inside0) {
+        p.final_T[pix_id] = T0; p.n_contrib[pix_id] = last0;
+        p.out_color[pix_id] = __fmaf_rn(T0, bg0, Ca0); p.out_color[HW + pix_id] = __fmaf_rn(T0, bg1, Ca1); p.out_color[2 * HW + pix_id] = __fmaf_rn(T0, bg2, Ca2);
+    }
+    if (inside1) {
+        p.final_T[pix_id + 1] = T1; p.n_contrib[pix_id + 1] = last1;
+        p.out_color[pix_id + 1] = __fmaf_rn(T1, bg0, Cb0); p.out_color[HW + pix_id + 1] = __fmaf_rn(T1, bg1, Cb1); p.out_color[2 * HW + pix_id + 1] = __fmaf_rn(T1, bg2, Cb2);
+    }
+}
+
 static int g_blend_variant = 0;
 void set_blend_variant(int v) { g_blend_variant = v; }
 
@@ -364,6 +499,7 @@ void launch_blend_forward(const BlendArgs& a, cudaStream_t s) {
     p.row0 = r0;
     dim3 grid((a.W + 15) / 16, r1 - r0, 1);
     if (g_blend_variant == 1) blend_fwd_kernel<<<grid, kBlendThreads, 0, s>>>(p);      // one pixel per thread (A/B reference)
+    else if (g_blend_variant == 2) blend_fwd3_kernel<<<grid, kBlend2Threads, 0, s>>>(p);   // cp.async staging (A/B, measured: DESIGN section 3)
     else blend_fwd2_kernel<<<grid, kBlend2Threads, 0, s>>>(p);
     count_launch();
 }

@@ -372,7 +372,7 @@ GSR_API int gsr_blend_stats(int P, int W, int H, const void* geom_buffer, const 
  * unicast peer kernel into a link-diagnostic mode -- 0x1xx = remote loads only, 0x2xx = remote stores only -- that does NOT
  * compute the sum; tools/peer_diag.py uses it to time the two directions and nothing else may) ---- */
 enum { GSR_OPT_SORT_VARIANT = 0,  /* onesweep tile shape for u32 keys: 0 = default, 1..5 see gsr_binning.cu */
-       GSR_OPT_BLEND_VARIANT = 1, /* forward blend: 0 = two pixels per thread, packed FP32x2 (default); 1 = one pixel per thread */
+       GSR_OPT_BLEND_VARIANT = 1, /* forward blend: 0 = two pixels per thread, packed FP32x2 (default); 1 = one pixel per thread; 2 = as 0 with cp.async staging (A/B) */
        GSR_OPT_PEER_CTAS_PER_SM = 2, /* gsr_peer_allreduce_sum*: grid cap in CTAs per SM, 0 = default */
        GSR_OPT_PEER_TIMEOUT_MS = 6, /* peer barrier watchdog in milliseconds (default 600 000 = 10 min, NCCL-like); on expiry the
                                        barrier posts gsr_peer_error and the data kernel behind it writes NaN */
