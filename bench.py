@@ -377,6 +377,7 @@ def dp_rank1_variants(impl, d, cam_of, w, timer, Kb, world, dev, only=None):
     modes = {"dense_rows": (False, 1), "packed_rows": (True, 1)}
     peer_err, peer_red = None, None
     if world > 1 and not os.environ.get("GSR_BENCH_NO_PEER"):
+        impl.capi.check(impl.capi.lib.gsr_set_option(6, 60000), "gsr_set_option")      # peer watchdog 60 s for the bench
         try:                 # the 11 dense floats summed over NVLink peer memory (gsr_peer_allreduce_sum) instead of NCCL
             peer_red = gdist.PeerAllReduce(11 * ((P_ + 3) // 4 * 4), dev, staging_gaussians=P_)
             modes["packed_rows_peer_sum"] = (True, 1)
@@ -404,7 +405,8 @@ def dp_rank1_variants(impl, d, cam_of, w, timer, Kb, world, dev, only=None):
                 d["bg"], d["means3D"], radii, e_, d["scales"], d["rotations"], 1.0, e_, cam.world_view_transform,
                 cam.full_proj_transform, cam.tanfovx, cam.tanfovy, w, d["shs"], d["sh_degree"], cam.camera_center, gb, N, bb, ib,
                 False, compact_sh=True,
-                between_phases=lambda drgb: exch.start_gather(drgb, cam.camera_center, d["means3D"], d["sh_degree"], M_, radii=radii),
+                between_phases=lambda drgb: (exch.start_owner_sum(dev) if fused else None,
+                                             exch.start_gather(drgb, cam.camera_center, d["means3D"], d["sh_degree"], M_, radii=radii)),
                 preprocess_chunks=nch,
                 after_chunk=(lambda first, count, rows: exch.start_reduce_chunk(rows)) if nch > 1 else None,
                 dense_out=peer_red.data if use_peer else None, push=peer_red.push_args if fused else None)

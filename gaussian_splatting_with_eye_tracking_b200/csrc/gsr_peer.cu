@@ -14,6 +14,8 @@
 
 namespace gsr {
 
+void preload_preprocess_backward();       // gsr_preprocess.cu
+
 namespace {
 
 constexpr int kMaxPeers = 8;
@@ -154,14 +156,19 @@ uint32_t* peer_error_word() {
     return w;
 }
 
-// ---- fused exchange, second half (gsr_peer_owner_sum): rank r sums the rows staged for its slice of Gaussians and delivers the
-// totals to every rank.  A thread owns 4 consecutive Gaussians so that every array of the dense block is written with 128-bit
-// stores: means3D 3 x float4, opacity 1, scales 3, rotations 4.
+// ---- fused exchange, second half (gsr_peer_owner_sum): a STREAMING consumer.  It runs beside preprocess_bwd_kernel (its own
+// stream, a few dozen resident CTAs) and follows it block by block: a 256-Gaussian block is summed the moment the `world` ranks
+// have staged it -- each producer CTA publishes (fence + release store) a ready word per block at the owner -- and the totals
+// leave for every rank at once.  When the producers finish only the last few blocks and the closing barrier are exposed.
+// A CTA reads a block's world x 12 KB of staged rows as whole 128-bit coalesced runs, adds them in rank order (the same float
+// expression on every run, so every rank receives the SAME bits; rows of invisible Gaussians were staged as zeros, exactly the
+// terms the dense per-view tensors hold), transposes the [256][12] totals through shared memory and writes every array of the
+// dense block with 128-bit stores: means3D 3 x float4 per 4 Gaussians, opacity 1, scales 3, rotations 4.
 struct OwnerSumParams {
     char* const* bases; float* mc;            // mc != nullptr: multicast mapping of the buffers (one multimem.st per value)
-    size_t staging_offset, final_offset, flag_offset;
-    int P, P4, rows_per_rank, world, rank;
-    const uint32_t* masks; size_t mask_stride;
+    size_t staging_offset, final_offset, ready_offset, flag_offset;
+    int P4, rows_per_rank, world, rank;
+    uint32_t epoch; long long timeout_ns; uint32_t* host_err;
 };
 
 template <bool MC>
@@ -176,48 +183,77 @@ __device__ __forceinline__ void deliver(const OwnerSumParams& p, size_t float_in
 
 template <bool MC>
 __global__ void __launch_bounds__(kPeerThreads) peer_owner_sum_kernel(const OwnerSumParams p) {
-    const bool poisoned = peer_poisoned(p.bases, p.flag_offset, p.world, p.rank);
+    __shared__ float4 s_tot[3 * 256];           // the block's totals, row-major [256 Gaussians][12 floats]
+    __shared__ int s_bad;
+    const float* s_f = reinterpret_cast<const float*>(s_tot);
+    const int tid = threadIdx.x;
     const float nanv = __int_as_float(0x7fc00000);
     const float4* staging = reinterpret_cast<const float4*>(p.bases[p.rank] + p.staging_offset);
+    const uint32_t* ready = reinterpret_cast<const uint32_t*>(p.bases[p.rank] + p.ready_offset);
+    uint32_t* mine = reinterpret_cast<uint32_t*>(p.bases[p.rank] + p.flag_offset);
     const size_t P4 = (size_t)p.P4;
+    const int nblk = p.rows_per_rank >> 8;
+    if (tid == 0) s_bad = 0;
     // this rank owns the 256-Gaussian blocks rank, rank + world, rank + 2 world, ... (block-cyclic, see preprocess_bwd_kernel);
-    // local row g4 of the staging slots <-> Gaussian ((g4 >> 8) * world + rank) * 256 + (g4 & 255)
-    for (int g4 = (blockIdx.x * kPeerThreads + threadIdx.x) * 4; g4 < p.rows_per_rank; g4 += gridDim.x * kPeerThreads * 4) {
-        const int idx = (((g4 >> 8) * p.world + p.rank) << 8) | (g4 & 255);   // 4 Gaussians idx .. idx + 3, same mask word
-        if (idx >= p.P4) continue;
-        float row[4][11];
-#pragma unroll
-        for (int q = 0; q < 4; ++q)
-#pragma unroll
-            for (int c = 0; c < 11; ++c) row[q][c] = poisoned ? nanv : 0.f;
-        if (!poisoned) {
-            for (int k = 0; k < p.world; ++k) {                           // rank order: the same float expression on every run
-                const uint32_t word = __ldg(p.masks + (size_t)k * p.mask_stride + (idx >> 5));
-                const uint32_t bits = (word >> (idx & 31)) & 0xfu;
-                if (!bits) continue;
-                const float4* src = staging + ((size_t)k * p.rows_per_rank + g4) * 3;
-#pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                    if (!((bits >> q) & 1u)) continue;
-                    const float4 a = __ldcg(src + 3 * q), b = __ldcg(src + 3 * q + 1), c = __ldcg(src + 3 * q + 2);
-                    row[q][0] += a.x; row[q][1] += a.y; row[q][2] += a.z; row[q][3] += a.w;
-                    row[q][4] += b.x; row[q][5] += b.y; row[q][6] += b.z; row[q][7] += b.w;
-                    row[q][8] += c.x; row[q][9] += c.y; row[q][10] += c.z;
+    // local block j <-> Gaussians ((j * world + rank) * 256 ...)
+    for (int j = blockIdx.x; j < nblk; j += gridDim.x) {
+        const long long idx0 = ((long long)j * p.world + p.rank) << 8;
+        if (idx0 >= (long long)P4) break;
+        __syncthreads();                                                  // s_tot / s_bad of the previous block are free
+        if (tid < p.world) {                                              // thread k waits for rank k's copy of block j
+            const uint32_t* w = ready + (size_t)tid * nblk + j;
+            unsigned long long t0 = 0;
+            unsigned spins = 0;
+            while ((int32_t)(ld_acquire_sys(w) - p.epoch) < 0) {
+                if ((++spins & 255u) == 0u) {
+                    unsigned long long t1;
+                    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+                    if (t0 == 0) t0 = t1;
+                    else if ((long long)(t1 - t0) > p.timeout_ns) {      // never a silent sum of stale rows (see peer_barrier_kernel)
+                        mine[p.world] = 1u;
+                        if (p.host_err) { *((volatile uint32_t*)p.host_err) = 1u; __threadfence_system(); }
+                        s_bad = 1;
+                        break;
+                    }
                 }
+                __nanosleep(200);
             }
         }
-        // dense block: [means3D 3 x P4 | opacity P4 | scales 3 x P4 | rotations 4 x P4]
-        const size_t i = (size_t)idx;
-        deliver<MC>(p, 3 * i,      make_float4(row[0][0], row[0][1], row[0][2], row[1][0]));
-        deliver<MC>(p, 3 * i + 4,  make_float4(row[1][1], row[1][2], row[2][0], row[2][1]));
-        deliver<MC>(p, 3 * i + 8,  make_float4(row[2][2], row[3][0], row[3][1], row[3][2]));
-        deliver<MC>(p, 3 * P4 + i, make_float4(row[0][3], row[1][3], row[2][3], row[3][3]));
-        deliver<MC>(p, 4 * P4 + 3 * i,     make_float4(row[0][4], row[0][5], row[0][6], row[1][4]));
-        deliver<MC>(p, 4 * P4 + 3 * i + 4, make_float4(row[1][5], row[1][6], row[2][4], row[2][5]));
-        deliver<MC>(p, 4 * P4 + 3 * i + 8, make_float4(row[2][6], row[3][4], row[3][5], row[3][6]));
+        __syncthreads();
+        const bool poisoned = s_bad != 0 || ((volatile const uint32_t*)mine)[p.world] != 0u;
 #pragma unroll
-        for (int q = 0; q < 4; ++q)
-            deliver<MC>(p, 7 * P4 + 4 * (i + q), make_float4(row[q][7], row[q][8], row[q][9], row[q][10]));
+        for (int q = 0; q < 3; ++q) {
+            const int f = tid + q * kPeerThreads;                          // float4 f of the block's 768
+            const float4* src = staging + (size_t)j * 768 + f;
+            float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+            for (int k = 0; k < p.world; ++k) {                            // rank order
+                const float4 v = __ldcg(src + (size_t)k * p.rows_per_rank * 3);
+                acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+            }
+            if (poisoned) acc = make_float4(nanv, nanv, nanv, nanv);
+            s_tot[f] = acc;
+        }
+        __syncthreads();
+        // dense block: [means3D 3 x P4 | opacity P4 | scales 3 x P4 | rotations 4 x P4]; this block's n Gaussians (multiple of 4)
+        const int n = (int)min((long long)256, (long long)P4 - idx0);
+        const int n34 = 3 * n / 4, n4 = n / 4;
+        const size_t i0 = (size_t)idx0;
+        for (int t = tid; t < 2 * n34 + n4 + n; t += kPeerThreads) {
+            if (t < 2 * n34) {                                             // means3D (columns 0..2) or scales (columns 4..6)
+                const bool sc = t >= n34;
+                const int m = sc ? t - n34 : t, c0 = sc ? 4 : 0;
+                float v[4];
+#pragma unroll
+                for (int e = 0; e < 4; ++e) { const int el = 4 * m + e; v[e] = s_f[(el / 3) * 12 + c0 + el % 3]; }
+                deliver<MC>(p, (sc ? 4 * P4 : 0) + 3 * i0 + 4 * (size_t)m, make_float4(v[0], v[1], v[2], v[3]));
+            } else if (t < 2 * n34 + n4) {                                 // opacity (column 3)
+                const int m = t - 2 * n34;
+                deliver<MC>(p, 3 * P4 + i0 + 4 * (size_t)m, make_float4(s_f[(4 * m) * 12 + 3], s_f[(4 * m + 1) * 12 + 3], s_f[(4 * m + 2) * 12 + 3], s_f[(4 * m + 3) * 12 + 3]));
+            } else {                                                       // rotations (columns 7..10)
+                const int m = t - 2 * n34 - n4;
+                deliver<MC>(p, 7 * P4 + 4 * (i0 + m), make_float4(s_f[m * 12 + 7], s_f[m * 12 + 8], s_f[m * 12 + 9], s_f[m * 12 + 10]));
+            }
+        }
     }
     __threadfence_system();
 }
@@ -238,6 +274,7 @@ void preload(int world) {
     cudaFuncGetAttributes(&fa, peer_reduce_mc_kernel);
     cudaFuncGetAttributes(&fa, peer_owner_sum_kernel<true>);
     cudaFuncGetAttributes(&fa, peer_owner_sum_kernel<false>);
+    preload_preprocess_backward();            // the producer the streaming owner sum waits for
     switch (world) {
         case 2: preload_reduce<2>(); break; case 3: preload_reduce<3>(); break; case 4: preload_reduce<4>(); break;
         case 5: preload_reduce<5>(); break; case 6: preload_reduce<6>(); break; case 7: preload_reduce<7>(); break;
@@ -283,27 +320,29 @@ int gsr_peer_error(void) {
     return v ? 1 : 0;
 }
 
-int gsr_peer_owner_sum(void* const* peer_bases, void* multicast_base, size_t staging_offset, size_t final_offset, int P,
-                       int rows_per_rank, const uint32_t* view_masks, size_t mask_stride_words, size_t flag_offset,
-                       int world, int rank, unsigned epoch, void* stream) {
-    if (world < 1 || world > kMaxPeers || rank < 0 || rank >= world || !peer_bases || !view_masks) {
+int gsr_peer_owner_sum(void* const* peer_bases, void* multicast_base, size_t staging_offset, size_t final_offset,
+                       size_t ready_offset, int P, int rows_per_rank, size_t flag_offset, int world, int rank, unsigned epoch,
+                       int ctas, void* stream) {
+    if (world < 1 || world > kMaxPeers || rank < 0 || rank >= world || !peer_bases) {
         set_error("peer_owner_sum: bad arguments (world %d, rank %d)", world, rank); return GSR_ERR_INVALID;
     }
     if (P < 0 || rows_per_rank <= 0 || (rows_per_rank % 256) != 0 || (long long)rows_per_rank * world < (long long)P ||
-        (staging_offset & 15) || (final_offset & 15) || (flag_offset & 3) || ((uintptr_t)multicast_base & 15) ||
-        mask_stride_words < (size_t)((P + 31) / 32)) {
+        (staging_offset & 15) || (final_offset & 15) || (flag_offset & 3) || (ready_offset & 3) || ((uintptr_t)multicast_base & 15)) {
         set_error("peer_owner_sum: bad sizes / alignment (P %d, rows per rank %d)", P, rows_per_rank); return GSR_ERR_INVALID;
     }
     cudaStream_t s = (cudaStream_t)stream;
     char* const* bases = (char* const*)peer_bases;
     preload(world);
+    // opening barrier: every rank is past the last reader of the totals of the previous exchange (the broadcasts below overwrite them)
     peer_barrier_kernel<<<1, 32, 0, s>>>(bases, flag_offset, world, rank, epoch, peer_timeout_ns(), peer_error_word());
     OwnerSumParams p;
-    p.bases = bases; p.mc = (float*)multicast_base; p.staging_offset = staging_offset; p.final_offset = final_offset; p.flag_offset = flag_offset;
-    p.P = P; p.P4 = (P + 3) / 4 * 4; p.rows_per_rank = rows_per_rank; p.world = world; p.rank = rank;
-    p.masks = view_masks; p.mask_stride = mask_stride_words;
-    long long blocks = ((long long)rows_per_rank / 4 + kPeerThreads - 1) / kPeerThreads;
-    blocks = std::max(1LL, std::min(blocks, 148LL * (g_peer_ctas_per_sm ? g_peer_ctas_per_sm : 2)));
+    p.bases = bases; p.mc = (float*)multicast_base; p.staging_offset = staging_offset; p.final_offset = final_offset;
+    p.ready_offset = ready_offset; p.flag_offset = flag_offset;
+    p.P4 = (P + 3) / 4 * 4; p.rows_per_rank = rows_per_rank; p.world = world; p.rank = rank;
+    p.epoch = epoch; p.timeout_ns = peer_timeout_ns(); p.host_err = peer_error_word();
+    const int mine = (int)((((long long)p.P4 + 255) / 256 + world - 1 - rank) / world);       // blocks this rank owns
+    int blocks = ctas > 0 ? ctas : (g_peer_ctas_per_sm ? 148 * g_peer_ctas_per_sm : 74);
+    blocks = std::max(1, std::min(blocks, std::max(1, mine)));
     if (multicast_base) peer_owner_sum_kernel<true><<<(unsigned)blocks, kPeerThreads, 0, s>>>(p);
     else peer_owner_sum_kernel<false><<<(unsigned)blocks, kPeerThreads, 0, s>>>(p);
     peer_barrier_kernel<<<1, 32, 0, s>>>(bases, flag_offset, world, rank, epoch + 1u, peer_timeout_ns(), peer_error_word());

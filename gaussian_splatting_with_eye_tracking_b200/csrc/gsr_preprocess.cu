@@ -483,6 +483,7 @@ struct PreBwdParams {
     float* dL_drgb_clamped;        // optional [P,3]; with dL_dsh == nullptr the SH rows are not written (gsr_grads)
     // fused view-parallel exchange (gsr_grads.push_*): rows of the 11 dense floats go to the owner rank's staging area
     char* const* push_bases; size_t push_offset; int push_rank, push_world, push_rows_per_rank;
+    uint32_t push_epoch; size_t push_ready_offset;
 };
 
 // SH rows are staged through shared memory (STAGED): a thread's 3M coefficients / gradients are 192 B apart from its
@@ -501,7 +502,8 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreBwdParams 
     __syncthreads();
     const int idx = (blockIdx.x + p.block0) * 256 + tid;
     const bool valid = idx < p.P;
-    if (!STAGED && !valid) return;
+    const bool pushing = p.push_bases != nullptr;                   // whole CTAs stay: every row is pushed, then the block is published
+    if (!STAGED && !valid && !pushing) return;
     const size_t i3 = 3 * (size_t)idx;
 
     const bool visible = valid && p.radii[idx] > 0;
@@ -705,8 +707,7 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreBwdParams 
             }
         }
     }
-    const bool push_staged = STAGED && p.push_bases != nullptr;     // whole warps stay for the cooperative row push below
-    if (!valid && !push_staged) return;
+    if (!valid && !pushing) return;
 
     // ---------------- cov3D -> scale, rotation (backward.cu:278-341)
     if (visible && p.cov_from_scales) {
@@ -749,40 +750,52 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreBwdParams 
 #pragma unroll
         for (int i = 0; i < 6; ++i) p.dL_dcov3D[6 * (size_t)idx + i] = dcov[i];
     }
-    if (p.push_bases != nullptr) {
+    if (pushing) {
         // One 48-byte row per Gaussian into the owner's staging area (peer memory over NVLink).  Ownership is block-cyclic
         // (256-Gaussian blocks dealt round-robin to the ranks): at any moment the CTAs in flight push to ALL owners at once;
         // contiguous slices would make every rank push to the same owner at the same time (7-to-1 incast on one GPU's ingress).
         // A warp's 32 rows are consecutive at the owner: they are transposed through shared memory and leave as three fully
         // contiguous 512-byte stores (per-lane 16-byte pieces 48 bytes apart travel as 96 small NVLink packets per warp: measured
-        // slower than the all-reduce they replace).  Rows of invisible Gaussians go out as zeros -- whole lines, no read-modify-
-        // write at the owner; a warp without any visible Gaussian sends nothing (the owner skips it by the visibility masks).
-        // No fence here: the kernel's completion orders these stores before the barrier that follows.
+        // slower than the all-reduce they replace).  Rows of invisible Gaussians go out as zeros -- the terms the dense per-view
+        // tensors hold for them -- so the owner adds all ranks' rows unconditionally: whole lines, no masks, no read-modify-write.
         const int blk = idx >> 8, owner = blk % p.push_world, local = ((blk / p.push_world) << 8) | (idx & 255);
-        if (push_staged) {
-            const uint32_t any_vis = __ballot_sync(0xffffffffu, visible);
-            if (any_vis) {
-                float4* wrow = reinterpret_cast<float4*>(s_sh + wid * 32 * kShStride);      // the warp's SH staging rows are dead by now
-                __syncwarp();
-                wrow[3 * lane] = visible ? make_float4(dmx, dmy, dmz, sB.y) : make_float4(0.f, 0.f, 0.f, 0.f);
-                wrow[3 * lane + 1] = visible ? make_float4(dscale[0], dscale[1], dscale[2], drot.x) : make_float4(0.f, 0.f, 0.f, 0.f);
-                wrow[3 * lane + 2] = visible ? make_float4(drot.y, drot.z, drot.w, 0.f) : make_float4(0.f, 0.f, 0.f, 0.f);
-                __syncwarp();
-                float4* dst = reinterpret_cast<float4*>(p.push_bases[owner] + p.push_offset) + ((size_t)p.push_rank * p.push_rows_per_rank + (local - lane)) * 3;
+        const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+        const float4 r0 = visible ? make_float4(dmx, dmy, dmz, sB.y) : z4;
+        const float4 r1 = visible ? make_float4(dscale[0], dscale[1], dscale[2], drot.x) : z4;
+        const float4 r2 = visible ? make_float4(drot.y, drot.z, drot.w, 0.f) : z4;
+        float4* row = reinterpret_cast<float4*>(p.push_bases[owner] + p.push_offset) + ((size_t)p.push_rank * p.push_rows_per_rank + local) * 3;
+        if (STAGED) {
+            float4* wrow = reinterpret_cast<float4*>(s_sh + wid * 32 * kShStride);      // the warp's SH staging rows are dead by now
+            __syncwarp();
+            wrow[3 * lane] = r0; wrow[3 * lane + 1] = r1; wrow[3 * lane + 2] = r2;
+            __syncwarp();
+            float4* dst = row - 3 * lane;
 #pragma unroll
-                for (int k = 0; k < 3; ++k) dst[k * 32 + lane] = wrow[k * 32 + lane];
-            }
-        } else if (visible) {
-            float4* dst = reinterpret_cast<float4*>(p.push_bases[owner] + p.push_offset) + ((size_t)p.push_rank * p.push_rows_per_rank + local) * 3;
-            dst[0] = make_float4(dmx, dmy, dmz, sB.y);
-            dst[1] = make_float4(dscale[0], dscale[1], dscale[2], drot.x);
-            dst[2] = make_float4(drot.y, drot.z, drot.w, 0.f);
+            for (int k = 0; k < 3; ++k) dst[k * 32 + lane] = wrow[k * 32 + lane];
+        } else {
+            row[0] = r0; row[1] = r1; row[2] = r2;
+        }
+        // publish the block: all 256 rows are out (bar.sync orders the other warps' stores before thread 0's fence; the fence is
+        // cumulative), then a release store of the epoch into this rank's ready word for the block at the owner
+        __syncthreads();
+        if (tid == 0 && p.push_ready_offset != 0) {
+            __threadfence_system();
+            uint32_t* w = reinterpret_cast<uint32_t*>(p.push_bases[owner] + p.push_ready_offset) +
+                          (size_t)p.push_rank * (p.push_rows_per_rank >> 8) + blk / p.push_world;
+            asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(w), "r"(p.push_epoch) : "memory");
         }
         return;
     }
     p.dL_dmeans3D[i3] = dmx; p.dL_dmeans3D[i3 + 1] = dmy; p.dL_dmeans3D[i3 + 2] = dmz;
     p.dL_dscales[i3] = dscale[0]; p.dL_dscales[i3 + 1] = dscale[1]; p.dL_dscales[i3 + 2] = dscale[2];
     reinterpret_cast<float4*>(p.dL_drot)[idx] = drot;
+}
+
+// resolve both instantiations now (lazy module loading, see gsr_peer.cu preload)
+void preload_preprocess_backward() {
+    cudaFuncAttributes fa;
+    cudaFuncGetAttributes(&fa, preprocess_bwd_kernel<true>);
+    cudaFuncGetAttributes(&fa, preprocess_bwd_kernel<false>);
 }
 
 void launch_preprocess_backward(const PreBwdArgs& a, cudaStream_t s) {
@@ -805,6 +818,7 @@ void launch_preprocess_backward(const PreBwdArgs& a, cudaStream_t s) {
     p.dL_drgb_clamped = a.out.dL_dcolors_clamped;
     p.push_bases = (char* const*)a.out.push_bases; p.push_offset = a.out.push_offset; p.push_rank = a.out.push_rank;
     p.push_rows_per_rank = a.out.push_rows_per_rank; p.push_world = a.out.push_world > 0 ? a.out.push_world : 1;
+    p.push_epoch = a.out.push_epoch; p.push_ready_offset = a.out.push_ready_offset;
     // staged SH path: needs M % 4 == 0 (128-bit rows), M <= 16 (row fits the staged stride) and 16 B-aligned tensors
     const bool staged = (p.dL_dsh != nullptr || p.colors_from_sh) && p.M > 0 && p.M <= 16 && (p.M % 4) == 0 && ((size_t)p.dL_dsh & 15) == 0 &&
                         (!p.colors_from_sh || p.shs_rest != nullptr || ((size_t)p.shs & 15) == 0);

@@ -199,7 +199,9 @@ class PeerAllReduce:
         self.staging_P = int(staging_gaussians)
         nblk = (self.staging_P + 255) // 256
         self.rows_per_rank = (nblk + self.world - 1) // self.world * 256 if self.staging_P else 0      # 256-blocks dealt round-robin
-        self.staging_floats = self.world * self.rows_per_rank * 12
+        # staging rows, then one ready word per (source rank, owned block), rounded to 64 words
+        self.ready_words = (self.world * (self.rows_per_rank // 256) + 63) // 64 * 64 if self.staging_P else 0
+        self.staging_floats = self.world * self.rows_per_rank * 12 + self.ready_words
         total = self.numel + self.staging_floats + self.flag_bytes // 4
         dev = torch.device(device)
         if self.world > 1:
@@ -223,7 +225,7 @@ class PeerAllReduce:
             self.bases_dev = self._bases_keep.data_ptr()
             self.hdl = None
             self.multicast_ptr = 0
-        self.buf[self.numel + self.staging_floats:].zero_()                # flag words: zero on every rank before anyone signals
+        self.buf[self.numel + self.staging_floats - self.ready_words:].zero_()   # ready + flag words: zero on every rank before anyone signals
         torch.cuda.synchronize(dev)
         if self.world > 1:
             dist.barrier(group)
@@ -256,27 +258,32 @@ class PeerAllReduce:
         return (self.numel + self.staging_floats) * 4
 
     @property
+    def ready_offset(self) -> int:
+        return (self.numel + self.world * self.rows_per_rank * 12) * 4
+
+    @property
     def push_args(self):
-        """What ``_host.rasterize_gaussians_backward(..., push=...)`` needs: (peer base table, staging offset, rank, world, rows per rank)."""
+        """What ``_host.rasterize_gaussians_backward(..., push=...)`` needs: (peer base table, staging offset, rank, world, rows per
+        rank, epoch, ready-word offset).  The epoch is the one the NEXT ``owner_sum`` call waits for: read this, queue owner_sum,
+        run the backward -- no other exchange on this object in between."""
         if not self.rows_per_rank:
             raise RuntimeError("PeerAllReduce was built without a staging area (staging_gaussians=P)")
-        return (self.bases_dev, self.numel * 4, self.rank, self.world, self.rows_per_rank)
+        return (self.bases_dev, self.numel * 4, self.rank, self.world, self.rows_per_rank, self.epoch, self.ready_offset)
 
-    def owner_sum(self, P: int, view_masks: torch.Tensor) -> None:
-        """Second half of the fused exchange, queued on the CURRENT stream (gsr_peer_owner_sum): barrier, this rank sums the rows
-        staged for its slice of Gaussians (visibility of Gaussian i in rank k's view = bit i of ``view_masks[k]``, int32
-        [world, >= ceil(P/32)] on the device) and writes the totals into the dense block at the start of EVERY rank's ``data``,
-        barrier."""
+    def owner_sum(self, P: int, ctas: int = 0) -> None:
+        """Second half of the fused exchange, queued on the CURRENT stream (gsr_peer_owner_sum): barrier, then this rank follows the
+        ready words of the blocks it owns, sums every block's staged rows in rank order as soon as all ranks have pushed it and
+        writes the totals into the dense block at the start of EVERY rank's ``data``, barrier.  Queue it on a side stream BEFORE
+        the backward that pushes (``push_args``): it then runs beside that kernel and only the last blocks remain after it."""
         import ctypes as C
         from ._capi import check
-        if int(P) != self.staging_P or view_masks.dtype != torch.int32 or not view_masks.is_contiguous() or view_masks.dim() != 2 \
-                or view_masks.shape[0] != self.world or view_masks.shape[1] < (int(P) + 31) // 32:
-            raise RuntimeError("PeerAllReduce.owner_sum: P / view_masks do not match the staging area")
+        if int(P) != self.staging_P:
+            raise RuntimeError("PeerAllReduce.owner_sum: P does not match the staging area")
         with torch.cuda.device(self.buf.device):
             st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
             check(self._lib.gsr_peer_owner_sum(C.c_void_p(self.bases_dev), C.c_void_p(self.multicast_ptr) if self.multicast_ptr else None,
-                                               self.numel * 4, 0, int(P), self.rows_per_rank, C.c_void_p(view_masks.data_ptr()),
-                                               int(view_masks.shape[1]), self.flag_offset, self.world, self.rank, self.epoch, st),
+                                               self.numel * 4, 0, self.ready_offset, int(P), self.rows_per_rank, self.flag_offset,
+                                               self.world, self.rank, self.epoch, int(ctas), st),
                   "gsr_peer_owner_sum")
         self.epoch += 2
 
@@ -314,12 +321,15 @@ class ShGradExchange:
         self.reducer = GradientAllReduce(bucket_bytes, group)
         self.peer = peer               # the 11 dense floats summed in place over NVLink peer memory instead of NCCL
         self._peer_stream = None
-        # fused: the preprocess-stage backward pushes every visible Gaussian's 11 floats to the owner rank's staging area
-        # (peer.push_args) and start_reduce only queues the owner sum + broadcast; needs packed rows (their masks tell the
-        # owner which ranks staged a row) and a peer buffer with a staging area
+        # fused: the preprocess-stage backward pushes every Gaussian's 11 floats to the owner rank's staging area
+        # (peer.push_args) while the owner sum + broadcast (start_owner_sum, queued between the backward phases) follows it
+        # block by block on its own stream; needs a peer buffer with a staging area
         self.fused = bool(fused)
-        if self.fused and (peer is None or not packed or not peer.rows_per_rank):
-            raise RuntimeError("ShGradExchange(fused=True) needs packed=True and a PeerAllReduce with staging_gaussians=P")
+        if self.fused and (peer is None or not peer.rows_per_rank):
+            raise RuntimeError("ShGradExchange(fused=True) needs a PeerAllReduce with staging_gaussians=P")
+        self._owner_sum_queued = False
+        self._fused_calls = 0
+        self.fused_warm_steps = 2
         self._gather_event = None
         self._rebuild = rebuild
         self.packed = bool(packed)
@@ -454,17 +464,32 @@ class ShGradExchange:
             self._side_allocs = [cams]
         self._rebuild_call = lambda: rebuild(means3D, cams, self._meta_all, rows_all.view(w, cap, 3), degree, M)
 
+    def start_owner_sum(self, device) -> None:
+        """Fused mode: queue the streaming owner sum on its own (high-priority) stream behind everything the caller's stream
+        holds so far.  Call between the two backward phases, BEFORE the preprocess-stage backward that pushes the rows
+        (``between_phases`` of _host.rasterize_gaussians_backward): the sum then runs beside that kernel.
+        The first ``fused_warm_steps`` calls do nothing (start_reduce then queues the sum BEHIND the backward): a kernel's first
+        launch may load its module under a context-wide synchronisation, which a consumer already spinning on the device would
+        block until the watchdog -- so it only runs beside the backward once every kernel of a step has been launched."""
+        self._fused_calls += 1
+        if self._fused_calls > self.fused_warm_steps:
+            self._queue_owner_sum(device)
+
+    def _queue_owner_sum(self, device) -> None:
+        dev = torch.device(device)
+        if self._peer_stream is None:
+            self._peer_stream = comm_stream(dev)
+        self._peer_stream.wait_stream(torch.cuda.current_stream(dev))          # the last reader of the previous totals is behind us
+        with torch.cuda.stream(self._peer_stream):
+            self.peer.owner_sum(self.peer.staging_P)
+        self._owner_sum_queued = True
+
     def start_reduce(self, dense_grads: Sequence[torch.Tensor]) -> None:
         """Queue the in-place SUM of the remaining gradients (means3D, opacity, scales, rotations)."""
         if self.fused:
-            dev = dense_grads[0].device
-            if self._peer_stream is None:
-                self._peer_stream = comm_stream(dev)
-            self._peer_stream.wait_stream(torch.cuda.current_stream(dev))      # this rank's pushes are queued behind the backward
-            if self._gather_event is not None:
-                self._peer_stream.wait_event(self._gather_event)
-            with torch.cuda.stream(self._peer_stream):
-                self.peer.owner_sum(self.peer.staging_P, self._meta_all)
+            if not self._owner_sum_queued:         # not started beside the backward: run it behind it (same result, nothing hidden)
+                self._queue_owner_sum(dense_grads[0].device)
+            self._owner_sum_queued = False
             return
         if self.peer is not None:
             lo = min(t.data_ptr() for t in dense_grads)

@@ -1,6 +1,7 @@
 """The fused view-parallel gradient exchange: the preprocess-stage backward pushes the 11 dense floats of every
-visible Gaussian into the OWNER rank's staging area (gsr_grads.push_*), gsr_peer_owner_sum adds the staged rows in rank order and
-delivers the totals to every rank.  Exercised on ONE device: the `world` rank buffers all live on cuda:0 and each "rank" runs on
+Gaussian (zeros where it is not visible) into the OWNER rank's staging area and publishes each 256-Gaussian block
+(gsr_grads.push_*); gsr_peer_owner_sum follows the ready words, adds the staged rows in rank order and delivers the totals to
+every rank.  Exercised on ONE device: the `world` rank buffers all live on cuda:0 and each "rank" runs on
 its own stream -- the kernels only see a table of base pointers, so this is the code path of the multi-GPU run
 (tests/test_gpu_peer_multi.py and bench.py's packed_rows_fused_push variant run it across real devices).
 
@@ -31,25 +32,49 @@ def _backward(d, camd, cam, dpix, radii, gb, N, bb, ib, **kw):
         camd.full_proj_transform, cam.tanfovx, cam.tanfovy, dpix, d["shs"], d["sh_degree"], camd.camera_center, gb, N, bb, ib, False, **kw)
 
 
-@pytest.mark.parametrize("world", [1, 2, 3, 8])
-def test_pushed_rows_plus_owner_sum_equal_the_rank_ordered_sum(world, cuda_device):
+def _setup(world, P, dev, lib):
+    P4 = (P + 3) // 4 * 4
+    rows = ((P + 255) // 256 + world - 1) // world * 256           # 256-Gaussian blocks dealt round-robin to the ranks
+    numel = 11 * P4
+    staging = world * rows * 12
+    ready = (world * (rows // 256) + 63) // 64 * 64
+    fb = int(lib.gsr_peer_flag_bytes(world))
+    bufs = [torch.full((numel + staging + ready + fb // 4,), float("nan"), dtype=torch.float32, device=dev) for _ in range(world)]
+    for b in bufs:
+        b[numel + staging:].zero_()
+    bases = torch.tensor([b.data_ptr() for b in bufs], dtype=torch.int64, device=dev)
+    return P4, rows, numel, staging, ready, bufs, bases
+
+
+def _owner_sum(lib, _capi, bases, numel, staging, ready, P, rows, world, r, epoch, stream, ctas=0):
+    _capi.check(lib.gsr_peer_owner_sum(C.c_void_p(bases.data_ptr()), None, numel * 4, 0, (numel + staging) * 4, P, rows,
+                                       (numel + staging + ready) * 4, world, r, epoch, ctas, C.c_void_p(stream.cuda_stream)),
+                "gsr_peer_owner_sum")
+
+
+@pytest.mark.parametrize("world,consumer_first", [(1, False), (2, False), (3, True), (8, False), (4, True)])
+def test_pushed_rows_plus_owner_sum_equal_the_rank_ordered_sum(world, consumer_first, cuda_device):
+    """consumer_first: the owner sums are queued BEFORE the backward passes that push (their own streams), as in the training step
+    -- they wait on the ready words and follow the producers block by block."""
     from gaussian_splatting_with_eye_tracking_b200 import _capi, _host
     lib = _capi.lib
     dev = cuda_device
     sc, _ = common.make_case("small")
     P = sc["means3D"].shape[0]
-    P4 = (P + 3) // 4 * 4
-    rows = ((P + 255) // 256 + world - 1) // world * 256           # 256-Gaussian blocks dealt round-robin to the ranks
-    numel = 11 * P4
-    staging = world * rows * 12
-    fb = int(lib.gsr_peer_flag_bytes(world))
-    bufs = [torch.full((numel + staging + fb // 4,), float("nan"), dtype=torch.float32, device=dev) for _ in range(world)]
-    for b in bufs:
-        b[numel + staging:].zero_()
-    bases = torch.tensor([b.data_ptr() for b in bufs], dtype=torch.int64, device=dev)
-    W32 = (P + 31) // 32
-    masks = torch.zeros((world, W32 + 3), dtype=torch.int32, device=dev)
+    P4, rows, numel, staging, ready, bufs, bases = _setup(world, P, dev, lib)
+    epoch = 5
+    streams = [torch.cuda.Stream(device=dev) for _ in range(world)]
     want = [torch.zeros(P, 3), torch.zeros(P, 1), torch.zeros(P, 3), torch.zeros(P, 4)]
+    if consumer_first:                         # every kernel of the pass has been launched once before a consumer spins beside it
+        d, camd = common.cuda_inputs(sc, _views(world)[0], dev)
+        cam0 = _views(world)[0]
+        N, img, radii, gb, bb, ib = _host.rasterize_gaussians(*common.fwd_args(d, camd), False)
+        _backward(d, camd, cam0, common.upstream_gradient(cam0, seed=1).to(dev), radii, gb, N, bb, ib)[3].cpu()
+        _capi.check(lib.gsr_set_option(6, 20000), "gsr_set_option")        # a protocol bug fails in 20 s, not 10 min
+    torch.cuda.synchronize()
+    if consumer_first:
+        for r in range(world):
+            _owner_sum(lib, _capi, bases, numel, staging, ready, P, rows, world, r, epoch, streams[r], ctas=2)
     for r, cam in enumerate(_views(world)):
         d, camd = common.cuda_inputs(sc, cam, dev)
         dpix = common.upstream_gradient(cam, seed=3003 + r).to(dev)
@@ -57,19 +82,14 @@ def test_pushed_rows_plus_owner_sum_equal_the_rank_ordered_sum(world, cuda_devic
         ref = _backward(d, camd, cam, dpix, radii, gb, N, bb, ib)
         for acc, k in zip(want, (3, 2, 6, 7)):
             acc += ref[k].cpu().reshape(acc.shape)              # rank order, float32
-        vis = (radii > 0).cpu().numpy()
-        bits = np.zeros(W32 * 32, dtype=np.uint8); bits[:P] = vis
-        masks[r, :W32] = torch.from_numpy(np.packbits(bits.reshape(-1, 32)[:, ::-1], axis=1).view(">u4").astype(np.uint32).view(np.int32).reshape(-1)).to(dev)
         _backward(d, camd, cam, dpix, radii, gb, N, bb, ib, dense_out=bufs[r][:numel],
-                  push=(bases.data_ptr(), numel * 4, r, world, rows))
+                  push=(bases.data_ptr(), numel * 4, r, world, rows, epoch, (numel + staging) * 4))
+    if not consumer_first:
+        torch.cuda.synchronize()
+        for r in range(world):
+            _owner_sum(lib, _capi, bases, numel, staging, ready, P, rows, world, r, epoch, streams[r])
     torch.cuda.synchronize()
-    streams = [torch.cuda.Stream(device=dev) for _ in range(world)]
-    for r in range(world):
-        with torch.cuda.stream(streams[r]):
-            _capi.check(lib.gsr_peer_owner_sum(C.c_void_p(bases.data_ptr()), None, numel * 4, 0, P, rows, C.c_void_p(masks.data_ptr()),
-                                               masks.shape[1], (numel + staging) * 4, world, r, 1, C.c_void_p(streams[r].cuda_stream)),
-                        "gsr_peer_owner_sum")
-    torch.cuda.synchronize()
+    _capi.check(lib.gsr_set_option(6, 0), "gsr_set_option")
     assert lib.gsr_peer_error() == 0
     for b in bufs:
         flat = b[:numel].cpu()
@@ -82,21 +102,38 @@ def test_pushed_rows_plus_owner_sum_equal_the_rank_ordered_sum(world, cuda_devic
     # every rank holds the SAME bits
     for b in bufs[1:]:
         assert torch.equal(b[:numel], bufs[0][:numel])
-    # and the sum is exactly the rank-ordered float32 sum of what was staged
-    P4_ = P4
-    stag = [b[numel:numel + staging].view(world, rows, 12).cpu() for b in bufs]        # stag[owner][src rank][local row]
-    mk = masks[:, :W32].cpu().numpy().view(np.uint32)
-    vis = np.stack([np.unpackbits(mk[r].view(np.uint8).reshape(-1, 4)[:, ::-1], axis=1).reshape(-1, 32)[:, ::-1].reshape(-1)[:P] for r in range(world)])
+    # and the sum is exactly the rank-ordered float32 sum of what was staged, for all four arrays
+    stag = [b[numel:numel + world * rows * 12].view(world, rows, 12).cpu() for b in bufs]        # stag[owner][src rank][local row]
     flat0 = bufs[0][:numel].cpu()
-    m3 = flat0[0:3 * P].view(P, 3)
-    for idx in range(0, P, max(1, P // 257)):
+    m3, op = flat0[0:3 * P].view(P, 3), flat0[3 * P4:3 * P4 + P]
+    s3, r4 = flat0[4 * P4:4 * P4 + 3 * P].view(P, 3), flat0[7 * P4:7 * P4 + 4 * P].view(P, 4)
+    for idx in list(range(0, P, max(1, P // 257))) + [P - 1]:
         blk = idx // 256
         owner, local = blk % world, (blk // world) * 256 + idx % 256
-        acc = torch.zeros(3)
+        acc = torch.zeros(12)
         for r in range(world):
-            if vis[r, idx]:
-                acc = acc + stag[owner][r, local, 0:3]
-        assert torch.equal(m3[idx], acc), idx
+            acc = acc + stag[owner][r, local]
+        assert torch.equal(m3[idx], acc[0:3]) and torch.equal(op[idx], acc[3]) and torch.equal(s3[idx], acc[4:7]) and torch.equal(r4[idx], acc[7:11]), idx
+
+
+def test_owner_sum_watchdog_poisons_a_block_that_never_arrives(cuda_device):
+    """A rank that never pushes: the owner's totals are NaN after the (shortened) watchdog time and gsr_peer_error() reports it."""
+    from gaussian_splatting_with_eye_tracking_b200 import _capi
+    lib = _capi.lib
+    dev = cuda_device
+    P, world = 1000, 1
+    P4, rows, numel, staging, ready, bufs, bases = _setup(world, P, dev, lib)
+    st = torch.cuda.Stream(device=dev)
+    _capi.check(lib.gsr_set_option(6, 200), "gsr_set_option")
+    try:
+        lib.gsr_peer_error()
+        _owner_sum(lib, _capi, bases, numel, staging, ready, P, rows, world, 0, 3, st)
+        st.synchronize()
+        assert lib.gsr_peer_error() == 1
+        assert bool(torch.isnan(bufs[0][:numel]).all())
+    finally:
+        _capi.check(lib.gsr_set_option(6, 0), "gsr_set_option")
+        lib.gsr_peer_error()
 
 
 def test_fused_exchange_through_the_host_classes_single_rank(cuda_device):
@@ -112,10 +149,11 @@ def test_fused_exchange_through_the_host_classes_single_rank(cuda_device):
     ref = _backward(d, camd, cam, dpix, radii, gb, N, bb, ib)
     peer = gdist.PeerAllReduce(11 * ((P + 3) // 4 * 4), dev, staging_gaussians=P)
     exch = gdist.ShGradExchange(packed=True, peer=peer, fused=True)
-    for _ in range(2):                                         # twice: epochs advance, buffers are reused
+    for _ in range(4):                                         # epochs advance, buffers are reused; steps 3+ stream beside the backward
         exch.post_visible_count(_host.last_counts(gb, P)[2], dev)
         g = _backward(d, camd, cam, dpix, radii, gb, N, bb, ib, compact_sh=True,
-                      between_phases=lambda drgb: exch.start_gather(drgb, camd.camera_center, d["means3D"], d["sh_degree"], M, radii=radii),
+                      between_phases=lambda drgb: (exch.start_owner_sum(dev),
+                                                   exch.start_gather(drgb, camd.camera_center, d["means3D"], d["sh_degree"], M, radii=radii)),
                       dense_out=peer.data, push=peer.push_args)
         exch.start_reduce([g[3], g[2], g[6], g[7]])
         dsh = exch.finish()

@@ -26,6 +26,8 @@ def main():
     ap.add_argument("--iters", type=int, default=5)
     a = ap.parse_args()
     rank, world = gdist.init()
+    from gaussian_splatting_with_eye_tracking_b200 import _capi
+    _capi.check(_capi.lib.gsr_set_option(6, 30000), "gsr_set_option")      # peer watchdog: a protocol bug fails in 30 s, not 10 min
     dev = torch.device("cuda", int(os.environ.get("LOCAL_RANK", rank)))
     sc = scenes.make_unbounded_scene(P=a.gaussians, seed=2002)
     d = {k: (v.to(dev).contiguous() if isinstance(v, torch.Tensor) else v) for k, v in sc.items()}
@@ -55,20 +57,50 @@ def main():
             acc += t
         want.append(acc)
 
+    # the single-rank step the efficiency is quoted against: forward + the plain backward, no exchange
+    for _ in range(2):
+        N, img, radii, gb, bb, ib = fwd(); bwd(N, radii, gb, bb, ib)
+    torch.cuda.synchronize(); dist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(a.iters):
+        N, img, radii, gb, bb, ib = fwd(); bwd(N, radii, gb, bb, ib)
+    e1.record(); e1.synchronize()
+    n1 = torch.tensor([e0.elapsed_time(e1) / a.iters], device=dev)
+    dist.all_reduce(n1, op=dist.ReduceOp.MAX)
     peer = gdist.PeerAllReduce(11 * ((P + 3) // 4 * 4), dev, staging_gaussians=P)
     variants = {"fused_push": dict(fused=True, peer=peer), "peer_sum": dict(fused=False, peer=peer), "nccl_sum": dict(fused=False, peer=None)}
-    out = {"world": world, "gaussians": P, "multicast": bool(peer.multicast_ptr)}
+    out = {"world": world, "gaussians": P, "multicast": bool(peer.multicast_ptr), "no_exchange_ms_per_step": round(float(n1), 4)}
     for name, kw in variants.items():
         exch = gdist.ShGradExchange(packed=True, **kw)
 
-        def step():
+        def step(tl=None):
+            def mark(name, stream=None):
+                if tl is not None:
+                    ev = torch.cuda.Event(enable_timing=True)
+                    ev.record(stream if stream is not None else torch.cuda.current_stream())
+                    tl.append((name, ev))
+            mark("start")
             N, img, radii, gb, bb, ib = fwd()
+            mark("forward_done")
             exch.post_visible_count(_host.last_counts(gb, P)[2], dev)
-            gr = bwd(N, radii, gb, bb, ib, compact_sh=True,
-                     between_phases=lambda drgb: exch.start_gather(drgb, cam.camera_center, d["means3D"], d["sh_degree"], M, radii=radii),
+
+            def between(drgb):
+                mark("blend_bwd_done")
+                if kw["fused"]:
+                    exch.start_owner_sum(dev)          # the streaming owner sum runs beside the preprocess-stage backward
+                exch.start_gather(drgb, cam.camera_center, d["means3D"], d["sh_degree"], M, radii=radii)
+                mark("row_gather_done", exch._stream)
+            gr = bwd(N, radii, gb, bb, ib, compact_sh=True, between_phases=between,
                      dense_out=peer.data if kw["peer"] is not None else None, push=peer.push_args if kw["fused"] else None)
+            mark("preprocess_bwd_done")
             exch.start_reduce([gr[3], gr[2], gr[6], gr[7]])
-            dsh = exch.finish()
+            if exch._peer_stream is not None and kw["peer"] is not None:
+                mark("dense_sum_done", exch._peer_stream)
+            dsh = exch.finish_sh()
+            mark("sh_rebuild_done")
+            exch.finish_dense()
+            mark("end")
             return gr, dsh
         gr, dsh = step()
         torch.cuda.synchronize()
@@ -89,6 +121,13 @@ def main():
         e1.record(); e1.synchronize()
         t = torch.tensor([e0.elapsed_time(e1) / a.iters], device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        tl = []
+        step(tl)
+        torch.cuda.synchronize()
+        timeline = {nm: round(tl[0][1].elapsed_time(ev), 4) for nm, ev in tl[1:]}
+        allt = [None] * world
+        dist.all_gather_object(allt, timeline)
+        out[name + "_timeline_ms_per_rank"] = allt if world <= 2 else [allt[0], allt[world // 2], allt[-1]]
         out[name] = {"dense_equals_rank_ordered_sum_bitwise": exact, "dense_max_rel_diff": close, "same_on_all_ranks": all(float(c) == float(allchk[0]) for c in allchk),
                      "sh_max_rel_diff": sh_err, "ms_per_step": round(float(t), 4)}
     out["peer_error_word"] = int(__import__("gaussian_splatting_with_eye_tracking_b200._capi", fromlist=["lib"]).lib.gsr_peer_error())
