@@ -50,7 +50,7 @@ class GsrGrads(C.Structure):
         "dL_dmeans2D", "dL_dcolors", "dL_dopacity", "dL_dmeans3D", "dL_dcov3D", "dL_dsh", "dL_dscales",
         "dL_drotations", "dL_dconic", "scratch", "dL_dcolors_clamped")] + [
         ("push_bases", C.c_void_p), ("push_offset", C.c_size_t), ("push_rank", C.c_int), ("push_world", C.c_int),
-        ("push_rows_per_rank", C.c_int), ("push_epoch", C.c_uint), ("push_ready_offset", C.c_size_t)]
+        ("push_rows_per_rank", C.c_int), ("push_epoch", C.c_uint)]
 
 
 class GsrAdamTensor(C.Structure):
@@ -119,7 +119,7 @@ SYMBOLS = {
     "gsr_pack_rgb8": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
     "gsr_peer_flag_bytes": (C.c_size_t, [C.c_int]),
     "gsr_peer_barrier": (C.c_int, [C.c_void_p, C.c_size_t, C.c_int, C.c_int, C.c_uint, C.c_void_p]),
-    "gsr_peer_owner_sum": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t, C.c_size_t, C.c_int, C.c_int, C.c_size_t,
+    "gsr_peer_owner_sum": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t, C.c_int, C.c_int, C.c_size_t,
                                      C.c_int, C.c_int, C.c_uint, C.c_int, C.c_void_p]),
     "gsr_peer_error": (C.c_int, []),
     "gsr_peer_allreduce_sum": (C.c_int, [C.c_void_p, C.c_size_t, C.c_longlong, C.c_size_t, C.c_int, C.c_int, C.c_uint, C.c_void_p]),

@@ -182,9 +182,9 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
     ``dense_out``: caller-owned float32 buffer of at least 11 * ceil4(P) elements that receives the four dense gradients
     (means3D, opacity, scales, rotations, back to back) instead of a fresh allocation -- a view-parallel caller passes
     peer-mapped memory here so that dist.PeerAllReduce sums them in place over NVLink.
-    ``push`` = (peer_bases_dev_ptr, staging_offset_bytes, rank, world, rows_per_rank, epoch, ready_offset_bytes)
+    ``push`` = (peer_bases_dev_ptr, staging_offset_bytes, rank, world, rows_per_rank, epoch)
     (= dist.PeerAllReduce.push_args): fused exchange (gsr_grads.push_*) -- the preprocess stage stores the 11 dense floats of
-    every Gaussian into the OWNER rank's staging area instead of writing the four dense tensors and publishes each block;
+    every Gaussian into the OWNER rank's staging area (self-validating 128-byte lines) instead of writing the four dense tensors;
     dist.PeerAllReduce.owner_sum, queued beside it, fills them (in ``dense_out``) on every rank."""
     H, W = int(dL_dout_color.size(1)), int(dL_dout_color.size(2))
     sc, cam, keep, P, M = _scene_camera(background, means3D, colors, torch.empty(0), scales, rotations, scale_modifier,
@@ -226,8 +226,7 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
             if push is not None:
                 grads.push_bases = C.c_void_p(int(push[0])); grads.push_offset = int(push[1]); grads.push_rank = int(push[2])
                 grads.push_world = int(push[3]); grads.push_rows_per_rank = int(push[4])
-                if len(push) > 5:
-                    grads.push_epoch = int(push[5]) & 0xffffffff; grads.push_ready_offset = int(push[6])
+                grads.push_epoch = int(push[5]) & 0xffffffff
             bufs = (_p(geomBuffer.contiguous()), _p(binningBuffer.contiguous()), _p(imageBuffer.contiguous()))
             if compact and between_phases is not None:
                 rc = lib.gsr_backward_phase(C.byref(sc), C.byref(cam), _p(radii_t), *bufs, int(R), _p(dpix), C.byref(grads),

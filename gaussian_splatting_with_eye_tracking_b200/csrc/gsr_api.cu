@@ -429,7 +429,7 @@ static int backward_impl(const gsr_scene* sc, const gsr_camera* cam, const int* 
         set_error("raw-parameter backward needs M in {4, 8, 12, 16} and a 16-byte aligned dL_dsh (M = %d)", sc->sh_coeffs); return GSR_ERR_INVALID;
     }
     if (gr->push_bases && (gr->push_world < 1 || gr->push_rank < 0 || gr->push_rank >= gr->push_world || gr->push_rows_per_rank <= 0 ||
-                           (gr->push_rows_per_rank % 256) != 0 || (gr->push_offset & 15) != 0 || (gr->push_ready_offset & 3) != 0 ||
+                           (gr->push_rows_per_rank % 256) != 0 || (gr->push_offset & 127) != 0 || gr->push_epoch == 0 ||
                            (long long)gr->push_rows_per_rank * gr->push_world < (long long)P)) {
         set_error("bad push_* fields (world %d, rank %d, rows per rank %d for P = %d)", gr->push_world, gr->push_rank, gr->push_rows_per_rank, P);
         return GSR_ERR_INVALID;

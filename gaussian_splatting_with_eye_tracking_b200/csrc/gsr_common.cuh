@@ -35,6 +35,11 @@ __host__ __device__ inline size_t sort_temp_bytes(long long n) {
 }
 
 // ---------------------------------------------------------------- geometry buffer
+// fused gradient exchange (gsr_grads.push_*): a 256-Gaussian block travels as 94 lines of 128 bytes (30 floats + 2 flag words)
+// in a slot of 96 lines = 768 float4 = 12 KB
+constexpr int kPushLines = 94;
+constexpr int kPushSlotF4 = 768;
+
 struct GeomHeader {      // lives at the start of the (aligned) geometry buffer, device memory
     uint32_t magic;
     uint32_t P;

@@ -157,16 +157,16 @@ uint32_t* peer_error_word() {
 }
 
 // ---- fused exchange, second half (gsr_peer_owner_sum): a STREAMING consumer.  It runs beside preprocess_bwd_kernel (its own
-// stream, a few dozen resident CTAs) and follows it block by block: a 256-Gaussian block is summed the moment the `world` ranks
-// have staged it -- each producer CTA publishes (fence + release store) a ready word per block at the owner -- and the totals
-// leave for every rank at once.  When the producers finish only the last few blocks and the closing barrier are exposed.
-// A CTA reads a block's world x 12 KB of staged rows as whole 128-bit coalesced runs, adds them in rank order (the same float
+// stream, a few dozen resident CTAs) and follows it block by block.  A 256-Gaussian block travels as 94 self-validating 128-byte
+// lines (30 floats + a 2-word epoch flag, written whole by 8 lanes of one store: see the producer): a CTA loads line e of the
+// block from all `world` slots, re-loads the ones whose flag is not this epoch yet, adds them in rank order (the same float
 // expression on every run, so every rank receives the SAME bits; rows of invisible Gaussians were staged as zeros, exactly the
-// terms the dense per-view tensors hold), transposes the [256][12] totals through shared memory and writes every array of the
-// dense block with 128-bit stores: means3D 3 x float4 per 4 Gaussians, opacity 1, scales 3, rotations 4.
+// terms the dense per-view tensors hold), gathers the [256][11] totals in shared memory and writes every array of the dense
+// block with 128-bit stores: means3D 3 x float4 per 4 Gaussians, opacity 1, scales 3, rotations 4 -- to all ranks at once.
+// When the producers finish only the last few blocks and the closing barrier are exposed.
 struct OwnerSumParams {
     char* const* bases; float* mc;            // mc != nullptr: multicast mapping of the buffers (one multimem.st per value)
-    size_t staging_offset, final_offset, ready_offset, flag_offset;
+    size_t staging_offset, final_offset, flag_offset;
     int P4, rows_per_rank, world, rank;
     uint32_t epoch; long long timeout_ns; uint32_t* host_err;
 };
@@ -181,78 +181,101 @@ __device__ __forceinline__ void deliver(const OwnerSumParams& p, size_t float_in
     }
 }
 
+__device__ __forceinline__ float4 ld_line_piece(const float4* p) {
+    float4 v;
+    asm volatile("ld.volatile.global.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+    return v;
+}
+
 template <bool MC>
 __global__ void __launch_bounds__(kPeerThreads) peer_owner_sum_kernel(const OwnerSumParams p) {
-    __shared__ float4 s_tot[3 * 256];           // the block's totals, row-major [256 Gaussians][12 floats]
+    __shared__ float s_f[2816 + 8];             // the block's totals, [256 Gaussians][11 floats]
     __shared__ int s_bad;
-    const float* s_f = reinterpret_cast<const float*>(s_tot);
-    const int tid = threadIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31;
     const float nanv = __int_as_float(0x7fc00000);
     const float4* staging = reinterpret_cast<const float4*>(p.bases[p.rank] + p.staging_offset);
-    const uint32_t* ready = reinterpret_cast<const uint32_t*>(p.bases[p.rank] + p.ready_offset);
     uint32_t* mine = reinterpret_cast<uint32_t*>(p.bases[p.rank] + p.flag_offset);
     const size_t P4 = (size_t)p.P4;
     const int nblk = p.rows_per_rank >> 8;
     if (tid == 0) s_bad = 0;
+    bool bad = false;                           // this warp's watchdog fired: it stops waiting for good
     // this rank owns the 256-Gaussian blocks rank, rank + world, rank + 2 world, ... (block-cyclic, see preprocess_bwd_kernel);
     // local block j <-> Gaussians ((j * world + rank) * 256 ...)
     for (int j = blockIdx.x; j < nblk; j += gridDim.x) {
         const long long idx0 = ((long long)j * p.world + p.rank) << 8;
         if (idx0 >= (long long)P4) break;
-        __syncthreads();                                                  // s_tot / s_bad of the previous block are free
-        if (tid < p.world) {                                              // thread k waits for rank k's copy of block j
-            const uint32_t* w = ready + (size_t)tid * nblk + j;
-            unsigned long long t0 = 0;
-            unsigned spins = 0;
-            while ((int32_t)(ld_acquire_sys(w) - p.epoch) < 0) {
-                if ((++spins & 255u) == 0u) {
-                    unsigned long long t1;
-                    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
-                    if (t0 == 0) t0 = t1;
-                    else if ((long long)(t1 - t0) > p.timeout_ns) {      // never a silent sum of stale rows (see peer_barrier_kernel)
-                        mine[p.world] = 1u;
-                        if (p.host_err) { *((volatile uint32_t*)p.host_err) = 1u; __threadfence_system(); }
-                        s_bad = 1;
-                        break;
+        __syncthreads();                                                  // s_f of the previous block has been read
+        for (int e0 = 0; e0 < kPushLines * 8; e0 += kPeerThreads) {       // whole warps stay: the line votes are warp-wide
+            const int e = e0 + tid;
+            const bool act = e < kPushLines * 8;
+            const bool flag_lane = (lane & 7) == 7;
+            const float4* src = staging + (size_t)j * kPushSlotF4 + (act ? e : 0);
+            const size_t slot = (size_t)nblk * kPushSlotF4;               // float4s between two ranks' copies of the block
+            float4 v[kMaxPeers];
+#pragma unroll
+            for (int k = 0; k < kMaxPeers; ++k)
+                if (k < p.world) v[k] = ld_line_piece(src + k * slot);
+            float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+            for (int k = 0; k < kMaxPeers; ++k) {
+                if (k >= p.world) break;
+                // a line is valid when the flag its 8th piece carries is this epoch; the 8 pieces come from ONE load instruction
+                unsigned long long t0 = 0;
+                unsigned spins = 0;
+                for (;;) {
+                    const bool ok = !act || !flag_lane || (__float_as_uint(v[k].z) == p.epoch && __float_as_uint(v[k].w) == p.epoch);
+                    if (__all_sync(0xffffffffu, ok) || bad) break;
+                    if ((++spins & 63u) == 0u) {
+                        unsigned long long t1;
+                        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+                        if (t0 == 0) t0 = t1;
+                        else if ((long long)(t1 - t0) > p.timeout_ns) bad = true;      // never a silent sum of stale rows
                     }
+                    bad = __any_sync(0xffffffffu, bad);
+                    if (bad) break;
+                    __nanosleep(500);
+                    v[k] = ld_line_piece(src + k * slot);                  // the whole warp re-loads: pieces and flag stay one load
                 }
-                __nanosleep(200);
+                acc.x += v[k].x; acc.y += v[k].y; acc.z += v[k].z; acc.w += v[k].w;      // rank order
+            }
+            if (bad && lane == 0) {
+                mine[p.world] = 1u;
+                if (p.host_err) { *((volatile uint32_t*)p.host_err) = 1u; __threadfence_system(); }
+                s_bad = 1;
+            }
+            if (act) {
+                const int f0 = (e >> 3) * 30 + (e & 7) * 4;
+                s_f[f0] = acc.x; s_f[f0 + 1] = acc.y;                     // (the last line's tail lands in the 8 pad floats)
+                if (!flag_lane) { s_f[f0 + 2] = acc.z; s_f[f0 + 3] = acc.w; }
             }
         }
         __syncthreads();
         const bool poisoned = s_bad != 0 || ((volatile const uint32_t*)mine)[p.world] != 0u;
-#pragma unroll
-        for (int q = 0; q < 3; ++q) {
-            const int f = tid + q * kPeerThreads;                          // float4 f of the block's 768
-            const float4* src = staging + (size_t)j * 768 + f;
-            float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-            for (int k = 0; k < p.world; ++k) {                            // rank order
-                const float4 v = __ldcg(src + (size_t)k * p.rows_per_rank * 3);
-                acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
-            }
-            if (poisoned) acc = make_float4(nanv, nanv, nanv, nanv);
-            s_tot[f] = acc;
-        }
-        __syncthreads();
         // dense block: [means3D 3 x P4 | opacity P4 | scales 3 x P4 | rotations 4 x P4]; this block's n Gaussians (multiple of 4)
         const int n = (int)min((long long)256, (long long)P4 - idx0);
         const int n34 = 3 * n / 4, n4 = n / 4;
         const size_t i0 = (size_t)idx0;
         for (int t = tid; t < 2 * n34 + n4 + n; t += kPeerThreads) {
+            float4 o;
+            size_t at;
             if (t < 2 * n34) {                                             // means3D (columns 0..2) or scales (columns 4..6)
                 const bool sc = t >= n34;
                 const int m = sc ? t - n34 : t, c0 = sc ? 4 : 0;
                 float v[4];
 #pragma unroll
-                for (int e = 0; e < 4; ++e) { const int el = 4 * m + e; v[e] = s_f[(el / 3) * 12 + c0 + el % 3]; }
-                deliver<MC>(p, (sc ? 4 * P4 : 0) + 3 * i0 + 4 * (size_t)m, make_float4(v[0], v[1], v[2], v[3]));
+                for (int q = 0; q < 4; ++q) { const int el = 4 * m + q; v[q] = s_f[(el / 3) * 11 + c0 + el % 3]; }
+                o = make_float4(v[0], v[1], v[2], v[3]); at = (sc ? 4 * P4 : 0) + 3 * i0 + 4 * (size_t)m;
             } else if (t < 2 * n34 + n4) {                                 // opacity (column 3)
                 const int m = t - 2 * n34;
-                deliver<MC>(p, 3 * P4 + i0 + 4 * (size_t)m, make_float4(s_f[(4 * m) * 12 + 3], s_f[(4 * m + 1) * 12 + 3], s_f[(4 * m + 2) * 12 + 3], s_f[(4 * m + 3) * 12 + 3]));
+                o = make_float4(s_f[(4 * m) * 11 + 3], s_f[(4 * m + 1) * 11 + 3], s_f[(4 * m + 2) * 11 + 3], s_f[(4 * m + 3) * 11 + 3]);
+                at = 3 * P4 + i0 + 4 * (size_t)m;
             } else {                                                       // rotations (columns 7..10)
                 const int m = t - 2 * n34 - n4;
-                deliver<MC>(p, 7 * P4 + 4 * (i0 + m), make_float4(s_f[m * 12 + 7], s_f[m * 12 + 8], s_f[m * 12 + 9], s_f[m * 12 + 10]));
+                o = make_float4(s_f[m * 11 + 7], s_f[m * 11 + 8], s_f[m * 11 + 9], s_f[m * 11 + 10]);
+                at = 7 * P4 + 4 * (i0 + m);
             }
+            if (poisoned) o = make_float4(nanv, nanv, nanv, nanv);
+            deliver<MC>(p, at, o);
         }
     }
     __threadfence_system();
@@ -321,13 +344,13 @@ int gsr_peer_error(void) {
 }
 
 int gsr_peer_owner_sum(void* const* peer_bases, void* multicast_base, size_t staging_offset, size_t final_offset,
-                       size_t ready_offset, int P, int rows_per_rank, size_t flag_offset, int world, int rank, unsigned epoch,
+                       int P, int rows_per_rank, size_t flag_offset, int world, int rank, unsigned epoch,
                        int ctas, void* stream) {
     if (world < 1 || world > kMaxPeers || rank < 0 || rank >= world || !peer_bases) {
         set_error("peer_owner_sum: bad arguments (world %d, rank %d)", world, rank); return GSR_ERR_INVALID;
     }
     if (P < 0 || rows_per_rank <= 0 || (rows_per_rank % 256) != 0 || (long long)rows_per_rank * world < (long long)P ||
-        (staging_offset & 15) || (final_offset & 15) || (flag_offset & 3) || (ready_offset & 3) || ((uintptr_t)multicast_base & 15)) {
+        (staging_offset & 127) || (final_offset & 15) || (flag_offset & 3) || ((uintptr_t)multicast_base & 15) || epoch == 0) {
         set_error("peer_owner_sum: bad sizes / alignment (P %d, rows per rank %d)", P, rows_per_rank); return GSR_ERR_INVALID;
     }
     cudaStream_t s = (cudaStream_t)stream;
@@ -337,7 +360,7 @@ int gsr_peer_owner_sum(void* const* peer_bases, void* multicast_base, size_t sta
     peer_barrier_kernel<<<1, 32, 0, s>>>(bases, flag_offset, world, rank, epoch, peer_timeout_ns(), peer_error_word());
     OwnerSumParams p;
     p.bases = bases; p.mc = (float*)multicast_base; p.staging_offset = staging_offset; p.final_offset = final_offset;
-    p.ready_offset = ready_offset; p.flag_offset = flag_offset;
+    p.flag_offset = flag_offset;
     p.P4 = (P + 3) / 4 * 4; p.rows_per_rank = rows_per_rank; p.world = world; p.rank = rank;
     p.epoch = epoch; p.timeout_ns = peer_timeout_ns(); p.host_err = peer_error_word();
     const int mine = (int)((((long long)p.P4 + 255) / 256 + world - 1 - rank) / world);       // blocks this rank owns

@@ -483,7 +483,7 @@ struct PreBwdParams {
     float* dL_drgb_clamped;        // optional [P,3]; with dL_dsh == nullptr the SH rows are not written (gsr_grads)
     // fused view-parallel exchange (gsr_grads.push_*): rows of the 11 dense floats go to the owner rank's staging area
     char* const* push_bases; size_t push_offset; int push_rank, push_world, push_rows_per_rank;
-    uint32_t push_epoch; size_t push_ready_offset;
+    uint32_t push_epoch;
 };
 
 // SH rows are staged through shared memory (STAGED): a thread's 3M coefficients / gradients are 192 B apart from its
@@ -751,38 +751,33 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(const PreBwdParams 
         for (int i = 0; i < 6; ++i) p.dL_dcov3D[6 * (size_t)idx + i] = dcov[i];
     }
     if (pushing) {
-        // One 48-byte row per Gaussian into the owner's staging area (peer memory over NVLink).  Ownership is block-cyclic
+        // The CTA's 256 x 11 dense floats go to the rank that OWNS the block (peer memory over NVLink).  Ownership is block-cyclic
         // (256-Gaussian blocks dealt round-robin to the ranks): at any moment the CTAs in flight push to ALL owners at once;
         // contiguous slices would make every rank push to the same owner at the same time (7-to-1 incast on one GPU's ingress).
-        // A warp's 32 rows are consecutive at the owner: they are transposed through shared memory and leave as three fully
-        // contiguous 512-byte stores (per-lane 16-byte pieces 48 bytes apart travel as 96 small NVLink packets per warp: measured
-        // slower than the all-reduce they replace).  Rows of invisible Gaussians go out as zeros -- the terms the dense per-view
-        // tensors hold for them -- so the owner adds all ranks' rows unconditionally: whole lines, no masks, no read-modify-write.
-        const int blk = idx >> 8, owner = blk % p.push_world, local = ((blk / p.push_world) << 8) | (idx & 255);
-        const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
-        const float4 r0 = visible ? make_float4(dmx, dmy, dmz, sB.y) : z4;
-        const float4 r1 = visible ? make_float4(dscale[0], dscale[1], dscale[2], drot.x) : z4;
-        const float4 r2 = visible ? make_float4(drot.y, drot.z, drot.w, 0.f) : z4;
-        float4* row = reinterpret_cast<float4*>(p.push_bases[owner] + p.push_offset) + ((size_t)p.push_rank * p.push_rows_per_rank + local) * 3;
-        if (STAGED) {
-            float4* wrow = reinterpret_cast<float4*>(s_sh + wid * 32 * kShStride);      // the warp's SH staging rows are dead by now
-            __syncwarp();
-            wrow[3 * lane] = r0; wrow[3 * lane + 1] = r1; wrow[3 * lane + 2] = r2;
-            __syncwarp();
-            float4* dst = row - 3 * lane;
-#pragma unroll
-            for (int k = 0; k < 3; ++k) dst[k * 32 + lane] = wrow[k * 32 + lane];
-        } else {
-            row[0] = r0; row[1] = r1; row[2] = r2;
-        }
-        // publish the block: all 256 rows are out (bar.sync orders the other warps' stores before thread 0's fence; the fence is
-        // cumulative), then a release store of the epoch into this rank's ready word for the block at the owner
+        // Wire format = 128-byte LINES of 30 data floats + a 2-word flag (the epoch), each written by 8 lanes of one store
+        // instruction: a line arrives whole, so the owner validates every line by its own flag and no fence, ready word or kernel
+        // boundary is needed -- gsr_peer_owner_sum consumes the block while this kernel is still running.  (A fence.sys + ready
+        // word per CTA was measured first: the fence drains the SM's whole memory pipeline, 0.72 -> 1.53 ms for the kernel.)
+        // Rows of invisible Gaussians are zeros -- the terms the dense per-view tensors hold for them -- so the owner adds all
+        // ranks' lines unconditionally: no masks, no read-modify-write.  94 lines (2816 floats) per block in a 12 KB slot.
+        const int blk = blockIdx.x + p.block0, owner = blk % p.push_world;
+        float* brow = s_sh;                                                 // [256][11]; the SH staging rows are dead by now
         __syncthreads();
-        if (tid == 0 && p.push_ready_offset != 0) {
-            __threadfence_system();
-            uint32_t* w = reinterpret_cast<uint32_t*>(p.push_bases[owner] + p.push_ready_offset) +
-                          (size_t)p.push_rank * (p.push_rows_per_rank >> 8) + blk / p.push_world;
-            asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(w), "r"(p.push_epoch) : "memory");
+        float* r = brow + tid * 11;
+        r[0] = visible ? dmx : 0.f; r[1] = visible ? dmy : 0.f; r[2] = visible ? dmz : 0.f; r[3] = visible ? sB.y : 0.f;
+        r[4] = visible ? dscale[0] : 0.f; r[5] = visible ? dscale[1] : 0.f; r[6] = visible ? dscale[2] : 0.f;
+        r[7] = visible ? drot.x : 0.f; r[8] = visible ? drot.y : 0.f; r[9] = visible ? drot.z : 0.f; r[10] = visible ? drot.w : 0.f;
+        __syncthreads();
+        float4* dst = reinterpret_cast<float4*>(p.push_bases[owner] + p.push_offset) +
+                      ((size_t)p.push_rank * (p.push_rows_per_rank >> 8) + blk / p.push_world) * kPushSlotF4;
+        const float flag = __uint_as_float(p.push_epoch);
+        for (int e = tid; e < kPushLines * 8; e += 256) {
+            const int f0 = (e >> 3) * 30 + (e & 7) * 4;                     // first data float of this 16-byte piece
+            float4 v;
+            v.x = f0 < 2816 ? brow[f0] : 0.f; v.y = f0 + 1 < 2816 ? brow[f0 + 1] : 0.f;
+            if ((e & 7) == 7) { v.z = flag; v.w = flag; }
+            else { v.z = f0 + 2 < 2816 ? brow[f0 + 2] : 0.f; v.w = f0 + 3 < 2816 ? brow[f0 + 3] : 0.f; }
+            dst[e] = v;
         }
         return;
     }
@@ -818,7 +813,7 @@ void launch_preprocess_backward(const PreBwdArgs& a, cudaStream_t s) {
     p.dL_drgb_clamped = a.out.dL_dcolors_clamped;
     p.push_bases = (char* const*)a.out.push_bases; p.push_offset = a.out.push_offset; p.push_rank = a.out.push_rank;
     p.push_rows_per_rank = a.out.push_rows_per_rank; p.push_world = a.out.push_world > 0 ? a.out.push_world : 1;
-    p.push_epoch = a.out.push_epoch; p.push_ready_offset = a.out.push_ready_offset;
+    p.push_epoch = a.out.push_epoch;
     // staged SH path: needs M % 4 == 0 (128-bit rows), M <= 16 (row fits the staged stride) and 16 B-aligned tensors
     const bool staged = (p.dL_dsh != nullptr || p.colors_from_sh) && p.M > 0 && p.M <= 16 && (p.M % 4) == 0 && ((size_t)p.dL_dsh & 15) == 0 &&
                         (!p.colors_from_sh || p.shs_rest != nullptr || ((size_t)p.shs & 15) == 0);
@@ -828,7 +823,7 @@ void launch_preprocess_backward(const PreBwdArgs& a, cudaStream_t s) {
         if (!attr_done) { cudaFuncSetAttribute(preprocess_bwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem); attr_done = true; }
         preprocess_bwd_kernel<true><<<(end - first + 255) / 256, 256, smem, s>>>(p);
     } else {
-        preprocess_bwd_kernel<false><<<(end - first + 255) / 256, 256, 0, s>>>(p);
+        preprocess_bwd_kernel<false><<<(end - first + 255) / 256, 256, p.push_bases ? 256 * 11 * (int)sizeof(float) : 0, s>>>(p);
     }
     count_launch();
 }

@@ -199,9 +199,8 @@ class PeerAllReduce:
         self.staging_P = int(staging_gaussians)
         nblk = (self.staging_P + 255) // 256
         self.rows_per_rank = (nblk + self.world - 1) // self.world * 256 if self.staging_P else 0      # 256-blocks dealt round-robin
-        # staging rows, then one ready word per (source rank, owned block), rounded to 64 words
-        self.ready_words = (self.world * (self.rows_per_rank // 256) + 63) // 64 * 64 if self.staging_P else 0
-        self.staging_floats = self.world * self.rows_per_rank * 12 + self.ready_words
+        self.numel = (self.numel + 31) // 32 * 32 if self.staging_P else self.numel       # the staging slots are 128-byte aligned
+        self.staging_floats = self.world * self.rows_per_rank * 12                          # a 12 KB slot per (rank, owned block)
         total = self.numel + self.staging_floats + self.flag_bytes // 4
         dev = torch.device(device)
         if self.world > 1:
@@ -225,7 +224,7 @@ class PeerAllReduce:
             self.bases_dev = self._bases_keep.data_ptr()
             self.hdl = None
             self.multicast_ptr = 0
-        self.buf[self.numel + self.staging_floats - self.ready_words:].zero_()   # ready + flag words: zero on every rank before anyone signals
+        self.buf[self.numel:].zero_()                # staging lines (flag 0 = never valid) and flag words: zero before anyone signals
         torch.cuda.synchronize(dev)
         if self.world > 1:
             dist.barrier(group)
@@ -258,21 +257,17 @@ class PeerAllReduce:
         return (self.numel + self.staging_floats) * 4
 
     @property
-    def ready_offset(self) -> int:
-        return (self.numel + self.world * self.rows_per_rank * 12) * 4
-
-    @property
     def push_args(self):
         """What ``_host.rasterize_gaussians_backward(..., push=...)`` needs: (peer base table, staging offset, rank, world, rows per
-        rank, epoch, ready-word offset).  The epoch is the one the NEXT ``owner_sum`` call waits for: read this, queue owner_sum,
-        run the backward -- no other exchange on this object in between."""
+        rank, epoch).  The epoch is the one the NEXT ``owner_sum`` call waits for: read this, queue owner_sum, run the
+        backward -- no other exchange on this object in between."""
         if not self.rows_per_rank:
             raise RuntimeError("PeerAllReduce was built without a staging area (staging_gaussians=P)")
-        return (self.bases_dev, self.numel * 4, self.rank, self.world, self.rows_per_rank, self.epoch, self.ready_offset)
+        return (self.bases_dev, self.numel * 4, self.rank, self.world, self.rows_per_rank, self.epoch)
 
     def owner_sum(self, P: int, ctas: int = 0) -> None:
         """Second half of the fused exchange, queued on the CURRENT stream (gsr_peer_owner_sum): barrier, then this rank follows the
-        ready words of the blocks it owns, sums every block's staged rows in rank order as soon as all ranks have pushed it and
+        blocks it owns, sums every block's staged lines in rank order as soon as all ranks have pushed them and
         writes the totals into the dense block at the start of EVERY rank's ``data``, barrier.  Queue it on a side stream BEFORE
         the backward that pushes (``push_args``): it then runs beside that kernel and only the last blocks remain after it."""
         import ctypes as C
@@ -282,7 +277,7 @@ class PeerAllReduce:
         with torch.cuda.device(self.buf.device):
             st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
             check(self._lib.gsr_peer_owner_sum(C.c_void_p(self.bases_dev), C.c_void_p(self.multicast_ptr) if self.multicast_ptr else None,
-                                               self.numel * 4, 0, self.ready_offset, int(P), self.rows_per_rank, self.flag_offset,
+                                               self.numel * 4, 0, int(P), self.rows_per_rank, self.flag_offset,
                                                self.world, self.rank, self.epoch, int(ctas), st),
                   "gsr_peer_owner_sum")
         self.epoch += 2

@@ -130,22 +130,21 @@ typedef struct gsr_grads {
                                   exchanges these 3 floats per Gaussian and view and rebuilds the summed SH gradient with
                                   gsr_sh_grad_from_views (the per-view SH gradient is the rank-1 product basis x this). */
     /* ---- view-parallel training, fused gradient exchange (optional; push_bases == NULL: off).  The preprocess-stage
-     * backward then does NOT write dL_dmeans3D / dL_dopacity / dL_dscales / dL_drotations locally: it stores every Gaussian's
-     * 11 floats (zeros when the Gaussian is not visible in this view) as one 48-byte row straight into the staging area of the
-     * rank that OWNS the Gaussian (peer memory over NVLink, under the kernel's own run time):
-     *     block = idx / 256,  owner = block % push_world  (256-Gaussian blocks dealt round-robin, so that all owners receive at once),
-     *     local = (block / push_world) * 256 + idx % 256,
-     *     row address = push_bases[owner] + push_offset + (push_rank * push_rows_per_rank + local) * 48
-     * and, when a block's 256 rows are out, publishes (system fence + release store) push_epoch into the block's ready word
-     *     push_bases[owner] + push_ready_offset + (push_rank * (push_rows_per_rank / 256) + block / push_world) * 4.
-     * gsr_peer_owner_sum -- queued on another stream BEFORE this backward, so that it runs beside it -- follows the ready
-     * words, sums every block in rank order as soon as all ranks staged it and delivers the totals to all ranks.
-     * push_rows_per_rank must be a multiple of 256; the ready words start at zero and epochs only grow. */
+     * backward then does NOT write dL_dmeans3D / dL_dopacity / dL_dscales / dL_drotations locally: the 256 x 11 floats of every
+     * 256-Gaussian block (zeros where a Gaussian is not visible in this view) go straight into the staging area of the rank
+     * that OWNS the block (peer memory over NVLink, under the kernel's own run time):
+     *     block = idx / 256,  owner = block % push_world  (blocks dealt round-robin, so that all owners receive at once),
+     *     slot address = push_bases[owner] + push_offset + (push_rank * (push_rows_per_rank / 256) + block / push_world) * 12288
+     * A slot holds the block's 2816 floats ([256][11], row-major) as 94 lines of 128 bytes: 30 data floats followed by two words
+     * that both hold push_epoch.  A line is written by 8 lanes of one store instruction and arrives whole, so it validates
+     * itself: gsr_peer_owner_sum -- queued on another stream BEFORE this backward, so that it runs beside it -- re-reads a
+     * line until its flag is the epoch, sums every block in rank order and delivers the totals to all ranks.  No fence, no
+     * kernel boundary between producer and consumer.  push_rows_per_rank must be a multiple of 256, push_offset of 128;
+     * epochs only grow and are never 0. */
     void* const* push_bases;   /* DEVICE array of `push_world` peer-mapped base pointers (as for gsr_peer_allreduce_sum) */
-    size_t push_offset;        /* byte offset of the staging area inside every rank's buffer, 16-byte aligned */
+    size_t push_offset;        /* byte offset of the staging area inside every rank's buffer, 128-byte aligned */
     int push_rank, push_world, push_rows_per_rank;
     unsigned push_epoch;       /* the epoch the matching gsr_peer_owner_sum call waits for */
-    size_t push_ready_offset;  /* byte offset of the ready words (push_world * push_rows_per_rank / 256 of them), 4-byte aligned */
 } gsr_grads;
 
 /* ---- sizes of the three work buffers (bytes, including alignment slack) ---- */
@@ -349,17 +348,18 @@ GSR_API int gsr_peer_barrier(void* const* peer_bases, size_t flag_offset, int wo
 GSR_API int gsr_peer_allreduce_sum_mc(void* const* peer_bases, void* multicast_base, size_t data_offset, long long n_floats,
                                       size_t flag_offset, int world, int rank, unsigned epoch, void* stream);
 /* Second half of the fused exchange (see gsr_grads.push_*), a streaming consumer: barrier(epoch) -- every rank is past the last
- * reader of the previous totals --, then rank r takes the blocks it owns (block % world == r) in order; a block is summed as soon
- * as its `world` ready words hold `epoch` (rank order, so every run gives the same bits and every rank the same totals) and the
- * totals are written into EVERY rank's dense gradient block at final_offset -- [means3D 3 x P4 | opacity P4 | scales 3 x P4 |
- * rotations 4 x P4] floats, P4 = P rounded up to 4, the layout the torch host carves the four tensors from -- through the
- * multicast mapping when multicast_base != NULL (one store per value, replicated by the NVSwitch) or with one store per peer;
- * barrier(epoch + 1).  Queue it on its own stream before the backward that pushes the rows: it then runs beside that kernel
- * (`ctas` resident CTAs of 256 threads, 0 = default 74) and only the last blocks and the closing barrier remain when the
- * backward ends.  A ready word that does not arrive within the watchdog time poisons the totals (NaN) and raises gsr_peer_error. */
+ * reader of the previous totals --, then rank r takes the blocks it owns (block % world == r) in order; every 128-byte line of
+ * a block is re-read from each rank's slot until its flag words hold `epoch`, the lines are added in rank order (so every run
+ * gives the same bits and every rank the same totals) and the totals are written into EVERY rank's dense gradient block at
+ * final_offset -- [means3D 3 x P4 | opacity P4 | scales 3 x P4 | rotations 4 x P4] floats, P4 = P rounded up to 4, the layout
+ * the torch host carves the four tensors from -- through the multicast mapping when multicast_base != NULL (one store per
+ * value, replicated by the NVSwitch) or with one store per peer; barrier(epoch + 1).  Queue it on its own stream before the
+ * backward that pushes: it then runs beside that kernel (`ctas` resident CTAs of 256 threads, 0 = default 74) and only the
+ * last blocks and the closing barrier remain when the backward ends.  A line that does not arrive within the watchdog time
+ * poisons the totals (NaN) and raises gsr_peer_error.  epoch must not be 0. */
 GSR_API int gsr_peer_owner_sum(void* const* peer_bases, void* multicast_base, size_t staging_offset, size_t final_offset,
-                               size_t ready_offset, int P, int rows_per_rank, size_t flag_offset, int world, int rank,
-                               unsigned epoch, int ctas, void* stream);
+                               int P, int rows_per_rank, size_t flag_offset, int world, int rank, unsigned epoch, int ctas,
+                               void* stream);
 /* 1 if a peer barrier of this process timed out since the last call (the word is cleared); the kernels that follow a timed-out
  * barrier write NaN instead of sums, so a rank that ran ahead can never train on stale gradients silently. */
 GSR_API int gsr_peer_error(void);

@@ -35,20 +35,20 @@ def _backward(d, camd, cam, dpix, radii, gb, N, bb, ib, **kw):
 def _setup(world, P, dev, lib):
     P4 = (P + 3) // 4 * 4
     rows = ((P + 255) // 256 + world - 1) // world * 256           # 256-Gaussian blocks dealt round-robin to the ranks
-    numel = 11 * P4
-    staging = world * rows * 12
-    ready = (world * (rows // 256) + 63) // 64 * 64
+    numel = (11 * P4 + 31) // 32 * 32                                # the staging slots are 128-byte aligned
+    staging = world * rows * 12                                      # a 12 KB slot per (rank, owned block)
     fb = int(lib.gsr_peer_flag_bytes(world))
-    bufs = [torch.full((numel + staging + ready + fb // 4,), float("nan"), dtype=torch.float32, device=dev) for _ in range(world)]
+    bufs = [torch.full((numel + staging + fb // 4 + 32,), float("nan"), dtype=torch.float32, device=dev) for _ in range(world)]
+    bufs = [b[(-b.data_ptr() // 4) % 32:][:numel + staging + fb // 4] for b in bufs]                 # 128-byte aligned bases
     for b in bufs:
-        b[numel + staging:].zero_()
+        b[numel:].zero_()
     bases = torch.tensor([b.data_ptr() for b in bufs], dtype=torch.int64, device=dev)
-    return P4, rows, numel, staging, ready, bufs, bases
+    return P4, rows, numel, staging, bufs, bases
 
 
-def _owner_sum(lib, _capi, bases, numel, staging, ready, P, rows, world, r, epoch, stream, ctas=0):
-    _capi.check(lib.gsr_peer_owner_sum(C.c_void_p(bases.data_ptr()), None, numel * 4, 0, (numel + staging) * 4, P, rows,
-                                       (numel + staging + ready) * 4, world, r, epoch, ctas, C.c_void_p(stream.cuda_stream)),
+def _owner_sum(lib, _capi, bases, numel, staging, P, rows, world, r, epoch, stream, ctas=0):
+    _capi.check(lib.gsr_peer_owner_sum(C.c_void_p(bases.data_ptr()), None, numel * 4, 0, P, rows,
+                                       (numel + staging) * 4, world, r, epoch, ctas, C.c_void_p(stream.cuda_stream)),
                 "gsr_peer_owner_sum")
 
 
@@ -61,7 +61,7 @@ def test_pushed_rows_plus_owner_sum_equal_the_rank_ordered_sum(world, consumer_f
     dev = cuda_device
     sc, _ = common.make_case("small")
     P = sc["means3D"].shape[0]
-    P4, rows, numel, staging, ready, bufs, bases = _setup(world, P, dev, lib)
+    P4, rows, numel, staging, bufs, bases = _setup(world, P, dev, lib)
     epoch = 5
     streams = [torch.cuda.Stream(device=dev) for _ in range(world)]
     want = [torch.zeros(P, 3), torch.zeros(P, 1), torch.zeros(P, 3), torch.zeros(P, 4)]
@@ -74,7 +74,7 @@ def test_pushed_rows_plus_owner_sum_equal_the_rank_ordered_sum(world, consumer_f
     torch.cuda.synchronize()
     if consumer_first:
         for r in range(world):
-            _owner_sum(lib, _capi, bases, numel, staging, ready, P, rows, world, r, epoch, streams[r], ctas=2)
+            _owner_sum(lib, _capi, bases, numel, staging, P, rows, world, r, epoch, streams[r], ctas=2)
     for r, cam in enumerate(_views(world)):
         d, camd = common.cuda_inputs(sc, cam, dev)
         dpix = common.upstream_gradient(cam, seed=3003 + r).to(dev)
@@ -83,11 +83,11 @@ def test_pushed_rows_plus_owner_sum_equal_the_rank_ordered_sum(world, consumer_f
         for acc, k in zip(want, (3, 2, 6, 7)):
             acc += ref[k].cpu().reshape(acc.shape)              # rank order, float32
         _backward(d, camd, cam, dpix, radii, gb, N, bb, ib, dense_out=bufs[r][:numel],
-                  push=(bases.data_ptr(), numel * 4, r, world, rows, epoch, (numel + staging) * 4))
+                  push=(bases.data_ptr(), numel * 4, r, world, rows, epoch))
     if not consumer_first:
         torch.cuda.synchronize()
         for r in range(world):
-            _owner_sum(lib, _capi, bases, numel, staging, ready, P, rows, world, r, epoch, streams[r])
+            _owner_sum(lib, _capi, bases, numel, staging, P, rows, world, r, epoch, streams[r])
     torch.cuda.synchronize()
     _capi.check(lib.gsr_set_option(6, 0), "gsr_set_option")
     assert lib.gsr_peer_error() == 0
@@ -103,16 +103,20 @@ def test_pushed_rows_plus_owner_sum_equal_the_rank_ordered_sum(world, consumer_f
     for b in bufs[1:]:
         assert torch.equal(b[:numel], bufs[0][:numel])
     # and the sum is exactly the rank-ordered float32 sum of what was staged, for all four arrays
-    stag = [b[numel:numel + world * rows * 12].view(world, rows, 12).cpu() for b in bufs]        # stag[owner][src rank][local row]
+    def rows_of(buf):          # [world][blocks][256][11] from the 94-line slots (30 data floats + 2 flag words per 128-byte line)
+        slots = buf[numel:numel + staging].view(world, rows // 256, 96, 32).cpu()
+        assert bool((slots[:, :, :94, 30:].view(torch.int32) == epoch).all()), "every line carries the epoch flag"
+        return slots[:, :, :94, :30].reshape(world, rows // 256, 94 * 30)[:, :, :2816].reshape(world, rows // 256, 256, 11)
+    stag = [rows_of(b) for b in bufs]                               # stag[owner][src rank][local block][row][11]
     flat0 = bufs[0][:numel].cpu()
     m3, op = flat0[0:3 * P].view(P, 3), flat0[3 * P4:3 * P4 + P]
     s3, r4 = flat0[4 * P4:4 * P4 + 3 * P].view(P, 3), flat0[7 * P4:7 * P4 + 4 * P].view(P, 4)
     for idx in list(range(0, P, max(1, P // 257))) + [P - 1]:
         blk = idx // 256
-        owner, local = blk % world, (blk // world) * 256 + idx % 256
-        acc = torch.zeros(12)
+        owner = blk % world
+        acc = torch.zeros(11)
         for r in range(world):
-            acc = acc + stag[owner][r, local]
+            acc = acc + stag[owner][r, blk // world, idx % 256]
         assert torch.equal(m3[idx], acc[0:3]) and torch.equal(op[idx], acc[3]) and torch.equal(s3[idx], acc[4:7]) and torch.equal(r4[idx], acc[7:11]), idx
 
 
@@ -122,12 +126,12 @@ def test_owner_sum_watchdog_poisons_a_block_that_never_arrives(cuda_device):
     lib = _capi.lib
     dev = cuda_device
     P, world = 1000, 1
-    P4, rows, numel, staging, ready, bufs, bases = _setup(world, P, dev, lib)
+    P4, rows, numel, staging, bufs, bases = _setup(world, P, dev, lib)
     st = torch.cuda.Stream(device=dev)
     _capi.check(lib.gsr_set_option(6, 200), "gsr_set_option")
     try:
         lib.gsr_peer_error()
-        _owner_sum(lib, _capi, bases, numel, staging, ready, P, rows, world, 0, 3, st)
+        _owner_sum(lib, _capi, bases, numel, staging, P, rows, world, 0, 3, st)
         st.synchronize()
         assert lib.gsr_peer_error() == 1
         assert bool(torch.isnan(bufs[0][:numel]).all())
