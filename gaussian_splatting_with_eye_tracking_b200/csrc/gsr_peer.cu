@@ -364,7 +364,10 @@ int gsr_peer_owner_sum(void* const* peer_bases, void* multicast_base, size_t sta
     p.P4 = (P + 3) / 4 * 4; p.rows_per_rank = rows_per_rank; p.world = world; p.rank = rank;
     p.epoch = epoch; p.timeout_ns = peer_timeout_ns(); p.host_err = peer_error_word();
     const int mine = (int)((((long long)p.P4 + 255) / 256 + world - 1 - rank) / world);       // blocks this rank owns
-    int blocks = ctas > 0 ? ctas : (g_peer_ctas_per_sm ? 148 * g_peer_ctas_per_sm : 74);
+    // resident consumer CTAs: a block costs a CTA a few microseconds of load latency, the producers of all ranks together finish
+    // ~25 blocks per microsecond; one CTA per ~40 owned blocks keeps up (measured at world 2: 74 CTAs for 11.7 k blocks fell
+    // 0.16 ms behind, 148 do not), and every CTA taken here is an occupancy slot less for the backward beside it
+    int blocks = ctas > 0 ? ctas : (g_peer_ctas_per_sm ? 148 * g_peer_ctas_per_sm : std::max(37, std::min(148, mine / 40)));
     blocks = std::max(1, std::min(blocks, std::max(1, mine)));
     if (multicast_base) peer_owner_sum_kernel<true><<<(unsigned)blocks, kPeerThreads, 0, s>>>(p);
     else peer_owner_sum_kernel<false><<<(unsigned)blocks, kPeerThreads, 0, s>>>(p);

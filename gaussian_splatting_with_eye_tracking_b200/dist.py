@@ -323,6 +323,8 @@ class ShGradExchange:
         if self.fused and (peer is None or not peer.rows_per_rank):
             raise RuntimeError("ShGradExchange(fused=True) needs a PeerAllReduce with staging_gaussians=P")
         self._owner_sum_queued = False
+        self.rebuild_early = self.fused        # where the SH rebuild runs (see _start_gather_packed / finish_sh)
+        self._dsh_early = None
         self._fused_calls = 0
         self.fused_warm_steps = 2
         self._gather_event = None
@@ -457,6 +459,13 @@ class ShGradExchange:
                 self._gather_event.record(comm)          # the masks of all views are on this rank from here on
             cams = self._meta_all[:, L:L + 3].contiguous().view(torch.float32)
             self._side_allocs = [cams]
+            if self.rebuild_early:
+                # fused mode: the dense sum already runs under the preprocess-stage backward, so the rebuild is what would be
+                # left exposed behind it -- it runs here, on the side stream, beside that kernel (which is latency-bound, not
+                # HBM-bound) as soon as the rows of all views are in
+                self._dsh_early = rebuild(means3D, cams, self._meta_all, rows_all.view(w, cap, 3), degree, M)
+                self._rebuild_call = None
+                return
         self._rebuild_call = lambda: rebuild(means3D, cams, self._meta_all, rows_all.view(w, cap, 3), degree, M)
 
     def start_owner_sum(self, device) -> None:
@@ -522,7 +531,12 @@ class ShGradExchange:
         # The rebuild runs HERE, on the caller's stream behind the backward, not on the side stream: it is HBM-bound
         # like the preprocess-stage backward (running both at once only slows the backward down, measured), while the
         # all-reduce queued by start_reduce is NVLink-bound -- so the rebuild overlaps the all-reduce instead.
-        dsh = self._rebuild_call() if self._rebuild_call is not None else None
+        if self._dsh_early is not None:
+            dsh, self._dsh_early = self._dsh_early, None
+            if dsh.is_cuda:
+                dsh.record_stream(torch.cuda.current_stream())     # allocated and written on the side stream, used here
+        else:
+            dsh = self._rebuild_call() if self._rebuild_call is not None else None
         self._rebuild_call, self._keep = None, None
         # (the persistent gather buffers are safe: the next start_gather makes the side stream wait for this one)
         for t in self._side_allocs:

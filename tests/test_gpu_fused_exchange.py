@@ -103,11 +103,19 @@ def test_pushed_rows_plus_owner_sum_equal_the_rank_ordered_sum(world, consumer_f
     for b in bufs[1:]:
         assert torch.equal(b[:numel], bufs[0][:numel])
     # and the sum is exactly the rank-ordered float32 sum of what was staged, for all four arrays
+    owner_of = [0]
+
     def rows_of(buf):          # [world][blocks][256][11] from the 94-line slots (30 data floats + 2 flag words per 128-byte line)
         slots = buf[numel:numel + staging].view(world, rows // 256, 96, 32).cpu()
-        assert bool((slots[:, :, :94, 30:].view(torch.int32) == epoch).all()), "every line carries the epoch flag"
+        nb = (P + 255) // 256
+        for o_blk in range(rows // 256):                             # slots of blocks beyond P are never written
+            if (o_blk * world + owner_of[0]) < nb:
+                assert bool((slots[:, o_blk, :94, 30:].view(torch.int32) == epoch).all()), "every line carries the epoch flag"
         return slots[:, :, :94, :30].reshape(world, rows // 256, 94 * 30)[:, :, :2816].reshape(world, rows // 256, 256, 11)
-    stag = [rows_of(b) for b in bufs]                               # stag[owner][src rank][local block][row][11]
+    stag = []                                                       # stag[owner][src rank][local block][row][11]
+    for o, b in enumerate(bufs):
+        owner_of[0] = o
+        stag.append(rows_of(b))
     flat0 = bufs[0][:numel].cpu()
     m3, op = flat0[0:3 * P].view(P, 3), flat0[3 * P4:3 * P4 + P]
     s3, r4 = flat0[4 * P4:4 * P4 + 3 * P].view(P, 3), flat0[7 * P4:7 * P4 + 4 * P].view(P, 4)
