@@ -318,9 +318,10 @@ def pack_visible_rows(rows, radii, cap, out_rows=None, out_meta=None):
     return packed, meta
 
 
-def sh_grad_from_packed_views(means3D, cam_positions, meta, rows, degree, M):
+def sh_grad_from_packed_views(means3D, cam_positions, meta, rows, degree, M, out=None):
     """As sh_grad_from_views with every view's colour gradient packed by pack_visible_rows:
-    cam_positions [K,3], meta [K,L] int32 (L >= pack_meta_words(P)), rows [K,cap,3] -> dL_dsh [P,M,3]."""
+    cam_positions [K,3], meta [K,L] int32 (L >= pack_meta_words(P)), rows [K,cap,3] -> dL_dsh [P,M,3]
+    (``out``: a caller-owned contiguous float32 [P,M,3] tensor to write instead of a fresh allocation)."""
     P, K = int(means3D.size(0)), int(cam_positions.size(0))
     m = _dev_tensor(means3D, "means3D")
     cams = _dev_tensor(cam_positions, "cam_positions")
@@ -330,7 +331,10 @@ def sh_grad_from_packed_views(means3D, cam_positions, meta, rows, degree, M):
     if g.dim() != 3 or int(g.size(0)) != K or int(g.size(2)) != 3:
         raise RuntimeError(f"rows must have dimensions ({K}, cap, 3)")
     with torch.cuda.device(m.device):
-        out = torch.empty((P, int(M), 3), dtype=torch.float32, device=m.device)
+        if out is None:
+            out = torch.empty((P, int(M), 3), dtype=torch.float32, device=m.device)
+        elif tuple(out.shape) != (P, int(M), 3) or out.dtype != torch.float32 or not out.is_contiguous() or out.device != m.device:
+            raise RuntimeError(f"out must be a contiguous float32 ({P}, {int(M)}, 3) tensor on the same device")
         rc = lib.gsr_sh_grad_from_packed_views(P, int(degree), int(M), _p(m), K, _p(cams), _p(meta), int(meta.size(1)),
                                                _p(g), int(g.size(1)), _p(out), _stream())
         _capi.check(rc, "gsr_sh_grad_from_packed_views")

@@ -187,8 +187,11 @@ __device__ __forceinline__ float4 ld_line_piece(const float4* p) {
     return v;
 }
 
-template <bool MC>
-__global__ void __launch_bounds__(kPeerThreads) peer_owner_sum_kernel(const OwnerSumParams p) {
+// MAXW = compile-time bound of world (2, 4 or 8), DEPTH = 256-piece chunks of a block whose loads are issued before the first is
+// validated (3 = the whole block: three times fewer exposed load latencies per block, used at world 2 where an owner has the most
+// blocks).  64 registers at most: a consumer CTA then displaces exactly one CTA of the backward beside it.
+template <bool MC, int MAXW, int DEPTH>
+__global__ void __launch_bounds__(kPeerThreads, 4) peer_owner_sum_kernel(const OwnerSumParams p) {
     __shared__ float s_f[2816 + 8];             // the block's totals, [256 Gaussians][11 floats]
     __shared__ int s_bad;
     const int tid = threadIdx.x, lane = tid & 31;
@@ -197,6 +200,8 @@ __global__ void __launch_bounds__(kPeerThreads) peer_owner_sum_kernel(const Owne
     uint32_t* mine = reinterpret_cast<uint32_t*>(p.bases[p.rank] + p.flag_offset);
     const size_t P4 = (size_t)p.P4;
     const int nblk = p.rows_per_rank >> 8;
+    const size_t slot = (size_t)nblk * kPushSlotF4;                       // float4s between two ranks' copies of a block
+    const bool flag_lane = (lane & 7) == 7;
     if (tid == 0) s_bad = 0;
     bool bad = false;                           // this warp's watchdog fired: it stops waiting for good
     // this rank owns the 256-Gaussian blocks rank, rank + world, rank + 2 world, ... (block-cyclic, see preprocess_bwd_kernel);
@@ -205,48 +210,55 @@ __global__ void __launch_bounds__(kPeerThreads) peer_owner_sum_kernel(const Owne
         const long long idx0 = ((long long)j * p.world + p.rank) << 8;
         if (idx0 >= (long long)P4) break;
         __syncthreads();                                                  // s_f of the previous block has been read
-        for (int e0 = 0; e0 < kPushLines * 8; e0 += kPeerThreads) {       // whole warps stay: the line votes are warp-wide
-            const int e = e0 + tid;
-            const bool act = e < kPushLines * 8;
-            const bool flag_lane = (lane & 7) == 7;
-            const float4* src = staging + (size_t)j * kPushSlotF4 + (act ? e : 0);
-            const size_t slot = (size_t)nblk * kPushSlotF4;               // float4s between two ranks' copies of the block
-            float4 v[kMaxPeers];
+        for (int e0 = 0; e0 < kPushLines * 8; e0 += kPeerThreads * DEPTH) {       // whole warps stay: the line votes are warp-wide
+            float4 v[DEPTH][MAXW];
+            const float4* src[DEPTH];
+            bool act[DEPTH];
 #pragma unroll
-            for (int k = 0; k < kMaxPeers; ++k)
-                if (k < p.world) v[k] = ld_line_piece(src + k * slot);
-            float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+            for (int c = 0; c < DEPTH; ++c) {
+                const int e = e0 + c * kPeerThreads + tid;
+                act[c] = e < kPushLines * 8;
+                src[c] = staging + (size_t)j * kPushSlotF4 + (act[c] ? e : 0);
 #pragma unroll
-            for (int k = 0; k < kMaxPeers; ++k) {
-                if (k >= p.world) break;
-                // a line is valid when the flag its 8th piece carries is this epoch; the 8 pieces come from ONE load instruction
-                unsigned long long t0 = 0;
-                unsigned spins = 0;
-                for (;;) {
-                    const bool ok = !act || !flag_lane || (__float_as_uint(v[k].z) == p.epoch && __float_as_uint(v[k].w) == p.epoch);
-                    if (__all_sync(0xffffffffu, ok) || bad) break;
-                    if ((++spins & 63u) == 0u) {
-                        unsigned long long t1;
-                        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
-                        if (t0 == 0) t0 = t1;
-                        else if ((long long)(t1 - t0) > p.timeout_ns) bad = true;      // never a silent sum of stale rows
+                for (int k = 0; k < MAXW; ++k)
+                    if (k < p.world) v[c][k] = ld_line_piece(src[c] + k * slot);
+            }
+#pragma unroll
+            for (int c = 0; c < DEPTH; ++c) {
+                float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+                for (int k = 0; k < MAXW; ++k) {
+                    if (k >= p.world) break;
+                    // a line is valid when the flag its 8th piece carries is this epoch; the 8 pieces come from ONE load instruction
+                    unsigned long long t0 = 0;
+                    unsigned spins = 0;
+                    for (;;) {
+                        const bool ok = !act[c] || !flag_lane || (__float_as_uint(v[c][k].z) == p.epoch && __float_as_uint(v[c][k].w) == p.epoch);
+                        if (__all_sync(0xffffffffu, ok) || bad) break;
+                        if ((++spins & 63u) == 0u) {
+                            unsigned long long t1;
+                            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+                            if (t0 == 0) t0 = t1;
+                            else if ((long long)(t1 - t0) > p.timeout_ns) bad = true;      // never a silent sum of stale rows
+                        }
+                        bad = __any_sync(0xffffffffu, bad);
+                        if (bad) break;
+                        __nanosleep(500);
+                        v[c][k] = ld_line_piece(src[c] + k * slot);        // the whole warp re-loads: pieces and flag stay one load
                     }
-                    bad = __any_sync(0xffffffffu, bad);
-                    if (bad) break;
-                    __nanosleep(500);
-                    v[k] = ld_line_piece(src + k * slot);                  // the whole warp re-loads: pieces and flag stay one load
+                    acc.x += v[c][k].x; acc.y += v[c][k].y; acc.z += v[c][k].z; acc.w += v[c][k].w;      // rank order
                 }
-                acc.x += v[k].x; acc.y += v[k].y; acc.z += v[k].z; acc.w += v[k].w;      // rank order
+                if (act[c]) {
+                    const int e = e0 + c * kPeerThreads + tid;
+                    const int f0 = (e >> 3) * 30 + (e & 7) * 4;
+                    s_f[f0] = acc.x; s_f[f0 + 1] = acc.y;                 // (the last line's tail lands in the 8 pad floats)
+                    if (!flag_lane) { s_f[f0 + 2] = acc.z; s_f[f0 + 3] = acc.w; }
+                }
             }
             if (bad && lane == 0) {
                 mine[p.world] = 1u;
                 if (p.host_err) { *((volatile uint32_t*)p.host_err) = 1u; __threadfence_system(); }
                 s_bad = 1;
-            }
-            if (act) {
-                const int f0 = (e >> 3) * 30 + (e & 7) * 4;
-                s_f[f0] = acc.x; s_f[f0 + 1] = acc.y;                     // (the last line's tail lands in the 8 pad floats)
-                if (!flag_lane) { s_f[f0 + 2] = acc.z; s_f[f0 + 3] = acc.w; }
             }
         }
         __syncthreads();
@@ -295,8 +307,12 @@ void preload(int world) {
     cudaFuncAttributes fa;
     cudaFuncGetAttributes(&fa, peer_barrier_kernel);
     cudaFuncGetAttributes(&fa, peer_reduce_mc_kernel);
-    cudaFuncGetAttributes(&fa, peer_owner_sum_kernel<true>);
-    cudaFuncGetAttributes(&fa, peer_owner_sum_kernel<false>);
+    cudaFuncGetAttributes(&fa, peer_owner_sum_kernel<true, 2, 3>);
+    cudaFuncGetAttributes(&fa, peer_owner_sum_kernel<false, 2, 3>);
+    cudaFuncGetAttributes(&fa, peer_owner_sum_kernel<true, 4, 1>);
+    cudaFuncGetAttributes(&fa, peer_owner_sum_kernel<false, 4, 1>);
+    cudaFuncGetAttributes(&fa, peer_owner_sum_kernel<true, 8, 1>);
+    cudaFuncGetAttributes(&fa, peer_owner_sum_kernel<false, 8, 1>);
     preload_preprocess_backward();            // the producer the streaming owner sum waits for
     switch (world) {
         case 2: preload_reduce<2>(); break; case 3: preload_reduce<3>(); break; case 4: preload_reduce<4>(); break;
@@ -364,13 +380,21 @@ int gsr_peer_owner_sum(void* const* peer_bases, void* multicast_base, size_t sta
     p.P4 = (P + 3) / 4 * 4; p.rows_per_rank = rows_per_rank; p.world = world; p.rank = rank;
     p.epoch = epoch; p.timeout_ns = peer_timeout_ns(); p.host_err = peer_error_word();
     const int mine = (int)((((long long)p.P4 + 255) / 256 + world - 1 - rank) / world);       // blocks this rank owns
-    // resident consumer CTAs: a block costs a CTA a few microseconds of load latency, the producers of all ranks together finish
-    // ~25 blocks per microsecond; one CTA per ~40 owned blocks keeps up (measured at world 2: 74 CTAs for 11.7 k blocks fell
-    // 0.16 ms behind, 148 do not), and every CTA taken here is an occupancy slot less for the backward beside it
-    int blocks = ctas > 0 ? ctas : (g_peer_ctas_per_sm ? 148 * g_peer_ctas_per_sm : std::max(37, std::min(148, mine / 40)));
+    // resident consumer CTAs: every one of them takes an occupancy slot from the backward beside it (a register-file quarter of
+    // its SM: measured +0.13 ms on the 0.72 ms kernel with 74, +0.3 ms with 148), so as few as keep up with the producers:
+    // one per ~160 owned blocks, 37..74
+    int blocks = ctas > 0 ? ctas : (g_peer_ctas_per_sm ? 148 * g_peer_ctas_per_sm : std::max(37, std::min(74, mine / 160)));
     blocks = std::max(1, std::min(blocks, std::max(1, mine)));
-    if (multicast_base) peer_owner_sum_kernel<true><<<(unsigned)blocks, kPeerThreads, 0, s>>>(p);
-    else peer_owner_sum_kernel<false><<<(unsigned)blocks, kPeerThreads, 0, s>>>(p);
+    if (world <= 2) {
+        if (multicast_base) peer_owner_sum_kernel<true, 2, 3><<<(unsigned)blocks, kPeerThreads, 0, s>>>(p);
+        else peer_owner_sum_kernel<false, 2, 3><<<(unsigned)blocks, kPeerThreads, 0, s>>>(p);
+    } else if (world <= 4) {
+        if (multicast_base) peer_owner_sum_kernel<true, 4, 1><<<(unsigned)blocks, kPeerThreads, 0, s>>>(p);
+        else peer_owner_sum_kernel<false, 4, 1><<<(unsigned)blocks, kPeerThreads, 0, s>>>(p);
+    } else {
+        if (multicast_base) peer_owner_sum_kernel<true, 8, 1><<<(unsigned)blocks, kPeerThreads, 0, s>>>(p);
+        else peer_owner_sum_kernel<false, 8, 1><<<(unsigned)blocks, kPeerThreads, 0, s>>>(p);
+    }
     peer_barrier_kernel<<<1, 32, 0, s>>>(bases, flag_offset, world, rank, epoch + 1u, peer_timeout_ns(), peer_error_word());
     count_launch(3);
     return check_last("peer_owner_sum", false, s);

@@ -325,6 +325,8 @@ class ShGradExchange:
         self._owner_sum_queued = False
         self.rebuild_early = self.fused        # where the SH rebuild runs (see _start_gather_packed / finish_sh)
         self._dsh_early = None
+        self._dsh_bufs = None
+        self._dsh_flip = 0
         self._fused_calls = 0
         self.fused_warm_steps = 2
         self._gather_event = None
@@ -463,7 +465,18 @@ class ShGradExchange:
                 # fused mode: the dense sum already runs under the preprocess-stage backward, so the rebuild is what would be
                 # left exposed behind it -- it runs here, on the side stream, beside that kernel (which is latency-bound, not
                 # HBM-bound) as soon as the rows of all views are in
-                self._dsh_early = rebuild(means3D, cams, self._meta_all, rows_all.view(w, cap, 3), degree, M)
+                # into one of two persistent buffers (a fresh 1 GB allocation per step on a side stream would make the caching
+                # allocator fall back to cudaMalloc/cudaFree, i.e. device-wide stalls): the caller owns the returned tensor
+                # until the exchange after next
+                if self._dsh_bufs is None or self._dsh_bufs[0].shape != (P, M, 3) or self._dsh_bufs[0].device != dev:
+                    self._dsh_bufs = [torch.empty((P, M, 3), dtype=torch.float32, device=dev) for _ in range(2)]
+                self._dsh_flip ^= 1
+                out = self._dsh_bufs[self._dsh_flip]
+                if self._rebuild_packed is None:
+                    rebuild(means3D, cams, self._meta_all, rows_all.view(w, cap, 3), degree, M, out=out)
+                else:
+                    out.copy_(rebuild(means3D, cams, self._meta_all, rows_all.view(w, cap, 3), degree, M))
+                self._dsh_early = out
                 self._rebuild_call = None
                 return
         self._rebuild_call = lambda: rebuild(means3D, cams, self._meta_all, rows_all.view(w, cap, 3), degree, M)
@@ -532,9 +545,7 @@ class ShGradExchange:
         # like the preprocess-stage backward (running both at once only slows the backward down, measured), while the
         # all-reduce queued by start_reduce is NVLink-bound -- so the rebuild overlaps the all-reduce instead.
         if self._dsh_early is not None:
-            dsh, self._dsh_early = self._dsh_early, None
-            if dsh.is_cuda:
-                dsh.record_stream(torch.cuda.current_stream())     # allocated and written on the side stream, used here
+            dsh, self._dsh_early = self._dsh_early, None           # persistent buffer, written on the side stream waited for above
         else:
             dsh = self._rebuild_call() if self._rebuild_call is not None else None
         self._rebuild_call, self._keep = None, None

@@ -354,7 +354,7 @@ GSR_API int gsr_peer_allreduce_sum_mc(void* const* peer_bases, void* multicast_b
  * final_offset -- [means3D 3 x P4 | opacity P4 | scales 3 x P4 | rotations 4 x P4] floats, P4 = P rounded up to 4, the layout
  * the torch host carves the four tensors from -- through the multicast mapping when multicast_base != NULL (one store per
  * value, replicated by the NVSwitch) or with one store per peer; barrier(epoch + 1).  Queue it on its own stream before the
- * backward that pushes: it then runs beside that kernel (`ctas` resident CTAs of 256 threads, 0 = one per ~40 owned blocks, 37..148) and only the
+ * backward that pushes: it then runs beside that kernel (`ctas` resident CTAs of 256 threads, 0 = one per ~160 owned blocks, 37..74) and only the
  * last blocks and the closing barrier remain when the backward ends.  A line that does not arrive within the watchdog time
  * poisons the totals (NaN) and raises gsr_peer_error.  epoch must not be 0. */
 GSR_API int gsr_peer_owner_sum(void* const* peer_bases, void* multicast_base, size_t staging_offset, size_t final_offset,
