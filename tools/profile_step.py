@@ -25,6 +25,7 @@ def main():
     ap.add_argument("--camera", type=int, default=0)
     ap.add_argument("--amr", action="store_true")
     ap.add_argument("--no-bwd", action="store_true")
+    ap.add_argument("--dp", action="store_true", help="also the view-parallel pieces: compact backward, row packing, SH rebuild from 2 views")
     ap.add_argument("--warmup", type=int, default=2)
     a = ap.parse_args()
     dev = torch.device("cuda:0")
@@ -46,6 +47,15 @@ def main():
                                                d["shs"], d["sh_degree"], cam.camera_center, gb, N, bb, ib, False)
         if a.amr:
             _host.rasterize_gaussians_amr(*args, -2, e, eb, eb, eb, True, False)
+        if a.dp:
+            P, M = d["means3D"].shape[0], d["shs"].shape[1]
+            g = _host.rasterize_gaussians_backward(d["bg"], d["means3D"], radii, e, d["scales"], d["rotations"], 1.0, e,
+                                                   cam.world_view_transform, cam.full_proj_transform, cam.tanfovx, cam.tanfovy, w,
+                                                   d["shs"], d["sh_degree"], cam.camera_center, gb, N, bb, ib, False, compact_sh=True)
+            cap = (int((radii > 0).sum()) + 255) // 256 * 256
+            rows, meta = _host.pack_visible_rows(g[5], radii, cap)
+            cams = torch.stack([cam.camera_center.reshape(3), cam.camera_center.reshape(3) + 0.1])
+            _host.sh_grad_from_packed_views(d["means3D"], cams, torch.stack([meta, meta]), torch.stack([rows, rows]), d["sh_degree"], M)
         return N
 
     for _ in range(a.warmup):
