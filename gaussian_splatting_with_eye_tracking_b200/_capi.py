@@ -122,6 +122,8 @@ SYMBOLS = {
     "gsr_peer_owner_sum": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t, C.c_int, C.c_int, C.c_size_t,
                                      C.c_int, C.c_int, C.c_uint, C.c_int, C.c_void_p]),
     "gsr_peer_error": (C.c_int, []),
+    "gsr_pack_visible_rows_noalloc": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "gsr_pack_noalloc_max_gaussians": (C.c_int, []),
     "gsr_peer_allreduce_sum": (C.c_int, [C.c_void_p, C.c_size_t, C.c_longlong, C.c_size_t, C.c_int, C.c_int, C.c_uint, C.c_void_p]),
     "gsr_peer_allreduce_sum_mc": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_longlong, C.c_size_t, C.c_int, C.c_int, C.c_uint, C.c_void_p]),
     "gsr_launch_count": (C.c_ulonglong, []),

@@ -12,6 +12,8 @@
 //
 // HBM-bound stages: one thread per Gaussian, 128-bit loads where the AoS inputs allow it, culled
 // Gaussians leave after reading 12 B.
+#include <mutex>
+
 #include "gsr_common.cuh"
 #include "gsr_math.cuh"
 
@@ -1048,4 +1050,59 @@ void launch_clamped_rgb(int P, const int* radii, const float* scratch, const uns
     count_launch();
 }
 
+// ------------------------------------------------------------------------------------------------
+// gsr_pack_visible_rows_noalloc: gsr_pack_visible_rows with its scratch (the per-block counts / offsets of the scan) in a
+// file-scope device array instead of caller memory, for callers that cannot allocate (CUDA graph capture, serving loops,
+// harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// The array costs kPackStaticBytes of device memory on every GPU that loads the library, until exit.  All calls on a device
+// share it: two calls that overlap on the GPU (different streams) race.  Nothing in it has to start at zero -- every call writes
+// all the words it reads (pack_mask_kernel writes counts [0, nb), pack_scan_kernel rewrites them and writes word nb) -- so the
+// previous call's contents are harmless.
+// ------------------------------------------------------------------------------------------------
+constexpr int kPackStaticMaxP = 1 << 24;                                       // 16 777 216 Gaussians
+constexpr int kPackStaticWords = kPackStaticMaxP / kPackBlock + 64;            // nb + 1 words are used; 65 792 bytes
+static __device__ __align__(256) uint32_t g_pack_scratch[kPackStaticWords];
+
+// The array's name is a host-side stand-in in host code, not a device address: resolve it once per device, with that device
+// current (cudaGetSymbolAddress), and hand the kernels the resolved pointer.
+static int pack_scratch_address(uint32_t** out) {
+    static uint32_t* addr[64] = {};
+    static std::mutex mu;
+    int dev = 0;
+    int rc = check_cuda(cudaGetDevice(&dev), "cudaGetDevice");
+    if (rc) return rc;
+    if (dev < 0 || dev >= 64) { set_error("pack_visible_rows_noalloc: device index %d not supported", dev); return GSR_ERR_INVALID; }
+    std::lock_guard<std::mutex> lock(mu);
+    if (!addr[dev]) {
+        uint32_t* ptr = nullptr;
+        if ((rc = check_cuda(cudaGetSymbolAddress((void**)&ptr, g_pack_scratch), "cudaGetSymbolAddress(g_pack_scratch)"))) return rc;
+        if (!ptr) { set_error("pack_visible_rows_noalloc: no device address for the scratch array"); return GSR_ERR_CUDA; }
+        addr[dev] = ptr;
+    }
+    *out = addr[dev];
+    return GSR_OK;
+}
+
 }  // namespace gsr
+
+extern "C" int gsr_pack_visible_rows_noalloc(int P, const int* radii, const float* rows_in, int cap, float* rows_out, uint32_t* meta,
+                                             void* stream) {
+    using namespace gsr;
+    if (P < 0 || cap < 0) { set_error("pack_visible_rows_noalloc: bad sizes"); return GSR_ERR_INVALID; }
+    if (P > kPackStaticMaxP) {
+        set_error("pack_visible_rows_noalloc: P = %d exceeds the static scratch (at most %d Gaussians); use gsr_pack_visible_rows with caller scratch",
+                  P, kPackStaticMaxP);
+        return GSR_ERR_INVALID;
+    }
+    if (P == 0) return GSR_OK;
+    if (!radii || !rows_in || !meta || (cap > 0 && !rows_out)) { set_error("pack_visible_rows_noalloc: null pointer"); return GSR_ERR_INVALID; }
+    uint32_t* temp = nullptr;
+    int rc = pack_scratch_address(&temp);
+    if (rc) return rc;
+    const int W32 = (P + 31) / 32;
+    rc = launch_pack_visible_rows(P, radii, rows_in, cap, rows_out, meta, meta + W32, temp, (cudaStream_t)stream);
+    if (rc) return rc;
+    return check_last("pack_visible_rows_noalloc", false, (cudaStream_t)stream);
+}
+
+extern "C" int gsr_pack_noalloc_max_gaussians(void) { return gsr::kPackStaticMaxP; }

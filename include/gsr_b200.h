@@ -295,6 +295,17 @@ GSR_API size_t gsr_pack_meta_words(int P);
 GSR_API size_t gsr_pack_temp_bytes(int P);
 GSR_API int gsr_pack_visible_rows(int P, const int* radii, const float* rows_in, int cap, float* rows_out, uint32_t* meta,
                                   void* temp, size_t temp_bytes, void* stream);
+/* gsr_pack_visible_rows_noalloc: gsr_pack_visible_rows for callers that cannot allocate device memory (code under CUDA graph
+ *   capture, tight serving loops, harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ *   Same inputs, outputs and results; the scan scratch lives in a file-scope device array inside the
+ *   library (65 792 bytes on every GPU that loads the library, held until exit) instead of `temp`.  The entry point calls no
+ *   cudaMalloc / cudaFree / allocating routine.  Limit: P <= gsr_pack_noalloc_max_gaussians() = 16 777 216, larger P is
+ *   rejected with GSR_ERR_INVALID (use gsr_pack_visible_rows with caller scratch).  All calls on a device share the array:
+ *   calls that overlap on the GPU (different streams without an ordering between them) RACE -- keep them on one stream or order
+ *   them with events.  Nothing has to be cleared between calls: every call writes each scratch word before it reads it. */
+GSR_API int gsr_pack_visible_rows_noalloc(int P, const int* radii, const float* rows_in, int cap, float* rows_out, uint32_t* meta,
+                                          void* stream);
+GSR_API int gsr_pack_noalloc_max_gaussians(void);
 GSR_API int gsr_sh_grad_from_packed_views(int P, int sh_degree, int sh_coeffs, const float* means3D, int num_views,
                                           const float* cam_positions, const uint32_t* meta, size_t meta_stride_words,
                                           const float* rows, int cap, float* dL_dsh, void* stream);
