@@ -839,71 +839,86 @@ void launch_preprocess_backward(const PreBwdArgs& a, cudaStream_t s) {
 // ------------------------------------------------------------------------------------------------
 // PACKED: g_all holds, per view, only the rows of the Gaussians whose bit is set in that view's mask ([K][cap][3], index
 // order); meta holds per view `meta_stride` words: mask words [W32], then the number of set bits before each word [W32].
+// One half of a Gaussian's row: coefficients [8 HALF, 8 HALF + 8) summed over the views into 24 registers and parked in the
+// staged row.  Two passes of 24 accumulators instead of one of 48 keep the kernel at 64 registers = 4 CTAs per SM (the 48-wide
+// version sat at 89 registers, 2 CTAs, 23 % of the warp slots, 32 % of DRAM peak: r2 ncu); a pass re-reads the view's mask word
+// and 12-byte row, which hit L1.  Every accumulator still adds the views in index order, so the sums keep their bits.
+template <bool PACKED, int HALF>
+__device__ __forceinline__ void sh_views_half(int idx, int P, int D, int ncoef, float mx, float my, float mz, int K,
+                                              const float* __restrict__ cams, const float* __restrict__ g_all,
+                                              const uint32_t* __restrict__ meta, int meta_stride, int W32, int cap, float* row, int L) {
+    float acc[24];
+#pragma unroll
+    for (int i = 0; i < 24; ++i) acc[i] = 0.f;
+    for (int v = 0; v < K; ++v) {
+        const float* g;
+        if (PACKED) {
+            const uint32_t* mv = meta + (size_t)v * meta_stride;
+            const uint32_t word = __ldg(mv + (idx >> 5));
+            if (!((word >> (idx & 31)) & 1u)) continue;
+            const uint32_t slot = __ldg(mv + W32 + (idx >> 5)) + __popc(word & ((1u << (idx & 31)) - 1u));
+            if (slot >= (uint32_t)cap) continue;                    // cannot happen with a consistent pack; never read out of bounds
+            g = g_all + ((size_t)v * cap + slot) * 3;
+        } else {
+            g = g_all + ((size_t)v * P + idx) * 3;
+        }
+        const float g0 = __ldg(g), g1 = __ldg(g + 1), g2 = __ldg(g + 2);
+        if (g0 == 0.f && g1 == 0.f && g2 == 0.f) continue;          // culled or fully clamped in this view
+        const float ox = mx - __ldg(cams + 3 * v), oy = my - __ldg(cams + 3 * v + 1), oz = mz - __ldg(cams + 3 * v + 2);
+        const float inv_len = 1.f / sqrtf(ox * ox + oy * oy + oz * oz);
+        const float x = ox * inv_len, y = oy * inv_len, z = oz * inv_len;
+        float w[8];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) w[k] = 0.f;
+        const float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
+        if (HALF == 0) {
+            w[0] = kSH_C0;
+            if (D > 0) {
+                w[1] = -kSH_C1 * y; w[2] = kSH_C1 * z; w[3] = -kSH_C1 * x;
+                if (D > 1) { w[4] = kSH_C2_0 * xy; w[5] = kSH_C2_1 * yz; w[6] = kSH_C2_2 * (2.f * zz - xx - yy); w[7] = kSH_C2_3 * xz; }
+            }
+        } else {
+            if (D > 1) {
+                w[0] = kSH_C2_4 * (xx - yy);
+                if (D > 2) {
+                    w[1] = kSH_C3_0 * y * (3.f * xx - yy);
+                    w[2] = kSH_C3_1 * xy * z;
+                    w[3] = kSH_C3_2 * y * (4.f * zz - xx - yy);
+                    w[4] = kSH_C3_3 * z * (2.f * zz - 3.f * xx - 3.f * yy);
+                    w[5] = kSH_C3_4 * x * (4.f * zz - xx - yy);
+                    w[6] = kSH_C3_5 * z * (xx - yy);
+                    w[7] = kSH_C3_6 * x * (xx - 3.f * yy);
+                }
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            const float wk = (8 * HALF + k) < ncoef ? w[k] : 0.f;
+            // product first, then the sum over views: one view reproduces preprocess_bwd_kernel's rows bit for bit
+            acc[3 * k] += wk * g0; acc[3 * k + 1] += wk * g1; acc[3 * k + 2] += wk * g2;
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < 24; ++i) if (24 * HALF + i < L) row[24 * HALF + i] = acc[i];
+}
+
 template <bool PACKED>
-__global__ void __launch_bounds__(256) sh_grad_from_views_kernel(int P, int D, int M, const float* __restrict__ means3D, int K,
-                                                                 const float* __restrict__ cams, const float* __restrict__ g_all,
-                                                                 const uint32_t* __restrict__ meta, int meta_stride, int W32, int cap,
-                                                                 float* __restrict__ dL_dsh) {
+__global__ void __launch_bounds__(256, 4) sh_grad_from_views_kernel(int P, int D, int M, const float* __restrict__ means3D, int K,
+                                                                    const float* __restrict__ cams, const float* __restrict__ g_all,
+                                                                    const uint32_t* __restrict__ meta, int meta_stride, int W32, int cap,
+                                                                    float* __restrict__ dL_dsh) {
     extern __shared__ float s_rows[];            // [256][kShStride]
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const int idx = blockIdx.x * 256 + tid;
     const bool valid = idx < P;
     const int ncoef = min(16, min(M, (D + 1) * (D + 1)));
-    float acc[48];
-#pragma unroll
-    for (int i = 0; i < 48; ++i) acc[i] = 0.f;
-    if (valid) {
-        const float mx = __ldg(means3D + 3 * (size_t)idx), my = __ldg(means3D + 3 * (size_t)idx + 1), mz = __ldg(means3D + 3 * (size_t)idx + 2);
-        for (int v = 0; v < K; ++v) {
-            const float* g;
-            if (PACKED) {
-                const uint32_t* mv = meta + (size_t)v * meta_stride;
-                const uint32_t word = __ldg(mv + (idx >> 5));
-                if (!((word >> (idx & 31)) & 1u)) continue;
-                const uint32_t slot = __ldg(mv + W32 + (idx >> 5)) + __popc(word & ((1u << (idx & 31)) - 1u));
-                if (slot >= (uint32_t)cap) continue;                    // cannot happen with a consistent pack; never read out of bounds
-                g = g_all + ((size_t)v * cap + slot) * 3;
-            } else {
-                g = g_all + ((size_t)v * P + idx) * 3;
-            }
-            const float g0 = __ldg(g), g1 = __ldg(g + 1), g2 = __ldg(g + 2);
-            if (g0 == 0.f && g1 == 0.f && g2 == 0.f) continue;          // culled or fully clamped in this view
-            const float ox = mx - __ldg(cams + 3 * v), oy = my - __ldg(cams + 3 * v + 1), oz = mz - __ldg(cams + 3 * v + 2);
-            const float inv_len = 1.f / sqrtf(ox * ox + oy * oy + oz * oz);
-            const float x = ox * inv_len, y = oy * inv_len, z = oz * inv_len;
-            float w[16];
-            w[0] = kSH_C0;
-#pragma unroll
-            for (int k = 1; k < 16; ++k) w[k] = 0.f;
-            if (D > 0) {
-                w[1] = -kSH_C1 * y; w[2] = kSH_C1 * z; w[3] = -kSH_C1 * x;
-                if (D > 1) {
-                    const float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
-                    w[4] = kSH_C2_0 * xy; w[5] = kSH_C2_1 * yz; w[6] = kSH_C2_2 * (2.f * zz - xx - yy);
-                    w[7] = kSH_C2_3 * xz; w[8] = kSH_C2_4 * (xx - yy);
-                    if (D > 2) {
-                        w[9] = kSH_C3_0 * y * (3.f * xx - yy);
-                        w[10] = kSH_C3_1 * xy * z;
-                        w[11] = kSH_C3_2 * y * (4.f * zz - xx - yy);
-                        w[12] = kSH_C3_3 * z * (2.f * zz - 3.f * xx - 3.f * yy);
-                        w[13] = kSH_C3_4 * x * (4.f * zz - xx - yy);
-                        w[14] = kSH_C3_5 * z * (xx - yy);
-                        w[15] = kSH_C3_6 * x * (xx - 3.f * yy);
-                    }
-                }
-            }
-#pragma unroll
-            for (int k = 0; k < 16; ++k) {
-                const float wk = k < ncoef ? w[k] : 0.f;
-                // product first, then the sum over views: one view reproduces preprocess_bwd_kernel's rows bit for bit
-                acc[3 * k] += wk * g0; acc[3 * k + 1] += wk * g1; acc[3 * k + 2] += wk * g2;
-            }
-        }
-    }
     const int L = 3 * M;
     float* row = s_rows + tid * kShStride;
-#pragma unroll
-    for (int i = 0; i < 48; ++i) if (i < L) row[i] = acc[i];
+    if (valid) {
+        const float mx = __ldg(means3D + 3 * (size_t)idx), my = __ldg(means3D + 3 * (size_t)idx + 1), mz = __ldg(means3D + 3 * (size_t)idx + 2);
+        sh_views_half<PACKED, 0>(idx, P, D, ncoef, mx, my, mz, K, cams, g_all, meta, meta_stride, W32, cap, row, L);
+        if (L > 24) sh_views_half<PACKED, 1>(idx, P, D, ncoef, mx, my, mz, K, cams, g_all, meta, meta_stride, W32, cap, row, L);
+    }
     __syncwarp();
     const int warp_idx0 = blockIdx.x * 256 + wid * 32;
     const int nrows = min(32, P - warp_idx0);

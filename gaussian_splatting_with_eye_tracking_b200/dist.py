@@ -323,7 +323,9 @@ class ShGradExchange:
         if self.fused and (peer is None or not peer.rows_per_rank):
             raise RuntimeError("ShGradExchange(fused=True) needs a PeerAllReduce with staging_gaussians=P")
         self._owner_sum_queued = False
-        self.rebuild_early = self.fused        # where the SH rebuild runs (see _start_gather_packed / finish_sh)
+        # where the SH rebuild runs (see _start_gather_packed / finish_sh).  Measured at 6 M, N = 2: beside the preprocess-stage
+        # backward it doubles that kernel's time (both stream from HBM), behind it it costs its own 0.2-0.36 ms -- behind wins.
+        self.rebuild_early = False
         self._dsh_early = None
         self._dsh_bufs = None
         self._dsh_flip = 0

@@ -69,13 +69,13 @@ def main():
     n1 = torch.tensor([e0.elapsed_time(e1) / a.iters], device=dev)
     dist.all_reduce(n1, op=dist.ReduceOp.MAX)
     peer = gdist.PeerAllReduce(11 * ((P + 3) // 4 * 4), dev, staging_gaussians=P)
-    variants = {"fused_push": dict(fused=True, peer=peer), "fused_push_late_rebuild": dict(fused=True, peer=peer),
+    variants = {"fused_push": dict(fused=True, peer=peer), "fused_push_early_rebuild": dict(fused=True, peer=peer),
                 "peer_sum": dict(fused=False, peer=peer), "nccl_sum": dict(fused=False, peer=None)}
     out = {"world": world, "gaussians": P, "multicast": bool(peer.multicast_ptr), "no_exchange_ms_per_step": round(float(n1), 4)}
     for name, kw in variants.items():
         exch = gdist.ShGradExchange(packed=True, **kw)
-        if name.endswith("late_rebuild"):
-            exch.rebuild_early = False             # A/B: the SH rebuild behind the backward instead of beside it
+        if name.endswith("early_rebuild"):
+            exch.rebuild_early = True              # A/B: the SH rebuild beside the backward instead of behind it
 
         def step(tl=None):
             def mark(name, stream=None):
