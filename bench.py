@@ -46,9 +46,10 @@ FP32_INSTR_PER_PAIR_TEST = 20         # forward: one pixel x one examined list e
 FP32_INSTR_PER_HIT_BWD = 55           # backward: one pair-test that passes both skips (+ 1 MUFU, 9 reductions)
 
 
-# dram__bytes_read.sum + dram__bytes_write.sum of one preprocess_fwd_kernel launch from the committed `ncu --set full`
-# capture (profiles/r1_v11_ncu_full_preprocess_summary.csv; camera 0 of the C3 workload), keyed by the Gaussian count
-NCU_TRAFFIC_BYTES = {3_000_000: 448_445_696 + 221_628_160}
+# dram__bytes_read.sum + dram__bytes_write.sum of one launch from the committed `ncu --set full` capture
+# (profiles/r2_ncu_full_step_summary.csv; camera 0 of the C3 workload), keyed by the Gaussian count
+NCU_TRAFFIC_BYTES = {3_000_000: 452_450_816 + 247_781_120}           # preprocess_fwd_kernel
+NCU_BLEND_TRAFFIC_BYTES = {3_000_000: 45_811_712 + 5_523_712}        # blend_fwd2_kernel
 
 
 def parse_args():
@@ -1118,7 +1119,7 @@ def main():
             ach_f = bw["pair_tests_fwd"] * FP32_INSTR_PER_PAIR_TEST / (st["blend"] * 1e-3) / 1e9
             line["roofline"] = {"kernel": "blend_fwd2_kernel (per-tile front-to-back alpha blending; one launch per step; largest share of the step)",
                                 "bound": "fp32", "achieved": ach_f / 1e3, "peak": peak_lanes / 1e3, "unit": "T lane-instr/s", "frac": ach_f / peak_lanes,
-                                "traffic": None, "launch_ms": st["blend"], "share_of_step": st["blend"] / m["ms_per_step"],
+                                "traffic": NCU_BLEND_TRAFFIC_BYTES.get(args.gaussians), "launch_ms": st["blend"], "share_of_step": st["blend"] / m["ms_per_step"],
                                 "pair_tests_per_launch": bw["pair_tests_fwd"], "hits_per_launch": bw["hits"],
                                 "fp32_instr_per_pair_test": FP32_INSTR_PER_PAIR_TEST,
                                 "peak_source": f"{sm_count} SMs x 128 FP32 lanes x {f_sm_ghz} GHz (cudaGetDeviceProperties SM count, max SM clock)",
