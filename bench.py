@@ -1036,14 +1036,15 @@ def main():
         # barrier and the max-over-ranks of the timings.  NCCL's INFO log goes to a per-rank file so that the communicator
         # size is checkable while stdout stays the one JSON line.
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        os.environ.setdefault("NCCL_DEBUG", os.environ.get("GSR_NCCL_DEBUG", "INFO"))
-        os.environ.setdefault("NCCL_DEBUG_SUBSYS", "INIT")
-        log_dir = os.path.join(ROOT, "gpurun_out")
-        try:
-            os.makedirs(log_dir, exist_ok=True)
-            os.environ.setdefault("NCCL_DEBUG_FILE", os.path.join(log_dir, f"nccl_{args.impl}_n{world}_rank%h_%p.log"))
-        except OSError:
-            pass
+        # (forced, not setdefault: the N = 2 / N = 8 runs of round 2 showed a preset NCCL_DEBUG on the boxes, under which no INFO
+        # line was written anywhere.  Default sink = stderr -- fd 1 already points there, claim_stdout -- where whoever launched
+        # the bench captures it; GSR_NCCL_DEBUG_FILE=<path with %h %p> sends it to per-rank files instead.)
+        os.environ["NCCL_DEBUG"] = os.environ.get("GSR_NCCL_DEBUG", "INFO")
+        os.environ["NCCL_DEBUG_SUBSYS"] = os.environ.get("GSR_NCCL_DEBUG_SUBSYS", "INIT")
+        if os.environ.get("GSR_NCCL_DEBUG_FILE"):
+            os.environ["NCCL_DEBUG_FILE"] = os.environ["GSR_NCCL_DEBUG_FILE"]
+        else:
+            os.environ.pop("NCCL_DEBUG_FILE", None)
         if args.impl == "ours":
             from gaussian_splatting_with_eye_tracking_b200 import dist as gdist_
             dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank), pg_options=gdist_.nccl_options())
