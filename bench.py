@@ -1033,8 +1033,8 @@ def main():
     if world > 1:
         # one process per GPU for BOTH arms: ours exchanges gradients over NCCL in the training legs; the reference arm runs N
         # independent replicas (the reference has no multi-GPU path, hence no collective) and uses the group only for the
-        # barrier and the max-over-ranks of the timings.  NCCL's INFO log goes to a per-rank file so that the communicator
-        # size is checkable while stdout stays the one JSON line.
+        # barrier and the max-over-ranks of the timings.  NCCL's INFO log (communicator size, transports) goes to stderr while
+        # stdout stays the one JSON line.
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         # (forced, not setdefault: the N = 2 / N = 8 runs of round 2 showed a preset NCCL_DEBUG on the boxes, under which no INFO
         # line was written anywhere.  Default sink = stderr -- fd 1 already points there, claim_stdout -- where whoever launched
