@@ -139,7 +139,9 @@ typedef struct gsr_grads {
      * that both hold push_epoch.  A line is written by 8 lanes of one store instruction and arrives whole, so it validates
      * itself: gsr_peer_owner_sum -- queued on another stream BEFORE this backward, so that it runs beside it -- re-reads a
      * line until its flag is the epoch, sums every block in rank order and delivers the totals to all ranks.  No fence, no
-     * kernel boundary between producer and consumer.  push_rows_per_rank must be a multiple of 256, push_offset of 128;
+     * kernel boundary between producer and consumer.  Relies on an aligned 128-byte line written by one warp store instruction
+     * becoming visible whole -- true within a GPU and over NVLink (what NCCL's LL128 protocol relies on), NOT over PCIe: use it
+     * between NVLink peers only.  push_rows_per_rank must be a multiple of 256, push_offset of 128;
      * epochs only grow and are never 0. */
     void* const* push_bases;   /* DEVICE array of `push_world` peer-mapped base pointers (as for gsr_peer_allreduce_sum) */
     size_t push_offset;        /* byte offset of the staging area inside every rank's buffer, 128-byte aligned */
