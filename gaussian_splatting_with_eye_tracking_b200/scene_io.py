@@ -12,10 +12,21 @@
 * ``camera_to_json`` / ``cameras_from_json`` <- ``camera_to_JSON`` (utils/camera_utils.py:62-81) and the matrices a
   ``Camera`` derives from R, T, FoV (scene/cameras.py:47-57, utils/graphics_utils.py:38-76).
 
+* ``format_cfg_args`` / ``parse_cfg_args`` / ``read_cfg_args`` / ``combine_args`` <- the ``cfg_args`` file of a trained model
+  directory: written by train.py:142-143 as ``str(Namespace(**vars(args)))``, read back by ``get_combined_args``
+  (arguments/__init__.py:91-111) with ``eval`` and merged under the command line (a command-line value wins unless it is
+  None).  Here the text is parsed with ``ast`` (a ``Namespace(...)`` call of literal keyword values and nothing else), never
+  evaluated.
+* ``search_for_max_iteration`` / ``point_cloud_file`` / ``resolve_iteration`` <- the model-directory layout
+  (scene/__init__.py:43-87 ``Scene.__init__`` / ``save``, utils/system_utils.py:26-28):
+  ``<model>/point_cloud/iteration_<N>/point_cloud.ply``, ``load_iteration = -1`` = the largest N present.
+
 No CUDA here: this is file IO; tensors are created on the device the caller names.
 """
 from __future__ import annotations
 
+import argparse
+import ast
 import json
 import math
 import os
@@ -225,3 +236,84 @@ def cameras_from_json(path: str, device="cpu", ids: Optional[Sequence[int]] = No
         want = set(ids)
         entries = [e for e in entries if e["id"] in want]
     return [camera_from_json(e, device=device) for e in entries]
+
+
+# ------------------------------------------------------------------------------------------------
+# cfg_args and the model-directory layout
+# ------------------------------------------------------------------------------------------------
+def format_cfg_args(args) -> str:
+    """The text train.py:142-143 writes into ``<model>/cfg_args``: ``str(Namespace(**vars(args)))``.  ``args``: a Namespace or a dict."""
+    d = dict(args) if isinstance(args, dict) else dict(vars(args))
+    return str(argparse.Namespace(**d))
+
+
+def write_cfg_args(model_path: str, args) -> str:
+    os.makedirs(model_path, exist_ok=True)
+    path = os.path.join(model_path, "cfg_args")
+    with open(path, "w") as f:
+        f.write(format_cfg_args(args))
+    return path
+
+
+def parse_cfg_args(text: str) -> Dict[str, object]:
+    """``Namespace(k=v, ...)`` -> {k: v}.  The reference ``eval``s the file (arguments/__init__.py:104); here only a call of the
+    name ``Namespace`` with keyword arguments whose values are Python literals (numbers, strings, None, booleans, lists, tuples,
+    dicts of those) is accepted -- anything else raises ValueError and nothing is ever executed."""
+    try:
+        node = ast.parse(text.strip(), mode="eval").body
+    except SyntaxError as ex:
+        raise ValueError(f"cfg_args: not a Namespace(...) expression ({ex.msg})") from None
+    if not (isinstance(node, ast.Call) and isinstance(node.func, ast.Name) and node.func.id == "Namespace" and not node.args):
+        raise ValueError("cfg_args: expected Namespace(key=value, ...)")
+    out: Dict[str, object] = {}
+    for kw in node.keywords:
+        try:
+            val = ast.literal_eval(kw.value)
+        except (ValueError, SyntaxError):
+            raise ValueError(f"cfg_args: value of {kw.arg or '**'} is not a literal") from None
+        if kw.arg is None:                          # Namespace's repr puts non-identifier keys into a trailing **{...}
+            if not isinstance(val, dict):
+                raise ValueError("cfg_args: ** argument must be a dict literal")
+            out.update(val)
+        else:
+            out[kw.arg] = val
+    return out
+
+
+def read_cfg_args(model_path: Optional[str]) -> Dict[str, object]:
+    """{} when ``model_path`` is None (the reference swallows exactly that case, arguments/__init__.py:101-103); a model path
+    without the file raises FileNotFoundError like the reference's ``open``."""
+    if model_path is None:
+        return {}
+    with open(os.path.join(model_path, "cfg_args")) as f:
+        return parse_cfg_args(f.read())
+
+
+def combine_args(cmdline, cfg) -> argparse.Namespace:
+    """get_combined_args' merge (arguments/__init__.py:106-110): start from the file, every command-line entry whose value is
+    not None overrides -- including False / 0 / '' (a store_true flag absent from the command line therefore wins over the
+    file, as in the reference; its render scripts build ModelParams with sentinel=True so that those defaults ARE None)."""
+    merged = dict(cfg) if isinstance(cfg, dict) else dict(vars(cfg))
+    for k, v in (cmdline.items() if isinstance(cmdline, dict) else vars(cmdline).items()):
+        if v != None:          # noqa: E711  (the reference's comparison, kept: an object with a custom __eq__ behaves the same)
+            merged[k] = v
+    return argparse.Namespace(**merged)
+
+
+def search_for_max_iteration(folder: str) -> int:
+    """utils/system_utils.py:26-28: the largest <N> among the entries ``..._<N>`` of ``folder``."""
+    return max(int(name.split("_")[-1]) for name in os.listdir(folder))
+
+
+def resolve_iteration(model_path: str, load_iteration: Optional[int]) -> Optional[int]:
+    """Scene.__init__ (scene/__init__.py:43-48): None / 0 = nothing to load, -1 = the newest saved iteration, else as given."""
+    if not load_iteration:
+        return None
+    if load_iteration == -1:
+        return search_for_max_iteration(os.path.join(model_path, "point_cloud"))
+    return int(load_iteration)
+
+
+def point_cloud_file(model_path: str, iteration: int) -> str:
+    """Where Scene.save puts / Scene.__init__ finds the Gaussians (scene/__init__.py:77-87)."""
+    return os.path.join(model_path, "point_cloud", "iteration_" + str(iteration), "point_cloud.ply")

@@ -134,3 +134,63 @@ def test_cameras_json_matches_the_reference(tmp_path):
         np.testing.assert_allclose(c.camera_center.numpy(), m[f"center_{i}"], rtol=0, atol=1e-5)
         assert abs(c.FoVx - m[f"fov_{i}"][0]) < 1e-12 and abs(c.FoVy - m[f"fov_{i}"][1]) < 1e-12
     assert [c.image_width for c in scene_io.cameras_from_json(path, ids=[2])] == [ref_entries[2]["width"]]
+
+
+# ------------------------------------------------------------------------------------------------
+# cfg_args + model-directory layout, pinned on tests/golden/cfg_args.json = outputs of the reference's own
+# arguments/__init__.py, train.py:142-143 and utils/system_utils.py run by tests/golden/make_cfg_args_golden.py
+# ------------------------------------------------------------------------------------------------
+def _cfg_golden():
+    import json
+    import os
+    with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "cfg_args.json")) as f:
+        return json.load(f)
+
+
+def test_cfg_args_text_parse_and_merge_match_the_reference():
+    from gaussian_splatting_with_eye_tracking_b200 import scene_io
+    g = _cfg_golden()
+    assert len(g["cases"]) == 4
+    for case in g["cases"]:
+        parsed = scene_io.parse_cfg_args(case["cfg_text"])
+        assert parsed == case["parsed"]                                   # what the reference's eval() yields
+        assert list(parsed) == list(scene_io.parse_cfg_args(case["cfg_text"]))
+        assert scene_io.format_cfg_args(parsed) == case["cfg_text"]      # and the exact text train.py writes, key order included
+        merged = vars(scene_io.combine_args(case["cmdline"], parsed))
+        assert merged == case["merged"]
+    # the quirk the merge keeps: a False from the command line overrides a True in the file, a None does not
+    m = vars(scene_io.combine_args({"eval": False, "sh_degree": None}, {"eval": True, "sh_degree": 2}))
+    assert m == {"eval": False, "sh_degree": 2}
+
+
+def test_cfg_args_file_round_trip_and_directory_layout(tmp_path):
+    import argparse
+    import os
+    import pytest
+    from gaussian_splatting_with_eye_tracking_b200 import scene_io
+    g = _cfg_golden()
+    model = str(tmp_path / "out" / "m1")
+    ns = argparse.Namespace(**scene_io.parse_cfg_args(g["cases"][0]["cfg_text"]))      # (the fixture's dicts are key-sorted by json)
+    path = scene_io.write_cfg_args(model, ns)
+    assert os.path.basename(path) == "cfg_args" and open(path).read() == g["cases"][0]["cfg_text"]
+    assert scene_io.read_cfg_args(model) == g["cases"][0]["parsed"]
+    assert scene_io.read_cfg_args(None) == {}
+    with pytest.raises(FileNotFoundError):
+        scene_io.read_cfg_args(str(tmp_path / "nowhere"))
+    for name in g["iteration_dirs"]:
+        os.makedirs(os.path.join(model, "point_cloud", name))
+    assert scene_io.search_for_max_iteration(os.path.join(model, "point_cloud")) == g["max_iteration"]
+    assert scene_io.resolve_iteration(model, -1) == g["max_iteration"]
+    assert scene_io.resolve_iteration(model, None) is None and scene_io.resolve_iteration(model, 7000) == 7000
+    assert scene_io.point_cloud_file(model, 30000) == os.path.join(model, "point_cloud", "iteration_30000", "point_cloud.ply")
+
+
+def test_cfg_args_parser_never_executes_anything():
+    import pytest
+    from gaussian_splatting_with_eye_tracking_b200 import scene_io
+    for bad in ("__import__('os').system('true')", "Namespace(a=__import__('os'))", "Namespace(a=open('x'))", "Namespace(1)",
+                "print(1)", "Namespace(a=1); x=2", "Other(a=1)", "Namespace(a=[i for i in range(3)])", ""):
+        with pytest.raises(ValueError):
+            scene_io.parse_cfg_args(bad)
+    assert scene_io.parse_cfg_args("Namespace(a=1, b=[1, 2], c=None, d='x', **{'e f': -2.5})") == {"a": 1, "b": [1, 2], "c": None, "d": "x", "e f": -2.5}
+    assert scene_io.parse_cfg_args("Namespace()") == {}
